@@ -1,0 +1,186 @@
+/* libtcd -- C ABI of the B200-native per-frame detection hot path.
+ *
+ * The reference (filthyrake/telescope_cam_detection) is 100 % Python and has no FFI; its
+ * boundary for this path is the Python class surface.  The package
+ * telescope_cam_detection_b200 re-creates those classes and marshals into the entry points
+ * below through ctypes.  Every entry point names the reference code it replaces.
+ *
+ * Conventions: extern "C", opaque handles, plain pointers and sizes, int status
+ * (0 = TCD_OK), a thread-local last-error string, caller-provided CUDA stream (void*,
+ * NULL = the handle's own stream).  No hidden allocation after create.  There is no CPU
+ * fallback: every compute entry fails with TCD_ERR_CUDA when no sm_100 device is present.
+ */
+#ifndef TCD_H_
+#define TCD_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef enum {
+  TCD_OK = 0,
+  TCD_ERR_INVALID = 1,
+  TCD_ERR_CUDA = 2,
+  TCD_ERR_NOMEM = 3,
+  TCD_ERR_UNSUPPORTED = 4
+} tcd_status;
+
+const char* tcd_last_error(void);
+int tcd_version(void);
+/* number of kernels this library has launched in this process (bench.py gpu_launches) */
+uint64_t tcd_launch_count(void);
+
+/* ------------------------------------------------------------------ preprocess (K1+K2)
+ * Replaces YOLOXDetector.preprocess, src/yolox_detector.py:186-220 (HWC u8 -> float,
+ * bilinear stretch, align_corners=False, no antialias) and, with other settings,
+ * SpeciesClassifier.preprocess src/species_classifier.py:298-352.                      */
+typedef struct {
+  int32_t out_h, out_w;   /* network input size (640, 640)                                */
+  int32_t mode;           /* 0 = stretch (what the reference code does), 1 = letterbox    */
+  int32_t swap_rb;        /* 0 = keep BGR (reference), 1 = BGR->RGB                       */
+  float scale;            /* multiplied in before mean/std (1.0 reference; 1/255 typical) */
+  float mean[3];          /* subtracted after scale, per OUTPUT channel                   */
+  float inv_std[3];       /* multiplied after the subtraction                             */
+  float pad_value;        /* letterbox fill (114)                                         */
+} tcd_preproc_cfg;
+
+/* frames[b]: HWC u8 with row stride row_stride[b] bytes, on the device.
+ * out_layout 0: f32 NCHW [B,3,out_h,out_w]                (parity layout, = reference)
+ * out_layout 1: bf16 space-to-depth NHWC [B,out_h/2,out_w/2,16] (Focus stem input:
+ *               channels = TL,BL,TR,BR patches x 3, 4 zero pad channels)                 */
+tcd_status tcd_preprocess(const tcd_preproc_cfg* cfg, const uint8_t* const* frames,
+                          const int32_t* h, const int32_t* w, const int64_t* row_stride, int32_t B,
+                          int32_t out_layout, void* out_dev, void* stream);
+
+/* ------------------------------------------------------------------ conv engine (K3)
+ * One BaseConv / Conv2d of the detector: implicit GEMM on tcgen05 with TMA-fed operands,
+ * folded-BN bias + optional SiLU + optional residual in the epilogue.  Exposed for the
+ * per-layer parity tests; the detector below owns the full layer plan.
+ * x: bf16 NHWC [N,H,W,x_ctot] (device), reads channels [x_coff, x_coff+cin).
+ * w: f32 [cout,cin,k,k] and bias f32 [cout] on the HOST (packed per call: test entry).
+ * y: bf16 NHWC [N,Ho,Wo,y_ctot] (device), writes channels [y_coff, y_coff+cout).
+ * resid (optional, device): bf16 NHWC [N,Ho,Wo,r_ctot], channels [r_coff, r_coff+cout).  */
+tcd_status tcd_conv2d_nhwc_bf16(const void* x, int32_t N, int32_t H, int32_t W, int32_t x_ctot,
+                                int32_t x_coff, int32_t cin, const float* w, const float* bias,
+                                int32_t cout, int32_t k, int32_t stride, int32_t silu,
+                                const void* resid, int32_t r_ctot, int32_t r_coff, void* y,
+                                int32_t y_ctot, int32_t y_coff, void* stream);
+
+/* ------------------------------------------------------------------ detector (A1-A5)
+ * Replaces YOLOXDetector.load_model / detect / detect_batch, src/yolox_detector.py:84-184,
+ * 284-406 together with upstream YOLOX-S forward and yolox.utils.postprocess.            */
+typedef struct tcd_detector tcd_detector;
+
+typedef struct {
+  int32_t input_h, input_w;   /* multiples of 32; 640x640 for BASELINE                    */
+  int32_t max_batch;          /* frames per detect_batch call the arena is sized for      */
+  int32_t num_classes;        /* 80                                                       */
+  int32_t max_out;            /* rows per frame in the result table                       */
+  int32_t max_src_h, max_src_w; /* largest camera frame (staging buffer for host frames)  */
+  tcd_preproc_cfg pre;        /* out_h/out_w ignored (taken from input_h/input_w)         */
+} tcd_detector_cfg;
+
+/* packed_weights: blob written by telescope_cam_detection_b200.weights.pack_yolox()
+ * (BN already folded, fp32, canonical layer order; layout documented in DESIGN.md).      */
+tcd_status tcd_create_detector(const tcd_detector_cfg* cfg, const void* packed_weights,
+                               size_t packed_bytes, int32_t device, tcd_detector** out);
+void tcd_destroy_detector(tcd_detector* det);
+
+/* conf / nms thresholds of yolox.utils.postprocess (src/yolox_detector.py:309-314);
+ * cheap, lock-free for the caller, never re-captures a CUDA graph.                       */
+tcd_status tcd_detector_set_thresholds(tcd_detector* det, float conf_thre, float nms_thre);
+
+/* frames[b]: HWC u8 BGR.  frames_on_device = 0: host pointers (pinned or pageable), the
+ * H2D copy is part of the call; 1: device pointers.  out_dets: HOST [B,max_out,7] f32 rows
+ * [x1,y1,x2,y2,obj_conf,class_conf,class_id] in network-input pixel units, score-descending
+ * exactly like postprocess(); out_counts: HOST [B] int32 (rows kept, clamped to max_out).
+ * Synchronous on return (results are in host memory).                                    */
+tcd_status tcd_detect_batch(tcd_detector* det, const uint8_t* const* frames, const int32_t* h,
+                            const int32_t* w, const int64_t* row_stride, int32_t B,
+                            int32_t frames_on_device, float* out_dets, int32_t* out_counts);
+
+/* Split-phase variant used by the pipelined coordinator / bench: enqueue on the handle's
+ * stream `slot` (0 or 1), then wait.  H2D of batch k+1 overlaps compute of batch k.      */
+tcd_status tcd_detect_batch_async(tcd_detector* det, int32_t slot, const uint8_t* const* frames,
+                                  const int32_t* h, const int32_t* w, const int64_t* row_stride,
+                                  int32_t B, int32_t frames_on_device);
+tcd_status tcd_detect_batch_wait(tcd_detector* det, int32_t slot, float* out_dets,
+                                 int32_t* out_counts);
+
+/* Parity taps: run preprocess+network only and copy the decoded head output
+ * [B,n_anchors,5+num_classes] f32 (what upstream YOLOX.forward returns in eval) to HOST. */
+tcd_status tcd_forward(tcd_detector* det, const uint8_t* const* frames, const int32_t* h,
+                       const int32_t* w, const int64_t* row_stride, int32_t B,
+                       int32_t frames_on_device, float* out_pred_host);
+/* postprocess only, on a caller-supplied decoded prediction (HOST f32 [B,A,5+C]).        */
+tcd_status tcd_postprocess(tcd_detector* det, const float* pred_host, int32_t B, float* out_dets,
+                           int32_t* out_counts);
+int32_t tcd_detector_num_anchors(const tcd_detector* det);
+/* per-phase device times of the last synchronous detect_batch, ms:
+ * [0]=h2d [1]=preprocess [2]=network [3]=decode+nms [4]=d2h                              */
+tcd_status tcd_detector_last_timing(const tcd_detector* det, float out_ms[5]);
+/* debug tap: copy activation buffer `name` (bf16 NHWC) of the last forward to HOST as f32 */
+tcd_status tcd_detector_read_activation(tcd_detector* det, const char* name, float* out_host,
+                                        size_t out_elems, int32_t* shape4);
+
+/* ------------------------------------------------------------------ motion filter (K8+K9)
+ * Replaces cv2.createBackgroundSubtractorMOG2(...).apply + threshold(200) + GaussianBlur
+ * (21x21) + threshold(25) + countNonZero(roi) in MotionFilter.has_motion_in_bbox,
+ * src/motion_filter.py:56-60,68-127.                                                     */
+typedef struct tcd_mog2 tcd_mog2;
+tcd_status tcd_mog2_create(int32_t h, int32_t w, int32_t history, float var_threshold,
+                           int32_t detect_shadows, int32_t device, tcd_mog2** out);
+void tcd_mog2_destroy(tcd_mog2* m);
+tcd_status tcd_mog2_reset(tcd_mog2* m);
+/* One background-model update.  frame: HWC u8 BGR (host or device).  `repeats` >= 1 applies
+ * the same frame that many times (the reference calls apply() once per detection,
+ * src/motion_filter.py:88,161-162); the mask of the LAST apply is kept on the device.
+ * fg_mask_host (optional): raw MOG2 mask {0,127,255}.                                     */
+tcd_status tcd_mog2_apply(tcd_mog2* m, const uint8_t* frame, int64_t row_stride,
+                          int32_t frame_on_device, int32_t repeats, uint8_t* fg_mask_host);
+/* Mask clean-up on the last mask: (mask > shadow_thr) -> blur ksize x ksize (OpenCV u8
+ * fixed-point, REFLECT_101) -> (> blur_thr), then countNonZero inside each clamped integer
+ * ROI (x1,y1,x2,y2).  ksize == 0 skips the blur (motion_blur_size <= 0).
+ * clean_mask_host (optional): the cleaned 0/255 mask.                                    */
+tcd_status tcd_mog2_roi_counts(tcd_mog2* m, int32_t shadow_thr, int32_t ksize, int32_t blur_thr,
+                               const int32_t* rois, int32_t n_rois, int32_t* counts_host,
+                               uint8_t* clean_mask_host);
+
+/* ------------------------------------------------------------------ empty-frame gate (K10)
+ * Replaces EmptyFrameFilter.has_motion, src/empty_frame_filter.py:51-98.                 */
+typedef struct tcd_empty_filter tcd_empty_filter;
+tcd_status tcd_empty_filter_create(int32_t h, int32_t w, int32_t blur_size, int32_t device,
+                                   tcd_empty_filter** out);
+void tcd_empty_filter_destroy(tcd_empty_filter* f);
+tcd_status tcd_empty_filter_reset(tcd_empty_filter* f);
+/* changed_pixels_host: count of |cur-prev| > threshold (or -1 on the first frame).       */
+tcd_status tcd_empty_filter_step(tcd_empty_filter* f, const uint8_t* frame, int64_t row_stride,
+                                 int32_t frame_on_device, int32_t threshold,
+                                 int32_t* changed_pixels_host, uint8_t* gray_blur_host);
+
+/* ------------------------------------------------------------------ Stage-2 crops (K13)
+ * Replaces the per-detection slice frame[y1:y2, x1:x2] (src/two_stage_pipeline_yolox.py:289)
+ * + SpeciesClassifier.preprocess (src/species_classifier.py:311-350) for ALL crops of a
+ * frame in one launch.  boxes: HOST int32 [N,4] (x1,y1,x2,y2) already padded + clamped.
+ * out_layout 0: f32 NCHW [N,3,S,S]; 1: bf16 NHWC [N,S,S,4].  out is a DEVICE pointer.     */
+tcd_status tcd_crop_resize(const uint8_t* frame_dev, int32_t h, int32_t w, int64_t row_stride,
+                           const int32_t* boxes_host, int32_t n, int32_t S,
+                           const tcd_preproc_cfg* cfg, int32_t out_layout, void* out_dev,
+                           void* stream);
+
+/* ------------------------------------------------------------------ small utilities    */
+tcd_status tcd_malloc_device(size_t bytes, void** out);
+tcd_status tcd_free_device(void* p);
+tcd_status tcd_malloc_pinned(size_t bytes, void** out);
+tcd_status tcd_free_pinned(void* p);
+tcd_status tcd_memcpy_h2d(void* dst, const void* src, size_t bytes);
+tcd_status tcd_memcpy_d2h(void* dst, const void* src, size_t bytes);
+tcd_status tcd_device_synchronize(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* TCD_H_ */

@@ -1,0 +1,392 @@
+// C ABI glue, part 2: the YOLOX detector handle (preprocess -> network -> decode/NMS).
+// Two independent pipeline slots (own stream, staging, activation arena, CUDA graph, pinned
+// result table) let the H2D copy of batch k+1 overlap the compute of batch k.
+#include <map>
+#include <string.h>
+#include <vector>
+
+#include "kernels.cuh"
+#include "yolox_net.cuh"
+
+using namespace tcd;
+
+namespace {
+
+struct Slot {
+  cudaStream_t stream = nullptr;
+  uint8_t* staging = nullptr;     // device, max_batch frames of max_src bytes
+  size_t frame_cap = 0;
+  PreFrame* pre_dev = nullptr;    // device [max_batch]
+  PreFrame* pre_host = nullptr;   // pinned [max_batch]
+  std::map<int, YoloxPlan*> plans;
+  std::map<int, cudaGraphExec_t> graphs;
+  // postprocess buffers (sized for max_batch)
+  PostBuffers pb;
+  float* thr_dev = nullptr;
+  float* out_pinned = nullptr;    // [max_batch,max_out,7]
+  int* cnt_pinned = nullptr;      // [max_batch]
+  float* pred_in = nullptr;       // device scratch for tcd_postprocess [max_batch,A,5+C]
+  cudaEvent_t ev[6];
+  int pending_B = 0;
+};
+
+}  // namespace
+
+struct tcd_detector {
+  tcd_detector_cfg cfg;
+  int device = 0;
+  YoloxWeights wts;
+  Slot slot[2];
+  float thr_host[2] = {0.25f, 0.45f};
+  int n_anchors = 0, cap = 0;
+  float last_ms[5] = {0, 0, 0, 0, 0};
+  bool use_graph = true;
+};
+
+static int slot_init(tcd_detector* d, Slot& s) {
+  const tcd_detector_cfg& c = d->cfg;
+  const int MB = c.max_batch;
+  TCD_CUDA_OK(cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking));
+  s.frame_cap = ((size_t)c.max_src_h * c.max_src_w * 3 + 255) & ~(size_t)255;
+  TCD_CUDA_OK(cudaMalloc((void**)&s.staging, s.frame_cap * MB));
+  TCD_CUDA_OK(cudaMalloc((void**)&s.pre_dev, sizeof(PreFrame) * MB));
+  TCD_CUDA_OK(cudaMallocHost((void**)&s.pre_host, sizeof(PreFrame) * MB));
+  const int A = d->n_anchors, C = c.num_classes, cap = d->cap;
+  PostBuffers& pb = s.pb;
+  memset(&pb, 0, sizeof(pb));
+  pb.A = A; pb.C = C; pb.cap = cap; pb.max_out = c.max_out;
+  TCD_CUDA_OK(cudaMalloc((void**)&s.thr_dev, 2 * sizeof(float)));
+  pb.thr = s.thr_dev;
+  TCD_CUDA_OK(cudaMalloc((void**)&pb.cand_count, sizeof(int) * MB));
+  TCD_CUDA_OK(cudaMalloc((void**)&pb.cand, sizeof(float) * 8 * cap * MB));
+  TCD_CUDA_OK(cudaMalloc((void**)&pb.cand_anchor, sizeof(int) * cap * MB));
+  TCD_CUDA_OK(cudaMalloc((void**)&pb.srec, sizeof(float) * 8 * cap * MB));
+  TCD_CUDA_OK(cudaMalloc((void**)&pb.sbox, sizeof(float4) * cap * MB));
+  TCD_CUDA_OK(cudaMalloc((void**)&pb.n_sorted, sizeof(int) * MB));
+  TCD_CUDA_OK(cudaMalloc((void**)&pb.mask, (size_t)MB * cap * (cap / 64) * 8));
+  TCD_CUDA_OK(cudaMalloc((void**)&pb.out_dets, sizeof(float) * 7 * c.max_out * MB));
+  TCD_CUDA_OK(cudaMalloc((void**)&pb.out_counts, sizeof(int) * MB));
+  TCD_CUDA_OK(cudaMalloc((void**)&pb.decoded, sizeof(float) * (size_t)MB * A * (5 + C)));
+  TCD_CUDA_OK(cudaMalloc((void**)&s.pred_in, sizeof(float) * (size_t)MB * A * (5 + C)));
+  TCD_CUDA_OK(cudaMallocHost((void**)&s.out_pinned, sizeof(float) * 7 * c.max_out * MB));
+  TCD_CUDA_OK(cudaMallocHost((void**)&s.cnt_pinned, sizeof(int) * MB));
+  TCD_CUDA_OK(cudaMemcpy(s.thr_dev, d->thr_host, 2 * sizeof(float), cudaMemcpyHostToDevice));
+  for (int i = 0; i < 6; ++i) TCD_CUDA_OK(cudaEventCreate(&s.ev[i]));
+  return TCD_OK;
+}
+
+static void slot_free(Slot& s) {
+  for (auto& kv : s.graphs) cudaGraphExecDestroy(kv.second);
+  for (auto& kv : s.plans) { kv.second->release(); delete kv.second; }
+  PostBuffers& pb = s.pb;
+  void* ptrs[] = {s.staging, s.pre_dev, s.thr_dev, pb.cand_count, pb.cand, pb.cand_anchor, pb.srec,
+                  pb.sbox, pb.n_sorted, pb.mask, pb.out_dets, pb.out_counts, pb.decoded, s.pred_in};
+  for (void* p : ptrs) if (p) cudaFree(p);
+  if (s.pre_host) cudaFreeHost(s.pre_host);
+  if (s.out_pinned) cudaFreeHost(s.out_pinned);
+  if (s.cnt_pinned) cudaFreeHost(s.cnt_pinned);
+  for (int i = 0; i < 6; ++i) if (s.ev[i]) cudaEventDestroy(s.ev[i]);
+  if (s.stream) cudaStreamDestroy(s.stream);
+}
+
+static int get_plan(tcd_detector* d, Slot& s, int B, YoloxPlan** out) {
+  auto it = s.plans.find(B);
+  if (it != s.plans.end()) { *out = it->second; return TCD_OK; }
+  YoloxPlan* p = new YoloxPlan();
+  int rc = p->build(d->wts, B, d->cfg.input_h, d->cfg.input_w);
+  if (rc) { p->release(); delete p; return rc; }
+  s.plans[B] = p;
+  *out = p;
+  return TCD_OK;
+}
+
+static PostBuffers post_for(const Slot& s, const YoloxPlan* p, int B, const float* pred, bool want_decoded) {
+  PostBuffers pb = s.pb;
+  pb.B = B;
+  pb.pred = pred;
+  if (!want_decoded) pb.decoded = nullptr;
+  pb.n_levels = 3;
+  for (int l = 0; l < 3; ++l) {
+    pb.lvl_start[l] = p->lvl_start[l];
+    pb.lvl_w[l] = p->lvl_w[l];
+    pb.lvl_stride[l] = p->lvl_stride[l];
+  }
+  return pb;
+}
+
+// network + postprocess for batch B on the slot's stream (graph-captured once per B)
+static int run_net_post(tcd_detector* d, Slot& s, YoloxPlan* p, int B, bool want_decoded) {
+  if (d->use_graph && !want_decoded) {
+    auto it = s.graphs.find(B);
+    if (it == s.graphs.end()) {
+      cudaGraph_t g = nullptr;
+      TCD_CUDA_OK(cudaStreamBeginCapture(s.stream, cudaStreamCaptureModeThreadLocal));
+      int rc = p->run(s.stream);
+      if (rc == TCD_OK) rc = postproc_launch(post_for(s, p, B, p->pred_raw, false), 1, s.stream);
+      cudaError_t e = cudaStreamEndCapture(s.stream, &g);
+      if (rc) { if (g) cudaGraphDestroy(g); return rc; }
+      if (e != cudaSuccess) {
+        set_last_error("graph capture: %s", cudaGetErrorString(e));
+        return TCD_ERR_CUDA;
+      }
+      cudaGraphExec_t ge = nullptr;
+      e = cudaGraphInstantiate(&ge, g, 0);
+      cudaGraphDestroy(g);
+      if (e != cudaSuccess) {
+        set_last_error("graph instantiate: %s", cudaGetErrorString(e));
+        return TCD_ERR_CUDA;
+      }
+      s.graphs[B] = ge;
+      it = s.graphs.find(B);
+    }
+    TCD_CUDA_OK(cudaGraphLaunch(it->second, s.stream));
+    return TCD_OK;
+  }
+  int rc = p->run(s.stream);
+  if (rc) return rc;
+  return postproc_launch(post_for(s, p, B, p->pred_raw, want_decoded), 1, s.stream);
+}
+
+static int enqueue_input(tcd_detector* d, Slot& s, YoloxPlan* p, const uint8_t* const* frames,
+                         const int32_t* h, const int32_t* w, const int64_t* row_stride, int B,
+                         int on_device) {
+  tcd_preproc_cfg pc = d->cfg.pre;
+  pc.out_h = d->cfg.input_h;
+  pc.out_w = d->cfg.input_w;
+  for (int b = 0; b < B; ++b) {
+    const int64_t st = row_stride ? row_stride[b] : (int64_t)w[b] * 3;
+    const uint8_t* ptr = frames[b];
+    int64_t dst_stride = st;
+    if (!on_device) {
+      const size_t tight = (size_t)w[b] * 3;
+      TCD_REQUIRE((size_t)h[b] * tight <= s.frame_cap, "frame %d (%dx%d) exceeds max_src %dx%d", b, h[b],
+                  w[b], d->cfg.max_src_h, d->cfg.max_src_w);
+      uint8_t* dst = s.staging + (size_t)b * s.frame_cap;
+      if ((size_t)st == tight) {
+        TCD_CUDA_OK(cudaMemcpyAsync(dst, ptr, (size_t)h[b] * tight, cudaMemcpyHostToDevice, s.stream));
+      } else {
+        TCD_CUDA_OK(cudaMemcpy2DAsync(dst, tight, ptr, (size_t)st, tight, (size_t)h[b],
+                                      cudaMemcpyHostToDevice, s.stream));
+      }
+      ptr = dst;
+      dst_stride = (int64_t)tight;
+    }
+    preproc_describe(&pc, ptr, h[b], w[b], dst_stride, &s.pre_host[b]);
+  }
+  TCD_CUDA_OK(cudaEventRecord(s.ev[1], s.stream));
+  TCD_CUDA_OK(cudaMemcpyAsync(s.pre_dev, s.pre_host, sizeof(PreFrame) * B, cudaMemcpyHostToDevice, s.stream));
+  return preproc_launch(&pc, s.pre_host, s.pre_dev, B, 1, p->input, s.stream);
+}
+
+static int check_batch(tcd_detector* det, const uint8_t* const* frames, const int32_t* h,
+                       const int32_t* w, int B) {
+  TCD_REQUIRE(det && frames && h && w, "detect: null argument");
+  TCD_REQUIRE(B >= 1 && B <= det->cfg.max_batch, "detect: batch %d outside [1,%d]", B, det->cfg.max_batch);
+  for (int b = 0; b < B; ++b)
+    TCD_REQUIRE(frames[b] && h[b] > 0 && w[b] > 0, "detect: frame %d is empty", b);
+  return TCD_OK;
+}
+
+extern "C" {
+
+tcd_status tcd_create_detector(const tcd_detector_cfg* cfg, const void* packed_weights,
+                               size_t packed_bytes, int32_t device, tcd_detector** out) {
+  TCD_REQUIRE(cfg && packed_weights && out, "create_detector: null argument");
+  TCD_REQUIRE(cfg->max_batch >= 1 && cfg->max_batch <= 256, "create_detector: max_batch %d", cfg->max_batch);
+  TCD_REQUIRE(cfg->max_out >= 1, "create_detector: max_out %d", cfg->max_out);
+  TCD_CUDA_OK(cudaSetDevice(device));
+  int rc = require_sm100();
+  if (rc) return (tcd_status)rc;
+  tcd_detector* d = new tcd_detector();
+  d->cfg = *cfg;
+  d->device = device;
+  WeightBlob blob;
+  rc = blob.parse(packed_weights, packed_bytes);
+  if (rc == TCD_OK) rc = d->wts.upload(blob);
+  if (rc == TCD_OK && d->wts.num_classes != cfg->num_classes) {
+    set_last_error("create_detector: weights have %d classes, cfg says %d", d->wts.num_classes,
+                   cfg->num_classes);
+    rc = TCD_ERR_INVALID;
+  }
+  if (rc == TCD_OK) {
+    const int H = cfg->input_h, W = cfg->input_w;
+    d->n_anchors = (H / 8) * (W / 8) + (H / 16) * (W / 16) + (H / 32) * (W / 32);
+    int cap = (d->n_anchors + 63) / 64 * 64;
+    if (cap > 8448) cap = 8448;
+    d->cap = cap;
+    if (d->n_anchors >= 131072) {
+      set_last_error("create_detector: %d anchors exceed the sort key range", d->n_anchors);
+      rc = TCD_ERR_UNSUPPORTED;
+    }
+  }
+  for (int i = 0; i < 2 && rc == TCD_OK; ++i) rc = slot_init(d, d->slot[i]);
+  // build the max-batch plan up front so the first frame does not pay for it
+  YoloxPlan* p = nullptr;
+  for (int i = 0; i < 2 && rc == TCD_OK; ++i) rc = get_plan(d, d->slot[i], cfg->max_batch, &p);
+  if (rc) {
+    tcd_destroy_detector(d);
+    return (tcd_status)rc;
+  }
+  const char* ng = getenv("TCD_NO_GRAPH");
+  d->use_graph = !(ng && ng[0] == '1');
+  *out = d;
+  return TCD_OK;
+}
+
+void tcd_destroy_detector(tcd_detector* det) {
+  if (!det) return;
+  cudaSetDevice(det->device);
+  cudaDeviceSynchronize();
+  for (int i = 0; i < 2; ++i) slot_free(det->slot[i]);
+  det->wts.release();
+  delete det;
+}
+
+tcd_status tcd_detector_set_thresholds(tcd_detector* det, float conf_thre, float nms_thre) {
+  TCD_REQUIRE(det, "set_thresholds: null detector");
+  det->thr_host[0] = conf_thre;
+  det->thr_host[1] = nms_thre;
+  for (int i = 0; i < 2; ++i) {
+    // ordered after work already queued on the slot; never touches the captured graphs
+    TCD_CUDA_OK(cudaStreamSynchronize(det->slot[i].stream));
+    TCD_CUDA_OK(cudaMemcpy(det->slot[i].thr_dev, det->thr_host, 2 * sizeof(float), cudaMemcpyHostToDevice));
+  }
+  return TCD_OK;
+}
+
+int32_t tcd_detector_num_anchors(const tcd_detector* det) { return det ? det->n_anchors : 0; }
+
+tcd_status tcd_detect_batch_async(tcd_detector* det, int32_t slot, const uint8_t* const* frames,
+                                  const int32_t* h, const int32_t* w, const int64_t* row_stride,
+                                  int32_t B, int32_t frames_on_device) {
+  int rc = check_batch(det, frames, h, w, B);
+  if (rc) return (tcd_status)rc;
+  TCD_REQUIRE(slot == 0 || slot == 1, "detect: slot %d", slot);
+  Slot& s = det->slot[slot];
+  YoloxPlan* p = nullptr;
+  rc = get_plan(det, s, B, &p);
+  if (rc) return (tcd_status)rc;
+  TCD_CUDA_OK(cudaEventRecord(s.ev[0], s.stream));
+  rc = enqueue_input(det, s, p, frames, h, w, row_stride, B, frames_on_device);
+  if (rc) return (tcd_status)rc;
+  TCD_CUDA_OK(cudaEventRecord(s.ev[2], s.stream));
+  rc = run_net_post(det, s, p, B, false);
+  if (rc) return (tcd_status)rc;
+  TCD_CUDA_OK(cudaEventRecord(s.ev[3], s.stream));
+  TCD_CUDA_OK(cudaMemcpyAsync(s.out_pinned, s.pb.out_dets, sizeof(float) * 7 * det->cfg.max_out * B,
+                              cudaMemcpyDeviceToHost, s.stream));
+  TCD_CUDA_OK(cudaMemcpyAsync(s.cnt_pinned, s.pb.out_counts, sizeof(int) * B, cudaMemcpyDeviceToHost,
+                              s.stream));
+  TCD_CUDA_OK(cudaEventRecord(s.ev[4], s.stream));
+  s.pending_B = B;
+  return TCD_OK;
+}
+
+tcd_status tcd_detect_batch_wait(tcd_detector* det, int32_t slot, float* out_dets, int32_t* out_counts) {
+  TCD_REQUIRE(det && out_dets && out_counts && (slot == 0 || slot == 1), "detect_wait: bad argument");
+  Slot& s = det->slot[slot];
+  TCD_REQUIRE(s.pending_B > 0, "detect_wait: nothing pending on slot %d", slot);
+  TCD_CUDA_OK(cudaStreamSynchronize(s.stream));
+  const int B = s.pending_B;
+  s.pending_B = 0;
+  const size_t row = (size_t)7 * det->cfg.max_out;
+  for (int b = 0; b < B; ++b) {
+    const int n = s.cnt_pinned[b];
+    out_counts[b] = n;
+    memcpy(out_dets + b * row, s.out_pinned + b * row, sizeof(float) * 7 * (size_t)n);
+  }
+  float t;
+  // phases: [0]=h2d (ev0->ev1) [1]=preprocess (ev1->ev2) [2]=network+[3]post (ev2->ev3) [4]=d2h
+  if (cudaEventElapsedTime(&t, s.ev[0], s.ev[1]) == cudaSuccess) det->last_ms[0] = t;
+  if (cudaEventElapsedTime(&t, s.ev[1], s.ev[2]) == cudaSuccess) det->last_ms[1] = t;
+  if (cudaEventElapsedTime(&t, s.ev[2], s.ev[3]) == cudaSuccess) det->last_ms[2] = t;
+  det->last_ms[3] = 0.f;
+  if (cudaEventElapsedTime(&t, s.ev[3], s.ev[4]) == cudaSuccess) det->last_ms[4] = t;
+  return TCD_OK;
+}
+
+tcd_status tcd_detect_batch(tcd_detector* det, const uint8_t* const* frames, const int32_t* h,
+                            const int32_t* w, const int64_t* row_stride, int32_t B,
+                            int32_t frames_on_device, float* out_dets, int32_t* out_counts) {
+  tcd_status rc = tcd_detect_batch_async(det, 0, frames, h, w, row_stride, B, frames_on_device);
+  if (rc) return rc;
+  return tcd_detect_batch_wait(det, 0, out_dets, out_counts);
+}
+
+tcd_status tcd_detector_last_timing(const tcd_detector* det, float out_ms[5]) {
+  TCD_REQUIRE(det && out_ms, "last_timing: null argument");
+  for (int i = 0; i < 5; ++i) out_ms[i] = det->last_ms[i];
+  return TCD_OK;
+}
+
+tcd_status tcd_forward(tcd_detector* det, const uint8_t* const* frames, const int32_t* h,
+                       const int32_t* w, const int64_t* row_stride, int32_t B,
+                       int32_t frames_on_device, float* out_pred_host) {
+  int rc = check_batch(det, frames, h, w, B);
+  if (rc) return (tcd_status)rc;
+  TCD_REQUIRE(out_pred_host, "forward: null output");
+  Slot& s = det->slot[0];
+  YoloxPlan* p = nullptr;
+  rc = get_plan(det, s, B, &p);
+  if (rc) return (tcd_status)rc;
+  rc = enqueue_input(det, s, p, frames, h, w, row_stride, B, frames_on_device);
+  if (rc) return (tcd_status)rc;
+  rc = run_net_post(det, s, p, B, true);
+  if (rc) return (tcd_status)rc;
+  TCD_CUDA_OK(cudaMemcpyAsync(out_pred_host, s.pb.decoded,
+                              sizeof(float) * (size_t)B * det->n_anchors * (5 + det->cfg.num_classes),
+                              cudaMemcpyDeviceToHost, s.stream));
+  TCD_CUDA_OK(cudaStreamSynchronize(s.stream));
+  return TCD_OK;
+}
+
+tcd_status tcd_postprocess(tcd_detector* det, const float* pred_host, int32_t B, float* out_dets,
+                           int32_t* out_counts) {
+  TCD_REQUIRE(det && pred_host && out_dets && out_counts, "postprocess: null argument");
+  TCD_REQUIRE(B >= 1 && B <= det->cfg.max_batch, "postprocess: batch %d", B);
+  Slot& s = det->slot[0];
+  YoloxPlan* p = nullptr;
+  int rc = get_plan(det, s, det->cfg.max_batch, &p);
+  if (rc) return (tcd_status)rc;
+  const size_t n = (size_t)B * det->n_anchors * (5 + det->cfg.num_classes);
+  TCD_CUDA_OK(cudaMemcpyAsync(s.pred_in, pred_host, n * sizeof(float), cudaMemcpyHostToDevice, s.stream));
+  rc = postproc_launch(post_for(s, p, B, s.pred_in, false), 0, s.stream);
+  if (rc) return (tcd_status)rc;
+  TCD_CUDA_OK(cudaMemcpyAsync(s.out_pinned, s.pb.out_dets, sizeof(float) * 7 * det->cfg.max_out * B,
+                              cudaMemcpyDeviceToHost, s.stream));
+  TCD_CUDA_OK(cudaMemcpyAsync(s.cnt_pinned, s.pb.out_counts, sizeof(int) * B, cudaMemcpyDeviceToHost,
+                              s.stream));
+  TCD_CUDA_OK(cudaStreamSynchronize(s.stream));
+  const size_t row = (size_t)7 * det->cfg.max_out;
+  for (int b = 0; b < B; ++b) {
+    out_counts[b] = s.cnt_pinned[b];
+    memcpy(out_dets + b * row, s.out_pinned + b * row, sizeof(float) * 7 * (size_t)s.cnt_pinned[b]);
+  }
+  return TCD_OK;
+}
+
+tcd_status tcd_detector_read_activation(tcd_detector* det, const char* name, float* out_host,
+                                        size_t out_elems, int32_t* shape4) {
+  TCD_REQUIRE(det && name && shape4, "read_activation: null argument");
+  Slot& s = det->slot[0];
+  const YoloxPlan* p = nullptr;
+  for (auto& kv : s.plans) if (kv.second->acts.count(name)) p = kv.second;  // last built wins
+  // prefer the plan used most recently: the one whose batch equals pending/last B is unknown
+  // here, so callers read right after tcd_forward with the same B as max_batch or a single plan
+  TCD_REQUIRE(p != nullptr, "read_activation: no buffer named %s", name);
+  const Act& a = p->acts.at(name);
+  shape4[0] = p->B; shape4[1] = a.H; shape4[2] = a.W; shape4[3] = a.C;
+  const size_t n = (size_t)p->B * a.H * a.W * a.C;
+  if (!out_host) return TCD_OK;
+  TCD_REQUIRE(out_elems >= n, "read_activation: output too small (%zu < %zu)", out_elems, n);
+  std::vector<uint16_t> tmp(n);
+  TCD_CUDA_OK(cudaStreamSynchronize(s.stream));
+  TCD_CUDA_OK(cudaMemcpy(tmp.data(), a.p, n * 2, cudaMemcpyDeviceToHost));
+  for (size_t i = 0; i < n; ++i) {
+    uint32_t u = (uint32_t)tmp[i] << 16;
+    memcpy(out_host + i, &u, 4);
+  }
+  return TCD_OK;
+}
+
+}  // extern "C"

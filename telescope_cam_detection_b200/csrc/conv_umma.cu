@@ -1,0 +1,252 @@
+// Host side of the tcgen05 implicit-GEMM conv engine: tensor-map construction, tiling
+// choice, launch.  See conv_umma.cuh for the kernel and the design notes.
+#define TCD_CONV_KERNEL_IMPL
+#include "conv_umma.cuh"
+
+#include <atomic>
+#include <mutex>
+#include <string.h>
+#include <vector>
+
+namespace tcd {
+
+extern std::atomic<uint64_t> g_launch_count;
+
+typedef CUresult (*PFN_encodeTiled)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*,
+                                    const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
+                                    const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                    CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static PFN_encodeTiled get_encode() {
+  static PFN_encodeTiled fn = nullptr;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) ==
+            cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      fn = (PFN_encodeTiled)p;
+  });
+  return fn;
+}
+
+static CUtensorMapSwizzle swizzle_for_inner_bytes(int bytes) {
+  if (bytes == 128) return CU_TENSOR_MAP_SWIZZLE_128B;
+  if (bytes == 64) return CU_TENSOR_MAP_SWIZZLE_64B;
+  if (bytes == 32) return CU_TENSOR_MAP_SWIZZLE_32B;
+  return CU_TENSOR_MAP_SWIZZLE_NONE;
+}
+
+static int encode_map(CUtensorMap* m, void* base, int rank, const cuuint64_t* dims,
+                      const cuuint64_t* strides_bytes, const cuuint32_t* box, int inner_bytes,
+                      const char* what) {
+  PFN_encodeTiled enc = get_encode();
+  if (!enc) {
+    set_last_error("cuTensorMapEncodeTiled entry point unavailable (no CUDA driver?)");
+    return TCD_ERR_CUDA;
+  }
+  cuuint32_t es[5] = {1, 1, 1, 1, 1};
+  CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, (cuuint32_t)rank, base, dims, strides_bytes,
+                   box, es, CU_TENSOR_MAP_INTERLEAVE_NONE, swizzle_for_inner_bytes(inner_bytes),
+                   CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    set_last_error("cuTensorMapEncodeTiled(%s) failed: CUresult %d (dims %llu,%llu,%llu box %u,%u,%u)",
+                   what, (int)r, (unsigned long long)dims[0], (unsigned long long)dims[1],
+                   (unsigned long long)dims[2], box[0], box[1], box[2]);
+    return TCD_ERR_CUDA;
+  }
+  return TCD_OK;
+}
+
+uint16_t f32_to_bf16_rn(float f) {
+  uint32_t u;
+  memcpy(&u, &f, 4);
+  if ((u & 0x7fffffffu) > 0x7f800000u) return (uint16_t)((u >> 16) | 0x40);
+  u += 0x7fffu + ((u >> 16) & 1u);
+  return (uint16_t)(u >> 16);
+}
+
+void conv_pack_weights(const float* w, int cout, int cin, int k, int cout_pad, int cin_pad,
+                       uint16_t* out) {
+  const int taps = k * k;
+  memset(out, 0, sizeof(uint16_t) * (size_t)taps * cout_pad * cin_pad);
+  for (int o = 0; o < cout; ++o)
+    for (int c = 0; c < cin; ++c)
+      for (int t = 0; t < taps; ++t)
+        out[((size_t)t * cout_pad + o) * cin_pad + c] =
+            f32_to_bf16_rn(w[((size_t)o * cin + c) * taps + t]);
+}
+
+static void choose_tile(int Ho, int Wo, int* TW, int* TH) {
+  if (Wo % 16 == 0 && Ho % 8 == 0) {
+    *TW = 16;
+    *TH = 8;
+    return;
+  }
+  long best = -1;
+  int btw = 8, bth = 16;
+  for (int tw = 4; tw <= Wo && tw <= 128; ++tw) {
+    int th = 128 / tw;
+    if (th > Ho) th = Ho;
+    if (th < 1) continue;
+    long tiles = (long)cdiv(Wo, tw) * cdiv(Ho, th);
+    // fewer tiles first, then prefer wider rows (longer contiguous runs per pixel row)
+    long score = tiles * 1000 - tw;
+    if (best < 0 || score < best) {
+      best = score;
+      btw = tw;
+      bth = th;
+    }
+  }
+  *TW = btw;
+  *TH = bth;
+}
+
+int conv_plan_build(const ConvDesc& d, ConvPlan* plan) {
+  memset(plan, 0, sizeof(*plan));
+  TCD_REQUIRE(d.k == 1 || d.k == 3, "conv: kernel size %d unsupported", d.k);
+  TCD_REQUIRE(d.stride == 1 || d.stride == 2, "conv: stride %d unsupported", d.stride);
+  TCD_REQUIRE(d.cin % 16 == 0 && d.cin >= 16, "conv: cin %d must be a multiple of 16", d.cin);
+  TCD_REQUIRE(d.stride == 1 || (d.H % 2 == 0 && d.W % 2 == 0), "conv: stride 2 needs even H,W");
+  TCD_REQUIRE(d.stride == 1 || d.k == 3, "conv: stride 2 only for 3x3");
+  const int mode = d.out_f32 ? 1 : 0;
+  ConvArgs& a = plan->args;
+  a.Ho = d.H / d.stride;
+  a.Wo = d.W / d.stride;
+  choose_tile(a.Ho, a.Wo, &a.TW, &a.TH);
+  a.tiles_w = cdiv(a.Wo, a.TW);
+  const int tiles_h = cdiv(a.Ho, a.TH);
+  a.tiles_per_img = a.tiles_w * tiles_h;
+  a.taps = d.k * d.k;
+  a.ck = d.cin >= 64 ? 64 : d.cin;
+  TCD_REQUIRE(d.cin % a.ck == 0 && (a.ck == 16 || a.ck == 32 || a.ck == 64),
+              "conv: cin %d not chunkable", d.cin);
+  a.kchunks = d.cin / a.ck;
+  // N tile
+  int BN;
+  if (mode == 1) {
+    BN = d.cout_pad;
+    TCD_REQUIRE(BN % 16 == 0 && BN <= 256, "conv: pred cout_pad %d", BN);
+  } else {
+    TCD_REQUIRE(d.cout_pad == d.cout && d.cout % 32 == 0, "conv: cout %d must be a multiple of 32",
+                d.cout);
+    BN = d.cout >= 128 ? 128 : d.cout;
+    TCD_REQUIRE(d.cout % BN == 0, "conv: cout %d not tileable", d.cout);
+  }
+  a.BN = BN;
+  a.cin_off = d.x_coff;
+  a.cout_off = d.y_coff;
+  a.mode = mode;
+  a.silu = d.silu;
+  a.out_chunk = BN >= 64 ? 64 : 32;
+  a.n_valid = d.cout;
+  a.bias = d.bias;
+  a.resid = (const __nv_bfloat16*)d.resid;
+  a.r_ctot = d.r_ctot;
+  a.r_coff = d.r_coff;
+  a.out_f32 = d.out_f32;
+  a.out_ld = d.out_ld;
+  a.out_col = d.out_col;
+  a.rows_per_img = d.rows_per_img;
+  a.row_off = d.row_off;
+  int tc = 32;
+  while (tc < BN) tc <<= 1;
+  a.tmem_cols = tc;
+  // taps
+  for (int t = 0; t < a.taps; ++t) {
+    const int r = t / d.k, s = t % d.k;
+    if (d.k == 1) {
+      a.tap_map[t] = 0; a.tap_dx[t] = 0; a.tap_dy[t] = 0;
+    } else if (d.stride == 1) {
+      a.tap_map[t] = 0; a.tap_dx[t] = (int8_t)(s - 1); a.tap_dy[t] = (int8_t)(r - 1);
+    } else {
+      // in = 2*out + tap - 1  ->  parity hp = (r != 1), half-res shift = (r == 0 ? -1 : 0)
+      const int hp = (r != 1), wp = (s != 1);
+      a.tap_map[t] = (int8_t)(hp * 2 + wp);
+      a.tap_dx[t] = (int8_t)(s == 0 ? -1 : 0);
+      a.tap_dy[t] = (int8_t)(r == 0 ? -1 : 0);
+    }
+  }
+  // pipeline depth / smem
+  const int a_bytes = 128 * a.ck * 2, b_bytes = BN * a.ck * 2;
+  const int stage_bytes = a_bytes + b_bytes;
+  TCD_REQUIRE(stage_bytes % 1024 == 0, "conv: stage bytes %d not 1 KiB aligned", stage_bytes);
+  const int staging = mode == 0 ? 128 * BN * 2 : 0;
+  const int total_it = a.taps * a.kchunks;
+  int stages = total_it < 4 ? total_it : 4;
+  const int budget = 100 * 1024;  // two CTAs per SM
+  while (stages > 2 && stages * stage_bytes > budget) --stages;
+  while (stages * stage_bytes < staging) ++stages;
+  TCD_REQUIRE(stages >= 1 && stages <= kConvMaxStages, "conv: bad stage count %d", stages);
+  a.stages = stages;
+  plan->smem_bytes = stages * stage_bytes + 1024;
+  plan->grid = dim3((unsigned)(a.tiles_per_img * d.N), (unsigned)(d.cout_pad / BN), 1);
+  plan->flops = 2.0 * d.N * a.Ho * a.Wo * (double)d.cout * d.cin * a.taps;
+
+  // ---- tensor maps
+  const int inner = a.ck * 2;
+  const size_t es = 2;
+  if (d.stride == 1) {
+    cuuint64_t dims[4] = {(cuuint64_t)d.x_ctot, (cuuint64_t)d.W, (cuuint64_t)d.H, (cuuint64_t)d.N};
+    cuuint64_t st[3] = {(cuuint64_t)d.x_ctot * es, (cuuint64_t)d.W * d.x_ctot * es,
+                        (cuuint64_t)d.H * d.W * d.x_ctot * es};
+    cuuint32_t box[4] = {(cuuint32_t)a.ck, (cuuint32_t)a.TW, (cuuint32_t)a.TH, 1};
+    int rc = encode_map(&plan->maps.a[0], (void*)d.x, 4, dims, st, box, inner, "A");
+    if (rc) return rc;
+    for (int i = 1; i < 4; ++i) plan->maps.a[i] = plan->maps.a[0];
+  } else {
+    for (int hp = 0; hp < 2; ++hp)
+      for (int wp = 0; wp < 2; ++wp) {
+        uint8_t* base = (uint8_t*)d.x + ((size_t)hp * d.W + wp) * d.x_ctot * es;
+        cuuint64_t dims[4] = {(cuuint64_t)d.x_ctot, (cuuint64_t)d.W / 2, (cuuint64_t)d.H / 2,
+                              (cuuint64_t)d.N};
+        cuuint64_t st[3] = {(cuuint64_t)2 * d.x_ctot * es, (cuuint64_t)2 * d.W * d.x_ctot * es,
+                            (cuuint64_t)d.H * d.W * d.x_ctot * es};
+        cuuint32_t box[4] = {(cuuint32_t)a.ck, (cuuint32_t)a.TW, (cuuint32_t)a.TH, 1};
+        int rc = encode_map(&plan->maps.a[hp * 2 + wp], base, 4, dims, st, box, inner, "A/s2");
+        if (rc) return rc;
+      }
+  }
+  {
+    cuuint64_t dims[3] = {(cuuint64_t)d.cin, (cuuint64_t)d.cout_pad, (cuuint64_t)a.taps};
+    cuuint64_t st[2] = {(cuuint64_t)d.cin * es, (cuuint64_t)d.cout_pad * d.cin * es};
+    cuuint32_t box[3] = {(cuuint32_t)a.ck, (cuuint32_t)BN, 1};
+    int rc = encode_map(&plan->maps.b, (void*)d.w, 3, dims, st, box, inner, "B");
+    if (rc) return rc;
+  }
+  if (mode == 0) {
+    cuuint64_t dims[4] = {(cuuint64_t)d.y_ctot, (cuuint64_t)a.Wo, (cuuint64_t)a.Ho, (cuuint64_t)d.N};
+    cuuint64_t st[3] = {(cuuint64_t)d.y_ctot * es, (cuuint64_t)a.Wo * d.y_ctot * es,
+                        (cuuint64_t)a.Ho * a.Wo * d.y_ctot * es};
+    cuuint32_t box[4] = {(cuuint32_t)a.out_chunk, (cuuint32_t)a.TW, (cuuint32_t)a.TH, 1};
+    int rc = encode_map(&plan->maps.o, d.y, 4, dims, st, box, a.out_chunk * 2, "O");
+    if (rc) return rc;
+  } else {
+    plan->maps.o = plan->maps.b;
+  }
+  static std::once_flag once;
+  static cudaError_t attr_err = cudaSuccess;
+  std::call_once(once, [] {
+    attr_err = cudaFuncSetAttribute(conv_umma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                    200 * 1024);
+  });
+  if (attr_err != cudaSuccess) {
+    set_last_error("cudaFuncSetAttribute(conv_umma_kernel): %s", cudaGetErrorString(attr_err));
+    return TCD_ERR_CUDA;
+  }
+  return TCD_OK;
+}
+
+int conv_plan_launch(const ConvPlan& plan, cudaStream_t stream) {
+  conv_umma_kernel<<<plan.grid, kConvThreads, plan.smem_bytes, stream>>>(plan.maps, plan.args);
+  g_launch_count.fetch_add(1, std::memory_order_relaxed);
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) {
+    set_last_error("conv_umma_kernel launch: %s", cudaGetErrorString(e));
+    return TCD_ERR_CUDA;
+  }
+  return TCD_OK;
+}
+
+}  // namespace tcd

@@ -1,0 +1,265 @@
+// Implicit-GEMM convolution on tcgen05 (UMMA) with TMA-fed operands -- the K3 engine.
+//
+// Replaces every cudnn conv2d + BatchNorm(eval) + SiLU of upstream YOLOX-S that the
+// reference runs through self.model(batch) (src/yolox_detector.py:306,378).
+//
+// Formulation (B200-first, not a cuDNN translation):
+//   * activations are bf16 NHWC; one CTA owns a TH x TW patch of output pixels (<=128 = UMMA M)
+//     and BN output channels (UMMA N, accumulators in TMEM, fp32);
+//   * for every filter tap (r,s) and every chunk of ck input channels the A operand is ONE
+//     4-D TMA box load (ck, TW, TH, 1) at the shifted coordinate (x0+s-1, y0+r-1): the
+//     hardware zero-fills out-of-bounds pixels, which IS the conv padding.  The box lands
+//     in shared memory already in the canonical K-major swizzled UMMA layout (one pixel per
+//     row), so there is no im2col buffer and no gather code at all;
+//   * stride-2 convs use four parity views of the input (base pointer offset by (hp,wp),
+//     pixel strides doubled), so each tap is again a plain dense box;
+//   * weights are pre-packed [tap][Cout][Cin] bf16 and loaded with a 3-D TMA box;
+//   * warp 0 = TMA producer, warp 1 = TMEM allocator + single-thread MMA issuer,
+//     warps 2-5 = epilogue (tcgen05.ld -> +bias -> SiLU -> (+residual) -> bf16 ->
+//     swizzled smem -> TMA store, which clips partial tiles for free and writes straight
+//     into a channel slice of a concat buffer).
+#pragma once
+#include "tcd_common.cuh"
+
+namespace tcd {
+
+constexpr int kConvMaxStages = 8;
+constexpr int kConvThreads = 192;
+
+struct ConvMaps {
+  CUtensorMap a[4];
+  CUtensorMap b;
+  CUtensorMap o;
+};
+
+struct ConvArgs {
+  int Ho, Wo, TW, TH, tiles_w, tiles_per_img;
+  int taps, kchunks, ck, BN;
+  int cin_off, cout_off;
+  int mode;  // 0: bf16 NHWC via TMA store; 1: f32 rows (head predictions)
+  int silu, out_chunk, stages, tmem_cols, n_valid;
+  const float* bias;
+  const __nv_bfloat16* resid;
+  int r_ctot, r_coff;
+  float* out_f32;
+  int out_ld, out_col, rows_per_img, row_off;
+  int8_t tap_map[9], tap_dx[9], tap_dy[9];
+};
+
+#if defined(__CUDACC__) && defined(TCD_CONV_KERNEL_IMPL)
+
+template <int NC>
+__device__ __forceinline__ void conv_epilogue_cols(const ConvArgs& p, uint32_t taddr, int c0,
+                                                   const float* s_bias, int row, bool valid,
+                                                   int n_img, int y, int x, int n_tile,
+                                                   uint8_t* stage_base) {
+  uint32_t r[NC];
+  if constexpr (NC == 32) tmem_ld32(taddr + c0, r); else tmem_ld16(taddr + c0, r);
+  tmem_ld_wait();
+  float v[NC];
+#pragma unroll
+  for (int j = 0; j < NC; ++j) {
+    float a = __uint_as_float(r[j]) + s_bias[c0 + j];
+    v[j] = p.silu ? silu_f(a) : a;
+  }
+  if (p.mode == 0) {
+    if (p.resid != nullptr && valid) {
+      const __nv_bfloat16* rp = p.resid + ((size_t)((size_t)n_img * p.Ho + y) * p.Wo + x) * p.r_ctot +
+                                p.r_coff + n_tile * p.BN + c0;
+      const uint4* rp4 = reinterpret_cast<const uint4*>(rp);
+#pragma unroll
+      for (int u = 0; u < NC / 8; ++u) {
+        uint4 q = __ldg(rp4 + u);
+        const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&q);
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          float2 f = __bfloat1622float2(h[e]);
+          v[u * 8 + e * 2] += f.x;
+          v[u * 8 + e * 2 + 1] += f.y;
+        }
+      }
+    }
+    const int chunk = c0 / p.out_chunk;
+    const int row_bytes = p.out_chunk * 2;
+    const int u0 = (c0 % p.out_chunk) >> 3;
+    const int sw = (p.out_chunk == 64) ? (row & 7) : ((row >> 1) & 3);
+    uint8_t* rowp = stage_base + (size_t)chunk * 128 * row_bytes + (size_t)row * row_bytes;
+#pragma unroll
+    for (int u = 0; u < NC / 8; ++u) {
+      uint4 q;
+      q.x = pack_bf16x2(v[u * 8 + 0], v[u * 8 + 1]);
+      q.y = pack_bf16x2(v[u * 8 + 2], v[u * 8 + 3]);
+      q.z = pack_bf16x2(v[u * 8 + 4], v[u * 8 + 5]);
+      q.w = pack_bf16x2(v[u * 8 + 6], v[u * 8 + 7]);
+      *reinterpret_cast<uint4*>(rowp + (((u0 + u) ^ sw) << 4)) = q;
+    }
+  } else {
+    if (valid) {
+      float* op = p.out_f32 +
+                  ((size_t)n_img * p.rows_per_img + p.row_off + (size_t)y * p.Wo + x) * p.out_ld +
+                  p.out_col;
+#pragma unroll
+      for (int j = 0; j < NC; ++j)
+        if (c0 + j < p.n_valid) op[c0 + j] = v[j];
+    }
+  }
+}
+
+__global__ void __launch_bounds__(kConvThreads)
+conv_umma_kernel(const __grid_constant__ ConvMaps maps, const __grid_constant__ ConvArgs p) {
+  extern __shared__ uint8_t smem_raw[];
+  __shared__ uint64_t full_bar[kConvMaxStages];
+  __shared__ uint64_t empty_bar[kConvMaxStages];
+  __shared__ uint64_t tmem_full_bar;
+  __shared__ uint32_t tmem_base_s;
+  __shared__ float s_bias[256];
+
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
+                                             ~(uintptr_t)1023);
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const int a_bytes = 128 * p.ck * 2;
+  const int b_bytes = p.BN * p.ck * 2;
+  const int stage_bytes = a_bytes + b_bytes;
+
+  const int m_tile = blockIdx.x;
+  const int n_tile = blockIdx.y;
+  const int n_img = m_tile / p.tiles_per_img;
+  const int rem = m_tile - n_img * p.tiles_per_img;
+  const int ty = rem / p.tiles_w;
+  const int tx = rem - ty * p.tiles_w;
+  const int y0 = ty * p.TH;
+  const int x0 = tx * p.TW;
+  const int total_it = p.taps * p.kchunks;
+
+  if (warp == 0 && lane == 0) {
+    prefetch_tmap(&maps.a[0]);
+    prefetch_tmap(&maps.b);
+    if (p.mode == 0) prefetch_tmap(&maps.o);
+    for (int s = 0; s < p.stages; ++s) {
+      mbar_init(&full_bar[s], 1);
+      mbar_init(&empty_bar[s], 1);
+    }
+    mbar_init(&tmem_full_bar, 1);
+    fence_mbar_init();
+  }
+  if (warp == 1) tmem_alloc(&tmem_base_s, (uint32_t)p.tmem_cols);
+  if (warp >= 2) {
+    for (int i = threadIdx.x - 64; i < p.BN; i += 128) s_bias[i] = p.bias[n_tile * p.BN + i];
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = tmem_base_s;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      const uint32_t tx_bytes = (uint32_t)(p.TW * p.TH * p.ck * 2 + b_bytes);
+      int it = 0;
+      for (int tap = 0; tap < p.taps; ++tap) {
+        const CUtensorMap* am = &maps.a[p.tap_map[tap]];
+        const int cx = x0 + p.tap_dx[tap];
+        const int cy = y0 + p.tap_dy[tap];
+        for (int kc = 0; kc < p.kchunks; ++kc, ++it) {
+          const int s = it % p.stages;
+          const uint32_t ph = (uint32_t)(it / p.stages) & 1u;
+          mbar_wait(&empty_bar[s], ph ^ 1u);
+          uint8_t* sa = smem + (size_t)s * stage_bytes;
+          mbar_expect_tx(&full_bar[s], tx_bytes);
+          tma_load_4d(sa, am, &full_bar[s], p.cin_off + kc * p.ck, cx, cy, n_img);
+          tma_load_3d(sa + a_bytes, &maps.b, &full_bar[s], kc * p.ck, n_tile * p.BN, tap);
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      const uint32_t idesc = umma_idesc_bf16(128, p.BN);
+      const uint32_t lt = (p.ck == 64) ? 2u : (p.ck == 32 ? 4u : 6u);
+      const uint32_t sbo = (uint32_t)(8 * p.ck * 2);
+      const int ksteps = p.ck >> 4;
+      for (int it = 0; it < total_it; ++it) {
+        const int s = it % p.stages;
+        const uint32_t ph = (uint32_t)(it / p.stages) & 1u;
+        mbar_wait(&full_bar[s], ph);
+        tc_fence_after();
+        const uint32_t a_addr = smem_u32(smem + (size_t)s * stage_bytes);
+        const uint32_t b_addr = a_addr + (uint32_t)a_bytes;
+        for (int k = 0; k < ksteps; ++k) {
+          const uint64_t ad = umma_smem_desc(a_addr + k * 32, sbo, lt);
+          const uint64_t bd = umma_smem_desc(b_addr + k * 32, sbo, lt);
+          umma_bf16(tmem_base, ad, bd, idesc, (uint32_t)((it | k) != 0));
+        }
+        umma_commit(&empty_bar[s]);
+      }
+      umma_commit(&tmem_full_bar);
+    }
+  } else {
+    mbar_wait(&tmem_full_bar, 0);
+    tc_fence_after();
+    const int q = warp & 3;
+    const int row = q * 32 + lane;
+    const int ly = row / p.TW;
+    const int lx = row - ly * p.TW;
+    const int y = y0 + ly;
+    const int x = x0 + lx;
+    const bool valid = (row < p.TW * p.TH) && (y < p.Ho) && (x < p.Wo);
+    const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16);
+    int c0 = 0;
+    for (; c0 + 32 <= p.BN; c0 += 32)
+      conv_epilogue_cols<32>(p, taddr, c0, s_bias, row, valid, n_img, y, x, n_tile, smem);
+    if (c0 < p.BN)
+      conv_epilogue_cols<16>(p, taddr, c0, s_bias, row, valid, n_img, y, x, n_tile, smem);
+    if (p.mode == 0) {
+      fence_proxy_async_smem();
+      asm volatile("bar.sync 1, 128;" ::: "memory");
+      if (warp == 2 && lane == 0) {
+        const int nchunks = p.BN / p.out_chunk;
+        for (int c = 0; c < nchunks; ++c)
+          tma_store_4d(&maps.o, smem + (size_t)c * 128 * p.out_chunk * 2,
+                       p.cout_off + n_tile * p.BN + c * p.out_chunk, x0, y0, n_img);
+        tma_store_commit_wait();
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc(tmem_base, (uint32_t)p.tmem_cols);
+}
+
+#endif  // __CUDACC__ && TCD_CONV_KERNEL_IMPL
+
+// ---------------------------------------------------------------- host-side plan
+struct ConvDesc {
+  // input view
+  const void* x = nullptr;
+  int N = 0, H = 0, W = 0, x_ctot = 0, x_coff = 0, cin = 0;  // cin: padded to a multiple of 16
+  // weights: device, bf16 [taps][cout_pad][cin]; bias: device f32 [cout_pad]
+  const void* w = nullptr;
+  const float* bias = nullptr;
+  int cout = 0, cout_pad = 0, k = 1, stride = 1, silu = 1;
+  // bf16 output (mode 0)
+  void* y = nullptr;
+  int y_ctot = 0, y_coff = 0;
+  const void* resid = nullptr;
+  int r_ctot = 0, r_coff = 0;
+  // f32 row output (mode 1)
+  float* out_f32 = nullptr;
+  int out_ld = 0, out_col = 0, rows_per_img = 0, row_off = 0;
+};
+
+struct ConvPlan {
+  ConvMaps maps;
+  ConvArgs args;
+  dim3 grid;
+  int smem_bytes = 0;
+  double flops = 0;
+};
+
+int conv_plan_build(const ConvDesc& d, ConvPlan* plan);
+int conv_plan_launch(const ConvPlan& plan, cudaStream_t stream);
+// pack f32 [cout][cin][k][k] (host) -> bf16 [k*k][cout_pad][cin_pad] (host buffer)
+void conv_pack_weights(const float* w, int cout, int cin, int k, int cout_pad, int cin_pad,
+                       uint16_t* out);
+uint16_t f32_to_bf16_rn(float f);
+
+}  // namespace tcd

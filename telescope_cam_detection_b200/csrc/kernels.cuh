@@ -1,0 +1,84 @@
+// Argument structs and host launchers shared between the kernel TUs and the C-ABI glue.
+#pragma once
+#include "tcd_common.cuh"
+
+namespace tcd {
+
+// ---- preprocess (preproc.cu)
+struct PreFrame {
+  const uint8_t* ptr;
+  long long stride;
+  int h, w;
+  int content_h, content_w;  // letterbox content size (== out size in stretch mode)
+  float scale_y, scale_x;
+};
+int preproc_launch(const tcd_preproc_cfg* cfg, const PreFrame* frames_host, const PreFrame* frames_dev,
+                   int B, int layout, void* out_dev, cudaStream_t stream);
+void preproc_describe(const tcd_preproc_cfg* cfg, const uint8_t* ptr, int h, int w, long long stride,
+                      PreFrame* f);
+
+// ---- decode / filter / NMS (postproc.cu)
+struct PostBuffers {
+  int B, A, C, cap, max_out;
+  const float* pred;      // [B,A,5+C] raw head output or decoded prediction
+  float* decoded;         // optional [B,A,5+C]
+  const float* thr;       // device [2] = {conf, nms}
+  int* cand_count;        // [B]
+  float* cand;            // [B,cap,8]
+  int* cand_anchor;       // [B,cap]
+  float* srec;            // [B,cap,8] sorted rows
+  float4* sbox;           // [B,cap] sorted offset boxes
+  int* n_sorted;          // [B]
+  unsigned long long* mask;  // [B,cap,cap/64]
+  float* out_dets;        // [B,max_out,7]
+  int* out_counts;        // [B]
+  int n_levels;
+  int lvl_start[4], lvl_w[4], lvl_stride[4];
+};
+int postproc_launch(const PostBuffers& pb, int raw, cudaStream_t stream);
+
+// ---- motion (motion.cu)
+constexpr int kMogModes = 5;
+constexpr int kMogMaxRepeats = 16;
+struct Mog2Params {
+  int npix, w, h;
+  long long stride;
+  float Tb, TB, Tg, varInit, varMin, varMax, CT, tau;
+  int detect_shadows;
+  int repeats;
+  float alpha[kMogMaxRepeats];
+};
+// SoA over pixels: weight[m][npix], var[m][npix], mean[m][c][npix] (f32), nmodes[npix] (u8)
+struct Mog2State {
+  float* weight;
+  float* var;
+  float* mean;
+  uint8_t* nmodes;
+};
+constexpr int kBlurMaxK = 31;
+struct BlurArgs {
+  int w, h, ksize;         // ksize odd, <= 31
+  long long in_stride;
+  int src_mode;            // 0: u8 plane binarised (p > pre_thr ? 255 : 0); 1: BGR -> gray
+  int pre_thr;
+  int post_mode;           // 0: write (v > post_thr ? 255 : 0); 1: absdiff vs prev, count, prev = v
+  int post_thr;
+  int first;               // post_mode 1: no previous frame yet (just store)
+  uint16_t k[kBlurMaxK];   // 8.8 fixed-point taps, sum 256
+};
+int mog2_launch(const uint8_t* frame, const Mog2State& st, const Mog2Params& p, uint8_t* fgmask,
+                cudaStream_t stream);
+int blur_launch(const uint8_t* src, const BlurArgs& a, uint8_t* dst, uint8_t* prev,
+                unsigned int* counter, cudaStream_t stream);
+int threshold_launch(const uint8_t* src, int n, int thr, uint8_t* dst, cudaStream_t stream);
+int roi_count_launch(const uint8_t* mask, int w, int h, const int* rois_dev, int n,
+                     unsigned int* counts_dev, cudaStream_t stream);
+
+// ---- stage-2 crops (crop_resize.cu)
+int crop_resize_launch(const uint8_t* frame, int h, int w, long long stride, const int* boxes_dev,
+                       int n, int S, const tcd_preproc_cfg* cfg, int layout, void* out,
+                       cudaStream_t stream);
+
+int require_sm100();
+
+}  // namespace tcd

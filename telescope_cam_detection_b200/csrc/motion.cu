@@ -1,0 +1,343 @@
+// Motion kernels (K8, K9, K10): MOG2 background subtraction, OpenCV-exact u8 Gaussian blur,
+// thresholds, per-ROI countNonZero and the empty-frame gate.
+//
+// Replaces cv2.BackgroundSubtractorMOG2.apply / cv2.threshold / cv2.GaussianBlur /
+// cv2.countNonZero as used by MotionFilter.has_motion_in_bbox (src/motion_filter.py:68-127)
+// and cv2.cvtColor / GaussianBlur / absdiff / threshold / countNonZero in
+// EmptyFrameFilter.has_motion (src/empty_frame_filter.py:51-98).
+// Arithmetic follows the specification validated bit-exact against cv2 4.13 in SURVEY App. C;
+// this TU is compiled with -fmad=false so every fp32 intermediate rounds like the scalar code.
+#include "kernels.cuh"
+
+#include <atomic>
+#include <float.h>
+
+namespace tcd {
+extern std::atomic<uint64_t> g_launch_count;
+
+// ------------------------------------------------------------------ MOG2
+#define MOG_SWAP(i, j)                                                                     \
+  do {                                                                                     \
+    float _t;                                                                              \
+    _t = w[i]; w[i] = w[j]; w[j] = _t;                                                     \
+    _t = v[i]; v[i] = v[j]; v[j] = _t;                                                     \
+    _t = m0[i]; m0[i] = m0[j]; m0[j] = _t;                                                 \
+    _t = m1[i]; m1[i] = m1[j]; m1[j] = _t;                                                 \
+    _t = m2[i]; m2[i] = m2[j]; m2[j] = _t;                                                 \
+  } while (0)
+
+__global__ void __launch_bounds__(256)
+mog2_apply_kernel(const uint8_t* __restrict__ frame, const Mog2State st, const Mog2Params p,
+                  uint8_t* __restrict__ fgmask) {
+  const int idx = blockIdx.x * 256 + threadIdx.x;
+  if (idx >= p.npix) return;
+  const int py = idx / p.w, px = idx - py * p.w;
+  const uint8_t* pp = frame + (long long)py * p.stride + px * 3;
+  const float x0 = (float)pp[0], x1 = (float)pp[1], x2 = (float)pp[2];
+
+  float w[kMogModes], v[kMogModes], m0[kMogModes], m1[kMogModes], m2[kMogModes];
+  int n = st.nmodes[idx];
+#pragma unroll
+  for (int k = 0; k < kMogModes; ++k) {
+    if (k < n) {
+      const size_t o = (size_t)k * p.npix + idx;
+      w[k] = st.weight[o];
+      v[k] = st.var[o];
+      m0[k] = st.mean[((size_t)k * 3 + 0) * p.npix + idx];
+      m1[k] = st.mean[((size_t)k * 3 + 1) * p.npix + idx];
+      m2[k] = st.mean[((size_t)k * 3 + 2) * p.npix + idx];
+    } else {
+      w[k] = 0.f; v[k] = 0.f; m0[k] = 0.f; m1[k] = 0.f; m2[k] = 0.f;
+    }
+  }
+  int n_in = n;
+  bool bg = false;
+  for (int rep = 0; rep < p.repeats; ++rep) {
+    const float alpha = p.alpha[rep];
+    const float a1 = 1.0f - alpha;
+    const float prune = -(alpha * p.CT);
+    bg = false;
+    bool fits = false;
+    int nmodes = n;
+    float tot = 0.f;
+#pragma unroll
+    for (int mode = 0; mode < kMogModes; ++mode) {
+      if (mode < nmodes) {
+        float wt = (a1 * w[mode]) + prune;
+        int swap = 0;
+        if (!fits) {
+          const float var = v[mode];
+          const float d0 = m0[mode] - x0, d1 = m1[mode] - x1, d2 = m2[mode] - x2;
+          const float dist2 = ((d0 * d0) + (d1 * d1)) + (d2 * d2);
+          if (tot < p.TB && dist2 < (p.Tb * var)) bg = true;
+          if (dist2 < (p.Tg * var)) {
+            fits = true;
+            wt = wt + alpha;
+            const float k = alpha / wt;
+            m0[mode] = m0[mode] - (k * d0);
+            m1[mode] = m1[mode] - (k * d1);
+            m2[mode] = m2[mode] - (k * d2);
+            float vn = var + (k * (dist2 - var));
+            vn = fmaxf(vn, p.varMin);
+            vn = fminf(vn, p.varMax);
+            v[mode] = vn;
+            bool bubbling = true;
+#pragma unroll
+            for (int i = mode; i > 0; --i) {
+              if (bubbling) {
+                if (wt < w[i - 1]) {
+                  bubbling = false;
+                } else {
+                  ++swap;
+                  MOG_SWAP(i, i - 1);
+                }
+              }
+            }
+          }
+        }
+        if (wt < -prune) {
+          wt = 0.f;
+          --nmodes;
+        }
+        const int dst = mode - swap;
+#pragma unroll
+        for (int t = 0; t < kMogModes; ++t)
+          if (t == dst) w[t] = wt;
+        tot = tot + wt;
+      }
+    }
+    const float inv = (fabsf(tot) > FLT_EPSILON) ? 1.0f / tot : 0.f;
+#pragma unroll
+    for (int k = 0; k < kMogModes; ++k)
+      if (k < nmodes) w[k] = w[k] * inv;
+    if (!fits && alpha > 0.f) {
+      int mode;
+      if (nmodes == kMogModes) mode = kMogModes - 1; else mode = nmodes++;
+#pragma unroll
+      for (int t = 0; t < kMogModes; ++t) {
+        if (t == mode) {
+          w[t] = (nmodes == 1) ? 1.0f : alpha;
+          m0[t] = x0; m1[t] = x1; m2[t] = x2;
+          v[t] = p.varInit;
+        } else if (nmodes != 1 && t < nmodes - 1) {
+          w[t] = w[t] * a1;
+        }
+      }
+      bool stop = false;
+#pragma unroll
+      for (int i = kMogModes - 1; i > 0; --i) {
+        if (i <= nmodes - 1 && !stop) {
+          if (alpha < w[i - 1]) stop = true; else MOG_SWAP(i, i - 1);
+        }
+      }
+    }
+    n = nmodes;
+  }
+  // shadow test on the final state
+  uint8_t out = 0;
+  if (!bg) {
+    out = 255;
+    if (p.detect_shadows) {
+      float tW = 0.f;
+      bool done = false;
+#pragma unroll
+      for (int mode = 0; mode < kMogModes; ++mode) {
+        if (mode < n && !done) {
+          const float num = ((x0 * m0[mode]) + (x1 * m1[mode])) + (x2 * m2[mode]);
+          const float den = ((m0[mode] * m0[mode]) + (m1[mode] * m1[mode])) + (m2[mode] * m2[mode]);
+          if (den == 0.f) {
+            done = true;
+          } else {
+            if (num <= den && num >= (p.tau * den)) {
+              const float a = num / den;
+              const float e0 = (a * m0[mode]) - x0, e1 = (a * m1[mode]) - x1, e2 = (a * m2[mode]) - x2;
+              const float s = ((e0 * e0) + (e1 * e1)) + (e2 * e2);
+              if (s < (((p.Tb * v[mode]) * a) * a)) {
+                out = 127;
+                done = true;
+              }
+            }
+            if (!done) {
+              tW = tW + w[mode];
+              if (tW > p.TB) done = true;
+            }
+          }
+        }
+      }
+    }
+  }
+  fgmask[idx] = out;
+  const int n_wr = n > n_in ? n : n_in;  // slots that may have changed
+#pragma unroll
+  for (int k = 0; k < kMogModes; ++k) {
+    if (k < n_wr) {
+      const size_t o = (size_t)k * p.npix + idx;
+      st.weight[o] = w[k];
+      st.var[o] = v[k];
+      st.mean[((size_t)k * 3 + 0) * p.npix + idx] = m0[k];
+      st.mean[((size_t)k * 3 + 1) * p.npix + idx] = m1[k];
+      st.mean[((size_t)k * 3 + 2) * p.npix + idx] = m2[k];
+    }
+  }
+  st.nmodes[idx] = (uint8_t)n;
+}
+
+// ------------------------------------------------------------------ u8 Gaussian blur (OpenCV fixed point)
+constexpr int kBlurTW = 128;
+constexpr int kBlurTH = 64;
+constexpr int kBlurThreads = 256;
+
+__device__ __forceinline__ int reflect101(int i, int n) {
+  if (n == 1) return 0;
+  while (i < 0 || i >= n) {
+    if (i < 0) i = -i;
+    if (i >= n) i = 2 * n - 2 - i;
+  }
+  return i;
+}
+
+__global__ void __launch_bounds__(kBlurThreads)
+blur_kernel(const uint8_t* __restrict__ src, const BlurArgs a, uint8_t* __restrict__ dst,
+            uint8_t* __restrict__ prev, unsigned int* __restrict__ counter) {
+  extern __shared__ uint8_t sm_raw[];
+  const int R = a.ksize >> 1;
+  const int in_w = kBlurTW + 2 * R, in_h = kBlurTH + 2 * R;
+  uint8_t* s_in = sm_raw;                                              // [in_h][in_w]
+  uint16_t* s_h = reinterpret_cast<uint16_t*>(sm_raw + ((in_h * in_w + 15) & ~15));  // [in_h][TW]
+  const int x0 = blockIdx.x * kBlurTW, y0 = blockIdx.y * kBlurTH;
+
+  for (int i = threadIdx.x; i < in_h * in_w; i += kBlurThreads) {
+    const int ly = i / in_w, lx = i - ly * in_w;
+    const int gy = reflect101(y0 + ly - R, a.h), gx = reflect101(x0 + lx - R, a.w);
+    uint8_t val;
+    if (a.src_mode == 0) {
+      val = src[(long long)gy * a.in_stride + gx] > a.pre_thr ? 255 : 0;
+    } else {
+      const uint8_t* p = src + (long long)gy * a.in_stride + gx * 3;
+      // cv2.cvtColor BGR2GRAY, 15-bit coefficients (bit-exact vs cv2 4.13)
+      val = (uint8_t)(((int)p[0] * 3735 + (int)p[1] * 19235 + (int)p[2] * 9798 + 16384) >> 15);
+    }
+    s_in[i] = val;
+  }
+  __syncthreads();
+  // horizontal pass, exact 8.8 (no rounding)
+  for (int i = threadIdx.x; i < in_h * kBlurTW; i += kBlurThreads) {
+    const int ly = i / kBlurTW, lx = i - ly * kBlurTW;
+    const uint8_t* r = s_in + ly * in_w + lx;
+    unsigned int acc = 0;
+    for (int t = 0; t < a.ksize; ++t) acc += (unsigned int)a.k[t] * r[t];
+    s_h[i] = (uint16_t)acc;
+  }
+  __syncthreads();
+  unsigned int local = 0;
+  for (int i = threadIdx.x; i < kBlurTH * kBlurTW; i += kBlurThreads) {
+    const int ly = i / kBlurTW, lx = i - ly * kBlurTW;
+    const int gx = x0 + lx, gy = y0 + ly;
+    if (gx >= a.w || gy >= a.h) continue;
+    unsigned int acc = 0;
+    for (int t = 0; t < a.ksize; ++t) acc += (unsigned int)a.k[t] * s_h[(ly + t) * kBlurTW + lx];
+    const int v = (int)((acc + 32768u) >> 16);
+    const size_t o = (size_t)gy * a.w + gx;
+    if (a.post_mode == 0) {
+      dst[o] = v > a.post_thr ? 255 : 0;
+    } else {
+      if (!a.first) {
+        const int d = abs(v - (int)prev[o]);
+        local += d > a.post_thr ? 1u : 0u;
+      }
+      prev[o] = (uint8_t)v;
+      if (dst) dst[o] = (uint8_t)v;
+    }
+  }
+  if (a.post_mode == 1 && !a.first) {
+    for (int off = 16; off > 0; off >>= 1) local += __shfl_xor_sync(0xffffffffu, local, off);
+    if ((threadIdx.x & 31) == 0 && local) atomicAdd(counter, local);
+  }
+}
+
+// no-blur variant of the mask clean-up: (m > pre_thr) only (motion_blur_size <= 0)
+__global__ void threshold_kernel(const uint8_t* __restrict__ src, int n, int thr,
+                                 uint8_t* __restrict__ dst) {
+  const int i = blockIdx.x * 256 + threadIdx.x;
+  if (i < n) dst[i] = src[i] > thr ? 255 : 0;
+}
+
+// countNonZero inside each ROI; grid (n_rois, 16): each CTA takes a slice of the rows
+__global__ void __launch_bounds__(256)
+roi_count_kernel(const uint8_t* __restrict__ mask, int w, int h, const int* __restrict__ rois,
+                 unsigned int* __restrict__ counts) {
+  const int r = blockIdx.x;
+  const int x1 = rois[r * 4 + 0], y1 = rois[r * 4 + 1], x2 = rois[r * 4 + 2], y2 = rois[r * 4 + 3];
+  const int rw = x2 - x1, rh = y2 - y1;
+  if (rw <= 0 || rh <= 0) return;
+  const int rows_per = (rh + gridDim.y - 1) / gridDim.y;
+  const int ya = y1 + blockIdx.y * rows_per;
+  const int yb = min(ya + rows_per, y2);
+  unsigned int local = 0;
+  const int npx = (yb - ya) * rw;
+  for (int i = threadIdx.x; i < npx; i += 256) {
+    const int yy = i / rw, xx = i - yy * rw;
+    local += mask[(size_t)(ya + yy) * w + x1 + xx] != 0 ? 1u : 0u;
+  }
+  for (int off = 16; off > 0; off >>= 1) local += __shfl_xor_sync(0xffffffffu, local, off);
+  if ((threadIdx.x & 31) == 0 && local) atomicAdd(counts + r, local);
+}
+
+// ------------------------------------------------------------------ host launchers
+static size_t blur_smem(int ksize) {
+  const int R = ksize >> 1;
+  const int in_w = kBlurTW + 2 * R, in_h = kBlurTH + 2 * R;
+  return (size_t)((in_h * in_w + 15) & ~15) + (size_t)in_h * kBlurTW * 2;
+}
+
+int blur_launch(const uint8_t* src, const BlurArgs& a, uint8_t* dst, uint8_t* prev,
+                unsigned int* counter, cudaStream_t stream) {
+  static bool attr_done = false;
+  if (!attr_done) {
+    cudaFuncSetAttribute(blur_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                         (int)blur_smem(kBlurMaxK));
+    attr_done = true;
+  }
+  dim3 grid(cdiv(a.w, kBlurTW), cdiv(a.h, kBlurTH));
+  blur_kernel<<<grid, kBlurThreads, blur_smem(a.ksize), stream>>>(src, a, dst, prev, counter);
+  g_launch_count.fetch_add(1, std::memory_order_relaxed);
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) {
+    set_last_error("blur_kernel launch: %s", cudaGetErrorString(e));
+    return TCD_ERR_CUDA;
+  }
+  return TCD_OK;
+}
+
+int mog2_launch(const uint8_t* frame, const Mog2State& st, const Mog2Params& p, uint8_t* fgmask,
+                cudaStream_t stream) {
+  mog2_apply_kernel<<<cdiv(p.npix, 256), 256, 0, stream>>>(frame, st, p, fgmask);
+  g_launch_count.fetch_add(1, std::memory_order_relaxed);
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) {
+    set_last_error("mog2_apply_kernel launch: %s", cudaGetErrorString(e));
+    return TCD_ERR_CUDA;
+  }
+  return TCD_OK;
+}
+
+int threshold_launch(const uint8_t* src, int n, int thr, uint8_t* dst, cudaStream_t stream) {
+  threshold_kernel<<<cdiv(n, 256), 256, 0, stream>>>(src, n, thr, dst);
+  g_launch_count.fetch_add(1, std::memory_order_relaxed);
+  return cudaGetLastError() == cudaSuccess ? TCD_OK : TCD_ERR_CUDA;
+}
+
+int roi_count_launch(const uint8_t* mask, int w, int h, const int* rois_dev, int n,
+                     unsigned int* counts_dev, cudaStream_t stream) {
+  if (n <= 0) return TCD_OK;
+  roi_count_kernel<<<dim3(n, 16), 256, 0, stream>>>(mask, w, h, rois_dev, counts_dev);
+  g_launch_count.fetch_add(1, std::memory_order_relaxed);
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) {
+    set_last_error("roi_count_kernel launch: %s", cudaGetErrorString(e));
+    return TCD_ERR_CUDA;
+  }
+  return TCD_OK;
+}
+
+}  // namespace tcd

@@ -1,0 +1,288 @@
+// Decode + confidence filter + class-aware NMS (K4-K6), batched, warp-level.
+//
+// Replaces the YOLOX head decode [upstream yolo_head.py], yolox.utils.postprocess
+// [upstream boxes.py, SURVEY App. B] as called at src/yolox_detector.py:309-314,381-386, and
+// torchvision.ops.batched_nms in its coordinate-offset form (torchvision/ops/boxes.py:80-83):
+//   boxes_for_nms = boxes + class_id * (max_coordinate + 1)   (fp32)
+//   suppress j (lower score) when IoU(i, j) > nms_thre (strict), scores stable-descending.
+// This TU is compiled with -fmad=false so the IoU / decode arithmetic keeps the same
+// rounding sequence as the scalar reference code.
+//
+// Pipeline (fixed grids, thresholds read from device memory -> CUDA-graph friendly):
+//   1. decode_filter_kernel  one warp per anchor: sigmoid, arg-max over classes (first index
+//                            on ties), obj*cls >= conf -> append candidate
+//   2. sort_kernel           one CTA per frame: bitonic sort of 64-bit keys
+//                            (score desc, anchor asc), gather rows, offset boxes
+//   3. nms_mask_kernel       64x64 IoU tiles -> suppression bit matrix (upper triangle)
+//   4. nms_reduce_kernel     one CTA per frame: serial scan over the bit matrix staged in
+//                            shared memory, then parallel write of the kept rows
+#include "kernels.cuh"
+
+#include <atomic>
+
+namespace tcd {
+extern std::atomic<uint64_t> g_launch_count;
+
+__device__ __forceinline__ float sigmoid_acc(float x) { return 1.0f / (1.0f + expf(-x)); }
+
+__global__ void __launch_bounds__(256)
+decode_filter_kernel(const PostBuffers pb, const int raw) {
+  const int warp_global = (blockIdx.x * 256 + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  if (warp_global >= pb.B * pb.A) return;
+  const int b = warp_global / pb.A;
+  const int a = warp_global - b * pb.A;
+  const int E = 5 + pb.C;
+  const float* row = pb.pred + (size_t)warp_global * E;
+  float best = -1.0f;
+  int best_j = 0x7fffffff;
+  float head[3] = {0.f, 0.f, 0.f};
+  float dec[3];
+  int lvl = 0;
+  if (raw) {
+    while (lvl + 1 < pb.n_levels && a >= pb.lvl_start[lvl + 1]) ++lvl;
+  }
+#pragma unroll
+  for (int s = 0; s < 3; ++s) {
+    const int e = lane + 32 * s;
+    float v = 0.f;
+    if (e < E) {
+      v = row[e];
+      if (raw) {
+        if (e < 2) {
+          const int cell = a - pb.lvl_start[lvl];
+          const int gy = cell / pb.lvl_w[lvl], gx = cell - gy * pb.lvl_w[lvl];
+          v = (v + (float)(e == 0 ? gx : gy)) * (float)pb.lvl_stride[lvl];
+        } else if (e < 4) {
+          v = expf(v) * (float)pb.lvl_stride[lvl];
+        } else {
+          v = sigmoid_acc(v);
+        }
+      }
+      if (e >= 5) {
+        const int j = e - 5;
+        if (v > best) { best = v; best_j = j; }
+      }
+    }
+    dec[s] = v;
+    if (s == 0) head[0] = v;
+  }
+  if (pb.decoded != nullptr) {
+    float* drow = pb.decoded + (size_t)warp_global * E;
+#pragma unroll
+    for (int s = 0; s < 3; ++s) {
+      const int e = lane + 32 * s;
+      if (e < E) drow[e] = dec[s];
+    }
+  }
+  // arg-max over the warp, first index wins ties (torch.max semantics)
+#pragma unroll
+  for (int off = 16; off > 0; off >>= 1) {
+    const float ov = __shfl_xor_sync(0xffffffffu, best, off);
+    const int oj = __shfl_xor_sync(0xffffffffu, best_j, off);
+    if (ov > best || (ov == best && oj < best_j)) { best = ov; best_j = oj; }
+  }
+  const float cx = __shfl_sync(0xffffffffu, head[0], 0);
+  const float cy = __shfl_sync(0xffffffffu, head[0], 1);
+  const float w = __shfl_sync(0xffffffffu, head[0], 2);
+  const float h = __shfl_sync(0xffffffffu, head[0], 3);
+  const float obj = __shfl_sync(0xffffffffu, head[0], 4);
+  if (lane == 0) {
+    const float score = obj * best;
+    if (score >= pb.thr[0]) {
+      const int slot = atomicAdd(pb.cand_count + b, 1);
+      if (slot < pb.cap) {
+        float* c = pb.cand + ((size_t)b * pb.cap + slot) * 8;
+        c[0] = cx - w / 2.0f;
+        c[1] = cy - h / 2.0f;
+        c[2] = cx + w / 2.0f;
+        c[3] = cy + h / 2.0f;
+        c[4] = obj;
+        c[5] = best;
+        c[6] = (float)best_j;
+        c[7] = score;
+        pb.cand_anchor[(size_t)b * pb.cap + slot] = a;
+      }
+    }
+  }
+}
+
+__global__ void __launch_bounds__(1024) sort_kernel(const PostBuffers pb) {
+  extern __shared__ unsigned long long keys[];
+  __shared__ float s_max[32];
+  const int b = blockIdx.x;
+  int n = pb.cand_count[b];
+  if (n > pb.cap) n = pb.cap;
+  int P = 1;
+  while (P < n) P <<= 1;
+  const float* cand = pb.cand + (size_t)b * pb.cap * 8;
+  float lmax = -3.0e38f;
+  for (int i = threadIdx.x; i < P; i += 1024) {
+    unsigned long long k = 0ull;
+    if (i < n) {
+      const float* c = cand + (size_t)i * 8;
+      const unsigned int sb = __float_as_uint(c[7]);
+      const unsigned int an = (unsigned int)pb.cand_anchor[(size_t)b * pb.cap + i];
+      k = ((unsigned long long)sb << 32) | (unsigned long long)(((131071u - an) << 15) | (unsigned)i);
+      lmax = fmaxf(fmaxf(fmaxf(lmax, c[0]), fmaxf(c[1], c[2])), c[3]);
+    }
+    keys[i] = k;
+  }
+  // block max of coordinates
+  for (int off = 16; off > 0; off >>= 1) lmax = fmaxf(lmax, __shfl_xor_sync(0xffffffffu, lmax, off));
+  if ((threadIdx.x & 31) == 0) s_max[threadIdx.x >> 5] = lmax;
+  __syncthreads();
+  float maxc = s_max[0];
+  for (int i = 1; i < 32; ++i) maxc = fmaxf(maxc, s_max[i]);
+  // bitonic sort, descending
+  for (int k = 2; k <= P; k <<= 1) {
+    for (int j = k >> 1; j > 0; j >>= 1) {
+      for (int i = threadIdx.x; i < P; i += 1024) {
+        const int ixj = i ^ j;
+        if (ixj > i) {
+          const unsigned long long x = keys[i], y = keys[ixj];
+          const bool desc = ((i & k) == 0);
+          if (desc ? (x < y) : (x > y)) { keys[i] = y; keys[ixj] = x; }
+        }
+      }
+      __syncthreads();
+    }
+  }
+  const float off1 = maxc + 1.0f;
+  for (int i = threadIdx.x; i < n; i += 1024) {
+    const int slot = (int)(keys[i] & 0x7fffu);
+    const float* c = cand + (size_t)slot * 8;
+    float* o = pb.srec + ((size_t)b * pb.cap + i) * 8;
+#pragma unroll
+    for (int e = 0; e < 8; ++e) o[e] = c[e];
+    const float offs = c[6] * off1;
+    pb.sbox[(size_t)b * pb.cap + i] = make_float4(c[0] + offs, c[1] + offs, c[2] + offs, c[3] + offs);
+  }
+  if (threadIdx.x == 0) pb.n_sorted[b] = n;
+}
+
+__device__ __forceinline__ bool iou_gt(const float4 a, const float4 b, const float thr) {
+  const float left = fmaxf(a.x, b.x), right = fminf(a.z, b.z);
+  const float top = fmaxf(a.y, b.y), bottom = fminf(a.w, b.w);
+  const float width = fmaxf(right - left, 0.f), height = fmaxf(bottom - top, 0.f);
+  const float inter = width * height;
+  const float sa = (a.z - a.x) * (a.w - a.y);
+  const float sb = (b.z - b.x) * (b.w - b.y);
+  return (inter / (sa + sb - inter)) > thr;
+}
+
+__global__ void __launch_bounds__(64) nms_mask_kernel(const PostBuffers pb) {
+  __shared__ float4 cols[64];
+  const int b = blockIdx.y;
+  const int n = pb.n_sorted[b];
+  const int nb = (n + 63) >> 6;
+  const int words = pb.cap >> 6;
+  const int ntiles = nb * (nb + 1) / 2;
+  const float thr = pb.thr[1];
+  const float4* box = pb.sbox + (size_t)b * pb.cap;
+  for (int t = blockIdx.x; t < ntiles; t += gridDim.x) {
+    // decode (rb, cb), cb >= rb, row-major over the upper triangle
+    int rb = 0, rem = t;
+    while (rem >= nb - rb) { rem -= nb - rb; ++rb; }
+    const int cb = rb + rem;
+    const int j0 = cb * 64;
+    __syncthreads();
+    if (j0 + (int)threadIdx.x < n) cols[threadIdx.x] = box[j0 + threadIdx.x];
+    __syncthreads();
+    const int i = rb * 64 + threadIdx.x;
+    if (i < n) {
+      const float4 me = box[i];
+      const int ncol = min(64, n - j0);
+      unsigned long long bits = 0ull;
+      const int start = (rb == cb) ? (int)threadIdx.x + 1 : 0;
+      for (int j = start; j < ncol; ++j)
+        if (iou_gt(me, cols[j], thr)) bits |= 1ull << j;
+      pb.mask[((size_t)b * pb.cap + i) * words + cb] = bits;
+    }
+  }
+}
+
+__global__ void __launch_bounds__(256) nms_reduce_kernel(const PostBuffers pb, const int smem_rows) {
+  extern __shared__ unsigned long long sm[];
+  const int b = blockIdx.x;
+  const int n = pb.n_sorted[b];
+  const int nb = (n + 63) >> 6;
+  const int words = pb.cap >> 6;
+  unsigned long long* remv = sm;                 // [words]
+  int* keep = reinterpret_cast<int*>(sm + words);  // [cap]
+  unsigned long long* mrows = sm + words + (pb.cap + 1) / 2;  // [smem_rows * nb] when it fits
+  __shared__ int s_nk;
+  const unsigned long long* gmask = pb.mask + (size_t)b * pb.cap * words;
+  const bool staged = (n <= smem_rows) && ((size_t)n * nb <= (size_t)smem_rows * 16);
+  for (int i = threadIdx.x; i < nb; i += 256) remv[i] = 0ull;
+  if (staged) {
+    for (int i = threadIdx.x; i < n * nb; i += 256) {
+      const int r = i / nb, w = i - r * nb;
+      mrows[i] = (w >= (r >> 6)) ? gmask[(size_t)r * words + w] : 0ull;
+    }
+  }
+  __syncthreads();
+  if (threadIdx.x < 32) {
+    const int lane = threadIdx.x;
+    int nk = 0;
+    for (int i = 0; i < n; ++i) {
+      const int w = i >> 6;
+      const unsigned long long cur = remv[w];
+      if (!((cur >> (i & 63)) & 1ull)) {
+        if (lane == 0) keep[nk] = i;
+        ++nk;
+        if (staged) {
+          for (int ww = w + lane; ww < nb; ww += 32) remv[ww] |= mrows[i * nb + ww];
+        } else {
+          for (int ww = w + lane; ww < nb; ww += 32) remv[ww] |= gmask[(size_t)i * words + ww];
+        }
+        __syncwarp();
+      }
+    }
+    if (lane == 0) s_nk = nk;
+  }
+  __syncthreads();
+  int nk = s_nk;
+  if (nk > pb.max_out) nk = pb.max_out;
+  const float* srec = pb.srec + (size_t)b * pb.cap * 8;
+  float* out = pb.out_dets + (size_t)b * pb.max_out * 7;
+  for (int i = threadIdx.x; i < nk * 7; i += 256) {
+    const int r = i / 7, e = i - r * 7;
+    out[i] = srec[(size_t)keep[r] * 8 + e];
+  }
+  if (threadIdx.x == 0) pb.out_counts[b] = nk;
+}
+
+size_t post_reduce_smem_bytes(int cap, int smem_rows) {
+  const int words = cap >> 6;
+  return sizeof(unsigned long long) * ((size_t)words + (cap + 1) / 2 + (size_t)smem_rows * 16);
+}
+
+int postproc_launch(const PostBuffers& pb, int raw, cudaStream_t stream) {
+  static bool attr_done = false;
+  const int smem_rows = 1024;
+  const size_t red_smem = post_reduce_smem_bytes(pb.cap, smem_rows);
+  int P = 1;
+  while (P < pb.cap) P <<= 1;
+  const size_t sort_smem = (size_t)P * 8;
+  if (!attr_done) {
+    cudaFuncSetAttribute(sort_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sort_smem);
+    cudaFuncSetAttribute(nms_reduce_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)red_smem);
+    attr_done = true;
+  }
+  cudaMemsetAsync(pb.cand_count, 0, sizeof(int) * pb.B, stream);
+  const int warps = pb.B * pb.A;
+  decode_filter_kernel<<<cdiv(warps, 8), 256, 0, stream>>>(pb, raw);
+  sort_kernel<<<pb.B, 1024, sort_smem, stream>>>(pb);
+  nms_mask_kernel<<<dim3(296, pb.B), 64, 0, stream>>>(pb);
+  nms_reduce_kernel<<<pb.B, 256, red_smem, stream>>>(pb, smem_rows);
+  g_launch_count.fetch_add(4, std::memory_order_relaxed);
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) {
+    set_last_error("postproc launch: %s", cudaGetErrorString(e));
+    return TCD_ERR_CUDA;
+  }
+  return TCD_OK;
+}
+
+}  // namespace tcd

@@ -1,0 +1,221 @@
+// YOLOX-S plan builder + the three non-conv ops (nearest x2 upsample into a concat slice,
+// SPP max-pools).  See yolox_net.cuh.
+#include "yolox_net.cuh"
+
+#include <atomic>
+#include <string.h>
+
+namespace tcd {
+extern std::atomic<uint64_t> g_launch_count;
+
+// ------------------------------------------------------------------ weight blob
+// layout (little endian), written by telescope_cam_detection_b200/weights.py:
+//   char magic[8] = "TCDW0001"; u32 n_entries; u32 num_classes;
+//   per entry: char name[96]; i32 cout, cin, k, reserved; f32 w[cout*cin*k*k]; f32 b[cout]
+int WeightBlob::parse(const void* blob, size_t bytes) {
+  const uint8_t* p = (const uint8_t*)blob;
+  TCD_REQUIRE(bytes >= 16 && memcmp(p, "TCDW0001", 8) == 0, "weights: bad magic");
+  uint32_t n;
+  memcpy(&n, p + 8, 4);
+  size_t off = 16;
+  for (uint32_t i = 0; i < n; ++i) {
+    TCD_REQUIRE(off + 112 <= bytes, "weights: truncated at entry %u", i);
+    char name[97];
+    memcpy(name, p + off, 96);
+    name[96] = 0;
+    int32_t hdr[4];
+    memcpy(hdr, p + off + 96, 16);
+    off += 112;
+    WeightEntry e;
+    e.cout = hdr[0];
+    e.cin = hdr[1];
+    e.k = hdr[2];
+    TCD_REQUIRE(e.cout > 0 && e.cin > 0 && (e.k == 1 || e.k == 3), "weights: bad shape for %s", name);
+    const size_t nw = (size_t)e.cout * e.cin * e.k * e.k;
+    TCD_REQUIRE(off + (nw + e.cout) * 4 <= bytes, "weights: truncated data for %s", name);
+    e.w = (const float*)(p + off);
+    off += nw * 4;
+    e.b = (const float*)(p + off);
+    off += (size_t)e.cout * 4;
+    entries[name] = e;
+  }
+  return TCD_OK;
+}
+
+static int upload_conv(const std::vector<const WeightEntry*>& parts, int cin_pad, int cout_pad,
+                       DevConv* out) {
+  const int k = parts[0]->k, cin = parts[0]->cin;
+  int cout = 0;
+  for (auto* e : parts) {
+    TCD_REQUIRE(e->k == k && e->cin == cin, "weights: fused parts disagree on shape");
+    cout += e->cout;
+  }
+  if (cout_pad < cout) cout_pad = cout;
+  const int taps = k * k;
+  std::vector<uint16_t> hw((size_t)taps * cout_pad * cin_pad, 0);
+  std::vector<float> hb(cout_pad, 0.f);
+  int o0 = 0;
+  for (auto* e : parts) {
+    for (int o = 0; o < e->cout; ++o) {
+      hb[o0 + o] = e->b[o];
+      for (int c = 0; c < cin; ++c)
+        for (int t = 0; t < taps; ++t)
+          hw[((size_t)t * cout_pad + o0 + o) * cin_pad + c] =
+              f32_to_bf16_rn(e->w[((size_t)o * cin + c) * taps + t]);
+    }
+    o0 += e->cout;
+  }
+  TCD_CUDA_OK(cudaMalloc(&out->w, hw.size() * 2));
+  TCD_CUDA_OK(cudaMalloc((void**)&out->bias, hb.size() * 4));
+  TCD_CUDA_OK(cudaMemcpy(out->w, hw.data(), hw.size() * 2, cudaMemcpyHostToDevice));
+  TCD_CUDA_OK(cudaMemcpy(out->bias, hb.data(), hb.size() * 4, cudaMemcpyHostToDevice));
+  out->cout = cout;
+  out->cout_pad = cout_pad;
+  out->cin_pad = cin_pad;
+  out->k = k;
+  return TCD_OK;
+}
+
+int YoloxWeights::upload(const WeightBlob& blob) {
+  auto get = [&](const std::string& n) -> const WeightEntry* {
+    auto it = blob.entries.find(n);
+    return it == blob.entries.end() ? nullptr : &it->second;
+  };
+  auto one = [&](const std::string& dst, const std::string& src, int cin_pad = 0) -> int {
+    const WeightEntry* e = get(src);
+    TCD_REQUIRE(e != nullptr, "weights: missing entry %s", src.c_str());
+    return upload_conv({e}, cin_pad ? cin_pad : e->cin, 0, &convs[dst]);
+  };
+  auto fuse = [&](const std::string& dst, const std::string& a, const std::string& b,
+                  int cout_pad = 0) -> int {
+    const WeightEntry *ea = get(a), *eb = get(b);
+    TCD_REQUIRE(ea && eb, "weights: missing entry %s or %s", a.c_str(), b.c_str());
+    return upload_conv({ea, eb}, ea->cin, cout_pad, &convs[dst]);
+  };
+  int rc;
+#define W_TRY(x) do { rc = (x); if (rc) return rc; } while (0)
+  const std::string bb = "backbone.backbone.";
+  W_TRY(one("stem", bb + "stem.conv", 16));
+  auto csp = [&](const std::string& dst, const std::string& src, int n) -> int {
+    int r = fuse(dst + ".conv12", src + ".conv1", src + ".conv2");
+    if (r) return r;
+    for (int i = 0; i < n; ++i) {
+      const std::string m = ".m." + std::to_string(i);
+      if ((r = one(dst + m + ".conv1", src + m + ".conv1"))) return r;
+      if ((r = one(dst + m + ".conv2", src + m + ".conv2"))) return r;
+    }
+    return one(dst + ".conv3", src + ".conv3");
+  };
+  W_TRY(one("dark2.0", bb + "dark2.0"));
+  W_TRY(csp("dark2.1", bb + "dark2.1", 1));
+  W_TRY(one("dark3.0", bb + "dark3.0"));
+  W_TRY(csp("dark3.1", bb + "dark3.1", 3));
+  W_TRY(one("dark4.0", bb + "dark4.0"));
+  W_TRY(csp("dark4.1", bb + "dark4.1", 3));
+  W_TRY(one("dark5.0", bb + "dark5.0"));
+  W_TRY(one("dark5.1.conv1", bb + "dark5.1.conv1"));
+  W_TRY(one("dark5.1.conv2", bb + "dark5.1.conv2"));
+  W_TRY(csp("dark5.2", bb + "dark5.2", 1));
+  W_TRY(one("lateral_conv0", "backbone.lateral_conv0"));
+  W_TRY(csp("C3_p4", "backbone.C3_p4", 1));
+  W_TRY(one("reduce_conv1", "backbone.reduce_conv1"));
+  W_TRY(csp("C3_p3", "backbone.C3_p3", 1));
+  W_TRY(one("bu_conv2", "backbone.bu_conv2"));
+  W_TRY(csp("C3_n3", "backbone.C3_n3", 1));
+  W_TRY(one("bu_conv1", "backbone.bu_conv1"));
+  W_TRY(csp("C3_n4", "backbone.C3_n4", 1));
+  for (int l = 0; l < 3; ++l) {
+    const std::string s = std::to_string(l);
+    W_TRY(one("head.stem." + s, "head.stems." + s));
+    W_TRY(fuse("head.conv_a." + s, "head.cls_convs." + s + ".0", "head.reg_convs." + s + ".0"));
+    W_TRY(one("head.cls_b." + s, "head.cls_convs." + s + ".1"));
+    W_TRY(one("head.reg_b." + s, "head.reg_convs." + s + ".1"));
+    W_TRY(one("head.cls_pred." + s, "head.cls_preds." + s));
+    W_TRY(fuse("head.regobj_pred." + s, "head.reg_preds." + s, "head.obj_preds." + s, 16));
+    const WeightEntry* cp = get("head.cls_preds." + s);
+    num_classes = cp->cout;
+    TCD_REQUIRE(num_classes % 16 == 0, "weights: num_classes %d must be a multiple of 16", num_classes);
+  }
+#undef W_TRY
+  return TCD_OK;
+}
+
+void YoloxWeights::release() {
+  for (auto& kv : convs) {
+    if (kv.second.w) cudaFree(kv.second.w);
+    if (kv.second.bias) cudaFree(kv.second.bias);
+  }
+  convs.clear();
+}
+
+// ------------------------------------------------------------------ aux kernels
+// nearest x2 upsample of a channel slice into a channel slice (PAFPN top-down path)
+__global__ void __launch_bounds__(256)
+upsample2x_kernel(const uint4* __restrict__ src, uint4* __restrict__ dst, int N, int H, int W, int C8,
+                  int s_ctot8, int s_coff8, int d_ctot8, int d_coff8) {
+  const size_t total = (size_t)N * (2 * H) * (2 * W) * C8;
+  for (size_t i = (size_t)blockIdx.x * 256 + threadIdx.x; i < total; i += (size_t)gridDim.x * 256) {
+    const int c = (int)(i % C8);
+    size_t r = i / C8;
+    const int x = (int)(r % (2 * W));
+    r /= (2 * W);
+    const int y = (int)(r % (2 * H));
+    const int n = (int)(r / (2 * H));
+    const uint4 v = src[((size_t)((size_t)n * H + (y >> 1)) * W + (x >> 1)) * s_ctot8 + s_coff8 + c];
+    dst[((size_t)((size_t)n * 2 * H + y) * 2 * W + x) * d_ctot8 + d_coff8 + c] = v;
+  }
+}
+
+// SPPBottleneck pools: buf[..., 0:C] -> max 5x5 / 9x9 / 13x13 (stride 1, -inf padding) into
+// buf[..., C:2C], [2C:3C], [3C:4C].  One thread per (pixel, channel pair).
+__global__ void __launch_bounds__(256)
+spp_pool_kernel(__nv_bfloat162* __restrict__ buf, int N, int H, int W, int C2, int ctot2) {
+  const size_t total = (size_t)N * H * W * C2;
+  for (size_t i = (size_t)blockIdx.x * 256 + threadIdx.x; i < total; i += (size_t)gridDim.x * 256) {
+    const int c = (int)(i % C2);
+    size_t r = i / C2;
+    const int x = (int)(r % W);
+    r /= W;
+    const int y = (int)(r % H);
+    const int n = (int)(r / H);
+    float m5x = -INFINITY, m5y = -INFINITY, m9x = -INFINITY, m9y = -INFINITY, m13x = -INFINITY,
+          m13y = -INFINITY;
+    for (int dy = -6; dy <= 6; ++dy) {
+      const int yy = y + dy;
+      if (yy < 0 || yy >= H) continue;
+      for (int dx = -6; dx <= 6; ++dx) {
+        const int xx = x + dx;
+        if (xx < 0 || xx >= W) continue;
+        const float2 v = __bfloat1622float2(buf[((size_t)((size_t)n * H + yy) * W + xx) * ctot2 + c]);
+        const int ad = max(abs(dy), abs(dx));
+        m13x = fmaxf(m13x, v.x); m13y = fmaxf(m13y, v.y);
+        if (ad <= 4) { m9x = fmaxf(m9x, v.x); m9y = fmaxf(m9y, v.y); }
+        if (ad <= 2) { m5x = fmaxf(m5x, v.x); m5y = fmaxf(m5y, v.y); }
+      }
+    }
+    __nv_bfloat162* o = buf + ((size_t)((size_t)n * H + y) * W + x) * ctot2 + c;
+    o[C2] = __floats2bfloat162_rn(m5x, m5y);
+    o[2 * C2] = __floats2bfloat162_rn(m9x, m9y);
+    o[3 * C2] = __floats2bfloat162_rn(m13x, m13y);
+  }
+}
+
+int upsample2x_launch(const void* src, void* dst, int N, int H, int W, int C, int s_ctot, int s_coff,
+                      int d_ctot, int d_coff, cudaStream_t stream) {
+  const size_t total = (size_t)N * 4 * H * W * (C / 8);
+  const int blocks = (int)((total + 255) / 256 < 148 * 8 ? (total + 255) / 256 : 148 * 8);
+  upsample2x_kernel<<<blocks, 256, 0, stream>>>((const uint4*)src, (uint4*)dst, N, H, W, C / 8,
+                                                s_ctot / 8, s_coff / 8, d_ctot / 8, d_coff / 8);
+  g_launch_count.fetch_add(1, std::memory_order_relaxed);
+  return cudaGetLastError() == cudaSuccess ? TCD_OK : TCD_ERR_CUDA;
+}
+
+int spp_pool_launch(void* buf, int N, int H, int W, int C, int ctot, cudaStream_t stream) {
+  const size_t total = (size_t)N * H * W * (C / 2);
+  const int blocks = (int)((total + 255) / 256 < 148 * 8 ? (total + 255) / 256 : 148 * 8);
+  spp_pool_kernel<<<blocks, 256, 0, stream>>>((__nv_bfloat162*)buf, N, H, W, C / 2, ctot / 2);
+  g_launch_count.fetch_add(1, std::memory_order_relaxed);
+  return cudaGetLastError() == cudaSuccess ? TCD_OK : TCD_ERR_CUDA;
+}
+
+}  // namespace tcd
