@@ -1,0 +1,121 @@
+"""ctypes binding of libtcd.so (include/tcd.h).  No fallback: a missing library or a
+non-sm_100 device raises, it never silently routes to PyTorch or the CPU oracle."""
+import ctypes as C
+import os
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "libtcd.so")
+
+
+class TcdError(RuntimeError):
+    pass
+
+
+class PreprocCfg(C.Structure):
+    _fields_ = [("out_h", C.c_int32), ("out_w", C.c_int32), ("mode", C.c_int32),
+                ("swap_rb", C.c_int32), ("scale", C.c_float), ("mean", C.c_float * 3),
+                ("inv_std", C.c_float * 3), ("pad_value", C.c_float)]
+
+
+class DetectorCfg(C.Structure):
+    _fields_ = [("input_h", C.c_int32), ("input_w", C.c_int32), ("max_batch", C.c_int32),
+                ("num_classes", C.c_int32), ("max_out", C.c_int32), ("max_src_h", C.c_int32),
+                ("max_src_w", C.c_int32), ("pre", PreprocCfg)]
+
+
+def make_preproc_cfg(out_h, out_w, mode=0, swap_rb=0, scale=1.0, mean=(0.0, 0.0, 0.0),
+                     std=(1.0, 1.0, 1.0), pad_value=114.0):
+    cfg = PreprocCfg()
+    cfg.out_h, cfg.out_w, cfg.mode, cfg.swap_rb = int(out_h), int(out_w), int(mode), int(swap_rb)
+    cfg.scale = float(scale)
+    for i in range(3):
+        cfg.mean[i] = float(mean[i])
+        cfg.inv_std[i] = 1.0 / float(std[i])
+    cfg.pad_value = float(pad_value)
+    return cfg
+
+
+_P = C.c_void_p
+_I32P = C.POINTER(C.c_int32)
+_I64P = C.POINTER(C.c_int64)
+_F32P = C.POINTER(C.c_float)
+_U8P = C.POINTER(C.c_uint8)
+_PP = C.POINTER(C.c_void_p)
+
+# name -> (restype, argtypes); every symbol include/tcd.h declares
+SIGNATURES = {
+    "tcd_last_error": (C.c_char_p, []),
+    "tcd_version": (C.c_int, []),
+    "tcd_launch_count": (C.c_uint64, []),
+    "tcd_preprocess": (C.c_int, [C.POINTER(PreprocCfg), _PP, _I32P, _I32P, _I64P, C.c_int32, C.c_int32, _P, _P]),
+    "tcd_conv2d_nhwc_bf16": (C.c_int, [_P, C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_int32,
+                                       _F32P, _F32P, C.c_int32, C.c_int32, C.c_int32, C.c_int32, _P,
+                                       C.c_int32, C.c_int32, _P, C.c_int32, C.c_int32, _P]),
+    "tcd_create_detector": (C.c_int, [C.POINTER(DetectorCfg), _P, C.c_size_t, C.c_int32, _PP]),
+    "tcd_destroy_detector": (None, [_P]),
+    "tcd_detector_set_thresholds": (C.c_int, [_P, C.c_float, C.c_float]),
+    "tcd_detect_batch": (C.c_int, [_P, _PP, _I32P, _I32P, _I64P, C.c_int32, C.c_int32, _F32P, _I32P]),
+    "tcd_detect_batch_async": (C.c_int, [_P, C.c_int32, _PP, _I32P, _I32P, _I64P, C.c_int32, C.c_int32]),
+    "tcd_detect_batch_wait": (C.c_int, [_P, C.c_int32, _F32P, _I32P]),
+    "tcd_forward": (C.c_int, [_P, _PP, _I32P, _I32P, _I64P, C.c_int32, C.c_int32, _F32P]),
+    "tcd_postprocess": (C.c_int, [_P, _F32P, C.c_int32, _F32P, _I32P]),
+    "tcd_detector_num_anchors": (C.c_int32, [_P]),
+    "tcd_detector_last_timing": (C.c_int, [_P, _F32P]),
+    "tcd_detector_read_activation": (C.c_int, [_P, C.c_char_p, _F32P, C.c_size_t, _I32P]),
+    "tcd_mog2_create": (C.c_int, [C.c_int32, C.c_int32, C.c_int32, C.c_float, C.c_int32, C.c_int32, _PP]),
+    "tcd_mog2_destroy": (None, [_P]),
+    "tcd_mog2_reset": (C.c_int, [_P]),
+    "tcd_mog2_apply": (C.c_int, [_P, _P, C.c_int64, C.c_int32, C.c_int32, _P]),
+    "tcd_mog2_roi_counts": (C.c_int, [_P, C.c_int32, C.c_int32, C.c_int32, _I32P, C.c_int32, _I32P, _P]),
+    "tcd_empty_filter_create": (C.c_int, [C.c_int32, C.c_int32, C.c_int32, C.c_int32, _PP]),
+    "tcd_empty_filter_destroy": (None, [_P]),
+    "tcd_empty_filter_reset": (C.c_int, [_P]),
+    "tcd_empty_filter_step": (C.c_int, [_P, _P, C.c_int64, C.c_int32, C.c_int32, _I32P, _P]),
+    "tcd_crop_resize": (C.c_int, [_P, C.c_int32, C.c_int32, C.c_int64, _I32P, C.c_int32, C.c_int32,
+                                  C.POINTER(PreprocCfg), C.c_int32, _P, _P]),
+    "tcd_malloc_device": (C.c_int, [C.c_size_t, _PP]),
+    "tcd_free_device": (C.c_int, [_P]),
+    "tcd_malloc_pinned": (C.c_int, [C.c_size_t, _PP]),
+    "tcd_free_pinned": (C.c_int, [_P]),
+    "tcd_memcpy_h2d": (C.c_int, [_P, _P, C.c_size_t]),
+    "tcd_memcpy_d2h": (C.c_int, [_P, _P, C.c_size_t]),
+    "tcd_device_synchronize": (C.c_int, []),
+}
+
+_lib = None
+
+
+def load():
+    """Load libtcd.so (once).  Raises TcdError when it has not been built."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise TcdError("libtcd.so is missing (%s): run `python -c 'import __graft_entry__ as g; g.build()'` "
+                       "or `python telescope_cam_detection_b200/build.py`; there is no CPU fallback" % LIB_PATH)
+    lib = C.CDLL(LIB_PATH)
+    for name, (res, args) in SIGNATURES.items():
+        fn = getattr(lib, name)
+        fn.restype = res
+        fn.argtypes = args
+    _lib = lib
+    return lib
+
+
+def check(status, what=""):
+    if status != 0:
+        msg = load().tcd_last_error().decode("utf-8", "replace")
+        raise TcdError("%s failed (status %d): %s" % (what or "libtcd call", status, msg))
+
+
+def ptr_array(ptrs):
+    arr = (C.c_void_p * len(ptrs))(*[C.c_void_p(int(p)) for p in ptrs])
+    return arr
+
+
+def i32_array(vals):
+    return (C.c_int32 * len(vals))(*[int(v) for v in vals])
+
+
+def i64_array(vals):
+    return (C.c_int64 * len(vals))(*[int(v) for v in vals])

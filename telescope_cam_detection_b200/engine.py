@@ -1,0 +1,166 @@
+"""Thin Python handle classes over the libtcd C ABI (ctypes).  numpy for host buffers,
+torch only for device pointers handed in by the caller (GPU-tensor frames are part of the
+reference API, src/yolox_detector.py:197-203)."""
+import ctypes as C
+
+import numpy as np
+
+from . import _lib
+from ._lib import check
+
+
+def _is_torch(x):
+    return type(x).__module__.startswith("torch")
+
+
+def _frame_desc(frame):
+    """-> (ptr, h, w, row_stride_bytes, on_device, keepalive)"""
+    if _is_torch(frame):
+        t = frame
+        if t.dtype != __import__("torch").uint8:
+            raise TypeError("frames must be uint8, got %s" % t.dtype)
+        if t.ndim != 3 or t.shape[2] != 3:
+            raise ValueError("frame tensor must be HxWx3, got %s" % (tuple(t.shape),))
+        if t.stride(2) != 1 or t.stride(1) != 3:
+            t = t.contiguous()
+        on_dev = t.is_cuda
+        return t.data_ptr(), t.shape[0], t.shape[1], t.stride(0), on_dev, t
+    a = np.asarray(frame)
+    if a.dtype != np.uint8:
+        raise TypeError("frames must be uint8, got %s" % a.dtype)
+    if a.ndim != 3 or a.shape[2] != 3:
+        raise ValueError("frame must be HxWx3, got %s" % (a.shape,))
+    if a.strides[2] != 1 or a.strides[1] != 3:
+        a = np.ascontiguousarray(a)
+    return a.ctypes.data, a.shape[0], a.shape[1], a.strides[0], False, a
+
+
+class DetectorEngine:
+    """Owns one tcd_detector (weights, activation arenas, CUDA graphs) on one GPU."""
+
+    def __init__(self, weight_blob, input_size=(640, 640), max_batch=8, num_classes=80, max_out=1024,
+                 max_src=(1080, 1920), device=0, pre_mode=0, swap_rb=0, scale=1.0,
+                 mean=(0.0, 0.0, 0.0), std=(1.0, 1.0, 1.0), pad_value=114.0):
+        self.lib = _lib.load()
+        cfg = _lib.DetectorCfg()
+        cfg.input_h, cfg.input_w = int(input_size[0]), int(input_size[1])
+        cfg.max_batch, cfg.num_classes, cfg.max_out = int(max_batch), int(num_classes), int(max_out)
+        cfg.max_src_h, cfg.max_src_w = int(max_src[0]), int(max_src[1])
+        cfg.pre = _lib.make_preproc_cfg(input_size[0], input_size[1], pre_mode, swap_rb, scale, mean, std, pad_value)
+        self.cfg = cfg
+        self.max_batch, self.max_out, self.num_classes = cfg.max_batch, cfg.max_out, cfg.num_classes
+        self._blob = bytes(weight_blob)
+        h = C.c_void_p()
+        check(self.lib.tcd_create_detector(C.byref(cfg), self._blob, len(self._blob), int(device), C.byref(h)),
+              "tcd_create_detector")
+        self.handle = h
+        self.n_anchors = self.lib.tcd_detector_num_anchors(h)
+        self._out = np.zeros((self.max_batch, self.max_out, 7), np.float32)
+        self._cnt = np.zeros((self.max_batch,), np.int32)
+        self._pending = {}
+
+    def close(self):
+        if getattr(self, "handle", None):
+            self.lib.tcd_destroy_detector(self.handle)
+            self.handle = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def set_thresholds(self, conf, nms):
+        check(self.lib.tcd_detector_set_thresholds(self.handle, float(conf), float(nms)), "tcd_detector_set_thresholds")
+
+    def _marshal(self, frames):
+        if not 1 <= len(frames) <= self.max_batch:
+            raise ValueError("batch of %d frames outside [1, %d]" % (len(frames), self.max_batch))
+        descs = [_frame_desc(f) for f in frames]
+        on_dev = {d[4] for d in descs}
+        if len(on_dev) != 1:
+            raise ValueError("a batch must be all host frames or all device frames")
+        return (_lib.ptr_array([d[0] for d in descs]), _lib.i32_array([d[1] for d in descs]),
+                _lib.i32_array([d[2] for d in descs]), _lib.i64_array([d[3] for d in descs]),
+                len(descs), 1 if on_dev.pop() else 0, [d[5] for d in descs])
+
+    def _rows(self, B):
+        return [self._out[b, : self._cnt[b]].copy() for b in range(B)]
+
+    def detect_batch(self, frames):
+        """frames: list of HxWx3 uint8 (numpy, or torch CUDA tensors).  -> list of [n,7] float32 arrays
+        [x1,y1,x2,y2,obj_conf,class_conf,class_id] in network-input pixels, score-descending."""
+        p, h, w, s, B, dev, keep = self._marshal(frames)
+        check(self.lib.tcd_detect_batch(self.handle, p, h, w, s, B, dev,
+                                        self._out.ctypes.data_as(_lib._F32P), self._cnt.ctypes.data_as(_lib._I32P)),
+              "tcd_detect_batch")
+        return self._rows(B)
+
+    def submit(self, slot, frames):
+        p, h, w, s, B, dev, keep = self._marshal(frames)
+        check(self.lib.tcd_detect_batch_async(self.handle, int(slot), p, h, w, s, B, dev), "tcd_detect_batch_async")
+        self._pending[slot] = (B, keep)
+
+    def wait(self, slot):
+        B, _ = self._pending.pop(slot)
+        check(self.lib.tcd_detect_batch_wait(self.handle, int(slot), self._out.ctypes.data_as(_lib._F32P),
+                                             self._cnt.ctypes.data_as(_lib._I32P)), "tcd_detect_batch_wait")
+        return self._rows(B)
+
+    def forward(self, frames):
+        p, h, w, s, B, dev, keep = self._marshal(frames)
+        out = np.empty((B, self.n_anchors, 5 + self.num_classes), np.float32)
+        check(self.lib.tcd_forward(self.handle, p, h, w, s, B, dev, out.ctypes.data_as(_lib._F32P)), "tcd_forward")
+        return out
+
+    def postprocess(self, pred):
+        pred = np.ascontiguousarray(pred, np.float32)
+        B = pred.shape[0]
+        check(self.lib.tcd_postprocess(self.handle, pred.ctypes.data_as(_lib._F32P), B,
+                                       self._out.ctypes.data_as(_lib._F32P), self._cnt.ctypes.data_as(_lib._I32P)),
+              "tcd_postprocess")
+        return self._rows(B)
+
+    def last_timing(self):
+        t = (C.c_float * 5)()
+        check(self.lib.tcd_detector_last_timing(self.handle, t), "tcd_detector_last_timing")
+        return dict(zip(("h2d_ms", "preprocess_ms", "network_post_ms", "_", "d2h_ms"), list(t)))
+
+    def read_activation(self, name):
+        shape = (C.c_int32 * 4)()
+        check(self.lib.tcd_detector_read_activation(self.handle, name.encode(), None, 0, shape), "read_activation")
+        out = np.empty(tuple(shape), np.float32)
+        check(self.lib.tcd_detector_read_activation(self.handle, name.encode(), out.ctypes.data_as(_lib._F32P),
+                                                    out.size, shape), "read_activation")
+        return out
+
+
+def preprocess(frames_dev_ptrs, hs, ws, strides, out_ptr, out_size, layout=0, mode=0, swap_rb=0, scale=1.0,
+               mean=(0.0, 0.0, 0.0), std=(1.0, 1.0, 1.0), pad_value=114.0):
+    lib = _lib.load()
+    cfg = _lib.make_preproc_cfg(out_size[0], out_size[1], mode, swap_rb, scale, mean, std, pad_value)
+    check(lib.tcd_preprocess(C.byref(cfg), _lib.ptr_array(frames_dev_ptrs), _lib.i32_array(hs), _lib.i32_array(ws),
+                             _lib.i64_array(strides), len(hs), int(layout), C.c_void_p(int(out_ptr)), None),
+          "tcd_preprocess")
+
+
+def conv2d_nhwc_bf16(x_ptr, N, H, W, x_ctot, x_coff, cin, w, bias, k, stride, silu, y_ptr, y_ctot, y_coff,
+                     resid_ptr=0, r_ctot=0, r_coff=0):
+    lib = _lib.load()
+    w = np.ascontiguousarray(w, np.float32)
+    bias = np.ascontiguousarray(bias, np.float32)
+    cout = w.shape[0]
+    check(lib.tcd_conv2d_nhwc_bf16(C.c_void_p(int(x_ptr)), N, H, W, x_ctot, x_coff, cin,
+                                   w.ctypes.data_as(_lib._F32P), bias.ctypes.data_as(_lib._F32P), cout, k, stride,
+                                   int(silu), C.c_void_p(int(resid_ptr)) if resid_ptr else None, r_ctot, r_coff,
+                                   C.c_void_p(int(y_ptr)), y_ctot, y_coff, None), "tcd_conv2d_nhwc_bf16")
+
+
+def crop_resize(frame_ptr, h, w, stride, boxes, S, out_ptr, layout=0, swap_rb=1, scale=1.0 / 255.0,
+                mean=(0.485, 0.456, 0.406), std=(0.229, 0.224, 0.225)):
+    lib = _lib.load()
+    boxes = np.ascontiguousarray(boxes, np.int32).reshape(-1, 4)
+    cfg = _lib.make_preproc_cfg(S, S, 0, swap_rb, scale, mean, std, 0.0)
+    check(lib.tcd_crop_resize(C.c_void_p(int(frame_ptr)), int(h), int(w), int(stride),
+                              boxes.ctypes.data_as(_lib._I32P), boxes.shape[0], int(S), C.byref(cfg), int(layout),
+                              C.c_void_p(int(out_ptr)), None), "tcd_crop_resize")

