@@ -1,0 +1,347 @@
+#!/usr/bin/env python
+"""bench.py -- YOLOX-S frames/sec through libtcd on B200 (BASELINE.json metric, configs[1]).
+
+  python bench.py --gpus N --steps K --warmup W              our arm (one rank per GPU under torchrun)
+  python bench.py --impl reference --gpus N --steps K ...    the reference's CPU data path (oracle port)
+
+A step = one detect_batch over one batch of 8 synthetic 1080p BGR frames: preprocess ->
+YOLOX-S -> decode / confidence filter / class-aware NMS -> result table on the host.
+`value`   frames/s with the frames already resident in HBM (two pipeline slots in flight),
+`e2e`     the same through the public call with HOST (pinned) frames: H2D of every frame and
+          D2H of the result table inside the timed region,
+`roofline` the tcgen05 conv family: conv FLOPs of a step / summed conv-kernel device time,
+`cpu_baseline` the oracle port of the reference path on this box's host cores (reported, not a target).
+Multi-GPU: camera streams shard by rank, a replica per GPU, no collective on the compute path;
+the result tables are gathered to rank 0 over NCCL (weak scaling).
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+METRIC = "YOLOX-S frames/sec (1080p in, 640 in-net, preprocess->detect->NMS)"
+UNIT = "frames/s"
+WORKLOAD = "YOLOX-S batch of 8 synthetic 1080p camera frames -> 640 letterbox + decode/NMS on 1 B200"
+FRAME_H, FRAME_W = 1080, 1920
+POOL_FRAMES = 32  # 32 x 6.2 MB = 199 MB > 126 MB L2: every step reads frames that left the cache
+CONV_GFLOP_PER_FRAME = 26.686  # SURVEY.md section 8(d), 2 x 13.343 GMAC over the 83 convs at 640x640
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=200)
+    ap.add_argument("--warmup", type=int, default=20)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--batch", type=int, default=8)
+    ap.add_argument("--pre", default="letterbox", choices=["letterbox", "stretch"],
+                    help="letterbox = BASELINE.json metric; stretch = what the reference code does (SURVEY F3)")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--profile-iters", type=int, default=10)
+    return ap.parse_args()
+
+
+def synth_frame(seed, h=FRAME_H, w=FRAME_W):
+    """Structured synthetic camera frame (8x8 blocks + noise), same generator as tests/util.py."""
+    rng = np.random.default_rng(seed)
+    base = rng.integers(0, 255, (h // 8 + 1, w // 8 + 1, 3), dtype=np.uint8)
+    img = np.repeat(np.repeat(base, 8, 0), 8, 1)[:h, :w].astype(np.int16)
+    img += rng.integers(-20, 20, (h, w, 3), dtype=np.int16)
+    return np.clip(img, 0, 255).astype(np.uint8)
+
+
+def measured_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        with open(p) as f:
+            d = json.load(f)
+        return {"hbm_gbs": d["hbm_gbs"], "tf_burst": d["bf16_tflops"], "tf_sustained": d["bf16_tflops_sustained"],
+                "src": "measured"}
+    return {"hbm_gbs": 6650.0, "tf_burst": 1590.0, "tf_sustained": 1400.0, "src": "fallback"}
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled every 200 ms during the timed region."""
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "200"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._pump, daemon=True)
+            self.t.start()
+        except OSError:
+            self.proc = None
+
+    def _pump(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.25)
+        self.proc.terminate()
+        self.t.join(timeout=2)
+        sm = [float(r[0]) for r in self.rows if r and r[0].replace(".", "").isdigit()]
+        mx = [float(r[1]) for r in self.rows if len(r) > 1 and r[1].replace(".", "").isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for i, n in enumerate(names) if any(len(r) > 2 + i and r[2 + i] == "Active" for r in self.rows)]
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": reasons, "samples": len(sm)}
+
+
+# ----------------------------------------------------------------------------- CPU arms
+def _oracle_detector():
+    import torch
+    from oracle import synth_weights
+    from oracle.reference_detector import ReferenceYOLOXDetector
+    torch.set_num_threads(max(1, os.cpu_count() or 1))
+    model = synth_weights.make_model(seed=0)
+    return ReferenceYOLOXDetector(model, 0.25, 0.45, (640, 640), wildlife_only=True), torch.get_num_threads()
+
+
+def cpu_baseline(budget_s=12.0, chunk=4, max_frames=48):
+    """Oracle port of the reference path on the host cores, bounded sample (~10-20 s)."""
+    det, threads = _oracle_detector()
+    frames = [synth_frame(100 + i) for i in range(chunk)]
+    det.detect_batch(frames[:2])  # warm-up (thread pool, allocator)
+    n, t0 = 0, time.perf_counter()
+    while n < max_frames and time.perf_counter() - t0 < budget_s:
+        det.detect_batch(frames)
+        n += chunk
+    dt = time.perf_counter() - t0
+    return {"value": n / dt, "unit": UNIT, "cores": threads, "kind": "port",
+            "sample": "%d synthetic 1080p frames in batches of %d through oracle/reference_detector.py "
+                      "(stretch preprocess + YOLOX-S fp32 + postprocess + dict format), %.1f s" % (n, chunk, dt)}
+
+
+def run_reference(args):
+    """--impl reference: the reference's CPU implementation of the path (oracle port: the reference is
+    Python over an un-vendored YOLOX checkout and cannot travel to the GPU box)."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    det, threads = _oracle_detector()
+    pool = [synth_frame(100 + i) for i in range(args.batch)]
+    t0 = time.perf_counter()
+    det.detect_batch(pool[:1])
+    det.detect_batch(pool[:1])
+    t_frame = (time.perf_counter() - t0) / 2
+    # bounded sample: frames per step sized so K + W steps end within ~150 s
+    fps_budget = 150.0 / max(1e-3, t_frame * (args.steps + args.warmup))
+    per_step = int(max(1, min(args.batch, fps_budget)))
+    for i in range(args.warmup):
+        det.detect_batch(pool[:per_step])
+    t0 = time.perf_counter()
+    for i in range(args.steps):
+        det.detect_batch(pool[:per_step])
+    dt = time.perf_counter() - t0
+    fps = per_step * args.steps / dt
+    sample = ("each step = %d of the %d frames of the batch through oracle/reference_detector.py on %d host threads "
+              "(stretch preprocess as the reference code does, YOLOX-S fp32, postprocess, dict format)"
+              % (per_step, args.batch, threads))
+    line = {"impl": "reference", "metric": METRIC, "value": fps, "unit": UNIT, "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+            "data": "synthetic", "config": {"workload": WORKLOAD, "batch": args.batch, "frames_per_step": per_step,
+                                            "frame": [FRAME_H, FRAME_W, 3], "input_size": [640, 640]},
+            "cpu_baseline": {"value": fps, "unit": UNIT, "cores": threads, "kind": "port", "sample": sample},
+            "e2e": {"value": fps, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+
+
+# ----------------------------------------------------------------------------- GPU arm
+def _pipelined(eng, batches, steps, on_result=None):
+    """steps x detect_batch with both pipeline slots in flight (H2D of k+1 overlaps compute of k)."""
+    nb = len(batches)
+    for i in range(steps):
+        slot = i & 1
+        if i >= 2:
+            rows = eng.wait(slot)
+            if on_result:
+                on_result(rows)
+        eng.submit(slot, batches[i % nb])
+    for i in range(max(0, steps - 2), steps):
+        rows = eng.wait(i & 1)
+        if on_result:
+            on_result(rows)
+
+
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+    from oracle import synth_weights  # synthetic weight GENERATOR only (seeded init); nothing computed by it is timed
+    from telescope_cam_detection_b200 import _lib, weights
+    from telescope_cam_detection_b200.engine import DetectorEngine
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    B = args.batch
+    lib = _lib.load()
+
+    blob = weights.pack_yolox(synth_weights.make_model(seed=0).state_dict())
+    eng = DetectorEngine(blob, input_size=(640, 640), max_batch=B, max_out=300, max_src=(FRAME_H, FRAME_W),
+                         device=local, pre_mode=1 if args.pre == "letterbox" else 0)
+    # per-rank streams: rank r owns frames seeded r*POOL.. (its cameras); weak scaling
+    host_pool = torch.empty((POOL_FRAMES, FRAME_H, FRAME_W, 3), dtype=torch.uint8, pin_memory=True)
+    for i in range(POOL_FRAMES):
+        host_pool[i] = torch.from_numpy(synth_frame(1000 * rank + i))
+    dev_pool = host_pool.cuda()
+    host_np = host_pool.numpy()
+    nb = POOL_FRAMES // B
+    dev_batches = [[dev_pool[b * B + j] for j in range(B)] for b in range(nb)]
+    host_batches = [[host_np[b * B + j] for j in range(B)] for b in range(nb)]
+    s0 = torch.cuda.ExternalStream(eng.stream(0), device=local)
+    s1 = torch.cuda.ExternalStream(eng.stream(1), device=local)
+
+    gather_buf = torch.zeros((B, 300, 7), dtype=torch.float32, device="cuda")
+    gathered = [torch.zeros_like(gather_buf) for _ in range(world)] if (world > 1 and rank == 0) else None
+    det_count = [0]
+
+    def on_result(rows):
+        det_count[0] += sum(r.shape[0] for r in rows)
+        if world > 1:  # detections -> rank 0 for serving; side traffic, not on the compute path
+            for b, r in enumerate(rows):
+                gather_buf[b, : r.shape[0]].copy_(torch.from_numpy(r), non_blocking=True)
+            dist.gather(gather_buf, gathered, dst=0)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(batches, steps, cb):
+        barrier()
+        e0, e1a, e1b = (torch.cuda.Event(enable_timing=True) for _ in range(3))
+        e0.record(s0)
+        s1.wait_event(e0)
+        n0 = lib.tcd_launch_count()
+        t0 = time.perf_counter()
+        _pipelined(eng, batches, steps, cb)
+        e1a.record(s0)
+        e1b.record(s1)
+        barrier()
+        wall = time.perf_counter() - t0
+        ms = max(e0.elapsed_time(e1a), e0.elapsed_time(e1b))
+        if world > 1:
+            t = torch.tensor([ms], device="cuda")
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms = float(t.item())
+        return ms, lib.tcd_launch_count() - n0, wall
+
+    # ---- device-resident frames (value)
+    _pipelined(eng, dev_batches, max(3, args.warmup))
+    sampler = ClockSampler(local) if rank == 0 else None
+    if sampler:
+        sampler.start()
+    ms_dev, launches, _ = timed(dev_batches, args.steps, None)
+    # ---- host frames through the public call (e2e)
+    _pipelined(eng, host_batches, max(3, args.warmup))
+    ms_e2e, _, wall_e2e = timed(host_batches, args.steps, on_result)
+    clocks = sampler.stop() if sampler else None
+    fps_dev = world * B * args.steps / (ms_dev * 1e-3)
+    fps_e2e = world * B * args.steps / (ms_e2e * 1e-3)
+
+    # ---- synchronous single-batch latency (p50), host frames
+    lat = []
+    for i in range(30):
+        t0 = time.perf_counter()
+        eng.detect_batch(host_batches[i % nb])
+        lat.append(1e3 * (time.perf_counter() - t0))
+    phases = eng.last_timing()
+
+    if rank != 0:
+        if world > 1:
+            dist.barrier()
+            dist.destroy_process_group()
+        return
+
+    # ---- per-kernel device times (eager pass, event pair per kernel) -> roofline of the conv family
+    peaks = measured_peaks()
+    prof = eng.profile(dev_batches[0], iters=args.profile_iters)
+    prof = eng.profile(dev_batches[1 % nb], iters=args.profile_iters)
+    conv_ms = sum(o["ms"] for o in prof if o["kind"] == "conv")
+    conv_fl = sum(o["flops"] for o in prof if o["kind"] == "conv")
+    all_ms = sum(o["ms"] for o in prof)
+    n_conv = sum(1 for o in prof if o["kind"] == "conv")
+    achieved = conv_fl / (conv_ms * 1e-3) / 1e12
+    traffic = None
+    tpath = os.path.join(ROOT, "profiles", "traffic.json")
+    if os.path.exists(tpath):
+        with open(tpath) as f:
+            traffic = json.load(f).get("conv_umma_kernel_dram_bytes_per_step")
+    roofline = {"bound": "tensor", "kernel": "conv_umma_kernel (%d launches/step, tcgen05 implicit GEMM)" % n_conv,
+                "achieved": achieved, "peak": peaks["tf_burst"], "unit": "TFLOP/s", "frac": achieved / peaks["tf_burst"],
+                "peak_source": "%s bf16 burst (each kernel timed alone by its own event pair)" % peaks["src"],
+                "flops_per_step": conv_fl, "kernel_ms_per_step": conv_ms, "share_of_step": conv_ms / all_ms,
+                "traffic": traffic}
+    pre = prof[0]
+    pre_bytes = B * (FRAME_H * FRAME_W * 3 + 640 * 640 * 4 * 2)
+    if args.pre == "letterbox":  # only the source rows the 640x360 content taps are algorithmically needed
+        pre_bytes = B * (2 * 360 * FRAME_W * 3 + 640 * 640 * 4 * 2)
+    post_ms = sum(o["ms"] for o in prof[-4:])
+    kernels = {
+        "preprocess": {"ms": pre["ms"], "GB/s": pre_bytes / (pre["ms"] * 1e-3) / 1e9,
+                       "frac_hbm": pre_bytes / (pre["ms"] * 1e-3) / 1e9 / peaks["hbm_gbs"], "bytes": pre_bytes},
+        "decode_nms": {"ms": post_ms, "GB/s": B * 8400 * 85 * 4 / (post_ms * 1e-3) / 1e9},
+        "other_layers_ms": sum(o["ms"] for o in prof[1:-4] if o["kind"] != "conv"),
+        "eager_step_ms": all_ms,
+    }
+    slow = sorted((o for o in prof if o["kind"] == "conv"), key=lambda o: -o["ms"])[:8]
+    kernels["slowest_convs"] = [{"name": o["name"], "ms": round(o["ms"], 4),
+                                 "TFLOP/s": round(o["flops"] / (o["ms"] * 1e-3) / 1e12, 1)} for o in slow]
+
+    cpu = None if args.no_cpu_baseline or world > 1 else cpu_baseline()
+    line = {
+        "metric": METRIC, "value": fps_dev, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": ms_dev / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "bf16", "data": "synthetic",
+        "config": {"workload": WORKLOAD, "batch": B, "frame": [FRAME_H, FRAME_W, 3], "input_size": [640, 640],
+                   "preprocess": args.pre, "conf": 0.25, "nms": 0.45, "weights": "seeded random init (oracle/synth_weights.py)",
+                   "parallelism": "replica per GPU, streams sharded by rank" if world > 1 else "1 GPU",
+                   "l2": "inputs larger than L2: %d-frame pool (%.0f MB) cycled" % (POOL_FRAMES, POOL_FRAMES * 6.2208),
+                   "pipeline": "2 slots in flight, CUDA graph per slot"},
+        "e2e": {"value": fps_e2e, "unit": UNIT, "h2d_bytes_per_step": B * FRAME_H * FRAME_W * 3,
+                "d2h_bytes_per_step": B * 300 * 7 * 4 + B * 4, "ms_per_step": ms_e2e / args.steps,
+                "wall_fps": world * B * args.steps / wall_e2e, "detections": det_count[0]},
+        "latency_ms_p50_sync_batch": float(np.median(lat)), "phases_ms_sync_batch": phases,
+        "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline, "kernels": kernels,
+        "cpu_baseline": cpu,
+    }
+    print(json.dumps(line), flush=True)
+    eng.close()
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def main():
+    args = parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

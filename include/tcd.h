@@ -122,6 +122,19 @@ int32_t tcd_detector_num_anchors(const tcd_detector* det);
 /* per-phase device times of the last synchronous detect_batch, ms:
  * [0]=h2d [1]=preprocess [2]=network [3]=decode+nms [4]=d2h                              */
 tcd_status tcd_detector_last_timing(const tcd_detector* det, float out_ms[5]);
+/* CUDA stream (cudaStream_t) the handle launches pipeline slot 0/1 on -- lets a caller record
+ * its own events around async calls (bench.py times with events on THIS stream).           */
+void* tcd_detector_stream(tcd_detector* det, int32_t slot);
+/* Measurement aid: one eager (graph-less) pass per iteration with a CUDA-event pair around every
+ * kernel.  Ops in launch order: 0 = preprocess, 1..n_layers = layer plan (tcgen05 convs,
+ * upsample, SPP pool), then decode_filter, sort, nms_mask, nms_reduce.  op_ms[i] = mean ms.  */
+tcd_status tcd_detector_profile(tcd_detector* det, const uint8_t* const* frames, const int32_t* h,
+                                const int32_t* w, const int64_t* row_stride, int32_t B,
+                                int32_t frames_on_device, int32_t iters, float* op_ms, int32_t cap,
+                                int32_t* n_ops);
+const char* tcd_detector_op_name(tcd_detector* det, int32_t B, int32_t idx);
+int32_t tcd_detector_op_kind(tcd_detector* det, int32_t B, int32_t idx); /* 0 conv, 1 other */
+double tcd_detector_op_flops(tcd_detector* det, int32_t B, int32_t idx); /* 2*MACs, convs only */
 /* debug tap: copy activation buffer `name` (bf16 NHWC) of the last forward to HOST as f32 */
 tcd_status tcd_detector_read_activation(tcd_detector* det, const char* name, float* out_host,
                                         size_t out_elems, int32_t* shape4);

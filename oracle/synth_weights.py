@@ -4,10 +4,23 @@ The real yolox_s.pth cannot be downloaded here (no network; BASELINE.json asks f
 synthetic data / random-init weights).  Upstream's default init gives zero detections
 on random weights, so (SURVEY.md section 8d "Weights for parity"):
   * conv weights: torch default init under torch.manual_seed(seed)
-  * BN: gamma~U(0.5,1.5), beta~N(0,0.1); running stats CALIBRATED on one seeded noise
-    frame (trained-network-like activation scale), then perturbed a little
-  * head obj/cls biases shifted so a few % of the 8400 anchors pass conf 0.25; w/h bias > 0 so
-    neighbouring boxes overlap and NMS suppresses a good share of them
+  * BN: running stats CALIBRATED on two seeded frames (one structured, one white noise), then
+    perturbed a little; gamma~U(0.05,0.15), beta~N(0,0.02).
+    WHY SO SMALL A GAMMA: a random-weight BN+SiLU stack is chaotic -- every layer multiplies a
+    relative perturbation by ~1.2 (mean-field correlation slope of SiLU at unit pre-activation
+    variance), so the 2^-9 rounding of a 16-bit activation format grows ~100x over the 54
+    roundings of the longest path and ANY bf16 implementation (including a CPU emulation that
+    rounds fp32 results to bf16 at the same points, oracle/yolox_lowp.py) ends 0.5 away from
+    the fp32 scores.  Trained networks are not chaotic.  Small gamma keeps SiLU in its
+    near-linear range around 0, the slope drops to ~1.0 and the rounding noise only
+    accumulates in quadrature (~0.8 % at the head features, the floor for 54 bf16 roundings).
+  * prediction convs: rescaled so obj/cls logits have std 0.4 and box logits std 0.05 on the
+    calibration frames: 0.8 % feature noise x 0.4 x 4.5 sigma x sigmoid'(<=0.25) keeps bf16
+    scores within ~7e-3 of fp32 (north_star tolerance 1e-2) and boxes within ~0.35 px (0.5)
+  * head obj/cls biases shifted so 4-7 % of the 8400 anchors pass conf 0.25; a few classes get
+    a larger bias so neighbouring anchors share classes; w/h bias 1.3 (boxes 3.7 strides wide)
+    puts adjacent-anchor IoU at ~0.57 and diagonal IoU at ~0.36, away from nms_thre 0.45, so
+    class-aware NMS removes ~20 % of the candidates
 """
 import numpy as np
 import torch
@@ -33,9 +46,9 @@ def preprocess_ref(img, size=(640, 640)):
 
 
 @torch.no_grad()
-def make_model(seed=0, calibrate=True, obj_bias=-5.5, cls_bias=-3.0, wh_bias=1.5,
-               obj_std=1.5, cls_std=1.0, reg_std=0.5,
-               gamma=(0.5, 1.5), beta=(0.0, 0.1)):
+def make_model(seed=0, calibrate=True, obj_bias=-1.0, cls_bias=-2.4, wh_bias=1.3,
+               obj_std=0.4, cls_std=0.4, reg_std=0.05, cls_boost=3.0,
+               gamma=(0.05, 0.15), beta=(0.0, 0.02)):
     torch.manual_seed(seed)
     model = get_exp(None, "yolox-s").get_model()
     model.eval()
@@ -46,7 +59,9 @@ def make_model(seed=0, calibrate=True, obj_bias=-5.5, cls_bias=-3.0, wh_bias=1.5
         bn.weight.copy_(torch.rand(c, generator=g) * (gamma[1] - gamma[0]) + gamma[0])
         bn.bias.copy_(torch.randn(c, generator=g) * beta[1] + beta[0])
     if calibrate:
-        x = preprocess_ref(calib_frame())
+        # one structured and one white-noise frame, so both kinds of test input are in-distribution
+        noise = np.random.default_rng(4321).integers(0, 255, (1080, 1920, 3), dtype=np.uint8)
+        x = torch.cat([preprocess_ref(calib_frame()), preprocess_ref(noise)], 0)
         # sequential calibration: each BN sees inputs produced by already-calibrated layers
         hooks = []
 
@@ -91,8 +106,12 @@ def make_model(seed=0, calibrate=True, obj_bias=-5.5, cls_bias=-3.0, wh_bias=1.5
         conv.bias[2:4] = wh_bias  # boxes ~exp(1.5) strides wide: neighbours overlap, NMS has work to do
     for conv in model.head.obj_preds:
         conv.bias.fill_(obj_bias)
+    # a handful of classes (the reference's wildlife set among them) get a head start, so that
+    # neighbouring anchors often agree on the class and class-aware NMS has overlaps to resolve
+    boost = torch.zeros(model.head.num_classes)
+    boost[[0, 14, 15, 16, 21, 2, 56]] = torch.tensor([0.6, 0.5, 0.7, 0.6, 0.5, 0.4, 0.4]) * cls_boost
     for conv in model.head.cls_preds:
-        conv.bias.fill_(cls_bias)
+        conv.bias.copy_(cls_bias + boost)
     return model
 
 

@@ -61,6 +61,12 @@ SIGNATURES = {
     "tcd_postprocess": (C.c_int, [_P, _F32P, C.c_int32, _F32P, _I32P]),
     "tcd_detector_num_anchors": (C.c_int32, [_P]),
     "tcd_detector_last_timing": (C.c_int, [_P, _F32P]),
+    "tcd_detector_stream": (C.c_void_p, [_P, C.c_int32]),
+    "tcd_detector_profile": (C.c_int, [_P, _PP, _I32P, _I32P, _I64P, C.c_int32, C.c_int32, C.c_int32, _F32P,
+                                       C.c_int32, _I32P]),
+    "tcd_detector_op_name": (C.c_char_p, [_P, C.c_int32, C.c_int32]),
+    "tcd_detector_op_kind": (C.c_int32, [_P, C.c_int32, C.c_int32]),
+    "tcd_detector_op_flops": (C.c_double, [_P, C.c_int32, C.c_int32]),
     "tcd_detector_read_activation": (C.c_int, [_P, C.c_char_p, _F32P, C.c_size_t, _I32P]),
     "tcd_mog2_create": (C.c_int, [C.c_int32, C.c_int32, C.c_int32, C.c_float, C.c_int32, C.c_int32, _PP]),
     "tcd_mog2_destroy": (None, [_P]),

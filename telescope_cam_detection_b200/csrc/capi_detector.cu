@@ -1,6 +1,7 @@
 // C ABI glue, part 2: the YOLOX detector handle (preprocess -> network -> decode/NMS).
 // Two independent pipeline slots (own stream, staging, activation arena, CUDA graph, pinned
 // result table) let the H2D copy of batch k+1 overlap the compute of batch k.
+#include <atomic>
 #include <map>
 #include <string.h>
 #include <vector>
@@ -9,6 +10,10 @@
 #include "yolox_net.cuh"
 
 using namespace tcd;
+
+namespace tcd {
+extern std::atomic<uint64_t> g_launch_count;
+}
 
 namespace {
 
@@ -20,6 +25,7 @@ struct Slot {
   PreFrame* pre_host = nullptr;   // pinned [max_batch]
   std::map<int, YoloxPlan*> plans;
   std::map<int, cudaGraphExec_t> graphs;
+  std::map<int, uint64_t> graph_kernels;  // kernel nodes per captured graph (launch accounting)
   // postprocess buffers (sized for max_batch)
   PostBuffers pb;
   float* thr_dev = nullptr;
@@ -120,6 +126,7 @@ static int run_net_post(tcd_detector* d, Slot& s, YoloxPlan* p, int B, bool want
     auto it = s.graphs.find(B);
     if (it == s.graphs.end()) {
       cudaGraph_t g = nullptr;
+      const uint64_t launches_before = g_launch_count.load();
       TCD_CUDA_OK(cudaStreamBeginCapture(s.stream, cudaStreamCaptureModeThreadLocal));
       int rc = p->run(s.stream);
       if (rc == TCD_OK) rc = postproc_launch(post_for(s, p, B, p->pred_raw, false), 1, s.stream);
@@ -137,9 +144,14 @@ static int run_net_post(tcd_detector* d, Slot& s, YoloxPlan* p, int B, bool want
         return TCD_ERR_CUDA;
       }
       s.graphs[B] = ge;
+      // the launches made while capturing did not execute: move them to per-replay accounting
+      const uint64_t captured = g_launch_count.load() - launches_before;
+      g_launch_count.fetch_sub(captured);
+      s.graph_kernels[B] = captured;
       it = s.graphs.find(B);
     }
     TCD_CUDA_OK(cudaGraphLaunch(it->second, s.stream));
+    g_launch_count.fetch_add(s.graph_kernels[B]);
     return TCD_OK;
   }
   int rc = p->run(s.stream);
@@ -149,7 +161,7 @@ static int run_net_post(tcd_detector* d, Slot& s, YoloxPlan* p, int B, bool want
 
 static int enqueue_input(tcd_detector* d, Slot& s, YoloxPlan* p, const uint8_t* const* frames,
                          const int32_t* h, const int32_t* w, const int64_t* row_stride, int B,
-                         int on_device) {
+                         int on_device, bool launch_pre = true) {
   tcd_preproc_cfg pc = d->cfg.pre;
   pc.out_h = d->cfg.input_h;
   pc.out_w = d->cfg.input_w;
@@ -175,6 +187,7 @@ static int enqueue_input(tcd_detector* d, Slot& s, YoloxPlan* p, const uint8_t* 
   }
   TCD_CUDA_OK(cudaEventRecord(s.ev[1], s.stream));
   TCD_CUDA_OK(cudaMemcpyAsync(s.pre_dev, s.pre_host, sizeof(PreFrame) * B, cudaMemcpyHostToDevice, s.stream));
+  if (!launch_pre) return TCD_OK;
   return preproc_launch(&pc, s.pre_host, s.pre_dev, B, 1, p->input, s.stream);
 }
 
@@ -363,6 +376,100 @@ tcd_status tcd_postprocess(tcd_detector* det, const float* pred_host, int32_t B,
     memcpy(out_dets + b * row, s.out_pinned + b * row, sizeof(float) * 7 * (size_t)s.cnt_pinned[b]);
   }
   return TCD_OK;
+}
+
+void* tcd_detector_stream(tcd_detector* det, int32_t slot) {
+  if (!det || (slot != 0 && slot != 1)) return nullptr;
+  return (void*)det->slot[slot].stream;
+}
+
+// Eager (graph-less) pass with a CUDA-event pair around every kernel of one detect_batch:
+// op 0 = preprocess, then the layer plan in launch order, then decode_filter / sort /
+// nms_mask / nms_reduce.  op_ms[i] = mean device time of op i over `iters` passes.
+tcd_status tcd_detector_profile(tcd_detector* det, const uint8_t* const* frames, const int32_t* h,
+                                const int32_t* w, const int64_t* row_stride, int32_t B,
+                                int32_t frames_on_device, int32_t iters, float* op_ms, int32_t cap,
+                                int32_t* n_ops) {
+  int rc = check_batch(det, frames, h, w, B);
+  if (rc) return (tcd_status)rc;
+  TCD_REQUIRE(iters >= 1 && op_ms && n_ops, "profile: bad argument");
+  Slot& s = det->slot[0];
+  YoloxPlan* p = nullptr;
+  rc = get_plan(det, s, B, &p);
+  if (rc) return (tcd_status)rc;
+  const int n = 1 + (int)p->ops.size() + 4;
+  *n_ops = n;
+  TCD_REQUIRE(cap >= n, "profile: op_ms holds %d entries, %d needed", cap, n);
+  std::vector<cudaEvent_t> ev(2 * (size_t)n);
+  for (auto& e : ev) TCD_CUDA_OK(cudaEventCreate(&e));
+  std::vector<double> acc(n, 0.0);
+  for (int it = 0; it < iters && rc == TCD_OK; ++it) {
+    // inputs are staged outside the per-op brackets; op 0 brackets the preprocess kernel only
+    tcd_preproc_cfg pc = det->cfg.pre;
+    pc.out_h = det->cfg.input_h;
+    pc.out_w = det->cfg.input_w;
+    rc = enqueue_input(det, s, p, frames, h, w, row_stride, B, frames_on_device, false);
+    if (rc) break;
+    cudaEventRecord(ev[0], s.stream);
+    rc = preproc_launch(&pc, s.pre_host, s.pre_dev, B, 1, p->input, s.stream);
+    cudaEventRecord(ev[1], s.stream);
+    for (size_t i = 0; i < p->ops.size() && rc == TCD_OK; ++i) {
+      cudaEventRecord(ev[2 * (i + 1)], s.stream);
+      rc = p->run_one((int)i, s.stream);
+      cudaEventRecord(ev[2 * (i + 1) + 1], s.stream);
+    }
+    if (rc) break;
+    const int base = 1 + (int)p->ops.size();
+    rc = postproc_launch(post_for(s, p, B, p->pred_raw, false), 1, s.stream, &ev[2 * (size_t)base]);
+    if (rc) break;
+    cudaError_t e = cudaStreamSynchronize(s.stream);
+    if (e != cudaSuccess) {
+      set_last_error("profile: %s", cudaGetErrorString(e));
+      rc = TCD_ERR_CUDA;
+      break;
+    }
+    for (int i = 0; i < n; ++i) {
+      float t = 0.f;
+      cudaEventElapsedTime(&t, ev[2 * (size_t)i], ev[2 * (size_t)i + 1]);
+      acc[i] += t;
+    }
+  }
+  for (auto& e : ev) cudaEventDestroy(e);
+  if (rc) return (tcd_status)rc;
+  for (int i = 0; i < n; ++i) op_ms[i] = (float)(acc[i] / iters);
+  return TCD_OK;
+}
+
+static const char* kPostNames[4] = {"decode_filter", "sort", "nms_mask", "nms_reduce"};
+
+const char* tcd_detector_op_name(tcd_detector* det, int32_t B, int32_t idx) {
+  if (!det) return "";
+  auto it = det->slot[0].plans.find(B);
+  if (it == det->slot[0].plans.end() || idx < 0) return "";
+  const YoloxPlan* p = it->second;
+  if (idx == 0) return "preprocess";
+  if (idx <= (int)p->ops.size()) return p->ops[idx - 1].name.c_str();
+  idx -= 1 + (int)p->ops.size();
+  return idx < 4 ? kPostNames[idx] : "";
+}
+
+/* kind: 0 = conv (tcgen05), 1 = other kernel */
+int32_t tcd_detector_op_kind(tcd_detector* det, int32_t B, int32_t idx) {
+  if (!det) return -1;
+  auto it = det->slot[0].plans.find(B);
+  if (it == det->slot[0].plans.end()) return -1;
+  const YoloxPlan* p = it->second;
+  if (idx >= 1 && idx <= (int)p->ops.size()) return p->ops[idx - 1].kind == OP_CONV ? 0 : 1;
+  return 1;
+}
+
+double tcd_detector_op_flops(tcd_detector* det, int32_t B, int32_t idx) {
+  if (!det) return 0.0;
+  auto it = det->slot[0].plans.find(B);
+  if (it == det->slot[0].plans.end()) return 0.0;
+  const YoloxPlan* p = it->second;
+  if (idx >= 1 && idx <= (int)p->ops.size() && p->ops[idx - 1].kind == OP_CONV) return p->ops[idx - 1].conv.flops;
+  return 0.0;
 }
 
 tcd_status tcd_detector_read_activation(tcd_detector* det, const char* name, float* out_host,

@@ -35,7 +35,8 @@ struct PostBuffers {
   int n_levels;
   int lvl_start[4], lvl_w[4], lvl_stride[4];
 };
-int postproc_launch(const PostBuffers& pb, int raw, cudaStream_t stream);
+// evs (optional): 8 events, recorded as a pair around each of the 4 kernels (profiling pass)
+int postproc_launch(const PostBuffers& pb, int raw, cudaStream_t stream, cudaEvent_t* evs = nullptr);
 
 // ---- motion (motion.cu)
 constexpr int kMogModes = 5;

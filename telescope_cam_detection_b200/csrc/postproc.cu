@@ -258,7 +258,7 @@ size_t post_reduce_smem_bytes(int cap, int smem_rows) {
   return sizeof(unsigned long long) * ((size_t)words + (cap + 1) / 2 + (size_t)smem_rows * 16);
 }
 
-int postproc_launch(const PostBuffers& pb, int raw, cudaStream_t stream) {
+int postproc_launch(const PostBuffers& pb, int raw, cudaStream_t stream, cudaEvent_t* evs) {
   static bool attr_done = false;
   const int smem_rows = 1024;
   const size_t red_smem = post_reduce_smem_bytes(pb.cap, smem_rows);
@@ -272,10 +272,15 @@ int postproc_launch(const PostBuffers& pb, int raw, cudaStream_t stream) {
   }
   cudaMemsetAsync(pb.cand_count, 0, sizeof(int) * pb.B, stream);
   const int warps = pb.B * pb.A;
+  if (evs) cudaEventRecord(evs[0], stream);
   decode_filter_kernel<<<cdiv(warps, 8), 256, 0, stream>>>(pb, raw);
+  if (evs) { cudaEventRecord(evs[1], stream); cudaEventRecord(evs[2], stream); }
   sort_kernel<<<pb.B, 1024, sort_smem, stream>>>(pb);
+  if (evs) { cudaEventRecord(evs[3], stream); cudaEventRecord(evs[4], stream); }
   nms_mask_kernel<<<dim3(296, pb.B), 64, 0, stream>>>(pb);
+  if (evs) { cudaEventRecord(evs[5], stream); cudaEventRecord(evs[6], stream); }
   nms_reduce_kernel<<<pb.B, 256, red_smem, stream>>>(pb, smem_rows);
+  if (evs) cudaEventRecord(evs[7], stream);
   g_launch_count.fetch_add(4, std::memory_order_relaxed);
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) {

@@ -66,6 +66,7 @@ struct YoloxPlan {
 
   int build(const YoloxWeights& wts, int B, int in_h, int in_w);
   int run(cudaStream_t stream) const;
+  int run_one(int i, cudaStream_t stream) const;
   void release();
 };
 

@@ -231,7 +231,16 @@ int YoloxPlan::build(const YoloxWeights& wts, int B_, int in_h_, int in_w_) {
 }
 
 int YoloxPlan::run(cudaStream_t stream) const {
-  for (const NetOp& op : ops) {
+  for (size_t i = 0; i < ops.size(); ++i) {
+    int rc = run_one((int)i, stream);
+    if (rc) return rc;
+  }
+  return TCD_OK;
+}
+
+int YoloxPlan::run_one(int i, cudaStream_t stream) const {
+  {
+    const NetOp& op = ops[(size_t)i];
     int rc = TCD_OK;
     switch (op.kind) {
       case OP_CONV:
@@ -245,9 +254,8 @@ int YoloxPlan::run(cudaStream_t stream) const {
         rc = spp_pool_launch(op.dst, op.N, op.H, op.W, op.C, op.d_ctot, stream);
         break;
     }
-    if (rc) return rc;
+    return rc;
   }
-  return TCD_OK;
 }
 
 void YoloxPlan::release() {

@@ -126,6 +126,26 @@ class DetectorEngine:
         check(self.lib.tcd_detector_last_timing(self.handle, t), "tcd_detector_last_timing")
         return dict(zip(("h2d_ms", "preprocess_ms", "network_post_ms", "_", "d2h_ms"), list(t)))
 
+    def stream(self, slot=0):
+        """cudaStream_t (int) of pipeline slot `slot`."""
+        return int(self.lib.tcd_detector_stream(self.handle, int(slot)) or 0)
+
+    def profile(self, frames, iters=5):
+        """Per-kernel device times of one detect_batch (eager pass, CUDA-event pair per kernel).
+        -> list of dicts {name, kind ('conv'|'other'), ms, flops}."""
+        p, h, w, s, B, dev, keep = self._marshal(frames)
+        cap = 512
+        ms = (C.c_float * cap)()
+        n = C.c_int32(0)
+        check(self.lib.tcd_detector_profile(self.handle, p, h, w, s, B, dev, int(iters), ms, cap, C.byref(n)),
+              "tcd_detector_profile")
+        out = []
+        for i in range(n.value):
+            out.append({"name": self.lib.tcd_detector_op_name(self.handle, B, i).decode(),
+                        "kind": "conv" if self.lib.tcd_detector_op_kind(self.handle, B, i) == 0 else "other",
+                        "ms": float(ms[i]), "flops": float(self.lib.tcd_detector_op_flops(self.handle, B, i))})
+        return out
+
     def read_activation(self, name):
         shape = (C.c_int32 * 4)()
         check(self.lib.tcd_detector_read_activation(self.handle, name.encode(), None, 0, shape), "read_activation")

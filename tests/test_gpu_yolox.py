@@ -55,12 +55,13 @@ def test_preprocess_focus_layout_is_bf16_of_parity_layout():
 @pytest.fixture(scope="module")
 def det():
     from telescope_cam_detection_b200.engine import DetectorEngine
-    e = DetectorEngine(oracle_blob(0), input_size=(640, 640), max_batch=2, max_out=4096)
+    e = DetectorEngine(oracle_blob(0), input_size=(640, 640), max_batch=2, max_out=8448)
     yield e
     e.close()
 
 
 def test_forward_matches_oracle(det):
+    """north_star tolerance, bf16 build vs fp32 oracle: scores 1e-2 abs, boxes 0.5 px."""
     import torch
     from oracle.synth_weights import preprocess_ref
 
@@ -73,15 +74,30 @@ def test_forward_matches_oracle(det):
     d_xy = np.abs(pred[..., :2] - ref[..., :2])
     d_wh = np.abs(pred[..., 2:4] - ref[..., 2:4])
     d_sc = np.abs(pred[..., 4:] - ref[..., 4:])
-    score = ref[..., 4] * ref[..., 5:].max(-1)
-    hot = score >= 0.05
-    msg = "xy %.3f wh %.3f (hot wh %.3f) scores %.4f n_hot %d" % (
-        d_xy.max(), d_wh.max(), d_wh[hot].max() if hot.any() else 0, d_sc.max(), hot.sum())
+    msg = "vs fp32 oracle: xy %.3f px, wh %.3f px, scores %.4f" % (d_xy.max(), d_wh.max(), d_sc.max())
     print(msg)
     assert d_sc.max() <= 1e-2, msg
     assert d_xy.max() <= 0.5, msg
-    # w/h are exp() of a bf16-computed logit: relative tolerance, 0.5 px on anything that can be a detection
-    assert (d_wh <= 0.5 + 0.02 * np.abs(ref[..., 2:4])).all(), msg
+    assert d_wh.max() <= 0.5, msg
+
+
+def test_forward_matches_bf16_rounding_oracle(det):
+    """Tight check: the oracle with the build's rounding points emulated (oracle/yolox_lowp.py).
+    Remaining differences are fp32 summation order, fast exp in SiLU and the rare bf16 rounding
+    flips they cause: scores 3e-3, boxes 0.2 px."""
+    import torch
+    from oracle.synth_weights import preprocess_ref
+    from oracle.yolox_lowp import lowp_model
+
+    frames = [structured_frame(11), noise_frame(12)]
+    pred = det.forward(frames)
+    with torch.no_grad():
+        ref = lowp_model(oracle_model(0))(torch.cat([preprocess_ref(f) for f in frames], 0)).numpy()
+    d_box = np.abs(pred[..., :4] - ref[..., :4]).max()
+    d_sc = np.abs(pred[..., 4:] - ref[..., 4:]).max()
+    msg = "vs bf16-rounding oracle: boxes %.4f px, scores %.5f" % (d_box, d_sc)
+    print(msg)
+    assert d_sc <= 3e-3 and d_box <= 0.2, msg
 
 
 @pytest.mark.parametrize("conf", [0.25, 0.01])
