@@ -169,9 +169,11 @@ tcd_status tcd_empty_filter_create(int32_t h, int32_t w, int32_t blur_size, int3
                                    tcd_empty_filter** out);
 void tcd_empty_filter_destroy(tcd_empty_filter* f);
 tcd_status tcd_empty_filter_reset(tcd_empty_filter* f);
-/* changed_pixels_host: count of |cur-prev| > threshold (or -1 on the first frame).       */
+/* frame: HWC u8 BGR (channels = 3) or an already-gray plane (channels = 1, the reference
+ * accepts both, :65-68).  changed_pixels_host: count of |cur-prev| > threshold (strict), or -1
+ * on the first frame after create/reset.  gray_blur_host (optional): the blurred gray plane.   */
 tcd_status tcd_empty_filter_step(tcd_empty_filter* f, const uint8_t* frame, int64_t row_stride,
-                                 int32_t frame_on_device, int32_t threshold,
+                                 int32_t channels, int32_t frame_on_device, int32_t threshold,
                                  int32_t* changed_pixels_host, uint8_t* gray_blur_host);
 
 /* ------------------------------------------------------------------ Stage-2 crops (K13)

@@ -76,7 +76,7 @@ SIGNATURES = {
     "tcd_empty_filter_create": (C.c_int, [C.c_int32, C.c_int32, C.c_int32, C.c_int32, _PP]),
     "tcd_empty_filter_destroy": (None, [_P]),
     "tcd_empty_filter_reset": (C.c_int, [_P]),
-    "tcd_empty_filter_step": (C.c_int, [_P, _P, C.c_int64, C.c_int32, C.c_int32, _I32P, _P]),
+    "tcd_empty_filter_step": (C.c_int, [_P, _P, C.c_int64, C.c_int32, C.c_int32, C.c_int32, _I32P, _P]),
     "tcd_crop_resize": (C.c_int, [_P, C.c_int32, C.c_int32, C.c_int64, _I32P, C.c_int32, C.c_int32,
                                   C.POINTER(PreprocCfg), C.c_int32, _P, _P]),
     "tcd_malloc_device": (C.c_int, [C.c_size_t, _PP]),

@@ -238,10 +238,11 @@ tcd_status tcd_empty_filter_reset(tcd_empty_filter* f) {
 }
 
 tcd_status tcd_empty_filter_step(tcd_empty_filter* f, const uint8_t* frame, int64_t row_stride,
-                                 int32_t frame_on_device, int32_t threshold,
+                                 int32_t channels, int32_t frame_on_device, int32_t threshold,
                                  int32_t* changed_pixels_host, uint8_t* gray_blur_host) {
-  TCD_REQUIRE(f && frame && changed_pixels_host, "empty_filter_step: bad argument");
-  const size_t tight = (size_t)f->w * 3;
+  TCD_REQUIRE(f && frame && changed_pixels_host && (channels == 1 || channels == 3),
+              "empty_filter_step: bad argument");
+  const size_t tight = (size_t)f->w * channels;
   if (row_stride <= 0) row_stride = (int64_t)tight;
   const uint8_t* src = frame;
   long long stride = row_stride;
@@ -254,7 +255,7 @@ tcd_status tcd_empty_filter_step(tcd_empty_filter* f, const uint8_t* frame, int6
   BlurArgs a;
   memset(&a, 0, sizeof(a));
   a.w = f->w; a.h = f->h; a.ksize = f->blur_size; a.in_stride = stride;
-  a.src_mode = 1; a.post_mode = 1; a.post_thr = threshold; a.first = f->have_prev ? 0 : 1;
+  a.src_mode = channels == 3 ? 1 : 2; a.post_mode = 1; a.post_thr = threshold; a.first = f->have_prev ? 0 : 1;
   memcpy(a.k, f->k, sizeof(a.k));
   TCD_CUDA_OK(cudaMemsetAsync(f->counter, 0, sizeof(unsigned int), f->stream));
   int rc = blur_launch(src, a, nullptr, f->prev, f->counter, f->stream);

@@ -60,7 +60,7 @@ constexpr int kBlurMaxK = 31;
 struct BlurArgs {
   int w, h, ksize;         // ksize odd, <= 31
   long long in_stride;
-  int src_mode;            // 0: u8 plane binarised (p > pre_thr ? 255 : 0); 1: BGR -> gray
+  int src_mode;            // 0: u8 plane binarised (p > pre_thr ? 255 : 0); 1: BGR -> gray; 2: u8 plane as is
   int pre_thr;
   int post_mode;           // 0: write (v > post_thr ? 255 : 0); 1: absdiff vs prev, count, prev = v
   int post_thr;

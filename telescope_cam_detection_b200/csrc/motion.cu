@@ -212,6 +212,8 @@ blur_kernel(const uint8_t* __restrict__ src, const BlurArgs a, uint8_t* __restri
     uint8_t val;
     if (a.src_mode == 0) {
       val = src[(long long)gy * a.in_stride + gx] > a.pre_thr ? 255 : 0;
+    } else if (a.src_mode == 2) {
+      val = src[(long long)gy * a.in_stride + gx];
     } else {
       const uint8_t* p = src + (long long)gy * a.in_stride + gx * 3;
       // cv2.cvtColor BGR2GRAY, 15-bit coefficients (bit-exact vs cv2 4.13)

@@ -184,3 +184,106 @@ def crop_resize(frame_ptr, h, w, stride, boxes, S, out_ptr, layout=0, swap_rb=1,
     check(lib.tcd_crop_resize(C.c_void_p(int(frame_ptr)), int(h), int(w), int(stride),
                               boxes.ctypes.data_as(_lib._I32P), boxes.shape[0], int(S), C.byref(cfg), int(layout),
                               C.c_void_p(int(out_ptr)), None), "tcd_crop_resize")
+
+
+def _plane_desc(frame, channels):
+    """-> (ptr, h, w, row_stride_bytes, on_device, keepalive) for an HxWxC / HxW u8 frame."""
+    if _is_torch(frame):
+        t = frame
+        if t.stride(-1) != 1 or (channels == 3 and t.stride(1) != 3):
+            t = t.contiguous()
+        return t.data_ptr(), t.shape[0], t.shape[1], t.stride(0), t.is_cuda, t
+    a = np.asarray(frame)
+    if a.dtype != np.uint8:
+        raise TypeError("frames must be uint8, got %s" % a.dtype)
+    if a.strides[-1] != 1 or (channels == 3 and a.strides[1] != 3):
+        a = np.ascontiguousarray(a)
+    return a.ctypes.data, a.shape[0], a.shape[1], a.strides[0], False, a
+
+
+class Mog2Engine:
+    """One tcd_mog2 handle: device-resident 5-mode GMM per pixel for one camera stream
+    (replaces cv2.createBackgroundSubtractorMOG2, src/motion_filter.py:56-60)."""
+
+    def __init__(self, h, w, history=500, var_threshold=16, detect_shadows=True, device=0):
+        self.lib = _lib.load()
+        self.h, self.w = int(h), int(w)
+        hd = C.c_void_p()
+        check(self.lib.tcd_mog2_create(self.h, self.w, int(history), float(var_threshold),
+                                       1 if detect_shadows else 0, int(device), C.byref(hd)), "tcd_mog2_create")
+        self.handle = hd
+
+    def close(self):
+        if getattr(self, "handle", None):
+            self.lib.tcd_mog2_destroy(self.handle)
+            self.handle = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def reset(self):
+        check(self.lib.tcd_mog2_reset(self.handle), "tcd_mog2_reset")
+
+    def apply(self, frame, repeats=1, want_mask=False):
+        ptr, h, w, stride, on_dev, keep = _plane_desc(frame, 3)
+        if (h, w) != (self.h, self.w):
+            raise ValueError("frame is %dx%d, model is %dx%d" % (h, w, self.h, self.w))
+        mask = np.empty((self.h, self.w), np.uint8) if want_mask else None
+        check(self.lib.tcd_mog2_apply(self.handle, C.c_void_p(ptr), int(stride), 1 if on_dev else 0, int(repeats),
+                                      mask.ctypes.data_as(C.c_void_p) if want_mask else None), "tcd_mog2_apply")
+        return mask
+
+    def roi_counts(self, rois, shadow_thr=200, ksize=21, blur_thr=25, want_mask=False):
+        """rois: int32 [n,4] (x1,y1,x2,y2) already clamped to the frame.  -> (counts[n], clean mask or None)"""
+        rois = np.ascontiguousarray(rois, np.int32).reshape(-1, 4)
+        n = rois.shape[0]
+        counts = np.zeros((max(n, 1),), np.int32)
+        mask = np.empty((self.h, self.w), np.uint8) if want_mask else None
+        check(self.lib.tcd_mog2_roi_counts(self.handle, int(shadow_thr), int(ksize), int(blur_thr),
+                                           rois.ctypes.data_as(_lib._I32P), n, counts.ctypes.data_as(_lib._I32P),
+                                           mask.ctypes.data_as(C.c_void_p) if want_mask else None),
+              "tcd_mog2_roi_counts")
+        return counts[:n], mask
+
+
+class EmptyGateEngine:
+    """One tcd_empty_filter handle (previous blurred gray frame lives on the device)."""
+
+    def __init__(self, h, w, blur_size=21, device=0):
+        self.lib = _lib.load()
+        self.h, self.w = int(h), int(w)
+        hd = C.c_void_p()
+        check(self.lib.tcd_empty_filter_create(self.h, self.w, int(blur_size), int(device), C.byref(hd)),
+              "tcd_empty_filter_create")
+        self.handle = hd
+
+    def close(self):
+        if getattr(self, "handle", None):
+            self.lib.tcd_empty_filter_destroy(self.handle)
+            self.handle = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def reset(self):
+        check(self.lib.tcd_empty_filter_reset(self.handle), "tcd_empty_filter_reset")
+
+    def step(self, frame, threshold=25, want_blur=False):
+        """-> (changed pixel count, or -1 on the first frame; blurred gray plane or None)"""
+        channels = 3 if (frame.ndim == 3) else 1
+        ptr, h, w, stride, on_dev, keep = _plane_desc(frame, channels)
+        if (h, w) != (self.h, self.w):
+            raise ValueError("frame is %dx%d, filter is %dx%d" % (h, w, self.h, self.w))
+        cnt = C.c_int32(0)
+        blur = np.empty((self.h, self.w), np.uint8) if want_blur else None
+        check(self.lib.tcd_empty_filter_step(self.handle, C.c_void_p(ptr), int(stride), channels, 1 if on_dev else 0,
+                                             int(threshold), C.byref(cnt),
+                                             blur.ctypes.data_as(C.c_void_p) if want_blur else None),
+              "tcd_empty_filter_step")
+        return cnt.value, blur

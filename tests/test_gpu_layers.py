@@ -53,15 +53,25 @@ def test_stage_activations_match_oracle():
     taps = {}
     hooks = [mods[path].register_forward_hook(lambda m, i, o, p=path: taps.__setitem__(p, o.detach()))
              for _, path, _ in STAGES]
+    x = torch.cat([preprocess_ref(f) for f in frames], 0)
     with torch.no_grad():
-        model(torch.cat([preprocess_ref(f) for f in frames], 0))
+        model(x)
     for h in hooks:
         h.remove()
+    # same taps on the oracle with the build's bf16 rounding points emulated
+    from oracle.yolox_lowp import lowp_model
+    low = lowp_model(model)
+    lmods = dict(low.named_modules())
+    ltaps = {}
+    for _, path, _ in STAGES:
+        lmods[path].register_forward_hook(lambda m, i, o, p=path: ltaps.__setitem__(p, o.detach()))
+    with torch.no_grad():
+        low(x)
 
     eng = DetectorEngine(oracle_blob(0), input_size=(640, 640), max_batch=2, max_out=64)
     try:
         eng.forward(frames)
-        report, worst = [], 0.0
+        report, worst, worst_low, first_low = [], 0.0, 0.0, 0.0
         for depth, (buf, path, sl) in enumerate(STAGES):
             got = eng.read_activation(buf)  # [B,H,W,C] f32
             if sl is not None:
@@ -70,10 +80,23 @@ def test_stage_activations_match_oracle():
             assert got.shape == ref.shape, "%s: shape %s vs oracle %s" % (buf, got.shape, ref.shape)
             scale = float(np.abs(ref).mean()) + 1e-6
             err = float(np.abs(got - ref).mean()) / scale
-            report.append("%-18s <- %-32s mean|d|/mean|ref| = %.4f" % (buf, path, err))
+            lref = ltaps[path].permute(0, 2, 3, 1).numpy()
+            lerr = float(np.abs(got - lref).mean()) / scale
+            lmax = float(np.abs(got - lref).max()) / scale
+            report.append("%-18s <- %-32s vs fp32 %.4f | vs bf16-rounding oracle mean %.5f max %.4f" % (
+                buf, path, err, lerr, lmax))
             worst = max(worst, err)
+            worst_low = max(worst_low, lerr)
+            if depth < 4:
+                first_low = max(first_low, lerr)
         print("\n".join(report))
         # bf16 rounding is ~0.2-0.4 % per stored activation; 28 stages deep stays well below 3 %
         assert worst <= 0.03, "\n".join(report)
+        # Against the rounding-point emulation the first stages are bit-identical (measured 0.00000
+        # through stem/dark2.0).  A first bf16 rounding flip (fp32 summation order) then perturbs its
+        # whole receptive field by ~1e-3 relative, which flips a large share of the NEXT roundings:
+        # the two bf16 pipelines decorrelate and settle at the bf16 noise level itself (~0.7 %).
+        assert first_low <= 1e-3, "\n".join(report)
+        assert worst_low <= 0.02, "\n".join(report)
     finally:
         eng.close()
