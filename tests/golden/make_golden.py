@@ -1,0 +1,132 @@
+"""Generates tests/golden/*.npz|json by running the REFERENCE's own classes (imported from
+/root/reference, read-only) in the build container.  /root/reference does not exist on the GPU
+box, so the outputs are committed; rerun with `python tests/golden/make_golden.py`.
+
+  motion_ref.npz   MotionFilter.filter_detections on tests/util.motion_sequence (per-detection
+                   verdict + ratio, incl. the one-apply-per-detection quirk)
+  empty_ref.npz    EmptyFrameFilter.has_motion verdicts on the same frames
+  format_ref.json  YOLOXDetector._format_model_output_to_detections and
+                   InferenceEngine._post_process_detections on seeded postprocess rows, with the
+                   shipped per-class tables (config/config.yaml:238-264).  These two import
+                   src/yolox_detector.py, which needs a YOLOX checkout: a stub package exporting
+                   the oracle restatement is put on sys.path.
+Versions of the libraries that did the arithmetic are stored in every file.
+"""
+import json
+import os
+import shutil
+import sys
+import tempfile
+import types
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(os.path.dirname(HERE))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+sys.dont_write_bytecode = True
+REF = "/root/reference"
+
+
+def versions():
+    import cv2
+    import torch
+    import torchvision
+    return {"cv2": cv2.__version__, "numpy": np.__version__, "torch": torch.__version__,
+            "torchvision": torchvision.__version__, "reference": "filthyrake/telescope_cam_detection@249c75e"}
+
+
+def motion_and_empty():
+    sys.path.insert(0, REF)
+    from src.motion_filter import MotionFilter
+    from src.empty_frame_filter import EmptyFrameFilter
+    from util import motion_sequence
+    seq = motion_sequence()
+    mf = MotionFilter()
+    verdict, ratio, nper = [], [], []
+    for frame, boxes in seq:
+        dets = [{"bbox": dict(b), "idx": i} for i, b in enumerate(boxes)]
+        # per detection: has_motion_in_bbox applies MOG2 once, exactly what filter_detections does
+        for d in dets:
+            ok, r = mf.has_motion_in_bbox(frame, d["bbox"])
+            verdict.append(ok)
+            ratio.append(r)
+        nper.append(len(dets))
+    np.savez_compressed(os.path.join(HERE, "motion_ref.npz"), verdict=np.array(verdict), ratio=np.array(ratio),
+                        n_per_frame=np.array(nper), versions=json.dumps(versions()))
+    ef = EmptyFrameFilter()
+    ev = [ef.has_motion(f) for f, _ in seq]
+    ef2 = EmptyFrameFilter(min_motion_area=5000, threshold=10, blur_size=9)
+    ev2 = [ef2.has_motion(f) for f, _ in seq]
+    np.savez_compressed(os.path.join(HERE, "empty_ref.npz"), default=np.array(ev), tuned=np.array(ev2),
+                        versions=json.dumps(versions()))
+    print("motion: %d verdicts (%d true); empty: %d/%d true" % (len(verdict), sum(verdict), sum(ev), len(ev)))
+
+
+SHIPPED_CONF = {"person": 0.75, "bird": 0.70, "bear": 0.95, "dog": 0.70, "cat": 0.70}      # config.yaml:238-243
+SHIPPED_SIZE = {"bird": {"max": 8000}, "bear": {"min": 5000}, "dog": {"min": 1000}, "cat": {"min": 800},
+                "rabbit": {"min": 400, "max": 3000}}                                            # config.yaml:253-264
+
+
+def seeded_rows(seed, n=160):
+    """postprocess-shaped rows [x1,y1,x2,y2,obj,cls,class_id] (network pixels) covering wildlife and
+    other classes, tiny/huge/inverted boxes and confidences around every shipped threshold."""
+    rng = np.random.default_rng(seed)
+    cx, cy = rng.uniform(0, 640, n), rng.uniform(0, 640, n)
+    w, h = np.exp(rng.uniform(np.log(2), np.log(400), n)), np.exp(rng.uniform(np.log(2), np.log(400), n))
+    rows = np.stack([cx - w / 2, cy - h / 2, cx + w / 2, cy + h / 2, rng.uniform(0.3, 1, n), rng.uniform(0.3, 1, n),
+                     rng.choice([0, 14, 15, 16, 21, 2, 56, 17, 79], n).astype(np.float64)], 1).astype(np.float32)
+    rows[::17, [0, 2]] = rows[::17, [2, 0]]  # inverted x
+    order = np.argsort(-(rows[:, 4] * rows[:, 5]), kind="stable")
+    return rows[order]
+
+
+def stub_reference_tree():
+    """Scratch copy of /root/reference/src beside a stub YOLOX package (existence check at
+    src/yolox_detector.py:17-31) so the reference's own detector / engine modules import."""
+    tmp = tempfile.mkdtemp(prefix="tcd_ref_")
+    shutil.copytree(os.path.join(REF, "src"), os.path.join(tmp, "src"))
+    for sub in ("YOLOX/yolox", "YOLOX/yolox/exp", "YOLOX/yolox/utils"):
+        os.makedirs(os.path.join(tmp, sub))
+    open(os.path.join(tmp, "YOLOX/yolox/__init__.py"), "w").close()
+    with open(os.path.join(tmp, "YOLOX/yolox/exp/__init__.py"), "w") as f:
+        f.write("from oracle.yolox_s import get_exp\n")
+    with open(os.path.join(tmp, "YOLOX/yolox/utils/__init__.py"), "w") as f:
+        f.write("from oracle.postprocess import postprocess\n")
+    sys.path.insert(0, os.path.join(tmp, "src"))
+    sys.path.insert(0, tmp)
+    sys.modules.setdefault("timm", types.ModuleType("timm"))
+    return tmp
+
+
+def format_and_filter():
+    tmp = stub_reference_tree()
+    try:
+        for k in [k for k in sys.modules if k == "src" or k.startswith("src.")]:
+            del sys.modules[k]
+        from src.yolox_detector import YOLOXDetector
+        from src.inference_engine_yolox import InferenceEngine
+        out = {"versions": versions(), "cases": []}
+        for seed, (oh, ow), wildlife in [(0, (1080, 1920), True), (1, (720, 1280), True), (2, (1080, 1920), False),
+                                         (3, (640, 640), True)]:
+            rows = seeded_rows(seed)
+            det = YOLOXDetector(device="cpu", input_size=(640, 640), wildlife_only=wildlife)
+            dets = det._format_model_output_to_detections(rows, oh, ow)
+            formatted = json.loads(json.dumps(dets))
+            eng = InferenceEngine(device="cpu", conf_threshold=0.25, min_box_area=300, max_det=20,
+                                  class_confidence_overrides=dict(SHIPPED_CONF),
+                                  class_size_constraints=json.loads(json.dumps(SHIPPED_SIZE)), wildlife_only=wildlife)
+            kept = eng._post_process_detections(dets, np.zeros((oh, ow, 3), np.uint8))
+            out["cases"].append({"seed": seed, "orig_hw": [oh, ow], "wildlife_only": wildlife, "formatted": formatted,
+                                 "post_processed": json.loads(json.dumps(kept))})
+        with open(os.path.join(HERE, "format_ref.json"), "w") as f:
+            json.dump(out, f)
+        print("format: %s" % [(len(c["formatted"]), len(c["post_processed"])) for c in out["cases"]])
+    finally:
+        shutil.rmtree(tmp, ignore_errors=True)
+
+
+if __name__ == "__main__":
+    motion_and_empty()
+    format_and_filter()

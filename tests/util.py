@@ -34,3 +34,36 @@ def oracle_model(seed=0):
 def oracle_blob(seed=0):
     from telescope_cam_detection_b200 import weights
     return weights.pack_yolox(oracle_model(seed).state_dict())
+
+
+def motion_sequence(seed=7, h=480, w=640, n=40):
+    """Synthetic camera stream for the motion tests: static low-pass background + sensor noise,
+    moving bright rectangles from frame 8 on, a darkening ("shadow") episode, a few fully static
+    frames.  -> list of (frame u8 HxWx3, [bbox dicts]) ; boxes include moving, static, inverted,
+    out-of-frame and degenerate ones (the cases src/motion_filter.py:100-113 guards)."""
+    rng = np.random.default_rng(seed)
+    coarse = rng.integers(40, 200, (h // 16 + 1, w // 16 + 1, 3))
+    bg = np.repeat(np.repeat(coarse, 16, 0), 16, 1)[:h, :w].astype(np.int16)
+    out = []
+    for t in range(n):
+        f = bg + rng.integers(-5, 6, (h, w, 3))
+        boxes = []
+        if t >= 8 and t % 9 != 0:  # every 9th frame stays static
+            x = 20 + (t * 11) % (w - 140)
+            f[100:180, x:x + 90] = rng.integers(190, 256, (80, 90, 3))
+            boxes.append({"x1": x - 10.5, "y1": 92.25, "x2": x + 101.75, "y2": 188.5})
+            y = 250 + (t * 5) % 120
+            f[y:y + 40, 400:470] = rng.integers(0, 40, (40, 70, 3))
+            boxes.append({"x1": 395.0, "y1": float(y - 6), "x2": 476.0, "y2": float(y + 47)})
+        if 20 <= t < 30:
+            f[300:420, 50:250] = (f[300:420, 50:250] * 0.62).astype(np.int16)
+            boxes.append({"x1": 50.0, "y1": 300.0, "x2": 250.0, "y2": 420.0})
+        boxes.append({"x1": 500.0, "y1": 20.0, "x2": 620.0, "y2": 90.0})           # static region
+        if t % 4 == 0:
+            boxes.append({"x1": 300.0, "y1": 200.0, "x2": 180.0, "y2": 120.0})     # inverted corners
+        if t % 5 == 0:
+            boxes.append({"x1": float(w - 30), "y1": float(h - 25), "x2": float(w + 80), "y2": float(h + 60)})
+        if t % 7 == 0:
+            boxes.append({"x1": float(w + 5), "y1": 10.0, "x2": float(w + 50), "y2": 60.0})  # off-frame
+        out.append((np.clip(f, 0, 255).astype(np.uint8), boxes))
+    return out
