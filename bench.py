@@ -48,6 +48,7 @@ def parse_args():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--profile-iters", type=int, default=10)
     ap.add_argument("--latency-iters", type=int, default=30)
+    ap.add_argument("--dump-ops", default=None, help="write the per-kernel table of the eager profiling pass here")
     return ap.parse_args()
 
 
@@ -312,6 +313,9 @@ def run_ours(args):
     kernels["slowest_convs"] = [{"name": o["name"], "ms": round(o["ms"], 4),
                                  "TFLOP/s": round(o["flops"] / (o["ms"] * 1e-3) / 1e12, 1)} for o in slow]
 
+    if args.dump_ops:
+        with open(args.dump_ops, "w") as f:
+            json.dump(prof, f)
     cpu = None if args.no_cpu_baseline or world > 1 else cpu_baseline()
     line = {
         "metric": METRIC, "value": fps_dev, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,

@@ -5,6 +5,7 @@
 
 #include <atomic>
 #include <mutex>
+#include <stdlib.h>
 #include <string.h>
 #include <vector>
 
@@ -29,6 +30,23 @@ static PFN_encodeTiled get_encode() {
       fn = (PFN_encodeTiled)p;
   });
   return fn;
+}
+
+// TCD_NO_PDL=1 launches every conv with plain stream ordering (debug / A-B measurements)
+static const bool g_use_pdl = [] {
+  const char* e = getenv("TCD_NO_PDL");
+  return !(e && e[0] == '1');
+}();
+
+static int sm_count() {
+  static int n = 0;
+  if (n == 0) {
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess ||
+        cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0)
+      n = 148;
+  }
+  return n;
 }
 
 static CUtensorMapSwizzle swizzle_for_inner_bytes(int bytes) {
@@ -123,7 +141,9 @@ int conv_plan_build(const ConvDesc& d, ConvPlan* plan) {
   TCD_REQUIRE(d.cin % a.ck == 0 && (a.ck == 16 || a.ck == 32 || a.ck == 64),
               "conv: cin %d not chunkable", d.cin);
   a.kchunks = d.cin / a.ck;
-  // N tile
+  // N tile: the widest one that still yields enough tiles to occupy the chip
+  const int n_sm = sm_count();
+  const int m_tiles = a.tiles_per_img * d.N;
   int BN;
   if (mode == 1) {
     BN = d.cout_pad;
@@ -131,10 +151,18 @@ int conv_plan_build(const ConvDesc& d, ConvPlan* plan) {
   } else {
     TCD_REQUIRE(d.cout_pad == d.cout && d.cout % 32 == 0, "conv: cout %d must be a multiple of 32",
                 d.cout);
-    BN = d.cout >= 128 ? 128 : d.cout;
-    TCD_REQUIRE(d.cout % BN == 0, "conv: cout %d not tileable", d.cout);
+    BN = 32;
+    for (int cand = 128; cand >= 32; cand >>= 1) {
+      if (d.cout % cand) continue;
+      if ((long)m_tiles * (d.cout / cand) >= (long)(n_sm * 6) / 10 || cand == 32) {
+        BN = cand;
+        break;
+      }
+    }
   }
   a.BN = BN;
+  a.n_tiles_n = d.cout_pad / BN;
+  a.total_tiles = m_tiles * a.n_tiles_n;
   a.cin_off = d.x_coff;
   a.cout_off = d.y_coff;
   a.mode = mode;
@@ -150,9 +178,11 @@ int conv_plan_build(const ConvDesc& d, ConvPlan* plan) {
   a.out_col = d.out_col;
   a.rows_per_img = d.rows_per_img;
   a.row_off = d.row_off;
+  a.pdl = g_use_pdl ? 1 : 0;
   int tc = 32;
   while (tc < BN) tc <<= 1;
-  a.tmem_cols = tc;
+  a.acc_stride = tc;        // two accumulators, tc columns apart
+  a.tmem_cols = 2 * tc;
   // taps
   for (int t = 0; t < a.taps; ++t) {
     const int r = t / d.k, s = t % d.k;
@@ -168,20 +198,25 @@ int conv_plan_build(const ConvDesc& d, ConvPlan* plan) {
       a.tap_dy[t] = (int8_t)(r == 0 ? -1 : 0);
     }
   }
-  // pipeline depth / smem
+  // pipeline depth / smem: one persistent CTA per SM gets a deep ring; layers with many more
+  // tiles than SMs and short K loops run two CTAs per SM (twice the epilogue warps)
   const int a_bytes = 128 * a.ck * 2, b_bytes = BN * a.ck * 2;
   const int stage_bytes = a_bytes + b_bytes;
   TCD_REQUIRE(stage_bytes % 1024 == 0, "conv: stage bytes %d not 1 KiB aligned", stage_bytes);
   const int staging = mode == 0 ? 128 * BN * 2 : 0;
-  const int total_it = a.taps * a.kchunks;
-  int stages = total_it < 4 ? total_it : 4;
-  const int budget = 100 * 1024;  // two CTAs per SM
-  while (stages > 2 && stages * stage_bytes > budget) --stages;
-  while (stages * stage_bytes < staging) ++stages;
-  TCD_REQUIRE(stages >= 1 && stages <= kConvMaxStages, "conv: bad stage count %d", stages);
+  const int its_per_tile = a.taps * a.kchunks;
+  const bool two_per_sm = a.total_tiles >= 2 * n_sm && a.tmem_cols <= 256;
+  const int budget = (two_per_sm ? 110 : 220) * 1024 - 2048;
+  const long its_per_cta = (long)its_per_tile * cdiv(a.total_tiles, n_sm * (two_per_sm ? 2 : 1));
+  int stages = (budget - staging) / stage_bytes;
+  if (stages > kConvMaxStages) stages = kConvMaxStages;
+  if ((long)stages > its_per_cta) stages = (int)its_per_cta;
+  TCD_REQUIRE(stages >= 1, "conv: no room for a pipeline stage (%d B stage, %d B staging)", stage_bytes, staging);
   a.stages = stages;
-  plan->smem_bytes = stages * stage_bytes + 1024;
-  plan->grid = dim3((unsigned)(a.tiles_per_img * d.N), (unsigned)(d.cout_pad / BN), 1);
+  a.staging_off = stages * stage_bytes;
+  plan->smem_bytes = stages * stage_bytes + staging + 1024;
+  const int ctas = n_sm * (two_per_sm ? 2 : 1);
+  plan->grid = dim3((unsigned)(a.total_tiles < ctas ? a.total_tiles : ctas), 1, 1);
   plan->flops = 2.0 * d.N * a.Ho * a.Wo * (double)d.cout * d.cin * a.taps;
 
   // ---- tensor maps
@@ -229,7 +264,7 @@ int conv_plan_build(const ConvDesc& d, ConvPlan* plan) {
   static cudaError_t attr_err = cudaSuccess;
   std::call_once(once, [] {
     attr_err = cudaFuncSetAttribute(conv_umma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                    200 * 1024);
+                                    225 * 1024);
   });
   if (attr_err != cudaSuccess) {
     set_last_error("cudaFuncSetAttribute(conv_umma_kernel): %s", cudaGetErrorString(attr_err));
@@ -239,9 +274,19 @@ int conv_plan_build(const ConvDesc& d, ConvPlan* plan) {
 }
 
 int conv_plan_launch(const ConvPlan& plan, cudaStream_t stream) {
-  conv_umma_kernel<<<plan.grid, kConvThreads, plan.smem_bytes, stream>>>(plan.maps, plan.args);
+  cudaLaunchConfig_t cfg;
+  memset(&cfg, 0, sizeof(cfg));
+  cfg.gridDim = plan.grid;
+  cfg.blockDim = dim3(kConvThreads, 1, 1);
+  cfg.dynamicSmemBytes = (size_t)plan.smem_bytes;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = plan.args.pdl ? 1 : 0;
+  cudaError_t e = cudaLaunchKernelEx(&cfg, conv_umma_kernel, plan.maps, plan.args);
   g_launch_count.fetch_add(1, std::memory_order_relaxed);
-  cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) {
     set_last_error("conv_umma_kernel launch: %s", cudaGetErrorString(e));
     return TCD_ERR_CUDA;

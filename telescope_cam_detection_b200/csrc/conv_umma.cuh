@@ -17,7 +17,13 @@
 //   * warp 0 = TMA producer, warp 1 = TMEM allocator + single-thread MMA issuer,
 //     warps 2-5 = epilogue (tcgen05.ld -> +bias -> SiLU -> (+residual) -> bf16 ->
 //     swizzled smem -> TMA store, which clips partial tiles for free and writes straight
-//     into a channel slice of a concat buffer).
+//     into a channel slice of a concat buffer);
+//   * CTAs are PERSISTENT: each loops over output tiles (static round-robin), the smem ring
+//     never drains across tile boundaries, and the accumulator is double-buffered in TMEM so
+//     the epilogue of tile i overlaps the loads + MMAs of tile i+1;
+//   * launched with programmatic dependent launch inside the CUDA graph: barrier init, TMEM
+//     allocation, descriptor prefetch and the first weight loads overlap the previous
+//     layer's tail; griddepcontrol.wait guards the first read of the previous layer's output.
 #pragma once
 #include "tcd_common.cuh"
 
@@ -38,6 +44,10 @@ struct ConvArgs {
   int cin_off, cout_off;
   int mode;  // 0: bf16 NHWC via TMA store; 1: f32 rows (head predictions)
   int silu, out_chunk, stages, tmem_cols, n_valid;
+  int n_tiles_n, total_tiles;   // persistent tile loop: tile t -> (m = t / n_tiles_n, n = t % n_tiles_n)
+  int acc_stride;               // TMEM columns between the two accumulator buffers
+  int staging_off;              // byte offset of the epilogue staging area inside dynamic smem
+  int pdl;                      // launched with programmatic stream serialization
   const float* bias;
   const __nv_bfloat16* resid;
   int r_ctot, r_coff;
@@ -48,32 +58,68 @@ struct ConvArgs {
 
 #if defined(__CUDACC__) && defined(TCD_CONV_KERNEL_IMPL)
 
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_launch_dependents() {
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+}
+__device__ __forceinline__ void tma_store_wait_read() {
+  asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+}
+__device__ __forceinline__ void tma_store_commit() {
+  asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+}
+
+struct ConvTile {
+  int n_img, y0, x0, n_tile;
+};
+__device__ __forceinline__ ConvTile conv_tile(const ConvArgs& p, int t) {
+  ConvTile c;
+  const int m_tile = t / p.n_tiles_n;
+  c.n_tile = t - m_tile * p.n_tiles_n;
+  c.n_img = m_tile / p.tiles_per_img;
+  const int rem = m_tile - c.n_img * p.tiles_per_img;
+  const int ty = rem / p.tiles_w;
+  c.y0 = ty * p.TH;
+  c.x0 = (rem - ty * p.tiles_w) * p.TW;
+  return c;
+}
+
+// One NC-column slab of the accumulator row owned by this thread: TMEM -> registers.
 template <int NC>
-__device__ __forceinline__ void conv_epilogue_cols(const ConvArgs& p, uint32_t taddr, int c0,
-                                                   const float* s_bias, int row, bool valid,
-                                                   int n_img, int y, int x, int n_tile,
-                                                   uint8_t* stage_base) {
-  uint32_t r[NC];
-  if constexpr (NC == 32) tmem_ld32(taddr + c0, r); else tmem_ld16(taddr + c0, r);
-  tmem_ld_wait();
+__device__ __forceinline__ void conv_load_cols(uint32_t taddr, uint32_t (&r)[NC]) {
+  if constexpr (NC == 32) tmem_ld32(taddr, r); else tmem_ld16(taddr, r);
+}
+
+template <int NC>
+__device__ __forceinline__ void conv_finish_cols(const ConvArgs& p, const uint32_t (&r)[NC], int c0,
+                                                 const float* bias_g, int row, bool valid,
+                                                 const ConvTile& t, int y, int x, uint8_t* stage_base) {
   float v[NC];
+  const float4* b4 = reinterpret_cast<const float4*>(bias_g + t.n_tile * p.BN + c0);
 #pragma unroll
-  for (int j = 0; j < NC; ++j) {
-    float a = __uint_as_float(r[j]) + s_bias[c0 + j];
-    v[j] = p.silu ? silu_f(a) : a;
+  for (int j = 0; j < NC / 4; ++j) {
+    const float4 b = __ldg(b4 + j);
+    v[4 * j + 0] = __uint_as_float(r[4 * j + 0]) + b.x;
+    v[4 * j + 1] = __uint_as_float(r[4 * j + 1]) + b.y;
+    v[4 * j + 2] = __uint_as_float(r[4 * j + 2]) + b.z;
+    v[4 * j + 3] = __uint_as_float(r[4 * j + 3]) + b.w;
+  }
+  if (p.silu) {
+#pragma unroll
+    for (int j = 0; j < NC; ++j) v[j] = silu_f(v[j]);
   }
   if (p.mode == 0) {
     if (p.resid != nullptr && valid) {
-      const __nv_bfloat16* rp = p.resid + ((size_t)((size_t)n_img * p.Ho + y) * p.Wo + x) * p.r_ctot +
-                                p.r_coff + n_tile * p.BN + c0;
+      const __nv_bfloat16* rp = p.resid + ((size_t)((size_t)t.n_img * p.Ho + y) * p.Wo + x) * p.r_ctot +
+                                p.r_coff + t.n_tile * p.BN + c0;
       const uint4* rp4 = reinterpret_cast<const uint4*>(rp);
 #pragma unroll
       for (int u = 0; u < NC / 8; ++u) {
-        uint4 q = __ldg(rp4 + u);
+        const uint4 q = __ldg(rp4 + u);
         const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&q);
 #pragma unroll
         for (int e = 0; e < 4; ++e) {
-          float2 f = __bfloat1622float2(h[e]);
+          const float2 f = __bfloat1622float2(h[e]);
           v[u * 8 + e * 2] += f.x;
           v[u * 8 + e * 2 + 1] += f.y;
         }
@@ -93,15 +139,12 @@ __device__ __forceinline__ void conv_epilogue_cols(const ConvArgs& p, uint32_t t
       q.w = pack_bf16x2(v[u * 8 + 6], v[u * 8 + 7]);
       *reinterpret_cast<uint4*>(rowp + (((u0 + u) ^ sw) << 4)) = q;
     }
-  } else {
-    if (valid) {
-      float* op = p.out_f32 +
-                  ((size_t)n_img * p.rows_per_img + p.row_off + (size_t)y * p.Wo + x) * p.out_ld +
-                  p.out_col;
+  } else if (valid) {
+    float* op = p.out_f32 +
+                ((size_t)t.n_img * p.rows_per_img + p.row_off + (size_t)y * p.Wo + x) * p.out_ld + p.out_col;
 #pragma unroll
-      for (int j = 0; j < NC; ++j)
-        if (c0 + j < p.n_valid) op[c0 + j] = v[j];
-    }
+    for (int j = 0; j < NC; ++j)
+      if (c0 + j < p.n_valid) op[c0 + j] = v[j];
   }
 }
 
@@ -110,9 +153,9 @@ conv_umma_kernel(const __grid_constant__ ConvMaps maps, const __grid_constant__ 
   extern __shared__ uint8_t smem_raw[];
   __shared__ uint64_t full_bar[kConvMaxStages];
   __shared__ uint64_t empty_bar[kConvMaxStages];
-  __shared__ uint64_t tmem_full_bar;
+  __shared__ uint64_t tmem_full_bar[2];
+  __shared__ uint64_t tmem_empty_bar[2];
   __shared__ uint32_t tmem_base_s;
-  __shared__ float s_bias[256];
 
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
                                              ~(uintptr_t)1023);
@@ -121,16 +164,7 @@ conv_umma_kernel(const __grid_constant__ ConvMaps maps, const __grid_constant__ 
   const int a_bytes = 128 * p.ck * 2;
   const int b_bytes = p.BN * p.ck * 2;
   const int stage_bytes = a_bytes + b_bytes;
-
-  const int m_tile = blockIdx.x;
-  const int n_tile = blockIdx.y;
-  const int n_img = m_tile / p.tiles_per_img;
-  const int rem = m_tile - n_img * p.tiles_per_img;
-  const int ty = rem / p.tiles_w;
-  const int tx = rem - ty * p.tiles_w;
-  const int y0 = ty * p.TH;
-  const int x0 = tx * p.TW;
-  const int total_it = p.taps * p.kchunks;
+  const int its_per_tile = p.taps * p.kchunks;
 
   if (warp == 0 && lane == 0) {
     prefetch_tmap(&maps.a[0]);
@@ -140,86 +174,137 @@ conv_umma_kernel(const __grid_constant__ ConvMaps maps, const __grid_constant__ 
       mbar_init(&full_bar[s], 1);
       mbar_init(&empty_bar[s], 1);
     }
-    mbar_init(&tmem_full_bar, 1);
+    for (int a = 0; a < 2; ++a) {
+      mbar_init(&tmem_full_bar[a], 1);
+      mbar_init(&tmem_empty_bar[a], 4);  // one arrive per epilogue warp
+    }
     fence_mbar_init();
   }
   if (warp == 1) tmem_alloc(&tmem_base_s, (uint32_t)p.tmem_cols);
-  if (warp >= 2) {
-    for (int i = threadIdx.x - 64; i < p.BN; i += 128) s_bias[i] = p.bias[n_tile * p.BN + i];
-  }
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = tmem_base_s;
+  if (p.pdl && threadIdx.x == 0) pdl_launch_dependents();
 
   if (warp == 0) {
+    // ------------------------------------------------------------------ TMA producer
     if (lane == 0) {
       const uint32_t tx_bytes = (uint32_t)(p.TW * p.TH * p.ck * 2 + b_bytes);
       int it = 0;
-      for (int tap = 0; tap < p.taps; ++tap) {
-        const CUtensorMap* am = &maps.a[p.tap_map[tap]];
-        const int cx = x0 + p.tap_dx[tap];
-        const int cy = y0 + p.tap_dy[tap];
-        for (int kc = 0; kc < p.kchunks; ++kc, ++it) {
-          const int s = it % p.stages;
-          const uint32_t ph = (uint32_t)(it / p.stages) & 1u;
-          mbar_wait(&empty_bar[s], ph ^ 1u);
-          uint8_t* sa = smem + (size_t)s * stage_bytes;
-          mbar_expect_tx(&full_bar[s], tx_bytes);
-          tma_load_4d(sa, am, &full_bar[s], p.cin_off + kc * p.ck, cx, cy, n_img);
-          tma_load_3d(sa + a_bytes, &maps.b, &full_bar[s], kc * p.ck, n_tile * p.BN, tap);
+      bool waited = !p.pdl;
+      for (int t = blockIdx.x; t < p.total_tiles; t += gridDim.x) {
+        const ConvTile c = conv_tile(p, t);
+        for (int tap = 0; tap < p.taps; ++tap) {
+          const CUtensorMap* am = &maps.a[p.tap_map[tap]];
+          const int cx = c.x0 + p.tap_dx[tap];
+          const int cy = c.y0 + p.tap_dy[tap];
+          for (int kc = 0; kc < p.kchunks; ++kc, ++it) {
+            const int s = it % p.stages;
+            const uint32_t ph = (uint32_t)(it / p.stages) & 1u;
+            mbar_wait(&empty_bar[s], ph ^ 1u);
+            uint8_t* sa = smem + (size_t)s * stage_bytes;
+            mbar_expect_tx(&full_bar[s], tx_bytes);
+            // weights do not depend on the previous layer: issue them before the dependency wait
+            tma_load_3d(sa + a_bytes, &maps.b, &full_bar[s], kc * p.ck, c.n_tile * p.BN, tap);
+            if (!waited) {
+              pdl_wait();
+              waited = true;
+            }
+            tma_load_4d(sa, am, &full_bar[s], p.cin_off + kc * p.ck, cx, cy, c.n_img);
+          }
         }
       }
     }
   } else if (warp == 1) {
+    // ------------------------------------------------------------------ MMA issuer
     if (lane == 0) {
       const uint32_t idesc = umma_idesc_bf16(128, p.BN);
       const uint32_t lt = (p.ck == 64) ? 2u : (p.ck == 32 ? 4u : 6u);
       const uint32_t sbo = (uint32_t)(8 * p.ck * 2);
       const int ksteps = p.ck >> 4;
-      for (int it = 0; it < total_it; ++it) {
-        const int s = it % p.stages;
-        const uint32_t ph = (uint32_t)(it / p.stages) & 1u;
-        mbar_wait(&full_bar[s], ph);
+      int it = 0, j = 0;
+      for (int t = blockIdx.x; t < p.total_tiles; t += gridDim.x, ++j) {
+        const int acc = j & 1;
+        const uint32_t aph = (uint32_t)(j >> 1) & 1u;
+        mbar_wait(&tmem_empty_bar[acc], aph ^ 1u);  // epilogue has drained this accumulator
         tc_fence_after();
-        const uint32_t a_addr = smem_u32(smem + (size_t)s * stage_bytes);
-        const uint32_t b_addr = a_addr + (uint32_t)a_bytes;
-        for (int k = 0; k < ksteps; ++k) {
-          const uint64_t ad = umma_smem_desc(a_addr + k * 32, sbo, lt);
-          const uint64_t bd = umma_smem_desc(b_addr + k * 32, sbo, lt);
-          umma_bf16(tmem_base, ad, bd, idesc, (uint32_t)((it | k) != 0));
+        const uint32_t d_tmem = tmem_base + (uint32_t)(acc * p.acc_stride);
+        for (int i = 0; i < its_per_tile; ++i, ++it) {
+          const int s = it % p.stages;
+          const uint32_t ph = (uint32_t)(it / p.stages) & 1u;
+          mbar_wait(&full_bar[s], ph);
+          tc_fence_after();
+          const uint32_t a_addr = smem_u32(smem + (size_t)s * stage_bytes);
+          const uint32_t b_addr = a_addr + (uint32_t)a_bytes;
+          for (int k = 0; k < ksteps; ++k) {
+            const uint64_t ad = umma_smem_desc(a_addr + k * 32, sbo, lt);
+            const uint64_t bd = umma_smem_desc(b_addr + k * 32, sbo, lt);
+            umma_bf16(d_tmem, ad, bd, idesc, (uint32_t)((i | k) != 0));
+          }
+          umma_commit(&empty_bar[s]);
         }
-        umma_commit(&empty_bar[s]);
+        umma_commit(&tmem_full_bar[acc]);
       }
-      umma_commit(&tmem_full_bar);
     }
   } else {
-    mbar_wait(&tmem_full_bar, 0);
-    tc_fence_after();
+    // ------------------------------------------------------------------ epilogue (4 warps)
     const int q = warp & 3;
     const int row = q * 32 + lane;
     const int ly = row / p.TW;
     const int lx = row - ly * p.TW;
-    const int y = y0 + ly;
-    const int x = x0 + lx;
-    const bool valid = (row < p.TW * p.TH) && (y < p.Ho) && (x < p.Wo);
-    const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16);
-    int c0 = 0;
-    for (; c0 + 32 <= p.BN; c0 += 32)
-      conv_epilogue_cols<32>(p, taddr, c0, s_bias, row, valid, n_img, y, x, n_tile, smem);
-    if (c0 < p.BN)
-      conv_epilogue_cols<16>(p, taddr, c0, s_bias, row, valid, n_img, y, x, n_tile, smem);
-    if (p.mode == 0) {
-      fence_proxy_async_smem();
-      asm volatile("bar.sync 1, 128;" ::: "memory");
-      if (warp == 2 && lane == 0) {
-        const int nchunks = p.BN / p.out_chunk;
-        for (int c = 0; c < nchunks; ++c)
-          tma_store_4d(&maps.o, smem + (size_t)c * 128 * p.out_chunk * 2,
-                       p.cout_off + n_tile * p.BN + c * p.out_chunk, x0, y0, n_img);
-        tma_store_commit_wait();
+    uint8_t* staging = smem + p.staging_off;
+    if (p.pdl && p.resid != nullptr) pdl_wait();
+    int j = 0;
+    for (int t = blockIdx.x; t < p.total_tiles; t += gridDim.x, ++j) {
+      const ConvTile c = conv_tile(p, t);
+      const int acc = j & 1;
+      const uint32_t aph = (uint32_t)(j >> 1) & 1u;
+      const int y = c.y0 + ly;
+      const int x = c.x0 + lx;
+      const bool valid = (row < p.TW * p.TH) && (y < p.Ho) && (x < p.Wo);
+      mbar_wait(&tmem_full_bar[acc], aph);
+      tc_fence_after();
+      if (p.mode == 0 && j > 0) {
+        // the previous tile's TMA store must have finished READING the staging area
+        if (warp == 2 && lane == 0) tma_store_wait_read();
+        asm volatile("bar.sync 1, 128;" ::: "memory");
+      }
+      const uint32_t taddr = tmem_base + (uint32_t)(acc * p.acc_stride) + ((uint32_t)(q * 32) << 16);
+      int c0 = 0;
+      for (; c0 + 32 <= p.BN; c0 += 32) {
+        uint32_t r[32];
+        conv_load_cols<32>(taddr + c0, r);
+        tmem_ld_wait();
+        if (c0 + 32 >= p.BN) {  // last slab read: hand the accumulator back to the MMA warp
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(&tmem_empty_bar[acc]);
+        }
+        conv_finish_cols<32>(p, r, c0, p.bias, row, valid, c, y, x, staging);
+      }
+      if (c0 < p.BN) {
+        uint32_t r[16];
+        conv_load_cols<16>(taddr + c0, r);
+        tmem_ld_wait();
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&tmem_empty_bar[acc]);
+        conv_finish_cols<16>(p, r, c0, p.bias, row, valid, c, y, x, staging);
+      }
+      if (p.mode == 0) {
+        fence_proxy_async_smem();
+        asm volatile("bar.sync 1, 128;" ::: "memory");
+        if (warp == 2 && lane == 0) {
+          const int nchunks = p.BN / p.out_chunk;
+          for (int ch = 0; ch < nchunks; ++ch)
+            tma_store_4d(&maps.o, staging + (size_t)ch * 128 * p.out_chunk * 2,
+                         p.cout_off + c.n_tile * p.BN + ch * p.out_chunk, c.x0, c.y0, c.n_img);
+          tma_store_commit();
+        }
       }
     }
+    if (p.mode == 0 && warp == 2 && lane == 0) tma_store_wait_read();
   }
   tc_fence_before();
   __syncthreads();

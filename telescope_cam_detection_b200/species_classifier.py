@@ -1,0 +1,202 @@
+"""SpeciesClassifier -- drop-in for the data path of the reference's src/species_classifier.py.
+
+What is rebuilt here is what north_star names for Stage 2: the crop -> [N,3,S,S] gather
+(`preprocess`, `crop_batch`: BGR->RGB, bilinear resize with the ATen tap rule, /255, ImageNet
+mean/std; reference :298-352) as ONE batched CUDA kernel for all crops of a frame
+(csrc/crop_resize.cu), and the result logic around the network (softmax / top-k / hierarchical
+taxonomy label / geographic whitelist; reference :179-236, :354-474).  The classifier BODY is a
+third-party timm model in the reference (:258-262) and the "next" row N2 of SURVEY.md section 8(f):
+any `torch.nn.Module` mapping [N,3,S,S] float32 -> [N,num_classes] logits can be plugged in
+(`model=` or `model_factory=`); `load_model` builds it with timm only if timm is importable.
+"""
+import json
+import logging
+import time
+from pathlib import Path
+from typing import Any, Callable, Dict, List, Optional, Tuple
+
+import numpy as np
+
+logger = logging.getLogger(__name__)
+
+
+class SpeciesClassifier:
+    def __init__(self, model_name: str = "tf_efficientnet_b4_ns", checkpoint_path: Optional[str] = None,
+                 device: str = "cuda", confidence_threshold: float = 0.3, taxonomy_file: Optional[str] = None,
+                 input_size: int = 224, use_hierarchical: bool = True, allowed_species: Optional[List[str]] = None,
+                 enable_geographic_filter: bool = False, model: Any = None,
+                 model_factory: Optional[Callable[[int], Any]] = None):
+        self.model_name = model_name
+        self.checkpoint_path = checkpoint_path
+        self.device = device
+        self.confidence_threshold = confidence_threshold
+        self.model = model
+        self._factory = model_factory
+        self.taxonomy: Dict[Any, Any] = {}
+        self.use_hierarchical = use_hierarchical
+        self.enable_geographic_filter = enable_geographic_filter
+        self.allowed_species = set(allowed_species) if allowed_species else set()
+        self.input_size = input_size
+        self.mean = [0.485, 0.456, 0.406]
+        self.std = [0.229, 0.224, 0.225]
+        self.hierarchy_thresholds = {"species": 0.5, "genus": 0.4, "family": 0.3, "order": 0.3, "class": 0.2}
+        if taxonomy_file:
+            self._load_taxonomy(taxonomy_file)
+
+    # ------------------------------------------------------------------ taxonomy (reference :112-236)
+    def _load_taxonomy(self, taxonomy_file: str, require_taxonomy: bool = False):
+        try:
+            path = Path(taxonomy_file)
+            if not path.exists():
+                raise FileNotFoundError("Taxonomy file not found: %s" % taxonomy_file)
+            if path.suffix == ".json":
+                with open(path) as f:
+                    data = json.load(f)
+                if not isinstance(data, dict):
+                    raise ValueError("taxonomy JSON must be an object keyed by class id")
+                self.taxonomy = data
+            else:
+                with open(path) as f:
+                    self.taxonomy = {str(i): line.strip() for i, line in enumerate(f) if line.strip()}
+        except Exception as e:
+            if require_taxonomy:
+                raise RuntimeError("Failed to load taxonomy from %s: %s" % (taxonomy_file, e))
+            logger.warning("%s - continuing with generic labels", e)
+            self.taxonomy = {}
+
+    def get_hierarchical_label(self, class_id: int, confidence: float) -> Tuple[Optional[str], Optional[str]]:
+        entry = self.taxonomy.get(str(class_id), {})
+        if isinstance(entry, str):
+            return entry, "species"
+        if not self.use_hierarchical:
+            if isinstance(entry, dict):
+                return (entry.get("common_name") or entry.get("name") or "species_%d" % class_id), "species"
+            return "species_%d" % class_id, "species"
+        th = self.hierarchy_thresholds
+        if confidence >= th["species"]:
+            return (entry.get("common_name") or entry.get("name", "species_%d" % class_id)), "species"
+        # one level per confidence band; an empty field in that band yields no label (reference :219-235)
+        for level in ("genus", "family", "order", "class"):
+            if confidence >= th[level]:
+                val = entry.get(level, "")
+                return (val, level) if val else (None, None)
+        return None, None
+
+    # ------------------------------------------------------------------ model
+    def load_model(self, num_classes: int = 1000, max_retries: int = 3) -> bool:
+        for attempt in range(max_retries):
+            try:
+                import torch
+                if self.model is None:
+                    if self._factory is not None:
+                        self.model = self._factory(num_classes)
+                    else:
+                        import timm  # the reference's dependency; not part of this image
+                        name = self.model_name
+                        if name.startswith("timm/") or "/" in name:
+                            name = "hf-hub:" + name
+                        self.model = timm.create_model(name, pretrained=(self.checkpoint_path is None),
+                                                       num_classes=num_classes)
+                    if self.checkpoint_path:
+                        ck = torch.load(self.checkpoint_path, map_location=self.device)
+                        self.model.load_state_dict(ck["model_state_dict"] if "model_state_dict" in ck else ck)
+                self.model = self.model.to(self.device).eval()
+                return True
+            except (RuntimeError, OSError, IOError, ConnectionError) as e:
+                if attempt < max_retries - 1:
+                    logger.warning("Model load failed (attempt %d/%d): %s", attempt + 1, max_retries, e)
+                    time.sleep(2 ** attempt)
+                else:
+                    logger.error("Failed to load species classifier after %d attempts: %s", max_retries, e)
+                    return False
+            except Exception as e:
+                logger.error("Failed to load species classifier: %s", e, exc_info=True)
+                return False
+        return False
+
+    # ------------------------------------------------------------------ crop gather (the CUDA part)
+    def _dev_frame(self, image):
+        import torch
+        t = image if isinstance(image, torch.Tensor) else torch.from_numpy(np.ascontiguousarray(image))
+        if not t.is_cuda:
+            t = t.to(self.device if str(self.device).startswith("cuda") else "cuda")
+        return t.contiguous()
+
+    def crop_batch(self, frame, boxes):
+        """All crops of one frame in one launch: boxes int [N,4] (x1,y1,x2,y2), already padded and
+        clamped -> float32 CUDA tensor [N,3,S,S], normalised like `preprocess`."""
+        import torch
+        from . import engine
+        t = self._dev_frame(frame)
+        boxes = np.ascontiguousarray(boxes, np.int32).reshape(-1, 4)
+        S = int(self.input_size)
+        out = torch.empty((boxes.shape[0], 3, S, S), dtype=torch.float32, device=t.device)
+        if boxes.shape[0]:
+            engine.crop_resize(t.data_ptr(), int(t.shape[0]), int(t.shape[1]), t.stride(0), boxes, S, out.data_ptr(),
+                               layout=0, swap_rb=1, scale=1.0 / 255.0, mean=self.mean, std=self.std)
+        return out
+
+    def preprocess(self, image):
+        """(h,w,3) u8 BGR crop -> (1,3,S,S) float32 on the GPU (reference :298-352)."""
+        h, w = int(image.shape[0]), int(image.shape[1])
+        return self.crop_batch(image, [[0, 0, w, h]])
+
+    # ------------------------------------------------------------------ results
+    def _rows_to_results(self, probs_row, idx_row) -> List[Dict[str, Any]]:
+        out = []
+        floor = 0.1 if self.use_hierarchical else self.confidence_threshold
+        for prob, idx in zip(probs_row, idx_row):
+            prob, idx = float(prob), int(idx)
+            if prob < floor:
+                continue
+            label, level = self.get_hierarchical_label(idx, prob)
+            if label is None:
+                continue
+            if self.enable_geographic_filter and self.allowed_species and label not in self.allowed_species:
+                continue
+            out.append({"species": label, "confidence": prob, "class_id": idx, "taxonomic_level": level})
+        return out
+
+    def _topk(self, batch, top_k):
+        import torch
+        with torch.no_grad():
+            probs = torch.softmax(self.model(batch), dim=1)
+            p, i = torch.topk(probs, min(top_k, probs.shape[1]), dim=1)
+        return p.cpu().numpy(), i.cpu().numpy()  # ONE sync for the whole batch (the reference .item()s per value)
+
+    def classify(self, image, top_k: int = 5) -> List[Dict[str, Any]]:
+        if self.model is None:
+            logger.error("Model not loaded. Call load_model() first.")
+            return []
+        try:
+            p, i = self._topk(self.preprocess(image), top_k)
+            return self._rows_to_results(p[0], i[0])
+        except Exception as e:
+            logger.error("Classification failed: %s", e)
+            return []
+
+    def classify_crops(self, frame, boxes, top_k: int = 5) -> List[List[Dict[str, Any]]]:
+        """Batched Stage 2: every box of `frame` gathered by one kernel, one forward, one D2H.
+        Per-crop results equal `classify(frame[y1:y2, x1:x2], top_k)`."""
+        if self.model is None:
+            logger.error("Model not loaded. Call load_model() first.")
+            return [[] for _ in boxes]
+        if len(boxes) == 0:
+            return []
+        p, i = self._topk(self.crop_batch(frame, boxes), top_k)
+        return [self._rows_to_results(p[n], i[n]) for n in range(len(boxes))]
+
+    def classify_batch(self, images: List[np.ndarray], top_k: int = 5) -> List[List[Dict[str, Any]]]:
+        """Reference :428-474: plain taxonomy lookup by int id, global threshold, no hierarchy."""
+        if self.model is None:
+            logger.error("Model not loaded. Call load_model() first.")
+            return []
+        try:
+            import torch
+            p, i = self._topk(torch.cat([self.preprocess(img) for img in images], 0), top_k)
+            return [[{"species": self.taxonomy.get(int(c), "species_%d" % int(c)), "confidence": float(q),
+                      "class_id": int(c)} for q, c in zip(p[n], i[n]) if float(q) >= self.confidence_threshold]
+                    for n in range(len(images))]
+        except Exception as e:
+            logger.error("Batch classification failed: %s", e)
+            return []

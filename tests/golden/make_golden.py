@@ -5,6 +5,9 @@ box, so the outputs are committed; rerun with `python tests/golden/make_golden.p
   motion_ref.npz   MotionFilter.filter_detections on tests/util.motion_sequence (per-detection
                    verdict + ratio, incl. the one-apply-per-detection quirk)
   empty_ref.npz    EmptyFrameFilter.has_motion verdicts on the same frames
+  stage2_ref.json  TwoStageDetectionPipeline.process_detections over recording classifiers: the crop
+                   windows the reference slices (read back from a coordinate-encoding frame), the
+                   top_k it asks for and the species fields it writes, incl. the time-of-day re-rank
   format_ref.json  YOLOXDetector._format_model_output_to_detections and
                    InferenceEngine._post_process_detections on seeded postprocess rows, with the
                    shipped per-class tables (config/config.yaml:238-264).  These two import
@@ -127,6 +130,73 @@ def format_and_filter():
         shutil.rmtree(tmp, ignore_errors=True)
 
 
+def index_frame(h=1080, w=1920):
+    """frame whose pixel values encode their own coordinates, so a crop reveals its window"""
+    ys, xs = np.mgrid[0:h, 0:w]
+    return np.stack([xs % 256, ys % 256, (xs // 256) * 16 + (ys // 256)], -1).astype(np.uint8)
+
+
+def stage2_detections(seed=5, n=60, h=1080, w=1920):
+    rng = np.random.default_rng(seed)
+    dets = []
+    for i in range(n):
+        bw, bh = np.exp(rng.uniform(np.log(20), np.log(700), 2))
+        x1, y1 = rng.uniform(-60, w - 10), rng.uniform(-60, h - 10)
+        box = {"x1": float(x1), "y1": float(y1), "x2": float(x1 + bw), "y2": float(y1 + bh)}
+        if i % 11 == 0:
+            box["x1"], box["x2"] = box["x2"], box["x1"]
+        d = {"class_id": int(rng.choice([14, 15, 16, 21, 0, 2])), "class_name": "x", "confidence": 0.9, "bbox": box}
+        if i % 3 == 0:
+            d["time_of_day"] = "day"
+        dets.append(d)
+    return dets
+
+
+CANNED = [{"species": "Great Horned Owl", "confidence": 0.62, "class_id": 7, "taxonomic_level": "species"},
+          {"species": "Gambel's Quail", "confidence": 0.41, "class_id": 9, "taxonomic_level": "genus"},
+          {"species": "Aves", "confidence": 0.35, "class_id": 3, "taxonomic_level": "class"}]
+
+
+def stage2():
+    tmp = stub_reference_tree()
+    try:
+        for k in [k for k in sys.modules if k == "src" or k.startswith("src.")]:
+            del sys.modules[k]
+        from src.two_stage_pipeline_yolox import TwoStageDetectionPipeline
+
+        class Recorder:
+            def __init__(self):
+                self.calls = []
+
+            def classify(self, crop, top_k=5):
+                c = np.asarray(crop)
+                x1 = int(c[0, 0, 0]) + 256 * (int(c[0, 0, 2]) // 16)
+                y1 = int(c[0, 0, 1]) + 256 * (int(c[0, 0, 2]) % 16)
+                self.calls.append([x1, y1, x1 + c.shape[1], y1 + c.shape[0], int(top_k)])
+                return [dict(r) for r in CANNED[:top_k]]
+
+        frame = index_frame()
+        out = {"versions": versions(), "cases": []}
+        for pad, min_crop in [(20, 64), (0, 32), (35, 100)]:
+            pipe = TwoStageDetectionPipeline(crop_padding_percent=pad, min_crop_size=min_crop, device="cpu")
+            rec_b, rec_m = Recorder(), Recorder()
+            pipe.add_species_classifier("bird", rec_b)
+            pipe.add_species_classifier("mammal", rec_m)
+            dets = pipe.process_detections(frame, stage2_detections())
+            out["cases"].append({"pad": pad, "min_crop": min_crop, "bird_calls": rec_b.calls, "mammal_calls": rec_m.calls,
+                                 "detections": json.loads(json.dumps(dets))})
+        with open(os.path.join(HERE, "stage2_ref.json"), "w") as f:
+            json.dump(out, f)
+        print("stage2: %s" % [(len(c["bird_calls"]), len(c["mammal_calls"])) for c in out["cases"]])
+    finally:
+        shutil.rmtree(tmp, ignore_errors=True)
+
+
 if __name__ == "__main__":
-    motion_and_empty()
-    format_and_filter()
+    which = sys.argv[1:] or ["motion", "format", "stage2"]
+    if "motion" in which:
+        motion_and_empty()
+    if "format" in which:
+        format_and_filter()
+    if "stage2" in which:
+        stage2()

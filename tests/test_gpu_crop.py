@@ -47,3 +47,38 @@ def test_crop_resize_matches_reference_ops(S):
         assert (got[i] - ref).abs().max().item() <= 2e-5, "crop %d %s" % (i, b)
     assert torch.equal(out16[..., :3].permute(0, 3, 1, 2).cpu(), got.to(torch.bfloat16))
     assert bool((out16[..., 3] == 0).all())
+
+
+def test_species_classifier_batched_equals_per_crop():
+    """stand-in classifier body (random-init conv net; the timm body is 'next' row N2): the batched
+    gather + single forward must give what the reference's one-crop-at-a-time loop gives"""
+    import torch
+    from telescope_cam_detection_b200.species_classifier import SpeciesClassifier
+    from telescope_cam_detection_b200.two_stage_pipeline_yolox import TwoStageDetectionPipeline
+    torch.manual_seed(0)
+    body = torch.nn.Sequential(torch.nn.Conv2d(3, 16, 7, 4), torch.nn.ReLU(), torch.nn.AdaptiveAvgPool2d(4),
+                               torch.nn.Flatten(), torch.nn.Linear(256, 50))
+    with torch.no_grad():
+        body[-1].weight.mul_(30.0)   # peaky softmax so several confidence bands occur
+    clf = SpeciesClassifier(device="cuda:0", input_size=224, model_factory=lambda n: body)
+    assert clf.load_model(num_classes=50)
+    clf.taxonomy = {str(i): {"common_name": "sp%d" % i, "genus": "g%d" % (i % 7), "family": "f%d" % (i % 3),
+                             "order": "o", "class": "c"} for i in range(50)}
+    frame = structured_frame(8)
+    boxes = [[100, 100, 400, 300], [0, 0, 224, 224], [1500, 700, 1920, 1080], [640, 360, 1000, 900]]
+    batched = clf.classify_crops(frame, boxes, top_k=3)
+    for b, res in zip(boxes, batched):
+        single = clf.classify(frame[b[1]:b[3], b[0]:b[2]], top_k=3)
+        assert [(r["class_id"], r["species"], r["taxonomic_level"]) for r in res] == \
+               [(r["class_id"], r["species"], r["taxonomic_level"]) for r in single]
+        assert all(abs(x["confidence"] - y["confidence"]) < 1e-5 for x, y in zip(res, single))
+    assert clf.preprocess(frame[100:300, 100:400]).shape == (1, 3, 224, 224)
+    pipe = TwoStageDetectionPipeline(min_crop_size=32)
+    pipe.add_species_classifier("bird", clf)
+    dets = [{"class_id": 14, "class_name": "bird", "confidence": 0.9,
+             "bbox": {"x1": 100.0, "y1": 100.0, "x2": 400.0, "y2": 300.0}},
+            {"class_id": 0, "class_name": "person", "confidence": 0.9,
+             "bbox": {"x1": 10.0, "y1": 10.0, "x2": 200.0, "y2": 300.0}}]
+    out = pipe.process_detections(torch.from_numpy(frame).cuda(), dets)      # GPU-tensor frames are part of the API
+    assert out[0]["stage2_category"] == "bird" and "species_confidence" in out[0]
+    assert out[1]["species"] is None and "stage2_category" not in out[1]
