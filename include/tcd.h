@@ -103,7 +103,8 @@ tcd_status tcd_detect_batch(tcd_detector* det, const uint8_t* const* frames, con
                             int32_t frames_on_device, float* out_dets, int32_t* out_counts);
 
 /* Split-phase variant used by the pipelined coordinator / bench: enqueue on the handle's
- * stream `slot` (0 or 1), then wait.  H2D of batch k+1 overlaps compute of batch k.      */
+ * stream `slot` (0 .. tcd_detector_num_slots()-1), then wait.  H2D of batch k+1 overlaps
+ * compute of batch k; low-occupancy layers of different slots share the chip.            */
 tcd_status tcd_detect_batch_async(tcd_detector* det, int32_t slot, const uint8_t* const* frames,
                                   const int32_t* h, const int32_t* w, const int64_t* row_stride,
                                   int32_t B, int32_t frames_on_device);
@@ -125,6 +126,11 @@ tcd_status tcd_detector_last_timing(const tcd_detector* det, float out_ms[5]);
 /* CUDA stream (cudaStream_t) the handle launches pipeline slot 0/1 on -- lets a caller record
  * its own events around async calls (bench.py times with events on THIS stream).           */
 void* tcd_detector_stream(tcd_detector* det, int32_t slot);
+int32_t tcd_detector_num_slots(const tcd_detector* det);
+/* Measurement aid: in-kernel timeline (clock64 / globaltimer stamps of the first and last CTA)
+ * of conv op `idx` of the batch-B layer plan; see conv_umma.cuh for the slot meaning (2x16 milestones + 4x16 per-tile stamps of CTA 0).   */
+tcd_status tcd_detector_trace_op(tcd_detector* det, int32_t B, int32_t idx, int32_t reps,
+                                 uint64_t out128[128], int32_t* grid, int32_t* smem_bytes);
 /* Measurement aid: one eager (graph-less) pass per iteration with a CUDA-event pair around every
  * kernel.  Ops in launch order: 0 = preprocess, 1..n_layers = layer plan (tcgen05 convs,
  * upsample, SPP pool), then decode_filter, sort, nms_mask, nms_reduce.  op_ms[i] = mean ms.  */

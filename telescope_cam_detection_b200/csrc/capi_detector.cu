@@ -1,6 +1,7 @@
 // C ABI glue, part 2: the YOLOX detector handle (preprocess -> network -> decode/NMS).
-// Two independent pipeline slots (own stream, staging, activation arena, CUDA graph, pinned
-// result table) let the H2D copy of batch k+1 overlap the compute of batch k.
+// kSlots independent pipeline slots (own stream, staging, activation arena, CUDA graph, pinned
+// result table) let the H2D copy of batch k+1 overlap the compute of batch k, and let the
+// short low-occupancy layers of one batch share the chip with another batch's.
 #include <atomic>
 #include <map>
 #include <string.h>
@@ -16,6 +17,9 @@ extern std::atomic<uint64_t> g_launch_count;
 }
 
 namespace {
+
+constexpr int kSlots = 4;
+constexpr int kProfileReps = 8;
 
 struct Slot {
   cudaStream_t stream = nullptr;
@@ -42,7 +46,7 @@ struct tcd_detector {
   tcd_detector_cfg cfg;
   int device = 0;
   YoloxWeights wts;
-  Slot slot[2];
+  Slot slot[kSlots];
   float thr_host[2] = {0.25f, 0.45f};
   int n_anchors = 0, cap = 0;
   float last_ms[5] = {0, 0, 0, 0, 0};
@@ -232,10 +236,10 @@ tcd_status tcd_create_detector(const tcd_detector_cfg* cfg, const void* packed_w
       rc = TCD_ERR_UNSUPPORTED;
     }
   }
-  for (int i = 0; i < 2 && rc == TCD_OK; ++i) rc = slot_init(d, d->slot[i]);
+  for (int i = 0; i < kSlots && rc == TCD_OK; ++i) rc = slot_init(d, d->slot[i]);
   // build the max-batch plan up front so the first frame does not pay for it
   YoloxPlan* p = nullptr;
-  for (int i = 0; i < 2 && rc == TCD_OK; ++i) rc = get_plan(d, d->slot[i], cfg->max_batch, &p);
+  for (int i = 0; i < kSlots && rc == TCD_OK; ++i) rc = get_plan(d, d->slot[i], cfg->max_batch, &p);
   if (rc) {
     tcd_destroy_detector(d);
     return (tcd_status)rc;
@@ -250,7 +254,7 @@ void tcd_destroy_detector(tcd_detector* det) {
   if (!det) return;
   cudaSetDevice(det->device);
   cudaDeviceSynchronize();
-  for (int i = 0; i < 2; ++i) slot_free(det->slot[i]);
+  for (int i = 0; i < kSlots; ++i) slot_free(det->slot[i]);
   det->wts.release();
   delete det;
 }
@@ -259,7 +263,7 @@ tcd_status tcd_detector_set_thresholds(tcd_detector* det, float conf_thre, float
   TCD_REQUIRE(det, "set_thresholds: null detector");
   det->thr_host[0] = conf_thre;
   det->thr_host[1] = nms_thre;
-  for (int i = 0; i < 2; ++i) {
+  for (int i = 0; i < kSlots; ++i) {
     // ordered after work already queued on the slot; never touches the captured graphs
     TCD_CUDA_OK(cudaStreamSynchronize(det->slot[i].stream));
     TCD_CUDA_OK(cudaMemcpy(det->slot[i].thr_dev, det->thr_host, 2 * sizeof(float), cudaMemcpyHostToDevice));
@@ -274,7 +278,7 @@ tcd_status tcd_detect_batch_async(tcd_detector* det, int32_t slot, const uint8_t
                                   int32_t B, int32_t frames_on_device) {
   int rc = check_batch(det, frames, h, w, B);
   if (rc) return (tcd_status)rc;
-  TCD_REQUIRE(slot == 0 || slot == 1, "detect: slot %d", slot);
+  TCD_REQUIRE(slot >= 0 && slot < kSlots, "detect: slot %d outside [0,%d)", slot, kSlots);
   Slot& s = det->slot[slot];
   YoloxPlan* p = nullptr;
   rc = get_plan(det, s, B, &p);
@@ -296,7 +300,7 @@ tcd_status tcd_detect_batch_async(tcd_detector* det, int32_t slot, const uint8_t
 }
 
 tcd_status tcd_detect_batch_wait(tcd_detector* det, int32_t slot, float* out_dets, int32_t* out_counts) {
-  TCD_REQUIRE(det && out_dets && out_counts && (slot == 0 || slot == 1), "detect_wait: bad argument");
+  TCD_REQUIRE(det && out_dets && out_counts && slot >= 0 && slot < kSlots, "detect_wait: bad argument");
   Slot& s = det->slot[slot];
   TCD_REQUIRE(s.pending_B > 0, "detect_wait: nothing pending on slot %d", slot);
   TCD_CUDA_OK(cudaStreamSynchronize(s.stream));
@@ -379,8 +383,40 @@ tcd_status tcd_postprocess(tcd_detector* det, const float* pred_host, int32_t B,
 }
 
 void* tcd_detector_stream(tcd_detector* det, int32_t slot) {
-  if (!det || (slot != 0 && slot != 1)) return nullptr;
+  if (!det || slot < 0 || slot >= kSlots) return nullptr;
   return (void*)det->slot[slot].stream;
+}
+
+int32_t tcd_detector_num_slots(const tcd_detector* det) { return det ? kSlots : 0; }
+
+// In-kernel timeline of ONE conv launch of the layer plan (op index as in tcd_detector_profile,
+// i.e. 1-based over the plan): the kernel stamps clock64/globaltimer at its pipeline milestones for
+// the first and the last CTA of the grid (slot meaning: conv_umma.cuh).  Runs the op `reps` times
+// eagerly on slot 0 and returns the stamps of the last run.
+tcd_status tcd_detector_trace_op(tcd_detector* det, int32_t B, int32_t idx, int32_t reps,
+                                 uint64_t out128[128], int32_t* grid, int32_t* smem_bytes) {
+  TCD_REQUIRE(det && out128, "trace_op: null argument");
+  Slot& s = det->slot[0];
+  YoloxPlan* p = nullptr;
+  int rc = get_plan(det, s, B, &p);
+  if (rc) return (tcd_status)rc;
+  TCD_REQUIRE(idx >= 1 && idx <= (int)p->ops.size() && p->ops[idx - 1].kind == OP_CONV,
+              "trace_op: op %d is not a conv", idx);
+  ConvPlan cp = p->ops[idx - 1].conv;
+  unsigned long long* buf = nullptr;
+  TCD_CUDA_OK(cudaMalloc((void**)&buf, 128 * sizeof(unsigned long long)));
+  TCD_CUDA_OK(cudaMemset(buf, 0, 128 * sizeof(unsigned long long)));
+  cp.args.trace = buf;
+  for (int r = 0; r < (reps < 1 ? 1 : reps) && rc == TCD_OK; ++r) {
+    rc = conv_plan_launch(cp, s.stream);
+    if (rc == TCD_OK && cudaStreamSynchronize(s.stream) != cudaSuccess) rc = TCD_ERR_CUDA;
+  }
+  if (rc == TCD_OK)
+    cudaMemcpy(out128, buf, 128 * sizeof(unsigned long long), cudaMemcpyDeviceToHost);
+  cudaFree(buf);
+  if (grid) *grid = (int32_t)cp.grid.x;
+  if (smem_bytes) *smem_bytes = cp.smem_bytes;
+  return (tcd_status)rc;
 }
 
 // Eager (graph-less) pass with a CUDA-event pair around every kernel of one detect_batch:
@@ -414,8 +450,11 @@ tcd_status tcd_detector_profile(tcd_detector* det, const uint8_t* const* frames,
     rc = preproc_launch(&pc, s.pre_host, s.pre_dev, B, 1, p->input, s.stream);
     cudaEventRecord(ev[1], s.stream);
     for (size_t i = 0; i < p->ops.size() && rc == TCD_OK; ++i) {
+      // conv launches are bracketed kProfileReps at a time (same launch repeated back to back, as
+      // the graph issues them) so the event pair does not dominate a 5 us kernel
+      const int reps = p->ops[i].kind == OP_CONV ? kProfileReps : 1;
       cudaEventRecord(ev[2 * (i + 1)], s.stream);
-      rc = p->run_one((int)i, s.stream);
+      for (int r = 0; r < reps && rc == TCD_OK; ++r) rc = p->run_one((int)i, s.stream);
       cudaEventRecord(ev[2 * (i + 1) + 1], s.stream);
     }
     if (rc) break;
@@ -431,7 +470,8 @@ tcd_status tcd_detector_profile(tcd_detector* det, const uint8_t* const* frames,
     for (int i = 0; i < n; ++i) {
       float t = 0.f;
       cudaEventElapsedTime(&t, ev[2 * (size_t)i], ev[2 * (size_t)i + 1]);
-      acc[i] += t;
+      const bool is_conv = i >= 1 && i <= (int)p->ops.size() && p->ops[i - 1].kind == OP_CONV;
+      acc[i] += is_conv ? t / kProfileReps : t;
     }
   }
   for (auto& e : ev) cudaEventDestroy(e);

@@ -38,6 +38,25 @@ static const bool g_use_pdl = [] {
   return !(e && e[0] == '1');
 }();
 
+// Tuning knobs for A/B measurements (bench.py records the environment it ran with):
+//   TCD_CONV_SMEM_KB   shared-memory budget of a one-CTA-per-SM launch (default 220; the
+//                      two-per-SM budget is half of it)
+//   TCD_CONV_STAGES    upper bound of the operand ring depth (default kConvMaxStages)
+static int env_int(const char* name, int dflt) {
+  const char* e = getenv(name);
+  if (!e || !e[0]) return dflt;
+  const int v = atoi(e);
+  return v > 0 ? v : dflt;
+}
+static const int g_smem_kb = env_int("TCD_CONV_SMEM_KB", 220);
+static const int g_max_stages = env_int("TCD_CONV_STAGES", kConvMaxStages);
+//   TCD_CONV_HALO=0    disable the halo formulation of 3x3 stride-1 convs (one box per tap instead)
+static const bool g_use_halo = [] {
+  const char* e = getenv("TCD_CONV_HALO");
+  return !(e && e[0] == '0');
+}();
+
+
 static int sm_count() {
   static int n = 0;
   if (n == 0) {
@@ -134,7 +153,29 @@ int conv_plan_build(const ConvDesc& d, ConvPlan* plan) {
   a.Wo = d.W / d.stride;
   choose_tile(a.Ho, a.Wo, &a.TW, &a.TH);
   a.tiles_w = cdiv(a.Wo, a.TW);
-  const int tiles_h = cdiv(a.Ho, a.TH);
+  int tiles_h = cdiv(a.Ho, a.TH);
+  // halo formulation (3x3, stride 1): an 8-wide x 16-tall output patch makes every 8-row core-matrix
+  // group one image line, so a tap shift is a constant row offset into the (TH+2)x(TW+2) halo box and
+  // the group stride (SBO) is one halo line.  Taken unless the fixed patch shape wastes > 25 % tiles.
+  a.halo = 0;
+  const int ck_probe = d.cin >= 64 ? 64 : d.cin;
+  // Measured (profiles/r01_conv_timeline.md): the halo form wins where all nine weight taps fit one
+  // <= 32 KiB stage (stem 73 -> 39 us, dark2 bottleneck 21 -> 14.5 us: one barrier round trip per
+  // k-chunk instead of nine); for the 128-channel layers its 47 KiB of halo buffers cost the second
+  // resident CTA per SM and it loses (head.conv_a.0 29 -> 57 us), so those keep one box per tap.
+  const bool halo_pays = 9 * (d.cout_pad >= 128 ? 128 : d.cout_pad) * ck_probe * 2 <= 32768 ||
+                         env_int("TCD_CONV_HALO", 1) == 2;
+  if (g_use_halo && halo_pays && d.k == 3 && d.stride == 1) {
+    const long t_halo = (long)cdiv(a.Wo, 8) * cdiv(a.Ho, 16);
+    if (4 * t_halo <= 5 * (long)a.tiles_w * tiles_h) {
+      a.halo = 1;
+      a.TW = 8;
+      a.TH = 16;
+      a.tiles_w = cdiv(a.Wo, 8);
+      tiles_h = cdiv(a.Ho, 16);
+    }
+  }
+  a.halo_w = a.TW + 2;
   a.tiles_per_img = a.tiles_w * tiles_h;
   a.taps = d.k * d.k;
   a.ck = d.cin >= 64 ? 64 : d.cin;
@@ -179,6 +220,7 @@ int conv_plan_build(const ConvDesc& d, ConvPlan* plan) {
   a.rows_per_img = d.rows_per_img;
   a.row_off = d.row_off;
   a.pdl = g_use_pdl ? 1 : 0;
+  a.dbg = env_int("TCD_CONV_DBG", 0);
   int tc = 32;
   while (tc < BN) tc <<= 1;
   a.acc_stride = tc;        // two accumulators, tc columns apart
@@ -200,21 +242,45 @@ int conv_plan_build(const ConvDesc& d, ConvPlan* plan) {
   }
   // pipeline depth / smem: one persistent CTA per SM gets a deep ring; layers with many more
   // tiles than SMs and short K loops run two CTAs per SM (twice the epilogue warps)
-  const int a_bytes = 128 * a.ck * 2, b_bytes = BN * a.ck * 2;
-  const int stage_bytes = a_bytes + b_bytes;
+  const int a_bytes = a.halo ? 0 : 128 * a.ck * 2, b_bytes = BN * a.ck * 2;
+  // halo mode: a weight stage carries as many filter taps as fit 32 KiB (fewer barrier round trips
+  // per tile -- the small-channel layers are otherwise paced by them, not by bytes)
+  a.tps = 1;
+  if (a.halo) a.tps = 9 * b_bytes <= 32768 ? 9 : (3 * b_bytes <= 32768 ? 3 : 1);
+  const int stage_bytes = a_bytes + b_bytes * a.tps;
   TCD_REQUIRE(stage_bytes % 1024 == 0, "conv: stage bytes %d not 1 KiB aligned", stage_bytes);
-  const int staging = mode == 0 ? 128 * BN * 2 : 0;
-  const int its_per_tile = a.taps * a.kchunks;
-  const bool two_per_sm = a.total_tiles >= 2 * n_sm && a.tmem_cols <= 256;
-  const int budget = (two_per_sm ? 110 : 220) * 1024 - 2048;
-  const long its_per_cta = (long)its_per_tile * cdiv(a.total_tiles, n_sm * (two_per_sm ? 2 : 1));
-  int stages = (budget - staging) / stage_bytes;
+  const int staging = mode == 0 ? 128 * BN * 2 : 128 * (BN + 1) * 4;
+  const int its_per_tile = a.taps * a.kchunks / a.tps;
+  bool two_per_sm = a.total_tiles >= 2 * n_sm && a.tmem_cols <= 256;
+  int stages = 0, halo_bytes = 0;
+  long its_per_cta = 0;
+  for (int attempt = 0; attempt < 2; ++attempt) {
+    const int budget = (two_per_sm ? g_smem_kb / 2 : g_smem_kb) * 1024 - 2048;
+    const long tiles_per_cta = cdiv(a.total_tiles, n_sm * (two_per_sm ? 2 : 1));
+    its_per_cta = (long)its_per_tile * tiles_per_cta;
+    halo_bytes = 0;
+    if (a.halo) {
+      a.a_stage_bytes = (((a.TW + 2) * (a.TH + 2) * a.ck * 2) + 1023) & ~1023;
+      const long want = (long)a.kchunks * tiles_per_cta;
+      a.a_stages = (int)(want < 3 ? want : 3);
+      // a weight ring of >= 4 stages matters more than a third halo buffer
+      while (a.a_stages > 2 && (budget - staging - a.a_stages * a.a_stage_bytes) / stage_bytes < 4) --a.a_stages;
+      halo_bytes = a.a_stages * a.a_stage_bytes;
+    }
+    stages = (budget - staging - halo_bytes) / stage_bytes;
+    if (stages >= (a.halo ? 4 : 2) || !two_per_sm || (long)stages >= its_per_cta) break;
+    two_per_sm = false;  // the half-SM budget starves the ring: one CTA per SM with a deep ring instead
+  }
   if (stages > kConvMaxStages) stages = kConvMaxStages;
+  if (stages > g_max_stages) stages = g_max_stages;
   if ((long)stages > its_per_cta) stages = (int)its_per_cta;
-  TCD_REQUIRE(stages >= 1, "conv: no room for a pipeline stage (%d B stage, %d B staging)", stage_bytes, staging);
+  TCD_REQUIRE(stages >= 1, "conv: no room for a pipeline stage (%d B stage, %d B staging, %d B halo)",
+              stage_bytes, staging, halo_bytes);
   a.stages = stages;
-  a.staging_off = stages * stage_bytes;
-  plan->smem_bytes = stages * stage_bytes + staging + 1024;
+  a.a_ring_off = stages * stage_bytes;
+  a.staging_off = a.a_ring_off + halo_bytes;
+  a.bias_n = d.cout_pad <= kConvMaxBias ? d.cout_pad : 0;
+  plan->smem_bytes = stages * stage_bytes + halo_bytes + staging + 1024;
   const int ctas = n_sm * (two_per_sm ? 2 : 1);
   plan->grid = dim3((unsigned)(a.total_tiles < ctas ? a.total_tiles : ctas), 1, 1);
   plan->flops = 2.0 * d.N * a.Ho * a.Wo * (double)d.cout * d.cin * a.taps;
@@ -226,7 +292,8 @@ int conv_plan_build(const ConvDesc& d, ConvPlan* plan) {
     cuuint64_t dims[4] = {(cuuint64_t)d.x_ctot, (cuuint64_t)d.W, (cuuint64_t)d.H, (cuuint64_t)d.N};
     cuuint64_t st[3] = {(cuuint64_t)d.x_ctot * es, (cuuint64_t)d.W * d.x_ctot * es,
                         (cuuint64_t)d.H * d.W * d.x_ctot * es};
-    cuuint32_t box[4] = {(cuuint32_t)a.ck, (cuuint32_t)a.TW, (cuuint32_t)a.TH, 1};
+    cuuint32_t box[4] = {(cuuint32_t)a.ck, (cuuint32_t)(a.halo ? a.TW + 2 : a.TW),
+                         (cuuint32_t)(a.halo ? a.TH + 2 : a.TH), 1};
     int rc = encode_map(&plan->maps.a[0], (void*)d.x, 4, dims, st, box, inner, "A");
     if (rc) return rc;
     for (int i = 1; i < 4; ++i) plan->maps.a[i] = plan->maps.a[0];
@@ -246,7 +313,7 @@ int conv_plan_build(const ConvDesc& d, ConvPlan* plan) {
   {
     cuuint64_t dims[3] = {(cuuint64_t)d.cin, (cuuint64_t)d.cout_pad, (cuuint64_t)a.taps};
     cuuint64_t st[2] = {(cuuint64_t)d.cin * es, (cuuint64_t)d.cout_pad * d.cin * es};
-    cuuint32_t box[3] = {(cuuint32_t)a.ck, (cuuint32_t)BN, 1};
+    cuuint32_t box[3] = {(cuuint32_t)a.ck, (cuuint32_t)BN, (cuuint32_t)a.tps};
     int rc = encode_map(&plan->maps.b, (void*)d.w, 3, dims, st, box, inner, "B");
     if (rc) return rc;
   }
@@ -264,7 +331,7 @@ int conv_plan_build(const ConvDesc& d, ConvPlan* plan) {
   static cudaError_t attr_err = cudaSuccess;
   std::call_once(once, [] {
     attr_err = cudaFuncSetAttribute(conv_umma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                    225 * 1024);
+                                    222 * 1024);
   });
   if (attr_err != cudaSuccess) {
     set_last_error("cudaFuncSetAttribute(conv_umma_kernel): %s", cudaGetErrorString(attr_err));

@@ -31,6 +31,8 @@ namespace tcd {
 
 constexpr int kConvMaxStages = 8;
 constexpr int kConvThreads = 192;
+constexpr int kConvMaxAStages = 4;
+constexpr int kConvMaxBias = 512;
 
 struct ConvMaps {
   CUtensorMap a[4];
@@ -48,12 +50,21 @@ struct ConvArgs {
   int acc_stride;               // TMEM columns between the two accumulator buffers
   int staging_off;              // byte offset of the epilogue staging area inside dynamic smem
   int pdl;                      // launched with programmatic stream serialization
+  // halo mode (3x3 stride 1): ONE (TH+2)x(TW+2) input box per k-chunk serves all nine taps through
+  // row-shifted UMMA descriptors (the swizzle is a function of the absolute shared-memory address for
+  // TMA and UMMA alike, so a view may start at any 128-byte row with base-offset 0 -- measured: the
+  // parity tests pass with 0 and fail with (start >> 7) & 7); the operand ring then carries weights only
+  int halo, a_stages, a_stage_bytes, a_ring_off, halo_w;
+  int dbg;                      // measurement only (TCD_CONV_DBG): 1 = no operand loads, 2 = no MMAs
+  int tps;                      // filter taps per weight stage (halo mode: 1, 3 or 9; else 1)
+  int bias_n;                   // entries of bias staged in shared memory (0: read from global)
   const float* bias;
   const __nv_bfloat16* resid;
   int r_ctot, r_coff;
   float* out_f32;
   int out_ld, out_col, rows_per_img, row_off;
   int8_t tap_map[9], tap_dx[9], tap_dy[9];
+  unsigned long long* trace;    // optional in-kernel timeline (tcd_detector_trace_op); nullptr on the product path
 };
 
 #if defined(__CUDACC__) && defined(TCD_CONV_KERNEL_IMPL)
@@ -68,6 +79,44 @@ __device__ __forceinline__ void tma_store_wait_read() {
 __device__ __forceinline__ void tma_store_commit() {
   asm volatile("cp.async.bulk.commit_group;" ::: "memory");
 }
+
+__device__ __forceinline__ unsigned long long gtimer_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+  return t;
+}
+// Timeline slots (first and last CTA of the grid, 16 slots each): 0 globaltimer at entry, 1 clock at
+// entry, 2 setup done, 3 first A load issued, 4 last load issued, 5 first operands landed, 6 last MMA
+// committed, 7 first accumulator ready, 8 last store issued, 9 stores drained, 10 clock at exit,
+// 11 globaltimer at exit.
+__device__ __forceinline__ void conv_trace(const ConvArgs& p, int k, bool wall = false) {
+  if (p.trace == nullptr) return;
+  int sel;
+  if (blockIdx.x == 0) sel = 0;
+  else if (blockIdx.x == gridDim.x - 1) sel = 1;
+  else return;
+  p.trace[sel * 16 + k] = wall ? gtimer_ns() : (unsigned long long)clock64();
+}
+
+// per-tile stamps of CTA 0 (first 16 tiles): 32+j producer starts tile j, 48+j MMA commits tile j,
+// 64+j epilogue sees accumulator j, 80+j epilogue issued the store of tile j
+__device__ __forceinline__ void conv_trace_tile(const ConvArgs& p, int base, int j) {
+  if (p.trace == nullptr || blockIdx.x != 0 || j >= 16) return;
+  p.trace[base + j] = (unsigned long long)clock64();
+}
+
+// stage index + phase bit of a shared-memory ring, advanced without a divide
+struct RingCursor {
+  int s;
+  uint32_t ph;
+  int n;
+  __device__ __forceinline__ void advance() {
+    if (++s == n) {
+      s = 0;
+      ph ^= 1u;
+    }
+  }
+};
 
 struct ConvTile {
   int n_img, y0, x0, n_tile;
@@ -98,7 +147,7 @@ __device__ __forceinline__ void conv_finish_cols(const ConvArgs& p, const uint32
   const float4* b4 = reinterpret_cast<const float4*>(bias_g + t.n_tile * p.BN + c0);
 #pragma unroll
   for (int j = 0; j < NC / 4; ++j) {
-    const float4 b = __ldg(b4 + j);
+    const float4 b = b4[j];
     v[4 * j + 0] = __uint_as_float(r[4 * j + 0]) + b.x;
     v[4 * j + 1] = __uint_as_float(r[4 * j + 1]) + b.y;
     v[4 * j + 2] = __uint_as_float(r[4 * j + 2]) + b.z;
@@ -139,13 +188,32 @@ __device__ __forceinline__ void conv_finish_cols(const ConvArgs& p, const uint32
       q.w = pack_bf16x2(v[u * 8 + 6], v[u * 8 + 7]);
       *reinterpret_cast<uint4*>(rowp + (((u0 + u) ^ sw) << 4)) = q;
     }
-  } else if (valid) {
+  } else {
+    // f32 prediction rows: park the slab in this warp's private staging rows (stride BN+1 words,
+    // conflict-free); conv_flush_rows() writes them out coalesced
+    float* srow = reinterpret_cast<float*>(stage_base) + (size_t)row * (p.BN + 1) + c0;
+#pragma unroll
+    for (int j = 0; j < NC; ++j) srow[j] = v[j];
+  }
+}
+
+// mode 1: each epilogue warp streams its 32 staged rows to out_f32, one row (n_valid consecutive
+// floats) per step with the lanes across columns.
+__device__ __forceinline__ void conv_flush_rows(const ConvArgs& p, const ConvTile& t, int q, int lane,
+                                                const uint8_t* stage_base) {
+  __syncwarp();
+  const float* st = reinterpret_cast<const float*>(stage_base);
+  for (int r = 0; r < 32; ++r) {
+    const int row = q * 32 + r;
+    const int ly = row / p.TW;
+    const int y = t.y0 + ly, x = t.x0 + (row - ly * p.TW);
+    if (row >= p.TW * p.TH || y >= p.Ho || x >= p.Wo) continue;
     float* op = p.out_f32 +
                 ((size_t)t.n_img * p.rows_per_img + p.row_off + (size_t)y * p.Wo + x) * p.out_ld + p.out_col;
-#pragma unroll
-    for (int j = 0; j < NC; ++j)
-      if (c0 + j < p.n_valid) op[c0 + j] = v[j];
+    const float* sr = st + (size_t)row * (p.BN + 1);
+    for (int c = lane; c < p.n_valid; c += 32) op[c] = sr[c];
   }
+  __syncwarp();
 }
 
 __global__ void __launch_bounds__(kConvThreads)
@@ -155,16 +223,20 @@ conv_umma_kernel(const __grid_constant__ ConvMaps maps, const __grid_constant__ 
   __shared__ uint64_t empty_bar[kConvMaxStages];
   __shared__ uint64_t tmem_full_bar[2];
   __shared__ uint64_t tmem_empty_bar[2];
+  __shared__ uint64_t a_full_bar[kConvMaxAStages];
+  __shared__ uint64_t a_empty_bar[kConvMaxAStages];
+  __shared__ __align__(16) float s_bias[kConvMaxBias];
   __shared__ uint32_t tmem_base_s;
 
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
                                              ~(uintptr_t)1023);
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
-  const int a_bytes = 128 * p.ck * 2;
+  const int a_bytes = p.halo ? 0 : 128 * p.ck * 2;
   const int b_bytes = p.BN * p.ck * 2;
-  const int stage_bytes = a_bytes + b_bytes;
+  const int stage_bytes = a_bytes + b_bytes * p.tps;
   const int its_per_tile = p.taps * p.kchunks;
+  if (threadIdx.x == 0) { conv_trace(p, 0, true); conv_trace(p, 1); }
 
   if (warp == 0 && lane == 0) {
     prefetch_tmap(&maps.a[0]);
@@ -178,43 +250,91 @@ conv_umma_kernel(const __grid_constant__ ConvMaps maps, const __grid_constant__ 
       mbar_init(&tmem_full_bar[a], 1);
       mbar_init(&tmem_empty_bar[a], 4);  // one arrive per epilogue warp
     }
+    for (int a = 0; a < p.a_stages; ++a) {
+      mbar_init(&a_full_bar[a], 1);
+      mbar_init(&a_empty_bar[a], 1);
+    }
     fence_mbar_init();
   }
   if (warp == 1) tmem_alloc(&tmem_base_s, (uint32_t)p.tmem_cols);
+  // the bias never depends on the previous layer: stage it while the pipeline spins up
+  if (warp >= 2)
+    for (int i = threadIdx.x - 64; i < p.bias_n; i += 128) s_bias[i] = __ldg(p.bias + i);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = tmem_base_s;
+  if (threadIdx.x == 0) conv_trace(p, 2);
   if (p.pdl && threadIdx.x == 0) pdl_launch_dependents();
 
   if (warp == 0) {
     // ------------------------------------------------------------------ TMA producer
     if (lane == 0) {
-      const uint32_t tx_bytes = (uint32_t)(p.TW * p.TH * p.ck * 2 + b_bytes);
-      int it = 0;
       bool waited = !p.pdl;
-      for (int t = blockIdx.x; t < p.total_tiles; t += gridDim.x) {
-        const ConvTile c = conv_tile(p, t);
-        for (int tap = 0; tap < p.taps; ++tap) {
-          const CUtensorMap* am = &maps.a[p.tap_map[tap]];
-          const int cx = c.x0 + p.tap_dx[tap];
-          const int cy = c.y0 + p.tap_dy[tap];
-          for (int kc = 0; kc < p.kchunks; ++kc, ++it) {
-            const int s = it % p.stages;
-            const uint32_t ph = (uint32_t)(it / p.stages) & 1u;
-            mbar_wait(&empty_bar[s], ph ^ 1u);
-            uint8_t* sa = smem + (size_t)s * stage_bytes;
-            mbar_expect_tx(&full_bar[s], tx_bytes);
-            // weights do not depend on the previous layer: issue them before the dependency wait
-            tma_load_3d(sa + a_bytes, &maps.b, &full_bar[s], kc * p.ck, c.n_tile * p.BN, tap);
-            if (!waited) {
-              pdl_wait();
-              waited = true;
+      bool first = true;
+      RingCursor ring{0, 0u, p.stages};
+      int jt = 0;
+      if (p.halo) {
+        const uint32_t a_tx = (uint32_t)((p.TW + 2) * (p.TH + 2) * p.ck * 2);
+        const uint32_t b_tx = (uint32_t)(b_bytes * p.tps);
+        RingCursor aring{0, 0u, p.a_stages};
+        for (int t = blockIdx.x; t < p.total_tiles; t += gridDim.x, ++jt) {
+          const ConvTile c = conv_tile(p, t);
+          conv_trace_tile(p, 32, jt);
+          for (int kc = 0; kc < p.kchunks; ++kc) {
+            for (int tap = 0; tap < 9; tap += p.tps) {
+              mbar_wait(&empty_bar[ring.s], ring.ph ^ 1u);
+              mbar_expect_tx(&full_bar[ring.s], (p.dbg & 1) ? 0u : b_tx);
+              if (!(p.dbg & 1))
+                tma_load_3d(smem + (size_t)ring.s * stage_bytes, &maps.b, &full_bar[ring.s], kc * p.ck,
+                            c.n_tile * p.BN, tap);
+              ring.advance();
+              if (tap == 0) {  // the halo box of this k-chunk, after the first weight load
+                mbar_wait(&a_empty_bar[aring.s], aring.ph ^ 1u);
+                mbar_expect_tx(&a_full_bar[aring.s], (p.dbg & 1) ? 0u : a_tx);
+                if (!waited) {
+                  pdl_wait();
+                  waited = true;
+                }
+                if (!(p.dbg & 1))
+                  tma_load_4d(smem + p.a_ring_off + (size_t)aring.s * p.a_stage_bytes, &maps.a[0],
+                            &a_full_bar[aring.s], p.cin_off + kc * p.ck, c.x0 - 1, c.y0 - 1, c.n_img);
+                aring.advance();
+                if (first) conv_trace(p, 3);
+                first = false;
+              }
             }
-            tma_load_4d(sa, am, &full_bar[s], p.cin_off + kc * p.ck, cx, cy, c.n_img);
+          }
+        }
+      } else {
+        const uint32_t tx_bytes = (uint32_t)(p.TW * p.TH * p.ck * 2 + b_bytes);
+        for (int t = blockIdx.x; t < p.total_tiles; t += gridDim.x, ++jt) {
+          const ConvTile c = conv_tile(p, t);
+          conv_trace_tile(p, 32, jt);
+          for (int tap = 0; tap < p.taps; ++tap) {
+            const CUtensorMap* am = &maps.a[p.tap_map[tap]];
+            const int cx = c.x0 + p.tap_dx[tap];
+            const int cy = c.y0 + p.tap_dy[tap];
+            for (int kc = 0; kc < p.kchunks; ++kc) {
+              mbar_wait(&empty_bar[ring.s], ring.ph ^ 1u);
+              uint8_t* sa = smem + (size_t)ring.s * stage_bytes;
+              mbar_expect_tx(&full_bar[ring.s], (p.dbg & 1) ? 0u : tx_bytes);
+              // weights do not depend on the previous layer: issue them before the dependency wait
+              if (!(p.dbg & 1))
+                tma_load_3d(sa + a_bytes, &maps.b, &full_bar[ring.s], kc * p.ck, c.n_tile * p.BN, tap);
+              if (!waited) {
+                pdl_wait();
+                waited = true;
+              }
+              if (!(p.dbg & 1)) tma_load_4d(sa, am, &full_bar[ring.s], p.cin_off + kc * p.ck, cx, cy, c.n_img);
+              ring.advance();
+              if (first) conv_trace(p, 3);
+              first = false;
+            }
           }
         }
       }
+      conv_trace(p, 4);
     }
   } else if (warp == 1) {
     // ------------------------------------------------------------------ MMA issuer
@@ -223,29 +343,66 @@ conv_umma_kernel(const __grid_constant__ ConvMaps maps, const __grid_constant__ 
       const uint32_t lt = (p.ck == 64) ? 2u : (p.ck == 32 ? 4u : 6u);
       const uint32_t sbo = (uint32_t)(8 * p.ck * 2);
       const int ksteps = p.ck >> 4;
-      int it = 0, j = 0;
+      int j = 0;
+      bool first = true;
+      RingCursor ring{0, 0u, p.stages};
+      RingCursor aring{0, 0u, p.a_stages};
       for (int t = blockIdx.x; t < p.total_tiles; t += gridDim.x, ++j) {
         const int acc = j & 1;
         const uint32_t aph = (uint32_t)(j >> 1) & 1u;
         mbar_wait(&tmem_empty_bar[acc], aph ^ 1u);  // epilogue has drained this accumulator
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + (uint32_t)(acc * p.acc_stride);
-        for (int i = 0; i < its_per_tile; ++i, ++it) {
-          const int s = it % p.stages;
-          const uint32_t ph = (uint32_t)(it / p.stages) & 1u;
-          mbar_wait(&full_bar[s], ph);
-          tc_fence_after();
-          const uint32_t a_addr = smem_u32(smem + (size_t)s * stage_bytes);
-          const uint32_t b_addr = a_addr + (uint32_t)a_bytes;
-          for (int k = 0; k < ksteps; ++k) {
-            const uint64_t ad = umma_smem_desc(a_addr + k * 32, sbo, lt);
-            const uint64_t bd = umma_smem_desc(b_addr + k * 32, sbo, lt);
-            umma_bf16(d_tmem, ad, bd, idesc, (uint32_t)((i | k) != 0));
+        if (p.halo) {
+          const int rowb = p.ck * 2;
+          const uint32_t sbo_a = (uint32_t)(p.halo_w * rowb);
+          for (int kc = 0; kc < p.kchunks; ++kc) {
+            mbar_wait(&a_full_bar[aring.s], aring.ph);
+            const uint32_t halo_addr = smem_u32(smem + p.a_ring_off + (size_t)aring.s * p.a_stage_bytes);
+            for (int tap0 = 0; tap0 < 9; tap0 += p.tps) {
+              mbar_wait(&full_bar[ring.s], ring.ph);
+              tc_fence_after();
+              if (first) conv_trace(p, 5);
+              first = false;
+              const uint32_t b_base = smem_u32(smem + (size_t)ring.s * stage_bytes);
+              for (int u = 0; u < p.tps; ++u) {
+                const int tap = tap0 + u;
+                const int ty = tap / 3, tx = tap - ty * 3;
+                const uint32_t a_addr = halo_addr + (uint32_t)((ty * p.halo_w + tx) * rowb);
+                const uint32_t b_addr = b_base + (uint32_t)(u * b_bytes);
+                for (int k = 0; k < ksteps; ++k) {
+                  const uint64_t ad = umma_smem_desc(a_addr + k * 32, sbo_a, lt);
+                  const uint64_t bd = umma_smem_desc(b_addr + k * 32, sbo, lt);
+                  if (!(p.dbg & 2)) umma_bf16(d_tmem, ad, bd, idesc, (uint32_t)((kc | tap | k) != 0));
+                }
+              }
+              umma_commit(&empty_bar[ring.s]);
+              ring.advance();
+            }
+            umma_commit(&a_empty_bar[aring.s]);
+            aring.advance();
           }
-          umma_commit(&empty_bar[s]);
+        } else {
+          for (int i = 0; i < its_per_tile; ++i) {
+            mbar_wait(&full_bar[ring.s], ring.ph);
+            tc_fence_after();
+            if (first) conv_trace(p, 5);
+            first = false;
+            const uint32_t a_addr = smem_u32(smem + (size_t)ring.s * stage_bytes);
+            const uint32_t b_addr = a_addr + (uint32_t)a_bytes;
+            for (int k = 0; k < ksteps; ++k) {
+              const uint64_t ad = umma_smem_desc(a_addr + k * 32, sbo, lt);
+              const uint64_t bd = umma_smem_desc(b_addr + k * 32, sbo, lt);
+              if (!(p.dbg & 2)) umma_bf16(d_tmem, ad, bd, idesc, (uint32_t)((i | k) != 0));
+            }
+            umma_commit(&empty_bar[ring.s]);
+            ring.advance();
+          }
         }
         umma_commit(&tmem_full_bar[acc]);
+        conv_trace_tile(p, 48, j);
       }
+      conv_trace(p, 6);
     }
   } else {
     // ------------------------------------------------------------------ epilogue (4 warps)
@@ -255,6 +412,7 @@ conv_umma_kernel(const __grid_constant__ ConvMaps maps, const __grid_constant__ 
     const int lx = row - ly * p.TW;
     uint8_t* staging = smem + p.staging_off;
     if (p.pdl && p.resid != nullptr) pdl_wait();
+    const float* bias_src = p.bias_n ? s_bias : p.bias;
     int j = 0;
     for (int t = blockIdx.x; t < p.total_tiles; t += gridDim.x, ++j) {
       const ConvTile c = conv_tile(p, t);
@@ -265,6 +423,8 @@ conv_umma_kernel(const __grid_constant__ ConvMaps maps, const __grid_constant__ 
       const bool valid = (row < p.TW * p.TH) && (y < p.Ho) && (x < p.Wo);
       mbar_wait(&tmem_full_bar[acc], aph);
       tc_fence_after();
+      if (j == 0 && warp == 2 && lane == 0) conv_trace(p, 7);
+      if (warp == 2 && lane == 0) conv_trace_tile(p, 64, j);
       if (p.mode == 0 && j > 0) {
         // the previous tile's TMA store must have finished READING the staging area
         if (warp == 2 && lane == 0) tma_store_wait_read();
@@ -281,7 +441,7 @@ conv_umma_kernel(const __grid_constant__ ConvMaps maps, const __grid_constant__ 
           __syncwarp();
           if (lane == 0) mbar_arrive(&tmem_empty_bar[acc]);
         }
-        conv_finish_cols<32>(p, r, c0, p.bias, row, valid, c, y, x, staging);
+        conv_finish_cols<32>(p, r, c0, bias_src, row, valid, c, y, x, staging);
       }
       if (c0 < p.BN) {
         uint32_t r[16];
@@ -290,8 +450,9 @@ conv_umma_kernel(const __grid_constant__ ConvMaps maps, const __grid_constant__ 
         tc_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive(&tmem_empty_bar[acc]);
-        conv_finish_cols<16>(p, r, c0, p.bias, row, valid, c, y, x, staging);
+        conv_finish_cols<16>(p, r, c0, bias_src, row, valid, c, y, x, staging);
       }
+      if (p.mode == 1) conv_flush_rows(p, c, q, lane, staging);
       if (p.mode == 0) {
         fence_proxy_async_smem();
         asm volatile("bar.sync 1, 128;" ::: "memory");
@@ -303,12 +464,18 @@ conv_umma_kernel(const __grid_constant__ ConvMaps maps, const __grid_constant__ 
           tma_store_commit();
         }
       }
+      if (warp == 2 && lane == 0) conv_trace_tile(p, 80, j);
     }
-    if (p.mode == 0 && warp == 2 && lane == 0) tma_store_wait_read();
+    if (warp == 2 && lane == 0) {
+      conv_trace(p, 8);
+      if (p.mode == 0) tma_store_wait_read();
+      conv_trace(p, 9);
+    }
   }
   tc_fence_before();
   __syncthreads();
   if (warp == 1) tmem_dealloc(tmem_base, (uint32_t)p.tmem_cols);
+  if (threadIdx.x == 32) { conv_trace(p, 10); conv_trace(p, 11, true); }
 }
 
 #endif  // __CUDACC__ && TCD_CONV_KERNEL_IMPL

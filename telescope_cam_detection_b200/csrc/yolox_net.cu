@@ -167,36 +167,53 @@ upsample2x_kernel(const uint4* __restrict__ src, uint4* __restrict__ dst, int N,
 }
 
 // SPPBottleneck pools: buf[..., 0:C] -> max 5x5 / 9x9 / 13x13 (stride 1, -inf padding) into
-// buf[..., C:2C], [2C:3C], [3C:4C].  One thread per (pixel, channel pair).
+// buf[..., C:2C], [2C:3C], [3C:4C].  One CTA owns one image x 16 channels: the whole HxW plane
+// sits in shared memory and the three pools are a cascade of separable 5-wide maxima
+// (5 o 5 = 9, 5 o 5 o 5 = 13; out-of-image taps are skipped, which equals -inf padding).
+__device__ __forceinline__ uint4 max_bf16x8(const uint4 a, const uint4 b) {
+  uint4 r;
+  const __nv_bfloat162* pa = reinterpret_cast<const __nv_bfloat162*>(&a);
+  const __nv_bfloat162* pb = reinterpret_cast<const __nv_bfloat162*>(&b);
+  __nv_bfloat162* pr = reinterpret_cast<__nv_bfloat162*>(&r);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) pr[i] = __hmax2(pa[i], pb[i]);
+  return r;
+}
+
 __global__ void __launch_bounds__(256)
-spp_pool_kernel(__nv_bfloat162* __restrict__ buf, int N, int H, int W, int C2, int ctot2) {
-  const size_t total = (size_t)N * H * W * C2;
-  for (size_t i = (size_t)blockIdx.x * 256 + threadIdx.x; i < total; i += (size_t)gridDim.x * 256) {
-    const int c = (int)(i % C2);
-    size_t r = i / C2;
-    const int x = (int)(r % W);
-    r /= W;
-    const int y = (int)(r % H);
-    const int n = (int)(r / H);
-    float m5x = -INFINITY, m5y = -INFINITY, m9x = -INFINITY, m9y = -INFINITY, m13x = -INFINITY,
-          m13y = -INFINITY;
-    for (int dy = -6; dy <= 6; ++dy) {
-      const int yy = y + dy;
-      if (yy < 0 || yy >= H) continue;
-      for (int dx = -6; dx <= 6; ++dx) {
-        const int xx = x + dx;
-        if (xx < 0 || xx >= W) continue;
-        const float2 v = __bfloat1622float2(buf[((size_t)((size_t)n * H + yy) * W + xx) * ctot2 + c]);
-        const int ad = max(abs(dy), abs(dx));
-        m13x = fmaxf(m13x, v.x); m13y = fmaxf(m13y, v.y);
-        if (ad <= 4) { m9x = fmaxf(m9x, v.x); m9y = fmaxf(m9y, v.y); }
-        if (ad <= 2) { m5x = fmaxf(m5x, v.x); m5y = fmaxf(m5y, v.y); }
+spp_pool_kernel(uint4* __restrict__ buf, int H, int W, int C8, int ctot8) {
+  extern __shared__ uint4 spp_sm[];
+  uint4* A = spp_sm;                 // [H*W][2]  current plane (16 channels = 2 x uint4 per pixel)
+  uint4* T = spp_sm + 2 * H * W;     // [H*W][2]  horizontal pass
+  const int n = blockIdx.y, cg = blockIdx.x;
+  const int E = 2 * H * W;
+  uint4* img = buf + (size_t)n * H * W * ctot8 + cg * 2;
+  for (int i = threadIdx.x; i < E; i += 256) A[i] = img[(size_t)(i >> 1) * ctot8 + (i & 1)];
+  __syncthreads();
+  for (int stage = 1; stage <= 3; ++stage) {
+    for (int i = threadIdx.x; i < E; i += 256) {
+      const int pix = i >> 1, x = pix % W;
+      uint4 m = A[i];
+#pragma unroll
+      for (int d = 1; d <= 2; ++d) {
+        if (x - d >= 0) m = max_bf16x8(m, A[i - 2 * d]);
+        if (x + d < W) m = max_bf16x8(m, A[i + 2 * d]);
       }
+      T[i] = m;
     }
-    __nv_bfloat162* o = buf + ((size_t)((size_t)n * H + y) * W + x) * ctot2 + c;
-    o[C2] = __floats2bfloat162_rn(m5x, m5y);
-    o[2 * C2] = __floats2bfloat162_rn(m9x, m9y);
-    o[3 * C2] = __floats2bfloat162_rn(m13x, m13y);
+    __syncthreads();
+    for (int i = threadIdx.x; i < E; i += 256) {
+      const int pix = i >> 1, y = pix / W;
+      uint4 m = T[i];
+#pragma unroll
+      for (int d = 1; d <= 2; ++d) {
+        if (y - d >= 0) m = max_bf16x8(m, T[i - 2 * d * W]);
+        if (y + d < H) m = max_bf16x8(m, T[i + 2 * d * W]);
+      }
+      A[i] = m;
+      img[(size_t)pix * ctot8 + stage * C8 + (i & 1)] = m;
+    }
+    __syncthreads();
   }
 }
 
@@ -211,9 +228,15 @@ int upsample2x_launch(const void* src, void* dst, int N, int H, int W, int C, in
 }
 
 int spp_pool_launch(void* buf, int N, int H, int W, int C, int ctot, cudaStream_t stream) {
-  const size_t total = (size_t)N * H * W * (C / 2);
-  const int blocks = (int)((total + 255) / 256 < 148 * 8 ? (total + 255) / 256 : 148 * 8);
-  spp_pool_kernel<<<blocks, 256, 0, stream>>>((__nv_bfloat162*)buf, N, H, W, C / 2, ctot / 2);
+  TCD_REQUIRE(C % 16 == 0 && ctot % 8 == 0, "spp: C %d must be a multiple of 16", C);
+  const size_t smem = (size_t)4 * H * W * sizeof(uint4);
+  TCD_REQUIRE(smem <= 200 * 1024, "spp: %dx%d plane does not fit shared memory", H, W);
+  static size_t attr_set = 0;
+  if (smem > 48 * 1024 && smem > attr_set) {
+    TCD_CUDA_OK(cudaFuncSetAttribute(spp_pool_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    attr_set = smem;
+  }
+  spp_pool_kernel<<<dim3(C / 16, N), 256, smem, stream>>>((uint4*)buf, H, W, C / 8, ctot / 8);
   g_launch_count.fetch_add(1, std::memory_order_relaxed);
   return cudaGetLastError() == cudaSuccess ? TCD_OK : TCD_ERR_CUDA;
 }

@@ -130,6 +130,37 @@ class DetectorEngine:
         """cudaStream_t (int) of pipeline slot `slot`."""
         return int(self.lib.tcd_detector_stream(self.handle, int(slot)) or 0)
 
+    @property
+    def num_slots(self):
+        return int(self.lib.tcd_detector_num_slots(self.handle))
+
+    def trace_op(self, B, idx, reps=3):
+        """In-kernel timeline of conv op `idx` (index as in profile()).  -> dict with the clock64
+        stamps of the first / last CTA relative to kernel entry, in SM cycles, and the wall ns."""
+        buf = (C.c_uint64 * 128)()
+        grid, smem = C.c_int32(0), C.c_int32(0)
+        check(self.lib.tcd_detector_trace_op(self.handle, int(B), int(idx), int(reps), buf, C.byref(grid),
+                                             C.byref(smem)), "tcd_detector_trace_op")
+        v = list(buf)
+        names = ("setup_done", "first_A_issued", "last_load_issued", "first_operands", "last_mma_commit",
+                 "first_acc_ready", "last_store_issued", "stores_drained", "exit")
+        out = {"grid": grid.value, "smem": smem.value}
+        for sel, tag in ((0, "cta0"), (1, "ctaN")):
+            b = v[sel * 16: sel * 16 + 16]
+            if b[1] == 0:
+                continue
+            out[tag] = {n: int(b[2 + i]) - int(b[1]) if b[2 + i] else None for i, n in enumerate(names)}
+            out[tag]["wall_ns"] = int(b[11]) - int(b[0])
+            out[tag]["start_ns"] = int(b[0])
+        t0 = v[1]
+        for base, tag in ((32, "tile_prod"), (48, "tile_mma"), (64, "tile_acc"), (80, "tile_store")):
+            out[tag] = [int(x) - int(t0) for x in v[base:base + 16] if x]
+        out["prod_it"] = [int(x) - int(t0) if x else None for x in v[96:112]]
+        out["mma_it"] = [int(x) - int(t0) if x else None for x in v[112:128]]
+        if "cta0" in out and "ctaN" in out:
+            out["ctaN_start_after_cta0_ns"] = out["ctaN"]["start_ns"] - out["cta0"]["start_ns"]
+        return out
+
     def profile(self, frames, iters=5):
         """Per-kernel device times of one detect_batch (eager pass, CUDA-event pair per kernel).
         -> list of dicts {name, kind ('conv'|'other'), ms, flops}."""
