@@ -192,6 +192,57 @@ tcd_status tcd_crop_resize(const uint8_t* frame_dev, int32_t h, int32_t w, int64
                            const tcd_preproc_cfg* cfg, int32_t out_layout, void* out_dev,
                            void* stream);
 
+/* ------------------------------------------------------------------ layer programs (RT-DETR)
+ * A program is an ordered list of kernels over device buffers it owns, replayed as one CUDA
+ * graph.  The host (telescope_cam_detection_b200/rtdetr_engine.py) lays RT-DETRv2-R50 out as
+ * such a list -- the replacement of RTDETRDetector.load_model / self.model(img, orig_size),
+ * src/rtdetr_detector.py:60-204,257,340 -- from tcgen05 convs / linears plus the transformer
+ * kernels of csrc/tfm_kernels.cuh.  Nothing is allocated after the last add_*.             */
+typedef struct tcd_program tcd_program;
+typedef struct {
+  char name[64];
+  const void* x; int32_t N, H, W, x_ctot, x_coff, cin; int64_t x_nstride;   /* bf16 NHWC input view  */
+  const float* w_host; const float* bias_host;        /* f32 [cout][cin][k][k], [cout] (BN folded)     */
+  int32_t cout, k, stride, act;                       /* act: 0 none 1 SiLU 2 ReLU 3 GELU              */
+  void* y; int32_t y_ctot, y_coff; int64_t y_nstride; /* bf16 output view (NULL when out_f32 is set)   */
+  const void* resid; int32_t r_ctot, r_coff, resid_pre; int64_t r_nstride;
+  float* out_f32; int32_t out_ld, out_col, rows_per_img, row_off;  /* f32 row output (logits etc.)    */
+} tcd_conv_desc;
+enum {
+  TCD_OP_LAYERNORM = 1, TCD_OP_ADD_ROWS, TCD_OP_MASK_ROWS, TCD_OP_MHA, TCD_OP_MSDA, TCD_OP_ROWMAX,
+  TCD_OP_TOPK, TCD_OP_GATHER, TCD_OP_REF_INIT, TCD_OP_REF_UPDATE, TCD_OP_DETR_POST, TCD_OP_MAXPOOL,
+  TCD_OP_AVGPOOL, TCD_OP_UPSAMPLE
+};
+typedef struct {
+  char name[64];
+  int32_t kind;
+  void* p[8];      /* device pointers, meaning per kind (see csrc/program.cu) */
+  int32_t i[12];
+  float f[4];
+} tcd_op_desc;
+tcd_status tcd_program_create(int32_t device, tcd_program** out);
+void tcd_program_destroy(tcd_program* prog);
+tcd_status tcd_program_alloc(tcd_program* prog, size_t bytes, void** out_dev);  /* zero-filled */
+tcd_status tcd_program_upload(tcd_program* prog, const void* host, size_t bytes, void** out_dev);
+tcd_status tcd_program_add_conv(tcd_program* prog, const tcd_conv_desc* d);
+tcd_status tcd_program_add_op(tcd_program* prog, const tcd_op_desc* d);
+/* enqueue one replay on the program's stream (graph != 0: captured CUDA graph); asynchronous */
+tcd_status tcd_program_run(tcd_program* prog, int32_t graph);
+tcd_status tcd_program_sync(tcd_program* prog);
+void* tcd_program_stream(tcd_program* prog);
+int32_t tcd_program_num_ops(const tcd_program* prog);
+const char* tcd_program_op_name(const tcd_program* prog, int32_t idx);
+double tcd_program_op_flops(const tcd_program* prog, int32_t idx);   /* 2*MACs, convs / linears only */
+/* eager pass with a CUDA-event pair around every op; op_ms[i] = mean ms over iters          */
+tcd_status tcd_program_profile(tcd_program* prog, int32_t iters, float* op_ms, int32_t cap);
+/* PIL-style antialiased resize + BGR->RGB + /255 (RTDETRDetector.preprocess,
+ * src/rtdetr_detector.py:206-236; T.Resize on a PIL image, :176-180) of n HWC u8 frames (host or
+ * device) into bf16 NHWC [n,out_h,out_w,16] at out_dev; out_u8_host (optional): the resized u8 RGB
+ * image [n,out_h,out_w,3] for bit-exact parity against PIL.                                   */
+tcd_status tcd_pil_resize(const uint8_t* const* frames, const int32_t* h, const int32_t* w,
+                          const int64_t* row_stride, int32_t n, int32_t frames_on_device, int32_t out_h,
+                          int32_t out_w, void* out_dev, uint8_t* out_u8_host, void* stream);
+
 /* ------------------------------------------------------------------ small utilities    */
 tcd_status tcd_malloc_device(size_t bytes, void** out);
 tcd_status tcd_free_device(void* p);

@@ -1,0 +1,203 @@
+"""RT-DETR oracle -- TEST INFRASTRUCTURE ONLY (tests/, __graft_entry__.smoke(), bench.py's CPU leg).
+
+The reference runs upstream lyuwenyu/RT-DETR `rtdetrv2_pytorch` (git submodule `RT-DETR` @
+e47c3646036e1f0d8ce29f36663a9865304afccd, EMPTY under /root/reference; call sites
+src/rtdetr_detector.py:102,132-172,257,340) in deploy mode.  That code is not on this box, so the CPU
+oracle for the network is the independent implementation SURVEY section 8(c) names:
+`transformers` 5.5.0 `RTDetrV2ForObjectDetection` (R50vd backbone, hybrid encoder, 6-layer
+MSDeformAttn decoder), configured like the reference's deploy settings (80 classes,
+anchor_image_size=None == eval_spatial_size None, src/rtdetr_detector.py:152-158), fp32, eval.
+The postprocessor (use_focal_loss, num_top_queries=300, deploy tuple (labels, boxes, scores);
+SURVEY App. D step 8) and the reference's own preprocess body (src/rtdetr_detector.py:206-236:
+BGR->RGB, T.ToPILImage, T.Resize (PIL antialiased bilinear), T.ToTensor) are restated below.
+
+PARITY UNPINNED: the reference holds no golden vectors for this path and its RT-DETR dependency is
+absent; results are "vs transformers RT-DETRv2 (independent implementation)".
+"""
+import numpy as np
+import torch
+
+
+def make_model(seed=0, num_queries=300):
+    """Seeded, well-conditioned random RT-DETRv2-R50 (no checkpoint can be downloaded here)."""
+    from transformers import RTDetrV2Config, RTDetrV2ForObjectDetection
+
+    cfg = RTDetrV2Config()
+    cfg.num_labels = 80
+    cfg.anchor_image_size = None
+    cfg.num_queries = num_queries
+    torch.manual_seed(seed)
+    model = RTDetrV2ForObjectDetection(cfg).eval()
+    g = torch.Generator().manual_seed(seed + 1)
+
+    def randn(shape, std):
+        return torch.randn(shape, generator=g) * std
+
+    def rand(shape, lo, hi):
+        return torch.rand(shape, generator=g) * (hi - lo) + lo
+
+    with torch.no_grad():
+        sd = model.state_dict()
+        for k, v in sd.items():
+            if k.endswith("num_batches_tracked") or k.endswith("n_points_scale"):
+                continue
+            is_bn = "normalization" in k or ".norm." in k or k.split(".")[-2] == "1" and (
+                "encoder_input_proj" in k or "decoder_input_proj" in k)
+            if v.ndim == 4:  # conv: He init with gain < 1 (a random net must not amplify rounding noise)
+                fan_in = v.shape[1] * v.shape[2] * v.shape[3]
+                v.copy_(randn(v.shape, 0.8 * (2.0 / fan_in) ** 0.5))
+            elif is_bn:
+                last_of_block = ".layer.2.normalization" in k
+                if k.endswith("running_var"):
+                    v.copy_(rand(v.shape, 0.8, 1.2))
+                elif k.endswith("running_mean"):
+                    v.copy_(randn(v.shape, 0.05))
+                elif k.endswith("weight"):
+                    v.copy_(rand(v.shape, 0.25, 0.35) if last_of_block else rand(v.shape, 0.8, 1.2))
+                else:
+                    v.copy_(randn(v.shape, 0.05))
+            elif "layer_norm" in k or k.startswith("model.enc_output.1"):
+                v.copy_(rand(v.shape, 0.8, 1.2) if k.endswith("weight") else randn(v.shape, 0.02))
+            elif v.ndim == 2:
+                std = 0.8 / v.shape[1] ** 0.5
+                if "sampling_offsets" in k:
+                    std = 0.3 / v.shape[1] ** 0.5
+                if ("bbox" in k and k.endswith("layers.2.weight")):
+                    std = 0.15 / v.shape[1] ** 0.5
+                if "class_embed" in k or "enc_score_head" in k:
+                    std = 1.5 / v.shape[1] ** 0.5
+                if "query_pos_head.layers.0" in k:
+                    std = 1.0
+                v.copy_(randn(v.shape, std))
+            elif v.ndim == 1:
+                if "sampling_offsets" in k:
+                    continue  # keep the grid-pattern bias the model initialises
+                if "class_embed" in k or "enc_score_head" in k:
+                    v.copy_(randn(v.shape, 0.3) - 3.0)
+                elif k == "model.enc_output.0.bias":
+                    # border anchors are masked to zero rows; with a zero bias their LayerNorm output is
+                    # just beta and their score stays at the class-bias floor instead of tying 316 ways
+                    # inside the top-300 (a trained model scores them low as well)
+                    v.zero_()
+                else:
+                    v.copy_(randn(v.shape, 0.02))
+        model.load_state_dict(sd)
+    return model
+
+
+def state_dict_numpy(model):
+    return {k: v.detach().cpu().numpy().astype(np.float32) for k, v in model.state_dict().items()
+            if v.dtype.is_floating_point}
+
+
+def preprocess_ref(frame_bgr, input_size=(640, 640)):
+    """The body of RTDETRDetector.preprocess (src/rtdetr_detector.py:206-236) without the class:
+    BGR->RGB (cv2.cvtColor == channel reversal), PIL resize (T.Resize default = BILINEAR, antialiased),
+    ToTensor (/255).  -> (float32 [1,3,H,W], int64 [1,2] = (orig_w, orig_h), uint8 resized RGB HWC)."""
+    from PIL import Image
+
+    img = np.ascontiguousarray(frame_bgr[:, :, ::-1])
+    h, w = img.shape[:2]
+    pil = Image.fromarray(img).resize((input_size[1], input_size[0]), Image.BILINEAR)
+    u8 = np.asarray(pil)
+    t = torch.from_numpy(u8.astype(np.float32) / 255.0).permute(2, 0, 1)[None]
+    return t, torch.tensor([[w, h]]), u8
+
+
+def pil_coeffs(in_size, out_size):
+    """Pillow's precompute_coeffs + normalize_coeffs_8bpc for the BILINEAR (triangle) filter
+    (libImaging/Resample.c), restated: -> (xmin[out], count[out], kk[out, ksize] int32), 22-bit fixed point."""
+    scale = in_size / out_size
+    filterscale = max(scale, 1.0)
+    support = 1.0 * filterscale
+    ksize = int(np.ceil(support)) * 2 + 1
+    xmin = np.zeros(out_size, np.int32)
+    cnt = np.zeros(out_size, np.int32)
+    kk = np.zeros((out_size, ksize), np.int32)
+    ss = 1.0 / filterscale
+    for xx in range(out_size):
+        center = (xx + 0.5) * scale
+        x0 = int(center - support + 0.5)
+        x0 = max(x0, 0)
+        x1 = int(center + support + 0.5)
+        x1 = min(x1, in_size)
+        n = x1 - x0
+        w = np.zeros(n, np.float64)
+        for x in range(n):
+            a = abs((x + x0 - center + 0.5) * ss)
+            w[x] = 1.0 - a if a < 1.0 else 0.0
+        tot = w.sum()
+        if tot != 0:
+            w = w / tot
+        xmin[xx], cnt[xx] = x0, n
+        for x in range(n):
+            v = w[x] * (1 << 22)
+            kk[xx, x] = int(v - 0.5) if v < 0 else int(v + 0.5)
+    return xmin, cnt, kk
+
+
+def pil_resize_ref(img_u8, out_h, out_w):
+    """NumPy restatement of Pillow's two-pass 8-bit resize (horizontal then vertical, each pass
+    rounded to u8: clip8((sum + 2^21) >> 22)); bit-exact vs PIL (tests/test_oracle_rtdetr.py)."""
+    h, w, c = img_u8.shape
+    xmin, cnt, kk = pil_coeffs(w, out_w)
+    tmp = np.zeros((h, out_w, c), np.uint8)
+    src = img_u8.astype(np.int64)
+    for xx in range(out_w):
+        acc = np.full((h, c), 1 << 21, np.int64)
+        for x in range(cnt[xx]):
+            acc += src[:, xmin[xx] + x, :] * int(kk[xx, x])
+        tmp[:, xx, :] = np.clip(acc >> 22, 0, 255)
+    ymin, ycnt, kky = pil_coeffs(h, out_h)
+    out = np.zeros((out_h, out_w, c), np.uint8)
+    src = tmp.astype(np.int64)
+    for yy in range(out_h):
+        acc = np.full((out_w, c), 1 << 21, np.int64)
+        for y in range(ycnt[yy]):
+            acc += src[ymin[yy] + y] * int(kky[yy, y])
+        out[yy] = np.clip(acc >> 22, 0, 255)
+    return out
+
+
+def postprocess(logits, pred_boxes, orig_sizes, num_top_queries=300):
+    """RT-DETR postprocessor, focal-loss branch, deploy mode:
+    scores = sigmoid(logits).flatten(1); top-k; label = idx % C; query = idx // C;
+    boxes cxcywh -> xyxy scaled by (w, h, w, h).  -> labels [B,k], boxes [B,k,4], scores [B,k]."""
+    B, Q, C = logits.shape
+    cx, cy, w, h = pred_boxes.unbind(-1)
+    xyxy = torch.stack([cx - 0.5 * w, cy - 0.5 * h, cx + 0.5 * w, cy + 0.5 * h], -1)
+    xyxy = xyxy * orig_sizes.to(xyxy.dtype).repeat(1, 2)[:, None, :]
+    scores = torch.sigmoid(logits).flatten(1)
+    scores, index = torch.topk(scores, num_top_queries, dim=-1)
+    labels = index % C
+    index = index // C
+    boxes = xyxy.gather(1, index[..., None].repeat(1, 1, 4))
+    return labels, boxes, scores
+
+
+def forward(model, x):
+    """-> dict: logits [B,Q,80], pred_boxes [B,Q,4] (cxcywh, [0,1]) plus the intermediates the stage
+    parity tests tap (all NCHW / token-major fp32 torch tensors)."""
+    taps = {}
+    hooks = []
+
+    def grab(name):
+        def fn(_m, _inp, out):
+            taps[name] = out
+        return fn
+
+    core = model.model
+    hooks.append(core.backbone.register_forward_hook(grab("backbone")))
+    hooks.append(core.encoder.aifi[0].register_forward_hook(grab("aifi")))
+    hooks.append(core.enc_output.register_forward_hook(grab("enc_output")))
+    with torch.no_grad():
+        out = model(pixel_values=x)
+    for h in hooks:
+        h.remove()
+    topk = torch.topk(out.enc_outputs_class.max(-1).values, model.config.num_queries, dim=1).indices
+    res = {"logits": out.logits, "pred_boxes": out.pred_boxes, "enc_outputs_class": out.enc_outputs_class,
+           "encoder": list(out.encoder_last_hidden_state), "topk": topk,
+           "backbone": [f for f, _mask in taps["backbone"]], "aifi": taps["aifi"],
+           "enc_output": taps["enc_output"],
+           "dec_hidden": out.intermediate_hidden_states, "dec_refs": out.intermediate_reference_points}
+    return res

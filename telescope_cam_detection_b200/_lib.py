@@ -23,6 +23,31 @@ class DetectorCfg(C.Structure):
                 ("max_src_w", C.c_int32), ("pre", PreprocCfg)]
 
 
+class ConvDesc(C.Structure):
+    """tcd_conv_desc (include/tcd.h)."""
+    _fields_ = [("name", C.c_char * 64),
+                ("x", C.c_void_p), ("N", C.c_int32), ("H", C.c_int32), ("W", C.c_int32), ("x_ctot", C.c_int32),
+                ("x_coff", C.c_int32), ("cin", C.c_int32), ("x_nstride", C.c_int64),
+                ("w_host", C.c_void_p), ("bias_host", C.c_void_p),
+                ("cout", C.c_int32), ("k", C.c_int32), ("stride", C.c_int32), ("act", C.c_int32),
+                ("y", C.c_void_p), ("y_ctot", C.c_int32), ("y_coff", C.c_int32), ("y_nstride", C.c_int64),
+                ("resid", C.c_void_p), ("r_ctot", C.c_int32), ("r_coff", C.c_int32), ("resid_pre", C.c_int32),
+                ("r_nstride", C.c_int64),
+                ("out_f32", C.c_void_p), ("out_ld", C.c_int32), ("out_col", C.c_int32),
+                ("rows_per_img", C.c_int32), ("row_off", C.c_int32)]
+
+
+class OpDesc(C.Structure):
+    """tcd_op_desc (include/tcd.h)."""
+    _fields_ = [("name", C.c_char * 64), ("kind", C.c_int32), ("p", C.c_void_p * 8), ("i", C.c_int32 * 12),
+                ("f", C.c_float * 4)]
+
+
+OP_KINDS = {"layernorm": 1, "add_rows": 2, "mask_rows": 3, "mha": 4, "msda": 5, "rowmax": 6, "topk": 7,
+            "gather": 8, "ref_init": 9, "ref_update": 10, "detr_post": 11, "maxpool": 12, "avgpool": 13,
+            "upsample": 14}
+
+
 def make_preproc_cfg(out_h, out_w, mode=0, swap_rb=0, scale=1.0, mean=(0.0, 0.0, 0.0),
                      std=(1.0, 1.0, 1.0), pad_value=114.0):
     cfg = PreprocCfg()
@@ -81,6 +106,20 @@ SIGNATURES = {
     "tcd_empty_filter_step": (C.c_int, [_P, _P, C.c_int64, C.c_int32, C.c_int32, C.c_int32, _I32P, _P]),
     "tcd_crop_resize": (C.c_int, [_P, C.c_int32, C.c_int32, C.c_int64, _I32P, C.c_int32, C.c_int32,
                                   C.POINTER(PreprocCfg), C.c_int32, _P, _P]),
+    "tcd_program_create": (C.c_int, [C.c_int32, _PP]),
+    "tcd_program_destroy": (None, [_P]),
+    "tcd_program_alloc": (C.c_int, [_P, C.c_size_t, _PP]),
+    "tcd_program_upload": (C.c_int, [_P, _P, C.c_size_t, _PP]),
+    "tcd_program_add_conv": (C.c_int, [_P, C.POINTER(ConvDesc)]),
+    "tcd_program_add_op": (C.c_int, [_P, C.POINTER(OpDesc)]),
+    "tcd_program_run": (C.c_int, [_P, C.c_int32]),
+    "tcd_program_sync": (C.c_int, [_P]),
+    "tcd_program_stream": (C.c_void_p, [_P]),
+    "tcd_program_num_ops": (C.c_int32, [_P]),
+    "tcd_program_op_name": (C.c_char_p, [_P, C.c_int32]),
+    "tcd_program_op_flops": (C.c_double, [_P, C.c_int32]),
+    "tcd_program_profile": (C.c_int, [_P, C.c_int32, _F32P, C.c_int32]),
+    "tcd_pil_resize": (C.c_int, [_PP, _I32P, _I32P, _I64P, C.c_int32, C.c_int32, C.c_int32, C.c_int32, _P, _P, _P]),
     "tcd_malloc_device": (C.c_int, [C.c_size_t, _PP]),
     "tcd_free_device": (C.c_int, [_P]),
     "tcd_malloc_pinned": (C.c_int, [C.c_size_t, _PP]),

@@ -16,7 +16,8 @@ OBJ = os.path.join(HERE, "build")
 
 # TUs whose fp32 arithmetic must round exactly like the scalar reference code (no FMA contraction)
 NO_FMAD = {"postproc.cu", "motion.cu"}
-SOURCES = ["capi_core.cu", "capi_detector.cu", "capi_motion.cu", "conv_umma.cu", "yolox_net.cu",
+SOURCES = ["capi_core.cu", "capi_detector.cu", "capi_motion.cu", "conv_umma.cu", "yolox_net.cu", "program.cu",
+           "tfm_kernels.cu", "tfm_kernels2.cu", "pil_resize.cu",
            "yolox_plan.cu", "preproc.cu", "postproc.cu", "motion.cu", "crop_resize.cu"]
 ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
 COMMON = ["-O3", "-std=c++17", "-lineinfo", "-Xcompiler", "-fPIC", "-Xptxas", "-v"]
@@ -63,7 +64,7 @@ def build(force=False, verbose=False):
             print(log)
         return obj
 
-    with ThreadPoolExecutor(max_workers=min(8, len(SOURCES))) as ex:
+    with ThreadPoolExecutor(max_workers=min(12, len(SOURCES))) as ex:
         objs = list(ex.map(compile_one, SOURCES))
     cmd = [nvcc, *ARCH, "-shared", "-o", OUT, *objs, "-lcudart"]
     r = subprocess.run(cmd, capture_output=True, text=True)

@@ -214,6 +214,8 @@ int conv_plan_build(const ConvDesc& d, ConvPlan* plan) {
   a.resid = (const __nv_bfloat16*)d.resid;
   a.r_ctot = d.r_ctot;
   a.r_coff = d.r_coff;
+  a.resid_pre = d.resid_pre;
+  a.r_nstride = d.r_nstride ? d.r_nstride : (long long)a.Ho * a.Wo * d.r_ctot;
   a.out_f32 = d.out_f32;
   a.out_ld = d.out_ld;
   a.out_col = d.out_col;
@@ -291,7 +293,7 @@ int conv_plan_build(const ConvDesc& d, ConvPlan* plan) {
   if (d.stride == 1) {
     cuuint64_t dims[4] = {(cuuint64_t)d.x_ctot, (cuuint64_t)d.W, (cuuint64_t)d.H, (cuuint64_t)d.N};
     cuuint64_t st[3] = {(cuuint64_t)d.x_ctot * es, (cuuint64_t)d.W * d.x_ctot * es,
-                        (cuuint64_t)d.H * d.W * d.x_ctot * es};
+                        (cuuint64_t)(d.x_nstride ? d.x_nstride : (long long)d.H * d.W * d.x_ctot) * es};
     cuuint32_t box[4] = {(cuuint32_t)a.ck, (cuuint32_t)(a.halo ? a.TW + 2 : a.TW),
                          (cuuint32_t)(a.halo ? a.TH + 2 : a.TH), 1};
     int rc = encode_map(&plan->maps.a[0], (void*)d.x, 4, dims, st, box, inner, "A");
@@ -304,7 +306,7 @@ int conv_plan_build(const ConvDesc& d, ConvPlan* plan) {
         cuuint64_t dims[4] = {(cuuint64_t)d.x_ctot, (cuuint64_t)d.W / 2, (cuuint64_t)d.H / 2,
                               (cuuint64_t)d.N};
         cuuint64_t st[3] = {(cuuint64_t)2 * d.x_ctot * es, (cuuint64_t)2 * d.W * d.x_ctot * es,
-                            (cuuint64_t)d.H * d.W * d.x_ctot * es};
+                            (cuuint64_t)(d.x_nstride ? d.x_nstride : (long long)d.H * d.W * d.x_ctot) * es};
         cuuint32_t box[4] = {(cuuint32_t)a.ck, (cuuint32_t)a.TW, (cuuint32_t)a.TH, 1};
         int rc = encode_map(&plan->maps.a[hp * 2 + wp], base, 4, dims, st, box, inner, "A/s2");
         if (rc) return rc;
@@ -320,7 +322,7 @@ int conv_plan_build(const ConvDesc& d, ConvPlan* plan) {
   if (mode == 0) {
     cuuint64_t dims[4] = {(cuuint64_t)d.y_ctot, (cuuint64_t)a.Wo, (cuuint64_t)a.Ho, (cuuint64_t)d.N};
     cuuint64_t st[3] = {(cuuint64_t)d.y_ctot * es, (cuuint64_t)a.Wo * d.y_ctot * es,
-                        (cuuint64_t)a.Ho * a.Wo * d.y_ctot * es};
+                        (cuuint64_t)(d.y_nstride ? d.y_nstride : (long long)a.Ho * a.Wo * d.y_ctot) * es};
     cuuint32_t box[4] = {(cuuint32_t)a.out_chunk, (cuuint32_t)a.TW, (cuuint32_t)a.TH, 1};
     int rc = encode_map(&plan->maps.o, d.y, 4, dims, st, box, a.out_chunk * 2, "O");
     if (rc) return rc;

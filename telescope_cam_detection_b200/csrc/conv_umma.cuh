@@ -61,6 +61,8 @@ struct ConvArgs {
   const float* bias;
   const __nv_bfloat16* resid;
   int r_ctot, r_coff;
+  int resid_pre;                // 1: residual added BEFORE the activation (ResNet), 0: after (CSP bottleneck)
+  long long r_nstride;          // elements between images of the residual tensor
   float* out_f32;
   int out_ld, out_col, rows_per_img, row_off;
   int8_t tap_map[9], tap_dx[9], tap_dy[9];
@@ -140,6 +142,25 @@ __device__ __forceinline__ void conv_load_cols(uint32_t taddr, uint32_t (&r)[NC]
 }
 
 template <int NC>
+__device__ __forceinline__ void conv_add_resid(const ConvArgs& p, float (&v)[NC], int c0, const ConvTile& t,
+                                               int y, int x) {
+  const __nv_bfloat16* rp = p.resid + (size_t)t.n_img * p.r_nstride + ((size_t)y * p.Wo + x) * p.r_ctot +
+                            p.r_coff + t.n_tile * p.BN + c0;
+  const uint4* rp4 = reinterpret_cast<const uint4*>(rp);
+#pragma unroll
+  for (int u = 0; u < NC / 8; ++u) {
+    const uint4 q = __ldg(rp4 + u);
+    const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&q);
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      const float2 f = __bfloat1622float2(h[e]);
+      v[u * 8 + e * 2] += f.x;
+      v[u * 8 + e * 2 + 1] += f.y;
+    }
+  }
+}
+
+template <int NC>
 __device__ __forceinline__ void conv_finish_cols(const ConvArgs& p, const uint32_t (&r)[NC], int c0,
                                                  const float* bias_g, int row, bool valid,
                                                  const ConvTile& t, int y, int x, uint8_t* stage_base) {
@@ -153,27 +174,19 @@ __device__ __forceinline__ void conv_finish_cols(const ConvArgs& p, const uint32
     v[4 * j + 2] = __uint_as_float(r[4 * j + 2]) + b.z;
     v[4 * j + 3] = __uint_as_float(r[4 * j + 3]) + b.w;
   }
-  if (p.silu) {
+  if (p.mode == 0 && p.resid != nullptr && p.resid_pre && valid) conv_add_resid<NC>(p, v, c0, t, y, x);
+  if (p.silu == 1) {
 #pragma unroll
     for (int j = 0; j < NC; ++j) v[j] = silu_f(v[j]);
+  } else if (p.silu == 2) {
+#pragma unroll
+    for (int j = 0; j < NC; ++j) v[j] = fmaxf(v[j], 0.f);
+  } else if (p.silu == 3) {
+#pragma unroll
+    for (int j = 0; j < NC; ++j) v[j] = 0.5f * v[j] * (1.0f + erff(v[j] * 0.70710678118654752f));
   }
   if (p.mode == 0) {
-    if (p.resid != nullptr && valid) {
-      const __nv_bfloat16* rp = p.resid + ((size_t)((size_t)t.n_img * p.Ho + y) * p.Wo + x) * p.r_ctot +
-                                p.r_coff + t.n_tile * p.BN + c0;
-      const uint4* rp4 = reinterpret_cast<const uint4*>(rp);
-#pragma unroll
-      for (int u = 0; u < NC / 8; ++u) {
-        const uint4 q = __ldg(rp4 + u);
-        const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&q);
-#pragma unroll
-        for (int e = 0; e < 4; ++e) {
-          const float2 f = __bfloat1622float2(h[e]);
-          v[u * 8 + e * 2] += f.x;
-          v[u * 8 + e * 2 + 1] += f.y;
-        }
-      }
-    }
+    if (p.resid != nullptr && !p.resid_pre && valid) conv_add_resid<NC>(p, v, c0, t, y, x);
     const int chunk = c0 / p.out_chunk;
     const int row_bytes = p.out_chunk * 2;
     const int u0 = (c0 % p.out_chunk) >> 3;
@@ -488,7 +501,12 @@ struct ConvDesc {
   // weights: device, bf16 [taps][cout_pad][cin]; bias: device f32 [cout_pad]
   const void* w = nullptr;
   const float* bias = nullptr;
-  int cout = 0, cout_pad = 0, k = 1, stride = 1, silu = 1;
+  int cout = 0, cout_pad = 0, k = 1, stride = 1;
+  int silu = 1;  // activation: 0 none, 1 SiLU, 2 ReLU, 3 GELU (erf)
+  // elements between consecutive images; 0 = dense (H*W*ctot).  Lets a conv read / write one pyramid
+  // level inside a [B, sum(HW), C] token tensor (RT-DETR memory).
+  long long x_nstride = 0, y_nstride = 0, r_nstride = 0;
+  int resid_pre = 0;  // residual added before (1) or after (0) the activation
   // bf16 output (mode 0)
   void* y = nullptr;
   int y_ctot = 0, y_coff = 0;

@@ -1,0 +1,55 @@
+// Non-conv kernels of the RT-DETR path (src/rtdetr_detector.py:238-403 -> upstream RT-DETRv2,
+// SURVEY App. D): LayerNorm(+residual), multi-head attention over a few hundred tokens,
+// multi-scale deformable attention (gather-and-weight), per-row top-k, pooling, and the small
+// reference-point / gather glue of the decoder.  All activations bf16 token-major / NHWC,
+// arithmetic fp32; reference points, sampling offsets, logits stay fp32.
+#pragma once
+#include "tcd_common.cuh"
+
+namespace tcd {
+
+// y[r,:] = LayerNorm(a[r,:] + (b ? b[r,:] : 0)) * gamma + beta      (C <= 1024, C % 8 == 0)
+int layernorm_launch(const void* a, const void* b, const float* gamma, const float* beta, void* y,
+                     int rows, int C, float eps, cudaStream_t st);
+// y[n,t,:] = a[n,t,:] + b[(bcast ? 0 : n),t,:]        (bf16, row length C % 8 == 0)
+int add_rows_launch(const void* a, const void* b, void* y, int N, int T, int C, int bcast_b,
+                    cudaStream_t st);
+// y[n,t,:] = x[n,t,:] * mask[t]   (mask f32 0/1 per token)
+int mask_rows_launch(const void* x, const float* mask, void* y, int N, int T, int C, cudaStream_t st);
+// softmax(q k^T * scale) v per head; q/k/v: bf16 rows with leading dims ldq/ldk/ldv (elements) and
+// column offsets; out bf16 [N,Tq,heads*32].  head_dim fixed at 32 (256 / 8).
+int mha_launch(const void* q, int ldq, int qoff, const void* k, int ldk, int koff, const void* v, int ldv,
+               int voff, void* out, int ldo, int N, int Tq, int Tk, int heads, float scale,
+               cudaStream_t st);
+// Multi-scale deformable attention v2 (HF modeling_rt_detr_v2.py:44-115,166-225): value bf16
+// [N,S,heads*32]; offsets f32 [N,Q,heads,L*P,2]; logits f32 [N,Q,heads,L*P]; ref f32 [N,Q,4] (sigmoid
+// space cx,cy,w,h); out bf16 [N,Q,heads*32].  grid_sample bilinear, zeros padding, align_corners=False.
+struct MsdaLevels {
+  int n_levels, n_points;
+  int h[4], w[4], start[4];
+};
+int msda_launch(const void* value, const float* offsets, const float* logits, const float* ref, void* out,
+                int N, int Q, int S, int heads, MsdaLevels lv, float offset_scale, cudaStream_t st);
+// per-row max of f32 [rows, C] -> f32 [rows]
+int rowmax_launch(const float* x, float* y, int rows, int C, cudaStream_t st);
+// per-row top-k (descending by value, ascending index on ties) of f32 [N, n] -> int32 idx [N, k]; k <= 512
+int topk_launch(const float* keys, int N, int n, int k, int* idx_out, cudaStream_t st);
+// out[n,i,:] = src[n, idx[n,i], :]   bf16 rows of C
+int gather_rows_launch(const void* src, const int* idx, void* out, int N, int S, int K, int C,
+                       cudaStream_t st);
+// ref_unact[n,i,:] = delta[n,i,0:4] (f32, leading dim ldd) + anchors[idx[n,i],:]; ref_sig = sigmoid(.)
+// also writes the bf16 [N,K,16] copy (4 real + 12 zero channels) the query-pos MLP reads
+int ref_init_launch(const float* delta, int ldd, const float* anchors, const int* idx, float* ref_sig,
+                    void* ref_bf16, int N, int K, cudaStream_t st);
+// ref_sig = sigmoid(delta + inverse_sigmoid(ref_sig)), eps 1e-5 (HF :551-556, :637-640)
+int ref_update_launch(const float* delta, int ldd, float* ref_sig, void* ref_bf16, int rows,
+                      cudaStream_t st);
+// RT-DETR postprocessor (use_focal_loss, src/rtdetr_detector.py:257 deploy tuple): idx [N,k] over the
+// flattened [Q*C] logits -> labels, boxes xyxy scaled by orig (w,h), scores = sigmoid(logit)
+int detr_post_launch(const float* logits, const float* ref_sig, const int* idx, const float* orig_wh,
+                     int N, int Q, int C, int k, int* labels, float* boxes, float* scores,
+                     cudaStream_t st);
+// bf16 NHWC pools: 3x3 stride 2 pad 1 max (ResNet stem), 2x2 stride 2 average (ResNet-vd shortcut)
+int maxpool3x3s2_launch(const void* x, void* y, int N, int H, int W, int C, cudaStream_t st);
+int avgpool2x2_launch(const void* x, void* y, int N, int H, int W, int C, cudaStream_t st);
+}  // namespace tcd
