@@ -187,13 +187,17 @@ class RTDetrEngine:
     """
 
     def __init__(self, sd, batch, input_size=(640, 640), num_queries=300, num_classes=80, heads=8,
-                 n_points=4, offset_scale=0.5, bn_eps=1e-5, ln_eps=1e-5, device=0, keep_taps=False):
+                 n_points=4, offset_scale=0.5, bn_eps=1e-5, ln_eps=1e-5, device=0, keep_taps=False,
+                 external_topk=False):
         self.B, self.IH, self.IW = int(batch), int(input_size[0]), int(input_size[1])
         if self.IH % 32 or self.IW % 32:
             raise ValueError("input size must be a multiple of 32, got %s" % (input_size,))
         self.Q, self.NC, self.heads, self.n_points = num_queries, num_classes, heads, n_points
         self.offset_scale, self.bn_eps, self.ln_eps = offset_scale, bn_eps, ln_eps
         self.sd = sd
+        # parity aid: skip the in-graph query selection and use indices written by set_topk() (lets a test
+        # compare the decoder on exactly the oracle's query set; the product path never sets it)
+        self.external_topk = bool(external_topk)
         self.prog = Program(device)
         self.taps = {} if keep_taps else None
         self._build()
@@ -429,7 +433,8 @@ class RTDetrEngine:
         enc_max = P.f32(B * S)
         P.op("enc.rowmax", "rowmax", [enc_cls, enc_max], [B * S, NC])
         self.topk_idx = P.alloc(B * Q * 4)
-        P.op("enc.topk", "topk", [enc_max, self.topk_idx], [B, S, Q])
+        if not self.external_topk:
+            P.op("enc.topk", "topk", [enc_max, self.topk_idx], [B, S, Q])
         target = P.act(B, 1, Q, D)
         P.op("enc.gather", "gather", [out_mem.ptr, self.topk_idx, target.ptr], [B, S, Q, D])
         t = self._linear("enc_bbox.0", target, "model.enc_bbox_head.layers.0", act=ACT_RELU)
@@ -497,6 +502,10 @@ class RTDetrEngine:
         buf = np.zeros((self.B, self.IH, self.IW, 16), np.uint16)
         buf[..., :3] = to_bf16_bits(x.transpose(0, 2, 3, 1))
         self.prog.h2d(self.x_in.ptr, buf)
+
+    def set_topk(self, idx):
+        assert self.external_topk, "engine was built with its own query selection"
+        self.prog.h2d(self.topk_idx, np.asarray(idx, np.int32).reshape(self.B, self.Q))
 
     def set_orig_sizes(self, wh):
         self.prog.h2d(self.orig_wh, np.asarray(wh, np.float32).reshape(self.B, 2))
