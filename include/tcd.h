@@ -168,6 +168,10 @@ tcd_status tcd_mog2_roi_counts(tcd_mog2* m, int32_t shadow_thr, int32_t ksize, i
                                const int32_t* rois, int32_t n_rois, int32_t* counts_host,
                                uint8_t* clean_mask_host);
 
+/* device time (CUDA events on the handle's stream) of the last call's kernels, ms:
+ * [0] one MOG2 apply, [1] mask clean-up (threshold + blur + threshold) + ROI counts       */
+tcd_status tcd_mog2_last_ms(const tcd_mog2* m, float out_ms[2]);
+
 /* ------------------------------------------------------------------ empty-frame gate (K10)
  * Replaces EmptyFrameFilter.has_motion, src/empty_frame_filter.py:51-98.                 */
 typedef struct tcd_empty_filter tcd_empty_filter;
@@ -181,6 +185,8 @@ tcd_status tcd_empty_filter_reset(tcd_empty_filter* f);
 tcd_status tcd_empty_filter_step(tcd_empty_filter* f, const uint8_t* frame, int64_t row_stride,
                                  int32_t channels, int32_t frame_on_device, int32_t threshold,
                                  int32_t* changed_pixels_host, uint8_t* gray_blur_host);
+
+float tcd_empty_filter_last_ms(const tcd_empty_filter* f);  /* fused gray+blur+absdiff+count kernel, ms */
 
 /* ------------------------------------------------------------------ Stage-2 crops (K13)
  * Replaces the per-detection slice frame[y1:y2, x1:x2] (src/two_stage_pipeline_yolox.py:289)

@@ -100,6 +100,8 @@ SIGNATURES = {
     "tcd_mog2_reset": (C.c_int, [_P]),
     "tcd_mog2_apply": (C.c_int, [_P, _P, C.c_int64, C.c_int32, C.c_int32, _P]),
     "tcd_mog2_roi_counts": (C.c_int, [_P, C.c_int32, C.c_int32, C.c_int32, _I32P, C.c_int32, _I32P, _P]),
+    "tcd_mog2_last_ms": (C.c_int, [_P, _F32P]),
+    "tcd_empty_filter_last_ms": (C.c_float, [_P]),
     "tcd_empty_filter_create": (C.c_int, [C.c_int32, C.c_int32, C.c_int32, C.c_int32, _PP]),
     "tcd_empty_filter_destroy": (None, [_P]),
     "tcd_empty_filter_reset": (C.c_int, [_P]),

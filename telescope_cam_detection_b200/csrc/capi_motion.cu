@@ -63,6 +63,8 @@ struct tcd_mog2 {
   unsigned int* counts_dev = nullptr;
   int roi_cap = 0;
   cudaStream_t stream = nullptr;
+  cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};  // apply begin/end, clean-up begin/end
+  float last_ms[2] = {0.f, 0.f};                             // per apply; blur+threshold+roi count
 };
 
 struct tcd_empty_filter {
@@ -72,6 +74,8 @@ struct tcd_empty_filter {
   uint8_t* prev = nullptr;
   unsigned int* counter = nullptr;
   cudaStream_t stream = nullptr;
+  cudaEvent_t ev[2] = {nullptr, nullptr};
+  float last_ms = 0.f;
   uint16_t k[kBlurMaxK];
 };
 
@@ -88,6 +92,7 @@ tcd_status tcd_mog2_create(int32_t h, int32_t w, int32_t history, float var_thre
   m->detect_shadows = detect_shadows; m->var_threshold = var_threshold;
   const size_t np = (size_t)h * w;
   TCD_CUDA_OK(cudaStreamCreateWithFlags(&m->stream, cudaStreamNonBlocking));
+  for (auto& e : m->ev) TCD_CUDA_OK(cudaEventCreate(&e));
   TCD_CUDA_OK(cudaMalloc((void**)&m->st.weight, np * kMogModes * 4));
   TCD_CUDA_OK(cudaMalloc((void**)&m->st.var, np * kMogModes * 4));
   TCD_CUDA_OK(cudaMalloc((void**)&m->st.mean, np * kMogModes * 3 * 4));
@@ -109,6 +114,7 @@ void tcd_mog2_destroy(tcd_mog2* m) {
   void* ptrs[] = {m->st.weight, m->st.var, m->st.mean, m->st.nmodes, m->frame_dev, m->fg, m->clean,
                   m->rois_dev, m->counts_dev};
   for (void* p : ptrs) if (p) cudaFree(p);
+  for (auto& e : m->ev) if (e) cudaEventDestroy(e);
   cudaStreamDestroy(m->stream);
   delete m;
 }
@@ -143,6 +149,7 @@ tcd_status tcd_mog2_apply(tcd_mog2* m, const uint8_t* frame, int64_t row_stride,
   p.varMax = 75.0f; p.CT = 0.05f; p.tau = 0.5f;
   p.detect_shadows = m->detect_shadows;
   int left = repeats;
+  cudaEventRecord(m->ev[0], m->stream);
   while (left > 0) {
     const int n = left < kMogMaxRepeats ? left : kMogMaxRepeats;
     p.repeats = n;
@@ -155,9 +162,12 @@ tcd_status tcd_mog2_apply(tcd_mog2* m, const uint8_t* frame, int64_t row_stride,
     if (rc) return (tcd_status)rc;
     left -= n;
   }
+  cudaEventRecord(m->ev[1], m->stream);
   if (fg_mask_host)
     TCD_CUDA_OK(cudaMemcpyAsync(fg_mask_host, m->fg, (size_t)m->h * m->w, cudaMemcpyDeviceToHost, m->stream));
   TCD_CUDA_OK(cudaStreamSynchronize(m->stream));
+  float t = 0.f;
+  if (cudaEventElapsedTime(&t, m->ev[0], m->ev[1]) == cudaSuccess) m->last_ms[0] = t / (float)repeats;
   return TCD_OK;
 }
 
@@ -168,6 +178,7 @@ tcd_status tcd_mog2_roi_counts(tcd_mog2* m, int32_t shadow_thr, int32_t ksize, i
   TCD_REQUIRE(n_rois <= m->roi_cap, "mog2_roi_counts: %d ROIs exceed capacity %d", n_rois, m->roi_cap);
   const int np = m->h * m->w;
   int rc;
+  cudaEventRecord(m->ev[2], m->stream);
   if (ksize > 1) {
     BlurArgs a;
     memset(&a, 0, sizeof(a));
@@ -189,11 +200,23 @@ tcd_status tcd_mog2_roi_counts(tcd_mog2* m, int32_t shadow_thr, int32_t ksize, i
     TCD_CUDA_OK(cudaMemsetAsync(m->counts_dev, 0, sizeof(unsigned int) * n_rois, m->stream));
     rc = roi_count_launch(m->clean, m->w, m->h, m->rois_dev, n_rois, m->counts_dev, m->stream);
     if (rc) return (tcd_status)rc;
+    cudaEventRecord(m->ev[3], m->stream);
     TCD_CUDA_OK(cudaMemcpyAsync(counts_host, m->counts_dev, sizeof(int) * n_rois, cudaMemcpyDeviceToHost, m->stream));
   }
   if (clean_mask_host)
     TCD_CUDA_OK(cudaMemcpyAsync(clean_mask_host, m->clean, (size_t)np, cudaMemcpyDeviceToHost, m->stream));
   TCD_CUDA_OK(cudaStreamSynchronize(m->stream));
+  float t = 0.f;
+  if (n_rois > 0 && cudaEventElapsedTime(&t, m->ev[2], m->ev[3]) == cudaSuccess) m->last_ms[1] = t;
+  return TCD_OK;
+}
+
+/* device time (CUDA events on the handle's stream) of the kernels of the last call, ms:
+ * [0] one MOG2 apply, [1] mask clean-up (threshold + blur + threshold) + ROI counts        */
+tcd_status tcd_mog2_last_ms(const tcd_mog2* m, float out_ms[2]) {
+  TCD_REQUIRE(m && out_ms, "mog2_last_ms: null argument");
+  out_ms[0] = m->last_ms[0];
+  out_ms[1] = m->last_ms[1];
   return TCD_OK;
 }
 
@@ -213,6 +236,7 @@ tcd_status tcd_empty_filter_create(int32_t h, int32_t w, int32_t blur_size, int3
   }
   const size_t np = (size_t)h * w;
   TCD_CUDA_OK(cudaStreamCreateWithFlags(&f->stream, cudaStreamNonBlocking));
+  for (auto& e : f->ev) TCD_CUDA_OK(cudaEventCreate(&e));
   TCD_CUDA_OK(cudaMalloc((void**)&f->frame_dev, np * 3));
   TCD_CUDA_OK(cudaMalloc((void**)&f->prev, np));
   TCD_CUDA_OK(cudaMalloc((void**)&f->counter, sizeof(unsigned int)));
@@ -227,6 +251,7 @@ void tcd_empty_filter_destroy(tcd_empty_filter* f) {
   cudaFree(f->frame_dev);
   cudaFree(f->prev);
   cudaFree(f->counter);
+  for (auto& e : f->ev) if (e) cudaEventDestroy(e);
   cudaStreamDestroy(f->stream);
   delete f;
 }
@@ -258,8 +283,10 @@ tcd_status tcd_empty_filter_step(tcd_empty_filter* f, const uint8_t* frame, int6
   a.src_mode = channels == 3 ? 1 : 2; a.post_mode = 1; a.post_thr = threshold; a.first = f->have_prev ? 0 : 1;
   memcpy(a.k, f->k, sizeof(a.k));
   TCD_CUDA_OK(cudaMemsetAsync(f->counter, 0, sizeof(unsigned int), f->stream));
+  cudaEventRecord(f->ev[0], f->stream);
   int rc = blur_launch(src, a, nullptr, f->prev, f->counter, f->stream);
   if (rc) return (tcd_status)rc;
+  cudaEventRecord(f->ev[1], f->stream);
   unsigned int cnt = 0;
   TCD_CUDA_OK(cudaMemcpyAsync(&cnt, f->counter, sizeof(cnt), cudaMemcpyDeviceToHost, f->stream));
   if (gray_blur_host)
@@ -267,7 +294,11 @@ tcd_status tcd_empty_filter_step(tcd_empty_filter* f, const uint8_t* frame, int6
   TCD_CUDA_OK(cudaStreamSynchronize(f->stream));
   *changed_pixels_host = f->have_prev ? (int32_t)cnt : -1;
   f->have_prev = true;
+  float t = 0.f;
+  if (cudaEventElapsedTime(&t, f->ev[0], f->ev[1]) == cudaSuccess) f->last_ms = t;
   return TCD_OK;
 }
+
+float tcd_empty_filter_last_ms(const tcd_empty_filter* f) { return f ? f->last_ms : 0.f; }
 
 }  // extern "C"

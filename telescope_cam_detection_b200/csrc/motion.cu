@@ -9,6 +9,8 @@
 // this TU is compiled with -fmad=false so every fp32 intermediate rounds like the scalar code.
 #include "kernels.cuh"
 
+#include <string.h>
+
 #include <atomic>
 #include <float.h>
 
@@ -257,6 +259,165 @@ blur_kernel(const uint8_t* __restrict__ src, const BlurArgs a, uint8_t* __restri
   }
 }
 
+// ---- 21-tap specialisation (the size both filters use: motion_blur_size = 21, blur_size = 21).
+// Same arithmetic as blur_kernel, bit for bit (horizontal pass exact 8.8, vertical 16.16, +32768 >> 16),
+// restructured so the integer pipes do four / two taps per instruction:
+//   stage A  4 pixels per thread: aligned 32-bit loads (tile origin x0-12), gray or threshold -> bytes in smem
+//   stage B  8 outputs per thread (4 columns x 2 rows): six 32-bit smem words per row, byte-shifted with
+//            funnel shifts, 6 x dp4a per output; the two rows are stored as one (even,odd) u16 pair
+//   stage C  8 rows x 1 column per thread over the row pairs: 11 x dp2a per output
+constexpr int kB21TW = 128, kB21TH = 32, kB21R = 10;
+constexpr int kB21InH = kB21TH + 2 * kB21R;          // 52 rows = 26 pairs
+constexpr int kB21InWords = (kB21TW + 24) / 4;       // 38 words: pixels x0-12 .. x0+TW+11
+
+struct Blur21Taps {
+  unsigned int h4[6];     // taps 4m..4m+3 as bytes (tap 20 alone in h4[5])
+  unsigned int ve[11];    // even output row: (k[2m], k[2m+1]) in bytes 0,1
+  unsigned int vo[11];    // odd output row:  (k[2m-1], k[2m])
+};
+
+template <int O>
+__device__ __forceinline__ unsigned int b21_window(const unsigned int (&w)[8]) {
+  // four consecutive bytes starting at byte offset O of the little-endian word array
+  constexpr int i = O >> 2, sh = (O & 3) * 8;
+  if constexpr (sh == 0) return w[i];
+  else return __funnelshift_r(w[i], w[i + 1], sh);
+}
+template <int J>
+__device__ __forceinline__ unsigned int b21_hsum(const unsigned int (&w)[8], const Blur21Taps& t) {
+  unsigned int acc = 0;
+  acc = __dp4a(b21_window<2 + J + 0>(w), t.h4[0], acc);
+  acc = __dp4a(b21_window<2 + J + 4>(w), t.h4[1], acc);
+  acc = __dp4a(b21_window<2 + J + 8>(w), t.h4[2], acc);
+  acc = __dp4a(b21_window<2 + J + 12>(w), t.h4[3], acc);
+  acc = __dp4a(b21_window<2 + J + 16>(w), t.h4[4], acc);
+  acc = __dp4a(b21_window<2 + J + 20>(w), t.h4[5], acc);
+  return acc;
+}
+
+__global__ void __launch_bounds__(256)
+blur21_kernel(const uint8_t* __restrict__ src, const BlurArgs a, const Blur21Taps taps,
+              uint8_t* __restrict__ dst, uint8_t* __restrict__ prev, unsigned int* __restrict__ counter) {
+  __shared__ unsigned int s_in[kB21InH][kB21InWords + 2];   // +2: the last group's 7th/8th word reads
+  __shared__ unsigned int s_h[kB21InH / 2][kB21TW];         // (row 2r, row 2r+1) u16 pairs
+  const int x0 = blockIdx.x * kB21TW, y0 = blockIdx.y * kB21TH;
+  const bool aligned = (a.in_stride & 3) == 0 && (reinterpret_cast<uintptr_t>(src) & 3) == 0;
+
+  // ---- stage A
+  for (int i = threadIdx.x; i < kB21InH * (kB21InWords + 2); i += 256) {
+    const int ly = i / (kB21InWords + 2), g = i - ly * (kB21InWords + 2);
+    unsigned int out = 0;
+    if (g < kB21InWords) {
+      const int gy = reflect101(y0 + ly - kB21R, a.h);
+      const int gx0 = x0 - 12 + 4 * g;
+      const uint8_t* row = src + (long long)gy * a.in_stride;
+      if (gx0 >= 0 && gx0 + 4 <= a.w && aligned) {
+        if (a.src_mode == 1) {
+          const uint3 q = *reinterpret_cast<const uint3*>(row + (size_t)gx0 * 3);   // 12 bytes, 4-byte aligned
+          const unsigned int b[3] = {q.x, q.y, q.z};
+#pragma unroll
+          for (int px = 0; px < 4; ++px) {
+            const int o = px * 3;
+            const unsigned int c0 = (b[o >> 2] >> ((o & 3) * 8)) & 255u;
+            const unsigned int c1 = (b[(o + 1) >> 2] >> (((o + 1) & 3) * 8)) & 255u;
+            const unsigned int c2 = (b[(o + 2) >> 2] >> (((o + 2) & 3) * 8)) & 255u;
+            out |= ((c0 * 3735u + c1 * 19235u + c2 * 9798u + 16384u) >> 15) << (8 * px);
+          }
+        } else {
+          const unsigned int q = *reinterpret_cast<const unsigned int*>(row + gx0);
+          if (a.src_mode == 2) {
+            out = q;
+          } else {
+#pragma unroll
+            for (int px = 0; px < 4; ++px)
+              out |= (((q >> (8 * px)) & 255u) > (unsigned int)a.pre_thr ? 255u : 0u) << (8 * px);
+          }
+        }
+      } else {
+        for (int px = 0; px < 4; ++px) {
+          const int gx = reflect101(gx0 + px, a.w);
+          unsigned int val;
+          if (a.src_mode == 0) {
+            val = row[gx] > a.pre_thr ? 255u : 0u;
+          } else if (a.src_mode == 2) {
+            val = row[gx];
+          } else {
+            const uint8_t* p = row + (size_t)gx * 3;
+            val = ((unsigned int)p[0] * 3735u + (unsigned int)p[1] * 19235u + (unsigned int)p[2] * 9798u + 16384u) >> 15;
+          }
+          out |= val << (8 * px);
+        }
+      }
+    }
+    s_in[ly][g] = out;
+  }
+  __syncthreads();
+
+  // ---- stage B: task = (row pair, group of 4 columns)
+  for (int i = threadIdx.x; i < (kB21InH / 2) * (kB21TW / 4); i += 256) {
+    const int rp = i / (kB21TW / 4), g = i - rp * (kB21TW / 4);
+    unsigned int h[2][4];
+#pragma unroll
+    for (int r = 0; r < 2; ++r) {
+      unsigned int w[8];
+#pragma unroll
+      for (int m = 0; m < 8; ++m) w[m] = s_in[2 * rp + r][g + m];
+      h[r][0] = b21_hsum<0>(w, taps);
+      h[r][1] = b21_hsum<1>(w, taps);
+      h[r][2] = b21_hsum<2>(w, taps);
+      h[r][3] = b21_hsum<3>(w, taps);
+    }
+    uint4 o;
+    o.x = h[0][0] | (h[1][0] << 16);
+    o.y = h[0][1] | (h[1][1] << 16);
+    o.z = h[0][2] | (h[1][2] << 16);
+    o.w = h[0][3] | (h[1][3] << 16);
+    *reinterpret_cast<uint4*>(&s_h[rp][4 * g]) = o;
+  }
+  __syncthreads();
+
+  // ---- stage C: task = (block of 8 output rows, column)
+  unsigned int local = 0;
+  for (int i = threadIdx.x; i < (kB21TH / 8) * kB21TW; i += 256) {
+    const int rb = i / kB21TW, lx = i - rb * kB21TW;
+    const int gx = x0 + lx;
+    unsigned int p[14];
+#pragma unroll
+    for (int m = 0; m < 14; ++m) p[m] = s_h[4 * rb + m][lx];
+    if (gx >= a.w) continue;
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      unsigned int ae = 0, ao = 0;
+#pragma unroll
+      for (int m = 0; m < 11; ++m) {
+        ae = __dp2a_lo(p[q + m], taps.ve[m], ae);
+        ao = __dp2a_lo(p[q + m], taps.vo[m], ao);
+      }
+#pragma unroll
+      for (int par = 0; par < 2; ++par) {
+        const int gy = y0 + 8 * rb + 2 * q + par;
+        if (gy >= a.h) continue;
+        const int v = (int)(((par ? ao : ae) + 32768u) >> 16);
+        const size_t o = (size_t)gy * a.w + gx;
+        if (a.post_mode == 0) {
+          dst[o] = v > a.post_thr ? 255 : 0;
+        } else {
+          if (!a.first) {
+            const int d = abs(v - (int)prev[o]);
+            local += d > a.post_thr ? 1u : 0u;
+          }
+          prev[o] = (uint8_t)v;
+          if (dst) dst[o] = (uint8_t)v;
+        }
+      }
+    }
+  }
+  if (a.post_mode == 1 && !a.first) {
+    for (int off = 16; off > 0; off >>= 1) local += __shfl_xor_sync(0xffffffffu, local, off);
+    if ((threadIdx.x & 31) == 0 && local) atomicAdd(counter, local);
+  }
+}
+
 // no-blur variant of the mask clean-up: (m > pre_thr) only (motion_blur_size <= 0)
 __global__ void threshold_kernel(const uint8_t* __restrict__ src, int n, int thr,
                                  uint8_t* __restrict__ dst) {
@@ -299,6 +460,28 @@ int blur_launch(const uint8_t* src, const BlurArgs& a, uint8_t* dst, uint8_t* pr
     cudaFuncSetAttribute(blur_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                          (int)blur_smem(kBlurMaxK));
     attr_done = true;
+  }
+  bool small_taps = true;
+  for (int t = 0; t < a.ksize; ++t) small_taps = small_taps && a.k[t] <= 255;
+  if (a.ksize == 21 && small_taps) {
+    Blur21Taps tp;
+    memset(&tp, 0, sizeof(tp));
+    auto k = [&](int t) -> unsigned int { return (t >= 0 && t < 21) ? a.k[t] : 0u; };
+    for (int m = 0; m < 6; ++m)
+      tp.h4[m] = k(4 * m) | (k(4 * m + 1) << 8) | (k(4 * m + 2) << 16) | (k(4 * m + 3) << 24);
+    for (int m = 0; m < 11; ++m) {
+      tp.ve[m] = k(2 * m) | (k(2 * m + 1) << 8);
+      tp.vo[m] = k(2 * m - 1) | (k(2 * m) << 8);
+    }
+    dim3 g21(cdiv(a.w, kB21TW), cdiv(a.h, kB21TH));
+    blur21_kernel<<<g21, 256, 0, stream>>>(src, a, tp, dst, prev, counter);
+    g_launch_count.fetch_add(1, std::memory_order_relaxed);
+    cudaError_t e21 = cudaGetLastError();
+    if (e21 != cudaSuccess) {
+      set_last_error("blur21_kernel launch: %s", cudaGetErrorString(e21));
+      return TCD_ERR_CUDA;
+    }
+    return TCD_OK;
   }
   dim3 grid(cdiv(a.w, kBlurTW), cdiv(a.h, kBlurTH));
   blur_kernel<<<grid, kBlurThreads, blur_smem(a.ksize), stream>>>(src, a, dst, prev, counter);

@@ -267,6 +267,12 @@ class Mog2Engine:
                                       mask.ctypes.data_as(C.c_void_p) if want_mask else None), "tcd_mog2_apply")
         return mask
 
+    def last_ms(self):
+        """Device time (CUDA events) of the last call's kernels: (one MOG2 apply, clean-up + ROI counts), ms."""
+        t = (C.c_float * 2)()
+        check(self.lib.tcd_mog2_last_ms(self.handle, t), "tcd_mog2_last_ms")
+        return float(t[0]), float(t[1])
+
     def roi_counts(self, rois, shadow_thr=200, ksize=21, blur_thr=25, want_mask=False):
         """rois: int32 [n,4] (x1,y1,x2,y2) already clamped to the frame.  -> (counts[n], clean mask or None)"""
         rois = np.ascontiguousarray(rois, np.int32).reshape(-1, 4)
@@ -304,6 +310,9 @@ class EmptyGateEngine:
 
     def reset(self):
         check(self.lib.tcd_empty_filter_reset(self.handle), "tcd_empty_filter_reset")
+
+    def last_ms(self):
+        return float(self.lib.tcd_empty_filter_last_ms(self.handle))
 
     def step(self, frame, threshold=25, want_blur=False):
         """-> (changed pixel count, or -1 on the first frame; blurred gray plane or None)"""

@@ -1,5 +1,5 @@
 set -x
-timeout 900 python -m pytest tests/test_gpu_rtdetr.py -q > gpurun_out/s16l_pytest.log 2>&1; echo rc=$?
-tail -40 gpurun_out/s16l_pytest.log
-timeout 600 python tools/rtdetr_check.py 2 > gpurun_out/s16l_rtdetr.txt 2>&1
-grep -E "overlap|scores max" gpurun_out/s16l_rtdetr.txt
+T=s16p
+timeout 300 python -m pytest tests/test_gpu_motion.py tests/test_gpu_shims.py -x -q > gpurun_out/${T}_pytest.log 2>&1; echo "rc=$?"
+tail -4 gpurun_out/${T}_pytest.log
+python tools/aux_probe.py 2>&1 | tail -3
