@@ -303,18 +303,41 @@ blur21_kernel(const uint8_t* __restrict__ src, const BlurArgs a, const Blur21Tap
   const int x0 = blockIdx.x * kB21TW, y0 = blockIdx.y * kB21TH;
   const bool aligned = (a.in_stride & 3) == 0 && (reinterpret_cast<uintptr_t>(src) & 3) == 0;
 
-  // ---- stage A
-  for (int i = threadIdx.x; i < kB21InH * (kB21InWords + 2); i += 256) {
-    const int ly = i / (kB21InWords + 2), g = i - ly * (kB21InWords + 2);
-    unsigned int out = 0;
-    if (g < kB21InWords) {
-      const int gy = reflect101(y0 + ly - kB21R, a.h);
-      const int gx0 = x0 - 12 + 4 * g;
-      const uint8_t* row = src + (long long)gy * a.in_stride;
-      if (gx0 >= 0 && gx0 + 4 <= a.w && aligned) {
+  // ---- stage A (three groups per thread in flight: all loads are issued before the first use)
+  constexpr int kGroups = kB21InH * (kB21InWords + 2);
+  for (int base = 0; base < kGroups; base += 256 * 3) {
+    uint3 q[3];
+    int state[3];   // 0: padding word / past the end, 1: fast path loaded, 2: border (per-pixel reflect)
+#pragma unroll
+    for (int u = 0; u < 3; ++u) {
+      const int i = base + u * 256 + (int)threadIdx.x;
+      state[u] = 0;
+      q[u] = make_uint3(0u, 0u, 0u);
+      if (i < kGroups) {
+        const int ly = i / (kB21InWords + 2), g = i - ly * (kB21InWords + 2);
+        if (g < kB21InWords) {
+          const int gy = reflect101(y0 + ly - kB21R, a.h);
+          const int gx0 = x0 - 12 + 4 * g;
+          const uint8_t* row = src + (long long)gy * a.in_stride;
+          if (gx0 >= 0 && gx0 + 4 <= a.w && aligned) {
+            state[u] = 1;
+            if (a.src_mode == 1) q[u] = *reinterpret_cast<const uint3*>(row + (size_t)gx0 * 3);
+            else q[u].x = *reinterpret_cast<const unsigned int*>(row + gx0);
+          } else {
+            state[u] = 2;
+          }
+        }
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < 3; ++u) {
+      const int i = base + u * 256 + (int)threadIdx.x;
+      if (i >= kGroups) continue;
+      const int ly = i / (kB21InWords + 2), g = i - ly * (kB21InWords + 2);
+      unsigned int out = 0;
+      if (state[u] == 1) {
         if (a.src_mode == 1) {
-          const uint3 q = *reinterpret_cast<const uint3*>(row + (size_t)gx0 * 3);   // 12 bytes, 4-byte aligned
-          const unsigned int b[3] = {q.x, q.y, q.z};
+          const unsigned int b[3] = {q[u].x, q[u].y, q[u].z};
 #pragma unroll
           for (int px = 0; px < 4; ++px) {
             const int o = px * 3;
@@ -323,17 +346,16 @@ blur21_kernel(const uint8_t* __restrict__ src, const BlurArgs a, const Blur21Tap
             const unsigned int c2 = (b[(o + 2) >> 2] >> (((o + 2) & 3) * 8)) & 255u;
             out |= ((c0 * 3735u + c1 * 19235u + c2 * 9798u + 16384u) >> 15) << (8 * px);
           }
+        } else if (a.src_mode == 2) {
+          out = q[u].x;
         } else {
-          const unsigned int q = *reinterpret_cast<const unsigned int*>(row + gx0);
-          if (a.src_mode == 2) {
-            out = q;
-          } else {
-#pragma unroll
-            for (int px = 0; px < 4; ++px)
-              out |= (((q >> (8 * px)) & 255u) > (unsigned int)a.pre_thr ? 255u : 0u) << (8 * px);
-          }
+          // per byte: (p > pre_thr) ? 255 : 0
+          out = __vcmpgtu4(q[u].x, (unsigned int)a.pre_thr * 0x01010101u);
         }
-      } else {
+      } else if (state[u] == 2) {
+        const int gy = reflect101(y0 + ly - kB21R, a.h);
+        const int gx0 = x0 - 12 + 4 * g;
+        const uint8_t* row = src + (long long)gy * a.in_stride;
         for (int px = 0; px < 4; ++px) {
           const int gx = reflect101(gx0 + px, a.w);
           unsigned int val;
@@ -348,8 +370,8 @@ blur21_kernel(const uint8_t* __restrict__ src, const BlurArgs a, const Blur21Tap
           out |= val << (8 * px);
         }
       }
+      s_in[ly][g] = out;
     }
-    s_in[ly][g] = out;
   }
   __syncthreads();
 
@@ -385,6 +407,13 @@ blur21_kernel(const uint8_t* __restrict__ src, const BlurArgs a, const Blur21Tap
 #pragma unroll
     for (int m = 0; m < 14; ++m) p[m] = s_h[4 * rb + m][lx];
     if (gx >= a.w) continue;
+    int pv[8];
+    const bool want_prev = a.post_mode == 1 && !a.first;
+#pragma unroll
+    for (int r = 0; r < 8; ++r) {
+      const int gy = y0 + 8 * rb + r;
+      pv[r] = (want_prev && gy < a.h) ? (int)prev[(size_t)gy * a.w + gx] : 0;
+    }
 #pragma unroll
     for (int q = 0; q < 4; ++q) {
       unsigned int ae = 0, ao = 0;
@@ -403,7 +432,7 @@ blur21_kernel(const uint8_t* __restrict__ src, const BlurArgs a, const Blur21Tap
           dst[o] = v > a.post_thr ? 255 : 0;
         } else {
           if (!a.first) {
-            const int d = abs(v - (int)prev[o]);
+            const int d = abs(v - pv[2 * q + par]);
             local += d > a.post_thr ? 1u : 0u;
           }
           prev[o] = (uint8_t)v;
@@ -412,9 +441,14 @@ blur21_kernel(const uint8_t* __restrict__ src, const BlurArgs a, const Blur21Tap
       }
     }
   }
-  if (a.post_mode == 1 && !a.first) {
+  if (a.post_mode == 1 && !a.first) {   // one atomic per CTA
+    __shared__ unsigned int s_cnt;
+    if (threadIdx.x == 0) s_cnt = 0;
+    __syncthreads();
     for (int off = 16; off > 0; off >>= 1) local += __shfl_xor_sync(0xffffffffu, local, off);
-    if ((threadIdx.x & 31) == 0 && local) atomicAdd(counter, local);
+    if ((threadIdx.x & 31) == 0 && local) atomicAdd(&s_cnt, local);
+    __syncthreads();
+    if (threadIdx.x == 0 && s_cnt) atomicAdd(counter, s_cnt);
   }
 }
 
@@ -425,25 +459,35 @@ __global__ void threshold_kernel(const uint8_t* __restrict__ src, int n, int thr
   if (i < n) dst[i] = src[i] > thr ? 255 : 0;
 }
 
-// countNonZero inside each ROI; grid (n_rois, 16): each CTA takes a slice of the rows
+// countNonZero inside each ROI; grid (n_rois, 64): warps stride over the ROI rows, lanes over aligned
+// 32-bit words of a row (bytes outside [x1, x2) masked off), nonzero bytes counted with SIMD compares
 __global__ void __launch_bounds__(256)
 roi_count_kernel(const uint8_t* __restrict__ mask, int w, int h, const int* __restrict__ rois,
                  unsigned int* __restrict__ counts) {
   const int r = blockIdx.x;
   const int x1 = rois[r * 4 + 0], y1 = rois[r * 4 + 1], x2 = rois[r * 4 + 2], y2 = rois[r * 4 + 3];
-  const int rw = x2 - x1, rh = y2 - y1;
-  if (rw <= 0 || rh <= 0) return;
-  const int rows_per = (rh + gridDim.y - 1) / gridDim.y;
-  const int ya = y1 + blockIdx.y * rows_per;
-  const int yb = min(ya + rows_per, y2);
+  if (x2 <= x1 || y2 <= y1) return;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const bool aligned = (w & 3) == 0 && (reinterpret_cast<uintptr_t>(mask) & 3) == 0;
   unsigned int local = 0;
-  const int npx = (yb - ya) * rw;
-  for (int i = threadIdx.x; i < npx; i += 256) {
-    const int yy = i / rw, xx = i - yy * rw;
-    local += mask[(size_t)(ya + yy) * w + x1 + xx] != 0 ? 1u : 0u;
+  for (int y = y1 + blockIdx.y * 8 + warp; y < y2; y += gridDim.y * 8) {
+    const uint8_t* row = mask + (size_t)y * w;
+    if (aligned) {
+      const int xa = x1 & ~3;
+      for (int x = xa + 4 * lane; x < x2; x += 128) {
+        unsigned int q = *reinterpret_cast<const unsigned int*>(row + x);
+        unsigned int keep = 0xFFFFFFFFu;
+        if (x < x1) keep &= 0xFFFFFFFFu << (8 * (x1 - x));
+        if (x + 4 > x2) keep &= 0xFFFFFFFFu >> (8 * (x + 4 - x2));
+        q &= keep;
+        local += __popc(__vcmpne4(q, 0u) & 0x01010101u);
+      }
+    } else {
+      for (int x = x1 + lane; x < x2; x += 32) local += row[x] != 0 ? 1u : 0u;
+    }
   }
   for (int off = 16; off > 0; off >>= 1) local += __shfl_xor_sync(0xffffffffu, local, off);
-  if ((threadIdx.x & 31) == 0 && local) atomicAdd(counts + r, local);
+  if (lane == 0 && local) atomicAdd(counts + r, local);
 }
 
 // ------------------------------------------------------------------ host launchers
@@ -515,7 +559,7 @@ int threshold_launch(const uint8_t* src, int n, int thr, uint8_t* dst, cudaStrea
 int roi_count_launch(const uint8_t* mask, int w, int h, const int* rois_dev, int n,
                      unsigned int* counts_dev, cudaStream_t stream) {
   if (n <= 0) return TCD_OK;
-  roi_count_kernel<<<dim3(n, 16), 256, 0, stream>>>(mask, w, h, rois_dev, counts_dev);
+  roi_count_kernel<<<dim3(n, 64), 256, 0, stream>>>(mask, w, h, rois_dev, counts_dev);
   g_launch_count.fetch_add(1, std::memory_order_relaxed);
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) {
