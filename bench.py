@@ -332,10 +332,11 @@ def run_ours(args):
 
     # detections -> rank 0 for serving: side traffic on its own stream, double-buffered, never on the
     # compute path; one pinned staging copy + one NCCL gather per step
-    gather_dev = [torch.zeros((B, 300, 7), dtype=torch.float32, device="cuda") for _ in range(2)]
-    gather_pin = [torch.zeros((B, 300, 7), dtype=torch.float32, pin_memory=True) for _ in range(2)]
+    from telescope_cam_detection_b200 import stream_shard
+    gather_dev = [torch.zeros((B, 301, 7), dtype=torch.float32, device="cuda") for _ in range(2)]
+    gather_pin = [torch.zeros((B, 301, 7), dtype=torch.float32, pin_memory=True) for _ in range(2)]
     gather_done = [torch.cuda.Event() for _ in range(2)]
-    gathered = [torch.zeros_like(gather_dev[0]) for _ in range(world)] if (world > 1 and rank == 0) else None
+    gatherer = stream_shard.ResultGather(world, rank, gather_dev[0])
     side = torch.cuda.Stream(device=local)
     det_count = [0]
     gstep = [0]
@@ -346,13 +347,10 @@ def run_ours(args):
             i = gstep[0] & 1
             gstep[0] += 1
             gather_done[i].synchronize()
-            pin = gather_pin[i].numpy()
-            for b, r in enumerate(rows):
-                pin[b, : r.shape[0]] = r
-                pin[b, r.shape[0]:] = 0
+            stream_shard.pack_table(rows, 300, out=gather_pin[i].numpy())
             with torch.cuda.stream(side):
                 gather_dev[i].copy_(gather_pin[i], non_blocking=True)
-                dist.gather(gather_dev[i], gathered, dst=0)
+                gatherer.gather(gather_dev[i])
                 gather_done[i].record(side)
 
     def barrier():
@@ -375,10 +373,7 @@ def run_ours(args):
         barrier()
         wall = time.perf_counter() - t0
         ms = max(e0.elapsed_time(ev) for ev in ends)
-        if world > 1:
-            t = torch.tensor([ms], device="cuda")
-            dist.all_reduce(t, op=dist.ReduceOp.MAX)
-            ms = float(t.item())
+        ms = stream_shard.max_over_ranks(ms, world, device="cuda")
         return ms, lib.tcd_launch_count() - n0, wall
 
     # ---- device-resident frames (value)
@@ -391,8 +386,8 @@ def run_ours(args):
     _pipelined(eng, host_batches, max(3, args.warmup), None, n_slots)
     ms_e2e, _, wall_e2e = timed(host_batches, args.steps, on_result)
     clocks = sampler.stop() if sampler else None
-    fps_dev = world * B * args.steps / (ms_dev * 1e-3)
-    fps_e2e = world * B * args.steps / (ms_e2e * 1e-3)
+    fps_dev = stream_shard.aggregate_fps(B, args.steps, world, ms_dev)
+    fps_e2e = stream_shard.aggregate_fps(B, args.steps, world, ms_e2e)
 
     # ---- synchronous single-batch latency (p50), host frames
     lat = []
@@ -421,12 +416,15 @@ def run_ours(args):
     tpath = os.path.join(ROOT, "profiles", "traffic.json")
     if os.path.exists(tpath):
         with open(tpath) as f:
-            traffic = json.load(f).get("conv_umma_kernel_dram_bytes_per_step")
+            traffic_step = json.load(f).get("conv_umma_kernel_dram_bytes_per_step")
+        traffic = traffic_step / n_conv if traffic_step else None   # per launch, like `achieved`
     roofline = {"bound": "tensor", "kernel": "conv_umma_kernel (%d launches/step, tcgen05 implicit GEMM)" % n_conv,
                 "achieved": achieved, "peak": peaks["tf_burst"], "unit": "TFLOP/s", "frac": achieved / peaks["tf_burst"],
                 "peak_source": "%s bf16 burst (each conv launch timed alone: 8 back-to-back launches per CUDA-event pair)" % peaks["src"],
                 "flops_per_step": conv_fl, "kernel_ms_per_step": conv_ms, "share_of_step": conv_ms / all_ms,
-                "traffic": traffic}
+                "flops_per_launch": conv_fl / n_conv, "ms_per_launch": conv_ms / n_conv,
+                "traffic": traffic, "traffic_note": "ncu dram read+write per launch, mean over the step's conv launches "
+                "(cold-cache serialised capture, profiles/traffic.json)"}
     pre = prof[0]
     pre_bytes = B * (FRAME_H * FRAME_W * 3 + 640 * 640 * 4 * 2)
     if args.pre == "letterbox":  # only the source rows the 640x360 content taps are algorithmically needed

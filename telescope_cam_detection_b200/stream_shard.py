@@ -1,0 +1,89 @@
+"""Host side of the multi-GPU layout: camera streams are sharded across ranks, one
+process per GPU, no exchange on the compute path.  The reference is single-GPU
+(src/shared_inference_coordinator.py:18-338 serves every camera from one model); here each rank runs
+that coordinator over its own cameras and only the small result tables travel to rank 0 for serving.
+
+Backend-agnostic (`nccl` on the GPU box, `gloo` in the CPU tests): tensors live wherever the caller
+puts them.  Nothing here touches the detection kernels.
+"""
+import numpy as np
+
+ROW = 7  # x1, y1, x2, y2, obj_conf, class_conf, class_id  (yolox.utils.postprocess row)
+
+
+def assign_streams(camera_ids, world):
+    """Stable round-robin over the SORTED camera ids: {rank: [camera_id, ...]}.  Per-stream state (MOG2
+    model, empty-frame reference image) lives on the owning rank and never migrates."""
+    out = {r: [] for r in range(world)}
+    for i, cam in enumerate(sorted(camera_ids)):
+        out[i % world].append(cam)
+    return out
+
+
+def my_streams(camera_ids, rank, world):
+    return assign_streams(camera_ids, world)[rank]
+
+
+def owner_of(camera_id, camera_ids, world):
+    return sorted(camera_ids).index(camera_id) % world
+
+
+def pack_table(rows, max_out, out=None):
+    """List of B arrays [n_i, 7] -> fixed table [B, max_out + 1, 7] f32; slot [b, 0, 0] carries n_i (a count
+    row, so one tensor travels), rows beyond n_i are zero.  Raises if a frame has more than max_out rows
+    (the kernels cap at max_out, so that is a caller bug, not data)."""
+    B = len(rows)
+    if out is None:
+        out = np.zeros((B, max_out + 1, ROW), np.float32)
+    for b, r in enumerate(rows):
+        n = 0 if r is None else int(r.shape[0])
+        if n > max_out:
+            raise ValueError("frame %d has %d rows > max_out %d" % (b, n, max_out))
+        out[b, 0] = 0
+        out[b, 0, 0] = n
+        if n:
+            out[b, 1:1 + n] = r
+        out[b, 1 + n:] = 0
+    return out
+
+
+def unpack_table(table):
+    """Inverse of pack_table: -> list of B arrays [n_i, 7]."""
+    table = np.asarray(table)
+    return [table[b, 1:1 + int(table[b, 0, 0])].copy() for b in range(table.shape[0])]
+
+
+class ResultGather:
+    """Per-step gather of the packed result tables to rank 0.  `gather(t)` returns, on rank 0, the list of
+    every rank's table (rank order); None elsewhere.  With world == 1 it is a pass-through."""
+
+    def __init__(self, world, rank, like):
+        import torch
+
+        self.world, self.rank = world, rank
+        self.bufs = [torch.zeros_like(like) for _ in range(world)] if (world > 1 and rank == 0) else None
+
+    def gather(self, t):
+        if self.world == 1:
+            return [t]
+        import torch.distributed as dist
+
+        dist.gather(t, self.bufs, dst=0)
+        return self.bufs
+
+
+def max_over_ranks(value, world, device="cpu"):
+    """Device-timed milliseconds -> max over ranks (the job's step time is its slowest rank's)."""
+    if world == 1:
+        return float(value)
+    import torch
+    import torch.distributed as dist
+
+    t = torch.tensor([float(value)], dtype=torch.float64, device=device)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return float(t.item())
+
+
+def aggregate_fps(frames_per_rank_step, steps, world, ms):
+    """Whole-job frames/s: the frames ALL ranks processed / the slowest rank's device time."""
+    return world * frames_per_rank_step * steps / (ms * 1e-3)

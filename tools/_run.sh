@@ -1,5 +1,8 @@
 set -x
-T=s16r
-timeout 300 python -m pytest tests/test_gpu_motion.py tests/test_gpu_shims.py -x -q > gpurun_out/${T}_pytest.log 2>&1; echo "rc=$?"
-tail -4 gpurun_out/${T}_pytest.log
-python tools/aux_probe.py 2>&1 | tail -3
+T=r01
+B="python bench.py --steps 2 --warmup 1 --no-cpu-baseline --no-aux --profile-iters 1 --latency-iters 0"
+timeout 300 $B > gpurun_out/${T}_prof_cmd.json 2> gpurun_out/${T}_prof_cmd.err; echo rc=$?
+TCD_NO_GRAPH=1 timeout 600 ncu --metrics gpu__time_duration.sum,dram__bytes_read.sum,dram__bytes_write.sum,sm__pipe_tensor_cycles_active.avg.pct_of_peak_sustained_active --clock-control none -c 400 --csv --log-file gpurun_out/${T}b_launches_ncu.csv $B > gpurun_out/${T}_ncu1.log 2>&1; echo rc=$?
+TCD_NO_GRAPH=1 timeout 900 ncu --set full --import-source on --clock-control none -k regex:conv_umma -s 0 -c 3 -o gpurun_out/${T}b_conv_stem_dark2 $B > gpurun_out/${T}_ncu2.log 2>&1; echo rc=$?
+TCD_NO_GRAPH=1 timeout 900 ncu --set full --import-source on --clock-control none -k regex:conv_umma -s 56 -c 3 -o gpurun_out/${T}b_conv_head0 $B > gpurun_out/${T}_ncu3.log 2>&1; echo rc=$?
+ls -la gpurun_out/ | tail
