@@ -358,6 +358,8 @@ def run_ours(args):
             dist.barrier()
         torch.cuda.synchronize()
 
+    h2d_bytes = [0]
+
     def timed(batches, steps, cb):
         barrier()
         e0 = torch.cuda.Event(enable_timing=True)
@@ -366,6 +368,7 @@ def run_ours(args):
         for st in streams[1:]:
             st.wait_event(e0)
         n0 = lib.tcd_launch_count()
+        h0 = lib.tcd_h2d_byte_count()
         t0 = time.perf_counter()
         _pipelined(eng, batches, steps, cb, n_slots)
         for ev, st in zip(ends, streams):
@@ -374,6 +377,7 @@ def run_ours(args):
         wall = time.perf_counter() - t0
         ms = max(e0.elapsed_time(ev) for ev in ends)
         ms = stream_shard.max_over_ranks(ms, world, device="cuda")
+        h2d_bytes[0] = (lib.tcd_h2d_byte_count() - h0) // max(1, steps)
         return ms, lib.tcd_launch_count() - n0, wall
 
     # ---- device-resident frames (value)
@@ -476,7 +480,11 @@ def run_ours(args):
                    "l2": "inputs larger than L2: %d-frame pool (%.0f MB) cycled" % (POOL_FRAMES, POOL_FRAMES * 6.2208),
                    "pipeline": "%d slots in flight, CUDA graph per slot" % n_slots,
                    "env": {k: v for k, v in os.environ.items() if k.startswith("TCD_")}},
-        "e2e": {"value": fps_e2e, "unit": UNIT, "h2d_bytes_per_step": B * FRAME_H * FRAME_W * 3,
+        "e2e": {"value": fps_e2e, "unit": UNIT, "h2d_bytes_per_step": int(h2d_bytes[0]),
+                "h2d_note": "frame bytes counted by the library (tcd_h2d_byte_count); full frames are %d B/step -- at the "
+                            "exact 3:1 letterbox only every third source row has a non-zero bilinear weight and only those "
+                            "rows are uploaded (bit-identical result; TCD_SPARSE_UPLOAD=0 uploads everything)"
+                            % (B * FRAME_H * FRAME_W * 3),
                 "d2h_bytes_per_step": B * 300 * 7 * 4 + B * 4, "ms_per_step": ms_e2e / args.steps,
                 "wall_fps": world * B * args.steps / wall_e2e, "detections": det_count[0]},
         "latency_ms_p50_sync_batch": float(np.median(lat)) if lat else None, "phases_ms_sync_batch": phases,

@@ -32,6 +32,9 @@ const char* tcd_last_error(void);
 int tcd_version(void);
 /* number of kernels this library has launched in this process (bench.py gpu_launches) */
 uint64_t tcd_launch_count(void);
+/* bytes of camera frames this library has copied host->device in this process (bench.py e2e.h2d_bytes_per_step);
+ * detect/submit upload only the source rows the resize taps with non-zero weight (see tcd_detector_submit) */
+uint64_t tcd_h2d_byte_count(void);
 
 /* ------------------------------------------------------------------ preprocess (K1+K2)
  * Replaces YOLOXDetector.preprocess, src/yolox_detector.py:186-220 (HWC u8 -> float,

@@ -72,6 +72,7 @@ SIGNATURES = {
     "tcd_last_error": (C.c_char_p, []),
     "tcd_version": (C.c_int, []),
     "tcd_launch_count": (C.c_uint64, []),
+    "tcd_h2d_byte_count": (C.c_uint64, []),
     "tcd_preprocess": (C.c_int, [C.POINTER(PreprocCfg), _PP, _I32P, _I32P, _I64P, C.c_int32, C.c_int32, _P, _P]),
     "tcd_conv2d_nhwc_bf16": (C.c_int, [_P, C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_int32,
                                        _F32P, _F32P, C.c_int32, C.c_int32, C.c_int32, C.c_int32, _P,

@@ -11,6 +11,7 @@
 namespace tcd {
 
 std::atomic<uint64_t> g_launch_count{0};
+std::atomic<uint64_t> g_h2d_bytes{0};
 static thread_local char g_err[1024] = "";
 
 void set_last_error(const char* fmt, ...) {
@@ -47,6 +48,7 @@ extern "C" {
 const char* tcd_last_error(void) { return g_err; }
 int tcd_version(void) { return 100; }
 uint64_t tcd_launch_count(void) { return g_launch_count.load(); }
+uint64_t tcd_h2d_byte_count(void) { return g_h2d_bytes.load(); }
 
 tcd_status tcd_malloc_device(size_t bytes, void** out) {
   TCD_CUDA_OK(cudaMalloc(out, bytes));

@@ -4,6 +4,7 @@
 // short low-occupancy layers of one batch share the chip with another batch's.
 #include <atomic>
 #include <map>
+#include <stdlib.h>
 #include <string.h>
 #include <vector>
 
@@ -14,6 +15,7 @@ using namespace tcd;
 
 namespace tcd {
 extern std::atomic<uint64_t> g_launch_count;
+extern std::atomic<uint64_t> g_h2d_bytes;
 }
 
 namespace {
@@ -163,6 +165,11 @@ static int run_net_post(tcd_detector* d, Slot& s, YoloxPlan* p, int B, bool want
   return postproc_launch(post_for(s, p, B, p->pred_raw, want_decoded), 1, s.stream);
 }
 
+static const bool g_sparse_upload = [] {
+  const char* e = getenv("TCD_SPARSE_UPLOAD");
+  return !(e && e[0] == '0');
+}();
+
 static int enqueue_input(tcd_detector* d, Slot& s, YoloxPlan* p, const uint8_t* const* frames,
                          const int32_t* h, const int32_t* w, const int64_t* row_stride, int B,
                          int on_device, bool launch_pre = true) {
@@ -178,11 +185,29 @@ static int enqueue_input(tcd_detector* d, Slot& s, YoloxPlan* p, const uint8_t* 
       TCD_REQUIRE((size_t)h[b] * tight <= s.frame_cap, "frame %d (%dx%d) exceeds max_src %dx%d", b, h[b],
                   w[b], d->cfg.max_src_h, d->cfg.max_src_w);
       uint8_t* dst = s.staging + (size_t)b * s.frame_cap;
-      if ((size_t)st == tight) {
+      // Row-sparse upload.  When the vertical resize ratio is an odd integer k (1080p -> 640 letterbox:
+      // k = 3 exactly), the bilinear tap of output row d is s = k*(d+0.5)-0.5 = k*d + (k-1)/2, an integer:
+      // the second tap's weight is exactly 0, so only every k-th source row contributes to the result and
+      // only those rows cross PCIe (one pitched copy).  The other staging rows keep whatever finite bytes
+      // they held and are multiplied by 0.0f; the output is bit-identical to a full upload
+      // (tests/test_gpu_yolox.py::test_row_sparse_upload_is_exact).
+      PreFrame probe;
+      preproc_describe(&pc, ptr, h[b], w[b], st, &probe);
+      const int k = (int)probe.scale_y;
+      const bool sparse = g_sparse_upload && (float)k == probe.scale_y && k >= 3 && (k & 1) &&
+                          (long long)k * probe.content_h <= (long long)h[b];
+      if (sparse) {
+        const size_t r0 = (size_t)(k - 1) / 2;
+        TCD_CUDA_OK(cudaMemcpy2DAsync(dst + r0 * tight, (size_t)k * tight, ptr + r0 * (size_t)st, (size_t)k * (size_t)st,
+                                      tight, (size_t)probe.content_h, cudaMemcpyHostToDevice, s.stream));
+        g_h2d_bytes.fetch_add((uint64_t)probe.content_h * tight, std::memory_order_relaxed);
+      } else if ((size_t)st == tight) {
         TCD_CUDA_OK(cudaMemcpyAsync(dst, ptr, (size_t)h[b] * tight, cudaMemcpyHostToDevice, s.stream));
+        g_h2d_bytes.fetch_add((uint64_t)h[b] * tight, std::memory_order_relaxed);
       } else {
         TCD_CUDA_OK(cudaMemcpy2DAsync(dst, tight, ptr, (size_t)st, tight, (size_t)h[b],
                                       cudaMemcpyHostToDevice, s.stream));
+        g_h2d_bytes.fetch_add((uint64_t)h[b] * tight, std::memory_order_relaxed);
       }
       ptr = dst;
       dst_stride = (int64_t)tight;

@@ -30,7 +30,8 @@
 namespace tcd {
 
 constexpr int kConvMaxStages = 8;
-constexpr int kConvThreads = 192;
+constexpr int kConvThreads = 192;   // warp 0 TMA producer, warp 1 MMA issuer, warps 2..5 epilogue
+constexpr int kConvEpiWarps = 4;
 constexpr int kConvMaxAStages = 4;
 constexpr int kConvMaxBias = 512;
 
@@ -55,7 +56,7 @@ struct ConvArgs {
   // TMA and UMMA alike, so a view may start at any 128-byte row with base-offset 0 -- measured: the
   // parity tests pass with 0 and fail with (start >> 7) & 7); the operand ring then carries weights only
   int halo, a_stages, a_stage_bytes, a_ring_off, halo_w;
-  int dbg;                      // measurement only (TCD_CONV_DBG): 1 = no operand loads, 2 = no MMAs
+  int dbg;                      // measurement only (TCD_CONV_DBG): 1 no operand loads, 2 no MMAs, 4 no SiLU, 8 no tcgen05.ld, 16 no staging stores
   int tps;                      // filter taps per weight stage (halo mode: 1, 3 or 9; else 1)
   int bias_n;                   // entries of bias staged in shared memory (0: read from global)
   const float* bias;
@@ -101,7 +102,7 @@ __device__ __forceinline__ void conv_trace(const ConvArgs& p, int k, bool wall =
 }
 
 // per-tile stamps of CTA 0 (first 16 tiles): 32+j producer starts tile j, 48+j MMA commits tile j,
-// 64+j epilogue sees accumulator j, 80+j epilogue issued the store of tile j
+// 64+j epilogue sees accumulator j, 96+j staging free, 112+j all slabs staged, 80+j store of tile j issued
 __device__ __forceinline__ void conv_trace_tile(const ConvArgs& p, int base, int j) {
   if (p.trace == nullptr || blockIdx.x != 0 || j >= 16) return;
   p.trace[base + j] = (unsigned long long)clock64();
@@ -161,7 +162,7 @@ __device__ __forceinline__ void conv_add_resid(const ConvArgs& p, float (&v)[NC]
 }
 
 template <int NC>
-__device__ __forceinline__ void conv_finish_cols(const ConvArgs& p, const uint32_t (&r)[NC], int c0,
+__device__ __forceinline__ void conv_finish_cols(const ConvArgs& p, const uint32_t (&r)[32], int c0,
                                                  const float* bias_g, int row, bool valid,
                                                  const ConvTile& t, int y, int x, uint8_t* stage_base) {
   float v[NC];
@@ -175,7 +176,7 @@ __device__ __forceinline__ void conv_finish_cols(const ConvArgs& p, const uint32
     v[4 * j + 3] = __uint_as_float(r[4 * j + 3]) + b.w;
   }
   if (p.mode == 0 && p.resid != nullptr && p.resid_pre && valid) conv_add_resid<NC>(p, v, c0, t, y, x);
-  if (p.silu == 1) {
+  if (p.silu == 1 && !(p.dbg & 4)) {
 #pragma unroll
     for (int j = 0; j < NC; ++j) v[j] = silu_f(v[j]);
   } else if (p.silu == 2) {
@@ -199,7 +200,7 @@ __device__ __forceinline__ void conv_finish_cols(const ConvArgs& p, const uint32
       q.y = pack_bf16x2(v[u * 8 + 2], v[u * 8 + 3]);
       q.z = pack_bf16x2(v[u * 8 + 4], v[u * 8 + 5]);
       q.w = pack_bf16x2(v[u * 8 + 6], v[u * 8 + 7]);
-      *reinterpret_cast<uint4*>(rowp + (((u0 + u) ^ sw) << 4)) = q;
+      if (!(p.dbg & 16)) *reinterpret_cast<uint4*>(rowp + (((u0 + u) ^ sw) << 4)) = q;
     }
   } else {
     // f32 prediction rows: park the slab in this warp's private staging rows (stride BN+1 words,
@@ -210,23 +211,37 @@ __device__ __forceinline__ void conv_finish_cols(const ConvArgs& p, const uint32
   }
 }
 
-// mode 1: each epilogue warp streams its 32 staged rows to out_f32, one row (n_valid consecutive
-// floats) per step with the lanes across columns.
-__device__ __forceinline__ void conv_flush_rows(const ConvArgs& p, const ConvTile& t, int q, int lane,
-                                                const uint8_t* stage_base) {
-  __syncwarp();
-  const float* st = reinterpret_cast<const float*>(stage_base);
-  for (int r = 0; r < 32; ++r) {
-    const int row = q * 32 + r;
-    const int ly = row / p.TW;
-    const int y = t.y0 + ly, x = t.x0 + (row - ly * p.TW);
-    if (row >= p.TW * p.TH || y >= p.Ho || x >= p.Wo) continue;
-    float* op = p.out_f32 +
-                ((size_t)t.n_img * p.rows_per_img + p.row_off + (size_t)y * p.Wo + x) * p.out_ld + p.out_col;
-    const float* sr = st + (size_t)row * (p.BN + 1);
-    for (int c = lane; c < p.n_valid; c += 32) op[c] = sr[c];
+// mode 1: each epilogue warp streams its 32 staged rows to out_f32.  The 32 x n_valid block is walked
+// flat (element e = it*32 + lane -> row e / n_valid, column e % n_valid, kept incrementally), so every
+// iteration is an independent shuffle + ld.shared + st.global and consecutive lanes write consecutive
+// floats of a row.  (The first version walked row by row with a divide and a dependent generic load per
+// row: 440 cycles per row, 7 us per tile -- profiles/r01_conv_timeline.md.)
+__device__ __forceinline__ void conv_flush_rows(const ConvArgs& p, const ConvTile& t, int q, int half, int lane,
+                                                const uint8_t* stage_base, bool valid, int y, int x) {
+  const int nv = p.n_valid;
+  // element offset of the row this lane produced (lane L owns staged row q*32 + L); < 0: outside the image
+  const long long my_off =
+      valid ? ((long long)t.n_img * p.rows_per_img + p.row_off + (long long)y * p.Wo + x) * p.out_ld + p.out_col
+            : -1;
+  const uint32_t st = smem_u32(stage_base) + (uint32_t)(q * 32) * (uint32_t)(p.BN + 1) * 4u;
+  // the warps of a quadrant interleave: warp `half` takes elements half*32 + lane + step*it
+  constexpr int step = 32 * (kConvEpiWarps / 4);
+  const int dr = step / nv, dc = step - dr * nv;
+  const int e0 = half * 32 + lane;
+  int r = e0 / nv, c = e0 - r * nv;
+  const int n_it = (32 * nv - half * 32 + step - 1) / step;
+#pragma unroll 4
+  for (int it = 0; it < n_it; ++it) {
+    const bool in = r < 32;
+    const long long off = __shfl_sync(0xffffffffu, my_off, r & 31);
+    if (in && off >= 0) p.out_f32[off + c] = lds_f32(st + (uint32_t)(r * (p.BN + 1) + c) * 4u);
+    r += dr;
+    c += dc;
+    if (c >= nv) {
+      c -= nv;
+      ++r;
+    }
   }
-  __syncwarp();
 }
 
 __global__ void __launch_bounds__(kConvThreads)
@@ -261,7 +276,7 @@ conv_umma_kernel(const __grid_constant__ ConvMaps maps, const __grid_constant__ 
     }
     for (int a = 0; a < 2; ++a) {
       mbar_init(&tmem_full_bar[a], 1);
-      mbar_init(&tmem_empty_bar[a], 4);  // one arrive per epilogue warp
+      mbar_init(&tmem_empty_bar[a], kConvEpiWarps);  // one arrive per epilogue warp
     }
     for (int a = 0; a < p.a_stages; ++a) {
       mbar_init(&a_full_bar[a], 1);
@@ -272,7 +287,7 @@ conv_umma_kernel(const __grid_constant__ ConvMaps maps, const __grid_constant__ 
   if (warp == 1) tmem_alloc(&tmem_base_s, (uint32_t)p.tmem_cols);
   // the bias never depends on the previous layer: stage it while the pipeline spins up
   if (warp >= 2)
-    for (int i = threadIdx.x - 64; i < p.bias_n; i += 128) s_bias[i] = __ldg(p.bias + i);
+    for (int i = threadIdx.x - 64; i < p.bias_n; i += 32 * kConvEpiWarps) s_bias[i] = __ldg(p.bias + i);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -418,14 +433,21 @@ conv_umma_kernel(const __grid_constant__ ConvMaps maps, const __grid_constant__ 
       conv_trace(p, 6);
     }
   } else {
-    // ------------------------------------------------------------------ epilogue (4 warps)
+    // ------------------------------------------------------------------ epilogue (kConvEpiWarps warps)
+    // A warp may only read the TMEM lane quadrant (warp % 4).  With 8 warps, two share a quadrant and take
+    // alternate 32-column slabs; measured, that bought nothing (tail 256 -> 231 us per step, and it costs
+    // the registers that let three layers be co-resident): a tile's epilogue is a ~3000-cycle chain of
+    // barrier / fence / TMA-issue latencies even with the TMEM loads, SiLU and staging stores removed
+    // (TCD_CONV_DBG=28, profiles/r01_conv_timeline.md), so it is hidden by co-resident CTAs instead.
     const int q = warp & 3;
+    const int half = (warp - 2) >> 2;
     const int row = q * 32 + lane;
     const int ly = row / p.TW;
     const int lx = row - ly * p.TW;
     uint8_t* staging = smem + p.staging_off;
     if (p.pdl && p.resid != nullptr) pdl_wait();
     const float* bias_src = p.bias_n ? s_bias : p.bias;
+    const int nslab = (p.BN + 31) >> 5;
     int j = 0;
     for (int t = blockIdx.x; t < p.total_tiles; t += gridDim.x, ++j) {
       const ConvTile c = conv_tile(p, t);
@@ -438,37 +460,57 @@ conv_umma_kernel(const __grid_constant__ ConvMaps maps, const __grid_constant__ 
       tc_fence_after();
       if (j == 0 && warp == 2 && lane == 0) conv_trace(p, 7);
       if (warp == 2 && lane == 0) conv_trace_tile(p, 64, j);
-      if (p.mode == 0 && j > 0) {
-        // the previous tile's TMA store must have finished READING the staging area
-        if (warp == 2 && lane == 0) tma_store_wait_read();
-        asm volatile("bar.sync 1, 128;" ::: "memory");
+      if (j > 0) {
+        // staging reuse: the previous tile's TMA store has finished READING it (mode 0) / every warp has
+        // finished flushing its rows (mode 1)
+        if (p.mode == 0 && warp == 2 && lane == 0) tma_store_wait_read();
+        asm volatile("bar.sync 1, %0;" ::"n"(32 * kConvEpiWarps) : "memory");
       }
+      if (warp == 2 && lane == 0) conv_trace_tile(p, 96, j);   // staging is free
       const uint32_t taddr = tmem_base + (uint32_t)(acc * p.acc_stride) + ((uint32_t)(q * 32) << 16);
-      int c0 = 0;
-      for (; c0 + 32 <= p.BN; c0 += 32) {
-        uint32_t r[32];
-        conv_load_cols<32>(taddr + c0, r);
-        tmem_ld_wait();
-        if (c0 + 32 >= p.BN) {  // last slab read: hand the accumulator back to the MMA warp
-          tc_fence_before();
-          __syncwarp();
-          if (lane == 0) mbar_arrive(&tmem_empty_bar[acc]);
-        }
-        conv_finish_cols<32>(p, r, c0, bias_src, row, valid, c, y, x, staging);
-      }
-      if (c0 < p.BN) {
-        uint32_t r[16];
-        conv_load_cols<16>(taddr + c0, r);
-        tmem_ld_wait();
+      // slabs of 32 accumulator columns (a ragged last one of 16), double-buffered in registers: the
+      // tcgen05.ld of slab s+1 is in flight while slab s goes through bias / activation / staging
+      // (167 registers: two CTAs of 192 threads per SM, which is what TCD_CONV_SHARE=2 plans for)
+      uint32_t ra[32], rb[32];
+      auto issue = [&](int sl, uint32_t (&r)[32]) {
+        if (p.dbg & 8) return;
+        if (p.BN - 32 * sl >= 32) tmem_ld32(taddr + 32 * sl, r); else tmem_ld16_lo(taddr + 32 * sl, r);
+      };
+      auto handback = [&]() {  // every column has been read: the accumulator goes back to the MMA warp
         tc_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive(&tmem_empty_bar[acc]);
-        conv_finish_cols<16>(p, r, c0, bias_src, row, valid, c, y, x, staging);
+      };
+      auto finish = [&](const uint32_t (&r)[32], int sl) {
+        if (p.BN - 32 * sl >= 32) conv_finish_cols<32>(p, r, 32 * sl, bias_src, row, valid, c, y, x, staging);
+        else conv_finish_cols<16>(p, r, 32 * sl, bias_src, row, valid, c, y, x, staging);
+      };
+      if (p.dbg & 8) {
+#pragma unroll
+        for (int u = 0; u < 32; ++u) ra[u] = rb[u] = 0;
       }
-      if (p.mode == 1) conv_flush_rows(p, c, q, lane, staging);
-      if (p.mode == 0) {
+      issue(0, ra);
+      for (int sl = 0; sl < nslab; sl += 2) {
+        tmem_ld_wait();
+        if (j == 0 && sl == 0 && warp == 2 && lane == 0) conv_trace(p, 12);   // first slab in registers
+        if (sl + 1 < nslab) issue(sl + 1, rb); else handback();
+        finish(ra, sl);
+        if (j == 0 && sl == 0 && warp == 2 && lane == 0) conv_trace(p, 13);   // first slab staged
+        if (sl + 1 < nslab) {
+          tmem_ld_wait();
+          if (sl + 2 < nslab) issue(sl + 2, ra); else handback();
+          finish(rb, sl + 1);
+        }
+      }
+      if (p.mode == 1) {
+        asm volatile("bar.sync 1, %0;" ::"n"(32 * kConvEpiWarps) : "memory");
+        conv_flush_rows(p, c, q, half, lane, staging, valid, y, x);
+      } else {
+        if (j == 0 && warp == 2 && lane == 0) conv_trace(p, 14);              // all slabs of warp 2 staged
         fence_proxy_async_smem();
-        asm volatile("bar.sync 1, 128;" ::: "memory");
+        if (j == 0 && warp == 2 && lane == 0) conv_trace(p, 15);              // proxy fence done
+        asm volatile("bar.sync 1, %0;" ::"n"(32 * kConvEpiWarps) : "memory");
+        if (warp == 2 && lane == 0) conv_trace_tile(p, 112, j);  // every warp has staged its slabs
         if (warp == 2 && lane == 0) {
           const int nchunks = p.BN / p.out_chunk;
           for (int ch = 0; ch < nchunks; ++ch)
@@ -507,6 +549,7 @@ struct ConvDesc {
   // level inside a [B, sum(HW), C] token tensor (RT-DETR memory).
   long long x_nstride = 0, y_nstride = 0, r_nstride = 0;
   int resid_pre = 0;  // residual added before (1) or after (0) the activation
+  int share = -1;     // plan for 1/share of an SM (co-residency with other streams' layers); -1 = TCD_CONV_SHARE
   // bf16 output (mode 0)
   void* y = nullptr;
   int y_ctot = 0, y_coff = 0;

@@ -2,6 +2,7 @@
 // tfm_kernels.cuh + the two YOLOX aux kernels) over device buffers it owns, replayed as ONE CUDA
 // graph.  The host side describes RT-DETRv2 as such a list (rtdetr_engine.py); this file owns
 // weights upload, plan construction, graph capture, replay and per-op profiling.
+#include <stdlib.h>
 #include <string.h>
 #include <string>
 #include <vector>
@@ -165,6 +166,11 @@ tcd_status tcd_program_add_conv(tcd_program* p, const tcd_conv_desc* c) {
   d.y = c->y; d.y_ctot = c->y_ctot; d.y_coff = c->y_coff; d.y_nstride = c->y_nstride;
   d.resid = c->resid; d.r_ctot = c->r_ctot; d.r_coff = c->r_coff; d.r_nstride = c->r_nstride;
   d.resid_pre = c->resid_pre;
+  // a program runs on ONE stream: nothing to be co-resident with, so each layer takes whole SMs
+  {
+    const char* e = getenv("TCD_PROGRAM_SHARE");
+    d.share = e ? atoi(e) : 0;
+  }
   d.out_f32 = c->out_f32; d.out_ld = c->out_ld; d.out_col = c->out_col; d.rows_per_img = c->rows_per_img;
   d.row_off = c->row_off;
   ProgOp op;

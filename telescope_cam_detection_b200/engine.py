@@ -150,13 +150,15 @@ class DetectorEngine:
             if b[1] == 0:
                 continue
             out[tag] = {n: int(b[2 + i]) - int(b[1]) if b[2 + i] else None for i, n in enumerate(names)}
+            for i, n in enumerate(("epi_slab0_loaded", "epi_slab0_staged", "epi_slabs_done", "epi_fence_done")):
+                out[tag][n] = int(b[12 + i]) - int(b[1]) if b[12 + i] else None
             out[tag]["wall_ns"] = int(b[11]) - int(b[0])
             out[tag]["start_ns"] = int(b[0])
         t0 = v[1]
         for base, tag in ((32, "tile_prod"), (48, "tile_mma"), (64, "tile_acc"), (80, "tile_store")):
             out[tag] = [int(x) - int(t0) for x in v[base:base + 16] if x]
-        out["prod_it"] = [int(x) - int(t0) if x else None for x in v[96:112]]
-        out["mma_it"] = [int(x) - int(t0) if x else None for x in v[112:128]]
+        out["tile_stage_free"] = [int(x) - int(t0) for x in v[96:112] if x]
+        out["tile_staged"] = [int(x) - int(t0) for x in v[112:128] if x]
         if "cta0" in out and "ctaN" in out:
             out["ctaN_start_after_cta0_ns"] = out["ctaN"]["start_ns"] - out["cta0"]["start_ns"]
         return out

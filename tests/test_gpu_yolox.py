@@ -149,3 +149,34 @@ def test_detect_batch_end_to_end(det):
         assert matched >= 0.95 * len(strong), "frame %d: %d/%d strong oracle detections matched (got %d rows)" % (
             b, matched, len(strong), len(g))
         assert np.all(np.diff(g[:, 4] * g[:, 5]) <= 1e-7), "rows not score-descending"
+
+
+def test_row_sparse_upload_is_exact():
+    """Letterbox 1080p -> 640 is an exact 3:1 decimation: the host-frame path uploads only every third source
+    row (tcd_h2d_byte_count), and must give bit-identical rows to the device-frame path that sees whole
+    frames -- whatever the staging area held before (here: a different frame, then noise)."""
+    from telescope_cam_detection_b200 import _lib
+    from telescope_cam_detection_b200.engine import DetectorEngine
+
+    lib = _lib.load()
+    e = DetectorEngine(oracle_blob(0), input_size=(640, 640), max_batch=2, max_out=8448, pre_mode=1)
+    try:
+        for seed, dirty in ((41, structured_frame(40)), (42, noise_frame(43))):
+            e.detect_batch([dirty, dirty])                       # leaves other bytes in the unsent rows
+            frames = [structured_frame(seed), noise_frame(seed + 100)]
+            n0 = lib.tcd_h2d_byte_count()
+            rows = e.detect_batch(frames)
+            sent = lib.tcd_h2d_byte_count() - n0
+            assert sent == 2 * 360 * 1920 * 3, sent              # 1 of every 3 rows
+            rows_dev = e.detect_batch(_dev_frames(frames))
+            for b in range(2):
+                assert rows[b].shape[0] > 0
+                assert np.array_equal(rows[b], rows_dev[b])
+        # a ratio that is not an odd integer uploads whole frames
+        f720 = [structured_frame(7, 720, 1280)] * 2
+        n0 = lib.tcd_h2d_byte_count()
+        r720 = e.detect_batch(f720)
+        assert lib.tcd_h2d_byte_count() - n0 == 2 * 720 * 1280 * 3
+        assert np.array_equal(r720[0], e.detect_batch(_dev_frames(f720))[0])
+    finally:
+        e.close()

@@ -1,8 +1,7 @@
 set -x
-T=r01
-B="python bench.py --steps 2 --warmup 1 --no-cpu-baseline --no-aux --profile-iters 1 --latency-iters 0"
-timeout 300 $B > gpurun_out/${T}_prof_cmd.json 2> gpurun_out/${T}_prof_cmd.err; echo rc=$?
-TCD_NO_GRAPH=1 timeout 600 ncu --metrics gpu__time_duration.sum,dram__bytes_read.sum,dram__bytes_write.sum,sm__pipe_tensor_cycles_active.avg.pct_of_peak_sustained_active --clock-control none -c 400 --csv --log-file gpurun_out/${T}b_launches_ncu.csv $B > gpurun_out/${T}_ncu1.log 2>&1; echo rc=$?
-TCD_NO_GRAPH=1 timeout 900 ncu --set full --import-source on --clock-control none -k regex:conv_umma -s 0 -c 3 -o gpurun_out/${T}b_conv_stem_dark2 $B > gpurun_out/${T}_ncu2.log 2>&1; echo rc=$?
-TCD_NO_GRAPH=1 timeout 900 ncu --set full --import-source on --clock-control none -k regex:conv_umma -s 56 -c 3 -o gpurun_out/${T}b_conv_head0 $B > gpurun_out/${T}_ncu3.log 2>&1; echo rc=$?
-ls -la gpurun_out/ | tail
+T=s17f
+B="python bench.py --steps 200 --warmup 10 --no-cpu-baseline --no-aux --rtdetr-batch 0 --latency-iters 0"
+for S in 0 2; do
+TCD_CONV_SHARE=$S timeout 300 $B --trace gpurun_out/${T}_trace_share$S.json > gpurun_out/${T}_bench_share$S.json 2> gpurun_out/${T}_bench_share$S.err; echo rc=$?
+done
+tail -c 400 gpurun_out/${T}_bench*.err
