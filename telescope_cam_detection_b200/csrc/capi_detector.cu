@@ -483,6 +483,10 @@ tcd_status tcd_detector_profile(tcd_detector* det, const uint8_t* const* frames,
       cudaEventRecord(ev[2 * (i + 1) + 1], s.stream);
     }
     if (rc) break;
+    // layers with an in-place residual have accumulated kProfileReps times: one clean pass so that decode / NMS
+    // are timed on the real prediction, not on an inflated candidate set
+    rc = p->run(s.stream);
+    if (rc) break;
     const int base = 1 + (int)p->ops.size();
     rc = postproc_launch(post_for(s, p, B, p->pred_raw, false), 1, s.stream, &ev[2 * (size_t)base]);
     if (rc) break;

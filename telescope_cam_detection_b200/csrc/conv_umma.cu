@@ -228,8 +228,16 @@ int conv_plan_build(const ConvDesc& d, ConvPlan* plan) {
   a.row_off = d.row_off;
   a.pdl = g_use_pdl ? 1 : 0;
   a.dbg = env_int("TCD_CONV_DBG", 0);
+  // accumulator rounds: narrow tiles (BN 32 / 64, one N tile) are grouped so that a round holds up to 128
+  // columns -- the per-round epilogue chain costs ~2 000 cycles whatever the tile holds
+  a.group = 1;
+  if (mode == 0 && a.n_tiles_n == 1 && BN <= 64 && BN % 32 == 0 && env_int("TCD_CONV_GROUP", 1, 0)) {
+    const long ctas_est = (long)n_sm * ((share || a.total_tiles < 2 * n_sm) ? 1 : 2);
+    const long tiles_per_cta_est = cdiv(a.total_tiles, ctas_est);
+    while (a.group * 2 * BN <= 128 && a.group * 2 <= tiles_per_cta_est) a.group *= 2;
+  }
   int tc = 32;
-  while (tc < BN) tc <<= 1;
+  while (tc < BN * a.group) tc <<= 1;
   a.acc_stride = tc;        // two accumulators, tc columns apart
   a.tmem_cols = 2 * tc;
   // taps
@@ -256,7 +264,7 @@ int conv_plan_build(const ConvDesc& d, ConvPlan* plan) {
   if (a.halo) a.tps = 9 * b_bytes <= 32768 ? 9 : (3 * b_bytes <= 32768 ? 3 : 1);
   const int stage_bytes = a_bytes + b_bytes * a.tps;
   TCD_REQUIRE(stage_bytes % 1024 == 0, "conv: stage bytes %d not 1 KiB aligned", stage_bytes);
-  const int staging = mode == 0 ? 128 * BN * 2 : 128 * (BN + 1) * 4;
+  const int staging = mode == 0 ? a.group * 128 * BN * 2 : 128 * (BN + 1) * 4;
   const int its_per_tile = a.taps * a.kchunks / a.tps;
   const int share_div = share ? share : 2;
   bool two_per_sm = (a.total_tiles >= 2 * n_sm || share) && a.tmem_cols <= 512 / share_div;
@@ -287,6 +295,10 @@ int conv_plan_build(const ConvDesc& d, ConvPlan* plan) {
   TCD_REQUIRE(stages >= 1, "conv: no room for a pipeline stage (%d B stage, %d B staging, %d B halo)",
               stage_bytes, staging, halo_bytes);
   a.stages = stages;
+  // halo form, one N tile: when a tile's weight stages all fit the ring they are loaded once per CTA -- the TMA
+  // engine is paced by box ROWS (32-byte rows for the 16-channel stem), not bytes, and half of the stem's rows
+  // were the same 9 KiB of weights re-fetched for each of its 43 tiles per CTA
+  a.b_resident = (a.halo && a.n_tiles_n == 1 && its_per_tile <= stages && env_int("TCD_CONV_BRES", 1, 0)) ? 1 : 0;
   a.a_ring_off = stages * stage_bytes;
   a.staging_off = a.a_ring_off + halo_bytes;
   a.bias_n = d.cout_pad <= kConvMaxBias ? d.cout_pad : 0;

@@ -56,12 +56,15 @@ struct ConvArgs {
   // TMA and UMMA alike, so a view may start at any 128-byte row with base-offset 0 -- measured: the
   // parity tests pass with 0 and fail with (start >> 7) & 7); the operand ring then carries weights only
   int halo, a_stages, a_stage_bytes, a_ring_off, halo_w;
-  int dbg;                      // measurement only (TCD_CONV_DBG): 1 no operand loads, 2 no MMAs, 4 no SiLU, 8 no tcgen05.ld, 16 no staging stores
+  int dbg;                      // measurement only (TCD_CONV_DBG): 1 = no operand loads, 2 = no MMAs
   int tps;                      // filter taps per weight stage (halo mode: 1, 3 or 9; else 1)
   int bias_n;                   // entries of bias staged in shared memory (0: read from global)
   const float* bias;
   const __nv_bfloat16* resid;
   int r_ctot, r_coff;
+  int b_resident;               // halo form: the weight stages of a tile fit the ring and every tile of the CTA uses
+                                // the same ones (n_tiles_n == 1): loaded for the first tile only
+  int group;                    // output tiles per accumulator round (1, 2 or 4; > 1 only with n_tiles_n == 1)
   int resid_pre;                // 1: residual added BEFORE the activation (ResNet), 0: after (CSP bottleneck)
   long long r_nstride;          // elements between images of the residual tensor
   float* out_f32;
@@ -161,7 +164,7 @@ __device__ __forceinline__ void conv_add_resid(const ConvArgs& p, float (&v)[NC]
   }
 }
 
-template <int NC>
+template <int NC, int OFF>
 __device__ __forceinline__ void conv_finish_cols(const ConvArgs& p, const uint32_t (&r)[32], int c0,
                                                  const float* bias_g, int row, bool valid,
                                                  const ConvTile& t, int y, int x, uint8_t* stage_base) {
@@ -170,13 +173,13 @@ __device__ __forceinline__ void conv_finish_cols(const ConvArgs& p, const uint32
 #pragma unroll
   for (int j = 0; j < NC / 4; ++j) {
     const float4 b = b4[j];
-    v[4 * j + 0] = __uint_as_float(r[4 * j + 0]) + b.x;
-    v[4 * j + 1] = __uint_as_float(r[4 * j + 1]) + b.y;
-    v[4 * j + 2] = __uint_as_float(r[4 * j + 2]) + b.z;
-    v[4 * j + 3] = __uint_as_float(r[4 * j + 3]) + b.w;
+    v[4 * j + 0] = __uint_as_float(r[OFF + 4 * j + 0]) + b.x;
+    v[4 * j + 1] = __uint_as_float(r[OFF + 4 * j + 1]) + b.y;
+    v[4 * j + 2] = __uint_as_float(r[OFF + 4 * j + 2]) + b.z;
+    v[4 * j + 3] = __uint_as_float(r[OFF + 4 * j + 3]) + b.w;
   }
   if (p.mode == 0 && p.resid != nullptr && p.resid_pre && valid) conv_add_resid<NC>(p, v, c0, t, y, x);
-  if (p.silu == 1 && !(p.dbg & 4)) {
+  if (p.silu == 1) {
 #pragma unroll
     for (int j = 0; j < NC; ++j) v[j] = silu_f(v[j]);
   } else if (p.silu == 2) {
@@ -200,7 +203,7 @@ __device__ __forceinline__ void conv_finish_cols(const ConvArgs& p, const uint32
       q.y = pack_bf16x2(v[u * 8 + 2], v[u * 8 + 3]);
       q.z = pack_bf16x2(v[u * 8 + 4], v[u * 8 + 5]);
       q.w = pack_bf16x2(v[u * 8 + 6], v[u * 8 + 7]);
-      if (!(p.dbg & 16)) *reinterpret_cast<uint4*>(rowp + (((u0 + u) ^ sw) << 4)) = q;
+      *reinterpret_cast<uint4*>(rowp + (((u0 + u) ^ sw) << 4)) = q;
     }
   } else {
     // f32 prediction rows: park the slab in this warp's private staging rows (stride BN+1 words,
@@ -309,14 +312,17 @@ conv_umma_kernel(const __grid_constant__ ConvMaps maps, const __grid_constant__ 
         for (int t = blockIdx.x; t < p.total_tiles; t += gridDim.x, ++jt) {
           const ConvTile c = conv_tile(p, t);
           conv_trace_tile(p, 32, jt);
+          const bool load_b = !p.b_resident || jt == 0;
           for (int kc = 0; kc < p.kchunks; ++kc) {
             for (int tap = 0; tap < 9; tap += p.tps) {
-              mbar_wait(&empty_bar[ring.s], ring.ph ^ 1u);
-              mbar_expect_tx(&full_bar[ring.s], (p.dbg & 1) ? 0u : b_tx);
-              if (!(p.dbg & 1))
-                tma_load_3d(smem + (size_t)ring.s * stage_bytes, &maps.b, &full_bar[ring.s], kc * p.ck,
-                            c.n_tile * p.BN, tap);
-              ring.advance();
+              if (load_b) {
+                mbar_wait(&empty_bar[ring.s], ring.ph ^ 1u);
+                mbar_expect_tx(&full_bar[ring.s], (p.dbg & 1) ? 0u : b_tx);
+                if (!(p.dbg & 1))
+                  tma_load_3d(smem + (size_t)ring.s * stage_bytes, &maps.b, &full_bar[ring.s], kc * p.ck,
+                              c.n_tile * p.BN, tap);
+                ring.advance();
+              }
               if (tap == 0) {  // the halo box of this k-chunk, after the first weight load
                 mbar_wait(&a_empty_bar[aring.s], aring.ph ^ 1u);
                 mbar_expect_tx(&a_full_bar[aring.s], (p.dbg & 1) ? 0u : a_tx);
@@ -375,20 +381,25 @@ conv_umma_kernel(const __grid_constant__ ConvMaps maps, const __grid_constant__ 
       bool first = true;
       RingCursor ring{0, 0u, p.stages};
       RingCursor aring{0, 0u, p.a_stages};
+      int rnd = 0, g = 0;  // accumulator round and tile within it: a round is p.group tiles, BN columns each
       for (int t = blockIdx.x; t < p.total_tiles; t += gridDim.x, ++j) {
-        const int acc = j & 1;
-        const uint32_t aph = (uint32_t)(j >> 1) & 1u;
-        mbar_wait(&tmem_empty_bar[acc], aph ^ 1u);  // epilogue has drained this accumulator
-        tc_fence_after();
-        const uint32_t d_tmem = tmem_base + (uint32_t)(acc * p.acc_stride);
+        const int acc = rnd & 1;
+        const uint32_t aph = (uint32_t)(rnd >> 1) & 1u;
+        if (g == 0) {
+          mbar_wait(&tmem_empty_bar[acc], aph ^ 1u);  // epilogue has drained this accumulator
+          tc_fence_after();
+        }
+        const uint32_t d_tmem = tmem_base + (uint32_t)(acc * p.acc_stride + g * p.BN);
         if (p.halo) {
           const int rowb = p.ck * 2;
           const uint32_t sbo_a = (uint32_t)(p.halo_w * rowb);
+          const bool wait_b = !p.b_resident || j == 0;
+          if (p.b_resident) ring.s = 0;  // resident weights: every tile walks the same stages
           for (int kc = 0; kc < p.kchunks; ++kc) {
             mbar_wait(&a_full_bar[aring.s], aring.ph);
             const uint32_t halo_addr = smem_u32(smem + p.a_ring_off + (size_t)aring.s * p.a_stage_bytes);
             for (int tap0 = 0; tap0 < 9; tap0 += p.tps) {
-              mbar_wait(&full_bar[ring.s], ring.ph);
+              if (wait_b) mbar_wait(&full_bar[ring.s], ring.ph);
               tc_fence_after();
               if (first) conv_trace(p, 5);
               first = false;
@@ -404,7 +415,7 @@ conv_umma_kernel(const __grid_constant__ ConvMaps maps, const __grid_constant__ 
                   if (!(p.dbg & 2)) umma_bf16(d_tmem, ad, bd, idesc, (uint32_t)((kc | tap | k) != 0));
                 }
               }
-              umma_commit(&empty_bar[ring.s]);
+              if (!p.b_resident) umma_commit(&empty_bar[ring.s]);
               ring.advance();
             }
             umma_commit(&a_empty_bar[aring.s]);
@@ -427,8 +438,12 @@ conv_umma_kernel(const __grid_constant__ ConvMaps maps, const __grid_constant__ 
             ring.advance();
           }
         }
-        umma_commit(&tmem_full_bar[acc]);
-        conv_trace_tile(p, 48, j);
+        if (++g == p.group || t + (int)gridDim.x >= p.total_tiles) {  // round complete (or the CTA's last tile)
+          umma_commit(&tmem_full_bar[acc]);
+          conv_trace_tile(p, 48, rnd);
+          g = 0;
+          ++rnd;
+        }
       }
       conv_trace(p, 6);
     }
@@ -448,74 +463,91 @@ conv_umma_kernel(const __grid_constant__ ConvMaps maps, const __grid_constant__ 
     if (p.pdl && p.resid != nullptr) pdl_wait();
     const float* bias_src = p.bias_n ? s_bias : p.bias;
     const int nslab = (p.BN + 31) >> 5;
-    int j = 0;
-    for (int t = blockIdx.x; t < p.total_tiles; t += gridDim.x, ++j) {
-      const ConvTile c = conv_tile(p, t);
+    // Accumulator rounds: p.group consecutive tiles of this CTA share one round (group * BN <= 128 columns),
+    // so the fixed per-round chain (barrier waits, proxy fence, TMA-store issue, staging hand-over: ~2 000
+    // cycles whatever the tile holds, profiles/r01_conv_timeline.md) is paid once per 128 columns instead of
+    // once per 32/64-column tile -- the stem has 21 such tiles per CTA.
+    const int n_mine = (p.total_tiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;
+    const int tile_stage_bytes = 128 * p.BN * 2;
+    int j = 0;  // round
+    for (int i0 = 0; i0 < n_mine; i0 += p.group, ++j) {
+      const int n_g = min(p.group, n_mine - i0);
       const int acc = j & 1;
       const uint32_t aph = (uint32_t)(j >> 1) & 1u;
-      const int y = c.y0 + ly;
-      const int x = c.x0 + lx;
-      const bool valid = (row < p.TW * p.TH) && (y < p.Ho) && (x < p.Wo);
+      // the tile the slab being finished belongs to; the first one is located while the MMAs still run
+      ConvTile c;
+      int y = 0, x = 0;
+      bool valid = false;
+      uint8_t* stg = staging;
+      auto set_tile = [&](int g) {
+        c = conv_tile(p, (int)blockIdx.x + (i0 + g) * (int)gridDim.x);
+        y = c.y0 + ly;
+        x = c.x0 + lx;
+        valid = (row < p.TW * p.TH) && (y < p.Ho) && (x < p.Wo);
+        stg = staging + (size_t)g * tile_stage_bytes;
+      };
+      set_tile(0);
       mbar_wait(&tmem_full_bar[acc], aph);
       tc_fence_after();
       if (j == 0 && warp == 2 && lane == 0) conv_trace(p, 7);
       if (warp == 2 && lane == 0) conv_trace_tile(p, 64, j);
       if (j > 0) {
-        // staging reuse: the previous tile's TMA store has finished READING it (mode 0) / every warp has
+        // staging reuse: the previous round's TMA stores have finished READING it (mode 0) / every warp has
         // finished flushing its rows (mode 1)
         if (p.mode == 0 && warp == 2 && lane == 0) tma_store_wait_read();
         asm volatile("bar.sync 1, %0;" ::"n"(32 * kConvEpiWarps) : "memory");
       }
       if (warp == 2 && lane == 0) conv_trace_tile(p, 96, j);   // staging is free
       const uint32_t taddr = tmem_base + (uint32_t)(acc * p.acc_stride) + ((uint32_t)(q * 32) << 16);
-      // slabs of 32 accumulator columns (a ragged last one of 16), double-buffered in registers: the
-      // tcgen05.ld of slab s+1 is in flight while slab s goes through bias / activation / staging
-      // (167 registers: two CTAs of 192 threads per SM, which is what TCD_CONV_SHARE=2 plans for)
+      // slabs of 32 accumulator columns (a ragged last one of 16 when group == 1), double-buffered in
+      // registers: the tcgen05.ld of slab s+1 is in flight while slab s goes through bias / activation /
+      // staging (167 registers: two CTAs of 192 threads per SM, which is what TCD_CONV_SHARE=2 plans for)
+      const int S = n_g * nslab;      // with group > 1, BN is a multiple of 32: slab s starts at column 32*s
       uint32_t ra[32], rb[32];
-      auto issue = [&](int sl, uint32_t (&r)[32]) {
-        if (p.dbg & 8) return;
-        if (p.BN - 32 * sl >= 32) tmem_ld32(taddr + 32 * sl, r); else tmem_ld16_lo(taddr + 32 * sl, r);
+      auto issue = [&](int sidx, uint32_t (&r)[32]) {
+        if (p.group > 1 || p.BN - 32 * sidx >= 32) tmem_ld32(taddr + 32 * sidx, r);
+        else tmem_ld16_lo(taddr + 32 * sidx, r);
       };
       auto handback = [&]() {  // every column has been read: the accumulator goes back to the MMA warp
         tc_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive(&tmem_empty_bar[acc]);
       };
-      auto finish = [&](const uint32_t (&r)[32], int sl) {
-        if (p.BN - 32 * sl >= 32) conv_finish_cols<32>(p, r, 32 * sl, bias_src, row, valid, c, y, x, staging);
-        else conv_finish_cols<16>(p, r, 32 * sl, bias_src, row, valid, c, y, x, staging);
+      int fg = 0, fsl = 0;            // (tile, slab) of the next finish() -- finish() runs in slab order
+      auto finish = [&](const uint32_t (&r)[32]) {
+        if (p.BN - 32 * fsl >= 32) conv_finish_cols<32, 0>(p, r, 32 * fsl, bias_src, row, valid, c, y, x, stg);
+        else conv_finish_cols<16, 0>(p, r, 32 * fsl, bias_src, row, valid, c, y, x, stg);
+        if (++fsl == nslab) {  // next tile of the round (its slab is already on its way from TMEM)
+          fsl = 0;
+          if (++fg < n_g) set_tile(fg);
+        }
       };
-      if (p.dbg & 8) {
-#pragma unroll
-        for (int u = 0; u < 32; ++u) ra[u] = rb[u] = 0;
-      }
       issue(0, ra);
-      for (int sl = 0; sl < nslab; sl += 2) {
+      for (int sidx = 0; sidx < S; sidx += 2) {
         tmem_ld_wait();
-        if (j == 0 && sl == 0 && warp == 2 && lane == 0) conv_trace(p, 12);   // first slab in registers
-        if (sl + 1 < nslab) issue(sl + 1, rb); else handback();
-        finish(ra, sl);
-        if (j == 0 && sl == 0 && warp == 2 && lane == 0) conv_trace(p, 13);   // first slab staged
-        if (sl + 1 < nslab) {
+        if (sidx + 1 < S) issue(sidx + 1, rb); else handback();
+        finish(ra);
+        if (sidx + 1 < S) {
           tmem_ld_wait();
-          if (sl + 2 < nslab) issue(sl + 2, ra); else handback();
-          finish(rb, sl + 1);
+          if (sidx + 2 < S) issue(sidx + 2, ra); else handback();
+          finish(rb);
         }
       }
       if (p.mode == 1) {
         asm volatile("bar.sync 1, %0;" ::"n"(32 * kConvEpiWarps) : "memory");
         conv_flush_rows(p, c, q, half, lane, staging, valid, y, x);
       } else {
-        if (j == 0 && warp == 2 && lane == 0) conv_trace(p, 14);              // all slabs of warp 2 staged
         fence_proxy_async_smem();
-        if (j == 0 && warp == 2 && lane == 0) conv_trace(p, 15);              // proxy fence done
         asm volatile("bar.sync 1, %0;" ::"n"(32 * kConvEpiWarps) : "memory");
         if (warp == 2 && lane == 0) conv_trace_tile(p, 112, j);  // every warp has staged its slabs
         if (warp == 2 && lane == 0) {
           const int nchunks = p.BN / p.out_chunk;
-          for (int ch = 0; ch < nchunks; ++ch)
-            tma_store_4d(&maps.o, staging + (size_t)ch * 128 * p.out_chunk * 2,
-                         p.cout_off + c.n_tile * p.BN + ch * p.out_chunk, c.x0, c.y0, c.n_img);
+          for (int g = 0; g < n_g; ++g) {
+            const ConvTile cg = conv_tile(p, (int)blockIdx.x + (i0 + g) * (int)gridDim.x);
+            for (int ch = 0; ch < nchunks; ++ch)
+              tma_store_4d(&maps.o, staging + (size_t)g * tile_stage_bytes + (size_t)ch * 128 * p.out_chunk * 2,
+                           p.cout_off + cg.n_tile * p.BN + ch * p.out_chunk, cg.x0, cg.y0, cg.n_img);
+          }
           tma_store_commit();
         }
       }

@@ -1,7 +1,8 @@
 set -x
-T=s17f
-B="python bench.py --steps 200 --warmup 10 --no-cpu-baseline --no-aux --rtdetr-batch 0 --latency-iters 0"
-for S in 0 2; do
-TCD_CONV_SHARE=$S timeout 300 $B --trace gpurun_out/${T}_trace_share$S.json > gpurun_out/${T}_bench_share$S.json 2> gpurun_out/${T}_bench_share$S.err; echo rc=$?
-done
-tail -c 400 gpurun_out/${T}_bench*.err
+T=s17l
+timeout 1500 python -m pytest tests -x -q -m gpu > gpurun_out/${T}_pytest.log 2>&1; echo rc=$?
+tail -5 gpurun_out/${T}_pytest.log
+timeout 900 python bench.py --dump-ops gpurun_out/${T}_ops.json > gpurun_out/${T}_bench.json 2> gpurun_out/${T}_bench.err; echo rc=$?
+timeout 600 python bench.py --impl reference > gpurun_out/${T}_bench_ref.json 2> gpurun_out/${T}_bench_ref.err; echo rc=$?
+timeout 300 python -c "import __graft_entry__ as g; g.smoke(); print('smoke ok')" > gpurun_out/${T}_smoke.log 2>&1; echo rc=$?
+tail -c 400 gpurun_out/${T}_bench*.err gpurun_out/${T}_smoke.log
