@@ -48,7 +48,7 @@ def parse_args():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--profile-iters", type=int, default=10)
     ap.add_argument("--latency-iters", type=int, default=30)
-    ap.add_argument("--slots", type=int, default=0, help="pipeline slots in flight (0 = all the library has)")
+    ap.add_argument("--slots", type=int, default=4, help="pipeline slots in flight (0 = all the library has)")
     ap.add_argument("--no-aux", action="store_true", help="skip the motion / crop / RT-DETR side measurements")
     ap.add_argument("--rtdetr-batch", type=int, default=32)
     ap.add_argument("--trace", default=None, help="write the in-kernel timeline of every conv launch here")
@@ -169,7 +169,7 @@ def run_reference(args):
             "cpu_baseline": {"value": fps, "unit": UNIT, "cores": threads, "kind": "port", "sample": sample},
             "e2e": {"value": fps, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
-    print(json.dumps(line), flush=True)
+    emit(json.dumps(line))
 
 
 # ----------------------------------------------------------------------------- side measurements
@@ -294,12 +294,12 @@ def _pipelined(eng, batches, steps, on_result=None, slots=2):
         if i >= slots:
             rows = eng.wait(slot)
             if on_result:
-                on_result(rows)
+                on_result(rows, slot)
         eng.submit(slot, batches[i % nb])
     for i in range(max(0, steps - slots), steps):
         rows = eng.wait(i % slots)
         if on_result:
-            on_result(rows)
+            on_result(rows, i % slots)
 
 
 def run_ours(args):
@@ -314,8 +314,8 @@ def run_ours(args):
     local = int(os.environ.get("LOCAL_RANK", "0"))
     torch.cuda.set_device(local)
     if world > 1:
-        if os.environ.get("NCCL_DEBUG", "").upper() in ("VERSION", "INFO"):
-            os.environ["NCCL_DEBUG"] = "WARN"   # keep NCCL's banner off stdout: rank 0 prints ONE JSON line
+        # NCCL writes its banner / debug lines to STDOUT by default: keep them, but on stderr -- rank 0 prints ONE JSON line
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     B = args.batch
     lib = _lib.load()
@@ -335,28 +335,35 @@ def run_ours(args):
     n_slots = min(args.slots, eng.num_slots) if args.slots > 0 else eng.num_slots
     streams = [torch.cuda.ExternalStream(eng.stream(i), device=local) for i in range(n_slots)]
 
-    # detections -> rank 0 for serving: side traffic on its own stream, double-buffered, never on the
-    # compute path; one pinned staging copy + one NCCL gather per step
     from telescope_cam_detection_b200 import stream_shard
-    gather_dev = [torch.zeros((B, 301, 7), dtype=torch.float32, device="cuda") for _ in range(2)]
-    gather_pin = [torch.zeros((B, 301, 7), dtype=torch.float32, pin_memory=True) for _ in range(2)]
-    gather_done = [torch.cuda.Event() for _ in range(2)]
+    # detections -> rank 0 for serving.  The slot's result table is already in device memory: one
+    # device-to-device copy + one NCCL gather per step on a side stream, ordered against the slot's stream by events --
+    # no host round trip, no host synchronisation, nothing on the compute streams
+    MAXO = 300
+    n_tab = B * MAXO * 7
+    gather_dev = [torch.zeros(n_tab + B, dtype=torch.float32, device="cuda") for _ in range(2)]
     gatherer = stream_shard.ResultGather(world, rank, gather_dev[0])
     side = torch.cuda.Stream(device=local)
+    slot_tab, slot_cnt = [], []
+    for sl in range(n_slots):
+        dp, cp = eng.result_device(sl)
+        slot_tab.append(torch.as_tensor(stream_shard.DeviceView(dp, (n_tab,), "<f4"), device="cuda"))
+        slot_cnt.append(torch.as_tensor(stream_shard.DeviceView(cp, (B,), "<f4"), device="cuda"))   # i32 bits, moved as-is
+    copied = [torch.cuda.Event() for _ in range(n_slots)]
     det_count = [0]
     gstep = [0]
 
-    def on_result(rows):
+    def on_result(rows, slot):
         det_count[0] += sum(r.shape[0] for r in rows)
         if world > 1:
             i = gstep[0] & 1
             gstep[0] += 1
-            gather_done[i].synchronize()
-            stream_shard.pack_table(rows, 300, out=gather_pin[i].numpy())
-            with torch.cuda.stream(side):
-                gather_dev[i].copy_(gather_pin[i], non_blocking=True)
+            with torch.cuda.stream(side):        # wait(slot) has returned: the table is final until the next submit(slot)
+                gather_dev[i][:n_tab].copy_(slot_tab[slot], non_blocking=True)
+                gather_dev[i][n_tab:].copy_(slot_cnt[slot], non_blocking=True)
+                copied[slot].record(side)
                 gatherer.gather(gather_dev[i])
-                gather_done[i].record(side)
+            streams[slot].wait_event(copied[slot])   # the slot's next batch may overwrite the table only after the copy
 
     def barrier():
         if world > 1:
@@ -507,14 +514,29 @@ def run_ours(args):
         "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline, "kernels": kernels,
         "cpu_baseline": cpu, "rtdetr": rtdetr,
     }
-    print(json.dumps(line), flush=True)
+    emit(json.dumps(line))
     eng.close()
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
 
 
+_JSON_OUT = None
+
+
+def emit(text):
+    """The ONE JSON line goes to the process's original stdout; everything else that writes to fd 1 (NCCL's version
+    banner, library chatter) was redirected to stderr by main()."""
+    out = _JSON_OUT or sys.stdout
+    out.write(text + "\n")
+    out.flush()
+
+
 def main():
+    global _JSON_OUT
+    sys.stdout.flush()
+    _JSON_OUT = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
     args = parse_args()
     if args.impl == "reference":
         run_reference(args)

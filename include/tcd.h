@@ -130,6 +130,10 @@ tcd_status tcd_detector_last_timing(const tcd_detector* det, float out_ms[5]);
  * its own events around async calls (bench.py times with events on THIS stream).           */
 void* tcd_detector_stream(tcd_detector* det, int32_t slot);
 int32_t tcd_detector_num_slots(const tcd_detector* det);
+/* Device copies of a slot's result table ([B,max_out,7] f32 rows, score-descending) and row counts ([B] i32), valid from
+ * tcd_detect_batch_wait(slot) until the next submit on that slot.  Lets a multi-GPU host forward the table to the
+ * serving rank (NCCL gather) without a host round trip; no counterpart in the single-GPU reference.                  */
+tcd_status tcd_detector_result_device(tcd_detector* det, int32_t slot, float** out_dets, int32_t** out_counts);
 /* Measurement aid: in-kernel timeline (clock64 / globaltimer stamps of the first and last CTA)
  * of conv op `idx` of the batch-B layer plan; see conv_umma.cuh for the slot meaning (2x16 milestones + 4x16 per-tile stamps of CTA 0).   */
 tcd_status tcd_detector_trace_op(tcd_detector* det, int32_t B, int32_t idx, int32_t reps,

@@ -89,6 +89,7 @@ SIGNATURES = {
     "tcd_detector_last_timing": (C.c_int, [_P, _F32P]),
     "tcd_detector_stream": (C.c_void_p, [_P, C.c_int32]),
     "tcd_detector_num_slots": (C.c_int32, [_P]),
+    "tcd_detector_result_device": (C.c_int, [_P, C.c_int32, C.POINTER(C.c_void_p), C.POINTER(C.c_void_p)]),
     "tcd_detector_trace_op": (C.c_int, [_P, C.c_int32, C.c_int32, C.c_int32, C.POINTER(C.c_uint64), _I32P, _I32P]),
     "tcd_detector_profile": (C.c_int, [_P, _PP, _I32P, _I32P, _I64P, C.c_int32, C.c_int32, C.c_int32, _F32P,
                                        C.c_int32, _I32P]),

@@ -20,7 +20,7 @@ extern std::atomic<uint64_t> g_h2d_bytes;
 
 namespace {
 
-constexpr int kSlots = 4;
+constexpr int kSlots = 6;
 constexpr int kProfileReps = 8;
 
 struct Slot {
@@ -413,6 +413,13 @@ void* tcd_detector_stream(tcd_detector* det, int32_t slot) {
 }
 
 int32_t tcd_detector_num_slots(const tcd_detector* det) { return det ? kSlots : 0; }
+
+tcd_status tcd_detector_result_device(tcd_detector* det, int32_t slot, float** out_dets, int32_t** out_counts) {
+  TCD_REQUIRE(det && slot >= 0 && slot < kSlots && out_dets && out_counts, "result_device: bad argument");
+  *out_dets = det->slot[slot].pb.out_dets;
+  *out_counts = det->slot[slot].pb.out_counts;
+  return TCD_OK;
+}
 
 // In-kernel timeline of ONE conv launch of the layer plan (op index as in tcd_detector_profile,
 // i.e. 1-based over the plan): the kernel stamps clock64/globaltimer at its pipeline milestones for

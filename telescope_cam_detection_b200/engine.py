@@ -130,6 +130,14 @@ class DetectorEngine:
         """cudaStream_t (int) of pipeline slot `slot`."""
         return int(self.lib.tcd_detector_stream(self.handle, int(slot)) or 0)
 
+    def result_device(self, slot):
+        """(dets_ptr, counts_ptr): device addresses of slot's [B,max_out,7] f32 table and [B] i32 counts, valid from
+        wait(slot) until the next submit(slot)."""
+        d, c = C.c_void_p(0), C.c_void_p(0)
+        check(self.lib.tcd_detector_result_device(self.handle, int(slot), C.byref(d), C.byref(c)),
+              "tcd_detector_result_device")
+        return int(d.value), int(c.value)
+
     @property
     def num_slots(self):
         return int(self.lib.tcd_detector_num_slots(self.handle))

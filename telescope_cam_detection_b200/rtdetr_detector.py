@@ -90,7 +90,13 @@ class RTDETRDetector:
         else:
             import torch
             ck = torch.load(self.model_path, map_location="cpu", weights_only=True)
-            sd = ck.get("state_dict", ck) if isinstance(ck, dict) else ck
+            # the reference takes checkpoint['ema']['module'], else checkpoint['model'] (src/rtdetr_detector.py:139-148)
+            if isinstance(ck, dict) and "ema" in ck and isinstance(ck["ema"], dict) and "module" in ck["ema"]:
+                sd = ck["ema"]["module"]
+            elif isinstance(ck, dict) and "model" in ck and isinstance(ck["model"], dict):
+                sd = ck["model"]
+            else:
+                sd = ck.get("state_dict", ck) if isinstance(ck, dict) else ck
         out = {}
         for k, v in sd.items():
             if hasattr(v, "detach"):
@@ -98,6 +104,9 @@ class RTDETRDetector:
                     continue
                 v = v.detach().cpu().float().numpy()
             out[k] = np.asarray(v, np.float32)
+        from . import rtdetr_keys
+        if rtdetr_keys.is_upstream(out):      # upstream rtdetrv2_pytorch names -> the names the builder reads
+            out = rtdetr_keys.from_upstream(out)
         return out
 
     def _engine(self, n):

@@ -53,6 +53,15 @@ def unpack_table(table):
     return [table[b, 1:1 + int(table[b, 0, 0])].copy() for b in range(table.shape[0])]
 
 
+class DeviceView:
+    """A device buffer owned by libtcd, exposed through __cuda_array_interface__ so torch can wrap it without a copy
+    (torch.as_tensor(DeviceView(...), device="cuda"))."""
+
+    def __init__(self, ptr, shape, typestr):
+        self.__cuda_array_interface__ = {"shape": tuple(shape), "typestr": typestr, "data": (int(ptr), False),
+                                         "version": 3, "strides": None}
+
+
 class ResultGather:
     """Per-step gather of the packed result tables to rank 0.  `gather(t)` returns, on rank 0, the list of
     every rank's table (rank order); None elsewhere.  With world == 1 it is a pass-through."""

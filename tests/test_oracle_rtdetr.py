@@ -91,3 +91,26 @@ def test_rtdetr_detector_fails_loudly_without_gpu():
     assert det.load_model() is False
     assert det.detect(np.zeros((8, 8, 3), np.uint8)) == []
     assert det.detect_batch([]) == []
+
+
+def test_upstream_key_map_round_trip():
+    """rtdetr_keys maps an upstream-named (rtdetrv2_pytorch) state dict onto exactly the keys the program builder
+    reads, values untouched (q/k/v split of in_proj included).  Completeness check only: the upstream code and
+    checkpoints are absent here."""
+    from oracle import rtdetr as oracle
+    from telescope_cam_detection_b200 import rtdetr_keys
+
+    sd = oracle.state_dict_numpy(oracle.make_model(0))
+    want = {k: v for k, v in sd.items() if not (k.startswith("class_embed.") or k.startswith("bbox_embed.")
+                                                or k.startswith("model.denoising_class_embed"))}
+    up = rtdetr_keys.to_upstream(sd)
+    assert rtdetr_keys.is_upstream(up) and not rtdetr_keys.is_upstream(sd)
+    assert "encoder.encoder.0.layers.0.self_attn.in_proj_weight" in up
+    assert up["decoder.decoder.layers.0.self_attn.in_proj_weight"].shape == (768, 256)
+    assert "backbone.res_layers.1.blocks.0.short.conv.conv.weight" in up and "backbone.res_layers.0.blocks.0.short.conv.weight" in up
+    back = rtdetr_keys.from_upstream(up)
+    assert set(back) == set(want)
+    for k in want:
+        assert np.array_equal(back[k], want[k]), k
+    with pytest.raises(KeyError):
+        rtdetr_keys.from_upstream({"backbone.unknown.weight": np.zeros(1, np.float32)})

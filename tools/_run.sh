@@ -1,8 +1,7 @@
 set -x
-T=s17l
-timeout 1500 python -m pytest tests -x -q -m gpu > gpurun_out/${T}_pytest.log 2>&1; echo rc=$?
-tail -5 gpurun_out/${T}_pytest.log
-timeout 900 python bench.py --dump-ops gpurun_out/${T}_ops.json > gpurun_out/${T}_bench.json 2> gpurun_out/${T}_bench.err; echo rc=$?
-timeout 600 python bench.py --impl reference > gpurun_out/${T}_bench_ref.json 2> gpurun_out/${T}_bench_ref.err; echo rc=$?
-timeout 300 python -c "import __graft_entry__ as g; g.smoke(); print('smoke ok')" > gpurun_out/${T}_smoke.log 2>&1; echo rc=$?
-tail -c 400 gpurun_out/${T}_bench*.err gpurun_out/${T}_smoke.log
+T=s17o
+B="python bench.py --steps 300 --warmup 10 --no-cpu-baseline --no-aux --rtdetr-batch 0 --latency-iters 0"
+for S in 4 6 3; do
+timeout 300 $B --slots $S > gpurun_out/${T}_bench_s$S.json 2> gpurun_out/${T}_bench_s$S.err; echo rc=$?
+done
+tail -c 300 gpurun_out/${T}_bench*.err
