@@ -48,6 +48,7 @@ def parse_args():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--profile-iters", type=int, default=10)
     ap.add_argument("--latency-iters", type=int, default=30)
+    ap.add_argument("--no-gather", action="store_true", help="N>1 only: skip the NCCL gather of result tables (A/B measurement)")
     ap.add_argument("--slots", type=int, default=4, help="pipeline slots in flight (0 = all the library has)")
     ap.add_argument("--no-aux", action="store_true", help="skip the motion / crop / RT-DETR side measurements")
     ap.add_argument("--rtdetr-batch", type=int, default=32)
@@ -340,30 +341,49 @@ def run_ours(args):
     # device-to-device copy + one NCCL gather per step on a side stream, ordered against the slot's stream by events --
     # no host round trip, no host synchronisation, nothing on the compute streams
     MAXO = 300
+    RING = 8
     n_tab = B * MAXO * 7
-    gather_dev = [torch.zeros(n_tab + B, dtype=torch.float32, device="cuda") for _ in range(2)]
-    gatherer = stream_shard.ResultGather(world, rank, gather_dev[0])
-    side = torch.cuda.Stream(device=local)
+    ringg = stream_shard.RingGather(world, RING, n_tab + B, "cuda")
+    copy_stream = torch.cuda.Stream(device=local)    # local device-to-device copies: the only thing a slot waits for
+    side = torch.cuda.Stream(device=local)           # NCCL: the ranks meet here, one collective per RING steps
     slot_tab, slot_cnt = [], []
     for sl in range(n_slots):
         dp, cp = eng.result_device(sl)
         slot_tab.append(torch.as_tensor(stream_shard.DeviceView(dp, (n_tab,), "<f4"), device="cuda"))
         slot_cnt.append(torch.as_tensor(stream_shard.DeviceView(cp, (B,), "<f4"), device="cuda"))   # i32 bits, moved as-is
     copied = [torch.cuda.Event() for _ in range(n_slots)]
+    ready = [torch.cuda.Event() for _ in range(2)]
+    gathered = [torch.cuda.Event() for _ in range(2)]
     det_count = [0]
     gstep = [0]
 
+    def collect(half):
+        ready[half].record(copy_stream)
+        side.wait_event(ready[half])
+        with torch.cuda.stream(side):
+            ringg.collect(half)
+            gathered[half].record(side)
+
     def on_result(rows, slot):
         det_count[0] += sum(r.shape[0] for r in rows)
-        if world > 1:
-            i = gstep[0] & 1
+        if world > 1 and not args.no_gather:
+            half, i = ringg.slot(gstep[0])
+            if i == 0 and gstep[0] >= 2 * RING:
+                copy_stream.wait_event(gathered[half])   # the collective that last read this half of the ring
             gstep[0] += 1
-            with torch.cuda.stream(side):        # wait(slot) has returned: the table is final until the next submit(slot)
-                gather_dev[i][:n_tab].copy_(slot_tab[slot], non_blocking=True)
-                gather_dev[i][n_tab:].copy_(slot_cnt[slot], non_blocking=True)
-                copied[slot].record(side)
-                gatherer.gather(gather_dev[i])
-            streams[slot].wait_event(copied[slot])   # the slot's next batch may overwrite the table only after the copy
+            with torch.cuda.stream(copy_stream):      # wait(slot) has returned: the table is final until the next submit(slot)
+                ringg.buf[half][i, :n_tab].copy_(slot_tab[slot], non_blocking=True)
+                ringg.buf[half][i, n_tab:].copy_(slot_cnt[slot], non_blocking=True)
+                copied[slot].record(copy_stream)
+            streams[slot].wait_event(copied[slot])    # the slot's next batch may overwrite the table only after the copy
+            if i == RING - 1:
+                collect(half)
+
+    def flush_results():
+        """Tables of the last, partial ring (every rank runs the same number of steps, so the collectives match)."""
+        if world > 1 and not args.no_gather and gstep[0] % RING:
+            collect(ringg.slot(gstep[0])[0])
+            gstep[0] += RING - gstep[0] % RING
 
     def barrier():
         if world > 1:
@@ -383,11 +403,19 @@ def run_ours(args):
         h0 = lib.tcd_h2d_byte_count()
         t0 = time.perf_counter()
         _pipelined(eng, batches, steps, cb, n_slots)
+        if cb is not None:
+            flush_results()
         for ev, st in zip(ends, streams):
             ev.record(st)
+        tail_evs = []
+        if cb is not None and world > 1:            # the copies and collectives belong to the timed region too
+            for st in (copy_stream, side):
+                ev = torch.cuda.Event(enable_timing=True)
+                ev.record(st)
+                tail_evs.append(ev)
         barrier()
         wall = time.perf_counter() - t0
-        ms = max(e0.elapsed_time(ev) for ev in ends)
+        ms = max(e0.elapsed_time(ev) for ev in ends + tail_evs)
         ms = stream_shard.max_over_ranks(ms, world, device="cuda")
         h2d_bytes[0] = (lib.tcd_h2d_byte_count() - h0) // max(1, steps)
         return ms, lib.tcd_launch_count() - n0, wall

@@ -52,6 +52,18 @@ def _worker(rank, world, port, q):
                     seen[(c, step)] = out[i]
                 for i in range(len(cams_r), B):
                     assert out[i].shape == (0, 7)
+    # ring of 4 steps in one collective (what bench.py does over NCCL every 8 steps)
+    rg = ss.RingGather(world, 4, 5, "cpu")
+    for step in range(6):
+        half, i = rg.slot(step)
+        assert (half, i) == ((step // 4) & 1, step % 4)
+        rg.buf[half][i] = torch.full((5,), float(10 * rank + step))
+        if i == 3 or step == 5:
+            out = rg.collect(half)
+            for r in range(world):
+                n = 4 if step == 3 else 2
+                exp = torch.tensor([10 * r + s for s in range(step - n + 1, step + 1)], dtype=torch.float32)
+                assert torch.equal(out[r, :n, 0], exp), (rank, r, step, out[r, :, 0])
     ms = ss.max_over_ranks(1.0 + rank, world)
     dist.barrier()
     dist.destroy_process_group()
