@@ -482,8 +482,8 @@ def run_ours(args):
                 "(cold-cache serialised capture, profiles/traffic.json)"}
     pre = prof[0]
     pre_bytes = B * (FRAME_H * FRAME_W * 3 + 640 * 640 * 4 * 2)
-    if args.pre == "letterbox":  # only the source rows the 640x360 content taps are algorithmically needed
-        pre_bytes = B * (2 * 360 * FRAME_W * 3 + 640 * 640 * 4 * 2)
+    if args.pre == "letterbox":  # exact 3:1: one source row per content row carries weight (the kernel reads only those)
+        pre_bytes = B * (360 * FRAME_W * 3 + 640 * 640 * 4 * 2)
     post_ms = sum(o["ms"] for o in prof[-4:])
     kernels = {
         "preprocess": {"ms": pre["ms"], "GB/s": pre_bytes / (pre["ms"] * 1e-3) / 1e9,

@@ -188,16 +188,15 @@ static int enqueue_input(tcd_detector* d, Slot& s, YoloxPlan* p, const uint8_t* 
       // Row-sparse upload.  When the vertical resize ratio is an odd integer k (1080p -> 640 letterbox:
       // k = 3 exactly), the bilinear tap of output row d is s = k*(d+0.5)-0.5 = k*d + (k-1)/2, an integer:
       // the second tap's weight is exactly 0, so only every k-th source row contributes to the result and
-      // only those rows cross PCIe (one pitched copy).  The other staging rows keep whatever finite bytes
-      // they held and are multiplied by 0.0f; the output is bit-identical to a full upload
+      // only those rows cross PCIe (one pitched copy); preproc_kernel reads only those rows as well
+      // (PreFrame::row_step), so the output is bit-identical to a full upload
       // (tests/test_gpu_yolox.py::test_row_sparse_upload_is_exact).
       PreFrame probe;
       preproc_describe(&pc, ptr, h[b], w[b], st, &probe);
-      const int k = (int)probe.scale_y;
-      const bool sparse = g_sparse_upload && (float)k == probe.scale_y && k >= 3 && (k & 1) &&
-                          (long long)k * probe.content_h <= (long long)h[b];
+      const int k = probe.row_step;
+      const bool sparse = g_sparse_upload && k > 1;
       if (sparse) {
-        const size_t r0 = (size_t)(k - 1) / 2;
+        const size_t r0 = (size_t)probe.row_phase;
         TCD_CUDA_OK(cudaMemcpy2DAsync(dst + r0 * tight, (size_t)k * tight, ptr + r0 * (size_t)st, (size_t)k * (size_t)st,
                                       tight, (size_t)probe.content_h, cudaMemcpyHostToDevice, s.stream));
         g_h2d_bytes.fetch_add((uint64_t)probe.content_h * tight, std::memory_order_relaxed);

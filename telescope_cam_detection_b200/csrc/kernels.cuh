@@ -11,6 +11,9 @@ struct PreFrame {
   int h, w;
   int content_h, content_w;  // letterbox content size (== out size in stretch mode)
   float scale_y, scale_x;
+  // vertical ratio an odd integer k (1080p -> 640 letterbox: 3): output row d taps source row k*d + (k-1)/2 with
+  // weight exactly 1 and its neighbour with weight exactly 0 -- only every k-th row is read (and uploaded)
+  int row_step, row_phase;   // 1, 0 in the general case
 };
 int preproc_launch(const tcd_preproc_cfg* cfg, const PreFrame* frames_host, const PreFrame* frames_dev,
                    int B, int layout, void* out_dev, cudaStream_t stream);

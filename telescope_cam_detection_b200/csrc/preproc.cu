@@ -62,8 +62,9 @@ preproc_kernel(const PreFrame* __restrict__ frames, const PreArgs a, void* __res
     tap(f.scale_x, cx_b - 1, f.w, &t0, &in_x1, &l);
     tap(f.scale_y, cy_b - 1, f.h, &t0, &in_y1, &l);
     if (staged) {
-      // aligned byte window [byte0, byte0 + row_bytes) of every needed row
-      const int nrows = in_y1 - in_y0 + 1;
+      // aligned byte window [byte0, byte0 + row_bytes) of every needed row; with row_step > 1 the needed rows are
+      // exactly one per output row (in_y0 + r * row_step), the rows between them carry weight 0 and are not read
+      const int nrows = f.row_step > 1 ? (cy_b - oy_a) : in_y1 - in_y0 + 1;
       const uintptr_t rowbase = (uintptr_t)f.ptr + (uintptr_t)((long long)in_y0 * f.stride);
       const long long b_lo = (long long)in_x0 * 3;
       const long long b_hi = (long long)(in_x1 + 1) * 3;
@@ -74,7 +75,7 @@ preproc_kernel(const PreFrame* __restrict__ frames, const PreArgs a, void* __res
       const int vec_per_row = row_bytes >> 4;
       for (int i = threadIdx.x; i < nrows * vec_per_row; i += kPreThreads) {
         const int r = i / vec_per_row, v = i - r * vec_per_row;
-        const uint4* src = reinterpret_cast<const uint4*>(f.ptr + (long long)(in_y0 + r) * f.stride +
+        const uint4* src = reinterpret_cast<const uint4*>(f.ptr + (long long)(in_y0 + r * f.row_step) * f.stride +
                                                           byte0) + v;
         uint4 q;
         asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
@@ -99,6 +100,7 @@ preproc_kernel(const PreFrame* __restrict__ frames, const PreArgs a, void* __res
       int y0, y1;
       float ly;
       tap(f.scale_y, oy, f.h, &y0, &y1, &ly);
+      if (f.row_step > 1) y1 = y0;  // ly == 0 exactly: the second tap is the first one again, times 0
 #pragma unroll
       for (int dx = 0; dx < 2; ++dx) {
         const int ox = ox0 + dx;
@@ -113,8 +115,10 @@ preproc_kernel(const PreFrame* __restrict__ frames, const PreArgs a, void* __res
         const float hx = 1.f - lx, hy = 1.f - ly;
         const uint8_t *p00, *p01, *p10, *p11;
         if (staged) {
-          const uint8_t* r0 = tile + (size_t)(y0 - in_y0) * a.smem_row_bytes - byte0;
-          const uint8_t* r1 = tile + (size_t)(y1 - in_y0) * a.smem_row_bytes - byte0;
+          const int s0 = f.row_step > 1 ? oy - oy_a : y0 - in_y0;
+          const int s1 = f.row_step > 1 ? oy - oy_a : y1 - in_y0;
+          const uint8_t* r0 = tile + (size_t)s0 * a.smem_row_bytes - byte0;
+          const uint8_t* r1 = tile + (size_t)s1 * a.smem_row_bytes - byte0;
           p00 = r0 + x0 * 3; p01 = r0 + x1 * 3; p10 = r1 + x0 * 3; p11 = r1 + x1 * 3;
         } else {
           const uint8_t* r0 = f.ptr + (long long)y0 * f.stride;
@@ -188,7 +192,7 @@ int preproc_launch(const tcd_preproc_cfg* cfg, const PreFrame* frames_host, cons
   for (int b = 0; b < B; ++b) {
     const PreFrame& f = frames_host[b];
     if ((f.stride & 15) != 0 || ((uintptr_t)f.ptr & 15) != 0) can_stage = false;
-    int rows = (int)(f.scale_y * kPreTileH) + 4;
+    int rows = f.row_step > 1 ? kPreTileH : (int)(f.scale_y * kPreTileH) + 4;
     int rb = (((int)(f.scale_x * kPreTileW) + 4) * 3 + 47) & ~15;
     if (rows > max_rows) max_rows = rows;
     if (rb > max_row_bytes) max_row_bytes = rb;
@@ -243,6 +247,11 @@ void preproc_describe(const tcd_preproc_cfg* cfg, const uint8_t* ptr, int h, int
     f->scale_x = (float)w / (float)cfg->out_w;
     f->scale_y = (float)h / (float)cfg->out_h;
   }
+  // s = k*(d+0.5)-0.5 = k*d + (k-1)/2 is an integer for an odd integer ratio k: exact in fp32, FMA or not
+  const int k = (int)f->scale_y;
+  const bool odd_int = (float)k == f->scale_y && k >= 3 && (k & 1) && (long long)k * f->content_h <= (long long)h;
+  f->row_step = odd_int ? k : 1;
+  f->row_phase = odd_int ? (k - 1) / 2 : 0;
 }
 
 }  // namespace tcd

@@ -130,8 +130,40 @@ int YoloxWeights::upload(const WeightBlob& blob) {
     W_TRY(fuse("head.conv_a." + s, "head.cls_convs." + s + ".0", "head.reg_convs." + s + ".0"));
     W_TRY(one("head.cls_b." + s, "head.cls_convs." + s + ".1"));
     W_TRY(one("head.reg_b." + s, "head.reg_convs." + s + ".1"));
-    W_TRY(one("head.cls_pred." + s, "head.cls_preds." + s));
-    W_TRY(fuse("head.regobj_pred." + s, "head.reg_preds." + s, "head.obj_preds." + s, 16));
+    // the three 1x1 prediction convs of a level as ONE block-diagonal GEMM over [cls_feat | reg_feat]:
+    // rows 0-3 reg, 4 obj (weights on the reg_feat half), rows 5.. cls (weights on the cls_feat half), zeros
+    // elsewhere.  Exact zeros add exact zeros to the fp32 accumulator, so every logit keeps its bits; the kernel
+    // writes whole 85-float rows instead of a 5-float and an 80-float piece from two launches.
+    {
+      const WeightEntry *er = get("head.reg_preds." + s), *eo = get("head.obj_preds." + s),
+                        *ec = get("head.cls_preds." + s);
+      TCD_REQUIRE(er && eo && ec, "weights: missing prediction convs of level %d", l);
+      TCD_REQUIRE(er->k == 1 && eo->k == 1 && ec->k == 1 && er->cin == ec->cin && eo->cin == ec->cin &&
+                      er->cout == 4 && eo->cout == 1,
+                  "weights: unexpected prediction conv shapes at level %d", l);
+      const int hc = ec->cin, cout = 5 + ec->cout, cout_pad = (cout + 15) & ~15, cin2 = 2 * hc;
+      std::vector<uint16_t> hw((size_t)cout_pad * cin2, 0);
+      std::vector<float> hb(cout_pad, 0.f);
+      for (int o = 0; o < 4; ++o) {
+        hb[o] = er->b[o];
+        for (int c = 0; c < hc; ++c) hw[(size_t)o * cin2 + hc + c] = f32_to_bf16_rn(er->w[(size_t)o * hc + c]);
+      }
+      hb[4] = eo->b[0];
+      for (int c = 0; c < hc; ++c) hw[(size_t)4 * cin2 + hc + c] = f32_to_bf16_rn(eo->w[c]);
+      for (int o = 0; o < ec->cout; ++o) {
+        hb[5 + o] = ec->b[o];
+        for (int c = 0; c < hc; ++c) hw[(size_t)(5 + o) * cin2 + c] = f32_to_bf16_rn(ec->w[(size_t)o * hc + c]);
+      }
+      DevConv* out = &convs["head.pred." + s];
+      TCD_CUDA_OK(cudaMalloc(&out->w, hw.size() * 2));
+      TCD_CUDA_OK(cudaMalloc((void**)&out->bias, hb.size() * 4));
+      TCD_CUDA_OK(cudaMemcpy(out->w, hw.data(), hw.size() * 2, cudaMemcpyHostToDevice));
+      TCD_CUDA_OK(cudaMemcpy(out->bias, hb.data(), hb.size() * 4, cudaMemcpyHostToDevice));
+      out->cout = cout;
+      out->cout_pad = cout_pad;
+      out->cin_pad = cin2;
+      out->k = 1;
+    }
     const WeightEntry* cp = get("head.cls_preds." + s);
     num_classes = cp->cout;
     TCD_REQUIRE(num_classes % 16 == 0, "weights: num_classes %d must be a multiple of 16", num_classes);

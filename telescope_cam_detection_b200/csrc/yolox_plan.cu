@@ -59,7 +59,7 @@ struct Builder {
     plan.ops.push_back(op);
   }
 
-  void pred(const std::string& wname, const Act& x, int col, int row_off, int rows_per_img) {
+  void pred(const std::string& wname, const Act& x, int col, int row_off, int rows_per_img, double flops = 0) {
     if (rc) return;
     const DevConv* w = dc(wname);
     if (!w || dry) return;
@@ -74,6 +74,7 @@ struct Builder {
     op.name = wname;
     rc = conv_plan_build(d, &op.conv);
     if (rc) return;
+    if (flops > 0) op.conv.flops = flops;  // block-diagonal weights: count the non-zero half only
     plan.conv_flops += op.conv.flops;
     plan.ops.push_back(op);
   }
@@ -193,12 +194,11 @@ struct Builder {
       conv("head.stem." + s, f, 0, st, 0, 1);
       Act ha = alloc("head.conv_a." + s, f.H, f.W, 2 * hc);
       conv("head.conv_a." + s, st, 0, ha, 0, 1);
-      Act hcls = alloc("head.cls_feat." + s, f.H, f.W, hc);
-      Act hreg = alloc("head.reg_feat." + s, f.H, f.W, hc);
-      conv("head.cls_b." + s, ha, 0, hcls, 0, 1);
-      conv("head.reg_b." + s, ha, hc, hreg, 0, 1);
-      pred("head.regobj_pred." + s, hreg, 0, row_off, A);
-      pred("head.cls_pred." + s, hcls, 5, row_off, A);
+      Act hfeat = alloc("head.feat." + s, f.H, f.W, 2 * hc);   // [cls_feat | reg_feat]
+      conv("head.cls_b." + s, ha, 0, hfeat, 0, 1);
+      conv("head.reg_b." + s, ha, hc, hfeat, hc, 1);
+      pred("head.pred." + s, hfeat, 0, row_off, A,
+           2.0 * B * f.H * f.W * (double)(5 + plan.num_classes) * hc);
       plan.lvl_start[l] = row_off;
       plan.lvl_w[l] = f.W;
       plan.lvl_stride[l] = strides[l];

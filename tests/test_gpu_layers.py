@@ -31,14 +31,14 @@ STAGES = [
     ("cat_n4", "backbone.bu_conv1", (0, 256)),
     ("pan_out0", "backbone.C3_n4", None),
     ("head.stem.0", "head.stems.0", None),
-    ("head.cls_feat.0", "head.cls_convs.0", None),
-    ("head.reg_feat.0", "head.reg_convs.0", None),
+    ("head.feat.0", "head.cls_convs.0", (0, 128)),
+    ("head.feat.0", "head.reg_convs.0", (128, 256)),
     ("head.stem.1", "head.stems.1", None),
-    ("head.cls_feat.1", "head.cls_convs.1", None),
-    ("head.reg_feat.1", "head.reg_convs.1", None),
+    ("head.feat.1", "head.cls_convs.1", (0, 128)),
+    ("head.feat.1", "head.reg_convs.1", (128, 256)),
     ("head.stem.2", "head.stems.2", None),
-    ("head.cls_feat.2", "head.cls_convs.2", None),
-    ("head.reg_feat.2", "head.reg_convs.2", None),
+    ("head.feat.2", "head.cls_convs.2", (0, 128)),
+    ("head.feat.2", "head.reg_convs.2", (128, 256)),
 ]
 
 
