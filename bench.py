@@ -279,6 +279,9 @@ def rtdetr_side(local, batch, peaks):
     msda = [o for o in prof if o["name"].endswith(".msda")]
     msda_ms = float(np.mean([o["ms"] for o in msda]))
     msda_bytes = batch * 300 * 8 * 12 * 4 * 32 * 2          # samples x taps x 32 ch x bf16
+    if os.environ.get("TCD_RTDETR_DUMP"):
+        with open(os.environ["TCD_RTDETR_DUMP"], "w") as f:
+            json.dump(prof, f)
     top = sorted(prof, key=lambda o: -o["ms"])[:6]
     res = {"workload": "RT-DETR-R50 640x640 batch %d, 300 queries, no NMS (device-resident input)" % batch,
            "frames_per_s": batch / (ms * 1e-3), "ms_per_batch": ms, "kernels_per_batch": len(prof),
