@@ -188,7 +188,13 @@ int conv_plan_build(const ConvDesc& d, ConvPlan* plan) {
   // TCD_CONV_SHARE=n (default 2, 0 = off): every launch is planned for 1/n of an SM (smem, TMEM, registers) with
   // one CTA per SM, so the next layer's prologue (PDL) and the layers of the other pipeline slots are co-resident
   // with it and fill its latency bubbles (measured: 8 940 -> 11 304 frames/s at n = 2)
-  const int share = d.share >= 0 ? d.share : env_int("TCD_CONV_SHARE", 2, 0);
+  int share = d.share >= 0 ? d.share : env_int("TCD_CONV_SHARE", 2, 0);
+  // layers with very many tiles per CTA are paced by the per-tile epilogue chain of ONE CTA: they take whole SMs
+  // (two CTAs each) even when everything else is planned for half an SM
+  {
+    const int thr = env_int("TCD_CONV_SHARE_MAX_TILES", 20, 0);  // measured: 20 (the stem only) +1.8 %, 8 (dark2 too) -1.4 %
+    if (thr > 0 && share > 0 && (long)m_tiles >= (long)thr * n_sm) share = 0;
+  }
   const int bn_cap = share >= 3 ? 64 : 128;
   int BN;
   if (mode == 1) {

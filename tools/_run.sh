@@ -1,7 +1,7 @@
 set -x
-T=s17z
-B="python bench.py --steps 20 --warmup 3 --no-cpu-baseline --latency-iters 0 --profile-iters 1"
-TCD_RTDETR_SPLIT=2 timeout 600 $B > gpurun_out/${T}_bench_sp2.json 2> gpurun_out/${T}_bench_sp2.err; echo rc=$?
-TCD_RTDETR_SPLIT=4 timeout 600 $B > gpurun_out/${T}_bench_sp4.json 2> gpurun_out/${T}_bench_sp4.err; echo rc=$?
-TCD_RTDETR_SPLIT=2 TCD_PROGRAM_SHARE=0 timeout 600 $B > gpurun_out/${T}_bench_sp2s0.json 2> gpurun_out/${T}_bench_sp2s0.err; echo rc=$?
+T=s18b
+B="python bench.py --steps 300 --warmup 10 --no-cpu-baseline --no-aux --rtdetr-batch 0 --latency-iters 0"
+for X in 0 20 8 4; do
+TCD_CONV_SHARE_MAX_TILES=$X timeout 300 $B > gpurun_out/${T}_bench_x$X.json 2> gpurun_out/${T}_bench_x$X.err; echo rc=$?
+done
 tail -c 300 gpurun_out/${T}_bench*.err
