@@ -57,6 +57,21 @@ static const bool g_use_halo = [] {
 }();
 
 
+using ConvKernelFn = void (*)(const ConvMaps, const ConvArgs);
+// (activation 0..3, halo form, f32-row output) -> kernel instantiation
+static ConvKernelFn conv_kernel_variant(int act, int halo, int f32) {
+  static const ConvKernelFn tbl[4][2][2] = {
+      {{conv_umma_kernel<0, false, false>, conv_umma_kernel<0, false, true>},
+       {conv_umma_kernel<0, true, false>, conv_umma_kernel<0, true, true>}},
+      {{conv_umma_kernel<1, false, false>, conv_umma_kernel<1, false, true>},
+       {conv_umma_kernel<1, true, false>, conv_umma_kernel<1, true, true>}},
+      {{conv_umma_kernel<2, false, false>, conv_umma_kernel<2, false, true>},
+       {conv_umma_kernel<2, true, false>, conv_umma_kernel<2, true, true>}},
+      {{conv_umma_kernel<3, false, false>, conv_umma_kernel<3, false, true>},
+       {conv_umma_kernel<3, true, false>, conv_umma_kernel<3, true, true>}}};
+  return tbl[act & 3][halo ? 1 : 0][f32 ? 1 : 0];
+}
+
 static int sm_count() {
   static int n = 0;
   if (n == 0) {
@@ -358,8 +373,9 @@ int conv_plan_build(const ConvDesc& d, ConvPlan* plan) {
   static std::once_flag once;
   static cudaError_t attr_err = cudaSuccess;
   std::call_once(once, [] {
-    attr_err = cudaFuncSetAttribute(conv_umma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                    222 * 1024);
+    for (int i = 0; i < 16 && attr_err == cudaSuccess; ++i)
+      attr_err = cudaFuncSetAttribute((const void*)conv_kernel_variant(i >> 2, (i >> 1) & 1, i & 1),
+                                      cudaFuncAttributeMaxDynamicSharedMemorySize, 222 * 1024);
   });
   if (attr_err != cudaSuccess) {
     set_last_error("cudaFuncSetAttribute(conv_umma_kernel): %s", cudaGetErrorString(attr_err));
@@ -380,7 +396,8 @@ int conv_plan_launch(const ConvPlan& plan, cudaStream_t stream) {
   attr[0].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = attr;
   cfg.numAttrs = plan.args.pdl ? 1 : 0;
-  cudaError_t e = cudaLaunchKernelEx(&cfg, conv_umma_kernel, plan.maps, plan.args);
+  cudaError_t e = cudaLaunchKernelEx(&cfg, conv_kernel_variant(plan.args.silu, plan.args.halo, plan.args.mode),
+                                     plan.maps, plan.args);
   g_launch_count.fetch_add(1, std::memory_order_relaxed);
   if (e != cudaSuccess) {
     set_last_error("conv_umma_kernel launch: %s", cudaGetErrorString(e));

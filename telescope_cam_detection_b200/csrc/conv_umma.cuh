@@ -164,7 +164,7 @@ __device__ __forceinline__ void conv_add_resid(const ConvArgs& p, float (&v)[NC]
   }
 }
 
-template <int NC, int OFF>
+template <int NC, int OFF, int ACT, int MODE>
 __device__ __forceinline__ void conv_finish_cols(const ConvArgs& p, const uint32_t (&r)[32], int c0,
                                                  const float* bias_g, int row, bool valid,
                                                  const ConvTile& t, int y, int x, uint8_t* stage_base) {
@@ -178,18 +178,18 @@ __device__ __forceinline__ void conv_finish_cols(const ConvArgs& p, const uint32
     v[4 * j + 2] = __uint_as_float(r[OFF + 4 * j + 2]) + b.z;
     v[4 * j + 3] = __uint_as_float(r[OFF + 4 * j + 3]) + b.w;
   }
-  if (p.mode == 0 && p.resid != nullptr && p.resid_pre && valid) conv_add_resid<NC>(p, v, c0, t, y, x);
-  if (p.silu == 1) {
+  if (MODE == 0 && p.resid != nullptr && p.resid_pre && valid) conv_add_resid<NC>(p, v, c0, t, y, x);
+  if (ACT == 1) {
 #pragma unroll
     for (int j = 0; j < NC; ++j) v[j] = silu_f(v[j]);
-  } else if (p.silu == 2) {
+  } else if (ACT == 2) {
 #pragma unroll
     for (int j = 0; j < NC; ++j) v[j] = fmaxf(v[j], 0.f);
-  } else if (p.silu == 3) {
+  } else if (ACT == 3) {
 #pragma unroll
     for (int j = 0; j < NC; ++j) v[j] = 0.5f * v[j] * (1.0f + erff(v[j] * 0.70710678118654752f));
   }
-  if (p.mode == 0) {
+  if (MODE == 0) {
     if (p.resid != nullptr && !p.resid_pre && valid) conv_add_resid<NC>(p, v, c0, t, y, x);
     const int chunk = c0 / p.out_chunk;
     const int row_bytes = p.out_chunk * 2;
@@ -247,8 +247,12 @@ __device__ __forceinline__ void conv_flush_rows(const ConvArgs& p, const ConvTil
   }
 }
 
+// Specialised on (activation, halo form, f32-row output): one generic kernel was ~7 800 SASS instructions and its
+// warps spent 10 % of their samples waiting for instruction fetch (ncu warp sampling, stall_no_inst).
+template <int ACT, bool HALO, bool F32>
 __global__ void __launch_bounds__(kConvThreads)
 conv_umma_kernel(const __grid_constant__ ConvMaps maps, const __grid_constant__ ConvArgs p) {
+  constexpr int kMode = F32 ? 1 : 0;
   extern __shared__ uint8_t smem_raw[];
   __shared__ uint64_t full_bar[kConvMaxStages];
   __shared__ uint64_t empty_bar[kConvMaxStages];
@@ -263,7 +267,7 @@ conv_umma_kernel(const __grid_constant__ ConvMaps maps, const __grid_constant__ 
                                              ~(uintptr_t)1023);
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
-  const int a_bytes = p.halo ? 0 : 128 * p.ck * 2;
+  const int a_bytes = HALO ? 0 : 128 * p.ck * 2;
   const int b_bytes = p.BN * p.ck * 2;
   const int stage_bytes = a_bytes + b_bytes * p.tps;
   const int its_per_tile = p.taps * p.kchunks;
@@ -272,7 +276,7 @@ conv_umma_kernel(const __grid_constant__ ConvMaps maps, const __grid_constant__ 
   if (warp == 0 && lane == 0) {
     prefetch_tmap(&maps.a[0]);
     prefetch_tmap(&maps.b);
-    if (p.mode == 0) prefetch_tmap(&maps.o);
+    if (kMode == 0) prefetch_tmap(&maps.o);
     for (int s = 0; s < p.stages; ++s) {
       mbar_init(&full_bar[s], 1);
       mbar_init(&empty_bar[s], 1);
@@ -305,7 +309,7 @@ conv_umma_kernel(const __grid_constant__ ConvMaps maps, const __grid_constant__ 
       bool first = true;
       RingCursor ring{0, 0u, p.stages};
       int jt = 0;
-      if (p.halo) {
+      if (HALO) {
         const uint32_t a_tx = (uint32_t)((p.TW + 2) * (p.TH + 2) * p.ck * 2);
         const uint32_t b_tx = (uint32_t)(b_bytes * p.tps);
         RingCursor aring{0, 0u, p.a_stages};
@@ -390,7 +394,7 @@ conv_umma_kernel(const __grid_constant__ ConvMaps maps, const __grid_constant__ 
           tc_fence_after();
         }
         const uint32_t d_tmem = tmem_base + (uint32_t)(acc * p.acc_stride + g * p.BN);
-        if (p.halo) {
+        if (HALO) {
           const int rowb = p.ck * 2;
           const uint32_t sbo_a = (uint32_t)(p.halo_w * rowb);
           const bool wait_b = !p.b_resident || j == 0;
@@ -494,7 +498,7 @@ conv_umma_kernel(const __grid_constant__ ConvMaps maps, const __grid_constant__ 
       if (j > 0) {
         // staging reuse: the previous round's TMA stores have finished READING it (mode 0) / every warp has
         // finished flushing its rows (mode 1)
-        if (p.mode == 0 && warp == 2 && lane == 0) tma_store_wait_read();
+        if (kMode == 0 && warp == 2 && lane == 0) tma_store_wait_read();
         asm volatile("bar.sync 1, %0;" ::"n"(32 * kConvEpiWarps) : "memory");
       }
       if (warp == 2 && lane == 0) conv_trace_tile(p, 96, j);   // staging is free
@@ -515,8 +519,8 @@ conv_umma_kernel(const __grid_constant__ ConvMaps maps, const __grid_constant__ 
       };
       int fg = 0, fsl = 0;            // (tile, slab) of the next finish() -- finish() runs in slab order
       auto finish = [&](const uint32_t (&r)[32]) {
-        if (p.BN - 32 * fsl >= 32) conv_finish_cols<32, 0>(p, r, 32 * fsl, bias_src, row, valid, c, y, x, stg);
-        else conv_finish_cols<16, 0>(p, r, 32 * fsl, bias_src, row, valid, c, y, x, stg);
+        if (p.BN - 32 * fsl >= 32) conv_finish_cols<32, 0, ACT, kMode>(p, r, 32 * fsl, bias_src, row, valid, c, y, x, stg);
+        else conv_finish_cols<16, 0, ACT, kMode>(p, r, 32 * fsl, bias_src, row, valid, c, y, x, stg);
         if (++fsl == nslab) {  // next tile of the round (its slab is already on its way from TMEM)
           fsl = 0;
           if (++fg < n_g) set_tile(fg);
@@ -533,7 +537,7 @@ conv_umma_kernel(const __grid_constant__ ConvMaps maps, const __grid_constant__ 
           finish(rb);
         }
       }
-      if (p.mode == 1) {
+      if (kMode == 1) {
         asm volatile("bar.sync 1, %0;" ::"n"(32 * kConvEpiWarps) : "memory");
         conv_flush_rows(p, c, q, half, lane, staging, valid, y, x);
       } else {
@@ -555,7 +559,7 @@ conv_umma_kernel(const __grid_constant__ ConvMaps maps, const __grid_constant__ 
     }
     if (warp == 2 && lane == 0) {
       conv_trace(p, 8);
-      if (p.mode == 0) tma_store_wait_read();
+      if (kMode == 0) tma_store_wait_read();
       conv_trace(p, 9);
     }
   }
