@@ -180,3 +180,39 @@ def test_row_sparse_upload_is_exact():
         assert np.array_equal(r720[0], e.detect_batch(_dev_frames(f720))[0])
     finally:
         e.close()
+
+
+def test_result_table_on_the_device_matches_the_host_rows():
+    """tcd_detector_result_device: the slot's [B,max_out,7] table + counts in device memory (what the N>1 host
+    forwards to the serving rank without a host round trip) equals the rows wait() returns, for every slot."""
+    import torch
+    from telescope_cam_detection_b200 import stream_shard as ss
+    from telescope_cam_detection_b200.engine import DetectorEngine
+
+    B, MAXO = 2, 300
+    e = DetectorEngine(oracle_blob(0), input_size=(640, 640), max_batch=B, max_out=MAXO, pre_mode=1)
+    try:
+        ring = ss.RingGather(1, 2, B * MAXO * 7 + B, "cuda")
+        for slot in range(min(3, e.num_slots)):
+            frames = [structured_frame(60 + slot), noise_frame(70 + slot)]
+            e.submit(slot, frames)
+            rows = e.wait(slot)
+            dp, cp = e.result_device(slot)
+            tab = torch.as_tensor(ss.DeviceView(dp, (B, MAXO, 7), "<f4"), device="cuda")
+            cnt = torch.as_tensor(ss.DeviceView(cp, (B,), "<i4"), device="cuda")
+            torch.cuda.synchronize()
+            n = cnt.cpu().numpy()
+            for b in range(B):
+                assert n[b] == rows[b].shape[0] and n[b] > 0
+                assert np.array_equal(tab[b, : n[b]].cpu().numpy(), rows[b])
+            # and through the ring the bench uses (world 1: collect == copy)
+            half, i = ring.slot(slot)
+            ring.buf[half][i, : B * MAXO * 7].copy_(tab.reshape(-1))
+            ring.buf[half][i, B * MAXO * 7:].copy_(cnt.view(torch.float32))
+            out = ring.collect(half)
+            torch.cuda.synchronize()
+            got = out[0, i, : B * MAXO * 7].reshape(B, MAXO, 7).cpu().numpy()
+            assert np.array_equal(got[0, : n[0]], rows[0])
+            assert np.array_equal(out[0, i, B * MAXO * 7:].view(torch.int32).cpu().numpy(), n)
+    finally:
+        e.close()
