@@ -1,4 +1,8 @@
 set -x
-T=s18d
-timeout 900 python -m pytest tests/test_gpu_yolox.py -x -q > gpurun_out/${T}_pytest.log 2>&1; echo rc=$?
-tail -15 gpurun_out/${T}_pytest.log
+T=s18e
+timeout 1500 python -m pytest tests -x -q -m gpu > gpurun_out/${T}_pytest.log 2>&1; echo rc=$?
+tail -4 gpurun_out/${T}_pytest.log
+timeout 900 python bench.py > gpurun_out/${T}_bench.json 2> gpurun_out/${T}_bench.err; echo rc=$?
+timeout 600 python bench.py --impl reference > gpurun_out/${T}_bench_ref.json 2> gpurun_out/${T}_bench_ref.err; echo rc=$?
+timeout 300 python -c "import __graft_entry__ as g; g.smoke(); print('smoke ok')" > gpurun_out/${T}_smoke.log 2>&1; echo rc=$?
+tail -c 300 gpurun_out/${T}_bench*.err gpurun_out/${T}_smoke.log
