@@ -1,8 +1,5 @@
 set -x
-T=s18e
-timeout 1500 python -m pytest tests -x -q -m gpu > gpurun_out/${T}_pytest.log 2>&1; echo rc=$?
-tail -4 gpurun_out/${T}_pytest.log
-timeout 900 python bench.py > gpurun_out/${T}_bench.json 2> gpurun_out/${T}_bench.err; echo rc=$?
-timeout 600 python bench.py --impl reference > gpurun_out/${T}_bench_ref.json 2> gpurun_out/${T}_bench_ref.err; echo rc=$?
-timeout 300 python -c "import __graft_entry__ as g; g.smoke(); print('smoke ok')" > gpurun_out/${T}_smoke.log 2>&1; echo rc=$?
-tail -c 300 gpurun_out/${T}_bench*.err gpurun_out/${T}_smoke.log
+T=r01f
+B="python bench.py --steps 2 --warmup 1 --no-cpu-baseline --no-aux --rtdetr-batch 0 --profile-iters 1 --latency-iters 0"
+timeout 300 $B > gpurun_out/${T}_prof_cmd.json 2> gpurun_out/${T}_prof_cmd.err; echo rc=$?
+TCD_NO_GRAPH=1 timeout 600 ncu --metrics gpu__time_duration.sum,dram__bytes_read.sum,dram__bytes_write.sum,sm__pipe_tensor_cycles_active.avg.pct_of_peak_sustained_active --clock-control none -c 400 --csv --log-file gpurun_out/${T}_launches_ncu.csv $B > gpurun_out/${T}_ncu1.log 2>&1; echo rc=$?
