@@ -141,109 +141,150 @@ int mask_rows_launch(const void* x, const float* mask, void* y, int N, int T, in
 }
 
 // ------------------------------------------------------------------ multi-head attention
-// grid (ceil(Tq/128), heads, N); one query per thread, the head's K and V (Tk x 32 bf16 each) staged
-// in shared memory, streaming (online) softmax in fp32.  Tk is a few hundred here (400 AIFI tokens,
-// 300 decoder queries), so the whole K/V head slice fits and every K/V row read is a broadcast.
+// Flash-style attention on the warp-level tensor-core path (mma.sync m16n8k16, bf16 in, fp32 accumulate): head
+// dim 32, a few hundred keys (400 AIFI tokens, 300 decoder queries), so the head's whole K (row-major) and V
+// (transposed) slices sit in shared memory.  grid (ceil(Tq/64), heads, N); each of the 4 warps owns 16 queries
+// and walks the keys 16 at a time: S = Q K^T (4 MMAs), online softmax on the accumulator fragments (row max /
+// sum across the 4 lanes of a quad), O += P V (4 MMAs) with P re-used straight from the S fragments.
+// (The first version was one query per thread on the CUDA cores: 0.245 ms per decoder layer at B = 32, then
+// 0.152 ms with fp32 staging; tcgen05 would want 128-query tiles, which 300 queries x 8 heads do not fill.)
+__device__ __forceinline__ void mma_bf16_16816(float (&d)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
+  asm volatile(
+      "mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+      : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
+      : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
+
+constexpr int kMhaKStride = 40;  // bf16 per staged K row (32 + 8 pad): conflict-free 32-bit fragment loads
+
 __global__ void __launch_bounds__(128)
 mha_kernel(const __nv_bfloat16* __restrict__ q, int ldq, int qoff, const __nv_bfloat16* __restrict__ k,
            int ldk, int koff, const __nv_bfloat16* __restrict__ v, int ldv, int voff,
            __nv_bfloat16* __restrict__ out, int ldo, int Tq, int Tk, float scale) {
-  // K / V head slices as fp32 in shared memory: every thread reads every row (a broadcast), so converting once at
-  // staging instead of once per thread per key halves the inner loop; keys are taken eight at a time so the
-  // running-max rescale of the 32 accumulators is paid once per eight keys (first version: 245 us per decoder
-  // self-attention at B = 32, ~240 instructions per key per thread)
-  extern __shared__ float4 mha_sm[];
-  float4* Ks = mha_sm;            // [Tk][8] float4 = 32 floats
-  float4* Vs = mha_sm + 8 * Tk;
+  extern __shared__ __align__(16) uint8_t mha_sm_raw[];
+  const int Tkp = (Tk + 15) & ~15;
+  const int vstride = Tkp + 8;                        // bf16 per transposed V row
+  __nv_bfloat16* Ks = reinterpret_cast<__nv_bfloat16*>(mha_sm_raw);   // [Tkp][40]
+  __nv_bfloat16* Vt = Ks + (size_t)Tkp * kMhaKStride;                 // [32][Tkp + 8]
   const int n = blockIdx.z, h = blockIdx.y;
   const __nv_bfloat16* kb = k + (size_t)n * Tk * ldk + koff + h * 32;
   const __nv_bfloat16* vb = v + (size_t)n * Tk * ldv + voff + h * 32;
-  for (int i = threadIdx.x; i < 4 * Tk; i += 128) {
+  for (int i = threadIdx.x; i < 4 * Tkp; i += 128) {
     const int t = i >> 2, c = i & 3;
-    float f[8];
-    bf16x8_to_f32(*reinterpret_cast<const uint4*>(kb + (size_t)t * ldk + c * 8), f);
-    Ks[8 * t + 2 * c] = make_float4(f[0], f[1], f[2], f[3]);
-    Ks[8 * t + 2 * c + 1] = make_float4(f[4], f[5], f[6], f[7]);
-    bf16x8_to_f32(*reinterpret_cast<const uint4*>(vb + (size_t)t * ldv + c * 8), f);
-    Vs[8 * t + 2 * c] = make_float4(f[0], f[1], f[2], f[3]);
-    Vs[8 * t + 2 * c + 1] = make_float4(f[4], f[5], f[6], f[7]);
+    uint4 kq = make_uint4(0u, 0u, 0u, 0u), vq = kq;
+    if (t < Tk) {
+      kq = *reinterpret_cast<const uint4*>(kb + (size_t)t * ldk + c * 8);
+      vq = *reinterpret_cast<const uint4*>(vb + (size_t)t * ldv + c * 8);
+    }
+    *reinterpret_cast<uint4*>(Ks + (size_t)t * kMhaKStride + c * 8) = kq;
+    const __nv_bfloat16* ve = reinterpret_cast<const __nv_bfloat16*>(&vq);
+#pragma unroll
+    for (int e = 0; e < 8; ++e) Vt[(size_t)(c * 8 + e) * vstride + t] = ve[e];
   }
   __syncthreads();
-  const int tq = blockIdx.x * 128 + threadIdx.x;
-  if (tq >= Tq) return;
-  float qf[32];
-  const __nv_bfloat16* qp = q + ((size_t)n * Tq + tq) * ldq + qoff + h * 32;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int g = lane >> 2, t4 = lane & 3;
+  const int q0 = blockIdx.x * 64 + warp * 16;
+  if (q0 >= Tq) return;
+  const int r_lo = q0 + g, r_hi = q0 + g + 8;
+  // Q fragments (A operand, row-major 16 x 16 per k-step)
+  uint32_t qa[2][4];
+  {
+    const __nv_bfloat16* qlo = q + ((size_t)n * Tq + (r_lo < Tq ? r_lo : 0)) * ldq + qoff + h * 32;
+    const __nv_bfloat16* qhi = q + ((size_t)n * Tq + (r_hi < Tq ? r_hi : 0)) * ldq + qoff + h * 32;
 #pragma unroll
-  for (int c = 0; c < 4; ++c) {
-    float t[8];
-    bf16x8_to_f32(*reinterpret_cast<const uint4*>(qp + c * 8), t);
-#pragma unroll
-    for (int e = 0; e < 8; ++e) qf[c * 8 + e] = t[e] * scale;
-  }
-  float acc[32];
-#pragma unroll
-  for (int e = 0; e < 32; ++e) acc[e] = 0.f;
-  float m = -INFINITY, l = 0.f;
-  for (int j0 = 0; j0 < Tk; j0 += 8) {
-    float sc[8];
-    float bm = -INFINITY;
-#pragma unroll
-    for (int jj = 0; jj < 8; ++jj) {
-      float s = -INFINITY;
-      if (j0 + jj < Tk) {
-        const float4* kr = Ks + 8 * (j0 + jj);
-        float s0 = 0.f, s1 = 0.f;   // two chains
-#pragma unroll
-        for (int c = 0; c < 8; c += 2) {
-          const float4 a4 = kr[c], b4 = kr[c + 1];
-          s0 = fmaf(qf[4 * c + 0], a4.x, s0); s0 = fmaf(qf[4 * c + 1], a4.y, s0);
-          s0 = fmaf(qf[4 * c + 2], a4.z, s0); s0 = fmaf(qf[4 * c + 3], a4.w, s0);
-          s1 = fmaf(qf[4 * c + 4], b4.x, s1); s1 = fmaf(qf[4 * c + 5], b4.y, s1);
-          s1 = fmaf(qf[4 * c + 6], b4.z, s1); s1 = fmaf(qf[4 * c + 7], b4.w, s1);
-        }
-        s = s0 + s1;
-      }
-      sc[jj] = s;
-      bm = fmaxf(bm, s);
+    for (int ks = 0; ks < 2; ++ks) {
+      qa[ks][0] = r_lo < Tq ? *reinterpret_cast<const uint32_t*>(qlo + ks * 16 + 2 * t4) : 0u;
+      qa[ks][1] = r_hi < Tq ? *reinterpret_cast<const uint32_t*>(qhi + ks * 16 + 2 * t4) : 0u;
+      qa[ks][2] = r_lo < Tq ? *reinterpret_cast<const uint32_t*>(qlo + ks * 16 + 2 * t4 + 8) : 0u;
+      qa[ks][3] = r_hi < Tq ? *reinterpret_cast<const uint32_t*>(qhi + ks * 16 + 2 * t4 + 8) : 0u;
     }
-    const float mn = fmaxf(m, bm);
-    const float corr = __expf(m - mn);
-    l *= corr;
-#pragma unroll
-    for (int e = 0; e < 32; ++e) acc[e] *= corr;
-#pragma unroll
-    for (int jj = 0; jj < 8; ++jj) {
-      if (j0 + jj < Tk) {
-        const float p = __expf(sc[jj] - mn);
-        l += p;
-        const float4* vr = Vs + 8 * (j0 + jj);
-#pragma unroll
-        for (int c = 0; c < 8; ++c) {
-          const float4 t4 = vr[c];
-          acc[4 * c + 0] = fmaf(p, t4.x, acc[4 * c + 0]);
-          acc[4 * c + 1] = fmaf(p, t4.y, acc[4 * c + 1]);
-          acc[4 * c + 2] = fmaf(p, t4.z, acc[4 * c + 2]);
-          acc[4 * c + 3] = fmaf(p, t4.w, acc[4 * c + 3]);
-        }
-      }
-    }
-    m = mn;
   }
-  const float inv = 1.0f / l;
-  __nv_bfloat16* op = out + ((size_t)n * Tq + tq) * ldo + h * 32;
+  float o[4][4];
 #pragma unroll
-  for (int c = 0; c < 4; ++c) {
-    float t[8];
+  for (int nb = 0; nb < 4; ++nb)
 #pragma unroll
-    for (int e = 0; e < 8; ++e) t[e] = acc[c * 8 + e] * inv;
-    *reinterpret_cast<uint4*>(op + c * 8) = f32_to_bf16x8(t);
+    for (int e = 0; e < 4; ++e) o[nb][e] = 0.f;
+  float m_lo = -INFINITY, m_hi = -INFINITY, l_lo = 0.f, l_hi = 0.f;   // l: this lane's partial row sums
+  for (int key0 = 0; key0 < Tkp; key0 += 16) {
+    float sc[2][4];
+#pragma unroll
+    for (int j = 0; j < 2; ++j) {
+#pragma unroll
+      for (int e = 0; e < 4; ++e) sc[j][e] = 0.f;
+      const __nv_bfloat16* kr = Ks + (size_t)(key0 + j * 8 + g) * kMhaKStride + 2 * t4;
+#pragma unroll
+      for (int ks = 0; ks < 2; ++ks)
+        mma_bf16_16816(sc[j], qa[ks], *reinterpret_cast<const uint32_t*>(kr + ks * 16),
+                       *reinterpret_cast<const uint32_t*>(kr + ks * 16 + 8));
+    }
+#pragma unroll
+    for (int j = 0; j < 2; ++j)
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        const int key = key0 + j * 8 + 2 * t4 + (e & 1);
+        sc[j][e] = key < Tk ? sc[j][e] * scale : -INFINITY;
+      }
+    float mx_lo = fmaxf(fmaxf(sc[0][0], sc[0][1]), fmaxf(sc[1][0], sc[1][1]));
+    float mx_hi = fmaxf(fmaxf(sc[0][2], sc[0][3]), fmaxf(sc[1][2], sc[1][3]));
+#pragma unroll
+    for (int off = 1; off <= 2; off <<= 1) {
+      mx_lo = fmaxf(mx_lo, __shfl_xor_sync(0xffffffffu, mx_lo, off));
+      mx_hi = fmaxf(mx_hi, __shfl_xor_sync(0xffffffffu, mx_hi, off));
+    }
+    const float mn_lo = fmaxf(m_lo, mx_lo), mn_hi = fmaxf(m_hi, mx_hi);
+    const float c_lo = __expf(m_lo - mn_lo), c_hi = __expf(m_hi - mn_hi);
+    m_lo = mn_lo;
+    m_hi = mn_hi;
+    float p[2][4];
+#pragma unroll
+    for (int j = 0; j < 2; ++j) {
+      p[j][0] = __expf(sc[j][0] - mn_lo);
+      p[j][1] = __expf(sc[j][1] - mn_lo);
+      p[j][2] = __expf(sc[j][2] - mn_hi);
+      p[j][3] = __expf(sc[j][3] - mn_hi);
+    }
+    l_lo = l_lo * c_lo + ((p[0][0] + p[0][1]) + (p[1][0] + p[1][1]));
+    l_hi = l_hi * c_hi + ((p[0][2] + p[0][3]) + (p[1][2] + p[1][3]));
+#pragma unroll
+    for (int nb = 0; nb < 4; ++nb) {
+      o[nb][0] *= c_lo; o[nb][1] *= c_lo;
+      o[nb][2] *= c_hi; o[nb][3] *= c_hi;
+    }
+    // the S accumulator fragments of two 8-key blocks ARE the A fragment of the 16-key P V step
+    uint32_t pa[4];
+    pa[0] = pack_bf16x2(p[0][0], p[0][1]);
+    pa[1] = pack_bf16x2(p[0][2], p[0][3]);
+    pa[2] = pack_bf16x2(p[1][0], p[1][1]);
+    pa[3] = pack_bf16x2(p[1][2], p[1][3]);
+#pragma unroll
+    for (int nb = 0; nb < 4; ++nb) {
+      const __nv_bfloat16* vr = Vt + (size_t)(nb * 8 + g) * vstride + key0 + 2 * t4;
+      mma_bf16_16816(o[nb], pa, *reinterpret_cast<const uint32_t*>(vr), *reinterpret_cast<const uint32_t*>(vr + 8));
+    }
+  }
+#pragma unroll
+  for (int off = 1; off <= 2; off <<= 1) {
+    l_lo += __shfl_xor_sync(0xffffffffu, l_lo, off);
+    l_hi += __shfl_xor_sync(0xffffffffu, l_hi, off);
+  }
+  const float i_lo = 1.0f / l_lo, i_hi = 1.0f / l_hi;
+#pragma unroll
+  for (int nb = 0; nb < 4; ++nb) {
+    if (r_lo < Tq)
+      *reinterpret_cast<uint32_t*>(out + ((size_t)n * Tq + r_lo) * ldo + h * 32 + nb * 8 + 2 * t4) =
+          pack_bf16x2(o[nb][0] * i_lo, o[nb][1] * i_lo);
+    if (r_hi < Tq)
+      *reinterpret_cast<uint32_t*>(out + ((size_t)n * Tq + r_hi) * ldo + h * 32 + nb * 8 + 2 * t4) =
+          pack_bf16x2(o[nb][2] * i_hi, o[nb][3] * i_hi);
   }
 }
 
 int mha_launch(const void* q, int ldq, int qoff, const void* k, int ldk, int koff, const void* v, int ldv,
                int voff, void* out, int ldo, int N, int Tq, int Tk, int heads, float scale,
                cudaStream_t st) {
-  const size_t smem = (size_t)16 * Tk * sizeof(float4);
+  const int Tkp = (Tk + 15) & ~15;
+  const size_t smem = ((size_t)Tkp * kMhaKStride + (size_t)32 * (Tkp + 8)) * 2;
   TCD_REQUIRE(smem <= 200 * 1024, "mha: %d keys do not fit shared memory", Tk);
   TCD_REQUIRE(ldq % 8 == 0 && ldk % 8 == 0 && ldv % 8 == 0 && ldo % 8 == 0 && qoff % 8 == 0 && koff % 8 == 0 &&
                   voff % 8 == 0, "mha: leading dims / offsets must be multiples of 8");
@@ -252,7 +293,7 @@ int mha_launch(const void* q, int ldq, int qoff, const void* k, int ldk, int kof
     TCD_CUDA_OK(cudaFuncSetAttribute(mha_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     attr_set = smem;
   }
-  mha_kernel<<<dim3(cdiv(Tq, 128), heads, N), 128, smem, st>>>(
+  mha_kernel<<<dim3(cdiv(Tq, 64), heads, N), 128, smem, st>>>(
       (const __nv_bfloat16*)q, ldq, qoff, (const __nv_bfloat16*)k, ldk, koff, (const __nv_bfloat16*)v, ldv,
       voff, (__nv_bfloat16*)out, ldo, Tq, Tk, scale);
   TFM_LAUNCH_OK("mha");

@@ -1,5 +1,7 @@
 set -x
-T=r01f
-B="python bench.py --steps 2 --warmup 1 --no-cpu-baseline --no-aux --rtdetr-batch 0 --profile-iters 1 --latency-iters 0"
-timeout 300 $B > gpurun_out/${T}_prof_cmd.json 2> gpurun_out/${T}_prof_cmd.err; echo rc=$?
-TCD_NO_GRAPH=1 timeout 600 ncu --metrics gpu__time_duration.sum,dram__bytes_read.sum,dram__bytes_write.sum,sm__pipe_tensor_cycles_active.avg.pct_of_peak_sustained_active --clock-control none -c 400 --csv --log-file gpurun_out/${T}_launches_ncu.csv $B > gpurun_out/${T}_ncu1.log 2>&1; echo rc=$?
+T=s18h
+timeout 1200 python -m pytest tests/test_gpu_rtdetr_kernels.py tests/test_gpu_rtdetr.py -x -q > gpurun_out/${T}_pytest.log 2>&1; echo rc=$?
+tail -12 gpurun_out/${T}_pytest.log
+B="python bench.py --steps 20 --warmup 3 --no-cpu-baseline --latency-iters 0 --profile-iters 1"
+TCD_RTDETR_DUMP=gpurun_out/${T}_rtdetr_ops.json timeout 600 $B > gpurun_out/${T}_bench.json 2> gpurun_out/${T}_bench.err; echo rc=$?
+tail -c 300 gpurun_out/${T}_bench*.err
