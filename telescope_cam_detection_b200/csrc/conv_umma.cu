@@ -4,6 +4,7 @@
 #include "conv_umma.cuh"
 
 #include <atomic>
+#include <algorithm>
 #include <mutex>
 #include <stdlib.h>
 #include <string.h>
@@ -230,6 +231,15 @@ int conv_plan_build(const ConvDesc& d, ConvPlan* plan) {
   a.BN = BN;
   a.n_tiles_n = d.cout_pad / BN;
   a.total_tiles = m_tiles * a.n_tiles_n;
+  {
+    auto magic = [](int dv) -> unsigned int { return dv <= 1 ? 0u : (unsigned int)((0x100000000ULL + dv - 1) / (unsigned)dv); };
+    a.magic_n = magic(a.n_tiles_n);
+    a.magic_img = magic(a.tiles_per_img);
+    a.magic_w = magic(a.tiles_w);
+    const unsigned long long dmax = (unsigned long long)std::max(a.n_tiles_n, std::max(a.tiles_per_img, a.tiles_w));
+    TCD_REQUIRE((unsigned long long)a.total_tiles * dmax < 0x100000000ULL, "conv: %d tiles overflow the multiply-high divide",
+                a.total_tiles);
+  }
   a.cin_off = d.x_coff;
   a.cout_off = d.y_coff;
   a.mode = mode;

@@ -47,6 +47,9 @@ struct ConvArgs {
   int cin_off, cout_off;
   int mode;  // 0: bf16 NHWC via TMA store; 1: f32 rows (head predictions)
   int silu, out_chunk, stages, tmem_cols, n_valid;
+  // ceil(2^32 / d) for d = n_tiles_n, tiles_per_img, tiles_w: t / d == __umulhi(t, magic) while t * d < 2^32
+  // (checked by the planner) -- an integer divide is ~40 instructions through the MUFU pipe the SiLUs keep busy
+  unsigned int magic_n, magic_img, magic_w;
   int n_tiles_n, total_tiles;   // persistent tile loop: tile t -> (m = t / n_tiles_n, n = t % n_tiles_n)
   int acc_stride;               // TMEM columns between the two accumulator buffers
   int staging_off;              // byte offset of the epilogue staging area inside dynamic smem
@@ -129,11 +132,11 @@ struct ConvTile {
 };
 __device__ __forceinline__ ConvTile conv_tile(const ConvArgs& p, int t) {
   ConvTile c;
-  const int m_tile = t / p.n_tiles_n;
+  const int m_tile = p.n_tiles_n == 1 ? t : (int)__umulhi((unsigned)t, p.magic_n);
   c.n_tile = t - m_tile * p.n_tiles_n;
-  c.n_img = m_tile / p.tiles_per_img;
+  c.n_img = p.tiles_per_img == 1 ? m_tile : (int)__umulhi((unsigned)m_tile, p.magic_img);
   const int rem = m_tile - c.n_img * p.tiles_per_img;
-  const int ty = rem / p.tiles_w;
+  const int ty = p.tiles_w == 1 ? rem : (int)__umulhi((unsigned)rem, p.magic_w);
   c.y0 = ty * p.TH;
   c.x0 = (rem - ty * p.tiles_w) * p.TW;
   return c;

@@ -1,7 +1,8 @@
 set -x
-T=s18h
-timeout 1200 python -m pytest tests/test_gpu_rtdetr_kernels.py tests/test_gpu_rtdetr.py -x -q > gpurun_out/${T}_pytest.log 2>&1; echo rc=$?
-tail -12 gpurun_out/${T}_pytest.log
-B="python bench.py --steps 20 --warmup 3 --no-cpu-baseline --latency-iters 0 --profile-iters 1"
-TCD_RTDETR_DUMP=gpurun_out/${T}_rtdetr_ops.json timeout 600 $B > gpurun_out/${T}_bench.json 2> gpurun_out/${T}_bench.err; echo rc=$?
+T=s18j
+timeout 1500 python -m pytest tests -x -q -m gpu > gpurun_out/${T}_pytest.log 2>&1; echo rc=$?
+tail -4 gpurun_out/${T}_pytest.log
+B="python bench.py --steps 300 --warmup 10 --no-cpu-baseline --no-aux --latency-iters 0"
+timeout 300 $B --dump-ops gpurun_out/${T}_ops.json > gpurun_out/${T}_bench.json 2> gpurun_out/${T}_bench.err; echo rc=$?
+timeout 300 $B > gpurun_out/${T}_bench_b.json 2> gpurun_out/${T}_bench_b.err; echo rc=$?
 tail -c 300 gpurun_out/${T}_bench*.err
