@@ -303,7 +303,7 @@ int conv_plan_build(const ConvDesc& d, ConvPlan* plan) {
   int stages = 0, halo_bytes = 0;
   long its_per_cta = 0;
   for (int attempt = 0; attempt < 2; ++attempt) {
-    const int budget = (two_per_sm ? g_smem_kb / share_div : g_smem_kb) * 1024 - 2048;
+    const int budget = (two_per_sm ? g_smem_kb / share_div : g_smem_kb) * 1024 - 6656;  // static smem (barriers + 8 KiB bias) and the 1 KiB the SM reserves per CTA: two CTAs must fit 228 KiB
     const long tiles_per_cta = cdiv(a.total_tiles, n_sm * (two_per_sm ? ctas_per_sm_max : 1));
     its_per_cta = (long)its_per_tile * tiles_per_cta;
     halo_bytes = 0;
@@ -332,7 +332,8 @@ int conv_plan_build(const ConvDesc& d, ConvPlan* plan) {
   a.b_resident = (a.halo && a.n_tiles_n == 1 && its_per_tile <= stages && env_int("TCD_CONV_BRES", 1, 0)) ? 1 : 0;
   a.a_ring_off = stages * stage_bytes;
   a.staging_off = a.a_ring_off + halo_bytes;
-  a.bias_n = d.cout_pad <= kConvMaxBias ? d.cout_pad : 0;
+  TCD_REQUIRE(d.cout_pad <= kConvMaxBias, "conv: cout_pad %d exceeds the %d staged bias entries", d.cout_pad, kConvMaxBias);
+  a.bias_n = d.cout_pad;
   plan->smem_bytes = stages * stage_bytes + halo_bytes + staging + 1024;
   const int ctas = n_sm * (two_per_sm ? ctas_per_sm_max : 1);
   plan->grid = dim3((unsigned)(a.total_tiles < ctas ? a.total_tiles : ctas), 1, 1);
@@ -385,7 +386,7 @@ int conv_plan_build(const ConvDesc& d, ConvPlan* plan) {
   std::call_once(once, [] {
     for (int i = 0; i < 16 && attr_err == cudaSuccess; ++i)
       attr_err = cudaFuncSetAttribute((const void*)conv_kernel_variant(i >> 2, (i >> 1) & 1, i & 1),
-                                      cudaFuncAttributeMaxDynamicSharedMemorySize, 222 * 1024);
+                                      cudaFuncAttributeMaxDynamicSharedMemorySize, 218 * 1024);
   });
   if (attr_err != cudaSuccess) {
     set_last_error("cudaFuncSetAttribute(conv_umma_kernel): %s", cudaGetErrorString(attr_err));

@@ -33,7 +33,7 @@ constexpr int kConvMaxStages = 8;
 constexpr int kConvThreads = 192;   // warp 0 TMA producer, warp 1 MMA issuer, warps 2..5 epilogue
 constexpr int kConvEpiWarps = 4;
 constexpr int kConvMaxAStages = 4;
-constexpr int kConvMaxBias = 512;
+constexpr int kConvMaxBias = 2048;  // every layer's bias is staged in shared memory (planner refuses wider layers)
 
 struct ConvMaps {
   CUtensorMap a[4];
@@ -468,7 +468,7 @@ conv_umma_kernel(const __grid_constant__ ConvMaps maps, const __grid_constant__ 
     const int lx = row - ly * p.TW;
     uint8_t* staging = smem + p.staging_off;
     if (p.pdl && p.resid != nullptr) pdl_wait();
-    const float* bias_src = p.bias_n ? s_bias : p.bias;
+    const float* bias_src = s_bias;   // always shared: a global/shared select makes every bias read a generic load
     const int nslab = (p.BN + 31) >> 5;
     // Accumulator rounds: p.group consecutive tiles of this CTA share one round (group * BN <= 128 columns),
     // so the fixed per-round chain (barrier waits, proxy fence, TMA-store issue, staging hand-over: ~2 000
