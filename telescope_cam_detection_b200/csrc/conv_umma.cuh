@@ -194,9 +194,11 @@ __device__ __forceinline__ void conv_finish_cols(const ConvArgs& p, const uint32
   }
   if (MODE == 0) {
     if (p.resid != nullptr && !p.resid_pre && valid) conv_add_resid<NC>(p, v, c0, t, y, x);
-    const int chunk = c0 / p.out_chunk;
+    // out_chunk is 32 or 64: shifts, not integer divides (which go through the MUFU pipe)
+    const int cs = p.out_chunk == 64 ? 6 : 5;
+    const int chunk = c0 >> cs;
     const int row_bytes = p.out_chunk * 2;
-    const int u0 = (c0 % p.out_chunk) >> 3;
+    const int u0 = (c0 & (p.out_chunk - 1)) >> 3;
     const int sw = (p.out_chunk == 64) ? (row & 7) : ((row >> 1) & 3);
     uint8_t* rowp = stage_base + (size_t)chunk * 128 * row_bytes + (size_t)row * row_bytes;
 #pragma unroll
@@ -548,7 +550,7 @@ conv_umma_kernel(const __grid_constant__ ConvMaps maps, const __grid_constant__ 
         asm volatile("bar.sync 1, %0;" ::"n"(32 * kConvEpiWarps) : "memory");
         if (warp == 2 && lane == 0) conv_trace_tile(p, 112, j);  // every warp has staged its slabs
         if (warp == 2 && lane == 0) {
-          const int nchunks = p.BN / p.out_chunk;
+          const int nchunks = p.BN >> (p.out_chunk == 64 ? 6 : 5);
           for (int g = 0; g < n_g; ++g) {
             const ConvTile cg = conv_tile(p, (int)blockIdx.x + (i0 + g) * (int)gridDim.x);
             for (int ch = 0; ch < nchunks; ++ch)

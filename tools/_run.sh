@@ -1,5 +1,5 @@
 set -x
-T=s18l
+T=s18m
 timeout 1500 python -m pytest tests -x -q -m gpu > gpurun_out/${T}_pytest.log 2>&1; echo rc=$?
 tail -4 gpurun_out/${T}_pytest.log
 B="python bench.py --steps 300 --warmup 10 --no-cpu-baseline --no-aux --latency-iters 0"
