@@ -1,8 +1,6 @@
 set -x
-T=s18m
-timeout 1500 python -m pytest tests -x -q -m gpu > gpurun_out/${T}_pytest.log 2>&1; echo rc=$?
-tail -4 gpurun_out/${T}_pytest.log
-B="python bench.py --steps 300 --warmup 10 --no-cpu-baseline --no-aux --latency-iters 0"
-timeout 300 $B --dump-ops gpurun_out/${T}_ops.json > gpurun_out/${T}_bench.json 2> gpurun_out/${T}_bench.err; echo rc=$?
-timeout 300 $B > gpurun_out/${T}_bench_b.json 2> gpurun_out/${T}_bench_b.err; echo rc=$?
-tail -c 300 gpurun_out/${T}_bench*.err
+T=s18o
+timeout 900 python bench.py > gpurun_out/${T}_bench.json 2> gpurun_out/${T}_bench.err; echo rc=$?
+timeout 600 python bench.py --impl reference > gpurun_out/${T}_bench_ref.json 2> gpurun_out/${T}_bench_ref.err; echo rc=$?
+timeout 300 python -c "import __graft_entry__ as g; g.smoke(); print('smoke ok')" > gpurun_out/${T}_smoke.log 2>&1; echo rc=$?
+tail -c 300 gpurun_out/${T}_bench*.err gpurun_out/${T}_smoke.log
