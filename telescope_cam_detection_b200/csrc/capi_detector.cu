@@ -1,7 +1,10 @@
 // C ABI glue, part 2: the YOLOX detector handle (preprocess -> network -> decode/NMS).
-// kSlots independent pipeline slots (own stream, staging, activation arena, CUDA graph, pinned
-// result table) let the H2D copy of batch k+1 overlap the compute of batch k, and let the
-// short low-occupancy layers of one batch share the chip with another batch's.
+// The pipeline has ENGINES (own stream, activation arena, CUDA graph, NMS scratch) and, per engine, kLanes LANES
+// (own frame staging, pinned result table, device result table, events).  A pipeline slot of the C ABI is one
+// (engine, lane) pair: slot v -> engine v % n_engines, lane v / n_engines.  Engines let the short low-occupancy
+// layers of one batch share the chip with another batch's; the second lane keeps an engine's stream fed -- the
+// batch of lane 1 is already queued (and its frames uploaded, on the engine's upload stream) when lane 0's batch
+// finishes, so neither the host's turn-around nor the H2D copy leaves the stream idle.
 #include <atomic>
 #include <map>
 #include <stdlib.h>
@@ -20,26 +23,36 @@ extern std::atomic<uint64_t> g_h2d_bytes;
 
 namespace {
 
-constexpr int kSlots = 6;
+constexpr int kEngines = 8;
+constexpr int kLanes = 2;
+constexpr int kSlots = kEngines * kLanes;
 constexpr int kProfileReps = 8;
 
-struct Slot {
-  cudaStream_t stream = nullptr;
+struct Lane {                     // what ONE in-flight batch owns besides its engine
   uint8_t* staging = nullptr;     // device, max_batch frames of max_src bytes
-  size_t frame_cap = 0;
   PreFrame* pre_dev = nullptr;    // device [max_batch]
   PreFrame* pre_host = nullptr;   // pinned [max_batch]
+  float* out_pinned = nullptr;    // [max_batch,max_out,7]
+  int* cnt_pinned = nullptr;      // [max_batch]
+  float* tab_dets = nullptr;      // device copy of the result table (tcd_detector_result_device)
+  int* tab_counts = nullptr;
+  cudaEvent_t ev[6] = {};
+  cudaEvent_t ev_up = nullptr;    // frames of this lane's batch are in staging
+  int pending_B = 0;
+};
+
+struct Slot {                     // an engine
+  cudaStream_t stream = nullptr;
+  cudaStream_t up = nullptr;      // frame uploads: copy-engine work off the compute stream
+  size_t frame_cap = 0;
+  Lane lane[kLanes];
   std::map<int, YoloxPlan*> plans;
   std::map<int, cudaGraphExec_t> graphs;
   std::map<int, uint64_t> graph_kernels;  // kernel nodes per captured graph (launch accounting)
   // postprocess buffers (sized for max_batch)
   PostBuffers pb;
   float* thr_dev = nullptr;
-  float* out_pinned = nullptr;    // [max_batch,max_out,7]
-  int* cnt_pinned = nullptr;      // [max_batch]
   float* pred_in = nullptr;       // device scratch for tcd_postprocess [max_batch,A,5+C]
-  cudaEvent_t ev[6];
-  int pending_B = 0;
 };
 
 }  // namespace
@@ -48,7 +61,8 @@ struct tcd_detector {
   tcd_detector_cfg cfg;
   int device = 0;
   YoloxWeights wts;
-  Slot slot[kSlots];
+  Slot slot[kEngines];
+  int n_engines = 6;              // TCD_ENGINES; slots exposed = n_engines * kLanes
   float thr_host[2] = {0.25f, 0.45f};
   int n_anchors = 0, cap = 0;
   float last_ms[5] = {0, 0, 0, 0, 0};
@@ -59,10 +73,19 @@ static int slot_init(tcd_detector* d, Slot& s) {
   const tcd_detector_cfg& c = d->cfg;
   const int MB = c.max_batch;
   TCD_CUDA_OK(cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking));
+  TCD_CUDA_OK(cudaStreamCreateWithFlags(&s.up, cudaStreamNonBlocking));
   s.frame_cap = ((size_t)c.max_src_h * c.max_src_w * 3 + 255) & ~(size_t)255;
-  TCD_CUDA_OK(cudaMalloc((void**)&s.staging, s.frame_cap * MB));
-  TCD_CUDA_OK(cudaMalloc((void**)&s.pre_dev, sizeof(PreFrame) * MB));
-  TCD_CUDA_OK(cudaMallocHost((void**)&s.pre_host, sizeof(PreFrame) * MB));
+  for (Lane& l : s.lane) {
+    TCD_CUDA_OK(cudaMalloc((void**)&l.staging, s.frame_cap * MB));
+    TCD_CUDA_OK(cudaMalloc((void**)&l.pre_dev, sizeof(PreFrame) * MB));
+    TCD_CUDA_OK(cudaMallocHost((void**)&l.pre_host, sizeof(PreFrame) * MB));
+    TCD_CUDA_OK(cudaMalloc((void**)&l.tab_dets, sizeof(float) * 7 * c.max_out * MB));
+    TCD_CUDA_OK(cudaMalloc((void**)&l.tab_counts, sizeof(int) * MB));
+    TCD_CUDA_OK(cudaMallocHost((void**)&l.out_pinned, sizeof(float) * 7 * c.max_out * MB));
+    TCD_CUDA_OK(cudaMallocHost((void**)&l.cnt_pinned, sizeof(int) * MB));
+    for (auto& e : l.ev) TCD_CUDA_OK(cudaEventCreate(&e));
+    TCD_CUDA_OK(cudaEventCreateWithFlags(&l.ev_up, cudaEventDisableTiming));
+  }
   const int A = d->n_anchors, C = c.num_classes, cap = d->cap;
   PostBuffers& pb = s.pb;
   memset(&pb, 0, sizeof(pb));
@@ -80,10 +103,7 @@ static int slot_init(tcd_detector* d, Slot& s) {
   TCD_CUDA_OK(cudaMalloc((void**)&pb.out_counts, sizeof(int) * MB));
   TCD_CUDA_OK(cudaMalloc((void**)&pb.decoded, sizeof(float) * (size_t)MB * A * (5 + C)));
   TCD_CUDA_OK(cudaMalloc((void**)&s.pred_in, sizeof(float) * (size_t)MB * A * (5 + C)));
-  TCD_CUDA_OK(cudaMallocHost((void**)&s.out_pinned, sizeof(float) * 7 * c.max_out * MB));
-  TCD_CUDA_OK(cudaMallocHost((void**)&s.cnt_pinned, sizeof(int) * MB));
   TCD_CUDA_OK(cudaMemcpy(s.thr_dev, d->thr_host, 2 * sizeof(float), cudaMemcpyHostToDevice));
-  for (int i = 0; i < 6; ++i) TCD_CUDA_OK(cudaEventCreate(&s.ev[i]));
   return TCD_OK;
 }
 
@@ -91,13 +111,19 @@ static void slot_free(Slot& s) {
   for (auto& kv : s.graphs) cudaGraphExecDestroy(kv.second);
   for (auto& kv : s.plans) { kv.second->release(); delete kv.second; }
   PostBuffers& pb = s.pb;
-  void* ptrs[] = {s.staging, s.pre_dev, s.thr_dev, pb.cand_count, pb.cand, pb.cand_anchor, pb.srec,
+  void* ptrs[] = {s.thr_dev, pb.cand_count, pb.cand, pb.cand_anchor, pb.srec,
                   pb.sbox, pb.n_sorted, pb.mask, pb.out_dets, pb.out_counts, pb.decoded, s.pred_in};
   for (void* p : ptrs) if (p) cudaFree(p);
-  if (s.pre_host) cudaFreeHost(s.pre_host);
-  if (s.out_pinned) cudaFreeHost(s.out_pinned);
-  if (s.cnt_pinned) cudaFreeHost(s.cnt_pinned);
-  for (int i = 0; i < 6; ++i) if (s.ev[i]) cudaEventDestroy(s.ev[i]);
+  for (Lane& l : s.lane) {
+    void* dp[] = {l.staging, l.pre_dev, l.tab_dets, l.tab_counts};
+    for (void* p : dp) if (p) cudaFree(p);
+    if (l.pre_host) cudaFreeHost(l.pre_host);
+    if (l.out_pinned) cudaFreeHost(l.out_pinned);
+    if (l.cnt_pinned) cudaFreeHost(l.cnt_pinned);
+    for (auto& e : l.ev) if (e) cudaEventDestroy(e);
+    if (l.ev_up) cudaEventDestroy(l.ev_up);
+  }
+  if (s.up) cudaStreamDestroy(s.up);
   if (s.stream) cudaStreamDestroy(s.stream);
 }
 
@@ -170,12 +196,15 @@ static const bool g_sparse_upload = [] {
   return !(e && e[0] == '0');
 }();
 
-static int enqueue_input(tcd_detector* d, Slot& s, YoloxPlan* p, const uint8_t* const* frames,
+static int enqueue_input(tcd_detector* d, Slot& s, Lane& l, YoloxPlan* p, const uint8_t* const* frames,
                          const int32_t* h, const int32_t* w, const int64_t* row_stride, int B,
                          int on_device, bool launch_pre = true) {
   tcd_preproc_cfg pc = d->cfg.pre;
   pc.out_h = d->cfg.input_h;
   pc.out_w = d->cfg.input_w;
+  // host frames travel on the engine's upload stream: the lane's staging buffer is free (the host has waited for
+  // the lane's previous batch), so the copy starts now, under whatever the engine's stream is still computing
+  cudaStream_t cs = on_device ? s.stream : s.up;
   for (int b = 0; b < B; ++b) {
     const int64_t st = row_stride ? row_stride[b] : (int64_t)w[b] * 3;
     const uint8_t* ptr = frames[b];
@@ -184,7 +213,7 @@ static int enqueue_input(tcd_detector* d, Slot& s, YoloxPlan* p, const uint8_t* 
       const size_t tight = (size_t)w[b] * 3;
       TCD_REQUIRE((size_t)h[b] * tight <= s.frame_cap, "frame %d (%dx%d) exceeds max_src %dx%d", b, h[b],
                   w[b], d->cfg.max_src_h, d->cfg.max_src_w);
-      uint8_t* dst = s.staging + (size_t)b * s.frame_cap;
+      uint8_t* dst = l.staging + (size_t)b * s.frame_cap;
       // Row-sparse upload.  When the vertical resize ratio is an odd integer k (1080p -> 640 letterbox:
       // k = 3 exactly), the bilinear tap of output row d is s = k*(d+0.5)-0.5 = k*d + (k-1)/2, an integer:
       // the second tap's weight is exactly 0, so only every k-th source row contributes to the result and
@@ -198,25 +227,29 @@ static int enqueue_input(tcd_detector* d, Slot& s, YoloxPlan* p, const uint8_t* 
       if (sparse) {
         const size_t r0 = (size_t)probe.row_phase;
         TCD_CUDA_OK(cudaMemcpy2DAsync(dst + r0 * tight, (size_t)k * tight, ptr + r0 * (size_t)st, (size_t)k * (size_t)st,
-                                      tight, (size_t)probe.content_h, cudaMemcpyHostToDevice, s.stream));
+                                      tight, (size_t)probe.content_h, cudaMemcpyHostToDevice, cs));
         g_h2d_bytes.fetch_add((uint64_t)probe.content_h * tight, std::memory_order_relaxed);
       } else if ((size_t)st == tight) {
-        TCD_CUDA_OK(cudaMemcpyAsync(dst, ptr, (size_t)h[b] * tight, cudaMemcpyHostToDevice, s.stream));
+        TCD_CUDA_OK(cudaMemcpyAsync(dst, ptr, (size_t)h[b] * tight, cudaMemcpyHostToDevice, cs));
         g_h2d_bytes.fetch_add((uint64_t)h[b] * tight, std::memory_order_relaxed);
       } else {
         TCD_CUDA_OK(cudaMemcpy2DAsync(dst, tight, ptr, (size_t)st, tight, (size_t)h[b],
-                                      cudaMemcpyHostToDevice, s.stream));
+                                      cudaMemcpyHostToDevice, cs));
         g_h2d_bytes.fetch_add((uint64_t)h[b] * tight, std::memory_order_relaxed);
       }
       ptr = dst;
       dst_stride = (int64_t)tight;
     }
-    preproc_describe(&pc, ptr, h[b], w[b], dst_stride, &s.pre_host[b]);
+    preproc_describe(&pc, ptr, h[b], w[b], dst_stride, &l.pre_host[b]);
   }
-  TCD_CUDA_OK(cudaEventRecord(s.ev[1], s.stream));
-  TCD_CUDA_OK(cudaMemcpyAsync(s.pre_dev, s.pre_host, sizeof(PreFrame) * B, cudaMemcpyHostToDevice, s.stream));
+  if (cs != s.stream) {
+    TCD_CUDA_OK(cudaEventRecord(l.ev_up, cs));
+    TCD_CUDA_OK(cudaStreamWaitEvent(s.stream, l.ev_up, 0));
+  }
+  TCD_CUDA_OK(cudaEventRecord(l.ev[1], s.stream));
+  TCD_CUDA_OK(cudaMemcpyAsync(l.pre_dev, l.pre_host, sizeof(PreFrame) * B, cudaMemcpyHostToDevice, s.stream));
   if (!launch_pre) return TCD_OK;
-  return preproc_launch(&pc, s.pre_host, s.pre_dev, B, 1, p->input, s.stream);
+  return preproc_launch(&pc, l.pre_host, l.pre_dev, B, 1, p->input, s.stream);
 }
 
 static int check_batch(tcd_detector* det, const uint8_t* const* frames, const int32_t* h,
@@ -260,10 +293,14 @@ tcd_status tcd_create_detector(const tcd_detector_cfg* cfg, const void* packed_w
       rc = TCD_ERR_UNSUPPORTED;
     }
   }
-  for (int i = 0; i < kSlots && rc == TCD_OK; ++i) rc = slot_init(d, d->slot[i]);
+  if (const char* e = getenv("TCD_ENGINES")) {
+    const int v = atoi(e);
+    if (v >= 1 && v <= kEngines) d->n_engines = v;
+  }
+  for (int i = 0; i < d->n_engines && rc == TCD_OK; ++i) rc = slot_init(d, d->slot[i]);
   // build the max-batch plan up front so the first frame does not pay for it
   YoloxPlan* p = nullptr;
-  for (int i = 0; i < kSlots && rc == TCD_OK; ++i) rc = get_plan(d, d->slot[i], cfg->max_batch, &p);
+  for (int i = 0; i < d->n_engines && rc == TCD_OK; ++i) rc = get_plan(d, d->slot[i], cfg->max_batch, &p);
   if (rc) {
     tcd_destroy_detector(d);
     return (tcd_status)rc;
@@ -278,7 +315,7 @@ void tcd_destroy_detector(tcd_detector* det) {
   if (!det) return;
   cudaSetDevice(det->device);
   cudaDeviceSynchronize();
-  for (int i = 0; i < kSlots; ++i) slot_free(det->slot[i]);
+  for (int i = 0; i < kEngines; ++i) slot_free(det->slot[i]);
   det->wts.release();
   delete det;
 }
@@ -287,7 +324,7 @@ tcd_status tcd_detector_set_thresholds(tcd_detector* det, float conf_thre, float
   TCD_REQUIRE(det, "set_thresholds: null detector");
   det->thr_host[0] = conf_thre;
   det->thr_host[1] = nms_thre;
-  for (int i = 0; i < kSlots; ++i) {
+  for (int i = 0; i < det->n_engines; ++i) {
     // ordered after work already queued on the slot; never touches the captured graphs
     TCD_CUDA_OK(cudaStreamSynchronize(det->slot[i].stream));
     TCD_CUDA_OK(cudaMemcpy(det->slot[i].thr_dev, det->thr_host, 2 * sizeof(float), cudaMemcpyHostToDevice));
@@ -302,32 +339,38 @@ tcd_status tcd_detect_batch_async(tcd_detector* det, int32_t slot, const uint8_t
                                   int32_t B, int32_t frames_on_device) {
   int rc = check_batch(det, frames, h, w, B);
   if (rc) return (tcd_status)rc;
-  TCD_REQUIRE(slot >= 0 && slot < kSlots, "detect: slot %d outside [0,%d)", slot, kSlots);
-  Slot& s = det->slot[slot];
+  const int n_slots = det->n_engines * kLanes;
+  TCD_REQUIRE(slot >= 0 && slot < n_slots, "detect: slot %d outside [0,%d)", slot, n_slots);
+  Slot& s = det->slot[slot % det->n_engines];
+  Lane& l = s.lane[slot / det->n_engines];
+  TCD_REQUIRE(l.pending_B == 0, "detect: slot %d still has a batch in flight (wait for it first)", slot);
   YoloxPlan* p = nullptr;
   rc = get_plan(det, s, B, &p);
   if (rc) return (tcd_status)rc;
-  TCD_CUDA_OK(cudaEventRecord(s.ev[0], s.stream));
-  rc = enqueue_input(det, s, p, frames, h, w, row_stride, B, frames_on_device);
+  TCD_CUDA_OK(cudaEventRecord(l.ev[0], s.stream));
+  rc = enqueue_input(det, s, l, p, frames, h, w, row_stride, B, frames_on_device);
   if (rc) return (tcd_status)rc;
-  TCD_CUDA_OK(cudaEventRecord(s.ev[2], s.stream));
+  TCD_CUDA_OK(cudaEventRecord(l.ev[2], s.stream));
   rc = run_net_post(det, s, p, B, false);
   if (rc) return (tcd_status)rc;
-  TCD_CUDA_OK(cudaEventRecord(s.ev[3], s.stream));
-  TCD_CUDA_OK(cudaMemcpyAsync(s.out_pinned, s.pb.out_dets, sizeof(float) * 7 * det->cfg.max_out * B,
-                              cudaMemcpyDeviceToHost, s.stream));
-  TCD_CUDA_OK(cudaMemcpyAsync(s.cnt_pinned, s.pb.out_counts, sizeof(int) * B, cudaMemcpyDeviceToHost,
-                              s.stream));
-  TCD_CUDA_OK(cudaEventRecord(s.ev[4], s.stream));
-  s.pending_B = B;
+  TCD_CUDA_OK(cudaEventRecord(l.ev[3], s.stream));
+  // the engine's table belongs to the next batch queued on this stream: the lane keeps its own copies
+  const size_t tab_bytes = sizeof(float) * 7 * det->cfg.max_out * B;
+  TCD_CUDA_OK(cudaMemcpyAsync(l.out_pinned, s.pb.out_dets, tab_bytes, cudaMemcpyDeviceToHost, s.stream));
+  TCD_CUDA_OK(cudaMemcpyAsync(l.cnt_pinned, s.pb.out_counts, sizeof(int) * B, cudaMemcpyDeviceToHost, s.stream));
+  TCD_CUDA_OK(cudaMemcpyAsync(l.tab_dets, s.pb.out_dets, tab_bytes, cudaMemcpyDeviceToDevice, s.stream));
+  TCD_CUDA_OK(cudaMemcpyAsync(l.tab_counts, s.pb.out_counts, sizeof(int) * B, cudaMemcpyDeviceToDevice, s.stream));
+  TCD_CUDA_OK(cudaEventRecord(l.ev[4], s.stream));
+  l.pending_B = B;
   return TCD_OK;
 }
 
 tcd_status tcd_detect_batch_wait(tcd_detector* det, int32_t slot, float* out_dets, int32_t* out_counts) {
-  TCD_REQUIRE(det && out_dets && out_counts && slot >= 0 && slot < kSlots, "detect_wait: bad argument");
-  Slot& s = det->slot[slot];
+  TCD_REQUIRE(det && out_dets && out_counts && slot >= 0 && slot < det->n_engines * kLanes,
+              "detect_wait: bad argument");
+  Lane& s = det->slot[slot % det->n_engines].lane[slot / det->n_engines];
   TCD_REQUIRE(s.pending_B > 0, "detect_wait: nothing pending on slot %d", slot);
-  TCD_CUDA_OK(cudaStreamSynchronize(s.stream));
+  TCD_CUDA_OK(cudaEventSynchronize(s.ev[4]));   // not the stream: the engine's other lane may be queued behind
   const int B = s.pending_B;
   s.pending_B = 0;
   const size_t row = (size_t)7 * det->cfg.max_out;
@@ -370,7 +413,7 @@ tcd_status tcd_forward(tcd_detector* det, const uint8_t* const* frames, const in
   YoloxPlan* p = nullptr;
   rc = get_plan(det, s, B, &p);
   if (rc) return (tcd_status)rc;
-  rc = enqueue_input(det, s, p, frames, h, w, row_stride, B, frames_on_device);
+  rc = enqueue_input(det, s, s.lane[0], p, frames, h, w, row_stride, B, frames_on_device);
   if (rc) return (tcd_status)rc;
   rc = run_net_post(det, s, p, B, true);
   if (rc) return (tcd_status)rc;
@@ -393,30 +436,34 @@ tcd_status tcd_postprocess(tcd_detector* det, const float* pred_host, int32_t B,
   TCD_CUDA_OK(cudaMemcpyAsync(s.pred_in, pred_host, n * sizeof(float), cudaMemcpyHostToDevice, s.stream));
   rc = postproc_launch(post_for(s, p, B, s.pred_in, false), 0, s.stream);
   if (rc) return (tcd_status)rc;
-  TCD_CUDA_OK(cudaMemcpyAsync(s.out_pinned, s.pb.out_dets, sizeof(float) * 7 * det->cfg.max_out * B,
+  Lane& l = s.lane[0];
+  TCD_REQUIRE(l.pending_B == 0, "postprocess: slot 0 has a batch in flight");
+  TCD_CUDA_OK(cudaMemcpyAsync(l.out_pinned, s.pb.out_dets, sizeof(float) * 7 * det->cfg.max_out * B,
                               cudaMemcpyDeviceToHost, s.stream));
-  TCD_CUDA_OK(cudaMemcpyAsync(s.cnt_pinned, s.pb.out_counts, sizeof(int) * B, cudaMemcpyDeviceToHost,
+  TCD_CUDA_OK(cudaMemcpyAsync(l.cnt_pinned, s.pb.out_counts, sizeof(int) * B, cudaMemcpyDeviceToHost,
                               s.stream));
   TCD_CUDA_OK(cudaStreamSynchronize(s.stream));
   const size_t row = (size_t)7 * det->cfg.max_out;
   for (int b = 0; b < B; ++b) {
-    out_counts[b] = s.cnt_pinned[b];
-    memcpy(out_dets + b * row, s.out_pinned + b * row, sizeof(float) * 7 * (size_t)s.cnt_pinned[b]);
+    out_counts[b] = l.cnt_pinned[b];
+    memcpy(out_dets + b * row, l.out_pinned + b * row, sizeof(float) * 7 * (size_t)l.cnt_pinned[b]);
   }
   return TCD_OK;
 }
 
 void* tcd_detector_stream(tcd_detector* det, int32_t slot) {
-  if (!det || slot < 0 || slot >= kSlots) return nullptr;
-  return (void*)det->slot[slot].stream;
+  if (!det || slot < 0 || slot >= det->n_engines * kLanes) return nullptr;
+  return (void*)det->slot[slot % det->n_engines].stream;
 }
 
-int32_t tcd_detector_num_slots(const tcd_detector* det) { return det ? kSlots : 0; }
+int32_t tcd_detector_num_slots(const tcd_detector* det) { return det ? det->n_engines * kLanes : 0; }
 
 tcd_status tcd_detector_result_device(tcd_detector* det, int32_t slot, float** out_dets, int32_t** out_counts) {
-  TCD_REQUIRE(det && slot >= 0 && slot < kSlots && out_dets && out_counts, "result_device: bad argument");
-  *out_dets = det->slot[slot].pb.out_dets;
-  *out_counts = det->slot[slot].pb.out_counts;
+  TCD_REQUIRE(det && slot >= 0 && slot < det->n_engines * kLanes && out_dets && out_counts,
+              "result_device: bad argument");
+  Lane& l = det->slot[slot % det->n_engines].lane[slot / det->n_engines];
+  *out_dets = l.tab_dets;
+  *out_counts = l.tab_counts;
   return TCD_OK;
 }
 
@@ -475,10 +522,10 @@ tcd_status tcd_detector_profile(tcd_detector* det, const uint8_t* const* frames,
     tcd_preproc_cfg pc = det->cfg.pre;
     pc.out_h = det->cfg.input_h;
     pc.out_w = det->cfg.input_w;
-    rc = enqueue_input(det, s, p, frames, h, w, row_stride, B, frames_on_device, false);
+    rc = enqueue_input(det, s, s.lane[0], p, frames, h, w, row_stride, B, frames_on_device, false);
     if (rc) break;
     cudaEventRecord(ev[0], s.stream);
-    rc = preproc_launch(&pc, s.pre_host, s.pre_dev, B, 1, p->input, s.stream);
+    rc = preproc_launch(&pc, s.lane[0].pre_host, s.lane[0].pre_dev, B, 1, p->input, s.stream);
     cudaEventRecord(ev[1], s.stream);
     for (size_t i = 0; i < p->ops.size() && rc == TCD_OK; ++i) {
       // conv launches are bracketed kProfileReps at a time (same launch repeated back to back, as
