@@ -344,6 +344,7 @@ def run_ours(args):
     host_batches = [[host_np[b * B + j] for j in range(B)] for b in range(nb)]
     n_slots = min(args.slots, eng.num_slots) if args.slots > 0 else eng.num_slots
     streams = [torch.cuda.ExternalStream(eng.stream(i), device=local) for i in range(n_slots)]
+    n_engines = len({eng.stream(i) for i in range(n_slots)})
 
     from telescope_cam_detection_b200 import stream_shard
     # detections -> rank 0 for serving.  The slot's result table is already in device memory: one
@@ -538,7 +539,7 @@ def run_ours(args):
                    "preprocess": args.pre, "conf": 0.25, "nms": 0.45, "weights": "seeded random init (oracle/synth_weights.py)",
                    "parallelism": "replica per GPU, streams sharded by rank" if world > 1 else "1 GPU",
                    "l2": "inputs larger than L2: %d-frame pool (%.0f MB) cycled" % (POOL_FRAMES, POOL_FRAMES * 6.2208),
-                   "pipeline": "%d slots in flight (%d engines x 2 lanes; CUDA graph per engine)" % (n_slots, len({eng.stream(i) for i in range(n_slots)})),
+                   "pipeline": "%d slots in flight (%d engines x 2 lanes; CUDA graph per engine)" % (n_slots, n_engines),
                    "env": {k: v for k, v in os.environ.items() if k.startswith("TCD_")}},
         "e2e": {"value": fps_e2e, "unit": UNIT, "h2d_bytes_per_step": int(h2d_bytes[0]),
                 "h2d_note": "frame bytes counted by the library (tcd_h2d_byte_count); full frames are %d B/step -- at the "
