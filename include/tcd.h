@@ -105,9 +105,12 @@ tcd_status tcd_detect_batch(tcd_detector* det, const uint8_t* const* frames, con
                             const int32_t* w, const int64_t* row_stride, int32_t B,
                             int32_t frames_on_device, float* out_dets, int32_t* out_counts);
 
-/* Split-phase variant used by the pipelined coordinator / bench: enqueue on the handle's
- * stream `slot` (0 .. tcd_detector_num_slots()-1), then wait.  H2D of batch k+1 overlaps
- * compute of batch k; low-occupancy layers of different slots share the chip.            */
+/* Split-phase variant used by the pipelined coordinator / bench: enqueue as pipeline slot
+ * `slot` (0 .. tcd_detector_num_slots()-1), then wait.  A slot is (engine, lane): engine
+ * slot % n_engines owns the stream, arena and CUDA graph, lane slot / n_engines owns the frame
+ * staging and the result table of ONE in-flight batch (n_engines = 6, env TCD_ENGINES 1..8;
+ * two lanes per engine).  Frames of a queued lane upload on the engine's copy stream while
+ * the other lane computes; low-occupancy layers of different engines share the chip.     */
 tcd_status tcd_detect_batch_async(tcd_detector* det, int32_t slot, const uint8_t* const* frames,
                                   const int32_t* h, const int32_t* w, const int64_t* row_stride,
                                   int32_t B, int32_t frames_on_device);
@@ -126,7 +129,7 @@ int32_t tcd_detector_num_anchors(const tcd_detector* det);
 /* per-phase device times of the last synchronous detect_batch, ms:
  * [0]=h2d [1]=preprocess [2]=network [3]=decode+nms [4]=d2h                              */
 tcd_status tcd_detector_last_timing(const tcd_detector* det, float out_ms[5]);
-/* CUDA stream (cudaStream_t) the handle launches pipeline slot 0/1 on -- lets a caller record
+/* CUDA stream (cudaStream_t) of the engine that pipeline slot `slot` runs on -- lets a caller record
  * its own events around async calls (bench.py times with events on THIS stream).           */
 void* tcd_detector_stream(tcd_detector* det, int32_t slot);
 int32_t tcd_detector_num_slots(const tcd_detector* det);

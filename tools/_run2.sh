@@ -1,6 +1,6 @@
-set -x
-T=s18p
-for N in 2 4 8; do
-  timeout 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port $((29500+N)) bench.py --gpus $N > gpurun_out/${T}_n$N.json 2> gpurun_out/${T}_n$N.err; echo rc=$?
-done
-tail -c 200 gpurun_out/${T}_n*.err
+T=s22
+timeout 300 python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29541 bench.py --gpus 2 > gpurun_out/${T}_bench_n2.json 2> gpurun_out/${T}_bench_n2.err; echo bench rc=$?
+tail -c 400 gpurun_out/${T}_bench_n2.err
+T=s21
+timeout 300 python bench.py > gpurun_out/${T}_bench.json 2> gpurun_out/${T}_bench.err; echo bench rc=$?
+tail -c 300 gpurun_out/${T}_bench.err
