@@ -82,7 +82,8 @@ typedef struct {
   int32_t max_batch;          /* frames per detect_batch call the arena is sized for      */
   int32_t num_classes;        /* 80                                                       */
   int32_t max_out;            /* rows per frame in the result table                       */
-  int32_t max_src_h, max_src_w; /* largest camera frame (staging buffer for host frames)  */
+  int32_t max_src_h, max_src_w; /* expected camera frame: initial size of the host-frame staging
+                                   buffers; a larger frame grows its lane's buffer on arrival      */
   tcd_preproc_cfg pre;        /* out_h/out_w ignored (taken from input_h/input_w)         */
 } tcd_detector_cfg;
 
@@ -95,6 +96,31 @@ void tcd_destroy_detector(tcd_detector* det);
 /* conf / nms thresholds of yolox.utils.postprocess (src/yolox_detector.py:309-314);
  * cheap, lock-free for the caller, never re-captures a CUDA graph.                       */
 tcd_status tcd_detector_set_thresholds(tcd_detector* det, float conf_thre, float nms_thre);
+
+/* Per-camera class filter, evaluated on the device on the rows that survive NMS, in score order -- the
+ * wildlife mask of YOLOXDetector._format_model_output_to_detections (src/yolox_detector.py:258,
+ * src/coco_constants.py:23-29) followed by InferenceEngine._post_process_detections
+ * (src/inference_engine_yolox.py:505-534): ensure_valid_bbox on the box un-scaled to camera pixels
+ * (ratio = orig / network size, fp32 product like the reference's np.float32 * float), per-class confidence
+ * (the override, else the global threshold), global minimum area, per-class min / max area, stop at max_det.
+ * All comparisons in double, like the Python floats they replace: the rows kept are exactly the dicts the
+ * reference's loop keeps.  Tables are per detector; table 0 is "no filter" and cannot be set.            */
+#define TCD_MAX_CLASSES 128
+#define TCD_MAX_FILTER_TABLES 64
+typedef struct {
+  double cls_conf[TCD_MAX_CLASSES];      /* confidence < cls_conf[c]  -> dropped                          */
+  double cls_min_area[TCD_MAX_CLASSES];  /* area < cls_min_area[c]    -> dropped (-inf: no constraint)    */
+  double cls_max_area[TCD_MAX_CLASSES];  /* area > cls_max_area[c]    -> dropped (+inf: no constraint)    */
+  double min_area;                       /* global min_box_area; <= 0: off                                */
+  uint64_t class_mask[2];                /* bit c set: class c allowed (wildlife_only: {0,14,15,16,21})   */
+  int32_t max_det;                       /* keep the first max_det survivors                              */
+  int32_t reserved;
+} tcd_class_filter;
+tcd_status tcd_detector_set_class_filter(tcd_detector* det, int32_t table, const tcd_class_filter* f);
+/* Parity tap: the filter of `table` applied on the device to caller-supplied rows (HOST f32 [n,7], network pixels,
+ * score order) of a frame of orig_h x orig_w; keep_host[i] = 1 for the rows that survive (max_det included).     */
+tcd_status tcd_detector_filter_rows(tcd_detector* det, int32_t table, const float* rows_host, int32_t n,
+                                    int32_t orig_h, int32_t orig_w, int32_t* keep_host);
 
 /* frames[b]: HWC u8 BGR.  frames_on_device = 0: host pointers (pinned or pageable), the
  * H2D copy is part of the call; 1: device pointers.  out_dets: HOST [B,max_out,7] f32 rows
@@ -114,6 +140,12 @@ tcd_status tcd_detect_batch(tcd_detector* det, const uint8_t* const* frames, con
 tcd_status tcd_detect_batch_async(tcd_detector* det, int32_t slot, const uint8_t* const* frames,
                                   const int32_t* h, const int32_t* w, const int64_t* row_stride,
                                   int32_t B, int32_t frames_on_device);
+/* The same with a class-filter table per frame (filter_table[b] in [0, TCD_MAX_FILTER_TABLES); NULL = all 0):
+ * frames of different cameras, each with its own thresholds, share one batch as they do in
+ * SharedInferenceCoordinator._process_batch (src/shared_inference_coordinator.py:226-288).               */
+tcd_status tcd_detector_submit(tcd_detector* det, int32_t slot, const uint8_t* const* frames,
+                               const int32_t* h, const int32_t* w, const int64_t* row_stride,
+                               int32_t B, int32_t frames_on_device, const int32_t* filter_table);
 tcd_status tcd_detect_batch_wait(tcd_detector* det, int32_t slot, float* out_dets,
                                  int32_t* out_counts);
 

@@ -23,6 +23,17 @@ class DetectorCfg(C.Structure):
                 ("max_src_w", C.c_int32), ("pre", PreprocCfg)]
 
 
+MAX_CLASSES = 128          # TCD_MAX_CLASSES
+MAX_FILTER_TABLES = 64     # TCD_MAX_FILTER_TABLES
+
+
+class ClassFilter(C.Structure):
+    """tcd_class_filter (include/tcd.h)."""
+    _fields_ = [("cls_conf", C.c_double * MAX_CLASSES), ("cls_min_area", C.c_double * MAX_CLASSES),
+                ("cls_max_area", C.c_double * MAX_CLASSES), ("min_area", C.c_double),
+                ("class_mask", C.c_uint64 * 2), ("max_det", C.c_int32), ("reserved", C.c_int32)]
+
+
 class ConvDesc(C.Structure):
     """tcd_conv_desc (include/tcd.h)."""
     _fields_ = [("name", C.c_char * 64),
@@ -80,6 +91,9 @@ SIGNATURES = {
     "tcd_create_detector": (C.c_int, [C.POINTER(DetectorCfg), _P, C.c_size_t, C.c_int32, _PP]),
     "tcd_destroy_detector": (None, [_P]),
     "tcd_detector_set_thresholds": (C.c_int, [_P, C.c_float, C.c_float]),
+    "tcd_detector_set_class_filter": (C.c_int, [_P, C.c_int32, C.POINTER(ClassFilter)]),
+    "tcd_detector_filter_rows": (C.c_int, [_P, C.c_int32, _F32P, C.c_int32, C.c_int32, C.c_int32, _I32P]),
+    "tcd_detector_submit": (C.c_int, [_P, C.c_int32, _PP, _I32P, _I32P, _I64P, C.c_int32, C.c_int32, _I32P]),
     "tcd_detect_batch": (C.c_int, [_P, _PP, _I32P, _I32P, _I64P, C.c_int32, C.c_int32, _F32P, _I32P]),
     "tcd_detect_batch_async": (C.c_int, [_P, C.c_int32, _PP, _I32P, _I32P, _I64P, C.c_int32, C.c_int32]),
     "tcd_detect_batch_wait": (C.c_int, [_P, C.c_int32, _F32P, _I32P]),

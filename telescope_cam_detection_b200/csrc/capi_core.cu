@@ -1,6 +1,8 @@
 // C ABI glue, part 1: error plumbing, utilities, stand-alone kernel entries
 // (tcd_preprocess, tcd_conv2d_nhwc_bf16, tcd_crop_resize).  Declarations: include/tcd.h.
 #include <atomic>
+#include <map>
+#include <mutex>
 #include <stdarg.h>
 #include <string.h>
 #include <vector>
@@ -19,6 +21,20 @@ void set_last_error(const char* fmt, ...) {
   va_start(ap, fmt);
   vsnprintf(g_err, sizeof(g_err), fmt, ap);
   va_end(ap);
+}
+
+int ensure_dyn_smem(const void* fn, size_t bytes) {
+  if (bytes <= 48 * 1024) return TCD_OK;
+  static std::mutex mu;
+  static std::map<std::pair<int, const void*>, size_t> high;
+  int dev = 0;
+  TCD_CUDA_OK(cudaGetDevice(&dev));
+  std::lock_guard<std::mutex> lk(mu);
+  size_t& h = high[std::make_pair(dev, fn)];
+  if (bytes <= h) return TCD_OK;
+  TCD_CUDA_OK(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
+  h = bytes;
+  return TCD_OK;
 }
 
 // Refuse to run anywhere but on a Blackwell data-centre part: no fallback path exists.

@@ -5,6 +5,7 @@
 // layers of one batch share the chip with another batch's; the second lane keeps an engine's stream fed -- the
 // batch of lane 1 is already queued (and its frames uploaded, on the engine's upload stream) when lane 0's batch
 // finishes, so neither the host's turn-around nor the H2D copy leaves the stream idle.
+#include <algorithm>
 #include <atomic>
 #include <map>
 #include <stdlib.h>
@@ -28,8 +29,12 @@ constexpr int kLanes = 2;
 constexpr int kSlots = kEngines * kLanes;
 constexpr int kProfileReps = 8;
 
+#define TCD_USE(handle) TCD_CUDA_OK(cudaSetDevice((handle)->device))   /* the current device is per host thread */
+
 struct Lane {                     // what ONE in-flight batch owns besides its engine
-  uint8_t* staging = nullptr;     // device, max_batch frames of max_src bytes
+  uint8_t* staging = nullptr;     // device, max_batch frames of frame_cap bytes (grows when a larger frame arrives)
+  size_t frame_cap = 0;
+  FrameMeta* meta_host = nullptr; // pinned [max_batch]: filter table + box un-scaling per frame
   PreFrame* pre_dev = nullptr;    // device [max_batch]
   PreFrame* pre_host = nullptr;   // pinned [max_batch]
   float* out_pinned = nullptr;    // [max_batch,max_out,7]
@@ -44,7 +49,7 @@ struct Lane {                     // what ONE in-flight batch owns besides its e
 struct Slot {                     // an engine
   cudaStream_t stream = nullptr;
   cudaStream_t up = nullptr;      // frame uploads: copy-engine work off the compute stream
-  size_t frame_cap = 0;
+  FrameMeta* meta_dev = nullptr;  // [max_batch], what the captured nms_reduce reads; refilled per batch
   Lane lane[kLanes];
   std::map<int, YoloxPlan*> plans;
   std::map<int, cudaGraphExec_t> graphs;
@@ -53,6 +58,7 @@ struct Slot {                     // an engine
   PostBuffers pb;
   float* thr_dev = nullptr;
   float* pred_in = nullptr;       // device scratch for tcd_postprocess [max_batch,A,5+C]
+  const tcd_class_filter* tables = nullptr;  // the detector's table array
 };
 
 }  // namespace
@@ -64,6 +70,7 @@ struct tcd_detector {
   Slot slot[kEngines];
   int n_engines = 6;              // TCD_ENGINES; slots exposed = n_engines * kLanes
   float thr_host[2] = {0.25f, 0.45f};
+  tcd_class_filter* tables_dev = nullptr;   // [kMaxFilterTables]
   int n_anchors = 0, cap = 0;
   float last_ms[5] = {0, 0, 0, 0, 0};
   bool use_graph = true;
@@ -74,9 +81,12 @@ static int slot_init(tcd_detector* d, Slot& s) {
   const int MB = c.max_batch;
   TCD_CUDA_OK(cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking));
   TCD_CUDA_OK(cudaStreamCreateWithFlags(&s.up, cudaStreamNonBlocking));
-  s.frame_cap = ((size_t)c.max_src_h * c.max_src_w * 3 + 255) & ~(size_t)255;
+  TCD_CUDA_OK(cudaMalloc((void**)&s.meta_dev, sizeof(FrameMeta) * MB));
+  TCD_CUDA_OK(cudaMemset(s.meta_dev, 0, sizeof(FrameMeta) * MB));
   for (Lane& l : s.lane) {
-    TCD_CUDA_OK(cudaMalloc((void**)&l.staging, s.frame_cap * MB));
+    l.frame_cap = ((size_t)c.max_src_h * c.max_src_w * 3 + 255) & ~(size_t)255;
+    TCD_CUDA_OK(cudaMalloc((void**)&l.staging, l.frame_cap * MB));
+    TCD_CUDA_OK(cudaMallocHost((void**)&l.meta_host, sizeof(FrameMeta) * MB));
     TCD_CUDA_OK(cudaMalloc((void**)&l.pre_dev, sizeof(PreFrame) * MB));
     TCD_CUDA_OK(cudaMallocHost((void**)&l.pre_host, sizeof(PreFrame) * MB));
     TCD_CUDA_OK(cudaMalloc((void**)&l.tab_dets, sizeof(float) * 7 * c.max_out * MB));
@@ -87,6 +97,7 @@ static int slot_init(tcd_detector* d, Slot& s) {
     TCD_CUDA_OK(cudaEventCreateWithFlags(&l.ev_up, cudaEventDisableTiming));
   }
   const int A = d->n_anchors, C = c.num_classes, cap = d->cap;
+  s.tables = d->tables_dev;
   PostBuffers& pb = s.pb;
   memset(&pb, 0, sizeof(pb));
   pb.A = A; pb.C = C; pb.cap = cap; pb.max_out = c.max_out;
@@ -111,13 +122,14 @@ static void slot_free(Slot& s) {
   for (auto& kv : s.graphs) cudaGraphExecDestroy(kv.second);
   for (auto& kv : s.plans) { kv.second->release(); delete kv.second; }
   PostBuffers& pb = s.pb;
-  void* ptrs[] = {s.thr_dev, pb.cand_count, pb.cand, pb.cand_anchor, pb.srec,
+  void* ptrs[] = {s.meta_dev, s.thr_dev, pb.cand_count, pb.cand, pb.cand_anchor, pb.srec,
                   pb.sbox, pb.n_sorted, pb.mask, pb.out_dets, pb.out_counts, pb.decoded, s.pred_in};
   for (void* p : ptrs) if (p) cudaFree(p);
   for (Lane& l : s.lane) {
     void* dp[] = {l.staging, l.pre_dev, l.tab_dets, l.tab_counts};
     for (void* p : dp) if (p) cudaFree(p);
     if (l.pre_host) cudaFreeHost(l.pre_host);
+    if (l.meta_host) cudaFreeHost(l.meta_host);
     if (l.out_pinned) cudaFreeHost(l.out_pinned);
     if (l.cnt_pinned) cudaFreeHost(l.cnt_pinned);
     for (auto& e : l.ev) if (e) cudaEventDestroy(e);
@@ -143,6 +155,8 @@ static PostBuffers post_for(const Slot& s, const YoloxPlan* p, int B, const floa
   pb.B = B;
   pb.pred = pred;
   if (!want_decoded) pb.decoded = nullptr;
+  pb.meta = s.meta_dev;
+  pb.tables = s.tables;
   pb.n_levels = 3;
   for (int l = 0; l < 3; ++l) {
     pb.lvl_start[l] = p->lvl_start[l];
@@ -196,24 +210,59 @@ static const bool g_sparse_upload = [] {
   return !(e && e[0] == '0');
 }();
 
+// A host frame larger than the lane's staging slots (the reference accepts any frame size; its shipped config has a
+// 2560x1440 camera): the lane's buffer is re-allocated.  The lane has no batch in flight (the caller checked), the
+// captured graphs never see the staging address (the preprocess kernel reads it from PreFrame), and cudaFree waits
+// for whatever the device still runs -- a one-off stall when a new camera size first shows up.
+static int grow_staging(tcd_detector* d, Lane& l, size_t need) {
+  if (need <= l.frame_cap) return TCD_OK;
+  const size_t cap = (need + 255) & ~(size_t)255;
+  uint8_t* fresh = nullptr;
+  TCD_CUDA_OK(cudaMalloc((void**)&fresh, cap * d->cfg.max_batch));
+  if (l.staging) cudaFree(l.staging);
+  l.staging = fresh;
+  l.frame_cap = cap;
+  return TCD_OK;
+}
+
 static int enqueue_input(tcd_detector* d, Slot& s, Lane& l, YoloxPlan* p, const uint8_t* const* frames,
                          const int32_t* h, const int32_t* w, const int64_t* row_stride, int B,
-                         int on_device, bool launch_pre = true) {
+                         int on_device, bool launch_pre = true, const int32_t* filter_table = nullptr) {
   tcd_preproc_cfg pc = d->cfg.pre;
   pc.out_h = d->cfg.input_h;
   pc.out_w = d->cfg.input_w;
   // host frames travel on the engine's upload stream: the lane's staging buffer is free (the host has waited for
   // the lane's previous batch), so the copy starts now, under whatever the engine's stream is still computing
   cudaStream_t cs = on_device ? s.stream : s.up;
+  if (!on_device) {
+    size_t need = 0;
+    for (int b = 0; b < B; ++b) need = std::max(need, (size_t)h[b] * (size_t)w[b] * 3);
+    int rc = grow_staging(d, l, need);
+    if (rc) return rc;
+  }
   for (int b = 0; b < B; ++b) {
+    const int tb = filter_table ? filter_table[b] : 0;
+    TCD_REQUIRE(tb >= 0 && tb < kMaxFilterTables, "detect: filter table %d of frame %d outside [0,%d)", tb, b,
+                kMaxFilterTables);
+    l.meta_host[b].table = tb;
+    // orig / network size evaluated like Python does (double division), then narrowed like np.float32(ratio)
+    if (d->cfg.pre.mode == 1) {
+      // letterbox: one isotropic ratio r = min(H/h, W/w); boxes un-scale by 1/r on both axes (the host formatter
+      // passes orig = input / r, so its ratio is (input / r) / input -- evaluated the same way here)
+      const double r = std::min((double)d->cfg.input_h / (double)h[b], (double)d->cfg.input_w / (double)w[b]);
+      l.meta_host[b].ratio_w = (float)(((double)d->cfg.input_w / r) / (double)d->cfg.input_w);
+      l.meta_host[b].ratio_h = (float)(((double)d->cfg.input_h / r) / (double)d->cfg.input_h);
+    } else {
+      l.meta_host[b].ratio_w = (float)((double)w[b] / (double)d->cfg.input_w);
+      l.meta_host[b].ratio_h = (float)((double)h[b] / (double)d->cfg.input_h);
+    }
+    l.meta_host[b].pad = 0;
     const int64_t st = row_stride ? row_stride[b] : (int64_t)w[b] * 3;
     const uint8_t* ptr = frames[b];
     int64_t dst_stride = st;
     if (!on_device) {
       const size_t tight = (size_t)w[b] * 3;
-      TCD_REQUIRE((size_t)h[b] * tight <= s.frame_cap, "frame %d (%dx%d) exceeds max_src %dx%d", b, h[b],
-                  w[b], d->cfg.max_src_h, d->cfg.max_src_w);
-      uint8_t* dst = l.staging + (size_t)b * s.frame_cap;
+      uint8_t* dst = l.staging + (size_t)b * l.frame_cap;
       // Row-sparse upload.  When the vertical resize ratio is an odd integer k (1080p -> 640 letterbox:
       // k = 3 exactly), the bilinear tap of output row d is s = k*(d+0.5)-0.5 = k*d + (k-1)/2, an integer:
       // the second tap's weight is exactly 0, so only every k-th source row contributes to the result and
@@ -248,6 +297,7 @@ static int enqueue_input(tcd_detector* d, Slot& s, Lane& l, YoloxPlan* p, const 
   }
   TCD_CUDA_OK(cudaEventRecord(l.ev[1], s.stream));
   TCD_CUDA_OK(cudaMemcpyAsync(l.pre_dev, l.pre_host, sizeof(PreFrame) * B, cudaMemcpyHostToDevice, s.stream));
+  TCD_CUDA_OK(cudaMemcpyAsync(s.meta_dev, l.meta_host, sizeof(FrameMeta) * B, cudaMemcpyHostToDevice, s.stream));
   if (!launch_pre) return TCD_OK;
   return preproc_launch(&pc, l.pre_host, l.pre_dev, B, 1, p->input, s.stream);
 }
@@ -297,6 +347,17 @@ tcd_status tcd_create_detector(const tcd_detector_cfg* cfg, const void* packed_w
     const int v = atoi(e);
     if (v >= 1 && v <= kEngines) d->n_engines = v;
   }
+  if (rc == TCD_OK && cfg->num_classes > TCD_MAX_CLASSES) {
+    set_last_error("create_detector: %d classes exceed TCD_MAX_CLASSES", cfg->num_classes);
+    rc = TCD_ERR_UNSUPPORTED;
+  }
+  if (rc == TCD_OK) {
+    const size_t tb = sizeof(tcd_class_filter) * kMaxFilterTables;
+    if (cudaMalloc((void**)&d->tables_dev, tb) != cudaSuccess || cudaMemset(d->tables_dev, 0, tb) != cudaSuccess) {
+      set_last_error("create_detector: filter tables: %s", cudaGetErrorString(cudaGetLastError()));
+      rc = TCD_ERR_CUDA;
+    }
+  }
   for (int i = 0; i < d->n_engines && rc == TCD_OK; ++i) rc = slot_init(d, d->slot[i]);
   // build the max-batch plan up front so the first frame does not pay for it
   YoloxPlan* p = nullptr;
@@ -317,11 +378,49 @@ void tcd_destroy_detector(tcd_detector* det) {
   cudaDeviceSynchronize();
   for (int i = 0; i < kEngines; ++i) slot_free(det->slot[i]);
   det->wts.release();
+  if (det->tables_dev) cudaFree(det->tables_dev);
   delete det;
+}
+
+tcd_status tcd_detector_set_class_filter(tcd_detector* det, int32_t table, const tcd_class_filter* f) {
+  TCD_REQUIRE(det && f, "set_class_filter: null argument");
+  TCD_REQUIRE(table >= 1 && table < kMaxFilterTables, "set_class_filter: table %d outside [1,%d)", table,
+              kMaxFilterTables);
+  TCD_USE(det);
+  // ordered after the batches already queued (they keep the table they were submitted under)
+  for (int i = 0; i < det->n_engines; ++i) TCD_CUDA_OK(cudaStreamSynchronize(det->slot[i].stream));
+  TCD_CUDA_OK(cudaMemcpy(det->tables_dev + table, f, sizeof(*f), cudaMemcpyHostToDevice));
+  return TCD_OK;
+}
+
+tcd_status tcd_detector_filter_rows(tcd_detector* det, int32_t table, const float* rows_host, int32_t n,
+                                    int32_t orig_h, int32_t orig_w, int32_t* keep_host) {
+  TCD_REQUIRE(det && rows_host && keep_host && n >= 0, "filter_rows: bad argument");
+  TCD_REQUIRE(table >= 1 && table < kMaxFilterTables, "filter_rows: table %d outside [1,%d)", table, kMaxFilterTables);
+  if (n == 0) return TCD_OK;
+  TCD_USE(det);
+  float* rows = nullptr;
+  int* keep = nullptr;
+  TCD_CUDA_OK(cudaMalloc((void**)&rows, sizeof(float) * 7 * n));
+  TCD_CUDA_OK(cudaMalloc((void**)&keep, sizeof(int) * n));
+  cudaStream_t st = det->slot[0].stream;
+  TCD_CUDA_OK(cudaMemcpyAsync(rows, rows_host, sizeof(float) * 7 * n, cudaMemcpyHostToDevice, st));
+  const float rw = (float)((double)orig_w / (double)det->cfg.input_w), rh = (float)((double)orig_h / (double)det->cfg.input_h);
+  int rc = class_filter_rows_launch(det->tables_dev, table, rows, n, rw, rh, keep, st);
+  cudaError_t e = cudaMemcpyAsync(keep_host, keep, sizeof(int) * n, cudaMemcpyDeviceToHost, st);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+  cudaFree(rows);
+  cudaFree(keep);
+  if (rc == TCD_OK && e != cudaSuccess) {
+    set_last_error("filter_rows: %s", cudaGetErrorString(e));
+    rc = TCD_ERR_CUDA;
+  }
+  return (tcd_status)rc;
 }
 
 tcd_status tcd_detector_set_thresholds(tcd_detector* det, float conf_thre, float nms_thre) {
   TCD_REQUIRE(det, "set_thresholds: null detector");
+  TCD_USE(det);
   det->thr_host[0] = conf_thre;
   det->thr_host[1] = nms_thre;
   for (int i = 0; i < det->n_engines; ++i) {
@@ -337,8 +436,15 @@ int32_t tcd_detector_num_anchors(const tcd_detector* det) { return det ? det->n_
 tcd_status tcd_detect_batch_async(tcd_detector* det, int32_t slot, const uint8_t* const* frames,
                                   const int32_t* h, const int32_t* w, const int64_t* row_stride,
                                   int32_t B, int32_t frames_on_device) {
+  return tcd_detector_submit(det, slot, frames, h, w, row_stride, B, frames_on_device, nullptr);
+}
+
+tcd_status tcd_detector_submit(tcd_detector* det, int32_t slot, const uint8_t* const* frames,
+                               const int32_t* h, const int32_t* w, const int64_t* row_stride,
+                               int32_t B, int32_t frames_on_device, const int32_t* filter_table) {
   int rc = check_batch(det, frames, h, w, B);
   if (rc) return (tcd_status)rc;
+  TCD_USE(det);
   const int n_slots = det->n_engines * kLanes;
   TCD_REQUIRE(slot >= 0 && slot < n_slots, "detect: slot %d outside [0,%d)", slot, n_slots);
   Slot& s = det->slot[slot % det->n_engines];
@@ -348,7 +454,7 @@ tcd_status tcd_detect_batch_async(tcd_detector* det, int32_t slot, const uint8_t
   rc = get_plan(det, s, B, &p);
   if (rc) return (tcd_status)rc;
   TCD_CUDA_OK(cudaEventRecord(l.ev[0], s.stream));
-  rc = enqueue_input(det, s, l, p, frames, h, w, row_stride, B, frames_on_device);
+  rc = enqueue_input(det, s, l, p, frames, h, w, row_stride, B, frames_on_device, true, filter_table);
   if (rc) return (tcd_status)rc;
   TCD_CUDA_OK(cudaEventRecord(l.ev[2], s.stream));
   rc = run_net_post(det, s, p, B, false);
@@ -368,6 +474,7 @@ tcd_status tcd_detect_batch_async(tcd_detector* det, int32_t slot, const uint8_t
 tcd_status tcd_detect_batch_wait(tcd_detector* det, int32_t slot, float* out_dets, int32_t* out_counts) {
   TCD_REQUIRE(det && out_dets && out_counts && slot >= 0 && slot < det->n_engines * kLanes,
               "detect_wait: bad argument");
+  TCD_USE(det);
   Lane& s = det->slot[slot % det->n_engines].lane[slot / det->n_engines];
   TCD_REQUIRE(s.pending_B > 0, "detect_wait: nothing pending on slot %d", slot);
   TCD_CUDA_OK(cudaEventSynchronize(s.ev[4]));   // not the stream: the engine's other lane may be queued behind
@@ -409,6 +516,7 @@ tcd_status tcd_forward(tcd_detector* det, const uint8_t* const* frames, const in
   int rc = check_batch(det, frames, h, w, B);
   if (rc) return (tcd_status)rc;
   TCD_REQUIRE(out_pred_host, "forward: null output");
+  TCD_USE(det);
   Slot& s = det->slot[0];
   YoloxPlan* p = nullptr;
   rc = get_plan(det, s, B, &p);
@@ -428,12 +536,14 @@ tcd_status tcd_postprocess(tcd_detector* det, const float* pred_host, int32_t B,
                            int32_t* out_counts) {
   TCD_REQUIRE(det && pred_host && out_dets && out_counts, "postprocess: null argument");
   TCD_REQUIRE(B >= 1 && B <= det->cfg.max_batch, "postprocess: batch %d", B);
+  TCD_USE(det);
   Slot& s = det->slot[0];
   YoloxPlan* p = nullptr;
   int rc = get_plan(det, s, det->cfg.max_batch, &p);
   if (rc) return (tcd_status)rc;
   const size_t n = (size_t)B * det->n_anchors * (5 + det->cfg.num_classes);
   TCD_CUDA_OK(cudaMemcpyAsync(s.pred_in, pred_host, n * sizeof(float), cudaMemcpyHostToDevice, s.stream));
+  TCD_CUDA_OK(cudaMemsetAsync(s.meta_dev, 0, sizeof(FrameMeta) * B, s.stream));   // table 0: no class filter
   rc = postproc_launch(post_for(s, p, B, s.pred_in, false), 0, s.stream);
   if (rc) return (tcd_status)rc;
   Lane& l = s.lane[0];
@@ -474,6 +584,7 @@ tcd_status tcd_detector_result_device(tcd_detector* det, int32_t slot, float** o
 tcd_status tcd_detector_trace_op(tcd_detector* det, int32_t B, int32_t idx, int32_t reps,
                                  uint64_t out128[128], int32_t* grid, int32_t* smem_bytes) {
   TCD_REQUIRE(det && out128, "trace_op: null argument");
+  TCD_USE(det);
   Slot& s = det->slot[0];
   YoloxPlan* p = nullptr;
   int rc = get_plan(det, s, B, &p);
@@ -507,6 +618,7 @@ tcd_status tcd_detector_profile(tcd_detector* det, const uint8_t* const* frames,
   int rc = check_batch(det, frames, h, w, B);
   if (rc) return (tcd_status)rc;
   TCD_REQUIRE(iters >= 1 && op_ms && n_ops, "profile: bad argument");
+  TCD_USE(det);
   Slot& s = det->slot[0];
   YoloxPlan* p = nullptr;
   rc = get_plan(det, s, B, &p);
@@ -597,6 +709,7 @@ double tcd_detector_op_flops(tcd_detector* det, int32_t B, int32_t idx) {
 tcd_status tcd_detector_read_activation(tcd_detector* det, const char* name, float* out_host,
                                         size_t out_elems, int32_t* shape4) {
   TCD_REQUIRE(det && name && shape4, "read_activation: null argument");
+  TCD_USE(det);
   Slot& s = det->slot[0];
   const YoloxPlan* p = nullptr;
   for (auto& kv : s.plans) if (kv.second->acts.count(name)) p = kv.second;  // last built wins

@@ -121,6 +121,7 @@ void tcd_mog2_destroy(tcd_mog2* m) {
 
 tcd_status tcd_mog2_reset(tcd_mog2* m) {
   TCD_REQUIRE(m, "mog2_reset: null handle");
+  TCD_CUDA_OK(cudaSetDevice(m->device));
   const size_t np = (size_t)m->h * m->w;
   m->nframes = 0;
   TCD_CUDA_OK(cudaMemsetAsync(m->st.nmodes, 0, np, m->stream));
@@ -132,6 +133,7 @@ tcd_status tcd_mog2_reset(tcd_mog2* m) {
 tcd_status tcd_mog2_apply(tcd_mog2* m, const uint8_t* frame, int64_t row_stride,
                           int32_t frame_on_device, int32_t repeats, uint8_t* fg_mask_host) {
   TCD_REQUIRE(m && frame && repeats >= 1, "mog2_apply: bad argument");
+  TCD_CUDA_OK(cudaSetDevice(m->device));
   const size_t tight = (size_t)m->w * 3;
   if (row_stride <= 0) row_stride = (int64_t)tight;
   const uint8_t* src = frame;
@@ -176,6 +178,7 @@ tcd_status tcd_mog2_roi_counts(tcd_mog2* m, int32_t shadow_thr, int32_t ksize, i
                                uint8_t* clean_mask_host) {
   TCD_REQUIRE(m && n_rois >= 0 && (n_rois == 0 || (rois && counts_host)), "mog2_roi_counts: bad argument");
   TCD_REQUIRE(n_rois <= m->roi_cap, "mog2_roi_counts: %d ROIs exceed capacity %d", n_rois, m->roi_cap);
+  TCD_CUDA_OK(cudaSetDevice(m->device));
   const int np = m->h * m->w;
   int rc;
   cudaEventRecord(m->ev[2], m->stream);
@@ -267,6 +270,7 @@ tcd_status tcd_empty_filter_step(tcd_empty_filter* f, const uint8_t* frame, int6
                                  int32_t* changed_pixels_host, uint8_t* gray_blur_host) {
   TCD_REQUIRE(f && frame && changed_pixels_host && (channels == 1 || channels == 3),
               "empty_filter_step: bad argument");
+  TCD_CUDA_OK(cudaSetDevice(f->device));
   const size_t tight = (size_t)f->w * channels;
   if (row_stride <= 0) row_stride = (int64_t)tight;
   const uint8_t* src = frame;

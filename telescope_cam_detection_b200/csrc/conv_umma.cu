@@ -381,18 +381,8 @@ int conv_plan_build(const ConvDesc& d, ConvPlan* plan) {
   } else {
     plan->maps.o = plan->maps.b;
   }
-  static std::once_flag once;
-  static cudaError_t attr_err = cudaSuccess;
-  std::call_once(once, [] {
-    for (int i = 0; i < 16 && attr_err == cudaSuccess; ++i)
-      attr_err = cudaFuncSetAttribute((const void*)conv_kernel_variant(i >> 2, (i >> 1) & 1, i & 1),
-                                      cudaFuncAttributeMaxDynamicSharedMemorySize, 218 * 1024);
-  });
-  if (attr_err != cudaSuccess) {
-    set_last_error("cudaFuncSetAttribute(conv_umma_kernel): %s", cudaGetErrorString(attr_err));
-    return TCD_ERR_CUDA;
-  }
-  return TCD_OK;
+  // per device, per instantiation (the plan is built on the device that will run it)
+  return ensure_dyn_smem((const void*)conv_kernel_variant(a.silu, a.halo, a.mode), (size_t)plan->smem_bytes);
 }
 
 int conv_plan_launch(const ConvPlan& plan, cudaStream_t stream) {

@@ -21,6 +21,13 @@ void preproc_describe(const tcd_preproc_cfg* cfg, const uint8_t* ptr, int h, int
                       PreFrame* f);
 
 // ---- decode / filter / NMS (postproc.cu)
+constexpr int kPostMaxWords = 132;      // cap <= 8448 candidates per frame -> 132 mask words per row
+constexpr int kMaxFilterTables = 64;    // per-camera class-filter tables of one detector (0 = pass-through)
+struct FrameMeta {                      // per frame of a batch: which filter table, and the un-scaling of its boxes
+  int table;
+  float ratio_w, ratio_h;               // orig / network size, as np.float32
+  int pad;
+};
 struct PostBuffers {
   int B, A, C, cap, max_out;
   const float* pred;      // [B,A,5+C] raw head output or decoded prediction
@@ -37,9 +44,13 @@ struct PostBuffers {
   int* out_counts;        // [B]
   int n_levels;
   int lvl_start[4], lvl_w[4], lvl_stride[4];
+  const FrameMeta* meta;          // device [B] or nullptr (no class filter)
+  const tcd_class_filter* tables; // device [kMaxFilterTables]
 };
 // evs (optional): 8 events, recorded as a pair around each of the 4 kernels (profiling pass)
 int postproc_launch(const PostBuffers& pb, int raw, cudaStream_t stream, cudaEvent_t* evs = nullptr);
+int class_filter_rows_launch(const tcd_class_filter* tables, int table, const float* rows_dev, int n, float rw, float rh,
+                             int* keep_dev, cudaStream_t stream);
 
 // ---- motion (motion.cu)
 constexpr int kMogModes = 5;

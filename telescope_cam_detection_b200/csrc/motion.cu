@@ -499,12 +499,7 @@ static size_t blur_smem(int ksize) {
 
 int blur_launch(const uint8_t* src, const BlurArgs& a, uint8_t* dst, uint8_t* prev,
                 unsigned int* counter, cudaStream_t stream) {
-  static bool attr_done = false;
-  if (!attr_done) {
-    cudaFuncSetAttribute(blur_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                         (int)blur_smem(kBlurMaxK));
-    attr_done = true;
-  }
+  if (int rc = ensure_dyn_smem((const void*)blur_kernel, blur_smem(kBlurMaxK))) return rc;
   bool small_taps = true;
   for (int t = 0; t < a.ksize; ++t) small_taps = small_taps && a.k[t] <= 255;
   if (a.ksize == 21 && small_taps) {

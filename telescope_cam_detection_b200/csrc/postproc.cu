@@ -202,74 +202,166 @@ __global__ void __launch_bounds__(64) nms_mask_kernel(const PostBuffers pb) {
   }
 }
 
-__global__ void __launch_bounds__(256) nms_reduce_kernel(const PostBuffers pb, const int smem_rows) {
-  extern __shared__ unsigned long long sm[];
+// Per-class filter of InferenceEngine._post_process_detections (src/inference_engine_yolox.py:505-534) and the
+// wildlife mask of YOLOXDetector._format_model_output_to_detections (src/yolox_detector.py:258), evaluated on a
+// kept row exactly as the Python code does: coordinates scaled in fp32 (np.float32 * weak Python float), then
+// widened; ensure_valid_bbox (swap, minimum size 1), area and every comparison in double.
+__device__ __forceinline__ bool class_filter_pass(const tcd_class_filter& f, const float* row, const float rw,
+                                                  const float rh) {
+  const int cid = (int)row[6];
+  if (cid < 0 || cid >= TCD_MAX_CLASSES) return false;
+  if (!((f.class_mask[cid >> 6] >> (cid & 63)) & 1ull)) return false;
+  double x1 = (double)(row[0] * rw), y1 = (double)(row[1] * rh);
+  double x2 = (double)(row[2] * rw), y2 = (double)(row[3] * rh);
+  const double conf = (double)(row[4] * row[5]);
+  if (x1 > x2) { const double t = x1; x1 = x2; x2 = t; }
+  if (x2 - x1 < 1.0) x2 = x1 + 1.0;
+  if (y1 > y2) { const double t = y1; y1 = y2; y2 = t; }
+  if (y2 - y1 < 1.0) y2 = y1 + 1.0;
+  const double area = (x2 - x1) * (y2 - y1);
+  if (conf < f.cls_conf[cid]) return false;
+  if (f.min_area > 0.0 && area < f.min_area) return false;
+  if (area < f.cls_min_area[cid] || area > f.cls_max_area[cid]) return false;
+  return true;
+}
+
+// One CTA per frame.  The greedy scan of torchvision's nms (row i is kept unless an earlier kept row
+// suppresses it) is serial only INSIDE a block of 64 rows, where it is 64 register steps of one warp on the
+// block's diagonal mask words; the effect of a block's kept rows on all later blocks is then ORed into the
+// removal words by the whole CTA in parallel.  (Round 1 scanned all n rows with one warp: 67 us for ~1000
+// candidates per frame.)  Kept rows then go through the per-camera class filter (table 0: none) and the
+// first max_det survivors are written in score order.
+__global__ void __launch_bounds__(256) nms_reduce_kernel(const PostBuffers pb) {
+  __shared__ unsigned long long remv[kPostMaxWords];
+  __shared__ unsigned long long keepw[kPostMaxWords];
+  __shared__ int base[kPostMaxWords + 1];
+  __shared__ int s_cnt[8];
   const int b = blockIdx.x;
   const int n = pb.n_sorted[b];
   const int nb = (n + 63) >> 6;
   const int words = pb.cap >> 6;
-  unsigned long long* remv = sm;                 // [words]
-  int* keep = reinterpret_cast<int*>(sm + words);  // [cap]
-  unsigned long long* mrows = sm + words + (pb.cap + 1) / 2;  // [smem_rows * nb] when it fits
-  __shared__ int s_nk;
   const unsigned long long* gmask = pb.mask + (size_t)b * pb.cap * words;
-  const bool staged = (n <= smem_rows) && ((size_t)n * nb <= (size_t)smem_rows * 16);
-  for (int i = threadIdx.x; i < nb; i += 256) remv[i] = 0ull;
-  if (staged) {
-    for (int i = threadIdx.x; i < n * nb; i += 256) {
-      const int r = i / nb, w = i - r * nb;
-      mrows[i] = (w >= (r >> 6)) ? gmask[(size_t)r * words + w] : 0ull;
-    }
-  }
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  for (int i = tid; i < nb; i += 256) { remv[i] = 0ull; keepw[i] = 0ull; }
   __syncthreads();
-  if (threadIdx.x < 32) {
-    const int lane = threadIdx.x;
-    int nk = 0;
-    for (int i = 0; i < n; ++i) {
-      const int w = i >> 6;
-      const unsigned long long cur = remv[w];
-      if (!((cur >> (i & 63)) & 1ull)) {
-        if (lane == 0) keep[nk] = i;
-        ++nk;
-        if (staged) {
-          for (int ww = w + lane; ww < nb; ww += 32) remv[ww] |= mrows[i * nb + ww];
-        } else {
-          for (int ww = w + lane; ww < nb; ww += 32) remv[ww] |= gmask[(size_t)i * words + ww];
+  for (int kb = 0; kb < nb; ++kb) {
+    if (warp == 0) {
+      const int r0 = kb * 64 + lane, r1 = r0 + 32;
+      const unsigned long long d0 = r0 < n ? gmask[(size_t)r0 * words + kb] : 0ull;
+      const unsigned long long d1 = r1 < n ? gmask[(size_t)r1 * words + kb] : 0ull;
+      unsigned long long cur = remv[kb], kept = 0ull;
+      const int lim = min(64, n - kb * 64);
+      for (int i = 0; i < lim; ++i) {
+        if (!((cur >> i) & 1ull)) {          // warp-uniform
+          kept |= 1ull << i;
+          cur |= __shfl_sync(0xffffffffu, i < 32 ? d0 : d1, i & 31);
         }
-        __syncwarp();
+      }
+      if (lane == 0) keepw[kb] = kept;
+    }
+    __syncthreads();
+    const unsigned long long kept = keepw[kb];
+    const int nw = nb - kb - 1;              // later words this block's kept rows may mark
+    if (nw > 0) {
+      for (int e = tid; e < 64 * nw; e += 256) {
+        const int r = e / nw, w = kb + 1 + (e - r * nw);
+        if ((kept >> r) & 1ull) {
+          const unsigned long long m = gmask[(size_t)(kb * 64 + r) * words + w];
+          if (m) atomicOr(&remv[w], m);
+        }
       }
     }
-    if (lane == 0) s_nk = nk;
+    __syncthreads();
+  }
+  // class filter on the kept rows (in place: keepw loses the rows that fail)
+  const float* srec = pb.srec + (size_t)b * pb.cap * 8;
+  int limit = pb.max_out;
+  if (pb.meta != nullptr && pb.meta[b].table > 0) {
+    const tcd_class_filter& f = pb.tables[pb.meta[b].table];
+    const float rw = pb.meta[b].ratio_w, rh = pb.meta[b].ratio_h;
+    for (int i = tid; i < n; i += 256)
+      if (((keepw[i >> 6] >> (i & 63)) & 1ull) && !class_filter_pass(f, srec + (size_t)i * 8, rw, rh))
+        atomicAnd(&keepw[i >> 6], ~(1ull << (i & 63)));
+    const int md = f.max_det < 1 ? 1 : f.max_det;   // `if len(kept) >= max_det: break` runs after the first append
+    if (md < limit) limit = md;
+    __syncthreads();
+  }
+  if (warp == 0) {
+    int run = 0;
+    for (int w0 = 0; w0 < nb; w0 += 32) {
+      const int w = w0 + lane;
+      const int c = w < nb ? __popcll(keepw[w]) : 0;
+      int inc = c;
+#pragma unroll
+      for (int off = 1; off < 32; off <<= 1) {
+        const int v = __shfl_up_sync(0xffffffffu, inc, off);
+        if (lane >= off) inc += v;
+      }
+      if (w < nb) base[w] = run + inc - c;
+      run += __shfl_sync(0xffffffffu, inc, 31);
+    }
+    if (lane == 0) s_cnt[0] = run;
   }
   __syncthreads();
-  int nk = s_nk;
-  if (nk > pb.max_out) nk = pb.max_out;
-  const float* srec = pb.srec + (size_t)b * pb.cap * 8;
+  int nk = s_cnt[0];
+  if (nk > limit) nk = limit;
   float* out = pb.out_dets + (size_t)b * pb.max_out * 7;
-  for (int i = threadIdx.x; i < nk * 7; i += 256) {
-    const int r = i / 7, e = i - r * 7;
-    out[i] = srec[(size_t)keep[r] * 8 + e];
+  for (int i = tid; i < n; i += 256) {
+    const unsigned long long kw = keepw[i >> 6];
+    if ((kw >> (i & 63)) & 1ull) {
+      const int pos = base[i >> 6] + __popcll(kw & ((1ull << (i & 63)) - 1ull));
+      if (pos < nk) {
+        const float* r = srec + (size_t)i * 8;
+        float* o = out + (size_t)pos * 7;
+#pragma unroll
+        for (int e = 0; e < 7; ++e) o[e] = r[e];
+      }
+    }
   }
-  if (threadIdx.x == 0) pb.out_counts[b] = nk;
+  if (tid == 0) pb.out_counts[b] = nk;
 }
 
-size_t post_reduce_smem_bytes(int cap, int smem_rows) {
-  const int words = cap >> 6;
-  return sizeof(unsigned long long) * ((size_t)words + (cap + 1) / 2 + (size_t)smem_rows * 16);
+// Parity tap: the class filter alone on caller-supplied rows [n,7] (one CTA; same predicate, same order-preserving
+// cut at max_det as the tail of nms_reduce_kernel).  keep[i] = 1 when row i survives.
+__global__ void __launch_bounds__(256)
+class_filter_rows_kernel(const tcd_class_filter* tables, int table, const float* rows, int n, float rw, float rh,
+                         int* keep) {
+  __shared__ int s_run;
+  const tcd_class_filter& f = tables[table];
+  if (threadIdx.x == 0) s_run = 0;
+  __syncthreads();
+  const int md = f.max_det < 1 ? 1 : f.max_det;
+  for (int i0 = 0; i0 < n; i0 += 256) {
+    const int i = i0 + threadIdx.x;
+    const bool pass = i < n && class_filter_pass(f, rows + (size_t)i * 7, rw, rh);
+    // order-preserving rank of this row among the survivors: ballot per warp + serial add over the 8 warps
+    __shared__ int wcnt[8];
+    const unsigned bal = __ballot_sync(0xffffffffu, pass);
+    if ((threadIdx.x & 31) == 0) wcnt[threadIdx.x >> 5] = __popc(bal);
+    __syncthreads();
+    int before = s_run;
+    for (int w = 0; w < (int)(threadIdx.x >> 5); ++w) before += wcnt[w];
+    before += __popc(bal & ((1u << (threadIdx.x & 31)) - 1u));
+    if (i < n) keep[i] = (pass && before < md) ? 1 : 0;
+    __syncthreads();
+    if (threadIdx.x == 0) { int t = 0; for (int w = 0; w < 8; ++w) t += wcnt[w]; s_run += t; }
+    __syncthreads();
+  }
+}
+
+int class_filter_rows_launch(const tcd_class_filter* tables, int table, const float* rows_dev, int n, float rw, float rh,
+                             int* keep_dev, cudaStream_t stream) {
+  class_filter_rows_kernel<<<1, 256, 0, stream>>>(tables, table, rows_dev, n, rw, rh, keep_dev);
+  g_launch_count.fetch_add(1, std::memory_order_relaxed);
+  return cudaGetLastError() == cudaSuccess ? TCD_OK : TCD_ERR_CUDA;
 }
 
 int postproc_launch(const PostBuffers& pb, int raw, cudaStream_t stream, cudaEvent_t* evs) {
-  static bool attr_done = false;
-  const int smem_rows = 1024;
-  const size_t red_smem = post_reduce_smem_bytes(pb.cap, smem_rows);
+  TCD_REQUIRE(pb.cap % 64 == 0 && (pb.cap >> 6) <= kPostMaxWords, "postproc: cap %d outside the mask word budget", pb.cap);
   int P = 1;
   while (P < pb.cap) P <<= 1;
   const size_t sort_smem = (size_t)P * 8;
-  if (!attr_done) {
-    cudaFuncSetAttribute(sort_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sort_smem);
-    cudaFuncSetAttribute(nms_reduce_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)red_smem);
-    attr_done = true;
-  }
+  if (int rc = ensure_dyn_smem((const void*)sort_kernel, sort_smem)) return rc;
   cudaMemsetAsync(pb.cand_count, 0, sizeof(int) * pb.B, stream);
   const int warps = pb.B * pb.A;
   if (evs) cudaEventRecord(evs[0], stream);
@@ -279,7 +371,7 @@ int postproc_launch(const PostBuffers& pb, int raw, cudaStream_t stream, cudaEve
   if (evs) { cudaEventRecord(evs[3], stream); cudaEventRecord(evs[4], stream); }
   nms_mask_kernel<<<dim3(296, pb.B), 64, 0, stream>>>(pb);
   if (evs) { cudaEventRecord(evs[5], stream); cudaEventRecord(evs[6], stream); }
-  nms_reduce_kernel<<<pb.B, 256, red_smem, stream>>>(pb, smem_rows);
+  nms_reduce_kernel<<<pb.B, 256, 0, stream>>>(pb);
   if (evs) cudaEventRecord(evs[7], stream);
   g_launch_count.fetch_add(4, std::memory_order_relaxed);
   cudaError_t e = cudaGetLastError();

@@ -206,11 +206,7 @@ int preproc_launch(const tcd_preproc_cfg* cfg, const PreFrame* frames_host, cons
     a.smem_rows = max_rows;
     a.smem_row_bytes = max_row_bytes;
   }
-  static bool attr_done = false;
-  if (!attr_done) {
-    cudaFuncSetAttribute(preproc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024);
-    attr_done = true;
-  }
+  if (int rc = ensure_dyn_smem((const void*)preproc_kernel, smem)) return rc;
   dim3 grid(cdiv(cfg->out_w, kPreTileW), cdiv(cfg->out_h, kPreTileH), B);
   preproc_kernel<<<grid, kPreThreads, smem, stream>>>(frames_dev, a, out_dev);
   g_launch_count.fetch_add(1, std::memory_order_relaxed);

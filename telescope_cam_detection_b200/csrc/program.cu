@@ -126,6 +126,7 @@ void tcd_program_destroy(tcd_program* p) {
 
 tcd_status tcd_program_alloc(tcd_program* p, size_t bytes, void** out_dev) {
   TCD_REQUIRE(p && out_dev && bytes > 0, "program_alloc: bad argument");
+  TCD_CUDA_OK(cudaSetDevice(p->device));
   void* d = nullptr;
   TCD_CUDA_OK(cudaMalloc(&d, (bytes + 1023) & ~(size_t)1023));
   TCD_CUDA_OK(cudaMemset(d, 0, (bytes + 1023) & ~(size_t)1023));
@@ -145,6 +146,7 @@ tcd_status tcd_program_upload(tcd_program* p, const void* host, size_t bytes, vo
 tcd_status tcd_program_add_conv(tcd_program* p, const tcd_conv_desc* c) {
   TCD_REQUIRE(p && c && c->x && c->w_host && c->bias_host && (c->y || c->out_f32), "add_conv: null argument");
   TCD_REQUIRE(p->graph == nullptr, "add_conv: program already captured");
+  TCD_CUDA_OK(cudaSetDevice(p->device));
   const int cin_pad = (c->cin + 15) / 16 * 16;
   const bool f32 = c->out_f32 != nullptr;
   const int cout_pad = f32 ? (c->cout + 15) / 16 * 16 : c->cout;
@@ -242,6 +244,7 @@ tcd_status tcd_program_run(tcd_program* p, int32_t graph) {
 
 tcd_status tcd_program_sync(tcd_program* p) {
   TCD_REQUIRE(p, "program_sync: null program");
+  TCD_CUDA_OK(cudaSetDevice(p->device));
   cudaError_t e = cudaStreamSynchronize(p->stream);
   if (e != cudaSuccess) {
     set_last_error("program_sync: %s", cudaGetErrorString(e));
@@ -263,6 +266,7 @@ double tcd_program_op_flops(const tcd_program* p, int32_t idx) {
 
 tcd_status tcd_program_profile(tcd_program* p, int32_t iters, float* op_ms, int32_t cap) {
   TCD_REQUIRE(p && op_ms && iters >= 1 && cap >= (int)p->ops.size(), "program_profile: bad argument");
+  TCD_CUDA_OK(cudaSetDevice(p->device));
   const size_t n = p->ops.size();
   std::vector<cudaEvent_t> ev(2 * n);
   for (auto& e : ev) TCD_CUDA_OK(cudaEventCreate(&e));

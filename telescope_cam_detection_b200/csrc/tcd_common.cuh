@@ -36,6 +36,11 @@ const char* status_name(int s);
 
 static inline int cdiv(int a, int b) { return (a + b - 1) / b; }
 
+// Raise cudaFuncAttributeMaxDynamicSharedMemorySize of `fn` on the CURRENT device to at least `bytes`.
+// The attribute is per device and per function: the high-water mark is kept per (device, fn) under a
+// mutex, so a second GPU in the process, or a later handle that needs more, gets its own opt-in.
+int ensure_dyn_smem(const void* fn, size_t bytes);
+
 // ---------------------------------------------------------------- device PTX wrappers
 #ifdef __CUDACC__
 

@@ -288,11 +288,7 @@ int mha_launch(const void* q, int ldq, int qoff, const void* k, int ldk, int kof
   TCD_REQUIRE(smem <= 200 * 1024, "mha: %d keys do not fit shared memory", Tk);
   TCD_REQUIRE(ldq % 8 == 0 && ldk % 8 == 0 && ldv % 8 == 0 && ldo % 8 == 0 && qoff % 8 == 0 && koff % 8 == 0 &&
                   voff % 8 == 0, "mha: leading dims / offsets must be multiples of 8");
-  static size_t attr_set = 0;
-  if (smem > 48 * 1024 && smem > attr_set) {
-    TCD_CUDA_OK(cudaFuncSetAttribute(mha_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    attr_set = smem;
-  }
+  if (int rc = ensure_dyn_smem((const void*)mha_kernel, smem)) return rc;
   mha_kernel<<<dim3(cdiv(Tq, 64), heads, N), 128, smem, st>>>(
       (const __nv_bfloat16*)q, ldq, qoff, (const __nv_bfloat16*)k, ldk, koff, (const __nv_bfloat16*)v, ldv,
       voff, (__nv_bfloat16*)out, ldo, Tq, Tk, scale);

@@ -263,11 +263,7 @@ int spp_pool_launch(void* buf, int N, int H, int W, int C, int ctot, cudaStream_
   TCD_REQUIRE(C % 16 == 0 && ctot % 8 == 0, "spp: C %d must be a multiple of 16", C);
   const size_t smem = (size_t)4 * H * W * sizeof(uint4);
   TCD_REQUIRE(smem <= 200 * 1024, "spp: %dx%d plane does not fit shared memory", H, W);
-  static size_t attr_set = 0;
-  if (smem > 48 * 1024 && smem > attr_set) {
-    TCD_CUDA_OK(cudaFuncSetAttribute(spp_pool_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    attr_set = smem;
-  }
+  if (int rc = ensure_dyn_smem((const void*)spp_pool_kernel, smem)) return rc;
   spp_pool_kernel<<<dim3(C / 16, N), 256, smem, stream>>>((uint4*)buf, H, W, C / 8, ctot / 8);
   g_launch_count.fetch_add(1, std::memory_order_relaxed);
   return cudaGetLastError() == cudaSuccess ? TCD_OK : TCD_ERR_CUDA;

@@ -6,17 +6,17 @@ and the previous blurred frame stays on the device.  All-integer path: bit-exact
 """
 import logging
 
-from .engine import EmptyGateEngine
+from .engine import EmptyGateEngine, device_index
 
 logger = logging.getLogger(__name__)
 
 
 class EmptyFrameFilter:
-    def __init__(self, min_motion_area: int = 200, threshold: int = 25, blur_size: int = 21, device: int = 0):
+    def __init__(self, min_motion_area: int = 200, threshold: int = 25, blur_size: int = 21, device=0):
         self.min_motion_area = min_motion_area
         self.threshold = threshold
         self.blur_size = blur_size if blur_size % 2 == 1 else blur_size + 1  # odd, like the reference (:37)
-        self.device = device
+        self.device = device_index(device)   # ordinal, "cuda:N" or N
         self._gate = None
         self.prev_gray = None  # kept for attribute compatibility; the plane itself lives on the GPU
         self.total_frames = 0

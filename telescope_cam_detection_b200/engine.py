@@ -9,6 +9,16 @@ from . import _lib
 from ._lib import check
 
 
+def device_index(device) -> int:
+    """'cuda:1' / 'cuda' / 1 -> ordinal.  Anything else is refused: there is no CPU path."""
+    if isinstance(device, int):
+        return device
+    s = str(device)
+    if not s.startswith("cuda"):
+        raise RuntimeError("the B200 build needs a CUDA device, got %r" % (device,))
+    return int(s.split(":")[1]) if ":" in s else 0
+
+
 def _is_torch(x):
     return type(x).__module__.startswith("torch")
 
@@ -73,6 +83,36 @@ class DetectorEngine:
     def set_thresholds(self, conf, nms):
         check(self.lib.tcd_detector_set_thresholds(self.handle, float(conf), float(nms)), "tcd_detector_set_thresholds")
 
+    def set_class_filter(self, table, cls_conf, cls_min_area=None, cls_max_area=None, min_area=0.0, max_det=1 << 30,
+                         allowed_classes=None):
+        """Device-side per-camera filter table `table` (1 .. MAX_FILTER_TABLES-1), see tcd_class_filter:
+        cls_conf: scalar or {class_id: threshold} over a default given under key None;
+        cls_min_area / cls_max_area: {class_id: area}; allowed_classes: iterable of ids (None = all)."""
+        f = _lib.ClassFilter()
+        default = cls_conf.get(None, float("-inf")) if isinstance(cls_conf, dict) else float(cls_conf)
+        for c in range(_lib.MAX_CLASSES):
+            f.cls_conf[c] = float(cls_conf.get(c, default)) if isinstance(cls_conf, dict) else default
+            f.cls_min_area[c] = float((cls_min_area or {}).get(c, float("-inf")))
+            f.cls_max_area[c] = float((cls_max_area or {}).get(c, float("inf")))
+        f.min_area = float(min_area)
+        f.max_det = int(min(max(int(max_det), -(1 << 30)), 1 << 30))
+        mask = [0, 0]
+        for c in (range(_lib.MAX_CLASSES) if allowed_classes is None else allowed_classes):
+            if 0 <= c < _lib.MAX_CLASSES:
+                mask[c >> 6] |= 1 << (c & 63)
+        f.class_mask[0], f.class_mask[1] = mask
+        check(self.lib.tcd_detector_set_class_filter(self.handle, int(table), C.byref(f)),
+              "tcd_detector_set_class_filter")
+
+    def filter_rows(self, table, rows, orig_h, orig_w):
+        """Parity tap: class filter `table` on rows [n,7] (network pixels, score order) -> bool keep mask."""
+        rows = np.ascontiguousarray(rows, np.float32).reshape(-1, 7)
+        keep = np.zeros((rows.shape[0],), np.int32)
+        check(self.lib.tcd_detector_filter_rows(self.handle, int(table), rows.ctypes.data_as(_lib._F32P), rows.shape[0],
+                                                int(orig_h), int(orig_w), keep.ctypes.data_as(_lib._I32P)),
+              "tcd_detector_filter_rows")
+        return keep.astype(bool)
+
     def _marshal(self, frames):
         if not 1 <= len(frames) <= self.max_batch:
             raise ValueError("batch of %d frames outside [1, %d]" % (len(frames), self.max_batch))
@@ -96,9 +136,15 @@ class DetectorEngine:
               "tcd_detect_batch")
         return self._rows(B)
 
-    def submit(self, slot, frames):
+    def submit(self, slot, frames, filter_tables=None):
+        """Enqueue a batch on pipeline slot `slot`; filter_tables: per-frame class-filter table ids (None = no filter)."""
         p, h, w, s, B, dev, keep = self._marshal(frames)
-        check(self.lib.tcd_detect_batch_async(self.handle, int(slot), p, h, w, s, B, dev), "tcd_detect_batch_async")
+        ft = None
+        if filter_tables is not None:
+            if len(filter_tables) != B:
+                raise ValueError("filter_tables has %d entries for %d frames" % (len(filter_tables), B))
+            ft = _lib.i32_array(filter_tables)
+        check(self.lib.tcd_detector_submit(self.handle, int(slot), p, h, w, s, B, dev, ft), "tcd_detector_submit")
         self._pending[slot] = (B, keep)
 
     def wait(self, slot):
@@ -106,6 +152,9 @@ class DetectorEngine:
         check(self.lib.tcd_detect_batch_wait(self.handle, int(slot), self._out.ctypes.data_as(_lib._F32P),
                                              self._cnt.ctypes.data_as(_lib._I32P)), "tcd_detect_batch_wait")
         return self._rows(B)
+
+    def pending(self, slot):
+        return slot in self._pending
 
     def forward(self, frames):
         p, h, w, s, B, dev, keep = self._marshal(frames)

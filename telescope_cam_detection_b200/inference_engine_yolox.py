@@ -73,6 +73,8 @@ class InferenceEngine:
         self.last_drop_warning_time = 0
         self.drop_count_since_warning = 0
 
+        self._filter_id: Optional[int] = None      # device-side copy of the per-class tables (K7), see _device_filter
+        self._filter_owner: Optional[Any] = None
         self.memory_manager = MemoryManager(device=self.device)
         self.degradation_active = False
         self.original_input_size = self.input_size
@@ -82,7 +84,8 @@ class InferenceEngine:
         if efc and efc.get("enabled", False):
             self.empty_frame_filter = EmptyFrameFilter(min_motion_area=efc.get("min_motion_area", 200),
                                                        threshold=efc.get("threshold", 25),
-                                                       blur_size=efc.get("blur_size", 21))
+                                                       blur_size=efc.get("blur_size", 21),
+                                                       device=self.device if str(self.device).startswith("cuda") else 0)
         self.sparse_detection_enabled = False
         self.keyframe_interval = 1
         self.sparse_mode = "simple"
@@ -175,10 +178,13 @@ class InferenceEngine:
                 cname = item.get("camera_name", self.camera_name)
                 t0 = time.time()
                 if self.shared_coordinator:
-                    self.shared_coordinator.infer_async(
-                        frame=frame, camera_id=cid,
-                        callback=lambda raw, f=frame, i=fid, t=ts, c=cid, n=cname, s=t0:
-                            self._handle_inference_callback(raw, f, i, t, c, n, s))
+                    cb = (lambda raw, f=frame, i=fid, t=ts, c=cid, n=cname, s=t0:
+                          self._handle_inference_callback(raw, f, i, t, c, n, s))
+                    tid = self._device_filter()
+                    if tid is not None:
+                        self.shared_coordinator.infer_async(frame=frame, camera_id=cid, callback=cb, filter_id=tid)
+                    else:
+                        self.shared_coordinator.infer_async(frame=frame, camera_id=cid, callback=cb)
                 else:
                     dets = self._run_inference(frame)
                     dt = time.time() - t0
@@ -217,6 +223,30 @@ class InferenceEngine:
                 self.drop_count_since_warning = 0
 
     # ------------------------------------------------------------------ A6: per-class filtering
+    def _device_filter(self, refresh: bool = False) -> Optional[int]:
+        """This camera's conf / area / max_det tables as a device-side filter table of the detector that will
+        run its frames (its own, or the coordinator's), so that the rows crossing PCIe are already the ones
+        _post_process_detections keeps.  None when the detector has no such facility (any other detector)."""
+        det = self.detector
+        if det is None and self.shared_coordinator is not None and getattr(self.shared_coordinator,
+                                                                            "supports_filter_ids", False):
+            det = getattr(self.shared_coordinator, "detector", None)
+        if det is None or not hasattr(det, "register_class_filter"):
+            return None
+        if self._filter_id is not None and self._filter_owner is det and not refresh:
+            return self._filter_id
+        with self.settings_lock:
+            args = (self.conf_threshold, dict(self.class_confidence_overrides), self.min_box_area,
+                    dict(self.class_size_constraints), self.max_det)
+        try:
+            self._filter_id = det.register_class_filter(*args, table=self._filter_id if self._filter_owner is det
+                                                        else None)
+            self._filter_owner = det
+        except Exception as e:
+            logger.warning("device-side class filter unavailable (%s); filtering on the host only", e)
+            self._filter_id, self._filter_owner = None, None
+        return self._filter_id
+
     def _post_process_detections(self, detections: List[Dict[str, Any]], frame) -> List[Dict[str, Any]]:
         """ensure_valid_bbox (area becomes float), per-class confidence override else the global
         threshold, global minimum area, per-class min/max area, stop at max_det, then Stage 2
@@ -245,7 +275,9 @@ class InferenceEngine:
 
     # ------------------------------------------------------------------ standalone path
     def _process_and_store_detections(self, frame):
-        dets = self._post_process_detections(self.detector.detect(frame), frame)
+        tid = self._device_filter()
+        raw = self.detector.detect(frame) if tid is None else self.detector.detect(frame, filter_id=tid)
+        dets = self._post_process_detections(raw, frame)
         self.last_detections = dets
         return dets
 
@@ -314,6 +346,8 @@ class InferenceEngine:
                 changed.append("class_size_constraints: %s" % class_size_constraints)
             if changed:
                 logger.info("Updated inference settings for %s: %s", self.camera_id, ", ".join(changed))
+        if changed and self._filter_id is not None:
+            self._device_filter(refresh=True)   # outside the lock: it takes its own snapshot
 
     def _apply_degradation(self, recommendations: Dict[str, Any]):
         if not recommendations:

@@ -15,7 +15,7 @@ from typing import Any, Dict, List, Tuple
 import numpy as np
 
 from .bbox_utils import ensure_valid_bbox
-from .engine import Mog2Engine
+from .engine import Mog2Engine, device_index
 
 logger = logging.getLogger(__name__)
 
@@ -23,7 +23,7 @@ logger = logging.getLogger(__name__)
 class MotionFilter:
     def __init__(self, history: int = 500, var_threshold: int = 16, detect_shadows: bool = True,
                  min_motion_area: int = 100, motion_required: bool = True, motion_blur_size: int = 21,
-                 min_motion_ratio: float = 0.05, device: int = 0):
+                 min_motion_ratio: float = 0.05, device=0):
         self.history = history
         self.var_threshold = var_threshold
         self.detect_shadows = detect_shadows
@@ -31,7 +31,7 @@ class MotionFilter:
         self.motion_required = motion_required
         self.motion_blur_size = motion_blur_size if motion_blur_size % 2 == 1 else motion_blur_size + 1
         self.min_motion_ratio = min_motion_ratio
-        self.device = device
+        self.device = device_index(device)   # ordinal, "cuda:N" or N
         self.bg_subtractor = None  # Mog2Engine, created at the first frame (needs the frame size)
         self._stale = True
         self.total_frames = 0

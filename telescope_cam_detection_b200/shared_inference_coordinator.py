@@ -7,9 +7,10 @@ callback gets `[]`; a failing batch gives every request in it `callback([])`; ca
 on the coordinator thread in request order; `get_stats()` has the same keys.
 
 What changes underneath: when the detector offers the split-phase `submit_batch/finish_batch`
-pair (YOLOXDetector of this package), batch k+1 is collected and its frames are copied to the
-GPU while batch k is still computing (two pipeline slots), instead of the GPU idling while
-Python formats results.  No allocator hygiene calls: libtcd works out of a static arena, so the
+pair (YOLOXDetector of this package), batches are submitted to every pipeline slot the library
+has (`detector.num_slots`: engines x lanes) before the oldest one is read back, so batch k+1..k+n
+are collected, uploaded and computing while Python formats the results of batch k, instead of the
+GPU idling behind the callbacks.  Results are delivered in submission order.  No allocator hygiene calls: libtcd works out of a static arena, so the
 reference's `empty_cache()` every 50 batches (:273-276) has nothing to do.
 """
 import logging
@@ -28,6 +29,7 @@ class PendingInference:
     callback: Callable[[List[Dict[str, Any]]], None]
     enqueue_time: float
     camera_id: Optional[str] = None
+    filter_id: Optional[int] = None   # addition: device-side class-filter table of the requesting camera
 
 
 class SharedInferenceCoordinator:
@@ -85,11 +87,14 @@ class SharedInferenceCoordinator:
         self.stop()
 
     # ------------------------------------------------------------------ producer side
+    supports_filter_ids = True
+
     def infer_async(self, frame: Any, callback: Callable[[List[Dict[str, Any]]], None],
-                    camera_id: Optional[str] = None):
+                    camera_id: Optional[str] = None, filter_id: Optional[int] = None):
         if not self.running:
             raise RuntimeError("Coordinator not running - call start() first")
-        req = PendingInference(frame=frame, callback=callback, enqueue_time=time.time(), camera_id=camera_id)
+        req = PendingInference(frame=frame, callback=callback, enqueue_time=time.time(), camera_id=camera_id,
+                               filter_id=filter_id)
         with self.queue_condition:
             if len(self.pending_queue) >= self.max_queue_depth:
                 victim = self.pending_queue.popleft()  # drop the oldest, tell its owner (reference :151-164)
@@ -171,29 +176,42 @@ class SharedInferenceCoordinator:
                 except Exception as e:
                     logger.error("Error in coordinator loop: %s", e, exc_info=True)
             return
-        inflight = None  # (slot, batch, t_submit)
-        slot = 0
+        n_slots = max(1, int(getattr(self.detector, "num_slots", 2) or 2))
+        inflight: deque = deque()        # (slot, batch, t_submit), oldest first
+        free = list(range(n_slots))
         while not self.stop_event.is_set():
             try:
-                # with a batch on the GPU, do not block: finish it as soon as nothing else is queued
-                batch = self._collect_batch(block=inflight is None)
-                submitted = None
+                batch = []
+                if free:
+                    # with batches on the GPU, do not block: read the oldest back as soon as nothing is queued
+                    batch = self._collect_batch(block=not inflight)
                 if batch:
                     t0 = time.time()
                     self._note_waits(batch, t0)
+                    slot = free.pop(0)
                     try:
-                        self.detector.submit_batch(slot, [r.frame for r in batch])
-                        submitted = (slot, batch, t0)
-                        slot ^= 1
+                        fids = [r.filter_id for r in batch]
+                        if any(f is not None for f in fids):
+                            self.detector.submit_batch(slot, [r.frame for r in batch], fids)
+                        else:
+                            self.detector.submit_batch(slot, [r.frame for r in batch])
+                        inflight.append((slot, batch, t0))
                     except Exception as e:
+                        free.append(slot)
                         self._fail(batch, e)
-                if inflight is not None:
-                    self._finish(inflight)
-                inflight = submitted
+                    if free:
+                        with self.queue_lock:
+                            more = bool(self.pending_queue)
+                        if more:
+                            continue     # keep filling slots while requests are waiting
+                if inflight:
+                    item = inflight.popleft()
+                    self._finish(item)
+                    free.append(item[0])
             except Exception as e:
                 logger.error("Error in coordinator loop: %s", e, exc_info=True)
-        if inflight is not None:
-            self._finish(inflight)
+        while inflight:
+            self._finish(inflight.popleft())
 
     def _finish(self, inflight):
         s, batch, t0 = inflight

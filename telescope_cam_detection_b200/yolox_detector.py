@@ -19,6 +19,7 @@ import numpy as np
 from .coco_constants import COCO_CLASSES, MAMMAL_CLASS_IDS, WILDLIFE_CLASSES
 
 logger = logging.getLogger(__name__)
+_WILDLIFE_IDS = np.array(sorted(WILDLIFE_CLASSES), np.int64)
 
 _VARIANTS = {"yolox-s": (0.33, 0.50), "yolox-m": (0.67, 0.75), "yolox-l": (1.0, 1.0), "yolox-x": (1.33, 1.25),
              "yolox-tiny": (0.33, 0.375), "yolox-nano": (0.33, 0.25)}
@@ -62,7 +63,8 @@ class YOLOXDetector:
                  device: str = "cuda:0", conf_threshold: float = 0.25, nms_threshold: float = 0.45,
                  input_size: tuple = (640, 640), wildlife_only: bool = True, use_tensorrt: bool = False,
                  state_dict: Optional[dict] = None, max_batch: int = 8, max_src: tuple = (1080, 1920),
-                 max_out: int = 1024):
+                 max_out: int = 1024, pre_mode: str = "stretch"):
+        # max_src sizes the initial host-frame staging buffers only: a larger frame grows them on arrival
         self.model_name = model_name
         self.model_path = model_path
         self.device = device
@@ -77,7 +79,12 @@ class YOLOXDetector:
         self._state_dict = state_dict
         self._blob = None
         self._max_batch, self._max_src, self._max_out = int(max_batch), tuple(max_src), int(max_out)
-        self._pushed = None       # (conf, nms, input_size) the engine currently holds
+        if pre_mode not in ("stretch", "letterbox"):
+            raise ValueError("pre_mode must be 'stretch' (what the reference code does) or 'letterbox'")
+        self._pre_mode = pre_mode
+        self.result_hook = None   # optional callable(slot), run after a slot's batch has finished (multi-GPU forwarders)
+        self._pushed = None       # (conf, nms, input_size, wildlife_only) the engine currently holds
+        self._tables = {}         # class-filter table id -> spec (re-pushed when the engine is rebuilt)
         self._sizes = {}          # slot -> [(h, w)] of the frames in flight
 
     # ------------------------------------------------------------------ loading
@@ -123,24 +130,77 @@ class YOLOXDetector:
             self.model = None
         eng = DetectorEngine(self._blob, input_size=tuple(self.input_size), max_batch=self._max_batch,
                              num_classes=80, max_out=self._max_out, max_src=self._max_src,
-                             device=_device_index(self.device))
+                             device=_device_index(self.device), pre_mode=1 if self._pre_mode == "letterbox" else 0)
         eng.set_thresholds(self.conf_threshold, self.nms_threshold)
         self.model = _ModelHandle(eng)
-        self._pushed = (self.conf_threshold, self.nms_threshold, tuple(self.input_size))
+        self._pushed = (self.conf_threshold, self.nms_threshold, tuple(self.input_size), bool(self.wildlife_only))
+        self._push_tables()
 
     def _sync_settings(self):
         """conf/nms/input_size are plain attributes that callers overwrite (hot reload, OOM degradation:
         src/inference_engine_yolox.py:677-684,730-732); bring the engine up to date before a launch."""
-        want = (self.conf_threshold, self.nms_threshold, tuple(self.input_size))
+        want = (self.conf_threshold, self.nms_threshold, tuple(self.input_size), bool(self.wildlife_only))
         if want == self._pushed:
             return
         if want[2] != self._pushed[2]:
             self._build_engine()  # new activation arena + graphs for the new network size
             if self.exp is not None:
                 self.exp.test_size = want[2]
-        else:
+            return
+        if want[:2] != self._pushed[:2]:
             self.model.engine.set_thresholds(want[0], want[1])
+        if want[3] != self._pushed[3]:
             self._pushed = want
+            self._push_tables()
+        self._pushed = want
+
+    # ------------------------------------------------------------------ device-side class filters (K7)
+    _OWN_TABLE = 1   # wildlife mask only: what detect()/detect_batch() apply when the caller names no table
+
+    def _push_table(self, tid):
+        spec = self._tables[tid]
+        allowed = sorted(WILDLIFE_CLASSES) if self.wildlife_only else None
+        if spec is None:   # the detector's own table
+            self.model.engine.set_class_filter(tid, float("-inf"), allowed_classes=allowed)
+            return
+        conf, overrides, min_area, limits, max_det = spec
+        ids = {n: i for i, n in enumerate(COCO_CLASSES)}
+        cc = {None: float(conf)}
+        cc.update({ids[n]: float(v) for n, v in overrides.items() if n in ids})
+        lo = {ids[n]: float(v["min"]) for n, v in limits.items() if n in ids and "min" in v}
+        hi = {ids[n]: float(v["max"]) for n, v in limits.items() if n in ids and "max" in v}
+        self.model.engine.set_class_filter(tid, cc, lo, hi, min_area=float(min_area), max_det=int(max_det),
+                                           allowed_classes=allowed)
+
+    def _push_tables(self):
+        if self.model is None:
+            return
+        self._tables.setdefault(self._OWN_TABLE, None)
+        for tid in self._tables:
+            self._push_table(tid)
+
+    def register_class_filter(self, conf_threshold, class_confidence_overrides=None, min_box_area=0,
+                              class_size_constraints=None, max_det=300, table=None) -> int:
+        """Install (table=None) or replace the per-camera filter of InferenceEngine._post_process_detections
+        (reference src/inference_engine_yolox.py:505-534) as a device-side table; returns its id, to be passed as
+        `filter_ids` to detect_batch / submit_batch.  The rows that come back are exactly the ones the Python loop
+        would keep (tests/test_gpu_filter.py), so that loop finds nothing left to drop."""
+        from . import _lib
+        if table is None:
+            used = set(self._tables) | {0, self._OWN_TABLE}
+            free = [t for t in range(2, _lib.MAX_FILTER_TABLES) if t not in used]
+            if not free:
+                raise RuntimeError("all %d class-filter tables are in use" % _lib.MAX_FILTER_TABLES)
+            table = free[0]
+        self._tables[table] = (conf_threshold, dict(class_confidence_overrides or {}), min_box_area,
+                               {k: dict(v) for k, v in (class_size_constraints or {}).items()}, max_det)
+        if self.model is not None:
+            self._push_table(table)
+        return table
+
+    def release_class_filter(self, table: int) -> None:
+        if table not in (0, self._OWN_TABLE):
+            self._tables.pop(table, None)
 
     # ------------------------------------------------------------------ data path
     def preprocess(self, img):
@@ -153,7 +213,8 @@ class YOLOXDetector:
         t = t.to("cuda:%d" % dev).contiguous()
         h, w = int(t.shape[0]), int(t.shape[1])
         out = torch.empty((1, 3, self.input_size[0], self.input_size[1]), dtype=torch.float32, device=t.device)
-        engine.preprocess([t.data_ptr()], [h], [w], [t.stride(0)], out.data_ptr(), tuple(self.input_size), layout=0)
+        with torch.cuda.device(dev):
+            engine.preprocess([t.data_ptr()], [h], [w], [t.stride(0)], out.data_ptr(), tuple(self.input_size), layout=0)
         return out
 
     @staticmethod
@@ -164,64 +225,90 @@ class YOLOXDetector:
         return int(shape[0]), int(shape[1])
 
     def _format_model_output_to_detections(self, output: np.ndarray, orig_h: int, orig_w: int) -> List[Dict[str, Any]]:
-        """(n,7) rows [x1,y1,x2,y2,obj,cls,class_id] in network pixels -> detection dicts (reference :222-282)."""
+        """(n,7) rows [x1,y1,x2,y2,obj,cls,class_id] in network pixels -> detection dicts (reference :222-282).
+        One NumPy pass over the table instead of the reference's per-row arithmetic; the dict list is built from
+        Python scalars in one comprehension."""
         if output is None or len(output) == 0:
             return []
         out = np.asarray(output, np.float32)
-        ratio_h = orig_h / self.input_size[0]
-        ratio_w = orig_w / self.input_size[1]
-        # float32 products like the reference's np.float32 * python-float scalars, then widened
-        xs1 = (out[:, 0] * np.float32(ratio_w)).astype(np.float64)
-        ys1 = (out[:, 1] * np.float32(ratio_h)).astype(np.float64)
-        xs2 = (out[:, 2] * np.float32(ratio_w)).astype(np.float64)
-        ys2 = (out[:, 3] * np.float32(ratio_h)).astype(np.float64)
-        conf = (out[:, 4] * out[:, 5]).astype(np.float64)
         cls = out[:, 6].astype(np.int64)
-        dets = []
-        for i in range(out.shape[0]):
-            cid = int(cls[i])
-            if self.wildlife_only and cid not in WILDLIFE_CLASSES:
-                continue
-            x1, y1, x2, y2 = float(xs1[i]), float(ys1[i]), float(xs2[i]), float(ys2[i])
-            dets.append({
-                "class_id": cid,
-                "class_name": COCO_CLASSES[cid] if cid < len(COCO_CLASSES) else "class_%d" % cid,
-                "confidence": float(conf[i]),
-                "bbox": {"x1": x1, "y1": y1, "x2": x2, "y2": y2, "area": int((x2 - x1) * (y2 - y1))},
-            })
-        return dets
+        if self.wildlife_only:
+            keep = np.isin(cls, _WILDLIFE_IDS)
+            if not keep.all():
+                out, cls = out[keep], cls[keep]
+                if len(out) == 0:
+                    return []
+        # float32 products like the reference's np.float32 * python-float scalars, then widened
+        rw, rh = np.float32(orig_w / self.input_size[1]), np.float32(orig_h / self.input_size[0])
+        x1 = (out[:, 0] * rw).astype(np.float64)
+        y1 = (out[:, 1] * rh).astype(np.float64)
+        x2 = (out[:, 2] * rw).astype(np.float64)
+        y2 = (out[:, 3] * rh).astype(np.float64)
+        conf = (out[:, 4] * out[:, 5]).astype(np.float64).tolist()
+        area = ((x2 - x1) * (y2 - y1)).astype(np.int64).tolist()     # int() truncates toward zero, so does astype
+        n_names = len(COCO_CLASSES)
+        return [{"class_id": c, "class_name": COCO_CLASSES[c] if c < n_names else "class_%d" % c, "confidence": cf,
+                 "bbox": {"x1": a, "y1": b, "x2": d, "y2": e, "area": ar}}
+                for c, cf, a, b, d, e, ar in zip(cls.tolist(), conf, x1.tolist(), y1.tolist(), x2.tolist(), y2.tolist(),
+                                                 area)]
 
-    def detect(self, frame) -> List[Dict[str, Any]]:
+    def detect(self, frame, filter_id: Optional[int] = None) -> List[Dict[str, Any]]:
         if self.model is None:
             logger.error("Model not loaded")
             return []
-        return self.detect_batch([frame])[0]
+        return self.detect_batch([frame], None if filter_id is None else [filter_id])[0]
 
-    def detect_batch(self, frames: List[Union[np.ndarray, Any]]) -> List[List[Dict[str, Any]]]:
+    def detect_batch(self, frames: List[Union[np.ndarray, Any]],
+                     filter_ids: Optional[List[int]] = None) -> List[List[Dict[str, Any]]]:
+        """frames -> per-frame detection dicts (reference :323-406).  Lists longer than the arena's batch run as
+        consecutive launches, every pipeline slot of the library in flight before the first result is read.
+        filter_ids (an addition): per-frame class-filter tables from register_class_filter()."""
         if self.model is None:
             logger.error("Model not loaded")
             return [[] for _ in frames]
         if not frames:
             return []
+        mb, n_slots = self._max_batch, self.model.engine.num_slots
         out: List[List[Dict[str, Any]]] = []
-        mb = self._max_batch
-        for i in range(0, len(frames), mb):  # batches larger than the arena run as consecutive launches
-            chunk = frames[i:i + mb]
-            self.submit_batch(0, chunk)
-            out.extend(self.finish_batch(0))
+        inflight = []
+        for k, i in enumerate(range(0, len(frames), mb)):
+            slot = k % n_slots
+            if len(inflight) == n_slots:
+                out.extend(self.finish_batch(inflight.pop(0)))
+            self.submit_batch(slot, frames[i:i + mb], None if filter_ids is None else filter_ids[i:i + mb])
+            inflight.append(slot)
+        for slot in inflight:
+            out.extend(self.finish_batch(slot))
         return out
 
-    # split-phase pair (pipelined coordinator): slot 0/1 own independent streams and arenas
-    def submit_batch(self, slot: int, frames) -> None:
+    # split-phase pair (pipelined coordinator): every slot owns the staging and result table of one batch in flight
+    @property
+    def num_slots(self) -> int:
+        return self.model.engine.num_slots if self.model is not None else 0
+
+    def submit_batch(self, slot: int, frames, filter_ids=None) -> None:
         sizes = [self._frame_hw(f) for f in frames]
         self._sync_settings()
-        self.model.engine.submit(slot, frames)
+        if filter_ids is None:
+            filter_ids = [self._OWN_TABLE if self.wildlife_only else 0] * len(frames)
+        else:
+            filter_ids = [(self._OWN_TABLE if self.wildlife_only else 0) if t is None else t for t in filter_ids]
+        self.model.engine.submit(slot, frames, filter_ids)
         self._sizes[slot] = sizes
 
     def finish_batch(self, slot: int) -> List[List[Dict[str, Any]]]:
         sizes = self._sizes.pop(slot)
         rows = self.model.engine.wait(slot)
+        if self.result_hook is not None:
+            self.result_hook(slot)
+        if self._pre_mode == "letterbox":
+            # boxes come back in letterboxed network pixels: one isotropic ratio r = min(H/h, W/w) (upstream YOLOX demo)
+            return [self._format_letterboxed(r, h, w) for r, (h, w) in zip(rows, sizes)]
         return [self._format_model_output_to_detections(r, h, w) for r, (h, w) in zip(rows, sizes)]
+
+    def _format_letterboxed(self, rows, h, w):
+        r = min(self.input_size[0] / h, self.input_size[1] / w)
+        return self._format_model_output_to_detections(rows, self.input_size[0] / r, self.input_size[1] / r)
 
     # ------------------------------------------------------------------ helpers of the reference API
     def is_wildlife_relevant(self, class_id: int) -> bool:

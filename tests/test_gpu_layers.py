@@ -42,61 +42,85 @@ STAGES = [
 ]
 
 
-def test_stage_activations_match_oracle():
+def _stage_errors(model, blob, frames, pre_mode=0, max_batch=None):
+    """-> list of (buffer, module path, err GPU vs fp32, err bf16-rounding oracle vs fp32, mean / max err GPU vs
+    bf16-rounding oracle), every error relative to the stage's mean |activation|."""
     import torch
-    from oracle.synth_weights import preprocess_ref
+    from oracle.reference_detector import preprocess_cfg
+    from oracle.yolox_lowp import lowp_model
     from telescope_cam_detection_b200.engine import DetectorEngine
 
-    frames = [structured_frame(41), noise_frame(42)]
-    model = oracle_model(0)
-    mods = dict(model.named_modules())
-    taps = {}
-    hooks = [mods[path].register_forward_hook(lambda m, i, o, p=path: taps.__setitem__(p, o.detach()))
-             for _, path, _ in STAGES]
-    x = torch.cat([preprocess_ref(f) for f in frames], 0)
-    with torch.no_grad():
-        model(x)
-    for h in hooks:
-        h.remove()
-    # same taps on the oracle with the build's bf16 rounding points emulated
-    from oracle.yolox_lowp import lowp_model
-    low = lowp_model(model)
-    lmods = dict(low.named_modules())
-    ltaps = {}
-    for _, path, _ in STAGES:
-        lmods[path].register_forward_hook(lambda m, i, o, p=path: ltaps.__setitem__(p, o.detach()))
-    with torch.no_grad():
-        low(x)
+    def taps_of(m, x):
+        mods, taps = dict(m.named_modules()), {}
+        hooks = [mods[path].register_forward_hook(lambda mo, i, o, p=path: taps.__setitem__(p, o.detach()))
+                 for _, path, _ in STAGES]
+        with torch.no_grad():
+            m(x)
+        for h in hooks:
+            h.remove()
+        return taps
 
-    eng = DetectorEngine(oracle_blob(0), input_size=(640, 640), max_batch=2, max_out=64)
+    x = torch.cat([preprocess_cfg(f, (640, 640), "letterbox" if pre_mode else "stretch") for f in frames], 0)
+    taps = taps_of(model, x)
+    ltaps = taps_of(lowp_model(model), x)   # same taps on the oracle with the build's bf16 rounding points emulated
+    eng = DetectorEngine(blob, input_size=(640, 640), max_batch=max_batch or len(frames), max_out=64, pre_mode=pre_mode)
+    out = []
     try:
         eng.forward(frames)
-        report, worst, worst_low, first_low = [], 0.0, 0.0, 0.0
-        for depth, (buf, path, sl) in enumerate(STAGES):
+        for buf, path, sl in STAGES:
             got = eng.read_activation(buf)  # [B,H,W,C] f32
             if sl is not None:
                 got = got[..., sl[0]:sl[1]]
             ref = taps[path].permute(0, 2, 3, 1).numpy()
             assert got.shape == ref.shape, "%s: shape %s vs oracle %s" % (buf, got.shape, ref.shape)
-            scale = float(np.abs(ref).mean()) + 1e-6
-            err = float(np.abs(got - ref).mean()) / scale
             lref = ltaps[path].permute(0, 2, 3, 1).numpy()
-            lerr = float(np.abs(got - lref).mean()) / scale
-            lmax = float(np.abs(got - lref).max()) / scale
-            report.append("%-18s <- %-32s vs fp32 %.4f | vs bf16-rounding oracle mean %.5f max %.4f" % (
-                buf, path, err, lerr, lmax))
-            worst = max(worst, err)
-            worst_low = max(worst_low, lerr)
-            if depth < 4:
-                first_low = max(first_low, lerr)
-        print("\n".join(report))
-        # bf16 rounding is ~0.2-0.4 % per stored activation; 28 stages deep stays well below 3 %
-        assert worst <= 0.03, "\n".join(report)
-        # Against the rounding-point emulation the first stages are bit-identical (measured 0.00000
-        # through stem/dark2.0).  A first bf16 rounding flip (fp32 summation order) then perturbs its
-        # whole receptive field by ~1e-3 relative, which flips a large share of the NEXT roundings:
-        # the two bf16 pipelines decorrelate and settle at the bf16 noise level itself (~0.7 %).
-        assert first_low <= 1e-3, "\n".join(report)
-        assert worst_low <= 0.02, "\n".join(report)
+            scale = float(np.abs(ref).mean()) + 1e-6
+            out.append((buf, path, float(np.abs(got - ref).mean()) / scale, float(np.abs(lref - ref).mean()) / scale,
+                        float(np.abs(got - lref).mean()) / scale, float(np.abs(got - lref).max()) / scale))
     finally:
         eng.close()
+    return out
+
+
+def _report(rows):
+    return "\n".join("%-18s <- %-32s GPU vs fp32 %.4f | bf16-rounding oracle vs fp32 %.4f | GPU vs bf16-rounding "
+                     "oracle mean %.5f max %.4f" % r for r in rows)
+
+
+@pytest.mark.parametrize("B,pre_mode", [(2, 0), (8, 1)], ids=["B2-stretch", "B8-letterbox"])
+def test_stage_activations_match_oracle(B, pre_mode):
+    """B = 2 stretch: the reference's own preprocessing.  B = 8 letterbox: the configuration bench.py times -- the
+    planner is batch-dependent (whole-SM stem plan, tile grouping, resident weights switch on with the tile count),
+    so the plan that produces the headline number is the one compared here."""
+    frames = [structured_frame(41), noise_frame(42)] + [structured_frame(43 + i) for i in range(B - 2)]
+    rows = _stage_errors(oracle_model(0), oracle_blob(0), frames, pre_mode=pre_mode)
+    rep = _report(rows)
+    print(rep)
+    # bf16 rounding is ~0.2-0.4 % per stored activation; 28 stages deep stays well below 3 %
+    assert max(r[2] for r in rows) <= 0.03, rep
+    # Against the rounding-point emulation the first stages are bit-identical (measured 0.00000
+    # through stem/dark2.0).  A first bf16 rounding flip (fp32 summation order) then perturbs its
+    # whole receptive field by ~1e-3 relative, which flips a large share of the NEXT roundings:
+    # the two bf16 pipelines decorrelate and settle at the bf16 noise level itself (~0.7 %).
+    assert max(r[4] for r in rows[:4]) <= 1e-3, rep
+    assert max(r[4] for r in rows) <= 0.02, rep
+
+
+def test_stage_activations_second_weight_set_nonlinear_silu():
+    """SURVEY 8(d)'s BN recipe (gamma ~ U(0.5,1.5), beta ~ N(0,0.1)): pre-activations of order 1-4, so the SiLU
+    epilogue works well outside its linear range (the default set keeps gamma at 0.05-0.15, oracle/synth_weights.py).
+    A random-weight stack at this gain is chaotic -- the CPU emulation of the build's rounding points is itself
+    ~0.5 % from fp32 at the stem and ~30 % at the head (measured) -- so end-to-end tolerances
+    do not apply.  What is asserted: bit-nearness to the rounding-point emulation through the first stages, and at
+    EVERY depth the GPU is no further from fp32 than the emulation is (x1.5 + 0.2 %): the kernels add no error of
+    their own where the activation function is curved."""
+    from oracle import synth_weights
+    from telescope_cam_detection_b200 import weights
+    model = synth_weights.make_model(seed=0, gamma=(0.5, 1.5), beta=(0.0, 0.1))
+    frames = [structured_frame(41), noise_frame(42)]
+    rows = _stage_errors(model, weights.pack_yolox(model.state_dict()), frames)
+    rep = _report(rows)
+    print(rep)
+    assert max(r[4] for r in rows[:2]) <= 2e-3, rep
+    for r in rows:
+        assert r[2] <= 1.5 * r[3] + 0.002, "%s: GPU %.4f from fp32, bf16 emulation %.4f\n%s" % (r[0], r[2], r[3], rep)
