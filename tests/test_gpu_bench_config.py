@@ -30,15 +30,20 @@ def _oracle_rows(frames, mode="letterbox"):
     return out
 
 
-def check_rows(got, ref, max_out, what):
-    """got: our [n,7] table of one frame; ref: the oracle's rows (all of them, score-descending)."""
+def check_rows(got, ref, max_out, what, stats):
+    """got: our [n,7] table of one frame; ref: the oracle's rows (all of them, score-descending).
+    The network outputs agree within north_star's tolerances (test_forward_b8_letterbox_matches_oracle); what can
+    still differ is a greedy-NMS decision whose IoU sits within the bf16 box noise (~0.02) of nms_thre -- with ~500
+    overlapping candidates per synthetic frame a few per cent of the rows are such cases, and one flip can release or
+    suppress a neighbour.  Hence: >= 94 % of the confident oracle rows must be matched (class exact, score 1e-2, box
+    0.75 px) and at most 6 % of ours may be unknown to the oracle."""
     assert got.shape[0] <= max_out
     sc = got[:, 4] * got[:, 5]
     assert np.all(np.diff(sc) <= 1e-7), "%s: rows not score-descending" % what
     assert np.all(sc >= 0.25 - 1e-6)
     if ref.shape[0] == 0:
         assert got.shape[0] <= 2, what
-        return 0
+        return
     rsc = ref[:, 4] * ref[:, 5]
     # the table holds the max_out best rows: compare with the oracle rows above the score of our last row (+ margin)
     floor = 0.27 if got.shape[0] < max_out else max(0.27, float(sc[-1]) + 0.02)
@@ -50,10 +55,11 @@ def check_rows(got, ref, max_out, what):
                                          (np.abs(same[:, 4] * same[:, 5] - row[4] * row[5]) <= 1e-2)).any())
     miss = sum(0 if matched(r, got) else 1 for r in strong)
     extra = sum(0 if matched(g, ref) else 1 for g in got[sc >= floor])
-    # an NMS decision within the bf16 tolerance of the IoU threshold may flip and take a neighbour with it
-    assert miss <= max(2, 0.04 * len(strong)), "%s: %d of %d confident oracle rows unmatched" % (what, miss, len(strong))
-    assert extra <= max(2, 0.04 * len(strong)), "%s: %d confident rows the oracle does not have" % (what, extra)
-    return len(strong)
+    stats.append((what, len(strong), miss, extra))
+    # per frame: one flip can cascade through a chain of overlapping boxes (the CPU emulation of the build's bf16
+    # rounding points, oracle/yolox_lowp.py, differs from fp32 by up to 6 + 5 rows of 182 on these frames)
+    assert miss <= max(3, 0.10 * len(strong)), "%s: %d of %d confident oracle rows unmatched" % (what, miss, len(strong))
+    assert extra <= max(3, 0.10 * len(strong)), "%s: %d confident rows the oracle does not have" % (what, extra)
 
 
 def test_forward_b8_letterbox_matches_oracle(eng):
@@ -72,8 +78,10 @@ def test_forward_b8_letterbox_matches_oracle(eng):
 
 
 def test_every_slot_in_flight_matches_oracle(eng):
-    """12 slots (6 engines x 2 lanes), a different batch on each, all submitted before the first wait -- then again
-    with the batches rotated, so a table, a staging buffer or a graph shared by mistake between lanes shows up."""
+    """12 slots (6 engines x 2 lanes), a different batch on each.  (1) every batch alone (synchronous call) against
+    the oracle; (2) all slots submitted before the first wait -- then again with the batches rotated -- must return
+    BIT-IDENTICAL tables to (1): a table, a staging buffer, a filter table or a graph shared by mistake between
+    lanes or engines shows up as a difference."""
     n_slots = eng.num_slots
     assert n_slots >= 2
     batches = []
@@ -84,8 +92,19 @@ def test_every_slot_in_flight_matches_oracle(eng):
         if s % 4 == 2:
             fr[5] = structured_frame(2600 + s, 720, 1280)       # a second camera size in the same batch
         batches.append(fr)
-    ref = [_oracle_rows(fr) for fr in batches]
-    total = 0
+    stats = []
+    base = []
+    for s, fr in enumerate(batches):
+        rows = eng.detect_batch(fr)
+        ref = _oracle_rows(fr)
+        for b in range(B):
+            check_rows(rows[b], ref[b], MAXO, "batch %d frame %d" % (s, b), stats)
+        base.append(rows)
+    tot = sum(x[1] for x in stats)
+    print("confident oracle rows %d, unmatched %d (%.2f %%), ours unknown to the oracle %d" % (
+        tot, sum(x[2] for x in stats), 100.0 * sum(x[2] for x in stats) / tot, sum(x[3] for x in stats)))
+    assert tot >= 50 * n_slots, "too few confident detections (%d) for the comparison to mean anything" % tot
+    assert sum(x[2] for x in stats) <= 0.04 * tot and sum(x[3] for x in stats) <= 0.04 * tot
     for rot in (0, 5):
         order = [(s + rot) % n_slots for s in range(n_slots)]
         for s in range(n_slots):
@@ -94,8 +113,8 @@ def test_every_slot_in_flight_matches_oracle(eng):
             rows = eng.wait(s)
             assert len(rows) == B
             for b in range(B):
-                total += check_rows(rows[b], ref[order[s]][b], MAXO, "rot %d slot %d frame %d" % (rot, s, b))
-    assert total >= 50 * n_slots, "too few confident detections (%d) for the comparison to mean anything" % total
+                assert np.array_equal(rows[b], base[order[s]][b]), "rot %d slot %d frame %d differs from the " \
+                    "synchronous run of the same batch" % (rot, s, b)
 
 
 def test_host_and_device_frames_agree_on_every_slot(eng):
