@@ -283,8 +283,15 @@ class YOLOXDetector:
                     out.extend(self.finish_batch(inflight.pop(0)))
                 self.submit_batch(slot, frames[i:i + mb], None if filter_ids is None else filter_ids[i:i + mb])
                 inflight.append(slot)
-            for slot in inflight:
-                out.extend(self.finish_batch(slot))
+            while inflight:
+                out.extend(self.finish_batch(inflight.pop(0)))
+        except Exception:
+            for slot in inflight:          # leave no slot with a batch in flight behind a failed call
+                try:
+                    self.finish_batch(slot)
+                except Exception:
+                    pass
+            raise   # like the reference's detect_batch: the coordinator / engine turn it into empty results
         finally:
             if paused:
                 gc.enable()
