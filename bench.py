@@ -55,6 +55,7 @@ def parse_args():
                     help="objectness bias of the seeded weights: -1.4 -> 1.3-1.9 %% of the 8400 anchors pass conf 0.25 "
                          "(SURVEY 8(d) asks for 1-3 %%); round 1 ran -1.0 (6.4 %%, every frame saturating max_out)")
     ap.add_argument("--no-parity-check", action="store_true")
+    ap.add_argument("--quick", action="store_true", help="device-resident leg only, one short JSON line (A/B experiments)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--profile-iters", type=int, default=10)
     ap.add_argument("--latency-iters", type=int, default=30)
@@ -536,6 +537,18 @@ def run_ours(args):
     _pipelined(eng, dev_batches, max(W, 2 * n_slots), None, n_slots)
     r_dev = timed(eng, lambda: _pipelined(eng, dev_batches, K, None, n_slots))
     fps_dev = stream_shard.aggregate_fps(B, K, world, r_dev["ms"])
+    if args.quick:
+        if rank == 0:
+            prof = eng.profile(dev_batches[0], iters=2)
+            conv_ms = sum(o["ms"] for o in prof if o["kind"] == "conv")
+            emit(json.dumps({"quick": True, "batch": B, "value": fps_dev, "ms_per_step": r_dev["ms"] / K, "slots": n_slots,
+                             "engines": n_engines, "eager_conv_ms": conv_ms, "eager_all_ms": sum(o["ms"] for o in prof),
+                             "env": {k: v for k, v in os.environ.items() if k.startswith("TCD_")}}))
+        eng.close()
+        if world > 1:
+            dist.barrier()
+            dist.destroy_process_group()
+        return
 
     # ---- engine handle with host frames (round 1's e2e; kept as a variant)
     g_eng = Gatherer(eng)

@@ -72,6 +72,15 @@ tcd_status tcd_conv2d_nhwc_bf16(const void* x, int32_t N, int32_t H, int32_t W, 
                                 const void* resid, int32_t r_ctot, int32_t r_coff, void* y,
                                 int32_t y_ctot, int32_t y_coff, void* stream);
 
+/* The same with `groups` groups: cout / groups output channels per group, group g reading the cin input channels
+ * at x_coff + g * cin; w is [cout][cin][k][k].  (The second 3x3 convs of the YOLOX head's cls and reg branches run
+ * as ONE such launch over the [cls | reg] buffer.)                                         */
+tcd_status tcd_conv2d_nhwc_bf16_grouped(const void* x, int32_t N, int32_t H, int32_t W, int32_t x_ctot,
+                                        int32_t x_coff, int32_t cin, const float* w, const float* bias,
+                                        int32_t cout, int32_t k, int32_t stride, int32_t silu,
+                                        const void* resid, int32_t r_ctot, int32_t r_coff, void* y,
+                                        int32_t y_ctot, int32_t y_coff, int32_t groups, void* stream);
+
 /* ------------------------------------------------------------------ detector (A1-A5)
  * Replaces YOLOXDetector.load_model / detect / detect_batch, src/yolox_detector.py:84-184,
  * 284-406 together with upstream YOLOX-S forward and yolox.utils.postprocess.            */

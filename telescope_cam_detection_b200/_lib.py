@@ -88,6 +88,9 @@ SIGNATURES = {
     "tcd_conv2d_nhwc_bf16": (C.c_int, [_P, C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_int32,
                                        _F32P, _F32P, C.c_int32, C.c_int32, C.c_int32, C.c_int32, _P,
                                        C.c_int32, C.c_int32, _P, C.c_int32, C.c_int32, _P]),
+    "tcd_conv2d_nhwc_bf16_grouped": (C.c_int, [_P, C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_int32,
+                                               _F32P, _F32P, C.c_int32, C.c_int32, C.c_int32, C.c_int32, _P,
+                                               C.c_int32, C.c_int32, _P, C.c_int32, C.c_int32, C.c_int32, _P]),
     "tcd_create_detector": (C.c_int, [C.POINTER(DetectorCfg), _P, C.c_size_t, C.c_int32, _PP]),
     "tcd_destroy_detector": (None, [_P]),
     "tcd_detector_set_thresholds": (C.c_int, [_P, C.c_float, C.c_float]),

@@ -126,7 +126,16 @@ tcd_status tcd_conv2d_nhwc_bf16(const void* x, int32_t N, int32_t H, int32_t W, 
                                 int32_t cout, int32_t k, int32_t stride, int32_t silu,
                                 const void* resid, int32_t r_ctot, int32_t r_coff, void* y,
                                 int32_t y_ctot, int32_t y_coff, void* stream) {
-  TCD_REQUIRE(x && w && bias && y, "tcd_conv2d: null argument");
+  return tcd_conv2d_nhwc_bf16_grouped(x, N, H, W, x_ctot, x_coff, cin, w, bias, cout, k, stride, silu, resid, r_ctot,
+                                      r_coff, y, y_ctot, y_coff, 1, stream);
+}
+
+tcd_status tcd_conv2d_nhwc_bf16_grouped(const void* x, int32_t N, int32_t H, int32_t W, int32_t x_ctot,
+                                        int32_t x_coff, int32_t cin, const float* w, const float* bias,
+                                        int32_t cout, int32_t k, int32_t stride, int32_t silu,
+                                        const void* resid, int32_t r_ctot, int32_t r_coff, void* y,
+                                        int32_t y_ctot, int32_t y_coff, int32_t groups, void* stream) {
+  TCD_REQUIRE(x && w && bias && y && groups >= 1, "tcd_conv2d: null argument");
   int rc = require_sm100();
   if (rc) return (tcd_status)rc;
   const int cin_pad = (cin + 15) / 16 * 16;
@@ -143,6 +152,7 @@ tcd_status tcd_conv2d_nhwc_bf16(const void* x, int32_t N, int32_t H, int32_t W, 
   d.w = dw; d.bias = db; d.cout = cout; d.cout_pad = cout; d.k = k; d.stride = stride; d.silu = silu;
   d.y = y; d.y_ctot = y_ctot; d.y_coff = y_coff;
   d.resid = resid; d.r_ctot = r_ctot; d.r_coff = r_coff;
+  d.groups = groups;
   ConvPlan plan;
   rc = conv_plan_build(d, &plan);
   if (rc == TCD_OK) rc = conv_plan_launch(plan, (cudaStream_t)stream);

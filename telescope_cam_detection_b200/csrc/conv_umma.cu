@@ -2,6 +2,7 @@
 // choice, launch.  See conv_umma.cuh for the kernel and the design notes.
 #define TCD_CONV_KERNEL_IMPL
 #include "conv_umma.cuh"
+#include "conv_pair.cuh"
 
 #include <atomic>
 #include <algorithm>
@@ -34,9 +35,11 @@ static PFN_encodeTiled get_encode() {
 }
 
 // TCD_NO_PDL=1 launches every conv with plain stream ordering (debug / A-B measurements)
-static const bool g_use_pdl = [] {
+static const int g_use_pdl = [] {
   const char* e = getenv("TCD_NO_PDL");
-  return !(e && e[0] == '1');
+  if (e && e[0] == '1') return 0;
+  const char* l = getenv("TCD_PDL_LATE");
+  return (l && l[0] == '1') ? 2 : 1;
 }();
 
 // Tuning knobs for A/B measurements (bench.py records the environment it ran with):
@@ -131,6 +134,122 @@ void conv_pack_weights(const float* w, int cout, int cin, int k, int cout_pad, i
             f32_to_bf16_rn(w[((size_t)o * cin + c) * taps + t]);
 }
 
+
+// ---------------------------------------------------------------- CTA-pair plan (conv_pair.cuh)
+//   TCD_CONV_PAIR=0 disables it (A/B measurements); TCD_CONV_PAIR_MIN = smallest map side that takes it (default 40)
+using PairKernelFn = void (*)(const ConvMaps, const PairArgs);
+static PairKernelFn pair_kernel_variant(int act) {
+  static const PairKernelFn tbl[4] = {conv_pair_kernel<0>, conv_pair_kernel<1>, conv_pair_kernel<2>, conv_pair_kernel<3>};
+  return tbl[act & 3];
+}
+
+static bool pair_eligible(const ConvDesc& d, int mode) {
+  if (!env_int("TCD_CONV_PAIR", 1, 0)) return false;
+  if (mode != 0 || d.k != 3 || d.stride != 1 || d.cin != 128) return false;
+  if (d.cout != d.cout_pad || d.cout % 128 || d.cout > kPairMaxCout) return false;
+  if (d.groups > 1 && d.cout / d.groups != 128) return false;
+  const int min_side = env_int("TCD_CONV_PAIR_MIN", 40);
+  if (d.H < min_side || d.W < min_side || d.W % 8) return false;
+  if (d.x_nstride || d.y_nstride) return false;   // dense NHWC only (token views keep the generic kernel)
+  return true;
+}
+
+static int pair_plan_build(const ConvDesc& d, ConvPlan* plan) {
+  ConvArgs& a = plan->args;
+  a.Ho = d.H;
+  a.Wo = d.W;
+  a.TW = 8;
+  a.TH = 16;
+  a.tiles_w = cdiv(a.Wo, 8);
+  a.tiles_per_img = a.tiles_w * cdiv(a.Ho, 16);
+  a.taps = 9; a.kchunks = 2; a.ck = 64; a.BN = 128;
+  a.cin_off = d.x_coff; a.cout_off = d.y_coff;
+  a.mode = 0; a.silu = d.silu; a.out_chunk = 64; a.n_valid = d.cout;
+  a.bias = d.bias; a.bias_n = d.cout;
+  a.resid = (const __nv_bfloat16*)d.resid; a.r_ctot = d.r_ctot; a.r_coff = d.r_coff; a.resid_pre = d.resid_pre;
+  a.r_nstride = d.r_nstride ? d.r_nstride : (long long)a.Ho * a.Wo * d.r_ctot;
+  a.pdl = g_use_pdl;
+  a.halo = 1; a.halo_w = 10;
+  auto magic = [](int dv) -> unsigned int { return dv <= 1 ? 0u : (unsigned int)((0x100000000ULL + dv - 1) / (unsigned)dv); };
+  a.magic_img = magic(a.tiles_per_img);
+  a.magic_w = magic(a.tiles_w);
+  a.n_tiles_n = d.cout / 128;
+  plan->pair = 1;
+  plan->pair_n_tiles = d.cout / 128;
+  plan->pair_m_tiles = a.tiles_per_img * d.N;
+  plan->pair_group_cin = d.groups > 1 ? d.cin : 0;
+  a.total_tiles = plan->pair_m_tiles * plan->pair_n_tiles;
+  TCD_REQUIRE((unsigned long long)(plan->pair_m_tiles + 2) * (unsigned)std::max(a.tiles_per_img, a.tiles_w) < 0x100000000ULL,
+              "conv pair: %d tiles overflow the multiply-high divide", plan->pair_m_tiles);
+  const int m_pairs = cdiv(plan->pair_m_tiles, 2);
+  int clusters = sm_count() / 2;
+  clusters -= clusters % plan->pair_n_tiles;
+  if (clusters > m_pairs * plan->pair_n_tiles) clusters = m_pairs * plan->pair_n_tiles;
+  TCD_REQUIRE(clusters >= plan->pair_n_tiles, "conv pair: no cluster for %d n-tiles", plan->pair_n_tiles);
+  plan->grid = dim3((unsigned)(2 * clusters), 1, 1);
+  plan->smem_bytes = kPairSmem;
+  plan->flops = 2.0 * d.N * a.Ho * a.Wo * (double)d.cout * d.cin * 9;
+  const size_t es = 2;
+  {
+    cuuint64_t dims[4] = {(cuuint64_t)d.x_ctot, (cuuint64_t)d.W, (cuuint64_t)d.H, (cuuint64_t)d.N};
+    cuuint64_t st[3] = {(cuuint64_t)d.x_ctot * es, (cuuint64_t)d.W * d.x_ctot * es, (cuuint64_t)d.H * d.W * d.x_ctot * es};
+    cuuint32_t box[4] = {64, 10, 18, 1};
+    int rc = encode_map(&plan->maps.a[0], (void*)d.x, 4, dims, st, box, 128, "A/pair");
+    if (rc) return rc;
+    for (int i = 1; i < 4; ++i) plan->maps.a[i] = plan->maps.a[0];
+  }
+  {
+    cuuint64_t dims[3] = {(cuuint64_t)d.cin, (cuuint64_t)d.cout_pad, 9};
+    cuuint64_t st[2] = {(cuuint64_t)d.cin * es, (cuuint64_t)d.cout_pad * d.cin * es};
+    cuuint32_t box[3] = {64, 64, 9};
+    int rc = encode_map(&plan->maps.b, (void*)d.w, 3, dims, st, box, 128, "B/pair");
+    if (rc) return rc;
+  }
+  {
+    cuuint64_t dims[4] = {(cuuint64_t)d.y_ctot, (cuuint64_t)a.Wo, (cuuint64_t)a.Ho, (cuuint64_t)d.N};
+    cuuint64_t st[3] = {(cuuint64_t)d.y_ctot * es, (cuuint64_t)a.Wo * d.y_ctot * es, (cuuint64_t)a.Ho * a.Wo * d.y_ctot * es};
+    cuuint32_t box[4] = {64, 8, 16, 1};
+    int rc = encode_map(&plan->maps.o, d.y, 4, dims, st, box, 128, "O/pair");
+    if (rc) return rc;
+  }
+  int rc = ensure_dyn_smem((const void*)pair_kernel_variant(a.silu), (size_t)kPairSmem);
+  if (rc) return rc;
+  return TCD_OK;
+}
+
+static int pair_plan_launch(const ConvPlan& plan, cudaStream_t stream) {
+  PairArgs pa;
+  memset(&pa, 0, sizeof(pa));
+  pa.c = plan.args;
+  pa.m_tiles = plan.pair_m_tiles;
+  pa.m_pairs = cdiv(plan.pair_m_tiles, 2);
+  pa.n_tiles = plan.pair_n_tiles;
+  pa.group_cin = plan.pair_group_cin;
+  pa.n_img = plan.pair_m_tiles / plan.args.tiles_per_img;
+  cudaLaunchConfig_t cfg;
+  memset(&cfg, 0, sizeof(cfg));
+  cfg.gridDim = plan.grid;
+  cfg.blockDim = dim3(kConvThreads, 1, 1);
+  cfg.dynamicSmemBytes = (size_t)plan.smem_bytes;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[2];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = 2;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[1].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = plan.args.pdl ? 2 : 1;
+  cudaError_t e = cudaLaunchKernelEx(&cfg, pair_kernel_variant(plan.args.silu), plan.maps, pa);
+  g_launch_count.fetch_add(1, std::memory_order_relaxed);
+  if (e != cudaSuccess) {
+    set_last_error("conv_pair_kernel launch: %s", cudaGetErrorString(e));
+    return TCD_ERR_CUDA;
+  }
+  return TCD_OK;
+}
+
 static void choose_tile(int Ho, int Wo, int* TW, int* TH) {
   if (Wo % 16 == 0 && Ho % 8 == 0) {
     *TW = 16;
@@ -164,6 +283,8 @@ int conv_plan_build(const ConvDesc& d, ConvPlan* plan) {
   TCD_REQUIRE(d.stride == 1 || (d.H % 2 == 0 && d.W % 2 == 0), "conv: stride 2 needs even H,W");
   TCD_REQUIRE(d.stride == 1 || d.k == 3, "conv: stride 2 only for 3x3");
   const int mode = d.out_f32 ? 1 : 0;
+  TCD_REQUIRE(d.groups >= 1 && d.cout % d.groups == 0, "conv: %d groups do not divide cout %d", d.groups, d.cout);
+  if (pair_eligible(d, mode)) return pair_plan_build(d, plan);
   ConvArgs& a = plan->args;
   a.Ho = d.H / d.stride;
   a.Wo = d.W / d.stride;
@@ -228,7 +349,15 @@ int conv_plan_build(const ConvDesc& d, ConvPlan* plan) {
       }
     }
   }
+  if (d.groups > 1) {   // one N tile per group: the tile index selects the group's input channels
+    BN = d.cout / d.groups;
+    TCD_REQUIRE(mode == 0 && BN % 32 == 0 && BN <= bn_cap && (BN & (BN - 1)) == 0,
+                "conv: grouped conv needs a bf16 output and 32/64/128 channels per group (got %d)", BN);
+  }
   a.BN = BN;
+  a.group_cin = (d.groups > 1 && d.cout / d.groups == BN) ? d.cin : 0;
+  TCD_REQUIRE(d.groups == 1 || a.group_cin > 0, "conv: grouped conv needs one N tile per group (cout/groups %d, BN %d)",
+              d.cout / d.groups, BN);
   a.n_tiles_n = d.cout_pad / BN;
   a.total_tiles = m_tiles * a.n_tiles_n;
   {
@@ -257,7 +386,7 @@ int conv_plan_build(const ConvDesc& d, ConvPlan* plan) {
   a.out_col = d.out_col;
   a.rows_per_img = d.rows_per_img;
   a.row_off = d.row_off;
-  a.pdl = g_use_pdl ? 1 : 0;
+  a.pdl = g_use_pdl;
   a.dbg = env_int("TCD_CONV_DBG", 0);
   // accumulator rounds: narrow tiles (BN 32 / 64, one N tile) are grouped so that a round holds up to 128
   // columns -- the per-round epilogue chain costs ~2 000 cycles whatever the tile holds
@@ -386,6 +515,7 @@ int conv_plan_build(const ConvDesc& d, ConvPlan* plan) {
 }
 
 int conv_plan_launch(const ConvPlan& plan, cudaStream_t stream) {
+  if (plan.pair) return pair_plan_launch(plan, stream);
   cudaLaunchConfig_t cfg;
   memset(&cfg, 0, sizeof(cfg));
   cfg.gridDim = plan.grid;

@@ -74,6 +74,7 @@ struct ConvArgs {
   int out_ld, out_col, rows_per_img, row_off;
   int8_t tap_map[9], tap_dx[9], tap_dy[9];
   unsigned long long* trace;    // optional in-kernel timeline (tcd_detector_trace_op); nullptr on the product path
+  int group_cin;                // grouped conv: n-tile t reads input channels [cin_off + t * group_cin, ...); else 0
 };
 
 #if defined(__CUDACC__) && defined(TCD_CONV_KERNEL_IMPL)
@@ -305,7 +306,9 @@ conv_umma_kernel(const __grid_constant__ ConvMaps maps, const __grid_constant__ 
   tc_fence_after();
   const uint32_t tmem_base = tmem_base_s;
   if (threadIdx.x == 0) conv_trace(p, 2);
-  if (p.pdl && threadIdx.x == 0) pdl_launch_dependents();
+  // pdl == 1: the next layer's CTAs may become resident now (their prologue overlaps this layer, but they hold an SM
+  // slot while they wait); pdl == 2: only once this CTA has issued its last MMA (TCD_PDL_LATE, A/B measurement)
+  if (p.pdl == 1 && threadIdx.x == 0) pdl_launch_dependents();
 
   if (warp == 0) {
     // ------------------------------------------------------------------ TMA producer
@@ -341,7 +344,8 @@ conv_umma_kernel(const __grid_constant__ ConvMaps maps, const __grid_constant__ 
                 }
                 if (!(p.dbg & 1))
                   tma_load_4d(smem + p.a_ring_off + (size_t)aring.s * p.a_stage_bytes, &maps.a[0],
-                            &a_full_bar[aring.s], p.cin_off + kc * p.ck, c.x0 - 1, c.y0 - 1, c.n_img);
+                            &a_full_bar[aring.s], p.cin_off + c.n_tile * p.group_cin + kc * p.ck, c.x0 - 1, c.y0 - 1,
+                            c.n_img);
                 aring.advance();
                 if (first) conv_trace(p, 3);
                 first = false;
@@ -369,7 +373,8 @@ conv_umma_kernel(const __grid_constant__ ConvMaps maps, const __grid_constant__ 
                 pdl_wait();
                 waited = true;
               }
-              if (!(p.dbg & 1)) tma_load_4d(sa, am, &full_bar[ring.s], p.cin_off + kc * p.ck, cx, cy, c.n_img);
+              if (!(p.dbg & 1))
+                tma_load_4d(sa, am, &full_bar[ring.s], p.cin_off + c.n_tile * p.group_cin + kc * p.ck, cx, cy, c.n_img);
               ring.advance();
               if (first) conv_trace(p, 3);
               first = false;
@@ -455,6 +460,7 @@ conv_umma_kernel(const __grid_constant__ ConvMaps maps, const __grid_constant__ 
         }
       }
       conv_trace(p, 6);
+      if (p.pdl == 2) pdl_launch_dependents();
     }
   } else {
     // ------------------------------------------------------------------ epilogue (kConvEpiWarps warps)
@@ -591,6 +597,8 @@ struct ConvDesc {
   long long x_nstride = 0, y_nstride = 0, r_nstride = 0;
   int resid_pre = 0;  // residual added before (1) or after (0) the activation
   int share = -1;     // plan for 1/share of an SM (co-residency with other streams' layers); -1 = TCD_CONV_SHARE
+  int groups = 1;     // grouped conv: cout / groups output channels per group, each reading `cin` input channels at
+                      // x_coff + g * cin (the fused cls / reg branch convs of the YOLOX head); weights [k*k][cout][cin]
   // bf16 output (mode 0)
   void* y = nullptr;
   int y_ctot = 0, y_coff = 0;
@@ -601,9 +609,12 @@ struct ConvDesc {
   int out_ld = 0, out_col = 0, rows_per_img = 0, row_off = 0;
 };
 
+struct PairArgs;
 struct ConvPlan {
   ConvMaps maps;
   ConvArgs args;
+  int pair = 0;        // 1: conv_pair_kernel (cta_group::2, resident weights, conv_pair.cuh); args then lives in pair_args
+  int pair_n_tiles = 0, pair_m_tiles = 0, pair_group_cin = 0;
   dim3 grid;
   int smem_bytes = 0;
   double flops = 0;

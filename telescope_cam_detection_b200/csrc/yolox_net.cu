@@ -128,8 +128,8 @@ int YoloxWeights::upload(const WeightBlob& blob) {
     const std::string s = std::to_string(l);
     W_TRY(one("head.stem." + s, "head.stems." + s));
     W_TRY(fuse("head.conv_a." + s, "head.cls_convs." + s + ".0", "head.reg_convs." + s + ".0"));
-    W_TRY(one("head.cls_b." + s, "head.cls_convs." + s + ".1"));
-    W_TRY(one("head.reg_b." + s, "head.reg_convs." + s + ".1"));
+    // the second 3x3 convs of the cls and reg branches as ONE grouped conv over [cls_a | reg_a] -> [cls_feat | reg_feat]
+    W_TRY(fuse("head.b." + s, "head.cls_convs." + s + ".1", "head.reg_convs." + s + ".1"));
     // the three 1x1 prediction convs of a level as ONE block-diagonal GEMM over [cls_feat | reg_feat]:
     // rows 0-3 reg, 4 obj (weights on the reg_feat half), rows 5.. cls (weights on the cls_feat half), zeros
     // elsewhere.  Exact zeros add exact zeros to the fp32 accumulator, so every logit keeps its bits; the kernel

@@ -39,7 +39,7 @@ struct Builder {
 
   // y[.., ycoff:ycoff+cout] = act(conv(x[.., xcoff:xcoff+cin])) (+ resid)
   void conv(const std::string& wname, const Act& x, int xcoff, const Act& y, int ycoff, int stride,
-            const Act* resid = nullptr, int rcoff = 0) {
+            const Act* resid = nullptr, int rcoff = 0, int groups = 1) {
     if (rc) return;
     const DevConv* w = dc(wname);
     if (!w) return;
@@ -47,7 +47,7 @@ struct Builder {
     ConvDesc d;
     d.x = x.p; d.N = B; d.H = x.H; d.W = x.W; d.x_ctot = x.C; d.x_coff = xcoff; d.cin = w->cin_pad;
     d.w = w->w; d.bias = w->bias; d.cout = w->cout; d.cout_pad = w->cout_pad; d.k = w->k;
-    d.stride = stride; d.silu = 1;
+    d.stride = stride; d.silu = 1; d.groups = groups;
     d.y = y.p; d.y_ctot = y.C; d.y_coff = ycoff;
     if (resid) { d.resid = resid->p; d.r_ctot = resid->C; d.r_coff = rcoff; }
     NetOp op;
@@ -195,8 +195,7 @@ struct Builder {
       Act ha = alloc("head.conv_a." + s, f.H, f.W, 2 * hc);
       conv("head.conv_a." + s, st, 0, ha, 0, 1);
       Act hfeat = alloc("head.feat." + s, f.H, f.W, 2 * hc);   // [cls_feat | reg_feat]
-      conv("head.cls_b." + s, ha, 0, hfeat, 0, 1);
-      conv("head.reg_b." + s, ha, hc, hfeat, hc, 1);
+      conv("head.b." + s, ha, 0, hfeat, 0, 1, nullptr, 0, 2);
       pred("head.pred." + s, hfeat, 0, row_off, A,
            2.0 * B * f.H * f.W * (double)(5 + plan.num_classes) * hc);
       plan.lvl_start[l] = row_off;

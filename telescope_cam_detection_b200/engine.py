@@ -255,15 +255,17 @@ def preprocess(frames_dev_ptrs, hs, ws, strides, out_ptr, out_size, layout=0, mo
 
 
 def conv2d_nhwc_bf16(x_ptr, N, H, W, x_ctot, x_coff, cin, w, bias, k, stride, silu, y_ptr, y_ctot, y_coff,
-                     resid_ptr=0, r_ctot=0, r_coff=0):
+                     resid_ptr=0, r_ctot=0, r_coff=0, groups=1):
+    """cin: input channels PER GROUP; w: [cout, cin, k, k]."""
     lib = _lib.load()
     w = np.ascontiguousarray(w, np.float32)
     bias = np.ascontiguousarray(bias, np.float32)
     cout = w.shape[0]
-    check(lib.tcd_conv2d_nhwc_bf16(C.c_void_p(int(x_ptr)), N, H, W, x_ctot, x_coff, cin,
-                                   w.ctypes.data_as(_lib._F32P), bias.ctypes.data_as(_lib._F32P), cout, k, stride,
-                                   int(silu), C.c_void_p(int(resid_ptr)) if resid_ptr else None, r_ctot, r_coff,
-                                   C.c_void_p(int(y_ptr)), y_ctot, y_coff, None), "tcd_conv2d_nhwc_bf16")
+    check(lib.tcd_conv2d_nhwc_bf16_grouped(C.c_void_p(int(x_ptr)), N, H, W, x_ctot, x_coff, cin,
+                                           w.ctypes.data_as(_lib._F32P), bias.ctypes.data_as(_lib._F32P), cout, k,
+                                           stride, int(silu), C.c_void_p(int(resid_ptr)) if resid_ptr else None,
+                                           r_ctot, r_coff, C.c_void_p(int(y_ptr)), y_ctot, y_coff, int(groups), None),
+          "tcd_conv2d_nhwc_bf16_grouped")
 
 
 def crop_resize(frame_ptr, h, w, stride, boxes, S, out_ptr, layout=0, swap_rb=1, scale=1.0 / 255.0,

@@ -21,7 +21,39 @@ CASES = [
     (2, 40, 40, 256, 512, 3, 2, 1, 0, 512, 256, 512, 0),
     (3, 20, 20, 1024, 512, 1, 1, 1, 0, 1024, 0, 512, 0),
     (1, 24, 40, 64, 64, 3, 1, 1, 0, 64, 0, 128, 64),
+    # CTA-pair kernel (conv_pair.cuh): several rounds per cluster, odd patch count (a no-op half pair), partial patches
+    (8, 80, 80, 128, 256, 3, 1, 1, 0, 128, 0, 256, 0),
+    (3, 40, 40, 128, 128, 3, 1, 1, 1, 256, 128, 256, 128),
+    (1, 48, 40, 128, 128, 3, 1, 0, 0, 128, 0, 384, 256),
 ]
+
+# N, H, W, cin per group, cout, groups: the fused cls_b | reg_b convs of the head (pair kernel at 80 / 40, generic at 20)
+GROUPED = [(8, 80, 80, 128, 256, 2), (2, 40, 40, 128, 256, 2), (2, 20, 20, 128, 256, 2), (2, 40, 40, 64, 128, 2)]
+
+
+@pytest.mark.parametrize("case", GROUPED)
+def test_grouped_conv_matches_torch(case):
+    import torch
+    import torch.nn.functional as F
+    from telescope_cam_detection_b200 import engine
+
+    torch.backends.cudnn.allow_tf32 = False
+    N, H, W, cin, cout, groups = case
+    g = torch.Generator(device="cpu").manual_seed(77 + H + cin)
+    dev = "cuda:0"
+    x = torch.randn(N, H, W, groups * cin, generator=g).to(dev).to(torch.bfloat16)
+    w = (torch.randn(cout, cin, 3, 3, generator=g) / (cin * 9) ** 0.5).float()
+    b = torch.randn(cout, generator=g).float() * 0.1
+    y = torch.zeros((N, H, W, cout), device=dev, dtype=torch.bfloat16)
+    engine.conv2d_nhwc_bf16(x.data_ptr(), N, H, W, groups * cin, 0, cin, w.numpy(), b.numpy(), 3, 1, 1,
+                            y.data_ptr(), cout, 0, groups=groups)
+    torch.cuda.synchronize()
+    ref = F.silu(F.conv2d(x.float().permute(0, 3, 1, 2), w.to(dev).to(torch.bfloat16).float(), b.to(dev), padding=1,
+                          groups=groups))
+    got = y.float().permute(0, 3, 1, 2)
+    err = (got - ref).abs()
+    assert bool((err <= 1e-2 + 8e-3 * ref.abs()).all()), "max err %.4g" % err.max().item()
+
 
 
 @pytest.mark.parametrize("case", CASES)

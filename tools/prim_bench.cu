@@ -164,6 +164,50 @@ __global__ void __launch_bounds__(64) ring_kernel(long long* out, int S, int ite
   if (warp == 1) tmem_dealloc(tmem_base_s, 32);
 }
 
+// Can TWO threads (different warps) issue tcgen05.mma concurrently at twice the rate of one?  Each issuer sends `per`
+// MMAs (M128 x N x K16) to its own accumulator columns, commits and waits; out[0] = cycles from the common start to the
+// later of the two completions.  issuers = 1: one thread issues all 2 * per.
+__global__ void __launch_bounds__(128) dual_issue_kernel(long long* out, int N, int per, int issuers) {
+  extern __shared__ uint8_t smem_raw[];
+  __shared__ uint64_t bars[2];
+  __shared__ uint32_t tmem_base_s;
+  __shared__ long long t_end[2];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (threadIdx.x == 0) {
+    mbar_init(&bars[0], 1);
+    mbar_init(&bars[1], 1);
+    fence_mbar_init();
+    t_end[0] = t_end[1] = 0;
+  }
+  if (warp == 1) tmem_alloc(&tmem_base_s, 512);
+  for (int i = threadIdx.x; i < 64 * 1024 / 4; i += 128) reinterpret_cast<uint32_t*>(smem)[i] = 0;
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = tmem_base_s;
+  const long long t0 = clock64();
+  const int me = warp == 0 ? 0 : (warp == 2 ? 1 : -1);
+  if (me >= 0 && lane == 0 && me < issuers) {
+    const uint32_t idesc = umma_idesc_bf16(128, N);
+    const uint32_t a_addr = smem_u32(smem), b_addr = smem_u32(smem + 16384);
+    const int n = issuers == 1 ? 2 * per : per;
+    for (int i = 0; i < n; ++i) {
+      const uint64_t ad = umma_smem_desc(a_addr + (i & 3) * 32, 1024, 2);
+      const uint64_t bd = umma_smem_desc(b_addr + (i & 3) * 32, 1024, 2);
+      umma_bf16(tmem + me * 256, ad, bd, idesc, (uint32_t)(i != 0));
+    }
+    umma_commit(&bars[me]);
+    mbar_wait(&bars[me], 0);
+    t_end[me] = clock64();
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) out[0] = (t_end[0] > t_end[1] ? t_end[0] : t_end[1]) - t0;
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc(tmem, 512);
+}
+
 int main() {
   long long* d;
   cudaMalloc(&d, 64 * sizeof(long long));
@@ -182,6 +226,16 @@ int main() {
     printf("--- UMMA N = %d (cycles)\n", n);
     for (int i = 0; i < 10; ++i) printf("  %-52s %lld\n", names[i], h[i]);
   }
+  cudaFuncSetAttribute(dual_issue_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024);
+  for (int n : {32, 64, 128})
+    for (int issuers : {1, 2}) {
+      dual_issue_kernel<<<1, 128, 80 * 1024>>>(d, n, 64, issuers);
+      cudaError_t e = cudaDeviceSynchronize();
+      if (e != cudaSuccess) { printf("dual_issue_kernel: %s\n", cudaGetErrorString(e)); return 1; }
+      long long h;
+      cudaMemcpy(&h, d, sizeof(h), cudaMemcpyDeviceToHost);
+      printf("128 MMAs N=%d from %d issuing thread(s): %lld cycles total = %.1f per MMA\n", n, issuers, h, h / 128.0);
+    }
   for (int commit = 0; commit < 2; ++commit)
     for (int S : {1, 2, 4, 8}) {
       ring_kernel<<<1, 64>>>(d, S, 512, commit);

@@ -5,9 +5,19 @@ import sys
 for f in sys.argv[1:]:
     try:
         d = json.load(open(f))
-        print("%-44s dev %6.0f  e2e %6.0f  ms/step %.3f  p50 %.3f  conv-frac %.4f  conv-ms %.3f  other %.3f  post %.3f" % (
-            f.split("/")[-1], d["value"], d["e2e"]["value"], d["ms_per_step"], d["latency_ms_p50_sync_batch"] or 0,
-            d["roofline"]["frac"], d["roofline"].get("kernel_ms_per_step") or d["roofline"]["isolated"]["kernel_ms_per_step"], d["kernels"]["other_layers_ms"],
-            d["kernels"]["decode_nms"]["ms"]))
+        r = d["roofline"]
+        print("%s: dev %.0f fps (%.4f ms/step)  e2e %.0f  p50 %.3f ms" % (f.split("/")[-1], d["value"], d["ms_per_step"],
+              d["e2e"]["value"], d["latency_ms_p50_sync_batch"] or 0))
+        print("  roofline: in-pipeline %.1f TF/s = %.3f of sustained, %.3f of burst; isolated %.1f TF/s (%.3f), conv ms %.3f of eager %.3f" % (
+              r["achieved"], r["frac"], r.get("frac_of_burst", 0), r["isolated"]["achieved"], r["isolated"]["frac"],
+              r["isolated"]["kernel_ms_per_step"], d["kernels"]["eager_step_ms"]))
+        for k, v in d["e2e"].get("variants", {}).items():
+            print("  e2e variant %-24s %.0f fps  %.3f ms/step  h2d %d" % (k, v["value"], v["ms_per_step"], v["h2d_bytes_per_step"]))
+        k = d["kernels"]
+        print("  preprocess %.1f us (%.2f of HBM)  decode+nms %.1f us %s  other %.1f us" % (
+              1e3 * k["preprocess"]["ms"], k["preprocess"]["frac_hbm"], 1e3 * k["decode_nms"]["ms"],
+              k["decode_nms"].get("parts_ms"), 1e3 * k["other_layers_ms"]))
+        print("  slowest convs: " + ", ".join("%s %.1fus %.0fTF" % (c["name"], 1e3 * c["ms"], c["TFLOP/s"]) for c in k["slowest_convs"]))
+        print("  parity:", d.get("parity_check"), " clocks:", d.get("clocks"))
     except Exception as e:
-        print(f, "ERR", e)
+        print(f, "ERR", repr(e))
