@@ -142,10 +142,13 @@ tcd_status tcd_detect_batch(tcd_detector* det, const uint8_t* const* frames, con
 
 /* Split-phase variant used by the pipelined coordinator / bench: enqueue as pipeline slot
  * `slot` (0 .. tcd_detector_num_slots()-1), then wait.  A slot is (engine, lane): engine
- * slot % n_engines owns the stream, arena and CUDA graph, lane slot / n_engines owns the frame
- * staging and the result table of ONE in-flight batch (n_engines = 6, env TCD_ENGINES 1..8;
- * two lanes per engine).  Frames of a queued lane upload on the engine's copy stream while
- * the other lane computes; low-occupancy layers of different engines share the chip.     */
+ * slot / n_lanes owns the stream, the activation arena and the CUDA graphs, lane slot % n_lanes owns
+ * the frame staging and the result table of ONE in-flight batch (n_engines = 3, env TCD_ENGINES 1..8;
+ * n_lanes = 4, env TCD_LANES 1..4).  Dynamic batching: a submit uploads and preprocesses its frames at
+ * once, the network + decode/NMS launch of an engine is deferred until its lanes are full or one of
+ * them is waited on, and then runs ONCE over all the frames its lanes hold (up to n_lanes x max_batch)
+ * -- under load the per-launch latencies are paid per group of batches, a lone batch runs at its own
+ * size.  Frames of a lane upload on the engine's copy stream while the engine computes.              */
 tcd_status tcd_detect_batch_async(tcd_detector* det, int32_t slot, const uint8_t* const* frames,
                                   const int32_t* h, const int32_t* w, const int64_t* row_stride,
                                   int32_t B, int32_t frames_on_device);

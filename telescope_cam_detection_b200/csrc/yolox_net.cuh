@@ -59,12 +59,15 @@ struct YoloxPlan {
   std::map<std::string, Act> acts;  // named activation buffers (debug taps)
   void* arena = nullptr;
   size_t arena_bytes = 0;
+  bool owns_arena = true;  // false: laid out over an arena another plan of the same engine owns (smaller batch sizes)
   void* input = nullptr;   // bf16 [B,in_h/2,in_w/2,16]
   float* pred_raw = nullptr;  // f32 [B,A,5+C]
   int lvl_start[3], lvl_w[3], lvl_stride[3];
   double conv_flops = 0;
 
-  int build(const YoloxWeights& wts, int B, int in_h, int in_w);
+  // ext_arena: lay the plan out over an existing arena (the engine's plan for its largest batch) instead of allocating;
+  // the network input is always the first buffer, so every plan of an engine shares the input address
+  int build(const YoloxWeights& wts, int B, int in_h, int in_w, void* ext_arena = nullptr, size_t ext_bytes = 0);
   int run(cudaStream_t stream) const;
   int run_one(int i, cudaStream_t stream) const;
   void release();

@@ -208,7 +208,7 @@ struct Builder {
 
 }  // namespace
 
-int YoloxPlan::build(const YoloxWeights& wts, int B_, int in_h_, int in_w_) {
+int YoloxPlan::build(const YoloxWeights& wts, int B_, int in_h_, int in_w_, void* ext_arena, size_t ext_bytes) {
   TCD_REQUIRE(in_h_ % 32 == 0 && in_w_ % 32 == 0 && in_h_ >= 64 && in_w_ >= 64,
               "plan: input size %dx%d must be a multiple of 32", in_h_, in_w_);
   B = B_;
@@ -222,8 +222,16 @@ int YoloxPlan::build(const YoloxWeights& wts, int B_, int in_h_, int in_w_) {
   b.run_pass();
   if (b.rc) return b.rc;
   arena_bytes = b.cursor;
-  TCD_CUDA_OK(cudaMalloc(&arena, arena_bytes));
-  TCD_CUDA_OK(cudaMemset(arena, 0, arena_bytes));
+  if (ext_arena) {
+    TCD_REQUIRE(arena_bytes <= ext_bytes, "plan: batch %d needs %zu B of arena, the engine's holds %zu", B_, arena_bytes,
+                ext_bytes);
+    arena = ext_arena;
+    owns_arena = false;
+  } else {
+    TCD_CUDA_OK(cudaMalloc(&arena, arena_bytes));
+    TCD_CUDA_OK(cudaMemset(arena, 0, arena_bytes));
+    owns_arena = true;
+  }
   b.dry = false;
   b.run_pass();
   return b.rc;
@@ -258,7 +266,7 @@ int YoloxPlan::run_one(int i, cudaStream_t stream) const {
 }
 
 void YoloxPlan::release() {
-  if (arena) cudaFree(arena);
+  if (arena && owns_arena) cudaFree(arena);
   arena = nullptr;
   ops.clear();
   acts.clear();
