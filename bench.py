@@ -541,6 +541,9 @@ def run_ours(args):
         if rank == 0:
             prof = eng.profile(dev_batches[0], iters=2)
             conv_ms = sum(o["ms"] for o in prof if o["kind"] == "conv")
+            if args.dump_ops:
+                with open(args.dump_ops, "w") as f:
+                    json.dump(prof, f)
             emit(json.dumps({"quick": True, "batch": B, "value": fps_dev, "ms_per_step": r_dev["ms"] / K, "slots": n_slots,
                              "engines": n_engines, "eager_conv_ms": conv_ms, "eager_all_ms": sum(o["ms"] for o in prof),
                              "env": {k: v for k, v in os.environ.items() if k.startswith("TCD_")}}))

@@ -143,7 +143,7 @@ tcd_status tcd_detect_batch(tcd_detector* det, const uint8_t* const* frames, con
 /* Split-phase variant used by the pipelined coordinator / bench: enqueue as pipeline slot
  * `slot` (0 .. tcd_detector_num_slots()-1), then wait.  A slot is (engine, lane): engine
  * slot / n_lanes owns the stream, the activation arena and the CUDA graphs, lane slot % n_lanes owns
- * the frame staging and the result table of ONE in-flight batch (n_engines = 3, env TCD_ENGINES 1..8;
+ * the frame staging and the result table of ONE in-flight batch (n_engines = 4, env TCD_ENGINES 1..8;
  * n_lanes = 4, env TCD_LANES 1..4).  Dynamic batching: a submit uploads and preprocesses its frames at
  * once, the network + decode/NMS launch of an engine is deferred until its lanes are full or one of
  * them is waited on, and then runs ONCE over all the frames its lanes hold (up to n_lanes x max_batch)

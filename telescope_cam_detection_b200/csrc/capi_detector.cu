@@ -13,6 +13,7 @@
 // each other (the low-occupancy layers of one group share the chip with another group's).
 #include <algorithm>
 #include <atomic>
+#include <math.h>
 #include <map>
 #include <stdlib.h>
 #include <string.h>
@@ -67,9 +68,13 @@ struct Slot {                     // an engine
   // postprocess buffers (sized for max_batch)
   PostBuffers pb;
   float* thr_dev = nullptr;
+  int* maybe_count = nullptr;     // candidate emission of the prediction convs: rows written per image ...
+  int* maybe_idx = nullptr;       // ... and their anchor indices [group_cap, cap]
   float* pred_in = nullptr;       // device scratch for tcd_postprocess [max_batch,A,5+C]
   const tcd_class_filter* tables = nullptr;  // the detector's table array
   const YoloxPlan* last_plan = nullptr;      // the plan whose activations the arena currently holds (debug taps)
+  PlanBranches br;                           // side streams for the head levels (YoloxPlan::run)
+  bool use_branches = true;                  // TCD_NO_BRANCH=1: one linear chain (A/B)
 };
 
 }  // namespace
@@ -79,7 +84,7 @@ struct tcd_detector {
   int device = 0;
   YoloxWeights wts;
   Slot slot[kEngines];
-  int n_engines = 3;              // TCD_ENGINES; slots exposed = n_engines * n_lanes
+  int n_engines = 4;              // TCD_ENGINES; slots exposed = n_engines * n_lanes
   int n_lanes = 4;                // TCD_LANES (1..kLanes): batches one engine coalesces into one launch
   int group_cap = 0;              // n_lanes * max_batch frames: what an engine's arena and scratch are sized for
   float thr_host[2] = {0.25f, 0.45f};
@@ -95,6 +100,12 @@ static int slot_init(tcd_detector* d, Slot& s) {
   const int GB = d->group_cap;     // frames per engine launch
   TCD_CUDA_OK(cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking));
   TCD_CUDA_OK(cudaStreamCreateWithFlags(&s.up, cudaStreamNonBlocking));
+  for (int b = 0; b < 2; ++b) {
+    TCD_CUDA_OK(cudaStreamCreateWithFlags(&s.br.aux[b], cudaStreamNonBlocking));
+    TCD_CUDA_OK(cudaEventCreateWithFlags(&s.br.fork[b], cudaEventDisableTiming));
+    TCD_CUDA_OK(cudaEventCreateWithFlags(&s.br.join[b], cudaEventDisableTiming));
+  }
+  s.use_branches = getenv("TCD_NO_BRANCH") == nullptr;
   TCD_CUDA_OK(cudaMalloc((void**)&s.meta_dev, sizeof(FrameMeta) * GB));
   TCD_CUDA_OK(cudaMemset(s.meta_dev, 0, sizeof(FrameMeta) * GB));
   for (int li = 0; li < d->n_lanes; ++li) {
@@ -116,8 +127,10 @@ static int slot_init(tcd_detector* d, Slot& s) {
   PostBuffers& pb = s.pb;
   memset(&pb, 0, sizeof(pb));
   pb.A = A; pb.C = C; pb.cap = cap; pb.max_out = c.max_out;
-  TCD_CUDA_OK(cudaMalloc((void**)&s.thr_dev, 2 * sizeof(float)));
+  TCD_CUDA_OK(cudaMalloc((void**)&s.thr_dev, 4 * sizeof(float)));   // conf, nms, emission threshold of the pred convs
   pb.thr = s.thr_dev;
+  TCD_CUDA_OK(cudaMalloc((void**)&s.maybe_count, sizeof(int) * GB));
+  TCD_CUDA_OK(cudaMalloc((void**)&s.maybe_idx, sizeof(int) * (size_t)cap * GB));
   TCD_CUDA_OK(cudaMalloc((void**)&pb.cand_count, sizeof(int) * GB));
   TCD_CUDA_OK(cudaMalloc((void**)&pb.cand, sizeof(float) * 8 * cap * GB));
   TCD_CUDA_OK(cudaMalloc((void**)&pb.cand_anchor, sizeof(int) * cap * GB));
@@ -130,6 +143,7 @@ static int slot_init(tcd_detector* d, Slot& s) {
   TCD_CUDA_OK(cudaMalloc((void**)&pb.decoded, sizeof(float) * (size_t)MB * A * (5 + C)));   // parity tap: one lane's worth
   TCD_CUDA_OK(cudaMalloc((void**)&s.pred_in, sizeof(float) * (size_t)MB * A * (5 + C)));
   TCD_CUDA_OK(cudaMemcpy(s.thr_dev, d->thr_host, 2 * sizeof(float), cudaMemcpyHostToDevice));
+  TCD_CUDA_OK(cudaMemcpy(s.thr_dev + 2, d->thr_host, sizeof(float), cudaMemcpyHostToDevice));
   return TCD_OK;
 }
 
@@ -138,7 +152,7 @@ static void slot_free(Slot& s) {
   for (auto& kv : s.plans) if (!kv.second->owns_arena) { kv.second->release(); delete kv.second; kv.second = nullptr; }
   for (auto& kv : s.plans) if (kv.second) { kv.second->release(); delete kv.second; }
   PostBuffers& pb = s.pb;
-  void* ptrs[] = {s.meta_dev, s.thr_dev, pb.cand_count, pb.cand, pb.cand_anchor, pb.srec,
+  void* ptrs[] = {s.maybe_count, s.maybe_idx, s.meta_dev, s.thr_dev, pb.cand_count, pb.cand, pb.cand_anchor, pb.srec,
                   pb.sbox, pb.n_sorted, pb.mask, pb.out_dets, pb.out_counts, pb.decoded, s.pred_in};
   for (void* p : ptrs) if (p) cudaFree(p);
   for (Lane& l : s.lane) {
@@ -151,6 +165,11 @@ static void slot_free(Slot& s) {
     for (auto& e : l.ev) if (e) cudaEventDestroy(e);
     if (l.ev_up) cudaEventDestroy(l.ev_up);
   }
+  for (int b = 0; b < 2; ++b) {
+    if (s.br.aux[b]) cudaStreamDestroy(s.br.aux[b]);
+    if (s.br.fork[b]) cudaEventDestroy(s.br.fork[b]);
+    if (s.br.join[b]) cudaEventDestroy(s.br.join[b]);
+  }
   if (s.up) cudaStreamDestroy(s.up);
   if (s.stream) cudaStreamDestroy(s.stream);
 }
@@ -159,6 +178,12 @@ static int get_plan(tcd_detector* d, Slot& s, int B, YoloxPlan** out) {
   auto it = s.plans.find(B);
   if (it != s.plans.end()) { *out = it->second; return TCD_OK; }
   YoloxPlan* p = new YoloxPlan();
+  if (getenv("TCD_NO_EMIT") == nullptr) {   // A/B: TCD_NO_EMIT=1 writes every prediction row and decodes densely
+    p->emit_thr = s.thr_dev + 2;
+    p->maybe_count = s.maybe_count;
+    p->maybe_idx = s.maybe_idx;
+    p->maybe_cap = d->cap;
+  }
   // every plan of an engine lives in the arena of its largest one (the group capacity, built at create)
   auto big = s.plans.find(d->group_cap);
   int rc = big == s.plans.end() ? p->build(d->wts, B, d->cfg.input_h, d->cfg.input_w)
@@ -177,6 +202,8 @@ static PostBuffers post_for(const Slot& s, const YoloxPlan* p, int B, const floa
   if (!want_decoded) pb.decoded = nullptr;
   pb.meta = s.meta_dev;
   pb.tables = s.tables;
+  pb.maybe_count = (pred == p->pred_raw && p->emit_thr != nullptr) ? s.maybe_count : nullptr;
+  pb.maybe_idx = s.maybe_idx;
   pb.n_levels = 3;
   for (int l = 0; l < 3; ++l) {
     pb.lvl_start[l] = p->lvl_start[l];
@@ -195,7 +222,8 @@ static int run_net_post(tcd_detector* d, Slot& s, YoloxPlan* p, int B, bool want
       cudaGraph_t g = nullptr;
       const uint64_t launches_before = g_launch_count.load();
       TCD_CUDA_OK(cudaStreamBeginCapture(s.stream, cudaStreamCaptureModeThreadLocal));
-      int rc = p->run(s.stream);
+      cudaMemsetAsync(s.maybe_count, 0, sizeof(int) * B, s.stream);
+      int rc = p->run(s.stream, s.use_branches ? &s.br : nullptr);
       if (rc == TCD_OK) rc = postproc_launch(post_for(s, p, B, p->pred_raw, false), 1, s.stream);
       cudaError_t e = cudaStreamEndCapture(s.stream, &g);
       if (rc) { if (g) cudaGraphDestroy(g); return rc; }
@@ -221,9 +249,17 @@ static int run_net_post(tcd_detector* d, Slot& s, YoloxPlan* p, int B, bool want
     g_launch_count.fetch_add(s.graph_kernels[B]);
     return TCD_OK;
   }
-  int rc = p->run(s.stream);
-  if (rc) return rc;
-  return postproc_launch(post_for(s, p, B, p->pred_raw, want_decoded), 1, s.stream);
+  // eager path.  The parity taps (want_decoded) need every row of the prediction: emission threshold -inf
+  const float ninf = -INFINITY;
+  if (want_decoded) TCD_CUDA_OK(cudaMemcpyAsync(s.thr_dev + 2, &ninf, sizeof(float), cudaMemcpyHostToDevice, s.stream));
+  TCD_CUDA_OK(cudaMemsetAsync(s.maybe_count, 0, sizeof(int) * B, s.stream));
+  int rc = p->run(s.stream, s.use_branches ? &s.br : nullptr);
+  if (rc == TCD_OK) rc = postproc_launch(post_for(s, p, B, p->pred_raw, want_decoded), 1, s.stream);
+  if (want_decoded) {
+    TCD_CUDA_OK(cudaStreamSynchronize(s.stream));   // ninf must outlive the copy; then restore the product threshold
+    TCD_CUDA_OK(cudaMemcpyAsync(s.thr_dev + 2, d->thr_host, sizeof(float), cudaMemcpyHostToDevice, s.stream));
+  }
+  return rc;
 }
 
 static const bool g_sparse_upload = [] {
@@ -460,6 +496,7 @@ tcd_status tcd_detector_set_thresholds(tcd_detector* det, float conf_thre, float
     // ordered after work already queued on the slot; never touches the captured graphs
     TCD_CUDA_OK(cudaStreamSynchronize(det->slot[i].stream));
     TCD_CUDA_OK(cudaMemcpy(det->slot[i].thr_dev, det->thr_host, 2 * sizeof(float), cudaMemcpyHostToDevice));
+    TCD_CUDA_OK(cudaMemcpy(det->slot[i].thr_dev + 2, det->thr_host, sizeof(float), cudaMemcpyHostToDevice));
   }
   return TCD_OK;
 }
@@ -726,6 +763,7 @@ tcd_status tcd_detector_profile(tcd_detector* det, const uint8_t* const* frames,
     if (rc) break;
     // layers with an in-place residual have accumulated kProfileReps times: one clean pass so that decode / NMS
     // are timed on the real prediction, not on an inflated candidate set
+    cudaMemsetAsync(s.maybe_count, 0, sizeof(int) * B, s.stream);
     rc = p->run(s.stream);
     if (rc) break;
     const int base = 1 + (int)p->ops.size();

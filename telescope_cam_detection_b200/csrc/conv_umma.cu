@@ -386,6 +386,11 @@ int conv_plan_build(const ConvDesc& d, ConvPlan* plan) {
   a.out_col = d.out_col;
   a.rows_per_img = d.rows_per_img;
   a.row_off = d.row_off;
+  a.emit_thr = mode == 1 ? d.emit_thr : nullptr;
+  a.maybe_count = d.maybe_count;
+  a.maybe_idx = d.maybe_idx;
+  a.maybe_cap = d.maybe_cap;
+  a.emit_col = d.emit_col;
   a.pdl = g_use_pdl;
   a.dbg = env_int("TCD_CONV_DBG", 0);
   // accumulator rounds: narrow tiles (BN 32 / 64, one N tile) are grouped so that a round holds up to 128

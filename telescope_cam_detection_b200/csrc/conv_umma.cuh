@@ -75,6 +75,13 @@ struct ConvArgs {
   int8_t tap_map[9], tap_dx[9], tap_dy[9];
   unsigned long long* trace;    // optional in-kernel timeline (tcd_detector_trace_op); nullptr on the product path
   int group_cin;                // grouped conv: n-tile t reads input channels [cin_off + t * group_cin, ...); else 0
+  // f32-row mode, YOLOX prediction convs: only rows whose objectness can still reach the confidence threshold are
+  // written, and their anchor index is appended to a per-image list the decode kernel works from
+  // (score = obj * cls <= obj: a row with sigmoid(obj) < conf can never be a candidate).  nullptr: every row.
+  const float* emit_thr;        // device float: confidence threshold (-inf: every row, the parity taps)
+  int* maybe_count;             // [images]
+  int* maybe_idx;               // [images][maybe_cap] anchor indices (row_off + y * Wo + x)
+  int maybe_cap, emit_col;      // emit_col: accumulator column of the objectness logit
 };
 
 #if defined(__CUDACC__) && defined(TCD_CONV_KERNEL_IMPL)
@@ -550,7 +557,18 @@ conv_umma_kernel(const __grid_constant__ ConvMaps maps, const __grid_constant__ 
       }
       if (kMode == 1) {
         asm volatile("bar.sync 1, %0;" ::"n"(32 * kConvEpiWarps) : "memory");
-        conv_flush_rows(p, c, q, half, lane, staging, valid, y, x);
+        bool keep = valid;
+        if (p.emit_thr != nullptr && valid) {
+          // a superset test (the decode kernel re-evaluates the exact score): drop the row only when its
+          // objectness alone is clearly below the threshold
+          const float obj = reinterpret_cast<const float*>(staging)[(size_t)row * (p.BN + 1) + p.emit_col];
+          keep = 1.0f / (1.0f + expf(-obj)) >= p.emit_thr[0] * 0.999f - 1e-6f;
+          if (keep) {
+            const int slot = atomicAdd(p.maybe_count + c.n_img, 1);
+            if (slot < p.maybe_cap) p.maybe_idx[(size_t)c.n_img * p.maybe_cap + slot] = p.row_off + y * p.Wo + x;
+          }
+        }
+        conv_flush_rows(p, c, q, half, lane, staging, keep, y, x);
       } else {
         fence_proxy_async_smem();
         asm volatile("bar.sync 1, %0;" ::"n"(32 * kConvEpiWarps) : "memory");
@@ -607,6 +625,11 @@ struct ConvDesc {
   // f32 row output (mode 1)
   float* out_f32 = nullptr;
   int out_ld = 0, out_col = 0, rows_per_img = 0, row_off = 0;
+  // f32 rows only: candidate emission (see ConvArgs)
+  const float* emit_thr = nullptr;
+  int* maybe_count = nullptr;
+  int* maybe_idx = nullptr;
+  int maybe_cap = 0, emit_col = 0;
 };
 
 struct PairArgs;

@@ -44,6 +44,8 @@ struct PostBuffers {
   int* out_counts;        // [B]
   int n_levels;
   int lvl_start[4], lvl_w[4], lvl_stride[4];
+  const int* maybe_count;         // [B] rows the prediction convs wrote (objectness could still reach conf); nullptr:
+  const int* maybe_idx;           // [B,cap] their anchor indices                                   every row is there
   const FrameMeta* meta;          // device [B] or nullptr (no class filter)
   const tcd_class_filter* tables; // device [kMaxFilterTables]
 };

@@ -25,13 +25,25 @@ extern std::atomic<uint64_t> g_launch_count;
 
 __device__ __forceinline__ float sigmoid_acc(float x) { return 1.0f / (1.0f + expf(-x)); }
 
+// SPARSE: one warp per entry of the per-image list the prediction convs emitted (grid.y = image); otherwise one
+// warp per anchor of the dense prediction.
+template <bool SPARSE>
 __global__ void __launch_bounds__(256)
 decode_filter_kernel(const PostBuffers pb, const int raw) {
-  const int warp_global = (blockIdx.x * 256 + threadIdx.x) >> 5;
   const int lane = threadIdx.x & 31;
-  if (warp_global >= pb.B * pb.A) return;
-  const int b = warp_global / pb.A;
-  const int a = warp_global - b * pb.A;
+  int b, a;
+  if (SPARSE) {
+    b = blockIdx.y;
+    const int e = blockIdx.x * 8 + (threadIdx.x >> 5);
+    if (e >= min(pb.maybe_count[b], pb.cap)) return;
+    a = pb.maybe_idx[(size_t)b * pb.cap + e];
+  } else {
+    const int wg = (blockIdx.x * 256 + threadIdx.x) >> 5;
+    if (wg >= pb.B * pb.A) return;
+    b = wg / pb.A;
+    a = wg - b * pb.A;
+  }
+  const int warp_global = b * pb.A + a;
   const int E = 5 + pb.C;
   const float* row = pb.pred + (size_t)warp_global * E;
   float best = -1.0f;
@@ -365,7 +377,10 @@ int postproc_launch(const PostBuffers& pb, int raw, cudaStream_t stream, cudaEve
   cudaMemsetAsync(pb.cand_count, 0, sizeof(int) * pb.B, stream);
   const int warps = pb.B * pb.A;
   if (evs) cudaEventRecord(evs[0], stream);
-  decode_filter_kernel<<<cdiv(warps, 8), 256, 0, stream>>>(pb, raw);
+  if (pb.maybe_count != nullptr)
+    decode_filter_kernel<true><<<dim3(cdiv(pb.cap, 8), pb.B), 256, 0, stream>>>(pb, raw);
+  else
+    decode_filter_kernel<false><<<cdiv(warps, 8), 256, 0, stream>>>(pb, raw);
   if (evs) { cudaEventRecord(evs[1], stream); cudaEventRecord(evs[2], stream); }
   sort_kernel<<<pb.B, 1024, sort_smem, stream>>>(pb);
   if (evs) { cudaEventRecord(evs[3], stream); cudaEventRecord(evs[4], stream); }

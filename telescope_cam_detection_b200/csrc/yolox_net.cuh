@@ -44,6 +44,15 @@ struct NetOp {
   void* dst = nullptr;
   int N = 0, H = 0, W = 0, C = 0, s_ctot = 0, s_coff = 0, d_ctot = 0, d_coff = 0;
   std::string name;
+  int branch = 0;        // 0: the engine's stream; 1, 2: side branches (head levels 0 / 1) that fork off the trunk
+  int fork_branch = 0;   // != 0: this op's output is what branch `fork_branch` waits for
+};
+
+// side streams + events an engine lends to its plans so that independent layers overlap (YoloxPlan::run)
+struct PlanBranches {
+  cudaStream_t aux[2] = {nullptr, nullptr};
+  cudaEvent_t fork[2] = {nullptr, nullptr};
+  cudaEvent_t join[2] = {nullptr, nullptr};
 };
 
 struct YoloxWeights {
@@ -64,11 +73,20 @@ struct YoloxPlan {
   float* pred_raw = nullptr;  // f32 [B,A,5+C]
   int lvl_start[3], lvl_w[3], lvl_stride[3];
   double conv_flops = 0;
+  // candidate emission of the prediction convs (set before build; nullptr: every row is written)
+  const float* emit_thr = nullptr;
+  int* maybe_count = nullptr;
+  int* maybe_idx = nullptr;
+  int maybe_cap = 0;
 
   // ext_arena: lay the plan out over an existing arena (the engine's plan for its largest batch) instead of allocating;
   // the network input is always the first buffer, so every plan of an engine shares the input address
   int build(const YoloxWeights& wts, int B, int in_h, int in_w, void* ext_arena = nullptr, size_t ext_bytes = 0);
-  int run(cudaStream_t stream) const;
+  // br != nullptr: the head of pyramid level 0 (4 launches, a third of the network's FLOPs) starts as soon as the
+  // PAFPN has produced P3 and runs beside the remaining bottom-up layers (C3_n3, C3_n4: low-occupancy 40x40 / 20x20
+  // maps), level 1 likewise after P4; everything joins before the decode.  Works eagerly and under stream capture
+  // (the cross-stream event waits become graph edges).
+  int run(cudaStream_t stream, const PlanBranches* br = nullptr) const;
   int run_one(int i, cudaStream_t stream) const;
   void release();
 };

@@ -14,6 +14,7 @@ struct Builder {
   size_t cursor = 0;
   bool dry = true;  // first pass sizes the arena
   int rc = TCD_OK;
+  int cur_branch = 0;
 
   Builder(const YoloxWeights& w, YoloxPlan& p, int b) : wts(w), plan(p), B(b) {}
 
@@ -53,6 +54,7 @@ struct Builder {
     NetOp op;
     op.kind = OP_CONV;
     op.name = wname;
+    op.branch = cur_branch;
     rc = conv_plan_build(d, &op.conv);
     if (rc) return;
     plan.conv_flops += op.conv.flops;
@@ -69,9 +71,12 @@ struct Builder {
     d.silu = 0;
     d.out_f32 = plan.pred_raw; d.out_ld = 5 + plan.num_classes; d.out_col = col;
     d.rows_per_img = rows_per_img; d.row_off = row_off;
+    d.emit_thr = plan.emit_thr; d.maybe_count = plan.maybe_count; d.maybe_idx = plan.maybe_idx;
+    d.maybe_cap = plan.maybe_cap; d.emit_col = 4 - col;   // the fused prediction rows are [reg 0-3 | obj 4 | cls 5..]
     NetOp op;
     op.kind = OP_CONV;
     op.name = wname;
+    op.branch = cur_branch;
     rc = conv_plan_build(d, &op.conv);
     if (rc) return;
     if (flops > 0) op.conv.flops = flops;  // block-diagonal weights: count the non-zero half only
@@ -173,9 +178,11 @@ struct Builder {
     upsample(cat_n3, bc * 4, bc * 4, cat_p3, 0);
     Act pan2 = alloc("pan_out2", H8, W8, bc * 4);
     csp("C3_p3", cat_p3, 0, count_bottlenecks("C3_p3"), false, pan2, 0, H8, W8);
+    if (!dry && !rc && !plan.ops.empty()) plan.ops.back().fork_branch = 1;   // P3 ready: head level 0 may start
     conv("bu_conv2", pan2, 0, cat_n3, 0, 2);
     Act pan1 = alloc("pan_out1", H16, W16, bc * 8);
     csp("C3_n3", cat_n3, 0, count_bottlenecks("C3_n3"), false, pan1, 0, H16, W16);
+    if (!dry && !rc && !plan.ops.empty()) plan.ops.back().fork_branch = 2;   // P4 ready: head level 1 may start
     conv("bu_conv1", pan1, 0, cat_n4, 0, 2);
     Act pan0 = alloc("pan_out0", H32, W32, bc * 16);
     csp("C3_n4", cat_n4, 0, count_bottlenecks("C3_n4"), false, pan0, 0, H32, W32);
@@ -187,6 +194,7 @@ struct Builder {
     for (int l = 0; l < 3; ++l) {
       const std::string s = std::to_string(l);
       const Act& f = *feats[l];
+      cur_branch = l < 2 ? l + 1 : 0;
       const DevConv* hs = dc("head.stem." + s);
       if (!hs) return;
       const int hc = hs->cout;  // 128
@@ -237,11 +245,28 @@ int YoloxPlan::build(const YoloxWeights& wts, int B_, int in_h_, int in_w_, void
   return b.rc;
 }
 
-int YoloxPlan::run(cudaStream_t stream) const {
+int YoloxPlan::run(cudaStream_t stream, const PlanBranches* br) const {
+  bool used[3] = {false, false, false};
   for (size_t i = 0; i < ops.size(); ++i) {
-    int rc = run_one((int)i, stream);
+    const NetOp& op = ops[i];
+    cudaStream_t st = stream;
+    if (br && op.branch > 0) {
+      st = br->aux[op.branch - 1];
+      if (!used[op.branch]) {   // first op of the branch: wait for the trunk op that produced its input
+        TCD_CUDA_OK(cudaStreamWaitEvent(st, br->fork[op.branch - 1], 0));
+        used[op.branch] = true;
+      }
+    }
+    int rc = run_one((int)i, st);
     if (rc) return rc;
+    if (br && op.fork_branch > 0) TCD_CUDA_OK(cudaEventRecord(br->fork[op.fork_branch - 1], stream));
   }
+  if (br)
+    for (int b = 1; b <= 2; ++b)
+      if (used[b]) {
+        TCD_CUDA_OK(cudaEventRecord(br->join[b - 1], br->aux[b - 1]));
+        TCD_CUDA_OK(cudaStreamWaitEvent(stream, br->join[b - 1], 0));
+      }
   return TCD_OK;
 }
 
