@@ -242,6 +242,31 @@ tcd_status tcd_empty_filter_step(tcd_empty_filter* f, const uint8_t* frame, int6
 
 float tcd_empty_filter_last_ms(const tcd_empty_filter* f);  /* fused gray+blur+absdiff+count kernel, ms */
 
+/* ------------------------------------------------------------------ stream bank (K8-K10, batched)
+ * The per-camera filters of BASELINE configs[2] (64 streams, 8 per GPU) for all streams of one GPU at once:
+ * frames are uploaded ONCE and shared by the empty-frame gate, the background model and the detector
+ * (tcd_stream_bank_frame -> tcd_detector_submit(..., frames_on_device = 1)); the gate is ONE kernel launch
+ * over the streams, MotionFilter.filter_detections ONE background-model pass + ONE clean-up launch per round of
+ * up to 16 detections per stream, with no host synchronisation in between.  Same arithmetic as tcd_mog2_* /
+ * tcd_empty_filter_* (bit-exact vs cv2; src/empty_frame_filter.py:51-98, src/motion_filter.py:68-176).      */
+typedef struct tcd_stream_bank tcd_stream_bank;
+tcd_status tcd_stream_bank_create(int32_t n_streams, int32_t h, int32_t w, int32_t history, float var_threshold,
+                                  int32_t detect_shadows, int32_t blur_size, int32_t device, tcd_stream_bank** out);
+void tcd_stream_bank_destroy(tcd_stream_bank* b);
+/* what: 1 = background model (MotionFilter.reset_background), 2 = gate reference plane (EmptyFrameFilter.reset) */
+tcd_status tcd_stream_bank_reset(tcd_stream_bank* b, int32_t stream, int32_t what);
+/* frames_host[s] (HWC u8 BGR, row stride strides[s]; strides NULL = tight) or NULL when stream s has no frame */
+tcd_status tcd_stream_bank_upload(tcd_stream_bank* b, const uint8_t* const* frames_host, const int64_t* strides);
+const uint8_t* tcd_stream_bank_frame(tcd_stream_bank* b, int32_t stream);   /* device frame, row stride w*3 */
+void* tcd_stream_bank_cuda_stream(tcd_stream_bank* b);
+/* changed_host[s]: pixels with |blur(gray) - previous| > threshold; -1 first frame; -2 no frame this step */
+tcd_status tcd_stream_bank_gate(tcd_stream_bank* b, int32_t threshold, int32_t* changed_host);
+/* boxes of stream s = rois[offsets[s] .. offsets[s+1]) (clamped integer x1,y1,x2,y2); counts_host[i] = non-zero
+ * pixels of the cleaned mask inside box i after its own model update (the reference updates once per detection) */
+tcd_status tcd_stream_bank_motion(tcd_stream_bank* b, const int32_t* rois, const int32_t* offsets, int32_t shadow_thr,
+                                  int32_t ksize, int32_t blur_thr, int32_t* counts_host);
+tcd_status tcd_stream_bank_last_ms(const tcd_stream_bank* b, float out_ms[3]);
+
 /* ------------------------------------------------------------------ Stage-2 crops (K13)
  * Replaces the per-detection slice frame[y1:y2, x1:x2] (src/two_stage_pipeline_yolox.py:289)
  * + SpeciesClassifier.preprocess (src/species_classifier.py:311-350) for ALL crops of a

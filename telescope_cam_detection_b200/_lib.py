@@ -125,6 +125,16 @@ SIGNATURES = {
     "tcd_empty_filter_destroy": (None, [_P]),
     "tcd_empty_filter_reset": (C.c_int, [_P]),
     "tcd_empty_filter_step": (C.c_int, [_P, _P, C.c_int64, C.c_int32, C.c_int32, C.c_int32, _I32P, _P]),
+    "tcd_stream_bank_create": (C.c_int, [C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_float, C.c_int32, C.c_int32,
+                                         C.c_int32, _PP]),
+    "tcd_stream_bank_destroy": (None, [_P]),
+    "tcd_stream_bank_reset": (C.c_int, [_P, C.c_int32, C.c_int32]),
+    "tcd_stream_bank_upload": (C.c_int, [_P, _PP, _I64P]),
+    "tcd_stream_bank_frame": (C.c_void_p, [_P, C.c_int32]),
+    "tcd_stream_bank_cuda_stream": (C.c_void_p, [_P]),
+    "tcd_stream_bank_gate": (C.c_int, [_P, C.c_int32, _I32P]),
+    "tcd_stream_bank_motion": (C.c_int, [_P, _I32P, _I32P, C.c_int32, C.c_int32, C.c_int32, _I32P]),
+    "tcd_stream_bank_last_ms": (C.c_int, [_P, _F32P]),
     "tcd_crop_resize": (C.c_int, [_P, C.c_int32, C.c_int32, C.c_int64, _I32P, C.c_int32, C.c_int32,
                                   C.POINTER(PreprocCfg), C.c_int32, _P, _P]),
     "tcd_program_create": (C.c_int, [C.c_int32, _PP]),

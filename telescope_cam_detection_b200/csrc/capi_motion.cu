@@ -1,4 +1,6 @@
 // C ABI glue, part 3: MOG2 motion filter and empty-frame gate handles.
+#include <algorithm>
+#include <atomic>
 #include <math.h>
 #include <string.h>
 #include <vector>
@@ -8,6 +10,7 @@
 using namespace tcd;
 
 namespace tcd {
+extern std::atomic<uint64_t> g_h2d_bytes;
 
 // OpenCV's bit-exact u8 GaussianBlur uses an 8.8 fixed-point 1-D kernel built by
 // getGaussianKernelBitExact + getGaussianKernelFixedPoint_ED (imgproc/src/smooth.dispatch.cpp,
@@ -304,5 +307,259 @@ tcd_status tcd_empty_filter_step(tcd_empty_filter* f, const uint8_t* frame, int6
 }
 
 float tcd_empty_filter_last_ms(const tcd_empty_filter* f) { return f ? f->last_ms : 0.f; }
+
+}  // extern "C"
+
+// ------------------------------------------------------------------ stream bank: the per-camera filters, batched
+// BASELINE configs[2] (SURVEY 8(d) cfg 3): the streams of one GPU share ONE launch per kernel per step instead of
+// one synchronous C call per stream (and per detection): frames are uploaded once and shared by the gate, the
+// background model and the detector's preprocess (tcd_stream_bank_frame -> frames_on_device = 1).
+struct tcd_stream_bank {
+  int n = 0, h = 0, w = 0, history = 0, device = 0, detect_shadows = 1, blur_size = 21;
+  float var_threshold = 16.f;
+  size_t npix = 0;
+  cudaStream_t stream = nullptr;
+  std::vector<Mog2State> st;
+  std::vector<long long> nframes;
+  std::vector<char> have_prev, has_frame;
+  uint8_t* frames = nullptr;         // [n][h*w*3] this step's frames
+  uint8_t* fg = nullptr;             // [n][kMogMaxRepeats][npix]
+  uint8_t* prev = nullptr;           // [n][npix]
+  unsigned int* gate_counts = nullptr;   // [n]
+  unsigned int* roi_counts = nullptr;    // [roi_cap]
+  int roi_cap = 0;
+  BankStream* desc_dev = nullptr;    // [kDescRing][n]
+  BankStream* desc_host = nullptr;   // pinned mirror
+  int ring_pos = 0;
+  unsigned int* counts_pinned = nullptr;   // [max(n, roi_cap)]
+  cudaEvent_t ev[6] = {};
+  float last_ms[3] = {0.f, 0.f, 0.f};
+  uint16_t k[kBlurMaxK];
+};
+static constexpr int kDescRing = 64;
+
+extern "C" {
+
+tcd_status tcd_stream_bank_create(int32_t n_streams, int32_t h, int32_t w, int32_t history, float var_threshold,
+                                  int32_t detect_shadows, int32_t blur_size, int32_t device, tcd_stream_bank** out) {
+  TCD_REQUIRE(out && n_streams >= 1 && n_streams <= 64 && h > 0 && w > 0 && history > 0, "stream_bank_create: bad argument");
+  TCD_REQUIRE(blur_size == 21, "stream_bank_create: the batched kernels are the 21-tap case (got %d)", blur_size);
+  TCD_CUDA_OK(cudaSetDevice(device));
+  int rc = require_sm100();
+  if (rc) return (tcd_status)rc;
+  tcd_stream_bank* b = new tcd_stream_bank();
+  b->n = n_streams; b->h = h; b->w = w; b->history = history; b->device = device;
+  b->detect_shadows = detect_shadows; b->var_threshold = var_threshold; b->blur_size = blur_size;
+  b->npix = (size_t)h * w;
+  gaussian_kernel_q8(blur_size, b->k);
+  b->st.resize(n_streams);
+  b->nframes.assign(n_streams, 0);
+  b->have_prev.assign(n_streams, 0);
+  b->has_frame.assign(n_streams, 0);
+  const size_t np = b->npix;
+  TCD_CUDA_OK(cudaStreamCreateWithFlags(&b->stream, cudaStreamNonBlocking));
+  for (auto& e : b->ev) TCD_CUDA_OK(cudaEventCreate(&e));
+  for (int i = 0; i < n_streams; ++i) {
+    TCD_CUDA_OK(cudaMalloc((void**)&b->st[i].weight, np * kMogModes * 4));
+    TCD_CUDA_OK(cudaMalloc((void**)&b->st[i].var, np * kMogModes * 4));
+    TCD_CUDA_OK(cudaMalloc((void**)&b->st[i].mean, np * kMogModes * 3 * 4));
+    TCD_CUDA_OK(cudaMalloc((void**)&b->st[i].nmodes, np));
+    TCD_CUDA_OK(cudaMemset(b->st[i].nmodes, 0, np));
+  }
+  TCD_CUDA_OK(cudaMalloc((void**)&b->frames, np * 3 * n_streams));
+  TCD_CUDA_OK(cudaMalloc((void**)&b->fg, np * kMogMaxRepeats * n_streams));
+  TCD_CUDA_OK(cudaMemset(b->fg, 0, np * kMogMaxRepeats * n_streams));
+  TCD_CUDA_OK(cudaMalloc((void**)&b->prev, np * n_streams));
+  TCD_CUDA_OK(cudaMalloc((void**)&b->gate_counts, sizeof(unsigned int) * n_streams));
+  b->roi_cap = 4096;
+  TCD_CUDA_OK(cudaMalloc((void**)&b->roi_counts, sizeof(unsigned int) * b->roi_cap));
+  TCD_CUDA_OK(cudaMalloc((void**)&b->desc_dev, sizeof(BankStream) * kDescRing * n_streams));
+  TCD_CUDA_OK(cudaMallocHost((void**)&b->desc_host, sizeof(BankStream) * kDescRing * n_streams));
+  TCD_CUDA_OK(cudaMallocHost((void**)&b->counts_pinned, sizeof(unsigned int) * (size_t)std::max(n_streams, b->roi_cap)));
+  *out = b;
+  return TCD_OK;
+}
+
+void tcd_stream_bank_destroy(tcd_stream_bank* b) {
+  if (!b) return;
+  cudaSetDevice(b->device);
+  cudaStreamSynchronize(b->stream);
+  for (auto& s : b->st) {
+    cudaFree(s.weight); cudaFree(s.var); cudaFree(s.mean); cudaFree(s.nmodes);
+  }
+  void* ptrs[] = {b->frames, b->fg, b->prev, b->gate_counts, b->roi_counts, b->desc_dev};
+  for (void* p : ptrs) if (p) cudaFree(p);
+  if (b->desc_host) cudaFreeHost(b->desc_host);
+  if (b->counts_pinned) cudaFreeHost(b->counts_pinned);
+  for (auto& e : b->ev) if (e) cudaEventDestroy(e);
+  cudaStreamDestroy(b->stream);
+  delete b;
+}
+
+tcd_status tcd_stream_bank_reset(tcd_stream_bank* b, int32_t stream, int32_t what) {
+  TCD_REQUIRE(b && stream >= 0 && stream < b->n, "stream_bank_reset: bad argument");
+  TCD_CUDA_OK(cudaSetDevice(b->device));
+  if (what & 1) {   // background model (MotionFilter.reset_background)
+    b->nframes[stream] = 0;
+    TCD_CUDA_OK(cudaMemsetAsync(b->st[stream].nmodes, 0, b->npix, b->stream));
+  }
+  if (what & 2) b->have_prev[stream] = 0;   // gate (EmptyFrameFilter.reset)
+  return TCD_OK;
+}
+
+/* frames_host[s]: this step's frame of stream s (HWC u8 BGR, row stride strides[s] or tight when strides is NULL),
+ * NULL = the stream has no frame this step.  One pitched H2D copy per frame; asynchronous. */
+tcd_status tcd_stream_bank_upload(tcd_stream_bank* b, const uint8_t* const* frames_host, const int64_t* strides) {
+  TCD_REQUIRE(b && frames_host, "stream_bank_upload: null argument");
+  TCD_CUDA_OK(cudaSetDevice(b->device));
+  const size_t tight = (size_t)b->w * 3;
+  TCD_CUDA_OK(cudaEventRecord(b->ev[0], b->stream));
+  for (int s = 0; s < b->n; ++s) {
+    b->has_frame[s] = frames_host[s] != nullptr;
+    if (!frames_host[s]) continue;
+    const size_t st = strides && strides[s] > 0 ? (size_t)strides[s] : tight;
+    uint8_t* dst = b->frames + (size_t)s * b->npix * 3;
+    if (st == tight) TCD_CUDA_OK(cudaMemcpyAsync(dst, frames_host[s], tight * b->h, cudaMemcpyHostToDevice, b->stream));
+    else TCD_CUDA_OK(cudaMemcpy2DAsync(dst, tight, frames_host[s], st, tight, (size_t)b->h, cudaMemcpyHostToDevice, b->stream));
+    g_h2d_bytes.fetch_add((uint64_t)tight * b->h, std::memory_order_relaxed);
+  }
+  return TCD_OK;
+}
+
+const uint8_t* tcd_stream_bank_frame(tcd_stream_bank* b, int32_t stream) {
+  if (!b || stream < 0 || stream >= b->n) return nullptr;
+  return b->frames + (size_t)stream * b->npix * 3;
+}
+void* tcd_stream_bank_cuda_stream(tcd_stream_bank* b) { return b ? (void*)b->stream : nullptr; }
+
+static BankStream* bank_next_desc(tcd_stream_bank* b, BankStream** host) {
+  if (b->ring_pos == kDescRing) {   // every slot of the descriptor ring is in flight: drain once
+    cudaStreamSynchronize(b->stream);
+    b->ring_pos = 0;
+  }
+  *host = b->desc_host + (size_t)b->ring_pos * b->n;
+  return b->desc_dev + (size_t)(b->ring_pos++) * b->n;
+}
+
+/* EmptyFrameFilter.has_motion of every stream that got a frame in the last upload, ONE launch:
+ * changed_host[s] = changed-pixel count, -1 = first frame of the stream, -2 = no frame this step. */
+tcd_status tcd_stream_bank_gate(tcd_stream_bank* b, int32_t threshold, int32_t* changed_host) {
+  TCD_REQUIRE(b && changed_host, "stream_bank_gate: null argument");
+  TCD_CUDA_OK(cudaSetDevice(b->device));
+  BankStream* host = nullptr;
+  BankStream* dev = bank_next_desc(b, &host);
+  for (int s = 0; s < b->n; ++s) {
+    BankStream& d = host[s];
+    memset(&d, 0, sizeof(d));
+    d.frame = b->frames + (size_t)s * b->npix * 3;
+    d.stride = (long long)b->w * 3;
+    d.prev = b->prev + (size_t)s * b->npix;
+    d.counter = b->gate_counts + s;
+    d.active = b->has_frame[s] ? 1 : 0;
+    d.first = b->have_prev[s] ? 0 : 1;
+  }
+  TCD_CUDA_OK(cudaMemcpyAsync(dev, host, sizeof(BankStream) * b->n, cudaMemcpyHostToDevice, b->stream));
+  TCD_CUDA_OK(cudaMemsetAsync(b->gate_counts, 0, sizeof(unsigned int) * b->n, b->stream));
+  BlurArgs a;
+  memset(&a, 0, sizeof(a));
+  a.w = b->w; a.h = b->h; a.ksize = b->blur_size; a.in_stride = (long long)b->w * 3;
+  a.src_mode = 1; a.post_mode = 1; a.post_thr = threshold;
+  memcpy(a.k, b->k, sizeof(a.k));
+  cudaEventRecord(b->ev[1], b->stream);
+  int rc = bank_gate_launch(dev, b->n, a, b->stream);
+  if (rc) return (tcd_status)rc;
+  cudaEventRecord(b->ev[2], b->stream);
+  TCD_CUDA_OK(cudaMemcpyAsync(b->counts_pinned, b->gate_counts, sizeof(unsigned int) * b->n, cudaMemcpyDeviceToHost, b->stream));
+  TCD_CUDA_OK(cudaStreamSynchronize(b->stream));
+  b->ring_pos = 0;
+  for (int s = 0; s < b->n; ++s) {
+    if (!b->has_frame[s]) { changed_host[s] = -2; continue; }
+    changed_host[s] = b->have_prev[s] ? (int32_t)b->counts_pinned[s] : -1;
+    b->have_prev[s] = 1;
+  }
+  float t = 0.f;
+  if (cudaEventElapsedTime(&t, b->ev[1], b->ev[2]) == cudaSuccess) b->last_ms[0] = t;
+  return TCD_OK;
+}
+
+/* MotionFilter.filter_detections of every stream, batched.  Boxes of stream s: rois[offsets[s] .. offsets[s+1])
+ * (clamped integer x1,y1,x2,y2; a degenerate box still costs its model update, like the reference's early return
+ * after apply()).  Per box, in order: one background-model update with the stream's frame, (mask > shadow_thr),
+ * 21x21 blur, (> blur_thr), count inside the box -> counts_host.  Rounds of up to 16 boxes per stream share one
+ * model pass (state read and written once); nothing synchronises with the host until every count is back. */
+tcd_status tcd_stream_bank_motion(tcd_stream_bank* b, const int32_t* rois, const int32_t* offsets, int32_t shadow_thr,
+                                  int32_t ksize, int32_t blur_thr, int32_t* counts_host) {
+  TCD_REQUIRE(b && offsets && (offsets[b->n] == 0 || (rois && counts_host)), "stream_bank_motion: null argument");
+  TCD_REQUIRE(ksize == 21, "stream_bank_motion: the batched clean-up is the 21-tap case (got %d)", ksize);
+  TCD_CUDA_OK(cudaSetDevice(b->device));
+  const int total = offsets[b->n];
+  TCD_REQUIRE(total <= b->roi_cap, "stream_bank_motion: %d boxes exceed capacity %d", total, b->roi_cap);
+  if (total == 0) return TCD_OK;
+  int max_n = 0;
+  for (int s = 0; s < b->n; ++s) {
+    const int n_s = offsets[s + 1] - offsets[s];
+    TCD_REQUIRE(n_s >= 0 && (n_s == 0 || b->has_frame[s]), "stream_bank_motion: stream %d has boxes but no frame", s);
+    max_n = std::max(max_n, n_s);
+    for (int i = offsets[s]; i < offsets[s + 1]; ++i) {
+      const int32_t* r = rois + 4 * i;
+      TCD_REQUIRE(r[0] >= 0 && r[1] >= 0 && r[2] <= b->w && r[3] <= b->h, "stream_bank_motion: box %d not clamped", i);
+    }
+  }
+  TCD_CUDA_OK(cudaMemsetAsync(b->roi_counts, 0, sizeof(unsigned int) * total, b->stream));
+  Mog2Params p;
+  memset(&p, 0, sizeof(p));
+  p.npix = (int)b->npix; p.w = b->w; p.h = b->h; p.stride = (long long)b->w * 3;
+  p.Tb = b->var_threshold; p.TB = 0.9f; p.Tg = 9.0f; p.varInit = 15.0f; p.varMin = 4.0f;
+  p.varMax = 75.0f; p.CT = 0.05f; p.tau = 0.5f;
+  p.detect_shadows = b->detect_shadows;
+  BlurArgs a;
+  memset(&a, 0, sizeof(a));
+  a.w = b->w; a.h = b->h; a.ksize = ksize; a.in_stride = b->w;
+  a.src_mode = 0; a.pre_thr = shadow_thr; a.post_mode = 2; a.post_thr = blur_thr;
+  memcpy(a.k, b->k, sizeof(a.k));
+  cudaEventRecord(b->ev[3], b->stream);
+  int rounds = 0;
+  for (int c0 = 0; c0 < max_n; c0 += kMogMaxRepeats, ++rounds) {
+    BankStream* host = nullptr;
+    BankStream* dev = bank_next_desc(b, &host);
+    for (int s = 0; s < b->n; ++s) {
+      BankStream& d = host[s];
+      memset(&d, 0, sizeof(d));
+      const int n_s = offsets[s + 1] - offsets[s];
+      const int reps = std::max(0, std::min(kMogMaxRepeats, n_s - c0));
+      d.frame = b->frames + (size_t)s * b->npix * 3;
+      d.stride = (long long)b->w * 3;
+      d.st = b->st[s];
+      d.fg = b->fg + (size_t)s * kMogMaxRepeats * b->npix;
+      d.roi_counts = b->roi_counts + offsets[s] + c0;
+      d.repeats = reps;
+      for (int i = 0; i < reps; ++i) {
+        ++b->nframes[s];
+        const long long den = 2 * b->nframes[s] < b->history ? 2 * b->nframes[s] : b->history;
+        d.alpha[i] = (float)(1.0 / (double)den);
+        memcpy(d.roi[i], rois + 4 * (offsets[s] + c0 + i), 4 * sizeof(int));
+      }
+    }
+    TCD_CUDA_OK(cudaMemcpyAsync(dev, host, sizeof(BankStream) * b->n, cudaMemcpyHostToDevice, b->stream));
+    int rc = bank_mog2_launch(dev, b->n, p, b->stream);
+    if (rc == TCD_OK) rc = bank_roi_launch(dev, b->n, a, b->stream);
+    if (rc) return (tcd_status)rc;
+  }
+  cudaEventRecord(b->ev[4], b->stream);
+  TCD_CUDA_OK(cudaMemcpyAsync(b->counts_pinned, b->roi_counts, sizeof(unsigned int) * total, cudaMemcpyDeviceToHost, b->stream));
+  TCD_CUDA_OK(cudaStreamSynchronize(b->stream));
+  b->ring_pos = 0;
+  for (int i = 0; i < total; ++i) counts_host[i] = (int32_t)b->counts_pinned[i];
+  float t = 0.f;
+  if (cudaEventElapsedTime(&t, b->ev[3], b->ev[4]) == cudaSuccess) { b->last_ms[1] = t; b->last_ms[2] = (float)rounds; }
+  return TCD_OK;
+}
+
+/* [0] gate kernel ms of the last gate call, [1] model updates + clean-up + counts of the last motion call, [2] its rounds */
+tcd_status tcd_stream_bank_last_ms(const tcd_stream_bank* b, float out_ms[3]) {
+  TCD_REQUIRE(b && out_ms, "stream_bank_last_ms: null argument");
+  for (int i = 0; i < 3; ++i) out_ms[i] = b->last_ms[i];
+  return TCD_OK;
+}
 
 }  // extern "C"

@@ -227,36 +227,25 @@ __device__ __forceinline__ void conv_finish_cols(const ConvArgs& p, const uint32
   }
 }
 
-// mode 1: each epilogue warp streams its 32 staged rows to out_f32.  The 32 x n_valid block is walked
-// flat (element e = it*32 + lane -> row e / n_valid, column e % n_valid, kept incrementally), so every
-// iteration is an independent shuffle + ld.shared + st.global and consecutive lanes write consecutive
-// floats of a row.  (The first version walked row by row with a divide and a dependent generic load per
-// row: 440 cycles per row, 7 us per tile -- profiles/r01_conv_timeline.md.)
+// mode 1: each epilogue warp streams the staged rows it keeps to out_f32, one row at a time: consecutive lanes write
+// consecutive floats of the row (ceil(n_valid / 32) independent ld.shared + st.global per row).  With candidate
+// emission (YOLOX prediction convs) only ~1-2 % of the rows are kept, most warps have none and skip the flush.
+// (The first version walked every row with a divide and a dependent generic load per row: 440 cycles per row.)
 __device__ __forceinline__ void conv_flush_rows(const ConvArgs& p, const ConvTile& t, int q, int half, int lane,
                                                 const uint8_t* stage_base, bool valid, int y, int x) {
+  (void)half;
   const int nv = p.n_valid;
-  // element offset of the row this lane produced (lane L owns staged row q*32 + L); < 0: outside the image
+  // element offset of the row this lane produced (lane L owns staged row q*32 + L)
   const long long my_off =
-      valid ? ((long long)t.n_img * p.rows_per_img + p.row_off + (long long)y * p.Wo + x) * p.out_ld + p.out_col
-            : -1;
+      valid ? ((long long)t.n_img * p.rows_per_img + p.row_off + (long long)y * p.Wo + x) * p.out_ld + p.out_col : 0;
   const uint32_t st = smem_u32(stage_base) + (uint32_t)(q * 32) * (uint32_t)(p.BN + 1) * 4u;
-  // the warps of a quadrant interleave: warp `half` takes elements half*32 + lane + step*it
-  constexpr int step = 32 * (kConvEpiWarps / 4);
-  const int dr = step / nv, dc = step - dr * nv;
-  const int e0 = half * 32 + lane;
-  int r = e0 / nv, c = e0 - r * nv;
-  const int n_it = (32 * nv - half * 32 + step - 1) / step;
-#pragma unroll 4
-  for (int it = 0; it < n_it; ++it) {
-    const bool in = r < 32;
-    const long long off = __shfl_sync(0xffffffffu, my_off, r & 31);
-    if (in && off >= 0) p.out_f32[off + c] = lds_f32(st + (uint32_t)(r * (p.BN + 1) + c) * 4u);
-    r += dr;
-    c += dc;
-    if (c >= nv) {
-      c -= nv;
-      ++r;
-    }
+  unsigned m = __ballot_sync(0xffffffffu, valid);
+  while (m) {
+    const int r = __ffs(m) - 1;
+    m &= m - 1;
+    const long long off = __shfl_sync(0xffffffffu, my_off, r);
+    const uint32_t src = st + (uint32_t)(r * (p.BN + 1)) * 4u;
+    for (int c = lane; c < nv; c += 32) p.out_f32[off + c] = lds_f32(src + (uint32_t)c * 4u);
   }
 }
 
@@ -484,6 +473,8 @@ conv_umma_kernel(const __grid_constant__ ConvMaps maps, const __grid_constant__ 
     uint8_t* staging = smem + p.staging_off;
     if (p.pdl && p.resid != nullptr) pdl_wait();
     const float* bias_src = s_bias;   // always shared: a global/shared select makes every bias read a generic load
+    // candidate emission (f32 rows): the threshold is read once, long before the first accumulator is ready
+    const float emit_thr = (kMode == 1 && p.emit_thr != nullptr) ? p.emit_thr[0] * 0.999f - 1e-6f : 0.f;
     const int nslab = (p.BN + 31) >> 5;
     // Accumulator rounds: p.group consecutive tiles of this CTA share one round (group * BN <= 128 columns),
     // so the fixed per-round chain (barrier waits, proxy fence, TMA-store issue, staging hand-over: ~2 000
@@ -562,13 +553,22 @@ conv_umma_kernel(const __grid_constant__ ConvMaps maps, const __grid_constant__ 
           // a superset test (the decode kernel re-evaluates the exact score): drop the row only when its
           // objectness alone is clearly below the threshold
           const float obj = reinterpret_cast<const float*>(staging)[(size_t)row * (p.BN + 1) + p.emit_col];
-          keep = 1.0f / (1.0f + expf(-obj)) >= p.emit_thr[0] * 0.999f - 1e-6f;
-          if (keep) {
-            const int slot = atomicAdd(p.maybe_count + c.n_img, 1);
-            if (slot < p.maybe_cap) p.maybe_idx[(size_t)c.n_img * p.maybe_cap + slot] = p.row_off + y * p.Wo + x;
-          }
+          keep = 1.0f / (1.0f + expf(-obj)) >= emit_thr;
         }
         conv_flush_rows(p, c, q, half, lane, staging, keep, y, x);
+        if (p.emit_thr != nullptr) {
+          // the kept rows' anchors go to the image's list: ONE atomic per warp and image run (a patch never spans
+          // two images), issued after the rows are on their way so nothing waits for its return value
+          const unsigned m = __ballot_sync(0xffffffffu, keep);
+          if (m) {
+            int base = 0;
+            if (lane == __ffs(m) - 1) base = atomicAdd(p.maybe_count + c.n_img, __popc(m));
+            base = __shfl_sync(0xffffffffu, base, __ffs(m) - 1);
+            const int slot = base + __popc(m & ((1u << lane) - 1u));
+            if (keep && slot < p.maybe_cap)
+              p.maybe_idx[(size_t)c.n_img * p.maybe_cap + slot] = p.row_off + y * p.Wo + x;
+          }
+        }
       } else {
         fence_proxy_async_smem();
         asm volatile("bar.sync 1, %0;" ::"n"(32 * kConvEpiWarps) : "memory");

@@ -83,6 +83,23 @@ struct BlurArgs {
   int first;               // post_mode 1: no previous frame yet (just store)
   uint16_t k[kBlurMaxK];   // 8.8 fixed-point taps, sum 256
 };
+// One stream of a bank, as the batched kernels see it (device array, rewritten per launch)
+struct BankStream {
+  const uint8_t* frame;        // this step's frame (device, HWC u8 BGR)
+  long long stride;
+  Mog2State st;
+  uint8_t* fg;                 // [kMogMaxRepeats][npix] raw MOG2 masks, one plane per model update of the launch
+  uint8_t* prev;               // gate: previous blurred gray plane
+  unsigned int* counter;       // gate: changed-pixel counter
+  unsigned int* roi_counts;    // [kMogMaxRepeats] counters of this launch's boxes
+  int active, first;           // gate: stream has a frame this step / has no previous plane yet
+  int repeats;                 // motion: model updates (= boxes) of this launch, 0 = none
+  float alpha[kMogMaxRepeats];
+  int roi[kMogMaxRepeats][4];  // clamped integer boxes (x1,y1,x2,y2)
+};
+int bank_gate_launch(const BankStream* streams_dev, int n_streams, const BlurArgs& a, cudaStream_t stream);
+int bank_mog2_launch(const BankStream* streams_dev, int n_streams, const Mog2Params& p, cudaStream_t stream);
+int bank_roi_launch(const BankStream* streams_dev, int n_streams, const BlurArgs& a, cudaStream_t stream);
 int mog2_launch(const uint8_t* frame, const Mog2State& st, const Mog2Params& p, uint8_t* fgmask,
                 cudaStream_t stream);
 int blur_launch(const uint8_t* src, const BlurArgs& a, uint8_t* dst, uint8_t* prev,

@@ -28,11 +28,52 @@ extern std::atomic<uint64_t> g_launch_count;
     _t = m2[i]; m2[i] = m2[j]; m2[j] = _t;                                                 \
   } while (0)
 
-__global__ void __launch_bounds__(256)
-mog2_apply_kernel(const uint8_t* __restrict__ frame, const Mog2State st, const Mog2Params p,
-                  uint8_t* __restrict__ fgmask) {
-  const int idx = blockIdx.x * 256 + threadIdx.x;
-  if (idx >= p.npix) return;
+// mask value of the current state: 0 background, 127 shadow, 255 foreground
+__device__ __forceinline__ uint8_t mog2_mask_value(const Mog2Params& p, bool bg, int n, float x0, float x1, float x2,
+                                                   const float (&w)[kMogModes], const float (&v)[kMogModes],
+                                                   const float (&m0)[kMogModes], const float (&m1)[kMogModes],
+                                                   const float (&m2)[kMogModes]) {
+  uint8_t out = 0;
+  if (!bg) {
+    out = 255;
+    if (p.detect_shadows) {
+      float tW = 0.f;
+      bool done = false;
+#pragma unroll
+      for (int mode = 0; mode < kMogModes; ++mode) {
+        if (mode < n && !done) {
+          const float num = ((x0 * m0[mode]) + (x1 * m1[mode])) + (x2 * m2[mode]);
+          const float den = ((m0[mode] * m0[mode]) + (m1[mode] * m1[mode])) + (m2[mode] * m2[mode]);
+          if (den == 0.f) {
+            done = true;
+          } else {
+            if (num <= den && num >= (p.tau * den)) {
+              const float a = num / den;
+              const float e0 = (a * m0[mode]) - x0, e1 = (a * m1[mode]) - x1, e2 = (a * m2[mode]) - x2;
+              const float s = ((e0 * e0) + (e1 * e1)) + (e2 * e2);
+              if (s < (((p.Tb * v[mode]) * a) * a)) {
+                out = 127;
+                done = true;
+              }
+            }
+            if (!done) {
+              tW = tW + w[mode];
+              if (tW > p.TB) done = true;
+            }
+          }
+        }
+      }
+    }
+  }
+  return out;
+}
+
+// One thread per pixel; p.repeats model updates with the same pixel, the state staying in registers (the reference
+// calls apply() once per detection with the same frame).  rois == nullptr: the mask of the LAST update goes
+// to fgmask.  rois != nullptr (the batched filter): update r is only judged inside box r, so its mask is written to
+// plane r of fgmask ([repeats][npix]) and only where the 21x21 clean-up of that box can see it (box +- 10 px).
+__device__ __forceinline__ void mog2_body(const uint8_t* __restrict__ frame, const Mog2State& st, const Mog2Params& p,
+                                          uint8_t* __restrict__ fgmask, const int idx, const int (*rois)[4]) {
   const int py = idx / p.w, px = idx - py * p.w;
   const uint8_t* pp = frame + (long long)py * p.stride + px * 3;
   const float x0 = (float)pp[0], x1 = (float)pp[1], x2 = (float)pp[2];
@@ -134,41 +175,13 @@ mog2_apply_kernel(const uint8_t* __restrict__ frame, const Mog2State st, const M
       }
     }
     n = nmodes;
-  }
-  // shadow test on the final state
-  uint8_t out = 0;
-  if (!bg) {
-    out = 255;
-    if (p.detect_shadows) {
-      float tW = 0.f;
-      bool done = false;
-#pragma unroll
-      for (int mode = 0; mode < kMogModes; ++mode) {
-        if (mode < n && !done) {
-          const float num = ((x0 * m0[mode]) + (x1 * m1[mode])) + (x2 * m2[mode]);
-          const float den = ((m0[mode] * m0[mode]) + (m1[mode] * m1[mode])) + (m2[mode] * m2[mode]);
-          if (den == 0.f) {
-            done = true;
-          } else {
-            if (num <= den && num >= (p.tau * den)) {
-              const float a = num / den;
-              const float e0 = (a * m0[mode]) - x0, e1 = (a * m1[mode]) - x1, e2 = (a * m2[mode]) - x2;
-              const float s = ((e0 * e0) + (e1 * e1)) + (e2 * e2);
-              if (s < (((p.Tb * v[mode]) * a) * a)) {
-                out = 127;
-                done = true;
-              }
-            }
-            if (!done) {
-              tW = tW + w[mode];
-              if (tW > p.TB) done = true;
-            }
-          }
-        }
-      }
+    if (rois != nullptr) {
+      const int* r = rois[rep];
+      if (px >= r[0] - 10 && px < r[2] + 10 && py >= r[1] - 10 && py < r[3] + 10)
+        fgmask[(size_t)rep * p.npix + idx] = mog2_mask_value(p, bg, n, x0, x1, x2, w, v, m0, m1, m2);
     }
   }
-  fgmask[idx] = out;
+  if (rois == nullptr) fgmask[idx] = mog2_mask_value(p, bg, n, x0, x1, x2, w, v, m0, m1, m2);
   const int n_wr = n > n_in ? n : n_in;  // slots that may have changed
 #pragma unroll
   for (int k = 0; k < kMogModes; ++k) {
@@ -182,6 +195,28 @@ mog2_apply_kernel(const uint8_t* __restrict__ frame, const Mog2State st, const M
     }
   }
   st.nmodes[idx] = (uint8_t)n;
+}
+
+__global__ void __launch_bounds__(256)
+mog2_apply_kernel(const uint8_t* __restrict__ frame, const Mog2State st, const Mog2Params p,
+                  uint8_t* __restrict__ fgmask) {
+  const int idx = blockIdx.x * 256 + threadIdx.x;
+  if (idx >= p.npix) return;
+  mog2_body(frame, st, p, fgmask, idx, nullptr);
+}
+
+// every stream of a bank in ONE launch (grid.y = stream): per-stream frame, state, update count and boxes
+__global__ void __launch_bounds__(256) bank_mog2_kernel(const BankStream* __restrict__ streams, const Mog2Params base) {
+  const BankStream& s = streams[blockIdx.y];
+  if (s.repeats <= 0) return;
+  const int idx = blockIdx.x * 256 + threadIdx.x;
+  if (idx >= base.npix) return;
+  Mog2Params p = base;
+  p.stride = s.stride;
+  p.repeats = s.repeats;
+#pragma unroll
+  for (int i = 0; i < kMogMaxRepeats; ++i) p.alpha[i] = s.alpha[i];
+  mog2_body(s.frame, s.st, p, s.fg, idx, s.roi);
 }
 
 // ------------------------------------------------------------------ u8 Gaussian blur (OpenCV fixed point)
@@ -295,12 +330,15 @@ __device__ __forceinline__ unsigned int b21_hsum(const unsigned int (&w)[8], con
   return acc;
 }
 
-__global__ void __launch_bounds__(256)
-blur21_kernel(const uint8_t* __restrict__ src, const BlurArgs a, const Blur21Taps taps,
-              uint8_t* __restrict__ dst, uint8_t* __restrict__ prev, unsigned int* __restrict__ counter) {
+// post_mode 2 (batched motion filter): nothing is written; pixels with v > post_thr inside roi = (x1,y1,x2,y2) are
+// counted into *counter (the cleaned mask is only ever looked at inside the detection's box).
+__device__ __forceinline__ void blur21_body(const uint8_t* __restrict__ src, const BlurArgs& a, const Blur21Taps& taps,
+                                            uint8_t* __restrict__ dst, uint8_t* __restrict__ prev,
+                                            unsigned int* __restrict__ counter, const int bx, const int by,
+                                            const int* roi) {
   __shared__ unsigned int s_in[kB21InH][kB21InWords + 2];   // +2: the last group's 7th/8th word reads
   __shared__ unsigned int s_h[kB21InH / 2][kB21TW];         // (row 2r, row 2r+1) u16 pairs
-  const int x0 = blockIdx.x * kB21TW, y0 = blockIdx.y * kB21TH;
+  const int x0 = bx * kB21TW, y0 = by * kB21TH;
   const bool aligned = (a.in_stride & 3) == 0 && (reinterpret_cast<uintptr_t>(src) & 3) == 0;
 
   // ---- stage A (three groups per thread in flight: all loads are issued before the first use)
@@ -430,6 +468,8 @@ blur21_kernel(const uint8_t* __restrict__ src, const BlurArgs a, const Blur21Tap
         const size_t o = (size_t)gy * a.w + gx;
         if (a.post_mode == 0) {
           dst[o] = v > a.post_thr ? 255 : 0;
+        } else if (a.post_mode == 2) {
+          local += (v > a.post_thr && gx >= roi[0] && gx < roi[2] && gy >= roi[1] && gy < roi[3]) ? 1u : 0u;
         } else {
           if (!a.first) {
             const int d = abs(v - pv[2 * q + par]);
@@ -441,7 +481,7 @@ blur21_kernel(const uint8_t* __restrict__ src, const BlurArgs a, const Blur21Tap
       }
     }
   }
-  if (a.post_mode == 1 && !a.first) {   // one atomic per CTA
+  if ((a.post_mode == 1 && !a.first) || a.post_mode == 2) {   // one atomic per CTA
     __shared__ unsigned int s_cnt;
     if (threadIdx.x == 0) s_cnt = 0;
     __syncthreads();
@@ -450,6 +490,40 @@ blur21_kernel(const uint8_t* __restrict__ src, const BlurArgs a, const Blur21Tap
     __syncthreads();
     if (threadIdx.x == 0 && s_cnt) atomicAdd(counter, s_cnt);
   }
+}
+
+__global__ void __launch_bounds__(256)
+blur21_kernel(const uint8_t* __restrict__ src, const BlurArgs a, const Blur21Taps taps,
+              uint8_t* __restrict__ dst, uint8_t* __restrict__ prev, unsigned int* __restrict__ counter) {
+  blur21_body(src, a, taps, dst, prev, counter, blockIdx.x, blockIdx.y, nullptr);
+}
+
+// Empty-frame gate of every stream of a bank in ONE launch (grid.z = stream): gray + 21x21 blur + absdiff against the
+// stream's previous plane + count, previous plane updated in place.
+__global__ void __launch_bounds__(256)
+bank_gate_kernel(const BankStream* __restrict__ streams, const BlurArgs base, const Blur21Taps taps) {
+  const BankStream& s = streams[blockIdx.z];
+  if (!s.active) return;
+  BlurArgs a = base;
+  a.in_stride = s.stride;
+  a.first = s.first;
+  blur21_body(s.frame, a, taps, nullptr, s.prev, s.counter, blockIdx.x, blockIdx.y, nullptr);
+}
+
+// Mask clean-up + count of round r of every stream (grid.z = stream * kMogMaxRepeats + r): shadow threshold, 21x21
+// blur, threshold, count inside box r -- only the tiles that touch the box do any work.
+__global__ void __launch_bounds__(256)
+bank_roi_kernel(const BankStream* __restrict__ streams, const BlurArgs base, const Blur21Taps taps) {
+  const BankStream& s = streams[blockIdx.z / kMogMaxRepeats];
+  const int r = blockIdx.z % kMogMaxRepeats;
+  if (r >= s.repeats) return;
+  const int* roi = s.roi[r];
+  const int x0 = blockIdx.x * kB21TW, y0 = blockIdx.y * kB21TH;
+  if (roi[2] <= roi[0] || roi[3] <= roi[1] || x0 >= roi[2] || x0 + kB21TW <= roi[0] || y0 >= roi[3] ||
+      y0 + kB21TH <= roi[1])
+    return;
+  blur21_body(s.fg + (size_t)r * base.w * base.h, base, taps, nullptr, nullptr, s.roi_counts + r, blockIdx.x,
+              blockIdx.y, roi);
 }
 
 // no-blur variant of the mask clean-up: (m > pre_thr) only (motion_blur_size <= 0)
@@ -543,6 +617,42 @@ int mog2_launch(const uint8_t* frame, const Mog2State& st, const Mog2Params& p, 
     return TCD_ERR_CUDA;
   }
   return TCD_OK;
+}
+
+static void blur21_taps(const BlurArgs& a, Blur21Taps* tp) {
+  memset(tp, 0, sizeof(*tp));
+  auto k = [&](int t) -> unsigned int { return (t >= 0 && t < 21) ? a.k[t] : 0u; };
+  for (int m = 0; m < 6; ++m)
+    tp->h4[m] = k(4 * m) | (k(4 * m + 1) << 8) | (k(4 * m + 2) << 16) | (k(4 * m + 3) << 24);
+  for (int m = 0; m < 11; ++m) {
+    tp->ve[m] = k(2 * m) | (k(2 * m + 1) << 8);
+    tp->vo[m] = k(2 * m - 1) | (k(2 * m) << 8);
+  }
+}
+
+int bank_gate_launch(const BankStream* streams_dev, int n_streams, const BlurArgs& a, cudaStream_t stream) {
+  TCD_REQUIRE(a.ksize == 21, "stream bank: the batched gate needs blur_size 21 (got %d)", a.ksize);
+  Blur21Taps tp;
+  blur21_taps(a, &tp);
+  bank_gate_kernel<<<dim3(cdiv(a.w, kB21TW), cdiv(a.h, kB21TH), n_streams), 256, 0, stream>>>(streams_dev, a, tp);
+  g_launch_count.fetch_add(1, std::memory_order_relaxed);
+  return cudaGetLastError() == cudaSuccess ? TCD_OK : TCD_ERR_CUDA;
+}
+
+int bank_mog2_launch(const BankStream* streams_dev, int n_streams, const Mog2Params& p, cudaStream_t stream) {
+  bank_mog2_kernel<<<dim3(cdiv(p.npix, 256), n_streams), 256, 0, stream>>>(streams_dev, p);
+  g_launch_count.fetch_add(1, std::memory_order_relaxed);
+  return cudaGetLastError() == cudaSuccess ? TCD_OK : TCD_ERR_CUDA;
+}
+
+int bank_roi_launch(const BankStream* streams_dev, int n_streams, const BlurArgs& a, cudaStream_t stream) {
+  TCD_REQUIRE(a.ksize == 21, "stream bank: the batched clean-up needs motion_blur_size 21 (got %d)", a.ksize);
+  Blur21Taps tp;
+  blur21_taps(a, &tp);
+  bank_roi_kernel<<<dim3(cdiv(a.w, kB21TW), cdiv(a.h, kB21TH), n_streams * kMogMaxRepeats), 256, 0, stream>>>(
+      streams_dev, a, tp);
+  g_launch_count.fetch_add(1, std::memory_order_relaxed);
+  return cudaGetLastError() == cudaSuccess ? TCD_OK : TCD_ERR_CUDA;
 }
 
 int threshold_launch(const uint8_t* src, int n, int thr, uint8_t* dst, cudaStream_t stream) {

@@ -388,3 +388,82 @@ class EmptyGateEngine:
                                              blur.ctypes.data_as(C.c_void_p) if want_blur else None),
               "tcd_empty_filter_step")
         return cnt.value, blur
+
+
+class StreamBankEngine:
+    """One tcd_stream_bank handle: the gate reference planes, MOG2 models and this step's frames of every camera
+    stream of one GPU, with batched kernels (include/tcd.h, stream bank)."""
+
+    def __init__(self, n_streams, h, w, history=500, var_threshold=16, detect_shadows=True, blur_size=21, device=0):
+        self.lib = _lib.load()
+        self.n, self.h, self.w = int(n_streams), int(h), int(w)
+        hd = C.c_void_p()
+        check(self.lib.tcd_stream_bank_create(self.n, self.h, self.w, int(history), float(var_threshold),
+                                              1 if detect_shadows else 0, int(blur_size), device_index(device),
+                                              C.byref(hd)), "tcd_stream_bank_create")
+        self.handle = hd
+        self._keep = None
+
+    def close(self):
+        if getattr(self, "handle", None):
+            self.lib.tcd_stream_bank_destroy(self.handle)
+            self.handle = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def reset(self, stream, model=True, gate=True):
+        check(self.lib.tcd_stream_bank_reset(self.handle, int(stream), (1 if model else 0) | (2 if gate else 0)),
+              "tcd_stream_bank_reset")
+
+    def upload(self, frames):
+        """frames: one HxWx3 uint8 host array (or None) per stream."""
+        if len(frames) != self.n:
+            raise ValueError("expected %d frames (None for idle streams), got %d" % (self.n, len(frames)))
+        ptrs, strides, keep = [], [], []
+        for f in frames:
+            if f is None:
+                ptrs.append(0)
+                strides.append(0)
+                continue
+            ptr, h, w, stride, on_dev, k = _plane_desc(f, 3)
+            if on_dev or (h, w) != (self.h, self.w):
+                raise ValueError("stream bank frames must be %dx%d host arrays" % (self.h, self.w))
+            ptrs.append(ptr)
+            strides.append(stride)
+            keep.append(k)
+        self._keep = keep   # the copies are asynchronous: the arrays stay alive until the next call synchronises
+        check(self.lib.tcd_stream_bank_upload(self.handle, _lib.ptr_array(ptrs), _lib.i64_array(strides)),
+              "tcd_stream_bank_upload")
+
+    def frame_ptr(self, stream):
+        return int(self.lib.tcd_stream_bank_frame(self.handle, int(stream)) or 0)
+
+    def cuda_stream(self):
+        return int(self.lib.tcd_stream_bank_cuda_stream(self.handle) or 0)
+
+    def gate(self, threshold=25):
+        """-> int32[n]: changed-pixel count per stream, -1 on a stream's first frame, -2 when it had no frame."""
+        out = np.zeros((self.n,), np.int32)
+        check(self.lib.tcd_stream_bank_gate(self.handle, int(threshold), out.ctypes.data_as(_lib._I32P)),
+              "tcd_stream_bank_gate")
+        return out
+
+    def motion(self, rois, offsets, shadow_thr=200, ksize=21, blur_thr=25):
+        """rois: int32 [total,4] clamped boxes, offsets: int32 [n+1].  -> int32[total] motion-pixel counts."""
+        rois = np.ascontiguousarray(rois, np.int32).reshape(-1, 4)
+        offsets = np.ascontiguousarray(offsets, np.int32)
+        counts = np.zeros((max(rois.shape[0], 1),), np.int32)
+        check(self.lib.tcd_stream_bank_motion(self.handle, rois.ctypes.data_as(_lib._I32P),
+                                              offsets.ctypes.data_as(_lib._I32P), int(shadow_thr), int(ksize),
+                                              int(blur_thr), counts.ctypes.data_as(_lib._I32P)),
+              "tcd_stream_bank_motion")
+        return counts[:rois.shape[0]]
+
+    def last_ms(self):
+        t = (C.c_float * 3)()
+        check(self.lib.tcd_stream_bank_last_ms(self.handle, t), "tcd_stream_bank_last_ms")
+        return {"gate_ms": float(t[0]), "motion_ms": float(t[1]), "motion_rounds": int(t[2])}

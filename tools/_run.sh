@@ -1,15 +1,7 @@
 #!/bin/bash
-T=${1:-s38}
+T=${1:-s40}
 mkdir -p gpurun_out
-timeout 900 python -m pytest tests -m gpu -q -x > gpurun_out/${T}_pytest.log 2>&1; echo "pytest rc=$?"
-grep -E "passed|failed|FAILED|Error|confident oracle" gpurun_out/${T}_pytest.log | head -40
-: > gpurun_out/${T}_ab.jsonl
-run() { echo "== $*" >> gpurun_out/${T}_ab.jsonl; env "$@" timeout 200 python bench.py --quick --steps 120 --warmup 10 ${BARGS} >> gpurun_out/${T}_ab.jsonl 2>> gpurun_out/${T}_ab.err; }
-BARGS="" run TCD_ENGINES=3
-BARGS="" run TCD_ENGINES=3 TCD_NO_BRANCH=1
-BARGS="" run TCD_ENGINES=3 TCD_NO_EMIT=1
-BARGS="" run TCD_ENGINES=4
-BARGS="" run TCD_ENGINES=2
-BARGS="" run TCD_ENGINES=4 TCD_CONV_SHARE=0
-cat gpurun_out/${T}_ab.jsonl | cut -c1-200
-tail -5 gpurun_out/${T}_ab.err
+timeout 600 python -m pytest tests/test_gpu_stream_bank.py tests/test_gpu_motion.py -q -x > gpurun_out/${T}_bank.log 2>&1; echo "bank rc=$?"
+grep -E "passed|failed|FAILED|Error|assert" gpurun_out/${T}_bank.log | head -20
+timeout 600 python bench.py --quick --steps 60 --warmup 10 --dump-ops gpurun_out/${T}_ops.json > gpurun_out/${T}_q.json 2>gpurun_out/${T}.err; cut -c1-200 gpurun_out/${T}_q.json
+python tools/show_ops.py gpurun_out/${T}_ops.json | grep -E "pred|decode|total"
