@@ -170,7 +170,8 @@ conv_pair_kernel(const __grid_constant__ ConvMaps maps, const __grid_constant__ 
   }
   if (warp == 1) tmem_alloc2(&tmem_base_s, 256);
   if (warp >= 2)
-    for (int i = threadIdx.x - 64; i < p.bias_n; i += 32 * kConvEpiWarps) s_bias[i] = __ldg(p.bias + i);
+    for (int i = threadIdx.x - 64; i < p.bias_n; i += 32 * kConvEpiWarps)
+      s_bias[i] = (ACT == 1 ? 0.5f : 1.0f) * __ldg(p.bias + i);   // SiLU layers: see conv_finish_silu
   tc_fence_before();
   __syncthreads();
   cluster_sync_all();                    // the peer's barriers are initialised before anything arrives on them

@@ -284,6 +284,7 @@ int conv_plan_build(const ConvDesc& d, ConvPlan* plan) {
   TCD_REQUIRE(d.stride == 1 || d.k == 3, "conv: stride 2 only for 3x3");
   const int mode = d.out_f32 ? 1 : 0;
   TCD_REQUIRE(d.groups >= 1 && d.cout % d.groups == 0, "conv: %d groups do not divide cout %d", d.groups, d.cout);
+  TCD_REQUIRE(!(d.silu == 1 && d.resid && d.resid_pre), "conv: SiLU layers add their residual after the activation");
   if (pair_eligible(d, mode)) return pair_plan_build(d, plan);
   ConvArgs& a = plan->args;
   a.Ho = d.H / d.stride;

@@ -175,10 +175,72 @@ __device__ __forceinline__ void conv_add_resid(const ConvArgs& p, float (&v)[NC]
   }
 }
 
+// SiLU + bf16 staging of one slab, the hot epilogue (every BaseConv of YOLOX): packed fp32 math.
+//   x*sigmoid(x) = h + h*tanh(h), h = x/2 = 0.5*acc + 0.5*bias: s_bias holds the HALVED bias for these kernels, so a
+//   slab of 32 columns costs 16 FFMA2 + 32 MUFU.TANH + 16 FFMA2 + 16 F2FP instead of 96 scalar fp32 ops + 32 MUFU
+//   (measured on dark3.1.conv12, ncu warp sampling: the epilogue warps issued one instruction per 4.6 cycles and
+//   spent 4 700 cycles per 128x128 tile against 512 cycles of MMA).  The residual of a CSP bottleneck is added after
+//   the activation, also as FADD2.  Staging stores are explicit st.shared (the generic form compiled to ST).
+template <int NC, int OFF>
+__device__ __forceinline__ void conv_finish_silu(const ConvArgs& p, const uint32_t (&r)[32], int c0, uint32_t bias_saddr,
+                                                 int row, bool valid, const ConvTile& t, int y, int x,
+                                                 uint32_t stage_saddr) {
+  const uint64_t half2 = f32x2(0.5f, 0.5f);
+  uint64_t o[NC / 2];
+  const uint32_t baddr = bias_saddr + (uint32_t)(t.n_tile * p.BN + c0) * 4u;
+#pragma unroll
+  for (int j = 0; j < NC / 4; ++j) {
+    const float4 b = lds_v4f(baddr + 16u * j);
+    const uint64_t h0 = fma_f32x2(f32x2_bits(r[OFF + 4 * j + 0], r[OFF + 4 * j + 1]), half2, f32x2(b.x, b.y));
+    const uint64_t h1 = fma_f32x2(f32x2_bits(r[OFF + 4 * j + 2], r[OFF + 4 * j + 3]), half2, f32x2(b.z, b.w));
+    float a0, a1, a2, a3;
+    f32x2_split(h0, a0, a1);
+    f32x2_split(h1, a2, a3);
+    o[2 * j + 0] = fma_f32x2(h0, f32x2(tanh_approx(a0), tanh_approx(a1)), h0);
+    o[2 * j + 1] = fma_f32x2(h1, f32x2(tanh_approx(a2), tanh_approx(a3)), h1);
+  }
+  if (p.resid != nullptr && valid) {   // YOLOX bottlenecks: y = act(conv(x)) + x
+    const __nv_bfloat16* rp = p.resid + (size_t)t.n_img * p.r_nstride + ((size_t)y * p.Wo + x) * p.r_ctot +
+                              p.r_coff + t.n_tile * p.BN + c0;
+    const uint4* rp4 = reinterpret_cast<const uint4*>(rp);
+#pragma unroll
+    for (int u = 0; u < NC / 8; ++u) {
+      const uint4 q = __ldg(rp4 + u);
+      const uint32_t w[4] = {q.x, q.y, q.z, q.w};
+#pragma unroll
+      for (int e = 0; e < 4; ++e)   // bf16 pair -> two fp32: the low half shifted up, the high half masked
+        o[u * 4 + e] = add_f32x2(o[u * 4 + e], f32x2_bits(w[e] << 16, w[e] & 0xffff0000u));
+    }
+  }
+  // out_chunk is 32 or 64: shifts, not integer divides (which go through the MUFU pipe)
+  const int cs = p.out_chunk == 64 ? 6 : 5;
+  const int chunk = c0 >> cs;
+  const int row_bytes = p.out_chunk * 2;
+  const int u0 = (c0 & (p.out_chunk - 1)) >> 3;
+  const int sw = (p.out_chunk == 64) ? (row & 7) : ((row >> 1) & 3);
+  const uint32_t rowa = stage_saddr + (uint32_t)(chunk * 128 * row_bytes + row * row_bytes);
+#pragma unroll
+  for (int u = 0; u < NC / 8; ++u) {
+    uint32_t w[4];
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      float lo, hi;
+      f32x2_split(o[u * 4 + e], lo, hi);
+      w[e] = pack_bf16x2(lo, hi);
+    }
+    sts_v4(rowa + (uint32_t)(((u0 + u) ^ sw) << 4), w[0], w[1], w[2], w[3]);
+  }
+}
+
 template <int NC, int OFF, int ACT, int MODE>
 __device__ __forceinline__ void conv_finish_cols(const ConvArgs& p, const uint32_t (&r)[32], int c0,
                                                  const float* bias_g, int row, bool valid,
                                                  const ConvTile& t, int y, int x, uint8_t* stage_base) {
+  if constexpr (ACT == 1 && MODE == 0) {
+    // (a residual BEFORE the activation only occurs with ReLU in the ResNet programs; SiLU layers add it after)
+    conv_finish_silu<NC, OFF>(p, r, c0, smem_u32(bias_g), row, valid, t, y, x, smem_u32(stage_base));
+    return;
+  }
   float v[NC];
   const float4* b4 = reinterpret_cast<const float4*>(bias_g + t.n_tile * p.BN + c0);
 #pragma unroll
@@ -221,9 +283,9 @@ __device__ __forceinline__ void conv_finish_cols(const ConvArgs& p, const uint32
   } else {
     // f32 prediction rows: park the slab in this warp's private staging rows (stride BN+1 words,
     // conflict-free); conv_flush_rows() writes them out coalesced
-    float* srow = reinterpret_cast<float*>(stage_base) + (size_t)row * (p.BN + 1) + c0;
+    const uint32_t srow = smem_u32(stage_base) + (uint32_t)(row * (p.BN + 1) + c0) * 4u;
 #pragma unroll
-    for (int j = 0; j < NC; ++j) srow[j] = v[j];
+    for (int j = 0; j < NC; ++j) asm volatile("st.shared.f32 [%0], %1;" ::"r"(srow + 4u * j), "f"(v[j]) : "memory");
   }
 }
 
@@ -296,7 +358,8 @@ conv_umma_kernel(const __grid_constant__ ConvMaps maps, const __grid_constant__ 
   if (warp == 1) tmem_alloc(&tmem_base_s, (uint32_t)p.tmem_cols);
   // the bias never depends on the previous layer: stage it while the pipeline spins up
   if (warp >= 2)
-    for (int i = threadIdx.x - 64; i < p.bias_n; i += 32 * kConvEpiWarps) s_bias[i] = __ldg(p.bias + i);
+    for (int i = threadIdx.x - 64; i < p.bias_n; i += 32 * kConvEpiWarps)
+      s_bias[i] = (ACT == 1 && kMode == 0 ? 0.5f : 1.0f) * __ldg(p.bias + i);   // SiLU layers: see conv_finish_silu
   tc_fence_before();
   __syncthreads();
   tc_fence_after();

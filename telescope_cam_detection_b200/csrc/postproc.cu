@@ -25,24 +25,9 @@ extern std::atomic<uint64_t> g_launch_count;
 
 __device__ __forceinline__ float sigmoid_acc(float x) { return 1.0f / (1.0f + expf(-x)); }
 
-// SPARSE: one warp per entry of the per-image list the prediction convs emitted (grid.y = image); otherwise one
-// warp per anchor of the dense prediction.
-template <bool SPARSE>
-__global__ void __launch_bounds__(256)
-decode_filter_kernel(const PostBuffers pb, const int raw) {
-  const int lane = threadIdx.x & 31;
-  int b, a;
-  if (SPARSE) {
-    b = blockIdx.y;
-    const int e = blockIdx.x * 8 + (threadIdx.x >> 5);
-    if (e >= min(pb.maybe_count[b], pb.cap)) return;
-    a = pb.maybe_idx[(size_t)b * pb.cap + e];
-  } else {
-    const int wg = (blockIdx.x * 256 + threadIdx.x) >> 5;
-    if (wg >= pb.B * pb.A) return;
-    b = wg / pb.A;
-    a = wg - b * pb.A;
-  }
+// one warp decodes anchor `a` of image `b`: sigmoid / exp / grid, arg-max over classes, candidate append
+__device__ __forceinline__ void decode_one(const PostBuffers& pb, const int raw, const int b, const int a,
+                                           const int lane) {
   const int warp_global = b * pb.A + a;
   const int E = 5 + pb.C;
   const float* row = pb.pred + (size_t)warp_global * E;
@@ -116,6 +101,25 @@ decode_filter_kernel(const PostBuffers pb, const int raw) {
         pb.cand_anchor[(size_t)b * pb.cap + slot] = a;
       }
     }
+  }
+}
+
+// SPARSE: the per-image lists the prediction convs emitted (grid.y = image, warps stride over the list: a fixed small
+// grid -- one CTA per 8 possible entries was 34 000 mostly empty CTAs at 32 frames); otherwise one warp per anchor of
+// the dense prediction.
+template <bool SPARSE>
+__global__ void __launch_bounds__(256)
+decode_filter_kernel(const PostBuffers pb, const int raw) {
+  const int lane = threadIdx.x & 31;
+  if (SPARSE) {
+    const int b = blockIdx.y;
+    const int n = min(pb.maybe_count[b], pb.cap);
+    for (int e = blockIdx.x * 8 + (threadIdx.x >> 5); e < n; e += gridDim.x * 8)
+      decode_one(pb, raw, b, pb.maybe_idx[(size_t)b * pb.cap + e], lane);
+  } else {
+    const int wg = (blockIdx.x * 256 + threadIdx.x) >> 5;
+    if (wg >= pb.B * pb.A) return;
+    decode_one(pb, raw, wg / pb.A, wg % pb.A, lane);
   }
 }
 
@@ -378,7 +382,7 @@ int postproc_launch(const PostBuffers& pb, int raw, cudaStream_t stream, cudaEve
   const int warps = pb.B * pb.A;
   if (evs) cudaEventRecord(evs[0], stream);
   if (pb.maybe_count != nullptr)
-    decode_filter_kernel<true><<<dim3(cdiv(pb.cap, 8), pb.B), 256, 0, stream>>>(pb, raw);
+    decode_filter_kernel<true><<<dim3(16, pb.B), 256, 0, stream>>>(pb, raw);
   else
     decode_filter_kernel<false><<<cdiv(warps, 8), 256, 0, stream>>>(pb, raw);
   if (evs) { cudaEventRecord(evs[1], stream); cudaEventRecord(evs[2], stream); }

@@ -1,7 +1,8 @@
 #!/bin/bash
-T=${1:-s40}
+T=${1:-s46}
 mkdir -p gpurun_out
-timeout 600 python -m pytest tests/test_gpu_stream_bank.py tests/test_gpu_motion.py -q -x > gpurun_out/${T}_bank.log 2>&1; echo "bank rc=$?"
-grep -E "passed|failed|FAILED|Error|assert" gpurun_out/${T}_bank.log | head -20
-timeout 600 python bench.py --quick --steps 60 --warmup 10 --dump-ops gpurun_out/${T}_ops.json > gpurun_out/${T}_q.json 2>gpurun_out/${T}.err; cut -c1-200 gpurun_out/${T}_q.json
-python tools/show_ops.py gpurun_out/${T}_ops.json | grep -E "pred|decode|total"
+timeout 900 python -m pytest tests -m gpu -q -x > gpurun_out/${T}_pytest.log 2>&1; echo "pytest rc=$?"
+grep -E "passed|failed|FAILED|Error|max err" gpurun_out/${T}_pytest.log | head -20
+timeout 300 python bench.py --quick --steps 120 --warmup 10 --dump-ops gpurun_out/${T}_ops.json > gpurun_out/${T}_q.json 2>gpurun_out/${T}.err; cut -c1-230 gpurun_out/${T}_q.json
+TCD_LANES=1 TCD_ENGINES=1 timeout 300 python bench.py --quick --batch 32 --steps 10 --warmup 3 --dump-ops gpurun_out/${T}_ops32.json > gpurun_out/${T}_q32.json 2>>gpurun_out/${T}.err; cut -c1-230 gpurun_out/${T}_q32.json
+python tools/show_ops.py gpurun_out/${T}_ops32.json | awk '$2>35 || /total/'
