@@ -352,24 +352,28 @@ def pin_rank_cpus(local, world):
     return None
 
 
-def drive_coordinator(co, frames, n_frames, n_cams=8, window=96):
+def drive_coordinator(co, frames, n_frames, n_cams=8, window=96, burst=8):
     """n_frames requests through SharedInferenceCoordinator.infer_async, at most `window` outstanding (the camera
-    threads of the reference block on their queues the same way); returns the number of detection dicts delivered."""
-    sem = threading.Semaphore(window)
+    threads of the reference block on their queues the same way).  The producer sleeps until a whole burst of results
+    has come back, so the two Python threads of a rank hand the GIL over once per batch, not once per frame.
+    Returns the number of detection dicts delivered."""
+    sem = threading.Semaphore(window // burst)
     done = threading.Event()
     state = [0, 0]
 
     def cb(dets):
         state[0] += 1
         state[1] += len(dets)
-        sem.release()
+        if state[0] % burst == 0:
+            sem.release()
         if state[0] == n_frames:
             done.set()
     nf = len(frames)
     cams = ["cam%d" % i for i in range(n_cams)]
-    for i in range(n_frames):
+    for i0 in range(0, n_frames, burst):
         sem.acquire()
-        co.infer_async(frames[i % nf], cb, cams[i % n_cams])
+        for i in range(i0, min(i0 + burst, n_frames)):
+            co.infer_async(frames[i % nf], cb, cams[i % n_cams])
     if not done.wait(timeout=300):
         raise RuntimeError("coordinator delivered %d of %d results" % (state[0], n_frames))
     return state[1]

@@ -18,11 +18,19 @@ import numpy as np
 import torch
 
 
-def make_model(seed=0, num_queries=300):
-    """Seeded, well-conditioned random RT-DETRv2-R50 (no checkpoint can be downloaded here)."""
-    from transformers import RTDetrV2Config, RTDetrV2ForObjectDetection
+def make_model(seed=0, num_queries=300, variant="r50vd"):
+    """Seeded, well-conditioned random RT-DETRv2 (no checkpoint can be downloaded here).  variant "r50vd" (BASELINE
+    configs[3]) or "r18vd" -- the variant the reference's shipped config selects (config/config.yaml:74,91):
+    BasicBlock backbone, hidden_expansion 0.5 (CSPRep conv3), three decoder layers."""
+    from transformers import RTDetrResNetConfig, RTDetrV2Config, RTDetrV2ForObjectDetection
 
-    cfg = RTDetrV2Config()
+    if variant == "r18vd":
+        bc = RTDetrResNetConfig(depths=[2, 2, 2, 2], hidden_sizes=[64, 128, 256, 512], layer_type="basic",
+                                out_features=["stage2", "stage3", "stage4"])
+        cfg = RTDetrV2Config(backbone_config=bc, encoder_in_channels=[128, 256, 512], hidden_expansion=0.5,
+                             decoder_layers=3)
+    else:
+        cfg = RTDetrV2Config()
     cfg.num_labels = 80
     cfg.anchor_image_size = None
     cfg.num_queries = num_queries
@@ -47,7 +55,7 @@ def make_model(seed=0, num_queries=300):
                 fan_in = v.shape[1] * v.shape[2] * v.shape[3]
                 v.copy_(randn(v.shape, 0.8 * (2.0 / fan_in) ** 0.5))
             elif is_bn:
-                last_of_block = ".layer.2.normalization" in k
+                last_of_block = ".layer.2.normalization" in k or (variant == "r18vd" and ".layer.1.normalization" in k)
                 if k.endswith("running_var"):
                     v.copy_(rand(v.shape, 0.8, 1.2))
                 elif k.endswith("running_mean"):

@@ -34,7 +34,7 @@ def _digest():
     h = hashlib.sha256()
     for root in (CSRC, os.path.join(HERE, "..", "include")):
         for name in sorted(os.listdir(root)):
-            if name.endswith((".cu", ".cuh", ".h")):
+            if name.endswith((".cu", ".cuh", ".h", ".c")):
                 with open(os.path.join(root, name), "rb") as f:
                     h.update(name.encode())
                     h.update(f.read())
@@ -70,9 +70,29 @@ def build(force=False, verbose=False):
     r = subprocess.run(cmd, capture_output=True, text=True)
     if r.returncode != 0:
         raise RuntimeError("link failed:\n" + r.stdout + r.stderr)
+    build_fmt()
     with open(stamp, "w") as f:
         f.write(dig)
     return OUT
+
+
+def fmt_path():
+    import sysconfig
+    return os.path.join(HERE, "_tcdfmt" + (sysconfig.get_config_var("EXT_SUFFIX") or ".so"))
+
+
+def build_fmt():
+    """The CPython helper that builds the detection dicts (csrc/tcdfmt.c; host logic, plain gcc)."""
+    import sysconfig
+    inc = sysconfig.get_paths()["include"]
+    if not os.path.exists(os.path.join(inc, "Python.h")):
+        return None   # no headers: YOLOXDetector keeps its NumPy formatter
+    out = fmt_path()
+    cmd = ["gcc", "-O2", "-fPIC", "-shared", "-ffp-contract=off", "-I", inc, os.path.join(CSRC, "tcdfmt.c"), "-o", out]
+    r = subprocess.run(cmd, capture_output=True, text=True)
+    if r.returncode != 0:
+        raise RuntimeError("gcc failed for tcdfmt.c:\n" + r.stdout + r.stderr)
+    return out
 
 
 if __name__ == "__main__":

@@ -279,18 +279,33 @@ class RTDetrEngine:
         T = P.act(x.N, x.H, x.W, 2 * h)
         P.conv(name + ".conv12", x, np.concatenate([w1, w2], 0), np.concatenate([b1, b2], 0), act=ACT_SILU, y=T)
         cur, cur_off = T, 0
-        if out is None:
-            out = P.act(x.N, x.H, x.W, h)
-        for i in range(3):
+        # hidden_expansion != 1 (0.5 in r18vd / r34vd): a 1x1 conv3 maps the h hidden channels back to the output width
+        has_c3 = (prefix + ".conv3.conv.weight") in self.sd
+        nb = 0
+        while ("%s.bottlenecks.%d.conv1.conv.weight" % (prefix, nb)) in self.sd:
+            nb += 1
+        if has_c3:
+            wc, bc = self._convbn(prefix + ".conv3")
+            mid = P.act(x.N, x.H, x.W, h)
+            if out is None:
+                out = P.act(x.N, x.H, x.W, wc.shape[0])
+        else:
+            if out is None:
+                out = P.act(x.N, x.H, x.W, h)
+            mid = out
+        for i in range(nb):
             w3, b3 = self._convbn("%s.bottlenecks.%d.conv1" % (prefix, i))
             wp, bp = self._convbn("%s.bottlenecks.%d.conv2" % (prefix, i))
             w3 = w3.copy()
             w3[:, :, 1, 1] += wp[:, :, 0, 0]
-            last = i == 2
-            dst = out if last else P.act(x.N, x.H, x.W, h)
-            P.conv("%s.rep%d" % (name, i), cur, w3, b3 + bp, k=3, act=ACT_SILU, y=dst, y_coff=out_coff if last else 0,
+            last = i == nb - 1
+            dst = mid if last else P.act(x.N, x.H, x.W, h)
+            off = out_coff if (last and not has_c3) else 0
+            P.conv("%s.rep%d" % (name, i), cur, w3, b3 + bp, k=3, act=ACT_SILU, y=dst, y_coff=off,
                    x_coff=cur_off, resid=T if last else None, r_coff=h)
-            cur, cur_off = dst, (out_coff if last else 0)
+            cur, cur_off = dst, off
+        if has_c3:
+            P.conv(name + ".conv3", mid, wc, bc, act=ACT_SILU, y=out, y_coff=out_coff)
         return out
 
     # ---- the network
@@ -332,14 +347,23 @@ class RTDetrEngine:
                 stride = 2 if (li == 0 and si > 0) else 1
                 w1, b1 = self._resnet_cb(pre + "layer.0")
                 w2, b2 = self._resnet_cb(pre + "layer.1")
-                w3, b3 = self._resnet_cb(pre + "layer.2")
-                mid, cout = w1.shape[0], w3.shape[0]
-                t1 = P.act(B, c.H, c.W, mid)
-                P.conv(nm + ".conv1", c, w1, b1, act=ACT_RELU, y=t1)
-                t2 = P.act(B, c.H // stride, c.W // stride, mid)
-                P.conv(nm + ".conv2", t1, w2, b2, k=3, stride=stride, act=ACT_RELU, y=t2)
+                basic = (pre + "layer.2.convolution.weight") not in self.sd   # r18vd / r34vd: two 3x3 convs per block
+                if basic:
+                    cout = w2.shape[0]
+                    t2 = P.act(B, c.H // stride, c.W // stride, w1.shape[0])
+                    P.conv(nm + ".conv1", c, w1, b1, k=3, stride=stride, act=ACT_RELU, y=t2)
+                    w3, b3, k3 = w2, b2, 3
+                else:
+                    w3, b3 = self._resnet_cb(pre + "layer.2")
+                    k3 = 1
+                    mid, cout = w1.shape[0], w3.shape[0]
+                    t1 = P.act(B, c.H, c.W, mid)
+                    P.conv(nm + ".conv1", c, w1, b1, act=ACT_RELU, y=t1)
+                    t2 = P.act(B, c.H // stride, c.W // stride, mid)
+                    P.conv(nm + ".conv2", t1, w2, b2, k=3, stride=stride, act=ACT_RELU, y=t2)
                 sc = c
-                if li == 0:
+                has_sc = (pre + "shortcut.1.convolution.weight") in self.sd or (pre + "shortcut.convolution.weight") in self.sd
+                if has_sc:
                     src = c
                     if stride == 2:
                         src = P.act(B, c.H // 2, c.W // 2, c.C)
@@ -350,7 +374,7 @@ class RTDetrEngine:
                     sc = P.act(B, src.H, src.W, cout)
                     P.conv(nm + ".shortcut", src, ws, bs, y=sc)
                 out = P.act(B, t2.H, t2.W, cout)
-                P.conv(nm + ".conv3", t2, w3, b3, act=ACT_RELU, y=out, resid=sc, resid_pre=1)
+                P.conv(nm + (".conv2" if basic else ".conv3"), t2, w3, b3, k=k3, act=ACT_RELU, y=out, resid=sc, resid_pre=1)
                 c = out
             if si >= 1:
                 feats.append(c)
@@ -358,7 +382,10 @@ class RTDetrEngine:
         assert len(feats) == 3, "expected three backbone feature levels"
 
         # -- encoder input projections (1x1 + BN) written straight into the CCFM concat buffers
-        D = 256
+        D = int(self._g("model.encoder_input_proj.0.0.weight").shape[0])
+        if D != 256:
+            raise ValueError("RT-DETR hidden_dim %d is not supported (r18vd / r34vd / r50vd use 256; the attention "
+                             "kernels are built for 8 heads of 32)" % D)
         H8, W8, H16, W16, H32, W32 = H // 8, W // 8, H // 16, W // 16, H // 32, W // 32
         catB = P.act(B, H8, W8, 2 * D)     # [up(L1) | proj0]
         catA = P.act(B, H16, W16, 2 * D)   # [up(L2) | proj1]

@@ -20,6 +20,11 @@ import numpy as np
 from .coco_constants import COCO_CLASSES, MAMMAL_CLASS_IDS, WILDLIFE_CLASSES
 
 logger = logging.getLogger(__name__)
+try:   # C builder of the detection dicts (csrc/tcdfmt.c); the NumPy formatter below is the same arithmetic
+    from . import _tcdfmt
+except ImportError:   # not built (no Python headers at build time)
+    _tcdfmt = None
+_COCO_TUPLE = tuple(COCO_CLASSES)
 _WILDLIFE_LUT = np.zeros(256, bool)
 _WILDLIFE_LUT[sorted(WILDLIFE_CLASSES)] = True
 
@@ -232,7 +237,10 @@ class YOLOXDetector:
         Python scalars in one comprehension."""
         if output is None or len(output) == 0:
             return []
-        out = np.asarray(output, np.float32)
+        out = np.ascontiguousarray(output, np.float32)
+        if _tcdfmt is not None and out.ndim == 2 and out.shape[1] == 7:
+            return _tcdfmt.format_rows(out, float(orig_h), float(orig_w), int(self.input_size[0]), int(self.input_size[1]),
+                                       bool(self.wildlife_only), _COCO_TUPLE)
         cls = out[:, 6].astype(np.int64)
         if self.wildlife_only:
             keep = _WILDLIFE_LUT[np.clip(cls, 0, 255)]

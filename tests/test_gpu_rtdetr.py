@@ -148,3 +148,32 @@ def test_detector_shim_end_to_end(run):
     only = det.detect(frames[0])
     assert all(d["class_id"] in (0, 14, 15, 16, 21) for d in only)
     assert det.detect_batch([]) == []
+
+
+def test_r18vd_variant_loads_and_matches_oracle():
+    """The variant the reference's shipped config selects (config/config.yaml:74,91): BasicBlock backbone, CSPRep
+    layers with hidden_expansion 0.5 (conv3), three decoder layers.  ADVICE r1: these weights used to fail with a
+    KeyError on layer.2."""
+    import torch
+    from oracle import rtdetr as oracle
+    from telescope_cam_detection_b200.rtdetr_engine import RTDetrEngine
+
+    model = oracle.make_model(0, variant="r18vd")
+    torch.manual_seed(2)
+    x = torch.rand(1, 3, 640, 640).to(torch.bfloat16).float()
+    ref = oracle.forward(model, x)
+    eng = RTDetrEngine(oracle.state_dict_numpy(model), batch=1, keep_taps=True)
+    try:
+        eng.set_input(x.numpy())
+        eng.set_orig_sizes([[1920, 1080]])
+        eng.run(graph=True)
+        for i in range(3):
+            assert _rms_rel(eng.read_tap("backbone.%d" % (i + 1)), ref["backbone"][i].permute(0, 2, 3, 1).numpy()) <= 0.015
+        for i in range(3):
+            assert _rms_rel(eng.read_tap("encoder.%d" % i), ref["encoder"][i].permute(0, 2, 3, 1).numpy()) <= 0.02
+        logits, boxes, topk = eng.raw_outputs()
+        common = np.intersect1d(topk[0], ref["topk"].numpy()[0])
+        assert len(common) >= 0.85 * 300, "only %d of the oracle's queries selected" % len(common)
+        assert ref["dec_hidden"].shape[1] == 3
+    finally:
+        eng.close()
