@@ -828,8 +828,8 @@ def run_streams(args):
     # one filter table per camera: the STRUCTURE of the shipped config (per-class confidence overrides, per-class area
     # limits, global minimum area, max_det) with thresholds scaled to the synthetic weights' score range -- the shipped
     # values (0.70-0.95) would drop every random-weight detection and leave the motion filter without work
-    conf = {k: round(0.45 + 0.3 * (v - 0.70), 3) for k, v in SHIPPED_CONF.items()}
-    tids = [det.register_class_filter(0.40, conf, 300, SHIPPED_SIZE, 8) for _ in range(S)]
+    conf = {k: round(0.28 + 0.2 * (v - 0.70), 3) for k, v in SHIPPED_CONF.items()}   # 0.28 .. 0.33 (weights' scores: 0.25-0.4)
+    tids = [det.register_class_filter(0.27, conf, 300, SHIPPED_SIZE, 8) for _ in range(S)]
     bank = StreamBank(S, (FRAME_H, FRAME_W), device=local)
     pool = torch.empty((S, T, FRAME_H, FRAME_W, 3), dtype=torch.uint8, pin_memory=True)
     for s in range(S):

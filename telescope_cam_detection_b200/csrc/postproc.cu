@@ -382,7 +382,7 @@ int postproc_launch(const PostBuffers& pb, int raw, cudaStream_t stream, cudaEve
   const int warps = pb.B * pb.A;
   if (evs) cudaEventRecord(evs[0], stream);
   if (pb.maybe_count != nullptr)
-    decode_filter_kernel<true><<<dim3(16, pb.B), 256, 0, stream>>>(pb, raw);
+    decode_filter_kernel<true><<<dim3(64, pb.B), 256, 0, stream>>>(pb, raw);
   else
     decode_filter_kernel<false><<<cdiv(warps, 8), 256, 0, stream>>>(pb, raw);
   if (evs) { cudaEventRecord(evs[1], stream); cudaEventRecord(evs[2], stream); }
