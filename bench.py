@@ -836,12 +836,14 @@ def run_streams(args):
         for t, f in enumerate(synth_stream(10_000 * rank + 97 * s, T)):
             pool[s, t] = torch.from_numpy(f)
     hp = pool.numpy()
-    dev_frames = bank.device_frames()
     stats = {"gated_out": 0, "detected": 0, "dets_in": 0, "dets_kept": 0, "gate_ms": 0.0, "motion_ms": 0.0, "rounds": 0}
 
-    def step(i):
-        bank.upload([hp[s, i % T] for s in range(S)])
+    def step(i, first=False):
+        if first:
+            bank.upload([hp[s, i % T] for s in range(S)])
         moving = bank.has_motion()
+        bank.upload([hp[s, (i + 1) % T] for s in range(S)])      # the next step's frames travel under this step's work
+        dev_frames = bank.device_frames()
         live = [s for s in range(S) if moving[s]]
         dets = [None] * S
         if live:
@@ -859,7 +861,7 @@ def run_streams(args):
         stats["rounds"] += km["motion_rounds"]
 
     for i in range(W):
-        step(i)
+        step(i, first=(i == 0))
     for k in stats:
         stats[k] = 0
     sampler = ClockSampler(local) if rank == 0 else None

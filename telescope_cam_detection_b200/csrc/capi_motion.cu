@@ -319,10 +319,14 @@ struct tcd_stream_bank {
   float var_threshold = 16.f;
   size_t npix = 0;
   cudaStream_t stream = nullptr;
+  cudaStream_t copy = nullptr;       // uploads: the next step's frames arrive while this step is being filtered
+  cudaEvent_t ev_up[2] = {nullptr, nullptr};
   std::vector<Mog2State> st;
   std::vector<long long> nframes;
-  std::vector<char> have_prev, has_frame;
-  uint8_t* frames = nullptr;         // [n][h*w*3] this step's frames
+  std::vector<char> have_prev, has_frame, has_frame_buf[2];
+  uint8_t* frames = nullptr;         // current step's frames: one of frame_buf[2], each [n][h*w*3]
+  uint8_t* frame_buf[2] = {nullptr, nullptr};
+  int cur = 0, pending = -1;         // buffer in use / buffer an upload has filled but gate() has not adopted yet
   uint8_t* fg = nullptr;             // [n][kMogMaxRepeats][npix]
   uint8_t* prev = nullptr;           // [n][npix]
   unsigned int* gate_counts = nullptr;   // [n]
@@ -358,7 +362,10 @@ tcd_status tcd_stream_bank_create(int32_t n_streams, int32_t h, int32_t w, int32
   b->has_frame.assign(n_streams, 0);
   const size_t np = b->npix;
   TCD_CUDA_OK(cudaStreamCreateWithFlags(&b->stream, cudaStreamNonBlocking));
+  TCD_CUDA_OK(cudaStreamCreateWithFlags(&b->copy, cudaStreamNonBlocking));
   for (auto& e : b->ev) TCD_CUDA_OK(cudaEventCreate(&e));
+  for (auto& e : b->ev_up) TCD_CUDA_OK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+  for (int k = 0; k < 2; ++k) b->has_frame_buf[k].assign(n_streams, 0);
   for (int i = 0; i < n_streams; ++i) {
     TCD_CUDA_OK(cudaMalloc((void**)&b->st[i].weight, np * kMogModes * 4));
     TCD_CUDA_OK(cudaMalloc((void**)&b->st[i].var, np * kMogModes * 4));
@@ -366,7 +373,8 @@ tcd_status tcd_stream_bank_create(int32_t n_streams, int32_t h, int32_t w, int32
     TCD_CUDA_OK(cudaMalloc((void**)&b->st[i].nmodes, np));
     TCD_CUDA_OK(cudaMemset(b->st[i].nmodes, 0, np));
   }
-  TCD_CUDA_OK(cudaMalloc((void**)&b->frames, np * 3 * n_streams));
+  for (int k = 0; k < 2; ++k) TCD_CUDA_OK(cudaMalloc((void**)&b->frame_buf[k], np * 3 * n_streams));
+  b->frames = b->frame_buf[0];
   TCD_CUDA_OK(cudaMalloc((void**)&b->fg, np * kMogMaxRepeats * n_streams));
   TCD_CUDA_OK(cudaMemset(b->fg, 0, np * kMogMaxRepeats * n_streams));
   TCD_CUDA_OK(cudaMalloc((void**)&b->prev, np * n_streams));
@@ -387,11 +395,14 @@ void tcd_stream_bank_destroy(tcd_stream_bank* b) {
   for (auto& s : b->st) {
     cudaFree(s.weight); cudaFree(s.var); cudaFree(s.mean); cudaFree(s.nmodes);
   }
-  void* ptrs[] = {b->frames, b->fg, b->prev, b->gate_counts, b->roi_counts, b->desc_dev};
+  cudaStreamSynchronize(b->copy);
+  void* ptrs[] = {b->frame_buf[0], b->frame_buf[1], b->fg, b->prev, b->gate_counts, b->roi_counts, b->desc_dev};
   for (void* p : ptrs) if (p) cudaFree(p);
   if (b->desc_host) cudaFreeHost(b->desc_host);
   if (b->counts_pinned) cudaFreeHost(b->counts_pinned);
   for (auto& e : b->ev) if (e) cudaEventDestroy(e);
+  for (auto& e : b->ev_up) if (e) cudaEventDestroy(e);
+  cudaStreamDestroy(b->copy);
   cudaStreamDestroy(b->stream);
   delete b;
 }
@@ -407,22 +418,27 @@ tcd_status tcd_stream_bank_reset(tcd_stream_bank* b, int32_t stream, int32_t wha
   return TCD_OK;
 }
 
-/* frames_host[s]: this step's frame of stream s (HWC u8 BGR, row stride strides[s] or tight when strides is NULL),
- * NULL = the stream has no frame this step.  One pitched H2D copy per frame; asynchronous. */
+/* frames_host[s]: the NEXT step's frame of stream s (HWC u8 BGR, row stride strides[s] or tight when strides is
+ * NULL), NULL = the stream has no frame in that step.  One copy per frame on the bank's copy stream into the buffer
+ * that is not in use: asynchronous, and it may be issued while the current step is still being filtered (the two
+ * frame buffers alternate; tcd_stream_bank_gate adopts the uploaded one). */
 tcd_status tcd_stream_bank_upload(tcd_stream_bank* b, const uint8_t* const* frames_host, const int64_t* strides) {
   TCD_REQUIRE(b && frames_host, "stream_bank_upload: null argument");
+  TCD_REQUIRE(b->pending < 0, "stream_bank_upload: the previous upload has not been adopted by a gate call yet");
   TCD_CUDA_OK(cudaSetDevice(b->device));
   const size_t tight = (size_t)b->w * 3;
-  TCD_CUDA_OK(cudaEventRecord(b->ev[0], b->stream));
+  const int k = b->cur ^ 1;
   for (int s = 0; s < b->n; ++s) {
-    b->has_frame[s] = frames_host[s] != nullptr;
+    b->has_frame_buf[k][s] = frames_host[s] != nullptr;
     if (!frames_host[s]) continue;
     const size_t st = strides && strides[s] > 0 ? (size_t)strides[s] : tight;
-    uint8_t* dst = b->frames + (size_t)s * b->npix * 3;
-    if (st == tight) TCD_CUDA_OK(cudaMemcpyAsync(dst, frames_host[s], tight * b->h, cudaMemcpyHostToDevice, b->stream));
-    else TCD_CUDA_OK(cudaMemcpy2DAsync(dst, tight, frames_host[s], st, tight, (size_t)b->h, cudaMemcpyHostToDevice, b->stream));
+    uint8_t* dst = b->frame_buf[k] + (size_t)s * b->npix * 3;
+    if (st == tight) TCD_CUDA_OK(cudaMemcpyAsync(dst, frames_host[s], tight * b->h, cudaMemcpyHostToDevice, b->copy));
+    else TCD_CUDA_OK(cudaMemcpy2DAsync(dst, tight, frames_host[s], st, tight, (size_t)b->h, cudaMemcpyHostToDevice, b->copy));
     g_h2d_bytes.fetch_add((uint64_t)tight * b->h, std::memory_order_relaxed);
   }
+  TCD_CUDA_OK(cudaEventRecord(b->ev_up[k], b->copy));
+  b->pending = k;
   return TCD_OK;
 }
 
@@ -446,6 +462,13 @@ static BankStream* bank_next_desc(tcd_stream_bank* b, BankStream** host) {
 tcd_status tcd_stream_bank_gate(tcd_stream_bank* b, int32_t threshold, int32_t* changed_host) {
   TCD_REQUIRE(b && changed_host, "stream_bank_gate: null argument");
   TCD_CUDA_OK(cudaSetDevice(b->device));
+  if (b->pending >= 0) {   // adopt the uploaded frames: they become "this step" for the gate, the detector and the model
+    b->cur = b->pending;
+    b->pending = -1;
+    b->frames = b->frame_buf[b->cur];
+    b->has_frame = b->has_frame_buf[b->cur];
+    TCD_CUDA_OK(cudaStreamWaitEvent(b->stream, b->ev_up[b->cur], 0));
+  }
   BankStream* host = nullptr;
   BankStream* dev = bank_next_desc(b, &host);
   for (int s = 0; s < b->n; ++s) {

@@ -45,16 +45,22 @@ class StreamBank:
 
     # ------------------------------------------------------------------ frames
     def upload(self, frames: List[Optional[np.ndarray]]) -> None:
-        self._have = [f is not None for f in frames]
+        """Start the (asynchronous) upload of the NEXT step's frames.  has_motion() adopts them; upload() for step
+        i+1 may be called as soon as has_motion() of step i has returned, i.e. under the detector and the motion
+        filter of step i."""
         self.engine.upload(frames)
 
     def device_frames(self):
-        """One CUDA uint8 tensor (h, w, 3) per stream viewing the bank's copy of this step's frame."""
+        """One CUDA uint8 tensor (h, w, 3) per stream viewing the bank's copy of the CURRENT step's frame (the one the
+        last has_motion() adopted; the bank alternates between two buffers so that the next upload can overlap)."""
         import torch
         if self._tensors is None:
-            self._tensors = [torch.as_tensor(DeviceView(self.engine.frame_ptr(s), (self.h, self.w, 3), "|u1"),
-                                             device="cuda") for s in range(self.n)]
-        return self._tensors
+            self._tensors = {}
+        key = self.engine.frame_ptr(0)
+        if key not in self._tensors:
+            self._tensors[key] = [torch.as_tensor(DeviceView(self.engine.frame_ptr(s), (self.h, self.w, 3), "|u1"),
+                                                  device="cuda") for s in range(self.n)]
+        return self._tensors[key]
 
     # ------------------------------------------------------------------ EmptyFrameFilter.has_motion, all streams
     def has_motion(self) -> List[Optional[bool]]:
