@@ -315,6 +315,35 @@ def rtdetr_side(local, batch, peaks):
                     "GB/s": msda_bytes / (msda_ms * 1e-3) / 1e9},
            "slowest_ops": [{"name": o["name"], "ms": round(o["ms"], 4)} for o in top]}
     eng.close()
+    # the same model through the reference's class: RTDETRDetector.detect_batch on 1080p HOST frames -- upload,
+    # tcd_pil_resize (PIL-exact antialiased resize, BGR->RGB, /255), the program, D2H of (labels, boxes, scores),
+    # threshold + wildlife filter + dict formatting (src/rtdetr_detector.py:307-403)
+    try:
+        from telescope_cam_detection_b200.rtdetr_detector import RTDETRDetector
+        det = RTDETRDetector(device="cuda:%d" % local, conf_threshold=0.25, input_size=(640, 640), wildlife_only=True,
+                             state_dict=oracle_rtdetr.state_dict_numpy(model), max_batch=batch)
+        if not det.load_model():
+            raise RuntimeError("RTDETRDetector.load_model() failed")
+        host = torch.empty((batch, FRAME_H, FRAME_W, 3), dtype=torch.uint8, pin_memory=True)
+        for i in range(batch):
+            host[i] = torch.from_numpy(synth_frame(500 + i))
+        frames = [host.numpy()[i] for i in range(batch)]
+        for _ in range(2):
+            out = det.detect_batch(frames)
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        n_it = 5
+        for _ in range(n_it):
+            out = det.detect_batch(frames)
+        dt = (time.perf_counter() - t0) / n_it
+        res["through_class"] = {"frames_per_s": batch / dt, "ms_per_batch": 1e3 * dt,
+                                "h2d_bytes_per_batch": batch * FRAME_H * FRAME_W * 3,
+                                "detections": sum(len(o) for o in out),
+                                "path": "RTDETRDetector.detect_batch(%d host 1080p frames) -> List[List[dict]] (wall clock)" % batch}
+        for e in det._engines.values():
+            e.close()
+    except Exception as e:  # noqa: BLE001
+        res["through_class"] = {"error": repr(e)}
     return res
 
 

@@ -332,6 +332,10 @@ int conv_plan_build(const ConvDesc& d, ConvPlan* plan) {
   {
     const int thr = env_int("TCD_CONV_SHARE_MAX_TILES", 20, 0);  // measured: 20 (the stem only) +1.8 %, 8 (dark2 too) -1.4 %
     if (thr > 0 && share > 0 && (long)m_tiles >= (long)thr * n_sm) share = 0;
+    // long-K layers are paced by operand delivery with the two ring stages half an SM leaves them: TCD_CONV_WHOLE_K = k
+    // gives every layer with Cin * taps >= k a whole SM (deep ring) instead (0 = off)
+    const int wk = env_int("TCD_CONV_WHOLE_K", 0, 0);
+    if (wk > 0 && share > 0 && d.cin * d.k * d.k >= wk) share = 0;
   }
   const int bn_cap = share >= 3 ? 64 : 128;
   int BN;
@@ -445,7 +449,11 @@ int conv_plan_build(const ConvDesc& d, ConvPlan* plan) {
     if (a.halo) {
       a.a_stage_bytes = (((a.TW + 2) * (a.TH + 2) * a.ck * 2) + 1023) & ~1023;
       const long want = (long)a.kchunks * tiles_per_cta;
-      a.a_stages = (int)(want < 3 ? want : 3);
+      // small halo boxes (the 16-channel stem: 180 rows of 32 bytes) are paced by the TMA round trip, not by bytes:
+      // per-tile stamps showed one box per ~3 400 cycles with three in flight (TCD_CONV_ASTAGES, default 6 / 3)
+      const int a_cap = a.a_stage_bytes <= 8192 ? env_int("TCD_CONV_ASTAGES", 6) : 3;
+      a.a_stages = (int)(want < a_cap ? want : a_cap);
+      if (a.a_stages > kConvMaxAStages) a.a_stages = kConvMaxAStages;
       // a weight ring of >= 4 stages matters more than a third halo buffer
       while (a.a_stages > 2 && (budget - staging - a.a_stages * a.a_stage_bytes) / stage_bytes < 4) --a.a_stages;
       halo_bytes = a.a_stages * a.a_stage_bytes;

@@ -32,7 +32,7 @@ namespace tcd {
 constexpr int kConvMaxStages = 8;
 constexpr int kConvThreads = 192;   // warp 0 TMA producer, warp 1 MMA issuer, warps 2..5 epilogue
 constexpr int kConvEpiWarps = 4;
-constexpr int kConvMaxAStages = 4;
+constexpr int kConvMaxAStages = 8;
 constexpr int kConvMaxBias = 2048;  // every layer's bias is staged in shared memory (planner refuses wider layers)
 
 struct ConvMaps {
