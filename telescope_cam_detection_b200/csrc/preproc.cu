@@ -27,6 +27,11 @@ struct PreArgs {
   int smem_row_bytes, smem_rows;  // 0 -> direct global loads
 };
 
+// u8 -> f32 without the conversion unit: I2F issues at 16 lanes/clk/SM (the XU pipe) and the kernel converts 12 bytes
+// per output pixel (39 M per step of 8 frames = 8 us of that pipe alone); 2^23 + b is exact in fp32, so one LOP3 and
+// one FADD give the same value at full rate
+__device__ __forceinline__ float u8f(uint8_t b) { return __uint_as_float(0x4B000000u | (unsigned)b) - 8388608.0f; }
+
 __device__ __forceinline__ void tap(float scale, int d, int in, int* i0, int* i1, float* l1) {
   float s = scale * ((float)d + 0.5f) - 0.5f;
   s = s < 0.f ? 0.f : s;
@@ -73,19 +78,43 @@ preproc_kernel(const PreFrame* __restrict__ frames, const PreArgs a, void* __res
       byte0 = b_lo - mis;
       row_bytes = (int)(((b_hi - byte0) + 15) & ~15LL);
       const int vec_per_row = row_bytes >> 4;
-      for (int i = threadIdx.x; i < nrows * vec_per_row; i += kPreThreads) {
-        const int r = i / vec_per_row, v = i - r * vec_per_row;
-        const uint4* src = reinterpret_cast<const uint4*>(f.ptr + (long long)(in_y0 + r * f.row_step) * f.stride +
-                                                          byte0) + v;
-        uint4 q;
-        asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
-                     : "=r"(q.x), "=r"(q.y), "=r"(q.z), "=r"(q.w)
-                     : "l"(src));
-        *reinterpret_cast<uint4*>(tile + (size_t)r * a.smem_row_bytes + (v << 4)) = q;
+      // cp.async: every 16-byte piece of the tile's source window is requested before any of them is waited for
+      // (4.5 per thread at the 3:1 letterbox) and lands in shared memory without passing through registers -- the
+      // load-then-store loop had ONE request in flight per thread and the kernel sat at 0.30 of the HBM rate
+      const uint32_t tile_s = (uint32_t)__cvta_generic_to_shared(tile);
+      // a warp per source row, lanes along the row: no divisions in the address math
+      for (int r = threadIdx.x >> 5; r < nrows; r += kPreThreads / 32) {
+        const uint8_t* src = f.ptr + (long long)(in_y0 + r * f.row_step) * f.stride + byte0;
+        const uint32_t dst = tile_s + (uint32_t)(r * a.smem_row_bytes);
+        for (int v = threadIdx.x & 31; v < vec_per_row; v += 32)
+          asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst + (uint32_t)(v << 4)), "l"(src + (v << 4))
+                       : "memory");
       }
+      asm volatile("cp.async.commit_group;" ::: "memory");
+      asm volatile("cp.async.wait_group 0;" ::: "memory");
     }
   }
   __syncthreads();
+
+  if (!has_content && a.layout == 1) {
+    // a tile of letterbox padding only (44 % of the tiles of a 1080p frame at 640x640): constant Focus pixels
+    const float pv[3] = {(a.pad_value * a.scale - a.mean[0]) * a.inv_std[0], (a.pad_value * a.scale - a.mean[1]) * a.inv_std[1],
+                         (a.pad_value * a.scale - a.mean[2]) * a.inv_std[2]};
+    uint4 lo, hi;
+    lo.x = pack_bf16x2(pv[0], pv[1]); lo.y = pack_bf16x2(pv[2], pv[0]); lo.z = pack_bf16x2(pv[1], pv[2]);
+    lo.w = pack_bf16x2(pv[0], pv[1]); hi.x = pack_bf16x2(pv[2], pv[0]); hi.y = pack_bf16x2(pv[1], pv[2]);
+    hi.z = 0u; hi.w = 0u;
+    for (int qi = threadIdx.x; qi < (kPreTileW / 2) * (kPreTileH / 2); qi += kPreThreads) {
+      const int qy = qi / (kPreTileW / 2), qx = qi - qy * (kPreTileW / 2);
+      const int ox0 = ox_a + 2 * qx, oy0 = oy_a + 2 * qy;
+      if (ox0 >= a.out_w || oy0 >= a.out_h) continue;
+      const size_t pix = ((size_t)blockIdx.z * (a.out_h / 2) + (oy0 >> 1)) * (a.out_w / 2) + (ox0 >> 1);
+      uint4* dst = reinterpret_cast<uint4*>(out) + pix * 2;
+      dst[0] = lo;
+      dst[1] = hi;
+    }
+    return;
+  }
 
   // 64 x 8 quads per tile, 2 per thread
   const int qw = kPreTileW / 2;
@@ -94,13 +123,20 @@ preproc_kernel(const PreFrame* __restrict__ frames, const PreArgs a, void* __res
     const int ox0 = ox_a + 2 * qx, oy0 = oy_a + 2 * qy;
     if (ox0 >= a.out_w || oy0 >= a.out_h) continue;
     float v[2][2][3];  // [dy][dx][c]
+    // taps of the two columns and the two rows of the quad, once each (they were recomputed per pixel)
+    int xa[2], xb[2], ya[2], yb[2];
+    float lxs[2], lys[2];
+#pragma unroll
+    for (int d = 0; d < 2; ++d) {
+      tap(f.scale_x, ox0 + d, f.w, &xa[d], &xb[d], &lxs[d]);
+      tap(f.scale_y, oy0 + d, f.h, &ya[d], &yb[d], &lys[d]);
+      if (f.row_step > 1) yb[d] = ya[d];  // ly == 0 exactly: the second tap is the first one again, times 0
+    }
 #pragma unroll
     for (int dy = 0; dy < 2; ++dy) {
       const int oy = oy0 + dy;
-      int y0, y1;
-      float ly;
-      tap(f.scale_y, oy, f.h, &y0, &y1, &ly);
-      if (f.row_step > 1) y1 = y0;  // ly == 0 exactly: the second tap is the first one again, times 0
+      const int y0 = ya[dy], y1 = yb[dy];
+      const float ly = lys[dy];
 #pragma unroll
       for (int dx = 0; dx < 2; ++dx) {
         const int ox = ox0 + dx;
@@ -109,9 +145,8 @@ preproc_kernel(const PreFrame* __restrict__ frames, const PreArgs a, void* __res
           for (int c = 0; c < 3; ++c) v[dy][dx][c] = a.pad_value;
           continue;
         }
-        int x0, x1;
-        float lx;
-        tap(f.scale_x, ox, f.w, &x0, &x1, &lx);
+        const int x0 = xa[dx], x1 = xb[dx];
+        const float lx = lxs[dx];
         const float hx = 1.f - lx, hy = 1.f - ly;
         const uint8_t *p00, *p01, *p10, *p11;
         if (staged) {
@@ -125,12 +160,26 @@ preproc_kernel(const PreFrame* __restrict__ frames, const PreArgs a, void* __res
           const uint8_t* r1 = f.ptr + (long long)y1 * f.stride;
           p00 = r0 + x0 * 3; p01 = r0 + x1 * 3; p10 = r1 + x0 * 3; p11 = r1 + x1 * 3;
         }
+        // A weight that is exactly 0 (integer resize ratios: 1920 -> 640 is 3:1 on x in both modes, 1080 -> 360 on y
+        // in letterbox) drops its taps: h*p + 0*q == p*h bit for bit, so the short forms below ARE the bilinear
+        // formula, with a quarter / half of the loads, conversions and FMAs
+        if (lx == 0.f && ly == 0.f) {
 #pragma unroll
-        for (int c = 0; c < 3; ++c) {
-          const int ci = a.swap_rb ? 2 - c : c;
-          const float top = hx * (float)p00[ci] + lx * (float)p01[ci];
-          const float bot = hx * (float)p10[ci] + lx * (float)p11[ci];
-          v[dy][dx][c] = hy * top + ly * bot;
+          for (int c = 0; c < 3; ++c) v[dy][dx][c] = u8f(p00[a.swap_rb ? 2 - c : c]);
+        } else if (lx == 0.f) {
+#pragma unroll
+          for (int c = 0; c < 3; ++c) {
+            const int ci = a.swap_rb ? 2 - c : c;
+            v[dy][dx][c] = hy * u8f(p00[ci]) + ly * u8f(p10[ci]);
+          }
+        } else {
+#pragma unroll
+          for (int c = 0; c < 3; ++c) {
+            const int ci = a.swap_rb ? 2 - c : c;
+            const float top = hx * u8f(p00[ci]) + lx * u8f(p01[ci]);
+            const float bot = hx * u8f(p10[ci]) + lx * u8f(p11[ci]);
+            v[dy][dx][c] = hy * top + ly * bot;
+          }
         }
       }
     }

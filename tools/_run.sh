@@ -1,5 +1,8 @@
 #!/bin/bash
-T=${1:-s52}
+T=${1:-s57}
 mkdir -p gpurun_out
-for i in 1 2 3; do timeout 300 python bench.py --quick --steps 20 --warmup 5 2>>gpurun_out/${T}.err | cut -c1-110; done
-timeout 900 python bench.py --steps 20 --warmup 5 --no-aux > gpurun_out/${T}_bench20.json 2>> gpurun_out/${T}.err; python tools/show_bench.py gpurun_out/${T}_bench20.json | head -6
+timeout 600 python -m pytest tests/test_gpu_yolox.py tests/test_gpu_bench_config.py tests/test_gpu_layers.py -q -x > gpurun_out/${T}_py.log 2>&1; echo "rc=$?"; tail -3 gpurun_out/${T}_py.log
+timeout 300 python bench.py --quick --steps 60 --warmup 10 --dump-ops gpurun_out/${T}_ops.json > gpurun_out/${T}_q.json 2>gpurun_out/${T}.err; cut -c1-120 gpurun_out/${T}_q.json
+python tools/show_ops.py gpurun_out/${T}_ops.json | grep -E "preproc|total"
+timeout 300 python bench.py --quick --pre stretch --steps 60 --warmup 10 --dump-ops gpurun_out/${T}_ops_s.json > gpurun_out/${T}_qs.json 2>>gpurun_out/${T}.err; cut -c1-120 gpurun_out/${T}_qs.json
+python tools/show_ops.py gpurun_out/${T}_ops_s.json | grep -E "preproc|total"
