@@ -439,10 +439,13 @@ int conv_plan_build(const ConvDesc& d, ConvPlan* plan) {
   const int share_div = share ? share : 2;
   bool two_per_sm = (a.total_tiles >= 2 * n_sm || share) && a.tmem_cols <= 512 / share_div;
   const int ctas_per_sm_max = share ? 1 : 2;
+  const int bias_bytes = (d.cout_pad * 4 + 127) & ~127;
   int stages = 0, halo_bytes = 0;
   long its_per_cta = 0;
   for (int attempt = 0; attempt < 2; ++attempt) {
-    const int budget = (two_per_sm ? g_smem_kb / share_div : g_smem_kb) * 1024 - 6656;  // static smem (barriers + 8 KiB bias) and the 1 KiB the SM reserves per CTA: two CTAs must fit 228 KiB
+    // static smem (barriers, < 0.5 KiB), the alignment slack and the 1 KiB the SM reserves per CTA -- two CTAs must fit
+    // 228 KiB -- and the layer's bias behind the staging area
+    const int budget = (two_per_sm ? g_smem_kb / share_div : g_smem_kb) * 1024 - 2560 - bias_bytes;
     const long tiles_per_cta = cdiv(a.total_tiles, n_sm * (two_per_sm ? ctas_per_sm_max : 1));
     its_per_cta = (long)its_per_tile * tiles_per_cta;
     halo_bytes = 0;
@@ -477,11 +480,16 @@ int conv_plan_build(const ConvDesc& d, ConvPlan* plan) {
   a.staging_off = a.a_ring_off + halo_bytes;
   TCD_REQUIRE(d.cout_pad <= kConvMaxBias, "conv: cout_pad %d exceeds the %d staged bias entries", d.cout_pad, kConvMaxBias);
   a.bias_n = d.cout_pad;
-  plan->smem_bytes = stages * stage_bytes + halo_bytes + staging + 1024;
+  a.bias_off = (a.staging_off + staging + 15) & ~15;
+  plan->smem_bytes = a.bias_off + bias_bytes + 1024;
   const int ctas = n_sm * (two_per_sm ? ctas_per_sm_max : 1);
   plan->grid = dim3((unsigned)(a.total_tiles < ctas ? a.total_tiles : ctas), 1, 1);
   plan->flops = 2.0 * d.N * a.Ho * a.Wo * (double)d.cout * d.cin * a.taps;
 
+  if (env_int("TCD_CONV_PLAN_DUMP", 0))
+    fprintf(stderr, "convplan N%d %dx%d cin%d cout%d k%d s%d f32:%d | halo%d BN%d group%d stages%d(%dB) a_stages%d(%dB) tps%d bres%d "
+            "staging%d smem%d grid%u share%d\n", d.N, d.H, d.W, d.cin, d.cout, d.k, d.stride, mode, a.halo, BN, a.group, stages,
+            stage_bytes, a.a_stages, a.a_stage_bytes, a.tps, a.b_resident, staging, plan->smem_bytes, plan->grid.x, share);
   // ---- tensor maps
   const int inner = a.ck * 2;
   const size_t es = 2;

@@ -53,6 +53,7 @@ struct ConvArgs {
   int n_tiles_n, total_tiles;   // persistent tile loop: tile t -> (m = t / n_tiles_n, n = t % n_tiles_n)
   int acc_stride;               // TMEM columns between the two accumulator buffers
   int staging_off;              // byte offset of the epilogue staging area inside dynamic smem
+  int bias_off;                 // byte offset of the staged bias (bias_n floats) inside dynamic smem
   int pdl;                      // launched with programmatic stream serialization
   // halo mode (3x3 stride 1): ONE (TH+2)x(TW+2) input box per k-chunk serves all nine taps through
   // row-shifted UMMA descriptors (the swizzle is a function of the absolute shared-memory address for
@@ -324,11 +325,13 @@ conv_umma_kernel(const __grid_constant__ ConvMaps maps, const __grid_constant__ 
   __shared__ uint64_t tmem_empty_bar[2];
   __shared__ uint64_t a_full_bar[kConvMaxAStages];
   __shared__ uint64_t a_empty_bar[kConvMaxAStages];
-  __shared__ __align__(16) float s_bias[kConvMaxBias];
   __shared__ uint32_t tmem_base_s;
 
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
                                              ~(uintptr_t)1023);
+  // the layer's bias lives behind the staging area, sized by the layer (a fixed 8 KiB array cost the prediction convs
+  // their second ring stage)
+  float* s_bias = reinterpret_cast<float*>(smem + p.bias_off);
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
   const int a_bytes = HALO ? 0 : 128 * p.ck * 2;
