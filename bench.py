@@ -274,6 +274,62 @@ def aux_kernels(local, dev_pool, peaks):
     return out
 
 
+def ingest_side(local, n_frames=240):
+    """Row N1: raw bgr24 1080p frames from a decoder pipe to device frames.  Ours: RTSPStreamCaptureGPU over the frame
+    ring (read() into pinned slots, one async upload, no clones).  Beside it the reference's per-frame chain restated
+    (stream_capture_gpu_ffmpeg.py:253-283: stdout.read -> frombuffer -> from_numpy().to(device) -> two clones) on the
+    same writer.  The writer is a synthetic process (no ffmpeg on this image): it bounds both at the pipe's rate."""
+    import queue
+    import subprocess
+    import torch
+    from telescope_cam_detection_b200.stream_capture_gpu_ffmpeg import RTSPStreamCaptureGPU
+    prog = ("import sys,os\nbuf=os.urandom(%d)\nw=sys.stdout.buffer\nfor i in range(%d):\n  w.write(buf)\nw.flush()\n"
+            % (FRAME_H * FRAME_W * 3, n_frames))
+    cmd = [sys.executable, "-c", prog]
+    out = {"frames": n_frames, "frame_bytes": FRAME_H * FRAME_W * 3}
+    q = queue.Queue(maxsize=8)
+    cap = RTSPStreamCaptureGPU("synthetic", q, FRAME_W, FRAME_H, camera_id="bench", command=cmd, max_failures=10 ** 9,
+                               keep_frames_on_gpu=True, device="cuda:%d" % local)
+    cap.start()
+    got, t0, c0 = 0, None, 0.0
+    while got < n_frames:
+        try:
+            q.get(timeout=10.0)
+        except queue.Empty:
+            break
+        if t0 is None:
+            t0, c0 = time.perf_counter(), time.process_time()   # the first frame pays the process start
+        got += 1
+    dt, dc = time.perf_counter() - (t0 or time.perf_counter()), time.process_time() - c0
+    cap.stop()
+    out["ours_fps"] = (got - 1) / dt if got > 1 and dt > 0 else 0.0
+    out["ours_GB/s"] = out["ours_fps"] * out["frame_bytes"] / 1e9
+    out["ours_host_cpu_ms_per_frame"] = 1e3 * dc / max(1, got - 1)   # this process, all threads
+    # the reference's loop body on the same writer
+    p = subprocess.Popen(cmd, stdout=subprocess.PIPE, stderr=subprocess.PIPE, bufsize=10 ** 8)
+    dev = torch.device("cuda", local)
+    got, t0, latest = 0, None, None
+    while got < n_frames:
+        raw = p.stdout.read(out["frame_bytes"])
+        if len(raw) != out["frame_bytes"]:
+            break
+        img = torch.from_numpy(np.frombuffer(raw, dtype=np.uint8).reshape(FRAME_H, FRAME_W, 3)).to(dev, non_blocking=True)
+        latest = img.clone()
+        queued = img.clone()  # noqa: F841 -- what the reference puts in its queue
+        if t0 is None:
+            torch.cuda.synchronize()
+            t0, c0 = time.perf_counter(), time.process_time()
+        got += 1
+    torch.cuda.synchronize()
+    dt, dc = time.perf_counter() - (t0 or time.perf_counter()), time.process_time() - c0
+    p.wait(timeout=10)
+    out["reference_chain_fps"] = (got - 1) / dt if got > 1 and dt > 0 else 0.0
+    out["reference_chain_host_cpu_ms_per_frame"] = 1e3 * dc / max(1, got - 1)
+    out["note"] = ("one camera, synthetic writer process -> pipe -> device frame in the consumer's queue; both legs are "
+                   "bounded by what one pipe delivers")
+    return out
+
+
 def rtdetr_side(local, batch, peaks):
     """BASELINE configs[3]: RT-DETR-R50 640x640 batch 32, 300 queries, no NMS -- graph replays timed with CUDA
     events on the program's stream; per-op eager pass for the MSDeformAttn kernel."""
@@ -348,21 +404,34 @@ def rtdetr_side(local, batch, peaks):
 
 
 # ----------------------------------------------------------------------------- GPU arm
+def _slot_order(eng, slots):
+    """Slots in submission order.  TCD_BENCH_SLOT_ORDER=interleave walks the engines first (engine 0 lane 0, engine 1
+    lane 0, ...), so a step count that is not a multiple of the slot count leaves every engine the same share."""
+    order = list(range(slots))
+    if os.environ.get("TCD_BENCH_SLOT_ORDER", "") == "interleave":
+        streams = [eng.stream(i) for i in range(slots)]
+        uniq = sorted(set(streams), key=streams.index)
+        by_eng = [[i for i in range(slots) if streams[i] == u] for u in uniq]
+        order = [g[l] for l in range(max(len(g) for g in by_eng)) for g in by_eng if l < len(g)]
+    return order
+
+
 def _pipelined(eng, batches, steps, on_result=None, slots=2):
     """steps x detect_batch with `slots` pipeline slots in flight (H2D of k+1 overlaps compute of k,
     and the low-occupancy layers of different batches share the chip)."""
     nb = len(batches)
+    order = _slot_order(eng, slots)
     for i in range(steps):
-        slot = i % slots
+        slot = order[i % slots]
         if i >= slots:
             rows = eng.wait(slot)
             if on_result:
                 on_result(rows, slot)
         eng.submit(slot, batches[i % nb])
     for i in range(max(0, steps - slots), steps):
-        rows = eng.wait(i % slots)
+        rows = eng.wait(order[i % slots])
         if on_result:
-            on_result(rows, i % slots)
+            on_result(rows, order[i % slots])
 
 
 def pin_rank_cpus(local, world):
@@ -574,6 +643,28 @@ def run_ours(args):
     _pipelined(eng, dev_batches, max(W, 2 * n_slots), None, n_slots)
     r_dev = timed(eng, lambda: _pipelined(eng, dev_batches, K, None, n_slots))
     fps_dev = stream_shard.aggregate_fps(B, K, world, r_dev["ms"])
+    dev_per_rank = None
+    if world > 1:     # the slowest rank sets `value`: keep every rank's own device time visible
+        t = torch.tensor([r_dev["ms_local"] / K], dtype=torch.float64, device="cuda")
+        allr = [torch.zeros_like(t) for _ in range(world)]
+        dist.all_gather(allr, t)
+        dev_per_rank = [round(float(x.item()), 4) for x in allr]
+    if args.quick and os.environ.get("TCD_BENCH_AB"):
+        # A/B of the submission order inside one process: (order, ms/step, per-rank ms/step) per repetition
+        ab = []
+        for rep in range(6):
+            order = "interleave" if rep % 2 else ""
+            os.environ["TCD_BENCH_SLOT_ORDER"] = order
+            r = timed(eng, lambda: _pipelined(eng, dev_batches, K, None, n_slots))
+            t = torch.tensor([r["ms_local"] / K], dtype=torch.float64, device="cuda")
+            allr = [torch.zeros_like(t) for _ in range(world)]
+            if world > 1:
+                dist.all_gather(allr, t)
+            else:
+                allr = [t]
+            ab.append((order or "sequential", round(r["ms"] / K, 4), [round(float(x.item()), 3) for x in allr]))
+        if rank == 0:
+            sys.stderr.write("AB %s\n" % json.dumps(ab))
     if args.quick:
         if rank == 0:
             prof = eng.profile(dev_batches[0], iters=2)
@@ -594,6 +685,7 @@ def run_ours(args):
                 with open(args.trace, "w") as f:
                     json.dump(tr, f)
             emit(json.dumps({"quick": True, "batch": B, "value": fps_dev, "ms_per_step": r_dev["ms"] / K, "slots": n_slots,
+                             "ms_per_step_per_rank": dev_per_rank,
                              "engines": n_engines, "eager_conv_ms": conv_ms, "eager_all_ms": sum(o["ms"] for o in prof),
                              "env": {k: v for k, v in os.environ.items() if k.startswith("TCD_")}}))
         eng.close()
@@ -773,6 +865,12 @@ def run_ours(args):
             rtdetr = rtdetr_side(local, args.rtdetr_batch, peaks)
         except Exception as e:  # noqa: BLE001
             rtdetr = {"error": repr(e)}
+    ingest = None
+    if not args.no_aux and world == 1:
+        try:
+            ingest = ingest_side(local)
+        except Exception as e:  # noqa: BLE001
+            ingest = {"error": repr(e)}
     cpu = None if args.no_cpu_baseline or world > 1 else cpu_baseline(obj_bias=args.obj_bias)
     e2e = {"value": e2e_main["value"], "unit": UNIT, "h2d_bytes_per_step": e2e_main["h2d_bytes_per_step"],
            "d2h_bytes_per_step": B * 300 * 7 * 4 + B * 4, "ms_per_step": e2e_main["ms_per_step"],
@@ -782,7 +880,8 @@ def run_ours(args):
     cfg = config_dict(args)
     line = {
         "metric": METRIC, "value": fps_dev, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": args.warmup,
-        "ms_per_step": r_dev["ms"] / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "ms_per_step": r_dev["ms"] / K, "ms_per_step_per_rank": dev_per_rank, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None,
         "dtype": "bf16", "data": "synthetic", "config": cfg,
         "details": {"parallelism": "replica per GPU, streams sharded by rank" if world > 1 else "1 GPU",
                     "pipeline": "%d slots in flight (%d engines x 2 lanes; CUDA graph per engine)" % (n_slots, n_engines),
@@ -790,7 +889,7 @@ def run_ours(args):
         "e2e": e2e, "parity_check": parity,
         "latency_ms_p50_sync_batch": float(np.median(lat)) if lat else None, "phases_ms_sync_batch": phases,
         "gpu_launches": int(r_dev["launches"]), "clocks": clocks, "roofline": roofline, "kernels": kernels,
-        "cpu_baseline": cpu, "rtdetr": rtdetr,
+        "cpu_baseline": cpu, "rtdetr": rtdetr, "ingest": ingest,
     }
     emit(json.dumps(line))
     if world > 1:

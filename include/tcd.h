@@ -267,6 +267,25 @@ tcd_status tcd_stream_bank_motion(tcd_stream_bank* b, const int32_t* rois, const
                                   int32_t ksize, int32_t blur_thr, int32_t* counts_host);
 tcd_status tcd_stream_bank_last_ms(const tcd_stream_bank* b, float out_ms[3]);
 
+/* ------------------------------------------------------------------ frame ring (ingest)
+ * Replaces the copy chain of the capture loop (src/stream_capture_gpu_ffmpeg.py:253-283: stdout.read -> bytes ->
+ * np.frombuffer -> torch.from_numpy(..).to(device) from pageable memory -> two .clone()s): raw bgr24 frames are read
+ * straight into a PINNED slot, uploaded once (asynchronously, on the ring's own copy stream) into the matching DEVICE
+ * slot, and consumers use the device slot itself (tcd_detector_submit(..., frames_on_device = 1),
+ * tcd_stream_bank, tcd_motion_apply ...).  A slot is rewritten n_slots frames later: size the ring for the deepest
+ * consumer queue.  One ring per camera, one producer thread per ring; slots are plain indices the caller cycles.  */
+typedef struct tcd_frame_ring tcd_frame_ring;
+tcd_status tcd_frame_ring_create(int32_t n_slots, int64_t frame_bytes, int32_t device, tcd_frame_ring** out);
+void tcd_frame_ring_destroy(tcd_frame_ring* r);
+uint8_t* tcd_frame_ring_host(tcd_frame_ring* r, int32_t slot);          /* pinned host slot */
+const uint8_t* tcd_frame_ring_device(tcd_frame_ring* r, int32_t slot);  /* device slot */
+/* blocking read()s from fd until the slot holds one frame; *got < frame_bytes = end of stream.  Waits for the slot's
+ * previous upload first.  (ctypes calls it without the GIL: a capture thread costs the interpreter nothing.) */
+tcd_status tcd_frame_ring_read_fd(tcd_frame_ring* r, int32_t slot, int32_t fd, int64_t* got);
+tcd_status tcd_frame_ring_publish(tcd_frame_ring* r, int32_t slot);     /* start the slot's upload */
+/* order `stream` (a cudaStream_t) after the slot's upload; NULL = wait on the host */
+tcd_status tcd_frame_ring_wait(tcd_frame_ring* r, int32_t slot, void* stream);
+
 /* ------------------------------------------------------------------ Stage-2 crops (K13)
  * Replaces the per-detection slice frame[y1:y2, x1:x2] (src/two_stage_pipeline_yolox.py:289)
  * + SpeciesClassifier.preprocess (src/species_classifier.py:311-350) for ALL crops of a

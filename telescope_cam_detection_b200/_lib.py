@@ -135,6 +135,13 @@ SIGNATURES = {
     "tcd_stream_bank_gate": (C.c_int, [_P, C.c_int32, _I32P]),
     "tcd_stream_bank_motion": (C.c_int, [_P, _I32P, _I32P, C.c_int32, C.c_int32, C.c_int32, _I32P]),
     "tcd_stream_bank_last_ms": (C.c_int, [_P, _F32P]),
+    "tcd_frame_ring_create": (C.c_int, [C.c_int32, C.c_int64, C.c_int32, _PP]),
+    "tcd_frame_ring_destroy": (None, [_P]),
+    "tcd_frame_ring_host": (C.c_void_p, [_P, C.c_int32]),
+    "tcd_frame_ring_device": (C.c_void_p, [_P, C.c_int32]),
+    "tcd_frame_ring_read_fd": (C.c_int, [_P, C.c_int32, C.c_int32, _I64P]),
+    "tcd_frame_ring_publish": (C.c_int, [_P, C.c_int32]),
+    "tcd_frame_ring_wait": (C.c_int, [_P, C.c_int32, _P]),
     "tcd_crop_resize": (C.c_int, [_P, C.c_int32, C.c_int32, C.c_int64, _I32P, C.c_int32, C.c_int32,
                                   C.POINTER(PreprocCfg), C.c_int32, _P, _P]),
     "tcd_program_create": (C.c_int, [C.c_int32, _PP]),
