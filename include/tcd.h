@@ -286,6 +286,32 @@ tcd_status tcd_frame_ring_publish(tcd_frame_ring* r, int32_t slot);     /* start
 /* order `stream` (a cudaStream_t) after the slot's upload; NULL = wait on the host */
 tcd_status tcd_frame_ring_wait(tcd_frame_ring* r, int32_t slot, void* stream);
 
+/* ------------------------------------------------------------------ crop enhancement
+ * Replaces ImageEnhancer.enhance_clahe_bilateral (src/image_enhancement.py:146-184): cv2.cvtColor BGR2LAB ->
+ * cv2.createCLAHE(clipLimit, tileGridSize).apply(L) -> cv2.cvtColor LAB2BGR -> cv2.bilateralFilter(d, sigmaColor,
+ * sigmaSpace); single-channel crops skip the colour conversions.  One call enhances a BATCH of crops in three kernel
+ * launches.  Colour conversions and CLAHE equal the library's 8-bit results bit for bit; the bilateral filter equals
+ * oracle/enhance.py bit for bit and the library within its own path-to-path spread. */
+typedef struct tcd_enhance_cfg {
+  float clip_limit;          /* CLAHE clipLimit (reference default 2.0) */
+  int32_t grid_x, grid_y;    /* CLAHE tileGridSize (8, 8) */
+  int32_t d;                 /* bilateral diameter (9); 3..15 */
+  float sigma_color, sigma_space; /* 75, 75 */
+} tcd_enhance_cfg;
+typedef struct tcd_enhancer tcd_enhancer;
+tcd_status tcd_enhancer_create(const tcd_enhance_cfg* cfg, int32_t device, tcd_enhancer** out);
+void tcd_enhancer_destroy(tcd_enhancer* e);
+/* imgs[i] / outs[i]: HWC u8 with `channels` (1 or 3) channels, h[i] x w[i], row strides in bytes (NULL or 0 = tight);
+ * host or device pointers as the two flags say (device crops may be views into a frame).  Returns when the outputs
+ * are complete. */
+tcd_status tcd_enhance_clahe_bilateral(tcd_enhancer* e, const uint8_t* const* imgs, const int32_t* h, const int32_t* w,
+                                       const int64_t* stride, int32_t n, int32_t channels, int32_t imgs_on_device,
+                                       uint8_t* const* outs, const int64_t* out_stride, int32_t outs_on_device);
+tcd_status tcd_enhancer_stream(tcd_enhancer* e, void** stream);
+/* the 8-bit colour-conversion tables the kernels use (host code, no GPU needed): gamma[256], cbrt[3072], yf[512],
+ * inv[4096], forward / inverse matrix coefficients cf[9] / ci[9] -- exported so that they can be checked without a GPU */
+tcd_status tcd_enhance_tables(uint16_t* gamma, uint16_t* cbrt, uint16_t* yf, uint8_t* inv, int32_t* cf, int32_t* ci);
+
 /* ------------------------------------------------------------------ Stage-2 crops (K13)
  * Replaces the per-detection slice frame[y1:y2, x1:x2] (src/two_stage_pipeline_yolox.py:289)
  * + SpeciesClassifier.preprocess (src/species_classifier.py:311-350) for ALL crops of a

@@ -59,6 +59,11 @@ OP_KINDS = {"layernorm": 1, "add_rows": 2, "mask_rows": 3, "mha": 4, "msda": 5, 
             "upsample": 14}
 
 
+class EnhanceCfg(C.Structure):
+    _fields_ = [("clip_limit", C.c_float), ("grid_x", C.c_int32), ("grid_y", C.c_int32), ("d", C.c_int32),
+                ("sigma_color", C.c_float), ("sigma_space", C.c_float)]
+
+
 def make_preproc_cfg(out_h, out_w, mode=0, swap_rb=0, scale=1.0, mean=(0.0, 0.0, 0.0),
                      std=(1.0, 1.0, 1.0), pad_value=114.0):
     cfg = PreprocCfg()
@@ -135,6 +140,12 @@ SIGNATURES = {
     "tcd_stream_bank_gate": (C.c_int, [_P, C.c_int32, _I32P]),
     "tcd_stream_bank_motion": (C.c_int, [_P, _I32P, _I32P, C.c_int32, C.c_int32, C.c_int32, _I32P]),
     "tcd_stream_bank_last_ms": (C.c_int, [_P, _F32P]),
+    "tcd_enhancer_create": (C.c_int, [C.POINTER(EnhanceCfg), C.c_int32, _PP]),
+    "tcd_enhancer_destroy": (None, [_P]),
+    "tcd_enhance_clahe_bilateral": (C.c_int, [_P, _PP, _I32P, _I32P, _I64P, C.c_int32, C.c_int32, C.c_int32, _PP, _I64P,
+                                              C.c_int32]),
+    "tcd_enhancer_stream": (C.c_int, [_P, _PP]),
+    "tcd_enhance_tables": (C.c_int, [C.POINTER(C.c_uint16), C.POINTER(C.c_uint16), C.POINTER(C.c_uint16), _U8P, _I32P, _I32P]),
     "tcd_frame_ring_create": (C.c_int, [C.c_int32, C.c_int64, C.c_int32, _PP]),
     "tcd_frame_ring_destroy": (None, [_P]),
     "tcd_frame_ring_host": (C.c_void_p, [_P, C.c_int32]),

@@ -113,6 +113,29 @@ int crop_resize_launch(const uint8_t* frame, int h, int w, long long stride, con
                        int n, int S, const tcd_preproc_cfg* cfg, int layout, void* out,
                        cudaStream_t stream);
 
+// ---- crop enhancement (enhance.cu)
+struct EnhTables {            // device pointers
+  const uint16_t* gamma;      // [256]  sRGB gamma x 8
+  const uint16_t* cbrt;       // [3072] cube root, 1.15 fixed point
+  const uint16_t* yf;         // [256][2] L -> (y, fy), 14-bit
+  const uint8_t* inv;         // [4096] inverse gamma
+};
+struct EnhImg {
+  const uint8_t* src;         // crop, HWC u8 (cn channels)
+  long long src_stride;
+  uint8_t* mid;               // after CLAHE (tight rows)
+  uint8_t* dst;
+  long long dst_stride;
+  uint8_t* luts;              // [gy*gx][256]
+  int h, w, cn, th, tw, clip;
+  float lut_scale, inv_tw, inv_th;
+};
+void enhance_host_tables(uint16_t* gamma, uint16_t* cbrt, uint16_t* yf, uint8_t* inv, int32_t* cf, int32_t* ci);
+int enhance_set_constants(const int32_t* cf, const int32_t* ci);
+int enhance_set_window(const int8_t* dy, const int8_t* dx, const float* w, int maxk);
+int enhance_launch(const EnhImg* imgs_dev, int n, int cn, int gx, int gy, int max_h, int max_w, const EnhTables& t,
+                   const float* color_w_dev, int radius, int maxk, cudaStream_t stream);
+
 int require_sm100();
 
 }  // namespace tcd

@@ -7,9 +7,12 @@ the host.  What changes: `process_detections` gathers ALL crops of a frame per c
 batched CUDA kernel and one classifier forward (SpeciesClassifier.classify_crops) instead of one
 slice + resize + forward + .item() sync per detection (:453-481).
 
-Not rebuilt (out of scope / "next" N3): the Real-ESRGAN / CLAHE enhancer and
-its LRU cache -- `enhancement_config` is accepted and ignored with a warning, which is also what
-the reference does when the enhancer fails to load (:104-106).  The species activity table
+Enhancement (`enhancement_config`, reference :90-121, :312-362): method "clahe" runs ImageEnhancer's batched CUDA
+path on all crops of a category at once; the LRU cache keeps the reference's key (MD5 of the 8x8 INTER_AREA grey
+thumbnail, :142-178) and eviction, so a cache hit returns exactly what the reference would return, and
+`enhancement_cache_size <= 0` skips hashing altogether (the batched kernels are cheaper than the thumbnail).  Real-ESRGAN
+is a third-party network outside the hot path: the enhancer fails to load and the pipeline continues without it, which is
+the reference's own behaviour for a load failure (:119-121).  The species activity table
 (src/species_activity_patterns.py) is used if importable, else every species counts as active.
 """
 import logging
@@ -57,8 +60,19 @@ class TwoStageDetectionPipeline:
         self.cache_misses = 0
         self.enhancer = None
         if enhancement_config and enhancement_config.get("enabled", False):
-            logger.warning("image enhancement (%s) is not part of the B200 hot path; continuing without it",
-                           enhancement_config.get("method", "none"))
+            try:
+                from .image_enhancement import ImageEnhancer
+                params = {"method": enhancement_config.get("method", "none"),
+                          "device": enhancement_config.get("device", self.device)}
+                for group in ("realesrgan", "clahe", "bilateral"):
+                    for key, value in (enhancement_config.get(group) or {}).items():
+                        params["%s_%s" % (group, key)] = value
+                self.enhancer = ImageEnhancer(**params)
+                logger.info("Image enhancer loaded (cache size: %d)", self.enhancement_cache_size)
+            except Exception as e:  # noqa: BLE001 -- reference :119-121
+                logger.error("Failed to load image enhancer (method=%s): %s", enhancement_config.get("method", "none"), e)
+                logger.warning("Continuing without image enhancement")
+                self.enhancer = None
         self.enhancement_times = deque(maxlen=1000)
         self.classification_times = deque(maxlen=1000)
         self._is_active = _activity_fn()
@@ -123,6 +137,56 @@ class TwoStageDetectionPipeline:
         else:
             self._set_detection_species_fields(detection, top["species"], top["confidence"], category, level)
 
+    # ------------------------------------------------------------------ enhancement (reference :142-178, :312-362)
+    @staticmethod
+    def _compute_crop_hash(crop) -> str:
+        import hashlib
+        import cv2
+        if not isinstance(crop, np.ndarray):
+            crop = crop.detach().cpu().numpy()
+            if crop.ndim == 3 and crop.shape[0] in (1, 3):
+                crop = crop.transpose(1, 2, 0)
+        small = cv2.resize(np.ascontiguousarray(crop), (8, 8), interpolation=cv2.INTER_AREA)
+        gray = cv2.cvtColor(small, cv2.COLOR_BGR2GRAY) if small.ndim == 3 else small
+        return hashlib.md5(gray.tobytes()).hexdigest()
+
+    def _enhance_crops(self, crops: List[Any]) -> List[Any]:
+        """All crops of one category: cache look-ups first, ONE batched enhancement for the misses."""
+        t0 = time.time()
+        if self.enhancement_cache_size <= 0:
+            out = self.enhancer.enhance_batch(crops) if self.enhancer.method == "clahe" else [self.enhancer.enhance(c) for c in crops]
+            dt = (time.time() - t0) * 1000 / max(len(crops), 1)
+            self.enhancement_times.extend([dt] * len(crops))
+            return out
+        out: List[Any] = [None] * len(crops)
+        keys = [self._compute_crop_hash(c) for c in crops]
+        miss: Dict[str, int] = {}
+        for n, key in enumerate(keys):
+            if key in self.enhancement_cache:
+                out[n] = self.enhancement_cache[key]
+                self.enhancement_cache.move_to_end(key)
+                self.cache_hits += 1
+            elif key in miss:       # the same thumbnail twice in one frame: the reference's second look-up is a hit
+                self.cache_hits += 1
+            else:
+                miss[key] = n
+                self.cache_misses += 1
+        if miss:
+            todo = [crops[n] for n in miss.values()]
+            done = self.enhancer.enhance_batch(todo) if self.enhancer.method == "clahe" else [self.enhancer.enhance(c) for c in todo]
+            dt = (time.time() - t0) * 1000 / len(todo)
+            for key, img in zip(miss, done):
+                self.enhancement_cache[key] = img
+                self.enhancement_times.append(dt)
+                if len(self.enhancement_cache) > self.enhancement_cache_size:
+                    self.enhancement_cache.popitem(last=False)
+        for n, key in enumerate(keys):
+            if out[n] is None:
+                out[n] = self.enhancement_cache.get(key)
+                if out[n] is None:   # evicted within this very batch (cache smaller than the frame's crop count)
+                    out[n] = done[list(miss).index(key)]
+        return out
+
     def classify_detection(self, frame, detection: Dict[str, Any]) -> Dict[str, Any]:
         """One detection (reference :203-451)."""
         if not self.enable_species_classification:
@@ -153,9 +217,21 @@ class TwoStageDetectionPipeline:
             t0 = time.time()
             try:
                 all_results: List[Any] = [None] * len(items)
+                enhanced = None
+                if self.enhancer is not None and self.enhancer.method != "none":
+                    try:
+                        enhanced = self._enhance_crops([frame[b[1]:b[3], b[0]:b[2]] for b in boxes])
+                    except Exception as e:  # noqa: BLE001 -- reference :364-366: classify the plain crop
+                        logger.warning("Enhancement failed: %s, using original crop", e)
                 for k in sorted(set(top_ks)):
                     sel = [n for n, kk in enumerate(top_ks) if kk == k]
-                    if hasattr(clf, "classify_crops"):
+                    if enhanced is not None:
+                        if hasattr(clf, "classify_crops"):
+                            res = [clf.classify_crops(enhanced[n], [(0, 0, int(enhanced[n].shape[1]), int(enhanced[n].shape[0]))],
+                                                      top_k=k)[0] for n in sel]
+                        else:
+                            res = [clf.classify(enhanced[n], top_k=k) for n in sel]
+                    elif hasattr(clf, "classify_crops"):
                         res = clf.classify_crops(frame, [boxes[n] for n in sel], top_k=k)
                     else:  # any classifier with the reference's per-crop API
                         res = [clf.classify(frame[boxes[n][1]:boxes[n][3], boxes[n][0]:boxes[n][2]], top_k=k)
@@ -179,6 +255,18 @@ class TwoStageDetectionPipeline:
         stats = {"stage2_enabled": self.enable_species_classification,
                  "classifiers_loaded": list(self.species_classifiers.keys()),
                  "num_classifiers": len(self.species_classifiers), "enhancement_enabled": self.enhancer is not None}
+        if self.enhancer is not None:    # reference :493-503
+            stats["enhancement_method"] = self.enhancer.method
+            if self.enhancement_times:
+                stats["avg_enhancement_ms"] = float(np.mean(self.enhancement_times))
+                stats["enhancement_count"] = len(self.enhancement_times)
+            total = self.cache_hits + self.cache_misses
+            if total > 0:
+                stats["enhancement_cache_hit_rate"] = float(self.cache_hits / total)
+                stats["enhancement_cache_hits"] = self.cache_hits
+                stats["enhancement_cache_misses"] = self.cache_misses
+                stats["enhancement_cache_size"] = len(self.enhancement_cache)
+                stats["enhancement_cache_max_size"] = self.enhancement_cache_size
         if self.classification_times:
             stats["avg_classification_ms"] = float(np.mean(self.classification_times))
             stats["classification_count"] = len(self.classification_times)

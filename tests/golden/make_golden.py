@@ -13,6 +13,9 @@ box, so the outputs are committed; rerun with `python tests/golden/make_golden.p
                    shipped per-class tables (config/config.yaml:238-264).  These two import
                    src/yolox_detector.py, which needs a YOLOX checkout: a stub package exporting
                    the oracle restatement is put on sys.path.
+  enhance_ref.npz  ImageEnhancer(method="clahe").enhance on seeded crops (tests/util.enhance_crops): colour crops of
+                   several sizes (tile-divisible and not), a grey crop (final outputs only: the stages are checked
+                   against cv2 itself, which is on both boxes)
 Versions of the libraries that did the arithmetic are stored in every file.
 """
 import json
@@ -192,8 +195,23 @@ def stage2():
         shutil.rmtree(tmp, ignore_errors=True)
 
 
+def enhance():
+    sys.path.insert(0, REF)
+    # image_enhancement.py imports torch and cv2 only; the Real-ESRGAN imports are inside _load_realesrgan
+    from src.image_enhancement import ImageEnhancer
+    from util import enhance_crops
+    enh = ImageEnhancer(method="clahe")
+    out = {"versions": json.dumps(versions())}
+    for i, crop in enumerate(enhance_crops()):
+        out["out%d" % i] = enh.enhance(crop)
+    np.savez_compressed(os.path.join(HERE, "enhance_ref.npz"), **out)
+    print("enhance: %d crops" % len(enhance_crops()))
+
+
 if __name__ == "__main__":
-    which = sys.argv[1:] or ["motion", "format", "stage2"]
+    which = sys.argv[1:] or ["motion", "format", "stage2", "enhance"]
+    if "enhance" in which:
+        enhance()
     if "motion" in which:
         motion_and_empty()
     if "format" in which:

@@ -67,3 +67,20 @@ def motion_sequence(seed=7, h=480, w=640, n=40):
             boxes.append({"x1": float(w + 5), "y1": 10.0, "x2": float(w + 50), "y2": 60.0})  # off-frame
         out.append((np.clip(f, 0, 255).astype(np.uint8), boxes))
     return out
+
+
+def enhance_crops():
+    """Seeded Stage-2 crops for the enhancement tests: structured colour crops (tile-divisible, not divisible in one /
+    both axes, dark, bright), one of pure noise, and a grey crop."""
+    rng = np.random.default_rng(2024)
+    out = []
+    for k, (h, w) in enumerate([(128, 128), (96, 203), (131, 77), (112, 168), (57, 64)]):
+        img = structured_frame(300 + k, h, w).astype(np.int16)
+        if k == 2:
+            img = img // 4            # a dark crop: the linear segments of both colour conversions
+        if k == 3:
+            img = 128 + img // 2
+        out.append(np.clip(img, 0, 255).astype(np.uint8))
+    out.append(rng.integers(0, 256, (80, 120, 3), dtype=np.uint8))
+    out.append(np.ascontiguousarray(structured_frame(310, 150, 170)[..., 1]))
+    return out
