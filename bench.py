@@ -368,6 +368,36 @@ def enhance_side(local, dev_pool, peaks, n_crops=64, side=224):
                     "bilateral kernel is arithmetic-bound (48 taps x 3 channels per pixel), not HBM-bound"}
 
 
+def jpeg_side(local, dev_pool, peaks, n_frames=8, quality=90):
+    """Row N4: the MJPEG tick of 8 cameras -- 8 device-resident 1080p frames -> 8 .jpg files in host memory, one
+    batched call (five launches); beside it cv2.imencode on the host cores, one frame at a time, as
+    web_server.py:923 runs it.  The files are byte-identical (tests/test_jpeg.py)."""
+    import cv2
+    import torch
+    from telescope_cam_detection_b200.jpeg_encode import JpegEncoder
+    frames = [dev_pool[i] for i in range(n_frames)]
+    enc = JpegEncoder((FRAME_H, FRAME_W), max_batch=n_frames, device="cuda:%d" % local)
+    for _ in range(3):
+        files = enc.encode_batch(frames, quality)
+    torch.cuda.synchronize()
+    reps = 20
+    t0 = time.perf_counter()
+    for _ in range(reps):
+        files = enc.encode_batch(frames, quality)
+    ms = 1e3 * (time.perf_counter() - t0) / reps
+    host = [f.cpu().numpy() for f in frames]
+    t0 = time.perf_counter()
+    refs = [cv2.imencode(".jpg", f, [cv2.IMWRITE_JPEG_QUALITY, quality])[1] for f in host]
+    cpu_ms = 1e3 * (time.perf_counter() - t0)
+    same = all(a.tobytes() == b.tobytes() for a, b in zip(files, refs))
+    enc.close()
+    px_bytes = n_frames * FRAME_H * FRAME_W * 3
+    return {"frames": n_frames, "quality": quality, "ms_per_batch": ms, "frames/s": n_frames / ms * 1e3,
+            "file_bytes_mean": float(np.mean([len(f) for f in files])), "pixel_GB/s": px_bytes / (ms * 1e-3) / 1e9,
+            "cv2_host_ms_per_batch": cpu_ms, "cv2_frames/s": n_frames / cpu_ms * 1e3, "bytes_identical_to_cv2": bool(same),
+            "note": "wall time of encode_batch: descriptor upload, 5 launches, size read-back, file D2H (two stream syncs)"}
+
+
 def rtdetr_side(local, batch, peaks):
     """BASELINE configs[3]: RT-DETR-R50 640x640 batch 32, 300 queries, no NMS -- graph replays timed with CUDA
     events on the program's stream; per-op eager pass for the MSDeformAttn kernel."""
@@ -913,6 +943,10 @@ def run_ours(args):
             kernels["enhance"] = enhance_side(local, dev_pool, peaks)
         except Exception as e:  # noqa: BLE001
             kernels["enhance"] = {"error": repr(e)}
+        try:
+            kernels["jpeg"] = jpeg_side(local, dev_pool, peaks)
+        except Exception as e:  # noqa: BLE001
+            kernels["jpeg"] = {"error": repr(e)}
     cpu = None if args.no_cpu_baseline or world > 1 else cpu_baseline(obj_bias=args.obj_bias)
     e2e = {"value": e2e_main["value"], "unit": UNIT, "h2d_bytes_per_step": e2e_main["h2d_bytes_per_step"],
            "d2h_bytes_per_step": B * 300 * 7 * 4 + B * 4, "ms_per_step": e2e_main["ms_per_step"],

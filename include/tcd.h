@@ -312,6 +312,20 @@ tcd_status tcd_enhancer_stream(tcd_enhancer* e, void** stream);
  * inv[4096], forward / inverse matrix coefficients cf[9] / ci[9] -- exported so that they can be checked without a GPU */
 tcd_status tcd_enhance_tables(uint16_t* gamma, uint16_t* cbrt, uint16_t* yf, uint8_t* inv, int32_t* cf, int32_t* ci);
 
+/* ------------------------------------------------------------------ JPEG encode
+ * Replaces cv2.imencode('.jpg', frame, [cv2.IMWRITE_JPEG_QUALITY, q]) on the result path (src/web_server.py:923: one
+ * encode per camera per MJPEG tick; src/snapshot_saver.py:160 ring-buffer compression, :358-404 cv2.imwrite) for a
+ * batch of BGR u8 frames, host or device.  Baseline sequential JPEG, YCbCr 4:2:0, Annex K Huffman tables, IJG quality
+ * scale; the files are byte-identical to the reference's encoder (libjpeg-turbo inside cv2). */
+typedef struct tcd_jpeg_encoder tcd_jpeg_encoder;
+tcd_status tcd_jpeg_encoder_create(int32_t max_h, int32_t max_w, int32_t max_batch, int32_t device, tcd_jpeg_encoder** out);
+void tcd_jpeg_encoder_destroy(tcd_jpeg_encoder* e);
+/* out[i]: HOST buffer of out_cap[i] bytes (tcd_jpeg_max_bytes never fails); out_size[i] = file length */
+tcd_status tcd_jpeg_encode(tcd_jpeg_encoder* e, const uint8_t* const* frames, const int32_t* h, const int32_t* w,
+                           const int64_t* stride, int32_t n, int32_t frames_on_device, int32_t quality,
+                           uint8_t* const* out, const int64_t* out_cap, int64_t* out_size);
+int64_t tcd_jpeg_max_bytes(int32_t h, int32_t w);
+
 /* ------------------------------------------------------------------ Stage-2 crops (K13)
  * Replaces the per-detection slice frame[y1:y2, x1:x2] (src/two_stage_pipeline_yolox.py:289)
  * + SpeciesClassifier.preprocess (src/species_classifier.py:311-350) for ALL crops of a

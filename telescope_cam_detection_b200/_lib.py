@@ -146,6 +146,10 @@ SIGNATURES = {
                                               C.c_int32]),
     "tcd_enhancer_stream": (C.c_int, [_P, _PP]),
     "tcd_enhance_tables": (C.c_int, [C.POINTER(C.c_uint16), C.POINTER(C.c_uint16), C.POINTER(C.c_uint16), _U8P, _I32P, _I32P]),
+    "tcd_jpeg_encoder_create": (C.c_int, [C.c_int32, C.c_int32, C.c_int32, C.c_int32, _PP]),
+    "tcd_jpeg_encoder_destroy": (None, [_P]),
+    "tcd_jpeg_encode": (C.c_int, [_P, _PP, _I32P, _I32P, _I64P, C.c_int32, C.c_int32, C.c_int32, _PP, _I64P, _I64P]),
+    "tcd_jpeg_max_bytes": (C.c_int64, [C.c_int32, C.c_int32]),
     "tcd_frame_ring_create": (C.c_int, [C.c_int32, C.c_int64, C.c_int32, _PP]),
     "tcd_frame_ring_destroy": (None, [_P]),
     "tcd_frame_ring_host": (C.c_void_p, [_P, C.c_int32]),

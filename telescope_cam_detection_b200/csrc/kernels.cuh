@@ -136,6 +136,24 @@ int enhance_set_window(const int8_t* dy, const int8_t* dx, const float* w, int m
 int enhance_launch(const EnhImg* imgs_dev, int n, int cn, int gx, int gy, int max_h, int max_w, const EnhTables& t,
                    const float* color_w_dev, int radius, int maxk, cudaStream_t stream);
 
+// ---- JPEG encode (jpeg.cu)
+struct JpegImg {
+  const uint8_t* src;          // BGR u8 HWC
+  long long stride;
+  int h, w, mcus_x, mcus_y, blocks_x, blocks_y;   // blocks_*: real luma blocks, ceil(w/8) x ceil(h/8)
+  const uint16_t* qtab;        // [2][64] natural order: luma, chroma
+  int16_t* coef;               // [mcus][6][64] zigzag order
+  unsigned int* bit_cnt;       // [mcus*6]
+  unsigned long long* bit_off; // [mcus*6]
+  unsigned int* words;         // zeroed bit stream (big-endian inside each word)
+  unsigned long long* meta;    // [0] total bits, [1] file bytes, [2] overflow flag
+  uint8_t* out;                // file buffer: header (written by the host side) + scan + EOI
+  long long out_cap;
+  int header_len;
+};
+int jpeg_set_tables(const uint8_t* zigzag_pos, const uint16_t* code, const uint8_t* size);
+int jpeg_launch(const JpegImg* imgs_dev, int n, int max_mcus_x, int max_mcus_y, cudaStream_t stream);
+
 int require_sm100();
 
 }  // namespace tcd
