@@ -308,6 +308,19 @@ tcd_status tcd_enhance_clahe_bilateral(tcd_enhancer* e, const uint8_t* const* im
                                        const int64_t* stride, int32_t n, int32_t channels, int32_t imgs_on_device,
                                        uint8_t* const* outs, const int64_t* out_stride, int32_t outs_on_device);
 tcd_status tcd_enhancer_stream(tcd_enhancer* e, void** stream);
+/* No counterpart in the reference.  tcd_enhance_clahe_bilateral for ONE
+ * crop for callers that cannot allocate: no handle, and no cudaMalloc / cudaFree / allocating library call inside --
+ * all device scratch (descriptor, colour tables, tile LUTs, the intermediate image) lives in a static 1 MiB device array
+ * inside libtcd, resident on every GPU that loads the library until exit.  img_dev / out_dev: DEVICE pointers, HWC u8,
+ * `channels` 1 or 3, row strides in bytes (0 = tight).  Limits: h * w * channels <= tcd_enhance_noalloc_max_image_bytes()
+ * (786 432 = 512 x 512 x 3) and grid_x * grid_y <= 64; larger requests fail with TCD_ERR_INVALID and a message that names
+ * the limit.  Work is enqueued on `stream` (a cudaStream_t, NULL = default) and the call returns once it is complete.
+ * Every call shares the one scratch array: calls that overlap on the GPU (other host threads / streams) race and must
+ * be serialised by the caller.  Results equal tcd_enhance_clahe_bilateral's bit for bit. */
+tcd_status tcd_enhance_clahe_bilateral_noalloc(const tcd_enhance_cfg* cfg, int32_t device, const uint8_t* img_dev, int32_t h,
+                                               int32_t w, int64_t stride, int32_t channels, uint8_t* out_dev,
+                                               int64_t out_stride, void* stream);
+int64_t tcd_enhance_noalloc_max_image_bytes(void);
 /* the 8-bit colour-conversion tables the kernels use (host code, no GPU needed): gamma[256], cbrt[3072], yf[512],
  * inv[4096], forward / inverse matrix coefficients cf[9] / ci[9] -- exported so that they can be checked without a GPU */
 tcd_status tcd_enhance_tables(uint16_t* gamma, uint16_t* cbrt, uint16_t* yf, uint8_t* inv, int32_t* cf, int32_t* ci);

@@ -144,6 +144,9 @@ SIGNATURES = {
     "tcd_enhancer_destroy": (None, [_P]),
     "tcd_enhance_clahe_bilateral": (C.c_int, [_P, _PP, _I32P, _I32P, _I64P, C.c_int32, C.c_int32, C.c_int32, _PP, _I64P,
                                               C.c_int32]),
+    "tcd_enhance_clahe_bilateral_noalloc": (C.c_int, [C.POINTER(EnhanceCfg), C.c_int32, _P, C.c_int32, C.c_int32, C.c_int64,
+                                                      C.c_int32, _P, C.c_int64, _P]),
+    "tcd_enhance_noalloc_max_image_bytes": (C.c_int64, []),
     "tcd_enhancer_stream": (C.c_int, [_P, _PP]),
     "tcd_enhance_tables": (C.c_int, [C.POINTER(C.c_uint16), C.POINTER(C.c_uint16), C.POINTER(C.c_uint16), _U8P, _I32P, _I32P]),
     "tcd_jpeg_encoder_create": (C.c_int, [C.c_int32, C.c_int32, C.c_int32, C.c_int32, _PP]),

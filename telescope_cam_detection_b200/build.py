@@ -15,8 +15,8 @@ OUT = os.path.join(HERE, "libtcd.so")
 OBJ = os.path.join(HERE, "build")
 
 # TUs whose fp32 arithmetic must round exactly like the scalar reference code (no FMA contraction)
-NO_FMAD = {"postproc.cu", "motion.cu", "enhance.cu"}
-SOURCES = ["capi_core.cu", "capi_detector.cu", "capi_motion.cu", "capi_ingest.cu", "capi_enhance.cu", "enhance.cu", "capi_jpeg.cu", "jpeg.cu", "conv_umma.cu", "yolox_net.cu", "program.cu",
+NO_FMAD = {"postproc.cu", "motion.cu", "enhance.cu", "noalloc.cu"}
+SOURCES = ["capi_core.cu", "capi_detector.cu", "capi_motion.cu", "capi_ingest.cu", "capi_enhance.cu", "enhance.cu", "capi_jpeg.cu", "jpeg.cu", "noalloc.cu", "conv_umma.cu", "yolox_net.cu", "program.cu",
            "tfm_kernels.cu", "tfm_kernels2.cu", "pil_resize.cu",
            "yolox_plan.cu", "preproc.cu", "postproc.cu", "motion.cu", "crop_resize.cu"]
 ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
