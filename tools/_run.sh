@@ -1,5 +1,8 @@
 #!/bin/bash
-T=${1:-t01}
+T=${1:-f02}
 mkdir -p gpurun_out
-timeout 300 python -m pytest tests/test_zz_no_alloc.py -q -x > gpurun_out/${T}_alone.log 2>&1; echo "alone rc=$?"; tail -4 gpurun_out/${T}_alone.log
-timeout 1500 python -m pytest tests -m gpu -x -q > gpurun_out/${T}_all.log 2>&1; echo "all rc=$?"; tail -4 gpurun_out/${T}_all.log
+for i in 1 2; do
+timeout 600 python bench.py --no-aux --no-cpu-baseline > gpurun_out/${T}_b$i.json 2> gpurun_out/${T}_b$i.err; echo "rc=$?"
+python tools/show_bench.py gpurun_out/${T}_b$i.json 2>/dev/null | sed -n 1,6p
+done
+nproc; lscpu | grep -E "Model name|MHz" | head -3
