@@ -672,7 +672,7 @@ def run_ours(args):
             dist.barrier()
         torch.cuda.synchronize()
 
-    def timed(e, body):
+    def timed(e, body, pause_gc=False):
         """body() runs K steps on engine handle `e`; device time = first event on its streams -> last event on any of
         them (and on the copy / NCCL streams), max over ranks."""
         streams = [torch.cuda.ExternalStream(e.stream(i), device=local) for i in range(e.num_slots)]
@@ -681,12 +681,13 @@ def run_ours(args):
             if e.stream(i) not in seen:
                 seen.add(e.stream(i))
                 uniq.append(st)
-        # a cyclic-GC pass over the benchmark's own object graph (frame lists, tensors) inside a 10 ms timed region shows
-        # up as one straggler rank at N = 8: collect now, keep the collector off while the steps are submitted (what
-        # YOLOXDetector.detect_batch does for its own loop)
+        # pause_gc (device-resident leg only, where the host does nothing but submit): a cyclic-GC pass over the
+        # benchmark's own object graph (frame lists, tensors) inside a 10 ms timed region shows up as one straggler rank
+        # at N = 8.  The e2e legs run with the collector as the application would have it.
         import gc
-        gc.collect()
-        gc.disable()
+        if pause_gc:
+            gc.collect()
+            gc.disable()
         barrier()
         e0 = torch.cuda.Event(enable_timing=True)
         e0.record(uniq[0])
@@ -702,7 +703,8 @@ def run_ours(args):
             ev.record(st)
             ends.append(ev)
         barrier()
-        gc.enable()
+        if pause_gc:
+            gc.enable()
         wall = time.perf_counter() - t0
         ms_local = max(e0.elapsed_time(ev) for ev in ends)
         ms = stream_shard.max_over_ranks(ms_local, world, device="cuda")
@@ -716,7 +718,7 @@ def run_ours(args):
 
     # ---- device-resident frames (value): engine handle, every slot in flight
     _pipelined(eng, dev_batches, max(W, 2 * n_slots), None, n_slots)
-    r_dev = timed(eng, lambda: _pipelined(eng, dev_batches, K, None, n_slots))
+    r_dev = timed(eng, lambda: _pipelined(eng, dev_batches, K, None, n_slots), pause_gc=True)
     fps_dev = stream_shard.aggregate_fps(B, K, world, r_dev["ms"])
     dev_per_rank = None
     if world > 1:     # the slowest rank sets `value`: keep every rank's own device time visible

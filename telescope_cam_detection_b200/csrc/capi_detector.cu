@@ -32,7 +32,7 @@ extern std::atomic<uint64_t> g_h2d_bytes;
 namespace {
 
 constexpr int kEngines = 8;
-constexpr int kLanes = 4;
+constexpr int kLanes = 8;
 constexpr int kProfileReps = 8;
 
 #define TCD_USE(handle) TCD_CUDA_OK(cudaSetDevice((handle)->device))   /* the current device is per host thread */
