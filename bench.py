@@ -67,6 +67,7 @@ def parse_args():
     ap.add_argument("--slots", type=int, default=0, help="pipeline slots in flight (0 = all the library has: engines x 2 lanes)")
     ap.add_argument("--no-aux", action="store_true", help="skip the motion / crop / RT-DETR side measurements")
     ap.add_argument("--rtdetr-batch", type=int, default=32)
+    ap.add_argument("--classifier-batch", type=int, default=64, help="Stage-2 crops per replay of the side measurement (0 = skip)")
     ap.add_argument("--trace", default=None, help="write the in-kernel timeline of every conv launch here")
     ap.add_argument("--dump-ops", default=None, help="write the per-kernel table of the eager profiling pass here")
     return ap.parse_args()
@@ -468,6 +469,77 @@ def rtdetr_side(local, batch, peaks):
             e.close()
     except Exception as e:  # noqa: BLE001
         res["through_class"] = {"error": repr(e)}
+    return res
+
+
+def classifier_side(local, batch, peaks, model_name="timm/eva02_large_patch14_clip_336.merged2b_ft_inat21"):
+    """BASELINE configs[4], Stage 2: `batch` crops of one 1080p device frame -> patch-row
+    gather -> the shipped configuration's classifier body (EVA02-L/14 at 336, 10 000 classes, random-init weights) ->
+    softmax / top-k.  Graph replays incl. the gather, CUDA events on the program's stream; per-op eager pass."""
+    import torch
+    from oracle import eva02 as oracle_eva02     # seeded weight GENERATOR only; nothing it computes is timed
+    from telescope_cam_detection_b200.eva02_engine import Eva02Engine
+    cfg = oracle_eva02.config_for(model_name, num_classes=10000)
+    sd = oracle_eva02.state_dict_numpy(oracle_eva02.make_model(cfg, 0))
+    eng = Eva02Engine(sd, batch=batch, img_size=cfg.img_size, top_k=5, device=local)
+    del sd
+    frame = torch.from_numpy(synth_frame(900)).cuda(local)
+    rng = np.random.default_rng(5)
+    boxes = []
+    for _ in range(batch):
+        w, h = int(rng.integers(60, 500)), int(rng.integers(60, 500))
+        x, y = int(rng.integers(0, FRAME_W - w)), int(rng.integers(0, FRAME_H - h))
+        boxes.append([x, y, x + w, y + h])
+    boxes = np.asarray(boxes, np.int32)
+    torch.cuda.synchronize()
+    st = torch.cuda.ExternalStream(eng.prog.stream(), device=local)
+
+    def step():
+        eng.crop_patches(frame.data_ptr(), FRAME_H, FRAME_W, frame.stride(0), boxes)
+        eng.run(True)
+    for _ in range(3):
+        step()
+    eng.sync()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    iters = 10
+    e0.record(st)
+    for _ in range(iters):
+        step()
+    e1.record(st)
+    eng.sync()
+    ms = e0.elapsed_time(e1) / iters
+    t0 = time.perf_counter()
+    step()
+    eng.sync()
+    p, i = eng.read_topk(batch)
+    wall = time.perf_counter() - t0
+    prof = eng.prog.profile(2)
+    fl = sum(o["flops"] for o in prof)
+    lin_ms = sum(o["ms"] for o in prof if o["flops"] > 0)
+    mha = [o["ms"] for o in prof if o["name"].endswith(".mha")]
+    attn_fl = 4.0 * eng.T * eng.T * eng.D * batch
+    by_kind = {}
+    for o in prof:
+        k = o["name"].split(".")[-1].split("[")[0] if o["name"].startswith("b") else o["name"].split("[")[0]
+        by_kind[k] = by_kind.get(k, 0.0) + o["ms"]
+    if os.environ.get("TCD_CLASSIFIER_DUMP"):
+        with open(os.environ["TCD_CLASSIFIER_DUMP"], "w") as f:
+            json.dump(prof, f)
+    total_fl = eng.flops_per_crop() * batch
+    res = {"workload": "Stage 2: %d crops of a 1080p device frame -> %s (D %d, %d blocks, %d tokens, %d classes), random-init"
+                       % (batch, model_name, eng.D, eng.depth, eng.T, eng.NC),
+           "crops_per_s": batch / (ms * 1e-3), "ms_per_batch": ms, "ms_per_crop": ms / batch,
+           "wall_ms_incl_topk_d2h": 1e3 * wall, "kernels_per_batch": len(prof) + 1,
+           "gflop_per_crop": eng.flops_per_crop() / 1e9,
+           "tflops": total_fl / (ms * 1e-3) / 1e12, "frac_bf16_burst": total_fl / (ms * 1e-3) / 1e12 / peaks["tf_burst"],
+           "frac_bf16_sustained": total_fl / (ms * 1e-3) / 1e12 / peaks["tf_sustained"],
+           "linears": {"gflop_per_batch": fl / 1e9, "ms_eager": lin_ms, "tflops_eager": fl / (lin_ms * 1e-3) / 1e12,
+                       "frac_bf16_burst": fl / (lin_ms * 1e-3) / 1e12 / peaks["tf_burst"]},
+           "attention": {"ms_per_layer": float(np.mean(mha)), "tflops": attn_fl / (float(np.mean(mha)) * 1e-3) / 1e12,
+                         "path": "mma.sync m16n8k16 (warp-level tensor cores), rotary embedding fused"},
+           "ms_by_op_kind_eager": {k: round(v, 3) for k, v in sorted(by_kind.items(), key=lambda kv: -kv[1])},
+           "top1_prob_mean": float(p[:, 0].mean())}
+    eng.close()
     return res
 
 
@@ -948,6 +1020,12 @@ def run_ours(args):
             rtdetr = rtdetr_side(local, args.rtdetr_batch, peaks)
         except Exception as e:  # noqa: BLE001
             rtdetr = {"error": repr(e)}
+    classifier = None
+    if not args.no_aux and world == 1 and args.classifier_batch > 0:
+        try:
+            classifier = classifier_side(local, args.classifier_batch, peaks)
+        except Exception as e:  # noqa: BLE001
+            classifier = {"error": repr(e)}
     ingest = None
     if not args.no_aux and world == 1:
         try:
@@ -972,7 +1050,7 @@ def run_ours(args):
         "e2e": e2e, "parity_check": parity,
         "latency_ms_p50_sync_batch": float(np.median(lat)) if lat else None, "phases_ms_sync_batch": phases,
         "gpu_launches": int(r_dev["launches"]), "clocks": clocks, "roofline": roofline, "kernels": kernels,
-        "cpu_baseline": cpu, "rtdetr": rtdetr, "ingest": ingest,
+        "cpu_baseline": cpu, "rtdetr": rtdetr, "classifier": classifier, "ingest": ingest,
     }
     emit(json.dumps(line))
     if world > 1:

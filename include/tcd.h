@@ -349,12 +349,30 @@ tcd_status tcd_crop_resize(const uint8_t* frame_dev, int32_t h, int32_t w, int64
                            const tcd_preproc_cfg* cfg, int32_t out_layout, void* out_dev,
                            void* stream);
 
-/* ------------------------------------------------------------------ layer programs (RT-DETR)
+/* Stage-2 crops straight into the classifier body: the same gather as tcd_crop_resize
+ * (src/two_stage_pipeline_yolox.py:289 + src/species_classifier.py:311-350), written as the bf16 PATCH ROWS the
+ * patch-embedding GEMM of a vision transformer reads (what timm's PatchEmbed Conv2d computes inside
+ * `self.model(input_tensor)`, src/species_classifier.py:386-388): rows_dev[(i*G + py)*G + px][c*patch*patch + ky*patch
+ * + kx], G = S / patch, k_pad >= 3*patch*patch columns per row (the caller keeps the padding columns zero).
+ * boxes_host: int32 [n,4], copied into boxes_scratch_dev (device, >= 16*n bytes, caller-owned: nothing is allocated).
+ * Asynchronous on `stream`. */
+tcd_status tcd_crop_patches(const uint8_t* frame_dev, int32_t h, int32_t w, int64_t row_stride,
+                            const int32_t* boxes_host, int32_t* boxes_scratch_dev, int32_t n, int32_t S, int32_t patch,
+                            int32_t k_pad, const tcd_preproc_cfg* cfg, void* rows_dev, void* stream);
+
+/* the same patch rows from an already preprocessed batch (x_dev: f32 NCHW [n,3,S,S], what SpeciesClassifier.preprocess
+ * returns, src/species_classifier.py:298-352); asynchronous on `stream` */
+tcd_status tcd_patchify_f32(const float* x_dev, int32_t n, int32_t S, int32_t patch, int32_t k_pad, void* rows_dev,
+                            void* stream);
+
+/* ------------------------------------------------------------------ layer programs (RT-DETR, Stage-2 classifier)
  * A program is an ordered list of kernels over device buffers it owns, replayed as one CUDA
  * graph.  The host (telescope_cam_detection_b200/rtdetr_engine.py) lays RT-DETRv2-R50 out as
  * such a list -- the replacement of RTDETRDetector.load_model / self.model(img, orig_size),
  * src/rtdetr_detector.py:60-204,257,340 -- from tcgen05 convs / linears plus the transformer
- * kernels of csrc/tfm_kernels.cuh.  Nothing is allocated after the last add_*.             */
+ * kernels of csrc/tfm_kernels.cuh; eva02_engine.py does the same for the Stage-2 classifier body
+ * (timm.create_model(...) / self.model(input_tensor), src/species_classifier.py:258-262,386-388).
+ * Nothing is allocated after the last add_*.                                                  */
 typedef struct tcd_program tcd_program;
 typedef struct {
   char name[64];
@@ -368,7 +386,9 @@ typedef struct {
 enum {
   TCD_OP_LAYERNORM = 1, TCD_OP_ADD_ROWS, TCD_OP_MASK_ROWS, TCD_OP_MHA, TCD_OP_MSDA, TCD_OP_ROWMAX,
   TCD_OP_TOPK, TCD_OP_GATHER, TCD_OP_REF_INIT, TCD_OP_REF_UPDATE, TCD_OP_DETR_POST, TCD_OP_MAXPOOL,
-  TCD_OP_AVGPOOL, TCD_OP_UPSAMPLE
+  TCD_OP_AVGPOOL, TCD_OP_UPSAMPLE,
+  /* Stage-2 classifier body (EVA02 vision transformer) */
+  TCD_OP_VIT_ASSEMBLE, TCD_OP_MHA_ROPE, TCD_OP_SWIGLU_LN, TCD_OP_SOFTMAX, TCD_OP_TAKE
 };
 typedef struct {
   char name[64];

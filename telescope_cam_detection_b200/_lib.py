@@ -56,7 +56,7 @@ class OpDesc(C.Structure):
 
 OP_KINDS = {"layernorm": 1, "add_rows": 2, "mask_rows": 3, "mha": 4, "msda": 5, "rowmax": 6, "topk": 7,
             "gather": 8, "ref_init": 9, "ref_update": 10, "detr_post": 11, "maxpool": 12, "avgpool": 13,
-            "upsample": 14}
+            "upsample": 14, "vit_assemble": 15, "mha_rope": 16, "swiglu_ln": 17, "softmax": 18, "take": 19}
 
 
 class EnhanceCfg(C.Structure):
@@ -162,6 +162,9 @@ SIGNATURES = {
     "tcd_frame_ring_wait": (C.c_int, [_P, C.c_int32, _P]),
     "tcd_crop_resize": (C.c_int, [_P, C.c_int32, C.c_int32, C.c_int64, _I32P, C.c_int32, C.c_int32,
                                   C.POINTER(PreprocCfg), C.c_int32, _P, _P]),
+    "tcd_crop_patches": (C.c_int, [_P, C.c_int32, C.c_int32, C.c_int64, _I32P, _P, C.c_int32, C.c_int32, C.c_int32,
+                                   C.c_int32, C.POINTER(PreprocCfg), _P, _P]),
+    "tcd_patchify_f32": (C.c_int, [_P, C.c_int32, C.c_int32, C.c_int32, C.c_int32, _P, _P]),
     "tcd_program_create": (C.c_int, [C.c_int32, _PP]),
     "tcd_program_destroy": (None, [_P]),
     "tcd_program_alloc": (C.c_int, [_P, C.c_size_t, _PP]),

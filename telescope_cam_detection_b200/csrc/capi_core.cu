@@ -9,6 +9,7 @@
 
 #include "conv_umma.cuh"
 #include "kernels.cuh"
+#include "tfm_kernels.cuh"
 
 namespace tcd {
 
@@ -192,6 +193,30 @@ tcd_status tcd_crop_resize(const uint8_t* frame_dev, int32_t h, int32_t w, int64
     return TCD_ERR_CUDA;
   }
   return (tcd_status)rc;
+}
+
+tcd_status tcd_crop_patches(const uint8_t* frame_dev, int32_t h, int32_t w, int64_t row_stride,
+                            const int32_t* boxes_host, int32_t* boxes_scratch_dev, int32_t n, int32_t S, int32_t patch,
+                            int32_t k_pad, const tcd_preproc_cfg* cfg, void* rows_dev, void* stream) {
+  TCD_REQUIRE(frame_dev && cfg && (n == 0 || (boxes_host && boxes_scratch_dev && rows_dev)), "tcd_crop_patches: null argument");
+  if (n == 0) return TCD_OK;
+  int rc = require_sm100();
+  if (rc) return (tcd_status)rc;
+  for (int i = 0; i < n; ++i) {
+    const int32_t* b = boxes_host + 4 * i;
+    TCD_REQUIRE(b[0] >= 0 && b[1] >= 0 && b[2] <= w && b[3] <= h, "tcd_crop_patches: box %d outside frame", i);
+  }
+  cudaStream_t st = (cudaStream_t)stream;
+  TCD_CUDA_OK(cudaMemcpyAsync(boxes_scratch_dev, boxes_host, sizeof(int) * 4 * n, cudaMemcpyHostToDevice, st));
+  return (tcd_status)crop_patch_launch(frame_dev, row_stride, boxes_scratch_dev, n, S, patch, k_pad, cfg, rows_dev, st);
+}
+
+tcd_status tcd_patchify_f32(const float* x_dev, int32_t n, int32_t S, int32_t patch, int32_t k_pad, void* rows_dev,
+                            void* stream) {
+  TCD_REQUIRE(x_dev && rows_dev && n >= 1, "tcd_patchify_f32: bad argument");
+  int rc = require_sm100();
+  if (rc) return (tcd_status)rc;
+  return (tcd_status)patchify_f32_launch(x_dev, rows_dev, n, S, patch, k_pad, (cudaStream_t)stream);
 }
 
 }  // extern "C"

@@ -75,6 +75,17 @@ int launch_small(const tcd_op_desc& d, cudaStream_t st) {
       return avgpool2x2_launch(p[0], p[1], i[0], i[1], i[2], i[3], st);
     case TCD_OP_UPSAMPLE:  // p: src, dst; i: N, H, W, C, s_ctot, s_coff, d_ctot, d_coff
       return upsample2x_launch(p[0], p[1], i[0], i[1], i[2], i[3], i[4], i[5], i[6], i[7], st);
+    case TCD_OP_VIT_ASSEMBLE:  // p: emb, pos, x; i: N, T, D
+      return vit_assemble_launch(p[0], (const float*)p[1], p[2], i[0], i[1], i[2], st);
+    case TCD_OP_MHA_ROPE:  // p: q, k, v, out, rope; i: ldq,qoff,ldk,koff,ldv,voff,ldo,N,T,heads,prefix; f: scale
+      return mha64_rope_launch(p[0], i[0], i[1], p[1], i[2], i[3], p[2], i[4], i[5], p[3], i[6], i[7], i[8], i[9],
+                               d.f[0], (const float*)p[4], i[10], st);
+    case TCD_OP_SWIGLU_LN:  // p: gu, gamma, beta, y; i: rows, H, Hp; f: eps
+      return swiglu_ln_launch(p[0], (const float*)p[1], (const float*)p[2], p[3], i[0], i[1], i[2], d.f[0], st);
+    case TCD_OP_SOFTMAX:  // p: x, y; i: rows, C, ldx, ldy
+      return softmax_rows_launch((const float*)p[0], i[2], (float*)p[1], i[3], i[0], i[1], st);
+    case TCD_OP_TAKE:  // p: src, idx, out; i: N, k, ld
+      return take_f32_launch((const float*)p[0], i[2], (const int*)p[1], (float*)p[2], i[0], i[1], st);
   }
   set_last_error("program: unknown op kind %d (%s)", d.kind, d.name);
   return TCD_ERR_INVALID;
@@ -192,7 +203,7 @@ tcd_status tcd_program_add_conv(tcd_program* p, const tcd_conv_desc* c) {
 tcd_status tcd_program_add_op(tcd_program* p, const tcd_op_desc* d) {
   TCD_REQUIRE(p && d, "add_op: null argument");
   TCD_REQUIRE(p->graph == nullptr, "add_op: program already captured");
-  TCD_REQUIRE(d->kind >= TCD_OP_LAYERNORM && d->kind <= TCD_OP_UPSAMPLE, "add_op: kind %d", d->kind);
+  TCD_REQUIRE(d->kind >= TCD_OP_LAYERNORM && d->kind <= TCD_OP_TAKE, "add_op: kind %d", d->kind);
   ProgOp op;
   op.name = std::string(d->name, strnlen(d->name, sizeof(d->name)));
   op.kind = d->kind;

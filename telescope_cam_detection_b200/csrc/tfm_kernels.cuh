@@ -52,4 +52,23 @@ int detr_post_launch(const float* logits, const float* ref_sig, const int* idx, 
 // bf16 NHWC pools: 3x3 stride 2 pad 1 max (ResNet stem), 2x2 stride 2 average (ResNet-vd shortcut)
 int maxpool3x3s2_launch(const void* x, void* y, int N, int H, int W, int C, cudaStream_t st);
 int avgpool2x2_launch(const void* x, void* y, int N, int H, int W, int C, cudaStream_t st);
+
+// ---- Stage-2 classifier body (EVA02 vision transformer, vit_kernels.cu; src/species_classifier.py:258-262)
+// rows[(n*G+py)*G+px][c*ps*ps+ky*ps+kx] = x[n][c][py*ps+ky][px*ps+kx], bf16, Kp >= 3*ps*ps columns (pad stays zero)
+int patchify_f32_launch(const float* x, void* rows, int N, int S, int ps, int Kp, cudaStream_t st);
+// the Stage-2 crop gather (crop_resize.cu) writing the same patch rows straight from a u8 BGR frame
+int crop_patch_launch(const uint8_t* frame, long long stride, const int* boxes_dev, int n, int S, int ps, int Kp,
+                      const tcd_preproc_cfg* cfg, void* rows, cudaStream_t st);
+// x[n,0,:] = pos[0,:] (class token already folded in); x[n,1+t,:] = emb[n,t,:] + pos[1+t,:];  pos f32 [T,D]
+int vit_assemble_launch(const void* emb, const float* pos, void* x, int N, int T, int D, cudaStream_t st);
+// softmax(rot(q) rot(k)^T * scale) v, head_dim 64; rope f32 [(T-prefix), 32, 2] (cos, sin) or NULL (no rotation)
+int mha64_rope_launch(const void* q, int ldq, int qoff, const void* k, int ldk, int koff, const void* v, int ldv,
+                      int voff, void* out, int ldo, int N, int T, int heads, float scale, const float* rope,
+                      int prefix, cudaStream_t st);
+// y[r,0:H) = LayerNorm(silu(gu[r,0:H)) * gu[r,Hp:Hp+H)); gu bf16 [rows, 2*Hp], y bf16 [rows, Hp] (pad zero)
+int swiglu_ln_launch(const void* gu, const float* gamma, const float* beta, void* y, int rows, int H, int Hp,
+                     float eps, cudaStream_t st);
+int softmax_rows_launch(const float* x, int ldx, float* y, int ldy, int rows, int C, cudaStream_t st);
+// out[n,i] = src[n*ld + idx[n*k+i]]
+int take_f32_launch(const float* src, int ld, const int* idx, float* out, int N, int k, cudaStream_t st);
 }  // namespace tcd

@@ -5,9 +5,14 @@ What is rebuilt here is what north_star names for Stage 2: the crop -> [N,3,S,S]
 mean/std; reference :298-352) as ONE batched CUDA kernel for all crops of a frame
 (csrc/crop_resize.cu), and the result logic around the network (softmax / top-k / hierarchical
 taxonomy label / geographic whitelist; reference :179-236, :354-474).  The classifier BODY is a
-third-party timm model in the reference (:258-262) and the "next" row N2 of SURVEY.md section 8(f):
-any `torch.nn.Module` mapping [N,3,S,S] float32 -> [N,num_classes] logits can be plugged in
-(`model=` or `model_factory=`); `load_model` builds it with timm only if timm is importable.
+third-party timm model in the reference (:258-262), row N2 of SURVEY.md section 8(f).  For the family
+the shipped configuration selects (`timm/eva02_large_patch14_clip_336...`, config/config.yaml:279-281;
+any `eva02_*` name) `load_model` builds the network as a libtcd layer program (eva02_engine.py:
+tcgen05 linears + hand-written attention / SwiGLU / softmax / top-k kernels) from the checkpoint's
+state dict (`checkpoint_path`, or `weights=` in memory), and `classify_crops` feeds it patch rows
+gathered straight from the frame.  Other timm names have no native body: a caller-supplied
+`torch.nn.Module` (`model=` / `model_factory=`) mapping [N,3,S,S] -> logits is driven as the reference
+drives its model, and without one `load_model` fails loudly (timm is not part of this image).
 """
 import json
 import logging
@@ -25,13 +30,17 @@ class SpeciesClassifier:
                  device: str = "cuda", confidence_threshold: float = 0.3, taxonomy_file: Optional[str] = None,
                  input_size: int = 224, use_hierarchical: bool = True, allowed_species: Optional[List[str]] = None,
                  enable_geographic_filter: bool = False, model: Any = None,
-                 model_factory: Optional[Callable[[int], Any]] = None):
+                 model_factory: Optional[Callable[[int], Any]] = None, weights: Optional[Dict[str, Any]] = None,
+                 max_batch: int = 64):
         self.model_name = model_name
         self.checkpoint_path = checkpoint_path
         self.device = device
         self.confidence_threshold = confidence_threshold
         self.model = model
         self._factory = model_factory
+        self._weights = weights          # in-memory state dict (timm key names) for the native EVA02 body
+        self.max_batch = int(max_batch)  # crops per replay of the native body
+        self.engine = None               # eva02_engine.Eva02Engine once load_model built it
         self.taxonomy: Dict[Any, Any] = {}
         self.use_hierarchical = use_hierarchical
         self.enable_geographic_filter = enable_geographic_filter
@@ -83,7 +92,40 @@ class SpeciesClassifier:
         return None, None
 
     # ------------------------------------------------------------------ model
+    _ENGINE_TOPK = 32   # the program's read-out width; classify(top_k <= 32) slices it
+
+    def _load_native(self, num_classes: int):
+        """EVA02 body as a libtcd layer program (replaces timm.create_model + load_state_dict, reference :258-268)."""
+        from . import eva02_engine
+        sd = self._weights
+        if sd is None:
+            if not self.checkpoint_path:
+                raise RuntimeError("%s: pretrained weights come from the HuggingFace hub in the reference "
+                                   "(pretrained=True); give checkpoint_path= or weights= here" % self.model_name)
+            import torch
+            ck = torch.load(self.checkpoint_path, map_location="cpu")
+            sd = ck["model_state_dict"] if "model_state_dict" in ck else ck
+        sd = {k: (v.detach().cpu().float().numpy() if hasattr(v, "detach") else np.asarray(v, np.float32))
+              for k, v in sd.items()}
+        if sd["head.weight"].shape[0] != num_classes:
+            raise ValueError("checkpoint head has %d classes, load_model asked for %d" % (sd["head.weight"].shape[0], num_classes))
+        dev = str(self.device)
+        idx = int(dev.split(":")[1]) if ":" in dev else 0
+        self.engine = eva02_engine.Eva02Engine(sd, batch=self.max_batch, img_size=int(self.input_size),
+                                               top_k=self._ENGINE_TOPK, device=idx)
+        self.model = self.engine
+        return True
+
     def load_model(self, num_classes: int = 1000, max_retries: int = 3) -> bool:
+        from .eva02_engine import is_eva02
+        if self.engine is not None:
+            return True
+        if self.model is None and self._factory is None and is_eva02(self.model_name):
+            try:
+                return self._load_native(num_classes)
+            except Exception as e:
+                logger.error("Failed to load species classifier: %s", e, exc_info=True)
+                return False
         for attempt in range(max_retries):
             try:
                 import torch
@@ -157,8 +199,27 @@ class SpeciesClassifier:
             out.append({"species": label, "confidence": prob, "class_id": idx, "taxonomic_level": level})
         return out
 
+    def _engine_topk(self, n, top_k):
+        self.engine.run()
+        self.engine.sync()
+        p, i = self.engine.read_topk(n)
+        k = min(top_k, p.shape[1])
+        return p[:, :k], i[:, :k]
+
     def _topk(self, batch, top_k):
         import torch
+        if self.engine is not None:
+            # preprocessed [n,3,S,S] float32 CUDA tensor -> patch rows -> program replay, max_batch crops at a time
+            batch = batch.contiguous().float()
+            torch.cuda.current_stream(batch.device).synchronize()
+            ps, is_ = [], []
+            for s0 in range(0, batch.shape[0], self.max_batch):
+                part = batch[s0:s0 + self.max_batch]
+                self.engine.patchify_device(part.data_ptr(), part.shape[0])
+                p, i = self._engine_topk(part.shape[0], top_k)
+                ps.append(p)
+                is_.append(i)
+            return np.concatenate(ps, 0), np.concatenate(is_, 0)
         with torch.no_grad():
             probs = torch.softmax(self.model(batch), dim=1)
             p, i = torch.topk(probs, min(top_k, probs.shape[1]), dim=1)
@@ -183,6 +244,20 @@ class SpeciesClassifier:
             return [[] for _ in boxes]
         if len(boxes) == 0:
             return []
+        if self.engine is not None:
+            # native body: the gather kernel writes the patch-embedding GEMM's operand directly (no NCHW tensor)
+            import torch
+            t = self._dev_frame(frame)
+            torch.cuda.current_stream(t.device).synchronize()
+            boxes = np.ascontiguousarray(boxes, np.int32).reshape(-1, 4)
+            out = []
+            for s0 in range(0, boxes.shape[0], self.max_batch):
+                part = boxes[s0:s0 + self.max_batch]
+                self.engine.crop_patches(t.data_ptr(), int(t.shape[0]), int(t.shape[1]), t.stride(0), part,
+                                         mean=self.mean, std=self.std)
+                p, i = self._engine_topk(part.shape[0], top_k)
+                out.extend(self._rows_to_results(p[n], i[n]) for n in range(part.shape[0]))
+            return out
         p, i = self._topk(self.crop_batch(frame, boxes), top_k)
         return [self._rows_to_results(p[n], i[n]) for n in range(len(boxes))]
 

@@ -1,0 +1,238 @@
+"""Stage-2 classifier body (src/species_classifier.py:258-262,386-391): the EVA02 layer
+program and its kernels against the fp32 restatement oracle/eva02.py (parity unpinned: timm is absent) and against
+plain torch fp32 for the single kernels.
+
+Tolerances: a kernel is compared on bf16-rounded operands and may differ by one bf16 output rounding (rel 2^-8) plus
+fp32 summation-order noise.  The network runs bf16 storage / fp32 accumulate against an fp32 oracle: class
+probabilities within 1e-2 absolute (north_star's score tolerance), the top-1 class equal wherever the oracle's margin
+exceeds that, logits within the floor the bf16 rounding-point emulation (oracle lowp=True) itself shows x 3.
+"""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+
+def _bf16(t):
+    import torch
+    return t.to(torch.bfloat16).float()
+
+
+def _prog():
+    from telescope_cam_detection_b200.rtdetr_engine import Program
+    return Program(0)
+
+
+def _up_bf16(P, t, shape4):
+    from telescope_cam_detection_b200.rtdetr_engine import Act, to_bf16_bits
+    return Act(P.upload(to_bf16_bits(t.numpy())), *shape4)
+
+
+def _rot(x):
+    import torch
+    return torch.stack([-x[..., 1::2], x[..., ::2]], -1).reshape(x.shape)
+
+
+@pytest.mark.parametrize("N,T,H,rope", [(2, 257, 3, True), (1, 577, 16, True), (3, 65, 5, True), (2, 100, 2, False)])
+def test_mha_rope_matches_torch(N, T, H, rope):
+    import torch
+    from telescope_cam_detection_b200.eva02_engine import rope_cos_sin
+    torch.manual_seed(3)
+    P = _prog()
+    D = 64 * H
+    qkv = _bf16(torch.randn(N, T, 3 * D))
+    QKV = _up_bf16(P, qkv, (N, 1, T, 3 * D))
+    O = P.act(N, 1, T, D)
+    G = int(round((T - 1) ** 0.5))
+    tab = rope_cos_sin(G, 16) if rope else None
+    P.op("mha", "mha_rope", [QKV.ptr, QKV.ptr, QKV.ptr, O.ptr, P.upload(tab) if rope else 0],
+         [3 * D, 0, 3 * D, D, 3 * D, 2 * D, D, N, T, H, 1], [64 ** -0.5])
+    P.run(False); P.sync()
+    q, k, v = [qkv[..., i * D:(i + 1) * D].view(N, T, H, 64).transpose(1, 2) for i in range(3)]
+    if rope:
+        cos = torch.from_numpy(tab[..., 0]).repeat_interleave(2, -1)
+        sin = torch.from_numpy(tab[..., 1]).repeat_interleave(2, -1)
+        q = torch.cat([q[:, :, :1], q[:, :, 1:] * cos + _rot(q[:, :, 1:]) * sin], 2)
+        k = torch.cat([k[:, :, :1], k[:, :, 1:] * cos + _rot(k[:, :, 1:]) * sin], 2)
+    ref = torch.nn.functional.scaled_dot_product_attention(_bf16(q), _bf16(k), v).transpose(1, 2).reshape(N, T, D)
+    got = torch.from_numpy(P.read_bf16(O))[:, 0]
+    assert torch.allclose(got, ref, atol=1.5e-2, rtol=1e-2), float((got - ref).abs().max())
+    P.close()
+
+
+@pytest.mark.parametrize("H", [2730, 512, 853])
+def test_swiglu_layernorm(H):
+    import torch
+    torch.manual_seed(4)
+    P = _prog()
+    rows, Hp = 37, (H + 63) // 64 * 64
+    gu = torch.zeros(rows, 2 * Hp)
+    gu[:, :H] = torch.randn(rows, H) * 2
+    gu[:, Hp:Hp + H] = torch.randn(rows, H)
+    gu[:, H:Hp] = 7.0          # garbage in the padding columns must not leak into the statistics
+    gu = _bf16(gu)
+    g, b = torch.rand(H) + 0.5, torch.randn(H) * 0.1
+    GU = _up_bf16(P, gu, (1, 1, rows, 2 * Hp))
+    Y = P.act(1, 1, rows, Hp)
+    P.op("sw", "swiglu_ln", [GU.ptr, P.upload(g.numpy()), P.upload(b.numpy()), Y.ptr], [rows, H, Hp], [1e-6])
+    P.run(False); P.sync()
+    h = torch.nn.functional.silu(gu[:, :H]) * gu[:, Hp:Hp + H]
+    ref = torch.nn.functional.layer_norm(h, (H,), g, b, 1e-6)
+    got = torch.from_numpy(P.read_bf16(Y))[0, 0]
+    assert torch.allclose(got[:, :H], ref, atol=2e-2, rtol=1e-2), float((got[:, :H] - ref).abs().max())
+    assert float(got[:, H:].abs().max()) == 0.0 if Hp > H else True
+    P.close()
+
+
+def test_token_assembly_softmax_topk():
+    import torch
+    torch.manual_seed(5)
+    P = _prog()
+    N, T, D = 3, 17, 192
+    emb = _bf16(torch.randn(N, T - 1, D))
+    pos = torch.randn(T, D)
+    E = _up_bf16(P, emb, (N, 1, T - 1, D))
+    X = P.act(N, 1, T, D)
+    P.op("tok", "vit_assemble", [E.ptr, P.upload(pos.numpy()), X.ptr], [N, T, D])
+    C, ld, k = 1000, 1024, 7
+    logits = torch.randn(N, ld) * 3
+    lg = P.upload(logits.numpy())
+    probs, idx, top = P.f32(N * C), P.alloc(N * k * 4), P.f32(N * k)
+    P.op("sm", "softmax", [lg, probs], [N, C, ld, C])
+    P.op("tk", "topk", [probs, idx], [N, C, k])
+    P.op("take", "take", [probs, idx, top], [N, k, C])
+    P.run(False); P.sync()
+    ref = torch.cat([pos[:1].expand(N, 1, D), emb + pos[1:]], 1)
+    got = torch.from_numpy(P.read_bf16(X))[:, 0]
+    assert torch.allclose(got, ref, atol=2e-2, rtol=1e-2)
+    pr = torch.softmax(logits[:, :C], 1)
+    gp = torch.from_numpy(P.d2h(probs, (N, C), np.float32))
+    assert torch.allclose(gp, pr, atol=1e-6, rtol=1e-5)
+    tp, ti = torch.topk(gp, k, 1)   # the read-out must be the top-k of the probabilities the device holds
+    assert np.array_equal(P.d2h(idx, (N, k), np.int32), ti.numpy().astype(np.int32))
+    assert np.array_equal(P.d2h(top, (N, k), np.float32), tp.numpy())
+    P.close()
+
+
+def test_crop_patches_equal_crop_resize_rows():
+    """tcd_crop_patches == tcd_crop_resize (the tested Stage-2 gather) re-laid out as patch rows and rounded to bf16."""
+    import torch
+    from telescope_cam_detection_b200 import engine
+    from telescope_cam_detection_b200.rtdetr_engine import to_bf16_bits
+    from telescope_cam_detection_b200.eva02_engine import Eva02Engine
+    from oracle import eva02
+    from util import noise_frame
+    cfg = eva02.Eva02Config(img_size=112, embed_dim=64, depth=1, num_heads=1, num_classes=40)
+    eng = Eva02Engine(eva02.state_dict_numpy(eva02.make_model(cfg, 0)), batch=4, img_size=112, top_k=5)
+    frame = torch.from_numpy(noise_frame(2, 480, 640)).cuda()
+    boxes = np.array([[10, 20, 200, 300], [0, 0, 640, 480], [300, 100, 412, 212], [5, 5, 45, 60]], np.int32)
+    n = eng.crop_patches(frame.data_ptr(), 480, 640, frame.stride(0), boxes)
+    eng.sync()
+    rows = eng.prog.d2h(eng.rows0.ptr, (4, 64, eng.Kp), np.uint16)
+    ref = torch.empty((4, 3, 112, 112), dtype=torch.float32, device="cuda")
+    engine.crop_resize(frame.data_ptr(), 480, 640, frame.stride(0), boxes, 112, ref.data_ptr(), layout=0)
+    torch.cuda.synchronize()
+    r = ref.cpu().view(4, 3, 8, 14, 8, 14).permute(0, 2, 4, 1, 3, 5).reshape(4, 64, 588).numpy()
+    want = to_bf16_bits(r)
+    # same arithmetic in two kernels: equal up to an fp32 contraction difference that flips a bf16 rounding
+    assert n == 4 and (rows[:, :, :588] != want).mean() < 1e-3
+    back = (rows[:, :, :588].astype(np.uint32) << 16).view(np.float32)
+    assert np.allclose(back, r, atol=1e-2, rtol=8e-3)
+    assert not rows[:, :, 588:].any()
+    # the f32 patchify entry is a pure re-layout + rounding of the NCHW tensor: exact
+    eng.patchify_device(ref.data_ptr(), 4)
+    eng.sync()
+    assert np.array_equal(eng.prog.d2h(eng.rows0.ptr, (4, 64, eng.Kp), np.uint16)[:, :, :588], want)
+    eng.close()
+
+
+def _compare(cfg, batch, n, seed=0, fused=True, tap_tol=0.06):
+    import torch
+    from telescope_cam_detection_b200.eva02_engine import Eva02Engine
+    from oracle import eva02
+    cfg.qkv_fused = fused
+    model = eva02.make_model(cfg, seed)
+    lowp = eva02.make_model(cfg, seed, lowp=True)
+    x = eva02.synthetic_input(cfg, n, seed=seed + 1)
+    taps = {}
+    with torch.no_grad():
+        ref = model(x, taps)
+        floor = float((lowp(x) - ref).abs().max())
+    eng = Eva02Engine(eva02.state_dict_numpy(model), batch=batch, img_size=cfg.img_size, top_k=5, keep_taps=True)
+    got = torch.from_numpy(eng.forward(x.numpy()))
+    # residual stream after every block: relative to the stream's own scale
+    for name in ["tokens"] + ["block%d" % i for i in range(cfg.depth)]:
+        t = torch.from_numpy(eng.read_tap(name))[:n]
+        err = float((t - taps[name]).abs().max() / taps[name].abs().max())
+        assert err <= tap_tol, (name, err)
+    d = float((got - ref).abs().max())
+    assert d <= max(3 * floor, 0.05), (d, floor)
+    pr, pg = torch.softmax(ref, 1), torch.softmax(got, 1)
+    assert float((pr - pg).abs().max()) <= 1e-2
+    top2 = torch.topk(pr, 2, 1).values
+    sure = (top2[:, 0] - top2[:, 1]) > 2e-2
+    assert bool((pr.argmax(1)[sure] == pg.argmax(1)[sure]).all())
+    p, i = eng.read_topk(n)
+    dev_probs = eng.read_probs(n)
+    assert np.allclose(dev_probs, pg.numpy(), atol=1e-6, rtol=1e-4)
+    tp, ti = torch.topk(torch.from_numpy(dev_probs), 5, 1)
+    assert np.array_equal(i, ti.numpy().astype(np.int32)) and np.array_equal(p, tp.numpy())
+    # the captured graph replays to the same bits as the eager pass
+    again = eng.forward(x.numpy(), graph=True)
+    eager = eng.forward(x.numpy(), graph=False)
+    assert np.array_equal(again, eager)
+    eng.close()
+    return d, floor
+
+
+def test_eva02_small_config_vs_oracle():
+    from oracle import eva02
+    _compare(eva02.Eva02Config(img_size=224, embed_dim=192, depth=4, num_heads=3, num_classes=1000), batch=5, n=5)
+
+
+def test_eva02_padded_hidden_separate_qkv_partial_batch():
+    """hidden = int(320 * 8 / 3) = 853 (padded to 896), separate q/k/v projections, 3 crops in an engine built for 4."""
+    from oracle import eva02
+    _compare(eva02.Eva02Config(img_size=112, embed_dim=320, depth=3, num_heads=5, num_classes=333), batch=4, n=3,
+             seed=2, fused=False)
+
+
+def test_eva02_large_shapes_one_block():
+    """The shipped model's layer shapes (D 1024, 16 heads, hidden 2730, 577 tokens, 10 000 classes), one block deep."""
+    from oracle import eva02
+    _compare(eva02.Eva02Config(img_size=336, embed_dim=1024, depth=1, num_heads=16, num_classes=10000), batch=2, n=2,
+             seed=3)
+
+
+def test_species_classifier_native_body():
+    """SpeciesClassifier('timm/eva02_...') builds the native body; classify_crops (gather -> patch rows) agrees with
+    classify on the sliced crop (preprocess -> NCHW -> patchify) and with the oracle on the reference's tensor."""
+    import torch
+    from telescope_cam_detection_b200.species_classifier import SpeciesClassifier
+    from oracle import eva02
+    from util import structured_frame
+    cfg = eva02.Eva02Config(img_size=224, embed_dim=192, depth=2, num_heads=3, num_classes=500)
+    model = eva02.make_model(cfg, 5, logit_std=4.0)
+    clf = SpeciesClassifier(model_name="timm/eva02_tiny_patch14_224.mim_in22k", input_size=224, use_hierarchical=False,
+                            confidence_threshold=0.0, weights=model.state_dict(), max_batch=3)
+    assert clf.load_model(num_classes=500) and clf.engine is not None
+    frame = structured_frame(4, 480, 640)
+    boxes = [(10, 20, 200, 300), (0, 0, 640, 480), (300, 100, 524, 324), (50, 60, 120, 200)]   # 4 crops > max_batch 3
+    res = clf.classify_crops(frame, boxes, top_k=5)
+    assert len(res) == 4
+    for (x1, y1, x2, y2), r in zip(boxes, res):
+        single = clf.classify(np.ascontiguousarray(frame[y1:y2, x1:x2]), top_k=5)
+        assert single[0]["class_id"] == r[0]["class_id"] and len(single) == len(r)
+        assert np.allclose([d["confidence"] for d in single], [d["confidence"] for d in r], atol=2e-3)
+        with torch.no_grad():
+            pr = torch.softmax(model(clf.preprocess(np.ascontiguousarray(frame[y1:y2, x1:x2])).cpu()), 1)[0]
+        for d in r:
+            assert abs(d["confidence"] - float(pr[d["class_id"]])) <= 1e-2
+            assert d["species"] == "species_%d" % d["class_id"]
+        if float(pr.max()) - float(torch.topk(pr, 2).values[1]) > 2e-2 and r:
+            assert r[0]["class_id"] == int(pr.argmax())
+    batch = clf.classify_batch([np.ascontiguousarray(frame[y1:y2, x1:x2]) for x1, y1, x2, y2 in boxes], top_k=3)
+    assert [[d["class_id"] for d in b] for b in batch] == [[d["class_id"] for d in r[:3]] for r in res]
+    assert clf.load_model(num_classes=500)          # idempotent
+    wrong = SpeciesClassifier(model_name="timm/eva02_tiny_patch14_224", input_size=224, weights=model.state_dict())
+    assert not wrong.load_model(num_classes=1000)   # head size mismatch fails loudly, like load_state_dict would

@@ -1,0 +1,100 @@
+"""CPU checks of the Stage-2 classifier oracle (oracle/eva02.py, parity unpinned: timm absent) and of the host side of
+the native body (eva02_engine.py tables / column splits, SpeciesClassifier.load_model's failure behaviour)."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import eva02
+
+
+def test_rope_table_is_a_rotation_by_position_times_band():
+    """Independent statement: channel pair j of a patch at (row y, col x) turns by angle pos * 1/10000^(j' / 16), pos =
+    y * 16/G for j < 16 and x * 16/G for j >= 16 (j' = j mod 16) -- checked through complex multiplication."""
+    G, hd = 24, 64
+    sin, cos = eva02.rope_table(G, 16, hd)
+    x = torch.randn(G * G, hd)
+    got = x * cos + eva02._rot(x) * sin
+    z = torch.view_as_complex(x.reshape(G * G, hd // 2, 2).contiguous())
+    j = torch.arange(hd // 2)
+    band = 1.0 / (10000.0 ** ((j % 16).float() / 16))
+    ys, xs = torch.meshgrid(torch.arange(G), torch.arange(G), indexing="ij")
+    pos = torch.where(j[None] < 16, ys.reshape(-1, 1).float(), xs.reshape(-1, 1).float()) * (16.0 / G)
+    ref = torch.view_as_real(z * torch.polar(torch.ones_like(pos), pos * band[None])).reshape(G * G, hd)
+    assert torch.allclose(got, ref, atol=1e-4)
+
+
+def test_engine_rope_table_equals_oracle():
+    from telescope_cam_detection_b200.eva02_engine import rope_cos_sin
+    for G in (8, 16, 24):
+        sin, cos = eva02.rope_table(G, 16, 64)
+        t = rope_cos_sin(G, 16)
+        assert t.shape == (G * G, 32, 2)
+        assert np.abs(t[..., 0] - cos.numpy()[:, ::2]).max() < 1e-6 and np.abs(t[..., 1] - sin.numpy()[:, ::2]).max() < 1e-6
+        assert np.array_equal(cos.numpy()[:, ::2], cos.numpy()[:, 1::2])
+
+
+def test_shipped_model_configuration():
+    cfg = eva02.config_for("timm/eva02_large_patch14_clip_336.merged2b_ft_inat21")
+    assert (cfg.embed_dim, cfg.depth, cfg.num_heads, cfg.img_size, cfg.hidden, cfg.grid) == (1024, 24, 16, 336, 2730, 24)
+    with torch.device("meta"):
+        n = sum(p.numel() for p in eva02.Eva02(cfg).parameters())
+    assert 300e6 < n < 320e6      # ViT-L/14 trunk (~304 M) + 10 000-class head
+    with pytest.raises(ValueError):
+        eva02.config_for("tf_efficientnet_b4_ns")
+
+
+def test_state_dict_uses_timm_key_names():
+    cfg = eva02.Eva02Config(img_size=112, embed_dim=64, depth=1, num_heads=1, num_classes=10)
+    keys = set(eva02.make_model(cfg).state_dict())
+    for k in ("patch_embed.proj.weight", "cls_token", "pos_embed", "blocks.0.norm1.weight", "blocks.0.attn.qkv.weight",
+              "blocks.0.attn.q_bias", "blocks.0.attn.v_bias", "blocks.0.attn.norm.weight", "blocks.0.attn.proj.bias",
+              "blocks.0.mlp.fc1_g.weight", "blocks.0.mlp.fc1_x.bias", "blocks.0.mlp.norm.weight", "blocks.0.mlp.fc2.weight",
+              "norm.weight", "head.bias"):
+        assert k in keys, k
+    assert not any("rope" in k for k in keys)      # the rotary tables are non-persistent buffers
+
+
+def test_fused_and_separate_qkv_agree():
+    cfg = eva02.Eva02Config(img_size=112, embed_dim=128, depth=2, num_heads=2, num_classes=50)
+    a = eva02.make_model(cfg, 1)
+    cfg2 = eva02.Eva02Config(img_size=112, embed_dim=128, depth=2, num_heads=2, num_classes=50, qkv_fused=False)
+    b = eva02.Eva02(cfg2).eval()
+    sd = dict(a.state_dict())
+    for i in range(cfg.depth):
+        p = "blocks.%d.attn." % i
+        w = sd.pop(p + "qkv.weight")
+        sd[p + "q_proj.weight"], sd[p + "k_proj.weight"], sd[p + "v_proj.weight"] = w[:128], w[128:256], w[256:]
+        sd[p + "q_proj.bias"], sd[p + "v_proj.bias"] = sd.pop(p + "q_bias"), sd.pop(p + "v_bias")
+    b.load_state_dict(sd)
+    x = eva02.synthetic_input(cfg, 2)
+    with torch.no_grad():
+        assert torch.allclose(a(x), b(x), atol=1e-5)
+
+
+def test_lowp_emulation_stays_near_fp32():
+    cfg = eva02.Eva02Config(img_size=112, embed_dim=128, depth=3, num_heads=2, num_classes=100)
+    x = eva02.synthetic_input(cfg, 3)
+    with torch.no_grad():
+        a, b = eva02.make_model(cfg, 0)(x), eva02.make_model(cfg, 0, lowp=True)(x)
+    assert float((a.softmax(1) - b.softmax(1)).abs().max()) < 1e-2
+
+
+def test_column_splits_respect_the_engine_limits():
+    from telescope_cam_detection_b200.eva02_engine import _chunks
+    for cout, step in ((5504, 128), (3072, 128), (1024, 128), (576, 32), (1792, 128), (4096, 128)):
+        parts = _chunks(cout, step)
+        assert parts[0][0] == 0 and sum(w for _, w in parts) == cout
+        assert all(w <= 2048 and w % step == 0 for _, w in parts)
+        assert all(parts[i][0] + parts[i][1] == parts[i + 1][0] for i in range(len(parts) - 1))
+
+
+def test_species_classifier_fails_loudly_without_a_body():
+    from telescope_cam_detection_b200.species_classifier import SpeciesClassifier
+    # EVA02 name, no checkpoint: the reference would download from the hub; here load_model reports failure
+    assert SpeciesClassifier(model_name="timm/eva02_large_patch14_clip_336.merged2b_ft_inat21", input_size=336).load_model(10000) is False
+    # any other timm name without timm installed and without a caller-supplied module: failure, not a silent stand-in
+    assert SpeciesClassifier(model_name="tf_efficientnet_b4_ns").load_model(1000, max_retries=1) is False
+    if not torch.cuda.is_available():
+        cfg = eva02.Eva02Config(img_size=112, embed_dim=64, depth=1, num_heads=1, num_classes=10)
+        clf = SpeciesClassifier(model_name="eva02_tiny_patch14_224", input_size=112, weights=eva02.make_model(cfg).state_dict())
+        assert clf.load_model(10) is False and clf.engine is None     # no sm_100 device: no CPU fallback
