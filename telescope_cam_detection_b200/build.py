@@ -17,7 +17,7 @@ OBJ = os.path.join(HERE, "build")
 # TUs whose fp32 arithmetic must round exactly like the scalar reference code (no FMA contraction)
 NO_FMAD = {"postproc.cu", "motion.cu", "enhance.cu", "noalloc.cu"}
 SOURCES = ["capi_core.cu", "capi_detector.cu", "capi_motion.cu", "capi_ingest.cu", "capi_enhance.cu", "enhance.cu", "capi_jpeg.cu", "jpeg.cu", "noalloc.cu", "conv_umma.cu", "yolox_net.cu", "program.cu",
-           "tfm_kernels.cu", "tfm_kernels2.cu", "vit_kernels.cu", "pil_resize.cu",
+           "tfm_kernels.cu", "tfm_kernels2.cu", "vit_kernels.cu", "fa_umma.cu", "pil_resize.cu",
            "yolox_plan.cu", "preproc.cu", "postproc.cu", "motion.cu", "crop_resize.cu"]
 ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
 COMMON = ["-O3", "-std=c++17", "-lineinfo", "-Xcompiler", "-fPIC", "-Xptxas", "-v"]

@@ -345,6 +345,8 @@ mha64_rope_kernel(const __nv_bfloat16* __restrict__ q, int ldq, int qoff, const 
 int mha64_rope_launch(const void* q, int ldq, int qoff, const void* k, int ldk, int koff, const void* v, int ldv,
                       int voff, void* out, int ldo, int N, int T, int heads, float scale, const float* rope,
                       int prefix, cudaStream_t st) {
+  if (fa64_umma_eligible(T))
+    return fa64_umma_launch(q, ldq, qoff, k, ldk, koff, v, ldv, voff, out, ldo, N, T, heads, scale, rope, prefix, st);
   const int Tkp = (T + 15) & ~15;
   const size_t smem = ((size_t)Tkp * kMha64KStride + (size_t)64 * (Tkp + 8)) * 2;
   TCD_REQUIRE(smem <= 220 * 1024, "mha64: %d tokens do not fit shared memory", T);
@@ -363,7 +365,7 @@ int mha64_rope_launch(const void* q, int ldq, int qoff, const void* k, int ldk, 
 }
 
 // ------------------------------------------------------------------ SwiGLU + LayerNorm
-// y[r, 0:H) = LayerNorm_H(silu(g[r,:]) * u[r,:]) * gamma + beta, columns [H, Hp) written as zeros.  g and u are the
+// y[r, 0:H) = LayerNorm_H(silu(g[r,:]) * u[r,:]) * gamma + beta, columns [H, Hp) written as zeros (gamma / beta hold Hp floats).  g and u are the
 // two halves of one fused fc1 output row: gu[r] = [g (Hp) | u (Hp)].  Two rows per CTA, 128 threads per row, up to
 // three 8-channel chunks per thread held in registers between the statistics and the normalisation.
 constexpr int kSwigluChunks = 3;   // Hp <= 3 * 128 * 8 = 3072
@@ -421,11 +423,13 @@ swiglu_ln_kernel(const uint4* __restrict__ gu, const float* __restrict__ gamma, 
     const int c = t + 128 * i;
     if (c < Hp8) {
       float o[8];
+      // gamma / beta are padded to Hp by the caller: two 16-byte loads each instead of eight scalar ones
+      const float4 g0 = *reinterpret_cast<const float4*>(gamma + c * 8), g1 = *reinterpret_cast<const float4*>(gamma + c * 8 + 4);
+      const float4 b0 = *reinterpret_cast<const float4*>(beta + c * 8), b1 = *reinterpret_cast<const float4*>(beta + c * 8 + 4);
+      const float gg[8] = {g0.x, g0.y, g0.z, g0.w, g1.x, g1.y, g1.z, g1.w};
+      const float bb[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
 #pragma unroll
-      for (int e = 0; e < 8; ++e) {
-        const int col = c * 8 + e;
-        o[e] = col < H ? (hv[i][e] - mean) * rstd * gamma[col] + beta[col] : 0.f;
-      }
+      for (int e = 0; e < 8; ++e) o[e] = (c * 8 + e < H) ? (hv[i][e] - mean) * rstd * gg[e] + bb[e] : 0.f;
       y[(size_t)row * Hp8 + c] = v_f32_to_bf16x8(o);
     }
   }

@@ -193,9 +193,9 @@ class Eva02Engine:
             self._linear(n + "fc1", yb, w1, b1, gu)
             if not self._has(p + "mlp.norm.weight"):
                 raise KeyError("EVA02 weights: %smlp.norm.* missing (scale_mlp = False variants are not supported)" % p)
-            P.op(n + "swiglu_ln", "swiglu_ln",
-                 [gu.ptr, P.upload(self._g(p + "mlp.norm.weight")), P.upload(self._g(p + "mlp.norm.bias")), hb.ptr],
-                 [rows, H, Hp], [self.ln_eps])
+            ng, nb = np.zeros(Hp, np.float32), np.zeros(Hp, np.float32)
+            ng[:H], nb[:H] = self._g(p + "mlp.norm.weight"), self._g(p + "mlp.norm.bias")
+            P.op(n + "swiglu_ln", "swiglu_ln", [gu.ptr, P.upload(ng), P.upload(nb), hb.ptr], [rows, H, Hp], [self.ln_eps])
             w2 = np.zeros((D, Hp), np.float32)
             w2[:, :H] = self._g(p + "mlp.fc2.weight")
             self._linear(n + "fc2", hb, w2, self._g(p + "mlp.fc2.bias"), x, resid=x2)

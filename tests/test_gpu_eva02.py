@@ -74,7 +74,9 @@ def test_swiglu_layernorm(H):
     g, b = torch.rand(H) + 0.5, torch.randn(H) * 0.1
     GU = _up_bf16(P, gu, (1, 1, rows, 2 * Hp))
     Y = P.act(1, 1, rows, Hp)
-    P.op("sw", "swiglu_ln", [GU.ptr, P.upload(g.numpy()), P.upload(b.numpy()), Y.ptr], [rows, H, Hp], [1e-6])
+    gp, bp = np.zeros(Hp, np.float32), np.zeros(Hp, np.float32)
+    gp[:H], bp[:H] = g.numpy(), b.numpy()
+    P.op("sw", "swiglu_ln", [GU.ptr, P.upload(gp), P.upload(bp), Y.ptr], [rows, H, Hp], [1e-6])
     P.run(False); P.sync()
     h = torch.nn.functional.silu(gu[:, :H]) * gu[:, Hp:Hp + H]
     ref = torch.nn.functional.layer_norm(h, (H,), g, b, 1e-6)
