@@ -354,6 +354,12 @@ int conv_plan_build(const ConvDesc& d, ConvPlan* plan) {
       }
     }
   }
+  // GEMM-shaped layers (1x1, long K, many tiles, whole-SM plans: the token linears of the layer programs): these are
+  // bound by L2 -> SM operand delivery (64 FLOP per byte for a 128 x 128 x 64 stage), and a 128 x 256 tile reads A
+  // once for twice the columns (87 FLOP per byte).  Its two accumulators fill the 512 TMEM columns: one CTA per SM.
+  if (mode == 0 && d.groups == 1 && share == 0 && d.k == 1 && d.cin >= 512 && d.cout % 256 == 0 &&
+      (long)m_tiles * (d.cout / 256) >= n_sm && env_int("TCD_CONV_BN256", 1, 0))
+    BN = 256;
   if (d.groups > 1) {   // one N tile per group: the tile index selects the group's input channels
     BN = d.cout / d.groups;
     TCD_REQUIRE(mode == 0 && BN % 32 == 0 && BN <= bn_cap && (BN & (BN - 1)) == 0,

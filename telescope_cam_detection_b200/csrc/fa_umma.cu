@@ -122,27 +122,38 @@ fa64_umma_kernel(const __nv_bfloat16* __restrict__ q, int ldq, int qoff, const _
     const __nv_bfloat16* kb = k + (size_t)n * T * ldk + koff + h * 64;
     const __nv_bfloat16* vb = v + (size_t)n * T * ldv + voff + h * 64;
     const int total = kv_rows * 8;
-    // four chunks per thread per round: eight independent 16-byte loads in flight (the loop is latency-bound otherwise)
-    for (int i0 = threadIdx.x; i0 < total; i0 += 4 * kFaThreads) {
-      uint4 kq[4], vq[4];
+    // six chunks per thread per round, K / V data and the rotation table loads all issued before the first use
+    // (twelve 16-byte loads + twelve table loads in flight: the loop is latency-bound otherwise)
+    for (int i0 = threadIdx.x; i0 < total; i0 += 6 * kFaThreads) {
+      uint4 kq[6], vq[6];
+      float4 c01[6], c23[6];
 #pragma unroll
-      for (int u = 0; u < 4; ++u) {
+      for (int u = 0; u < 6; ++u) {
         const int i = i0 + u * kFaThreads;
         const int t = i >> 3, c = i & 7;
         kq[u] = make_uint4(0u, 0u, 0u, 0u);
         vq[u] = kq[u];
+        c01[u] = make_float4(1.f, 0.f, 1.f, 0.f);
+        c23[u] = c01[u];
         if (i < total && t < T) {
           kq[u] = *reinterpret_cast<const uint4*>(kb + (size_t)t * ldk + c * 8);
           vq[u] = *reinterpret_cast<const uint4*>(vb + (size_t)t * ldv + c * 8);
+          if (rope != nullptr && t >= prefix) {
+            const float4* cs = reinterpret_cast<const float4*>(rope + (size_t)(t - prefix) * 32 + c * 4);
+            c01[u] = cs[0];
+            c23[u] = cs[1];
+          }
         }
       }
 #pragma unroll
-      for (int u = 0; u < 4; ++u) {
+      for (int u = 0; u < 6; ++u) {
         const int i = i0 + u * kFaThreads;
         if (i < total) {
-          const int t = i >> 3, c = i & 7;
-          if (t < T) fa_rope_chunk(kq[u], rope, t, c, prefix);
-          const uint32_t off = fa_swz(t, c);
+          kq[u].x = fa_rope_pair(kq[u].x, c01[u].x, c01[u].y);
+          kq[u].y = fa_rope_pair(kq[u].y, c01[u].z, c01[u].w);
+          kq[u].z = fa_rope_pair(kq[u].z, c23[u].x, c23[u].y);
+          kq[u].w = fa_rope_pair(kq[u].w, c23[u].z, c23[u].w);
+          const uint32_t off = fa_swz(i >> 3, i & 7);
           *reinterpret_cast<uint4*>(Ksm + off) = kq[u];
           *reinterpret_cast<uint4*>(Vsm + off) = vq[u];
         }
@@ -153,14 +164,34 @@ fa64_umma_kernel(const __nv_bfloat16* __restrict__ q, int ldq, int qoff, const _
     // the CTA's FIRST query tile goes in with the K / V rows (warp 9 alone needs ~16 000 cycles for a tile: fine one
     // tile ahead of the softmax warps, not in front of the first scores)
     const __nv_bfloat16* qb = q + (size_t)n * T * ldq + qoff + h * 64;
-    for (int i = threadIdx.x; i < kFaTile * 8; i += kFaThreads) {
-      const int rr = i >> 3, c = i & 7, tok = (int)blockIdx.x * kFaTile + rr;
-      uint4 qq = make_uint4(0u, 0u, 0u, 0u);
-      if (tok < T) {
-        qq = *reinterpret_cast<const uint4*>(qb + (size_t)tok * ldq + c * 8);
-        fa_rope_chunk(qq, rope, tok, c, prefix);
+    uint4 qq[3];
+    float4 c01[3], c23[3];
+#pragma unroll
+    for (int u = 0; u < 3; ++u) {
+      const int i = threadIdx.x + u * kFaThreads;
+      const int tok = (int)blockIdx.x * kFaTile + (i >> 3), c = i & 7;
+      qq[u] = make_uint4(0u, 0u, 0u, 0u);
+      c01[u] = make_float4(1.f, 0.f, 1.f, 0.f);
+      c23[u] = c01[u];
+      if (i < kFaTile * 8 && tok < T) {
+        qq[u] = *reinterpret_cast<const uint4*>(qb + (size_t)tok * ldq + c * 8);
+        if (rope != nullptr && tok >= prefix) {
+          const float4* cs = reinterpret_cast<const float4*>(rope + (size_t)(tok - prefix) * 32 + c * 4);
+          c01[u] = cs[0];
+          c23[u] = cs[1];
+        }
       }
-      *reinterpret_cast<uint4*>(Qsm + fa_swz(rr, c)) = qq;
+    }
+#pragma unroll
+    for (int u = 0; u < 3; ++u) {
+      const int i = threadIdx.x + u * kFaThreads;
+      if (i < kFaTile * 8) {
+        qq[u].x = fa_rope_pair(qq[u].x, c01[u].x, c01[u].y);
+        qq[u].y = fa_rope_pair(qq[u].y, c01[u].z, c01[u].w);
+        qq[u].z = fa_rope_pair(qq[u].z, c23[u].x, c23[u].y);
+        qq[u].w = fa_rope_pair(qq[u].w, c23[u].z, c23[u].w);
+        *reinterpret_cast<uint4*>(Qsm + fa_swz(i >> 3, i & 7)) = qq[u];
+      }
     }
   }
   fence_proxy_async_smem();
@@ -301,8 +332,15 @@ fa64_umma_kernel(const __nv_bfloat16* __restrict__ q, int ldq, int qoff, const _
         tmem_ld32(s_addr + 32, sb);
         tmem_ld_wait();
         if (warp == 0) FA_STAMP(0, s, 2);
+        if (n_valid < 64) {           // warp-uniform, last key tile only: masked keys score -inf (exp2 -> exactly 0)
+#pragma unroll
+          for (int i = 0; i < 32; ++i) {
+            if (i >= n_valid) sa[i] = 0xff800000u;
+            if (32 + i >= n_valid) sb[i] = 0xff800000u;
+          }
+        }
         float mx;
-        if (n_valid >= 64) {          // warp-uniform: every tile but the last has no masked key
+        {
           float m0 = fmaxf(__uint_as_float(sa[0]), __uint_as_float(sb[0])), m1 = fmaxf(__uint_as_float(sa[1]), __uint_as_float(sb[1]));
           float m2 = fmaxf(__uint_as_float(sa[2]), __uint_as_float(sb[2])), m3 = fmaxf(__uint_as_float(sa[3]), __uint_as_float(sb[3]));
 #pragma unroll
@@ -313,13 +351,6 @@ fa64_umma_kernel(const __nv_bfloat16* __restrict__ q, int ldq, int qoff, const _
             m3 = fmaxf(m3, fmaxf(__uint_as_float(sa[i + 3]), __uint_as_float(sb[i + 3])));
           }
           mx = fmaxf(fmaxf(m0, m1), fmaxf(m2, m3));
-        } else {
-          mx = -INFINITY;
-#pragma unroll
-          for (int i = 0; i < 32; ++i) {
-            if (i < n_valid) mx = fmaxf(mx, __uint_as_float(sa[i]));
-            if (32 + i < n_valid) mx = fmaxf(mx, __uint_as_float(sb[i]));
-          }
         }
         xch[b][r][half] = mx;
         fa_pair_sync(1 + quad);      // also: the partner has its scores in registers -- P may overwrite them now
@@ -330,42 +361,27 @@ fa64_umma_kernel(const __nv_bfloat16* __restrict__ q, int ldq, int qoff, const _
         // P_j: this half's 64 keys, bf16 pairs, into 32 columns of the score buffer itself (columns half*32 ..)
         const uint32_t p_addr = lane_base + b * 128u + (uint32_t)half * 32u;
         float sum;
-        if (n_valid >= 64) {
+        {
           float s0 = 0.f, s1 = 0.f;
 #pragma unroll
           for (int hh = 0; hh < 2; ++hh) {
             uint32_t pk[16];
+            if (hh * 32 < n_valid) {          // warp-uniform: 32 masked keys cost no exponentials
 #pragma unroll
-            for (int e = 0; e < 16; ++e) {
-              const float p0 = ex2_approx(fmaf(__uint_as_float(hh == 0 ? sa[e * 2] : sb[e * 2]), scale_log2, -m_new));
-              const float p1 = ex2_approx(fmaf(__uint_as_float(hh == 0 ? sa[e * 2 + 1] : sb[e * 2 + 1]), scale_log2, -m_new));
-              s0 += p0;
-              s1 += p1;
-              pk[e] = pack_bf16x2(p0, p1);
+              for (int e = 0; e < 16; ++e) {
+                const float p0 = ex2_approx(fmaf(__uint_as_float(hh == 0 ? sa[e * 2] : sb[e * 2]), scale_log2, -m_new));
+                const float p1 = ex2_approx(fmaf(__uint_as_float(hh == 0 ? sa[e * 2 + 1] : sb[e * 2 + 1]), scale_log2, -m_new));
+                s0 += p0;
+                s1 += p1;
+                pk[e] = pack_bf16x2(p0, p1);
+              }
+            } else {
+#pragma unroll
+              for (int e = 0; e < 16; ++e) pk[e] = 0u;
             }
             tmem_st16(p_addr + hh * 16, pk);
           }
           sum = s0 + s1;
-        } else {
-          sum = 0.f;
-#pragma unroll
-          for (int hh = 0; hh < 2; ++hh) {
-            uint32_t pk[16];
-#pragma unroll
-            for (int e = 0; e < 16; ++e) {
-              const int i = hh * 32 + e * 2;
-              const float v0 = __uint_as_float(hh == 0 ? sa[e * 2] : sb[e * 2]);
-              const float v1 = __uint_as_float(hh == 0 ? sa[e * 2 + 1] : sb[e * 2 + 1]);
-              float p0 = 0.f, p1 = 0.f;
-              if (hh * 32 < n_valid) {        // warp-uniform: 32 masked keys cost no exponentials
-                p0 = i < n_valid ? ex2_approx(fmaf(v0, scale_log2, -m_new)) : 0.f;
-                p1 = i + 1 < n_valid ? ex2_approx(fmaf(v1, scale_log2, -m_new)) : 0.f;
-              }
-              sum += p0 + p1;
-              pk[e] = pack_bf16x2(p0, p1);
-            }
-            tmem_st16(p_addr + hh * 16, pk);
-          }
         }
         l = fmaf(l, corr, sum);
         if (warp == 0) FA_STAMP(0, s, 4);

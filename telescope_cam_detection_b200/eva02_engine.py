@@ -118,12 +118,12 @@ class Eva02Engine:
         P.op("tap." + name, "gather", [act.ptr, self._tap_idx, keep.ptr], [1, rows, rows, act.C])
         self.taps[name] = keep
 
-    def _linear(self, name, x, w, b, y, resid=None, step=128):
+    def _linear(self, name, x, w, b, y, resid=None, step=256):
         """y[:, :cout] = x @ w.T + b (+ resid), split along cout so that each launch stays within the engine's bias
         staging limit.  x, y, resid: flat token views [1,1,rows,C]."""
         cout = w.shape[0]
         if cout % step:
-            step = 32
+            step = 128 if cout % 128 == 0 else 32
         for c0, cw in _chunks(cout, step):
             self.prog.conv(name if cout == cw else "%s[%d:%d]" % (name, c0, c0 + cw), x, w[c0:c0 + cw], b[c0:c0 + cw],
                            act=ACT_NONE, y=y, y_coff=c0, resid=resid, r_coff=c0 if resid is not None else 0)
@@ -139,7 +139,7 @@ class Eva02Engine:
         P, B, T, D, NP = self.prog, self.B, self.T, self.D, self.P
         rows = B * T
         H = int(self._g("blocks.0.mlp.fc1_g.weight").shape[0])
-        Hp = (H + 63) // 64 * 64
+        Hp = (H + 127) // 128 * 128        # 2 * Hp is a multiple of 256: the fused fc1 splits into 128 x 256 GEMM tiles
         self.hidden, self.hidden_pad = H, Hp
         # inputs: a preprocessed f32 batch (forward) or patch rows written by tcd_crop_patches (product path)
         self.in_f32 = P.f32(B * 3 * self.S * self.S)

@@ -65,7 +65,7 @@ def test_swiglu_layernorm(H):
     import torch
     torch.manual_seed(4)
     P = _prog()
-    rows, Hp = 37, (H + 63) // 64 * 64
+    rows, Hp = 37, (H + 127) // 128 * 128
     gu = torch.zeros(rows, 2 * Hp)
     gu[:, :H] = torch.randn(rows, H) * 2
     gu[:, Hp:Hp + H] = torch.randn(rows, H)

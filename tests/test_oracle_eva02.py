@@ -81,7 +81,7 @@ def test_lowp_emulation_stays_near_fp32():
 
 def test_column_splits_respect_the_engine_limits():
     from telescope_cam_detection_b200.eva02_engine import _chunks
-    for cout, step in ((5504, 128), (3072, 128), (1024, 128), (576, 32), (1792, 128), (4096, 128)):
+    for cout, step in ((5632, 256), (3072, 256), (1024, 256), (576, 32), (1792, 128), (4096, 256)):
         parts = _chunks(cout, step)
         assert parts[0][0] == 0 and sum(w for _, w in parts) == cout
         assert all(w <= 2048 and w % step == 0 for _, w in parts)
