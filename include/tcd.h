@@ -388,7 +388,7 @@ enum {
   TCD_OP_TOPK, TCD_OP_GATHER, TCD_OP_REF_INIT, TCD_OP_REF_UPDATE, TCD_OP_DETR_POST, TCD_OP_MAXPOOL,
   TCD_OP_AVGPOOL, TCD_OP_UPSAMPLE,
   /* Stage-2 classifier body (EVA02 vision transformer) */
-  TCD_OP_VIT_ASSEMBLE, TCD_OP_MHA_ROPE, TCD_OP_SWIGLU_LN, TCD_OP_SOFTMAX, TCD_OP_TAKE
+  TCD_OP_VIT_ASSEMBLE, TCD_OP_MHA_ROPE, TCD_OP_SWIGLU_LN, TCD_OP_SOFTMAX, TCD_OP_TAKE, TCD_OP_HEAD_GEMV
 };
 typedef struct {
   char name[64];

@@ -56,7 +56,7 @@ class OpDesc(C.Structure):
 
 OP_KINDS = {"layernorm": 1, "add_rows": 2, "mask_rows": 3, "mha": 4, "msda": 5, "rowmax": 6, "topk": 7,
             "gather": 8, "ref_init": 9, "ref_update": 10, "detr_post": 11, "maxpool": 12, "avgpool": 13,
-            "upsample": 14, "vit_assemble": 15, "mha_rope": 16, "swiglu_ln": 17, "softmax": 18, "take": 19}
+            "upsample": 14, "vit_assemble": 15, "mha_rope": 16, "swiglu_ln": 17, "softmax": 18, "take": 19, "head_gemv": 20}
 
 
 class EnhanceCfg(C.Structure):

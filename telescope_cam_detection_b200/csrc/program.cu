@@ -84,6 +84,8 @@ int launch_small(const tcd_op_desc& d, cudaStream_t st) {
       return swiglu_ln_launch(p[0], (const float*)p[1], (const float*)p[2], p[3], i[0], i[1], i[2], d.f[0], st);
     case TCD_OP_SOFTMAX:  // p: x, y; i: rows, C, ldx, ldy
       return softmax_rows_launch((const float*)p[0], i[2], (float*)p[1], i[3], i[0], i[1], st);
+    case TCD_OP_HEAD_GEMV:  // p: x, w, bias, out; i: B, K, NC, ld
+      return head_gemv_launch(p[0], p[1], (const float*)p[2], (float*)p[3], i[0], i[1], i[2], i[3], st);
     case TCD_OP_TAKE:  // p: src, idx, out; i: N, k, ld
       return take_f32_launch((const float*)p[0], i[2], (const int*)p[1], (float*)p[2], i[0], i[1], st);
   }
@@ -203,7 +205,7 @@ tcd_status tcd_program_add_conv(tcd_program* p, const tcd_conv_desc* c) {
 tcd_status tcd_program_add_op(tcd_program* p, const tcd_op_desc* d) {
   TCD_REQUIRE(p && d, "add_op: null argument");
   TCD_REQUIRE(p->graph == nullptr, "add_op: program already captured");
-  TCD_REQUIRE(d->kind >= TCD_OP_LAYERNORM && d->kind <= TCD_OP_TAKE, "add_op: kind %d", d->kind);
+  TCD_REQUIRE(d->kind >= TCD_OP_LAYERNORM && d->kind <= TCD_OP_HEAD_GEMV, "add_op: kind %d", d->kind);
   ProgOp op;
   op.name = std::string(d->name, strnlen(d->name, sizeof(d->name)));
   op.kind = d->kind;

@@ -389,7 +389,7 @@ swiglu_ln_kernel(const uint4* __restrict__ gu, const float* __restrict__ gamma, 
       v_bf16x8_to_f32(gu[(size_t)row * 2 * Hp8 + Hp8 + c], uf);
 #pragma unroll
       for (int e = 0; e < 8; ++e) {
-        const float s = gf[e] / (1.f + __expf(-gf[e]));
+        const float s = silu_f(gf[e]);     // h + h tanh(h), h = g / 2: one MUFU op, no division
         hv[i][e] = (c * 8 + e < H) ? s * uf[e] : 0.f;
         sum += hv[i][e];
       }
@@ -439,6 +439,80 @@ int swiglu_ln_launch(const void* gu, const float* gamma, const float* beta, void
   TCD_REQUIRE(Hp % 8 == 0 && H <= Hp && Hp <= kSwigluChunks * 128 * 8 && H >= 1, "swiglu_ln: H %d Hp %d", H, Hp);
   swiglu_ln_kernel<<<cdiv(rows, 2), 256, 0, st>>>((const uint4*)gu, gamma, beta, (uint4*)y, rows, H, Hp / 8, eps);
   VIT_LAUNCH_OK("swiglu_ln");
+}
+
+// ------------------------------------------------------------------ classifier head: few rows x many classes
+// out[b, c] = sum_k x[b, k] * w[c, k] + bias[c]   (x bf16 [B, K], w bf16 [NC, K], fp32 accumulate, f32 logits).
+// With B = 64 class tokens and 10 000 classes this is a weight-streaming problem (20 MB of weights, 1.3 GFLOP): the
+// conv engine's f32-row mode did it as forty 256-column launches of ONE CTA each (35 us apiece, 1.4 ms).  Here a
+// CTA owns 64 classes (8 per warp) and a tile of 32 rows of x in shared memory; a lane owns a slice of k, keeps the
+// weight slice of the current class in registers, and the 32 per-row partial sums of a warp are combined by a
+// reduce-scatter butterfly (31 shuffles; lane r ends up with row r).
+constexpr int kHeadRows = 32, kHeadMaxK = 1024;
+__global__ void __launch_bounds__(256)
+head_gemv_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ w, const float* __restrict__ bias,
+                 float* __restrict__ out, int B, int K, int NC, int ld) {
+  extern __shared__ __align__(16) uint8_t head_sm[];
+  uint4* xs = reinterpret_cast<uint4*>(head_sm);            // [32 rows][K / 8] uint4
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int K8 = K >> 3;
+  for (int b0 = 0; b0 < B; b0 += kHeadRows) {
+    __syncthreads();
+    for (int i = threadIdx.x; i < kHeadRows * K8; i += 256) {
+      const int rr = i / K8, c8 = i - rr * K8;
+      xs[i] = (b0 + rr < B) ? reinterpret_cast<const uint4*>(x + (size_t)(b0 + rr) * K)[c8] : make_uint4(0u, 0u, 0u, 0u);
+    }
+    __syncthreads();
+    for (int ci = 0; ci < 8; ++ci) {
+      const int c = blockIdx.x * 64 + warp * 8 + ci;
+      if (c >= NC) break;                                    // warp-uniform
+      float wf[4][8];
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const int k8 = lane + 32 * i;
+        uint4 q = make_uint4(0u, 0u, 0u, 0u);
+        if (k8 < K8) q = reinterpret_cast<const uint4*>(w + (size_t)c * K)[k8];
+        v_bf16x8_to_f32(q, wf[i]);
+      }
+      float part[kHeadRows];
+#pragma unroll
+      for (int rr = 0; rr < kHeadRows; ++rr) {
+        float acc = 0.f;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          const int k8 = lane + 32 * i;
+          if (k8 < K8) {
+            float xf[8];
+            v_bf16x8_to_f32(xs[rr * K8 + k8], xf);
+#pragma unroll
+            for (int e = 0; e < 8; ++e) acc = fmaf(xf[e], wf[i][e], acc);
+          }
+        }
+        part[rr] = acc;
+      }
+      // reduce-scatter over the warp: after the step with offset `off`, a lane keeps the half of its rows that
+      // matches its own bit `off`; lane r finishes with the full sum of row r in part[0]
+#pragma unroll
+      for (int off = 16; off >= 1; off >>= 1) {
+        const bool up = (lane & off) != 0;
+#pragma unroll
+        for (int i = 0; i < off; ++i) {
+          const float send = up ? part[i] : part[i + off];
+          const float keep = up ? part[i + off] : part[i];
+          part[i] = keep + __shfl_xor_sync(0xffffffffu, send, off);
+        }
+      }
+      if (b0 + lane < B) out[(size_t)(b0 + lane) * ld + c] = part[0] + bias[c];
+    }
+  }
+}
+int head_gemv_launch(const void* x, const void* w, const float* bias, float* out, int B, int K, int NC, int ld,
+                     cudaStream_t st) {
+  TCD_REQUIRE(K % 8 == 0 && K >= 8 && K <= kHeadMaxK && B >= 1 && NC >= 1 && ld >= NC, "head_gemv: B %d K %d NC %d", B, K, NC);
+  const size_t smem = (size_t)kHeadRows * K * 2;
+  if (int rc = ensure_dyn_smem((const void*)head_gemv_kernel, smem)) return rc;
+  head_gemv_kernel<<<cdiv(NC, 64), 256, smem, st>>>((const __nv_bfloat16*)x, (const __nv_bfloat16*)w, bias, out, B, K, NC, ld);
+  VIT_LAUNCH_OK("head_gemv");
 }
 
 // ------------------------------------------------------------------ softmax over f32 rows, top-k read-out

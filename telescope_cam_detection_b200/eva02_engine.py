@@ -23,7 +23,7 @@ import numpy as np
 
 from . import _lib
 from ._lib import check
-from .rtdetr_engine import ACT_NONE, Act, Program
+from .rtdetr_engine import ACT_NONE, Act, Program, to_bf16_bits
 
 # registered EVA02 sizes (timm/models/eva.py): embed_dim -> heads (head_dim is 64 in all of them)
 _HEAD_DIM = 64
@@ -209,17 +209,22 @@ class Eva02Engine:
         self.ld_logits = (self.NC + _HEAD_CHUNK - 1) // _HEAD_CHUNK * _HEAD_CHUNK
         self.logits = P.f32(B * self.ld_logits)
         hw, hbias = self._g("head.weight"), self._g("head.bias")
-        for c0 in range(0, self.NC, _HEAD_CHUNK):
-            cw = min(_HEAD_CHUNK, self.NC - c0)
-            d = _lib.ConvDesc()
-            d.name = ("head[%d:%d]" % (c0, c0 + cw)).encode()
-            d.x, d.N, d.H, d.W, d.x_ctot, d.x_coff, d.cin, d.x_nstride = clsn.ptr, 1, 1, B, D, 0, D, 0
-            w = np.ascontiguousarray(hw[c0:c0 + cw]).reshape(cw, D, 1, 1)
-            b = np.ascontiguousarray(hbias[c0:c0 + cw])
-            d.w_host, d.bias_host = w.ctypes.data, b.ctypes.data
-            d.cout, d.k, d.stride, d.act = cw, 1, 1, ACT_NONE
-            d.out_f32, d.out_ld, d.out_col, d.rows_per_img, d.row_off = self.logits, self.ld_logits, c0, B, 0
-            check(self.lib.tcd_program_add_conv(P.handle, C.byref(d)), "tcd_program_add_conv(head)")
+        if D <= 1024:
+            # few rows x many classes: a weight-streaming kernel (csrc/vit_kernels.cu head_gemv), one launch
+            P.op("head", "head_gemv", [clsn.ptr, P.upload(to_bf16_bits(hw)), P.upload(hbias), self.logits],
+                 [B, D, self.NC, self.ld_logits])
+        else:
+            for c0 in range(0, self.NC, _HEAD_CHUNK):     # f32-row mode of the conv engine, 256 columns per launch
+                cw = min(_HEAD_CHUNK, self.NC - c0)
+                d = _lib.ConvDesc()
+                d.name = ("head[%d:%d]" % (c0, c0 + cw)).encode()
+                d.x, d.N, d.H, d.W, d.x_ctot, d.x_coff, d.cin, d.x_nstride = clsn.ptr, 1, 1, B, D, 0, D, 0
+                w = np.ascontiguousarray(hw[c0:c0 + cw]).reshape(cw, D, 1, 1)
+                b = np.ascontiguousarray(hbias[c0:c0 + cw])
+                d.w_host, d.bias_host = w.ctypes.data, b.ctypes.data
+                d.cout, d.k, d.stride, d.act = cw, 1, 1, ACT_NONE
+                d.out_f32, d.out_ld, d.out_col, d.rows_per_img, d.row_off = self.logits, self.ld_logits, c0, B, 0
+                check(self.lib.tcd_program_add_conv(P.handle, C.byref(d)), "tcd_program_add_conv(head)")
         self.probs = P.f32(B * self.NC)
         P.op("softmax", "softmax", [self.logits, self.probs], [B, self.NC, self.ld_logits, self.NC])
         self.top_idx = P.alloc(B * self.top_k * 4)

@@ -116,6 +116,25 @@ def test_token_assembly_softmax_topk():
     P.close()
 
 
+@pytest.mark.parametrize("B,K,NC", [(64, 1024, 10000), (5, 192, 1000), (33, 320, 77)])
+def test_head_gemv(B, K, NC):
+    import torch
+    from telescope_cam_detection_b200.rtdetr_engine import to_bf16_bits
+    torch.manual_seed(6)
+    P = _prog()
+    x, w, b = _bf16(torch.randn(B, K)), _bf16(torch.randn(NC, K) * 0.1), torch.randn(NC)
+    ld = NC + 24
+    out = P.f32(B * ld)
+    P.op("head", "head_gemv", [P.upload(to_bf16_bits(x.numpy())), P.upload(to_bf16_bits(w.numpy())), P.upload(b.numpy()), out],
+         [B, K, NC, ld])
+    P.run(False); P.sync()
+    got = torch.from_numpy(P.d2h(out, (B, ld), np.float32))
+    ref = x.double() @ w.double().T + b.double()
+    assert torch.allclose(got[:, :NC].double(), ref, atol=2e-4, rtol=1e-5), float((got[:, :NC].double() - ref).abs().max())
+    assert float(got[:, NC:].abs().max()) == 0.0     # nothing written beyond the classes
+    P.close()
+
+
 def test_crop_patches_equal_crop_resize_rows():
     """tcd_crop_patches == tcd_crop_resize (the tested Stage-2 gather) re-laid out as patch rows and rounded to bf16."""
     import torch
