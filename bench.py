@@ -536,7 +536,8 @@ def classifier_side(local, batch, peaks, model_name="timm/eva02_large_patch14_cl
            "linears": {"gflop_per_batch": fl / 1e9, "ms_eager": lin_ms, "tflops_eager": fl / (lin_ms * 1e-3) / 1e12,
                        "frac_bf16_burst": fl / (lin_ms * 1e-3) / 1e12 / peaks["tf_burst"]},
            "attention": {"ms_per_layer": float(np.mean(mha)), "tflops": attn_fl / (float(np.mean(mha)) * 1e-3) / 1e12,
-                         "path": "mma.sync m16n8k16 (warp-level tensor cores), rotary embedding fused"},
+                         "path": "tcgen05: S = Q K^T and O = P V as UMMA (P read from tensor memory, V MN-major), rotary embedding fused"
+                                 if os.environ.get("TCD_MHA_UMMA", "1") != "0" else "mma.sync m16n8k16 (warp-level), rotary embedding fused"},
            "ms_by_op_kind_eager": {k: round(v, 3) for k, v in sorted(by_kind.items(), key=lambda kv: -kv[1])},
            "top1_prob_mean": float(p[:, 0].mean())}
     eng.close()

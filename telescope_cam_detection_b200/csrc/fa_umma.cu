@@ -87,7 +87,7 @@ __device__ __forceinline__ void fa_rope_chunk(uint4& q, const float2* rope, int 
 __global__ void __launch_bounds__(kFaThreads, 1)
 fa64_umma_kernel(const __nv_bfloat16* __restrict__ q, int ldq, int qoff, const __nv_bfloat16* __restrict__ k, int ldk,
                  int koff, const __nv_bfloat16* __restrict__ v, int ldv, int voff, __nv_bfloat16* __restrict__ out, int ldo,
-                 int T, float scale_log2, const float2* __restrict__ rope, int prefix, int n_tiles, int n_last, int trace) {
+                 int T, float scale_log2, const float2* __restrict__ rope, int prefix, int n_tiles, int n_last, int hd8, int trace) {
   extern __shared__ uint8_t fa_raw[];
   __shared__ uint32_t tr[2][8][8];   // TCD_FA_TRACE=1: clock stamps of CTA (0,0,0), first query tile (printed at exit)
   const bool tracing = trace != 0 && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0;
@@ -119,8 +119,9 @@ fa64_umma_kernel(const __nv_bfloat16* __restrict__ q, int ldq, int qoff, const _
   if (warp == 8) tmem_alloc(&tmem_base_s, 512u);
   {
     // K (rotated) and V of this (image, head): rows >= T are zeros (a masked key must contribute exactly 0 * 0)
-    const __nv_bfloat16* kb = k + (size_t)n * T * ldk + koff + h * 64;
-    const __nv_bfloat16* vb = v + (size_t)n * T * ldv + voff + h * 64;
+    const int hd = hd8 * 8;   // 64, or 32 with channels 32..63 of every staged row zero (the MMAs always run 64 wide)
+    const __nv_bfloat16* kb = k + (size_t)n * T * ldk + koff + h * hd;
+    const __nv_bfloat16* vb = v + (size_t)n * T * ldv + voff + h * hd;
     const int total = kv_rows * 8;
     // six chunks per thread per round, K / V data and the rotation table loads all issued before the first use
     // (twelve 16-byte loads + twelve table loads in flight: the loop is latency-bound otherwise)
@@ -135,7 +136,7 @@ fa64_umma_kernel(const __nv_bfloat16* __restrict__ q, int ldq, int qoff, const _
         vq[u] = kq[u];
         c01[u] = make_float4(1.f, 0.f, 1.f, 0.f);
         c23[u] = c01[u];
-        if (i < total && t < T) {
+        if (i < total && t < T && c < hd8) {
           kq[u] = *reinterpret_cast<const uint4*>(kb + (size_t)t * ldk + c * 8);
           vq[u] = *reinterpret_cast<const uint4*>(vb + (size_t)t * ldv + c * 8);
           if (rope != nullptr && t >= prefix) {
@@ -163,7 +164,7 @@ fa64_umma_kernel(const __nv_bfloat16* __restrict__ q, int ldq, int qoff, const _
   {
     // the CTA's FIRST query tile goes in with the K / V rows (warp 9 alone needs ~16 000 cycles for a tile: fine one
     // tile ahead of the softmax warps, not in front of the first scores)
-    const __nv_bfloat16* qb = q + (size_t)n * T * ldq + qoff + h * 64;
+    const __nv_bfloat16* qb = q + (size_t)n * T * ldq + qoff + h * (hd8 * 8);
     uint4 qq[3];
     float4 c01[3], c23[3];
 #pragma unroll
@@ -173,7 +174,7 @@ fa64_umma_kernel(const __nv_bfloat16* __restrict__ q, int ldq, int qoff, const _
       qq[u] = make_uint4(0u, 0u, 0u, 0u);
       c01[u] = make_float4(1.f, 0.f, 1.f, 0.f);
       c23[u] = c01[u];
-      if (i < kFaTile * 8 && tok < T) {
+      if (i < kFaTile * 8 && tok < T && c < hd8) {
         qq[u] = *reinterpret_cast<const uint4*>(qb + (size_t)tok * ldq + c * 8);
         if (rope != nullptr && tok >= prefix) {
           const float4* cs = reinterpret_cast<const float4*>(rope + (size_t)(tok - prefix) * 32 + c * 4);
@@ -207,7 +208,7 @@ fa64_umma_kernel(const __nv_bfloat16* __restrict__ q, int ldq, int qoff, const _
     // 96 threads, two rounds of up to six 16-byte chunks each with the rotation table loads issued beside the data
     // loads (one warp with dependent table loads needed 23 000 cycles per tile -- twice what the softmax warps
     // need to consume one).
-    const __nv_bfloat16* qb = q + (size_t)n * T * ldq + qoff + h * 64;
+    const __nv_bfloat16* qb = q + (size_t)n * T * ldq + qoff + h * (hd8 * 8);
     const int st = threadIdx.x - 9 * 32;
     int qi = 1;
     for (int qt = blockIdx.x + gridDim.x; qt < n_qt; qt += gridDim.x, ++qi) {   // tile 0 was staged with K / V
@@ -225,7 +226,7 @@ fa64_umma_kernel(const __nv_bfloat16* __restrict__ q, int ldq, int qoff, const _
           qq[u] = make_uint4(0u, 0u, 0u, 0u);
           c01[u] = make_float4(1.f, 0.f, 1.f, 0.f);
           c23[u] = c01[u];
-          if (i < kFaTile * 8 && tok < T) {
+          if (i < kFaTile * 8 && tok < T && c < hd8) {
             qq[u] = *reinterpret_cast<const uint4*>(qb + (size_t)tok * ldq + c * 8);
             if (rope != nullptr && tok >= prefix) {
               const float4* cs = reinterpret_cast<const float4*>(rope + (size_t)(tok - prefix) * 32 + c * 4);
@@ -415,8 +416,8 @@ fa64_umma_kernel(const __nv_bfloat16* __restrict__ q, int ldq, int qoff, const _
         xsum[r][half] = l;
         fa_pair_sync(1 + quad);       // (the next write of xsum is a whole query tile, i.e. many pair barriers, away)
         const float inv = 1.0f / (l + xsum[r][half ^ 1]);
-        if (tok < T) {
-          __nv_bfloat16* orow = out + ((size_t)n * T + tok) * ldo + h * 64 + half * 32;
+        if (tok < T && half * 4 < hd8) {
+          __nv_bfloat16* orow = out + ((size_t)n * T + tok) * ldo + h * (hd8 * 8) + half * 32;
           uint32_t w[16];
 #pragma unroll
           for (int i = 0; i < 32; i += 2)
@@ -455,8 +456,9 @@ static const bool g_fa_trace = [] {
 bool fa64_umma_eligible(int T) { return g_fa_enabled && T >= 1 && T <= kFaMaxTiles * kFaTile; }
 
 int fa64_umma_launch(const void* q, int ldq, int qoff, const void* k, int ldk, int koff, const void* v, int ldv, int voff,
-                     void* out, int ldo, int N, int T, int heads, float scale, const float* rope, int prefix,
+                     void* out, int ldo, int N, int T, int heads, int head_dim, float scale, const float* rope, int prefix,
                      cudaStream_t st) {
+  TCD_REQUIRE(head_dim == 64 || (head_dim == 32 && rope == nullptr), "fa64: head_dim %d unsupported", head_dim);
   const int n_tiles = (T + kFaTile - 1) / kFaTile;
   TCD_REQUIRE(n_tiles >= 1 && n_tiles <= kFaMaxTiles, "fa64: %d tokens unsupported", T);
   TCD_REQUIRE(ldq % 8 == 0 && ldk % 8 == 0 && ldv % 8 == 0 && ldo % 8 == 0 && qoff % 8 == 0 && koff % 8 == 0 &&
@@ -471,7 +473,7 @@ int fa64_umma_launch(const void* q, int ldq, int qoff, const void* k, int ldk, i
   if (gx > n_tiles) gx = n_tiles;
   fa64_umma_kernel<<<dim3(gx, heads, N), kFaThreads, smem, st>>>(
       (const __nv_bfloat16*)q, ldq, qoff, (const __nv_bfloat16*)k, ldk, koff, (const __nv_bfloat16*)v, ldv, voff,
-      (__nv_bfloat16*)out, ldo, T, scale * 1.4426950408889634f, (const float2*)rope, prefix, n_tiles, n_last, g_fa_trace ? 1 : 0);
+      (__nv_bfloat16*)out, ldo, T, scale * 1.4426950408889634f, (const float2*)rope, prefix, n_tiles, n_last, head_dim / 8, g_fa_trace ? 1 : 0);
   g_launch_count.fetch_add(1, std::memory_order_relaxed);
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) {

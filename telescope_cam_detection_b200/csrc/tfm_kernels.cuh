@@ -67,9 +67,10 @@ int mha64_rope_launch(const void* q, int ldq, int qoff, const void* k, int ldk, 
                       int prefix, cudaStream_t st);
 // the same attention on tcgen05 / TMEM (fa_umma.cu) for T <= 640 tokens; mha64_rope_launch takes it when eligible
 bool fa64_umma_eligible(int T);
+// head_dim 64, or 32 (rows zero-padded to 64 channels in shared memory; rope must be NULL)
 int fa64_umma_launch(const void* q, int ldq, int qoff, const void* k, int ldk, int koff, const void* v, int ldv,
-                     int voff, void* out, int ldo, int N, int T, int heads, float scale, const float* rope,
-                     int prefix, cudaStream_t st);
+                     int voff, void* out, int ldo, int N, int T, int heads, int head_dim, float scale,
+                     const float* rope, int prefix, cudaStream_t st);
 // y[r,0:H) = LayerNorm(silu(gu[r,0:H)) * gu[r,Hp:Hp+H)); gu bf16 [rows, 2*Hp], y bf16 [rows, Hp] (pad zero);
 // gamma / beta: Hp floats each (16-byte aligned, padding ignored)
 int swiglu_ln_launch(const void* gu, const float* gamma, const float* beta, void* y, int rows, int H, int Hp,

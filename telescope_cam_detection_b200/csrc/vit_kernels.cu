@@ -346,7 +346,7 @@ int mha64_rope_launch(const void* q, int ldq, int qoff, const void* k, int ldk, 
                       int voff, void* out, int ldo, int N, int T, int heads, float scale, const float* rope,
                       int prefix, cudaStream_t st) {
   if (fa64_umma_eligible(T))
-    return fa64_umma_launch(q, ldq, qoff, k, ldk, koff, v, ldv, voff, out, ldo, N, T, heads, scale, rope, prefix, st);
+    return fa64_umma_launch(q, ldq, qoff, k, ldk, koff, v, ldv, voff, out, ldo, N, T, heads, 64, scale, rope, prefix, st);
   const int Tkp = (T + 15) & ~15;
   const size_t smem = ((size_t)Tkp * kMha64KStride + (size_t)64 * (Tkp + 8)) * 2;
   TCD_REQUIRE(smem <= 220 * 1024, "mha64: %d tokens do not fit shared memory", T);
