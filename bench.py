@@ -482,7 +482,6 @@ def classifier_side(local, batch, peaks, model_name="timm/eva02_large_patch14_cl
     cfg = oracle_eva02.config_for(model_name, num_classes=10000)
     sd = oracle_eva02.state_dict_numpy(oracle_eva02.make_model(cfg, 0))
     eng = Eva02Engine(sd, batch=batch, img_size=cfg.img_size, top_k=5, device=local)
-    del sd
     frame = torch.from_numpy(synth_frame(900)).cuda(local)
     rng = np.random.default_rng(5)
     boxes = []
@@ -541,6 +540,43 @@ def classifier_side(local, batch, peaks, model_name="timm/eva02_large_patch14_cl
            "ms_by_op_kind_eager": {k: round(v, 3) for k, v in sorted(by_kind.items(), key=lambda kv: -kv[1])},
            "top1_prob_mean": float(p[:, 0].mean())}
     eng.close()
+    # BASELINE configs[4] through the reference's classes: TwoStageDetectionPipeline.process_detections(frame, dets) with a
+    # SpeciesClassifier built from the same weights (src/two_stage_pipeline_yolox.py:203-451: crop geometry with 30 %
+    # padding as the shipped config sets it, batched gather, classifier, softmax / top-k, taxonomy + result dicts)
+    try:
+        from telescope_cam_detection_b200.species_classifier import SpeciesClassifier
+        from telescope_cam_detection_b200.two_stage_pipeline_yolox import TwoStageDetectionPipeline
+        clf = SpeciesClassifier(model_name=model_name, input_size=cfg.img_size, confidence_threshold=0.0, use_hierarchical=False,
+                                weights=sd, max_batch=batch, device="cuda:%d" % local)
+        del sd
+        if not clf.load_model(num_classes=10000):
+            raise RuntimeError("SpeciesClassifier.load_model failed")
+        pipe = TwoStageDetectionPipeline(enable_species_classification=True, device="cuda:%d" % local,
+                                         crop_padding_percent=30, min_crop_size=40)
+        for cat in ("bird", "mammal", "reptile"):
+            pipe.add_species_classifier(cat, clf)
+        # one category for every box: a replay of the layer program always computes `batch` crop slots, so the detections
+        # of a frame should reach the classifier as ONE batch (a second category would replay the program again)
+        cls_ids = [k for k, v in pipe.class_id_to_category.items() if v == "mammal"] or [15]
+
+        def dets():
+            return [{"class_id": cls_ids[i % len(cls_ids)], "class_name": "animal", "confidence": 0.9,
+                     "bbox": {"x1": float(b[0]), "y1": float(b[1]), "x2": float(b[2]), "y2": float(b[3]),
+                              "area": int((b[2] - b[0]) * (b[3] - b[1]))}} for i, b in enumerate(boxes)]
+        out = pipe.process_detections(frame, dets())
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        n_it = 3
+        for _ in range(n_it):
+            out = pipe.process_detections(frame, dets())
+        dt = (time.perf_counter() - t0) / n_it
+        res["through_class"] = {"crops_per_s": batch / dt, "ms_per_frame_of_%d_detections" % batch: 1e3 * dt,
+                                "classified": sum(1 for d in out if d.get("species")),
+                                "path": "TwoStageDetectionPipeline.process_detections(device frame, %d detection dicts) -> "
+                                        "dicts with species fields (wall clock)" % batch}
+        clf.engine.close()
+    except Exception as e:  # noqa: BLE001
+        res["through_class"] = {"error": repr(e)}
     return res
 
 
