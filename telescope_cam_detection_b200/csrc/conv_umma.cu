@@ -3,6 +3,7 @@
 #define TCD_CONV_KERNEL_IMPL
 #include "conv_umma.cuh"
 #include "conv_pair.cuh"
+#include "gemm_pair.cuh"
 
 #include <atomic>
 #include <algorithm>
@@ -250,6 +251,107 @@ static int pair_plan_launch(const ConvPlan& plan, cudaStream_t stream) {
   return TCD_OK;
 }
 
+// ---------------------------------------------------------------- CTA-pair GEMM plan (gemm_pair.cuh)
+//   TCD_GEMM_PAIR=0 disables it (A/B measurements)
+using GemmPairKernelFn = void (*)(const ConvMaps, const GemmPairArgs);
+static GemmPairKernelFn gemm_pair_kernel_variant(int act) {
+  static const GemmPairKernelFn tbl[4] = {gemm_pair_kernel<0>, gemm_pair_kernel<1>, gemm_pair_kernel<2>, gemm_pair_kernel<3>};
+  return tbl[act & 3];
+}
+
+static bool gemm_pair_eligible(const ConvDesc& d, int mode) {
+  if (!env_int("TCD_GEMM_PAIR", 1, 0)) return false;
+  if (mode != 0 || d.k != 1 || d.stride != 1 || d.groups != 1) return false;
+  if (d.N != 1 || d.H != 1 || d.x_nstride || d.y_nstride || d.r_nstride) return false;   // flat token rows only
+  if (d.cin % 64 || d.cin < 512 || d.cout != d.cout_pad || d.cout % 256 || d.cout > kGpMaxCout) return false;
+  const int share = d.share >= 0 ? d.share : env_int("TCD_CONV_SHARE", 2, 0);
+  if (share != 0) return false;             // whole-SM plans (the layer programs): a pair owns two SMs outright
+  const long work = (long)cdiv(cdiv(d.W, 128), 2) * (d.cout / 256);
+  return work >= sm_count() / 2;
+}
+
+static int gemm_pair_plan_build(const ConvDesc& d, ConvPlan* plan) {
+  ConvArgs& a = plan->args;
+  a.Ho = 1; a.Wo = d.W; a.TW = 128; a.TH = 1;
+  a.tiles_w = cdiv(d.W, 128); a.tiles_per_img = a.tiles_w;
+  a.taps = 1; a.kchunks = d.cin / 64; a.ck = 64; a.BN = 256;
+  a.cin_off = d.x_coff; a.cout_off = d.y_coff;
+  a.mode = 0; a.silu = d.silu; a.out_chunk = 64; a.n_valid = d.cout;
+  a.bias = d.bias; a.bias_n = d.cout;
+  a.resid = (const __nv_bfloat16*)d.resid; a.r_ctot = d.r_ctot; a.r_coff = d.r_coff; a.resid_pre = d.resid_pre;
+  a.r_nstride = (long long)d.W * d.r_ctot;
+  a.pdl = g_use_pdl;
+  a.n_tiles_n = d.cout / 256;
+  plan->pair = 2;
+  plan->pair_n_tiles = d.cout / 256;
+  plan->pair_m_tiles = a.tiles_w;
+  a.total_tiles = plan->pair_m_tiles * plan->pair_n_tiles;
+  const int work = cdiv(plan->pair_m_tiles, 2) * plan->pair_n_tiles;
+  const int clusters = std::min(sm_count() / 2, work);
+  plan->grid = dim3((unsigned)(2 * clusters), 1, 1);
+  plan->smem_bytes = kGpSmem;
+  plan->flops = 2.0 * d.W * (double)d.cout * d.cin;
+  const size_t es = 2;
+  {
+    cuuint64_t dims[4] = {(cuuint64_t)d.x_ctot, (cuuint64_t)d.W, 1, 1};
+    cuuint64_t st[3] = {(cuuint64_t)d.x_ctot * es, (cuuint64_t)d.W * d.x_ctot * es, (cuuint64_t)d.W * d.x_ctot * es};
+    cuuint32_t box[4] = {64, 128, 1, 1};
+    int rc = encode_map(&plan->maps.a[0], (void*)d.x, 4, dims, st, box, 128, "A/gemm_pair");
+    if (rc) return rc;
+    for (int i = 1; i < 4; ++i) plan->maps.a[i] = plan->maps.a[0];
+  }
+  {
+    cuuint64_t dims[3] = {(cuuint64_t)d.cin, (cuuint64_t)d.cout_pad, 1};
+    cuuint64_t st[2] = {(cuuint64_t)d.cin * es, (cuuint64_t)d.cout_pad * d.cin * es};
+    cuuint32_t box[3] = {64, 128, 1};
+    int rc = encode_map(&plan->maps.b, (void*)d.w, 3, dims, st, box, 128, "B/gemm_pair");
+    if (rc) return rc;
+  }
+  {
+    cuuint64_t dims[4] = {(cuuint64_t)d.y_ctot, (cuuint64_t)d.W, 1, 1};
+    cuuint64_t st[3] = {(cuuint64_t)d.y_ctot * es, (cuuint64_t)d.W * d.y_ctot * es, (cuuint64_t)d.W * d.y_ctot * es};
+    cuuint32_t box[4] = {64, 128, 1, 1};
+    int rc = encode_map(&plan->maps.o, d.y, 4, dims, st, box, 128, "O/gemm_pair");
+    if (rc) return rc;
+  }
+  if (env_int("TCD_CONV_PLAN_DUMP", 0))
+    fprintf(stderr, "convplan gemm_pair rows%d cin%d cout%d | 256x256 per CTA pair, %d stages, grid %u\n", d.W, d.cin, d.cout,
+            kGpStages, plan->grid.x);
+  return ensure_dyn_smem((const void*)gemm_pair_kernel_variant(a.silu), (size_t)kGpSmem);
+}
+
+static int gemm_pair_plan_launch(const ConvPlan& plan, cudaStream_t stream) {
+  GemmPairArgs ga;
+  memset(&ga, 0, sizeof(ga));
+  ga.c = plan.args;
+  ga.m_tiles = plan.pair_m_tiles;
+  ga.m_pairs = cdiv(plan.pair_m_tiles, 2);
+  ga.n_tiles = plan.pair_n_tiles;
+  ga.kchunks = plan.args.kchunks;
+  cudaLaunchConfig_t cfg;
+  memset(&cfg, 0, sizeof(cfg));
+  cfg.gridDim = plan.grid;
+  cfg.blockDim = dim3(kConvThreads, 1, 1);
+  cfg.dynamicSmemBytes = (size_t)plan.smem_bytes;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[2];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = 2;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[1].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = plan.args.pdl ? 2 : 1;
+  cudaError_t e = cudaLaunchKernelEx(&cfg, gemm_pair_kernel_variant(plan.args.silu), plan.maps, ga);
+  g_launch_count.fetch_add(1, std::memory_order_relaxed);
+  if (e != cudaSuccess) {
+    set_last_error("gemm_pair_kernel launch: %s", cudaGetErrorString(e));
+    return TCD_ERR_CUDA;
+  }
+  return TCD_OK;
+}
+
 static void choose_tile(int Ho, int Wo, int* TW, int* TH) {
   if (Wo % 16 == 0 && Ho % 8 == 0) {
     *TW = 16;
@@ -286,6 +388,7 @@ int conv_plan_build(const ConvDesc& d, ConvPlan* plan) {
   TCD_REQUIRE(d.groups >= 1 && d.cout % d.groups == 0, "conv: %d groups do not divide cout %d", d.groups, d.cout);
   TCD_REQUIRE(!(d.silu == 1 && d.resid && d.resid_pre), "conv: SiLU layers add their residual after the activation");
   if (pair_eligible(d, mode)) return pair_plan_build(d, plan);
+  if (gemm_pair_eligible(d, mode)) return gemm_pair_plan_build(d, plan);
   ConvArgs& a = plan->args;
   a.Ho = d.H / d.stride;
   a.Wo = d.W / d.stride;
@@ -543,6 +646,7 @@ int conv_plan_build(const ConvDesc& d, ConvPlan* plan) {
 }
 
 int conv_plan_launch(const ConvPlan& plan, cudaStream_t stream) {
+  if (plan.pair == 2) return gemm_pair_plan_launch(plan, stream);
   if (plan.pair) return pair_plan_launch(plan, stream);
   cudaLaunchConfig_t cfg;
   memset(&cfg, 0, sizeof(cfg));

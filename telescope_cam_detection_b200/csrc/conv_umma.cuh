@@ -702,7 +702,7 @@ struct PairArgs;
 struct ConvPlan {
   ConvMaps maps;
   ConvArgs args;
-  int pair = 0;        // 1: conv_pair_kernel (cta_group::2, resident weights, conv_pair.cuh); args then lives in pair_args
+  int pair = 0;        // 1: conv_pair_kernel (cta_group::2, resident weights, conv_pair.cuh); 2: gemm_pair_kernel (gemm_pair.cuh)
   int pair_n_tiles = 0, pair_m_tiles = 0, pair_group_cin = 0;
   dim3 grid;
   int smem_bytes = 0;

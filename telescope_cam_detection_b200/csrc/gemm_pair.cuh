@@ -1,0 +1,196 @@
+// Token linears (1x1 convs over flat token rows, long K) on CTA PAIRS: tcgen05.mma.cta_group::2 with a
+// 256 x 256 output tile per pair, both operands streamed through a shared-memory ring.
+//
+// Why: these GEMMs (the qkv / proj / fc1 / fc2 linears of the Stage-2 classifier body, 36 928 token rows x
+// K >= 1024) are bound by L2 -> SM operand delivery, ~43 B/clk/SM with every SM pulling:
+//   128 x 128 tile, one CTA :  32 KiB per k-chunk for 2.1 MFLOP =  64 FLOP/B  (750 TFLOP/s measured)
+//   128 x 256 tile, one CTA :  48 KiB per k-chunk for 4.2 MFLOP =  87 FLOP/B  (877 TFLOP/s measured)
+//   256 x 256 tile, CTA pair:  each CTA loads ITS 128 rows of A and ITS 128 of the tile's 256 weight rows
+//                              = 32 KiB per k-chunk per SM for 4.2 MFLOP = 131 FLOP/B
+// The leader CTA's MMA thread issues M = 256, N = 256 MMAs that read A from both CTAs (128 rows each) and B from
+// both (N / 2 rows each); every CTA keeps its 128 x 256 fp32 accumulator (double-buffered: all 512 TMEM columns)
+// and runs its own epilogue (bias, activation, residual, bf16, swizzled staging, four TMA stores).
+// Barrier scheme as in conv_pair.cuh: the TMA loads of BOTH CTAs complete_tx on the LEADER's full barriers,
+// tcgen05.commit.cta_group::2 multicasts "stage free" / "accumulator ready" to both CTAs, the peer's epilogue
+// warps hand the accumulator back with a remote mbarrier.arrive on the leader.
+#pragma once
+#include "conv_pair.cuh"
+
+namespace tcd {
+
+constexpr int kGpABytes = 128 * 64 * 2;            // 128 token rows x 64 channels
+constexpr int kGpStageBytes = 2 * kGpABytes;       // + this CTA's 128 weight rows x 64 channels
+constexpr int kGpStages = 4;
+constexpr int kGpStaging = 128 * 256 * 2;          // 128 rows x 256 output channels, four 64-channel chunks
+constexpr int kGpMaxCout = kConvMaxBias;
+constexpr int kGpSmem = kGpStages * kGpStageBytes + kGpStaging + 1024;
+
+struct GemmPairArgs {
+  ConvArgs c;        // epilogue fields shared with conv_finish_cols (TW = 128, TH = 1, BN = 256, out_chunk = 64)
+  int m_tiles;       // ceil(rows / 128)
+  int m_pairs;       // ceil(m_tiles / 2)
+  int n_tiles;       // Cout / 256
+  int kchunks;       // Cin / 64
+};
+
+#if defined(__CUDACC__) && defined(TCD_CONV_KERNEL_IMPL)
+
+template <int ACT>
+__global__ void __launch_bounds__(kConvThreads, 1)
+gemm_pair_kernel(const __grid_constant__ ConvMaps maps, const __grid_constant__ GemmPairArgs ga) {
+  const ConvArgs& p = ga.c;
+  extern __shared__ uint8_t smem_raw[];
+  __shared__ uint64_t full_bar[kGpStages];
+  __shared__ uint64_t empty_bar[kGpStages];
+  __shared__ uint64_t tmem_full_bar[2];
+  __shared__ uint64_t tmem_empty_bar[2];
+  __shared__ __align__(16) float s_bias[kGpMaxCout];
+  __shared__ uint32_t tmem_base_s;
+
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  uint8_t* staging = smem + kGpStages * kGpStageBytes;
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const uint32_t rank = cluster_ctarank();           // 0 = leader (issues the MMAs, owns the full barriers)
+  const int n_clusters = (int)(gridDim.x >> 1);
+  const int cluster_id = (int)(blockIdx.x >> 1);
+  // work item w -> (row pair w / n_tiles, column tile w % n_tiles): neighbouring clusters share the A rows in L2
+  const int n_work = ga.m_pairs * ga.n_tiles;
+  const int n_mine = cluster_id < n_work ? (n_work - cluster_id + n_clusters - 1) / n_clusters : 0;
+
+  if (warp == 0 && lane == 0) {
+    prefetch_tmap(&maps.a[0]);
+    prefetch_tmap(&maps.b);
+    prefetch_tmap(&maps.o);
+    for (int s = 0; s < kGpStages; ++s) {
+      mbar_init(&full_bar[s], 1);        // leader: its own arrive.expect_tx (bytes of BOTH CTAs)
+      mbar_init(&empty_bar[s], 1);       // one multicast commit
+    }
+    for (int a = 0; a < 2; ++a) {
+      mbar_init(&tmem_full_bar[a], 1);                     // one multicast commit
+      mbar_init(&tmem_empty_bar[a], 2 * kConvEpiWarps);    // leader: every epilogue warp of both CTAs
+    }
+    fence_mbar_init();
+  }
+  if (warp == 1) tmem_alloc2(&tmem_base_s, 512);
+  if (warp >= 2)
+    for (int i = threadIdx.x - 64; i < p.bias_n; i += 32 * kConvEpiWarps)
+      s_bias[i] = (ACT == 1 ? 0.5f : 1.0f) * __ldg(p.bias + i);   // SiLU layers: see conv_finish_silu
+  tc_fence_before();
+  __syncthreads();
+  cluster_sync_all();                    // the peer's barriers are initialised before anything arrives on them
+  tc_fence_after();
+  const uint32_t tmem_base = tmem_base_s;
+  if (p.pdl == 1 && threadIdx.x == 0) pdl_launch_dependents();
+
+  if (warp == 0) {
+    // ------------------------------------------------------------------ TMA producer (one per CTA)
+    if (lane == 0 && n_mine > 0) {
+      bool waited = !p.pdl;
+      RingCursor ring{0, 0u, kGpStages};
+      for (int it = 0; it < n_mine; ++it) {
+        const int w = cluster_id + it * n_clusters;
+        const int n_tile = w % ga.n_tiles, m_pair = w / ga.n_tiles;
+        const int x0 = (2 * m_pair + (int)rank) * 128;      // beyond the last row: loads zero-fill, stores are clipped
+        for (int kc = 0; kc < ga.kchunks; ++kc) {
+          mbar_wait(&empty_bar[ring.s], ring.ph ^ 1u);
+          const uint32_t full_leader = mapa_u32(smem_u32(&full_bar[ring.s]), 0);
+          if (rank == 0) mbar_expect_tx(&full_bar[ring.s], 2u * (uint32_t)kGpStageBytes);
+          uint8_t* st = smem + (size_t)ring.s * kGpStageBytes;
+          // weights do not depend on the previous layer: issue them before the dependency wait
+          tma2_load_3d(st + kGpABytes, &maps.b, full_leader, kc * 64, n_tile * 256 + (int)rank * 128, 0);
+          if (!waited) {
+            pdl_wait();
+            waited = true;
+          }
+          tma2_load_4d(st, &maps.a[0], full_leader, p.cin_off + kc * 64, x0, 0, 0);
+          ring.advance();
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ------------------------------------------------------------------ MMA issuer (leader CTA only)
+    if (lane == 0 && rank == 0 && n_mine > 0) {
+      const uint32_t idesc = umma_idesc_bf16(256, 256);
+      const uint32_t ring_base = smem_u32(smem);
+      RingCursor ring{0, 0u, kGpStages};
+      for (int it = 0; it < n_mine; ++it) {
+        const int acc = it & 1;
+        mbar_wait(&tmem_empty_bar[acc], ((uint32_t)(it >> 1) & 1u) ^ 1u);   // both epilogues have drained it
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + (uint32_t)(acc * 256);
+        for (int kc = 0; kc < ga.kchunks; ++kc) {
+          mbar_wait(&full_bar[ring.s], ring.ph);
+          tc_fence_after();
+          const uint32_t a_addr = ring_base + (uint32_t)(ring.s * kGpStageBytes);
+          const uint64_t ad = umma_smem_desc(a_addr, 1024u, 2u), bd = umma_smem_desc(a_addr + kGpABytes, 1024u, 2u);
+#pragma unroll
+          for (int k = 0; k < 4; ++k) umma2_bf16(d_tmem, ad + 2 * k, bd + 2 * k, idesc, (uint32_t)((kc | k) != 0));
+          umma2_commit_mc(&empty_bar[ring.s], 3);     // this stage is free in both CTAs
+          ring.advance();
+        }
+        umma2_commit_mc(&tmem_full_bar[acc], 3);      // accumulator ready in both CTAs
+      }
+    }
+    if (lane == 0 && p.pdl == 2) pdl_launch_dependents();
+  } else {
+    // ------------------------------------------------------------------ epilogue (4 warps per CTA, own 128 rows)
+    const int q = warp & 3;
+    const int row = q * 32 + lane;
+    if (p.pdl && p.resid != nullptr) pdl_wait();
+    const uint32_t empty_leader0 = mapa_u32(smem_u32(&tmem_empty_bar[0]), 0);
+    const uint32_t empty_leader1 = mapa_u32(smem_u32(&tmem_empty_bar[1]), 0);
+    for (int it = 0; it < n_mine; ++it) {
+      const int acc = it & 1;
+      const int w = cluster_id + it * n_clusters;
+      ConvTile c;
+      c.n_tile = w % ga.n_tiles;
+      c.n_img = 0;
+      c.y0 = 0;
+      c.x0 = (2 * (w / ga.n_tiles) + (int)rank) * 128;
+      const int x = c.x0 + row;
+      const bool valid = x < p.Wo;
+      mbar_wait(&tmem_full_bar[acc], (uint32_t)(it >> 1) & 1u);
+      tc_fence_after();
+      if (it > 0) {
+        if (warp == 2 && lane == 0) tma_store_wait_read();    // the previous tile's stores have read the staging
+        asm volatile("bar.sync 1, %0;" ::"n"(32 * kConvEpiWarps) : "memory");
+      }
+      const uint32_t taddr = tmem_base + (uint32_t)(acc * 256) + ((uint32_t)(q * 32) << 16);
+      uint32_t ra[32], rb[32];
+      tmem_ld32(taddr, ra);
+#pragma unroll
+      for (int sl = 0; sl < 8; sl += 2) {
+        tmem_ld_wait();
+        tmem_ld32(taddr + 32 * (sl + 1), rb);
+        conv_finish_cols<32, 0, ACT, 0>(p, ra, 32 * sl, s_bias, row, valid, c, 0, x, staging);
+        tmem_ld_wait();
+        if (sl + 2 < 8) {
+          tmem_ld32(taddr + 32 * (sl + 2), ra);
+        } else {
+          // every column has been read: hand the accumulator back to the leader's MMA thread
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive_cluster(acc ? empty_leader1 : empty_leader0);
+        }
+        conv_finish_cols<32, 0, ACT, 0>(p, rb, 32 * (sl + 1), s_bias, row, valid, c, 0, x, staging);
+      }
+      fence_proxy_async_smem();
+      asm volatile("bar.sync 1, %0;" ::"n"(32 * kConvEpiWarps) : "memory");
+      if (warp == 2 && lane == 0) {
+        for (int ch = 0; ch < 4; ++ch)
+          tma_store_4d(&maps.o, staging + (size_t)ch * 128 * 128, p.cout_off + c.n_tile * 256 + ch * 64, c.x0, 0, 0);
+        tma_store_commit();
+      }
+    }
+    if (warp == 2 && lane == 0) tma_store_wait_read();
+  }
+  tc_fence_before();
+  __syncthreads();
+  cluster_sync_all();      // no CTA frees the pair's TMEM while its peer may still run MMAs into / read from it
+  if (warp == 1) tmem_dealloc2(tmem_base, 512);
+}
+
+#endif  // __CUDACC__ && TCD_CONV_KERNEL_IMPL
+
+}  // namespace tcd

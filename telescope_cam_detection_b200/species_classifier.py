@@ -31,7 +31,7 @@ class SpeciesClassifier:
                  input_size: int = 224, use_hierarchical: bool = True, allowed_species: Optional[List[str]] = None,
                  enable_geographic_filter: bool = False, model: Any = None,
                  model_factory: Optional[Callable[[int], Any]] = None, weights: Optional[Dict[str, Any]] = None,
-                 max_batch: int = 64):
+                 max_batch: int = 64, batch_buckets: Tuple[int, ...] = (4, 16)):
         self.model_name = model_name
         self.checkpoint_path = checkpoint_path
         self.device = device
@@ -40,7 +40,12 @@ class SpeciesClassifier:
         self._factory = model_factory
         self._weights = weights          # in-memory state dict (timm key names) for the native EVA02 body
         self.max_batch = int(max_batch)  # crops per replay of the native body
-        self.engine = None               # eva02_engine.Eva02Engine once load_model built it
+        self.engine = None               # eva02_engine.Eva02Engine (max_batch slots) once load_model built it
+        # A replay of a layer program computes every crop slot it was built for, so a frame with two detections should
+        # not pay for 64: smaller programs (own weights, own CUDA graph) are built on first use for these sizes.
+        self.batch_buckets = tuple(sorted(b for b in batch_buckets if 0 < b < self.max_batch))
+        self._engines: Dict[int, Any] = {}
+        self._sd = None
         self.taxonomy: Dict[Any, Any] = {}
         self.use_hierarchical = use_hierarchical
         self.enable_geographic_filter = enable_geographic_filter
@@ -111,10 +116,26 @@ class SpeciesClassifier:
             raise ValueError("checkpoint head has %d classes, load_model asked for %d" % (sd["head.weight"].shape[0], num_classes))
         dev = str(self.device)
         idx = int(dev.split(":")[1]) if ":" in dev else 0
+        self._sd, self._dev_idx = sd, idx
         self.engine = eva02_engine.Eva02Engine(sd, batch=self.max_batch, img_size=int(self.input_size),
                                                top_k=self._ENGINE_TOPK, device=idx)
+        self._engines = {self.max_batch: self.engine}
         self.model = self.engine
         return True
+
+    def _engine_for(self, n: int):
+        """The smallest program that holds n crops (built on first use; the full-size one always exists)."""
+        from . import eva02_engine
+        size = next((b for b in self.batch_buckets if b >= n), self.max_batch)
+        if size not in self._engines:
+            self._engines[size] = eva02_engine.Eva02Engine(self._sd, batch=size, img_size=int(self.input_size),
+                                                           top_k=self._ENGINE_TOPK, device=self._dev_idx)
+        return self._engines[size]
+
+    def close(self):
+        for e in self._engines.values():
+            e.close()
+        self._engines, self.engine, self._sd = {}, None, None
 
     def load_model(self, num_classes: int = 1000, max_retries: int = 3) -> bool:
         from .eva02_engine import is_eva02
@@ -199,10 +220,10 @@ class SpeciesClassifier:
             out.append({"species": label, "confidence": prob, "class_id": idx, "taxonomic_level": level})
         return out
 
-    def _engine_topk(self, n, top_k):
-        self.engine.run()
-        self.engine.sync()
-        p, i = self.engine.read_topk(n)
+    def _engine_topk(self, eng, n, top_k):
+        eng.run()
+        eng.sync()
+        p, i = eng.read_topk(n)
         k = min(top_k, p.shape[1])
         return p[:, :k], i[:, :k]
 
@@ -215,8 +236,9 @@ class SpeciesClassifier:
             ps, is_ = [], []
             for s0 in range(0, batch.shape[0], self.max_batch):
                 part = batch[s0:s0 + self.max_batch]
-                self.engine.patchify_device(part.data_ptr(), part.shape[0])
-                p, i = self._engine_topk(part.shape[0], top_k)
+                eng = self._engine_for(part.shape[0])
+                eng.patchify_device(part.data_ptr(), part.shape[0])
+                p, i = self._engine_topk(eng, part.shape[0], top_k)
                 ps.append(p)
                 is_.append(i)
             return np.concatenate(ps, 0), np.concatenate(is_, 0)
@@ -253,9 +275,9 @@ class SpeciesClassifier:
             out = []
             for s0 in range(0, boxes.shape[0], self.max_batch):
                 part = boxes[s0:s0 + self.max_batch]
-                self.engine.crop_patches(t.data_ptr(), int(t.shape[0]), int(t.shape[1]), t.stride(0), part,
-                                         mean=self.mean, std=self.std)
-                p, i = self._engine_topk(part.shape[0], top_k)
+                eng = self._engine_for(part.shape[0])
+                eng.crop_patches(t.data_ptr(), int(t.shape[0]), int(t.shape[1]), t.stride(0), part, mean=self.mean, std=self.std)
+                p, i = self._engine_topk(eng, part.shape[0], top_k)
                 out.extend(self._rows_to_results(p[n], i[n]) for n in range(part.shape[0]))
             return out
         p, i = self._topk(self.crop_batch(frame, boxes), top_k)

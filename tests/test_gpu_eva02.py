@@ -116,6 +116,35 @@ def test_token_assembly_softmax_topk():
     P.close()
 
 
+@pytest.mark.parametrize("rows,cin,cout,act,resid", [(20000 + 37, 1024, 512, 0, True), (19200, 512, 768, 1, False),
+                                                     (9700, 2816, 1024, 0, True)])
+def test_token_linear_on_cta_pairs(rows, cin, cout, act, resid):
+    """Long-K token linears with enough tiles take the cta_group::2 GEMM (csrc/gemm_pair.cuh: 256 x 256 per CTA pair):
+    odd tile counts, a ragged last tile, bias, SiLU, residual, a column slice of a wider output."""
+    import torch
+    from telescope_cam_detection_b200.rtdetr_engine import Act
+    torch.manual_seed(7)
+    P = _prog()
+    x = _bf16(torch.randn(rows, cin))
+    w = _bf16(torch.randn(cout, cin) / cin ** 0.5)
+    b = torch.randn(cout) * 0.1
+    r = _bf16(torch.randn(rows, cout + 256)) if resid else None
+    X = _up_bf16(P, x, (1, 1, rows, cin))
+    Y = Act(P.alloc(rows * (cout + 256) * 2), 1, 1, rows, cout + 256)
+    R = _up_bf16(P, r, (1, 1, rows, cout + 256)) if resid else None
+    P.conv("lin", X, w.numpy().reshape(cout, cin, 1, 1), b.numpy(), act=act, y=Y, y_coff=256, resid=R, r_coff=256 if resid else 0)
+    P.run(False); P.sync()
+    got = torch.from_numpy(P.read_bf16(Y))[0, 0]
+    ref = x @ w.T + b
+    if act == 1:
+        ref = torch.nn.functional.silu(ref)
+    if resid:
+        ref = ref + r[:, 256:]
+    assert torch.allclose(got[:, 256:], ref, atol=3e-2, rtol=1.5e-2), float((got[:, 256:] - ref).abs().max())
+    assert float(got[:, :256].abs().max()) == 0.0      # the columns left of the slice are untouched
+    P.close()
+
+
 @pytest.mark.parametrize("B,K,NC", [(64, 1024, 10000), (5, 192, 1000), (33, 320, 77)])
 def test_head_gemv(B, K, NC):
     import torch
@@ -235,7 +264,7 @@ def test_species_classifier_native_body():
     cfg = eva02.Eva02Config(img_size=224, embed_dim=192, depth=2, num_heads=3, num_classes=500)
     model = eva02.make_model(cfg, 5, logit_std=4.0)
     clf = SpeciesClassifier(model_name="timm/eva02_tiny_patch14_224.mim_in22k", input_size=224, use_hierarchical=False,
-                            confidence_threshold=0.0, weights=model.state_dict(), max_batch=3)
+                            confidence_threshold=0.0, weights=model.state_dict(), max_batch=3, batch_buckets=(1,))
     assert clf.load_model(num_classes=500) and clf.engine is not None
     frame = structured_frame(4, 480, 640)
     boxes = [(10, 20, 200, 300), (0, 0, 640, 480), (300, 100, 524, 324), (50, 60, 120, 200)]   # 4 crops > max_batch 3
@@ -254,6 +283,8 @@ def test_species_classifier_native_body():
             assert r[0]["class_id"] == int(pr.argmax())
     batch = clf.classify_batch([np.ascontiguousarray(frame[y1:y2, x1:x2]) for x1, y1, x2, y2 in boxes], top_k=3)
     assert [[d["class_id"] for d in b] for b in batch] == [[d["class_id"] for d in r[:3]] for r in res]
+    assert sorted(clf._engines) == [1, 3]           # single crops ran on the one-slot program, built on first use
     assert clf.load_model(num_classes=500)          # idempotent
+    clf.close()
     wrong = SpeciesClassifier(model_name="timm/eva02_tiny_patch14_224", input_size=224, weights=model.state_dict())
     assert not wrong.load_model(num_classes=1000)   # head size mismatch fails loudly, like load_state_dict would
