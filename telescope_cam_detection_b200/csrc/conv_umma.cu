@@ -262,15 +262,22 @@ static GemmPairKernelFn gemm_pair_kernel_variant(int act) {
 static bool gemm_pair_eligible(const ConvDesc& d, int mode) {
   if (!env_int("TCD_GEMM_PAIR", 1, 0)) return false;
   if (mode != 0 || d.k != 1 || d.stride != 1 || d.groups != 1) return false;
-  if (d.N != 1 || d.H != 1 || d.x_nstride || d.y_nstride || d.r_nstride) return false;   // flat token rows only
+  // dense views only: a 1x1 conv over a dense NHWC tensor IS a GEMM over its N*H*W pixel rows (token rows: N = H = 1)
+  if (d.x_nstride || d.y_nstride || d.r_nstride) return false;
   if (d.cin % 64 || d.cin < 512 || d.cout != d.cout_pad || d.cout % 256 || d.cout > kGpMaxCout) return false;
   const int share = d.share >= 0 ? d.share : env_int("TCD_CONV_SHARE", 2, 0);
   if (share != 0) return false;             // whole-SM plans (the layer programs): a pair owns two SMs outright
-  const long work = (long)cdiv(cdiv(d.W, 128), 2) * (d.cout / 256);
+  const long rows = (long)d.N * d.H * d.W;
+  if (rows >= (1L << 30)) return false;
+  const long work = (long)cdiv(cdiv((int)rows, 128), 2) * (d.cout / 256);
   return work >= sm_count() / 2;
 }
 
-static int gemm_pair_plan_build(const ConvDesc& d, ConvPlan* plan) {
+static int gemm_pair_plan_build(const ConvDesc& d0, ConvPlan* plan) {
+  ConvDesc d = d0;            // flattened: one "image" of N*H*W pixel rows
+  d.W = d0.N * d0.H * d0.W;
+  d.N = 1;
+  d.H = 1;
   ConvArgs& a = plan->args;
   a.Ho = 1; a.Wo = d.W; a.TW = 128; a.TH = 1;
   a.tiles_w = cdiv(d.W, 128); a.tiles_per_img = a.tiles_w;
