@@ -378,7 +378,9 @@ typedef struct {
   char name[64];
   const void* x; int32_t N, H, W, x_ctot, x_coff, cin; int64_t x_nstride;   /* bf16 NHWC input view  */
   const float* w_host; const float* bias_host;        /* f32 [cout][cin][k][k], [cout] (BN folded)     */
-  int32_t cout, k, stride, act;                       /* act: 0 none 1 SiLU 2 ReLU 3 GELU              */
+  int32_t cout, k, stride, act;                       /* act: 0 none 1 SiLU 2 ReLU 3 GELU; 4 gated     */
+  /* act 4 (token linears on CTA pairs only): 32-column slabs alternate gate / value, the output holds      */
+  /* silu(gate) * value and is cout / 2 columns wide (the fused fc1_g || fc1_x of a SwiGLU MLP)            */
   void* y; int32_t y_ctot, y_coff; int64_t y_nstride; /* bf16 output view (NULL when out_f32 is set)   */
   const void* resid; int32_t r_ctot, r_coff, resid_pre; int64_t r_nstride;
   float* out_f32; int32_t out_ld, out_col, rows_per_img, row_off;  /* f32 row output (logits etc.)    */

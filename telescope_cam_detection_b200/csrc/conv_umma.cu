@@ -255,12 +255,13 @@ static int pair_plan_launch(const ConvPlan& plan, cudaStream_t stream) {
 //   TCD_GEMM_PAIR=0 disables it (A/B measurements)
 using GemmPairKernelFn = void (*)(const ConvMaps, const GemmPairArgs);
 static GemmPairKernelFn gemm_pair_kernel_variant(int act) {
-  static const GemmPairKernelFn tbl[4] = {gemm_pair_kernel<0>, gemm_pair_kernel<1>, gemm_pair_kernel<2>, gemm_pair_kernel<3>};
-  return tbl[act & 3];
+  static const GemmPairKernelFn tbl[5] = {gemm_pair_kernel<0>, gemm_pair_kernel<1>, gemm_pair_kernel<2>, gemm_pair_kernel<3>,
+                                          gemm_pair_kernel<4>};
+  return tbl[act >= 0 && act <= 4 ? act : 0];
 }
 
 static bool gemm_pair_eligible(const ConvDesc& d, int mode) {
-  if (!env_int("TCD_GEMM_PAIR", 1, 0)) return false;
+  if (!env_int("TCD_GEMM_PAIR", 1, 0) && d.silu != 4) return false;
   if (mode != 0 || d.k != 1 || d.stride != 1 || d.groups != 1) return false;
   // dense views only: a 1x1 conv over a dense NHWC tensor IS a GEMM over its N*H*W pixel rows (token rows: N = H = 1)
   if (d.x_nstride || d.y_nstride || d.r_nstride) return false;
@@ -394,8 +395,12 @@ int conv_plan_build(const ConvDesc& d, ConvPlan* plan) {
   const int mode = d.out_f32 ? 1 : 0;
   TCD_REQUIRE(d.groups >= 1 && d.cout % d.groups == 0, "conv: %d groups do not divide cout %d", d.groups, d.cout);
   TCD_REQUIRE(!(d.silu == 1 && d.resid && d.resid_pre), "conv: SiLU layers add their residual after the activation");
+  TCD_REQUIRE(!(d.silu == 4 && d.resid), "conv: the gated epilogue takes no residual");
   if (pair_eligible(d, mode)) return pair_plan_build(d, plan);
   if (gemm_pair_eligible(d, mode)) return gemm_pair_plan_build(d, plan);
+  TCD_REQUIRE(d.silu != 4, "conv: the gated (SwiGLU) epilogue exists for CTA-pair GEMM shapes only (1x1, dense rows, Cin >= 512 in "
+                           "64s, Cout in 256s, >= %d tile pairs)", sm_count() / 2);
+  TCD_REQUIRE(d.silu >= 0 && d.silu <= 3, "conv: activation %d", d.silu);
   ConvArgs& a = plan->args;
   a.Ho = d.H / d.stride;
   a.Wo = d.W / d.stride;

@@ -10,6 +10,10 @@
 // The leader CTA's MMA thread issues M = 256, N = 256 MMAs that read A from both CTAs (128 rows each) and B from
 // both (N / 2 rows each); every CTA keeps its 128 x 256 fp32 accumulator (double-buffered: all 512 TMEM columns)
 // and runs its own epilogue (bias, activation, residual, bf16, swizzled staging, four TMA stores).
+// ACT == 4 is the gated form of the SwiGLU MLP's first Linear (fc1_g || fc1_x of timm's SwiGLU, oracle/eva02.py::_SwiGLU):
+// the host interleaves the weight rows so that within a 256-column tile the 32-column slabs alternate gate / value;
+// the epilogue then writes silu(gate + b_g) * (value + b_x) -- 128 columns per tile, in natural hidden order -- and
+// the 2 x hidden intermediate never exists in memory.
 // Barrier scheme as in conv_pair.cuh: the TMA loads of BOTH CTAs complete_tx on the LEADER's full barriers,
 // tcgen05.commit.cta_group::2 multicasts "stage free" / "accumulator ready" to both CTAs, the peer's epilogue
 // warps hand the accumulator back with a remote mbarrier.arrive on the leader.
@@ -34,6 +38,21 @@ struct GemmPairArgs {
 };
 
 #if defined(__CUDACC__) && defined(TCD_CONV_KERNEL_IMPL)
+
+// 32 fp32 values of one row -> bf16 -> the 128-byte-swizzled staging tile of 64-channel chunks (what TMA stores read)
+__device__ __forceinline__ void gp_stage_slab(const float (&v)[32], int c0, int row, uint8_t* stage_base) {
+  const int chunk = c0 >> 6, u0 = (c0 & 63) >> 3, sw = row & 7;
+  uint8_t* rowp = stage_base + (size_t)chunk * 128 * 128 + (size_t)row * 128;
+#pragma unroll
+  for (int u = 0; u < 4; ++u) {
+    uint4 q;
+    q.x = pack_bf16x2(v[u * 8 + 0], v[u * 8 + 1]);
+    q.y = pack_bf16x2(v[u * 8 + 2], v[u * 8 + 3]);
+    q.z = pack_bf16x2(v[u * 8 + 4], v[u * 8 + 5]);
+    q.w = pack_bf16x2(v[u * 8 + 6], v[u * 8 + 7]);
+    *reinterpret_cast<uint4*>(rowp + (((u0 + u) ^ sw) << 4)) = q;
+  }
+}
 
 template <int ACT>
 __global__ void __launch_bounds__(kConvThreads, 1)
@@ -163,8 +182,17 @@ gemm_pair_kernel(const __grid_constant__ ConvMaps maps, const __grid_constant__ 
       for (int sl = 0; sl < 8; sl += 2) {
         tmem_ld_wait();
         tmem_ld32(taddr + 32 * (sl + 1), rb);
-        conv_finish_cols<32, 0, ACT, 0>(p, ra, 32 * sl, s_bias, row, valid, c, 0, x, staging);
+        if constexpr (ACT != 4) conv_finish_cols<32, 0, ACT, 0>(p, ra, 32 * sl, s_bias, row, valid, c, 0, x, staging);
         tmem_ld_wait();
+        if constexpr (ACT == 4) {
+          // slab sl = gate, slab sl + 1 = value of hidden columns n_tile * 128 + sl * 16 .. + 31
+          const float* bg = s_bias + c.n_tile * 256 + 32 * sl;
+          float v[32];
+#pragma unroll
+          for (int i = 0; i < 32; ++i)
+            v[i] = silu_f(__uint_as_float(ra[i]) + bg[i]) * (__uint_as_float(rb[i]) + bg[32 + i]);
+          gp_stage_slab(v, 16 * sl, row, staging);
+        }
         if (sl + 2 < 8) {
           tmem_ld32(taddr + 32 * (sl + 2), ra);
         } else {
@@ -173,13 +201,14 @@ gemm_pair_kernel(const __grid_constant__ ConvMaps maps, const __grid_constant__ 
           __syncwarp();
           if (lane == 0) mbar_arrive_cluster(acc ? empty_leader1 : empty_leader0);
         }
-        conv_finish_cols<32, 0, ACT, 0>(p, rb, 32 * (sl + 1), s_bias, row, valid, c, 0, x, staging);
+        if constexpr (ACT != 4) conv_finish_cols<32, 0, ACT, 0>(p, rb, 32 * (sl + 1), s_bias, row, valid, c, 0, x, staging);
       }
       fence_proxy_async_smem();
       asm volatile("bar.sync 1, %0;" ::"n"(32 * kConvEpiWarps) : "memory");
       if (warp == 2 && lane == 0) {
-        for (int ch = 0; ch < 4; ++ch)
-          tma_store_4d(&maps.o, staging + (size_t)ch * 128 * 128, p.cout_off + c.n_tile * 256 + ch * 64, c.x0, 0, 0);
+        constexpr int kOutCols = ACT == 4 ? 128 : 256;     // the gated form writes half as many columns
+        for (int ch = 0; ch < kOutCols / 64; ++ch)
+          tma_store_4d(&maps.o, staging + (size_t)ch * 128 * 128, p.cout_off + c.n_tile * kOutCols + ch * 64, c.x0, 0, 0);
         tma_store_commit();
       }
     }

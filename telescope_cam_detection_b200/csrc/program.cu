@@ -80,8 +80,8 @@ int launch_small(const tcd_op_desc& d, cudaStream_t st) {
     case TCD_OP_MHA_ROPE:  // p: q, k, v, out, rope; i: ldq,qoff,ldk,koff,ldv,voff,ldo,N,T,heads,prefix; f: scale
       return mha64_rope_launch(p[0], i[0], i[1], p[1], i[2], i[3], p[2], i[4], i[5], p[3], i[6], i[7], i[8], i[9],
                                d.f[0], (const float*)p[4], i[10], st);
-    case TCD_OP_SWIGLU_LN:  // p: gu, gamma, beta, y; i: rows, H, Hp; f: eps
-      return swiglu_ln_launch(p[0], (const float*)p[1], (const float*)p[2], p[3], i[0], i[1], i[2], d.f[0], st);
+    case TCD_OP_SWIGLU_LN:  // p: gu, gamma, beta, y; i: rows, H, Hp, gated; f: eps
+      return swiglu_ln_launch(p[0], (const float*)p[1], (const float*)p[2], p[3], i[0], i[1], i[2], d.f[0], i[3], st);
     case TCD_OP_SOFTMAX:  // p: x, y; i: rows, C, ldx, ldy
       return softmax_rows_launch((const float*)p[0], i[2], (float*)p[1], i[3], i[0], i[1], st);
     case TCD_OP_HEAD_GEMV:  // p: x, w, bias, out; i: B, K, NC, ld

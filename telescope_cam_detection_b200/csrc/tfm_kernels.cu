@@ -84,13 +84,19 @@ layernorm_kernel(const uint4* __restrict__ a, const uint4* __restrict__ b, const
     const int c = lane + 32 * i;
     if (c < C8) {
       float o[8];
-      // gamma / beta as two 16-byte loads each (eight scalar loads per chunk made the kernel LSU-bound: 1.8 TB/s)
-      const float4 g0 = *reinterpret_cast<const float4*>(gamma + c * 8), g1 = *reinterpret_cast<const float4*>(gamma + c * 8 + 4);
-      const float4 b0 = *reinterpret_cast<const float4*>(beta + c * 8), b1 = *reinterpret_cast<const float4*>(beta + c * 8 + 4);
-      const float gg[8] = {g0.x, g0.y, g0.z, g0.w, g1.x, g1.y, g1.z, g1.w};
-      const float bb[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
+      if (gamma != nullptr) {
+        // gamma / beta as two 16-byte loads each (eight scalar loads per chunk made the kernel LSU-bound: 1.8 TB/s)
+        const float4 g0 = *reinterpret_cast<const float4*>(gamma + c * 8), g1 = *reinterpret_cast<const float4*>(gamma + c * 8 + 4);
+        const float4 b0 = *reinterpret_cast<const float4*>(beta + c * 8), b1 = *reinterpret_cast<const float4*>(beta + c * 8 + 4);
+        const float gg[8] = {g0.x, g0.y, g0.z, g0.w, g1.x, g1.y, g1.z, g1.w};
+        const float bb[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
 #pragma unroll
-      for (int e = 0; e < 8; ++e) o[e] = (v[i][e] - mean) * rstd * gg[e] + bb[e];
+        for (int e = 0; e < 8; ++e) o[e] = (v[i][e] - mean) * rstd * gg[e] + bb[e];
+      } else {
+        // no affine part: the caller folded gamma / beta into the Linear that reads y (W' = W diag(gamma), b' = b + W beta)
+#pragma unroll
+        for (int e = 0; e < 8; ++e) o[e] = (v[i][e] - mean) * rstd;
+      }
       y[(size_t)row * C8 + c] = f32_to_bf16x8(o);
     }
   }

@@ -8,7 +8,7 @@
 
 namespace tcd {
 
-// y[r,:] = LayerNorm(a[r,:] + (b ? b[r,:] : 0)) * gamma + beta      (C <= 1024, C % 8 == 0)
+// y[r,:] = LayerNorm(a[r,:] + (b ? b[r,:] : 0)) * gamma + beta      (C <= 1024, C % 8 == 0); gamma == NULL: no affine part
 int layernorm_launch(const void* a, const void* b, const float* gamma, const float* beta, void* y,
                      int rows, int C, float eps, cudaStream_t st);
 // y[n,t,:] = a[n,t,:] + b[(bcast ? 0 : n),t,:]        (bf16, row length C % 8 == 0)
@@ -72,9 +72,10 @@ int fa64_umma_launch(const void* q, int ldq, int qoff, const void* k, int ldk, i
                      int voff, void* out, int ldo, int N, int T, int heads, int head_dim, float scale,
                      const float* rope, int prefix, cudaStream_t st);
 // y[r,0:H) = LayerNorm(silu(gu[r,0:H)) * gu[r,Hp:Hp+H)); gu bf16 [rows, 2*Hp], y bf16 [rows, Hp] (pad zero);
-// gamma / beta: Hp floats each (16-byte aligned, padding ignored)
+// gamma / beta: Hp floats each (16-byte aligned, padding ignored), or both NULL (no affine part)
+// gated != 0: gu is already silu(g) * u, bf16 [rows, Hp] (written by the gated GEMM epilogue): LayerNorm only
 int swiglu_ln_launch(const void* gu, const float* gamma, const float* beta, void* y, int rows, int H, int Hp,
-                     float eps, cudaStream_t st);
+                     float eps, int gated, cudaStream_t st);
 // out[b,c] = x[b,:] . w[c,:] + bias[c]: x bf16 [B,K], w bf16 [NC,K] (K <= 1024, K % 8 == 0), out f32 [B, ld]
 int head_gemv_launch(const void* x, const void* w, const float* bias, float* out, int B, int K, int NC, int ld,
                      cudaStream_t st);

@@ -371,7 +371,7 @@ int mha64_rope_launch(const void* q, int ldq, int qoff, const void* k, int ldk, 
 constexpr int kSwigluChunks = 3;   // Hp <= 3 * 128 * 8 = 3072
 __global__ void __launch_bounds__(256)
 swiglu_ln_kernel(const uint4* __restrict__ gu, const float* __restrict__ gamma, const float* __restrict__ beta,
-                 uint4* __restrict__ y, int rows, int H, int Hp8, float eps) {
+                 uint4* __restrict__ y, int rows, int H, int Hp8, float eps, int gated) {
   __shared__ float red[2][2][4];
   const int half = threadIdx.x >> 7, t = threadIdx.x & 127, wq = t >> 5;
   const int row = blockIdx.x * 2 + half;
@@ -384,14 +384,24 @@ swiglu_ln_kernel(const uint4* __restrict__ gu, const float* __restrict__ gamma, 
 #pragma unroll
     for (int e = 0; e < 8; ++e) hv[i][e] = 0.f;
     if (live && c < Hp8) {
-      float gf[8], uf[8];
-      v_bf16x8_to_f32(gu[(size_t)row * 2 * Hp8 + c], gf);
-      v_bf16x8_to_f32(gu[(size_t)row * 2 * Hp8 + Hp8 + c], uf);
+      if (gated) {           // the fc1 epilogue already produced silu(g) * u (gemm_pair.cuh, ACT == 4): gu is [rows, Hp]
+        float hf[8];
+        v_bf16x8_to_f32(gu[(size_t)row * Hp8 + c], hf);
 #pragma unroll
-      for (int e = 0; e < 8; ++e) {
-        const float s = silu_f(gf[e]);     // h + h tanh(h), h = g / 2: one MUFU op, no division
-        hv[i][e] = (c * 8 + e < H) ? s * uf[e] : 0.f;
-        sum += hv[i][e];
+        for (int e = 0; e < 8; ++e) {
+          hv[i][e] = (c * 8 + e < H) ? hf[e] : 0.f;
+          sum += hv[i][e];
+        }
+      } else {
+        float gf[8], uf[8];
+        v_bf16x8_to_f32(gu[(size_t)row * 2 * Hp8 + c], gf);
+        v_bf16x8_to_f32(gu[(size_t)row * 2 * Hp8 + Hp8 + c], uf);
+#pragma unroll
+        for (int e = 0; e < 8; ++e) {
+          const float s = silu_f(gf[e]);     // h + h tanh(h), h = g / 2: one MUFU op, no division
+          hv[i][e] = (c * 8 + e < H) ? s * uf[e] : 0.f;
+          sum += hv[i][e];
+        }
       }
     }
   }
@@ -423,21 +433,110 @@ swiglu_ln_kernel(const uint4* __restrict__ gu, const float* __restrict__ gamma, 
     const int c = t + 128 * i;
     if (c < Hp8) {
       float o[8];
-      // gamma / beta are padded to Hp by the caller: two 16-byte loads each instead of eight scalar ones
-      const float4 g0 = *reinterpret_cast<const float4*>(gamma + c * 8), g1 = *reinterpret_cast<const float4*>(gamma + c * 8 + 4);
-      const float4 b0 = *reinterpret_cast<const float4*>(beta + c * 8), b1 = *reinterpret_cast<const float4*>(beta + c * 8 + 4);
-      const float gg[8] = {g0.x, g0.y, g0.z, g0.w, g1.x, g1.y, g1.z, g1.w};
-      const float bb[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
+      if (gamma != nullptr) {
+        // gamma / beta are padded to Hp by the caller: two 16-byte loads each instead of eight scalar ones
+        const float4 g0 = *reinterpret_cast<const float4*>(gamma + c * 8), g1 = *reinterpret_cast<const float4*>(gamma + c * 8 + 4);
+        const float4 b0 = *reinterpret_cast<const float4*>(beta + c * 8), b1 = *reinterpret_cast<const float4*>(beta + c * 8 + 4);
+        const float gg[8] = {g0.x, g0.y, g0.z, g0.w, g1.x, g1.y, g1.z, g1.w};
+        const float bb[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
 #pragma unroll
-      for (int e = 0; e < 8; ++e) o[e] = (c * 8 + e < H) ? (hv[i][e] - mean) * rstd * gg[e] + bb[e] : 0.f;
+        for (int e = 0; e < 8; ++e) o[e] = (c * 8 + e < H) ? (hv[i][e] - mean) * rstd * gg[e] + bb[e] : 0.f;
+      } else {
+#pragma unroll
+        for (int e = 0; e < 8; ++e) o[e] = (c * 8 + e < H) ? (hv[i][e] - mean) * rstd : 0.f;
+      }
       y[(size_t)row * Hp8 + c] = v_f32_to_bf16x8(o);
     }
   }
 }
+// LayerNorm over wide rows (the gated fc1 output, 2 816 columns of which 2 730 are real): one WARP per row, up to
+// twelve 8-channel chunks per lane in registers, no block barrier (the two-rows-per-CTA kernel above spent its time
+// in its two __syncthreads: 2.6 TB/s whether it read 406 or 203 MB).
+constexpr int kWideChunks = 12;    // Hp <= 12 * 32 * 8 = 3072
+__global__ void __launch_bounds__(256, 2)
+ln_wide_kernel(const uint4* __restrict__ h, const float* __restrict__ gamma, const float* __restrict__ beta,
+               uint4* __restrict__ y, int rows, int H, int Hp8, float eps) {
+  const int row = (blockIdx.x * 256 + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  if (row >= rows) return;
+  // chunks [0, full) are entirely real columns, chunk `full` may be partial (H % 8 real ones), the rest is padding:
+  // the padding and the partial chunk's tail are zeroed ONCE here, so the passes below carry no per-element masks
+  const int full = H >> 3, tail = H & 7;
+  uint4 raw[kWideChunks];
+#pragma unroll
+  for (int i = 0; i < kWideChunks; ++i) {
+    const int c = lane + 32 * i;
+    raw[i] = c < full + (tail ? 1 : 0) ? h[(size_t)row * Hp8 + c] : make_uint4(0u, 0u, 0u, 0u);
+    if (c == full && tail) {
+      uint32_t w[4] = {raw[i].x, raw[i].y, raw[i].z, raw[i].w};
+#pragma unroll
+      for (int e = 0; e < 8; ++e)
+        if (e >= tail) w[e >> 1] &= (e & 1) ? 0x0000ffffu : 0xffff0000u;
+      raw[i] = make_uint4(w[0], w[1], w[2], w[3]);
+    }
+  }
+  float sum = 0.f;
+#pragma unroll
+  for (int i = 0; i < kWideChunks; ++i) {
+    float f[8];
+    v_bf16x8_to_f32(raw[i], f);
+#pragma unroll
+    for (int e = 0; e < 8; ++e) sum += f[e];
+  }
+#pragma unroll
+  for (int off = 16; off > 0; off >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, off);
+  const float mean = sum / (float)H;
+  // variance about the mean (two-pass): the zeroed columns contribute (0 - mean)^2 each, taken out exactly below
+  float var = 0.f;
+#pragma unroll
+  for (int i = 0; i < kWideChunks; ++i) {
+    float f[8];
+    v_bf16x8_to_f32(raw[i], f);
+#pragma unroll
+    for (int e = 0; e < 8; ++e) {
+      const float d = f[e] - mean;
+      var = fmaf(d, d, var);
+    }
+  }
+#pragma unroll
+  for (int off = 16; off > 0; off >>= 1) var += __shfl_xor_sync(0xffffffffu, var, off);
+  var -= (float)(kWideChunks * 32 * 8 - H) * mean * mean;
+  const float rstd = rsqrtf(fmaxf(var, 0.f) / (float)H + eps);
+#pragma unroll
+  for (int i = 0; i < kWideChunks; ++i) {
+    const int c = lane + 32 * i;
+    if (c < Hp8) {
+      float f[8], o[8];
+      v_bf16x8_to_f32(raw[i], f);
+      if (gamma != nullptr) {
+        const float4 g0 = *reinterpret_cast<const float4*>(gamma + c * 8), g1 = *reinterpret_cast<const float4*>(gamma + c * 8 + 4);
+        const float4 b0 = *reinterpret_cast<const float4*>(beta + c * 8), b1 = *reinterpret_cast<const float4*>(beta + c * 8 + 4);
+        const float gg[8] = {g0.x, g0.y, g0.z, g0.w, g1.x, g1.y, g1.z, g1.w};
+        const float bb[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
+#pragma unroll
+        for (int e = 0; e < 8; ++e) o[e] = (f[e] - mean) * rstd * gg[e] + bb[e];
+      } else {
+#pragma unroll
+        for (int e = 0; e < 8; ++e) o[e] = (f[e] - mean) * rstd;
+      }
+      if (c >= full) {          // the partial chunk's tail and the padding chunks are written as zeros
+#pragma unroll
+        for (int e = 0; e < 8; ++e)
+          if (c > full || e >= tail) o[e] = 0.f;
+      }
+      y[(size_t)row * Hp8 + c] = v_f32_to_bf16x8(o);
+    }
+  }
+}
+
 int swiglu_ln_launch(const void* gu, const float* gamma, const float* beta, void* y, int rows, int H, int Hp,
-                     float eps, cudaStream_t st) {
+                     float eps, int gated, cudaStream_t st) {
+  if (gated && Hp % 8 == 0 && Hp <= kWideChunks * 32 * 8 && H >= 1 && H <= Hp) {
+    ln_wide_kernel<<<cdiv(rows, 8), 256, 0, st>>>((const uint4*)gu, gamma, beta, (uint4*)y, rows, H, Hp / 8, eps);
+    VIT_LAUNCH_OK("ln_wide");
+  }
   TCD_REQUIRE(Hp % 8 == 0 && H <= Hp && Hp <= kSwigluChunks * 128 * 8 && H >= 1, "swiglu_ln: H %d Hp %d", H, Hp);
-  swiglu_ln_kernel<<<cdiv(rows, 2), 256, 0, st>>>((const uint4*)gu, gamma, beta, (uint4*)y, rows, H, Hp / 8, eps);
+  swiglu_ln_kernel<<<cdiv(rows, 2), 256, 0, st>>>((const uint4*)gu, gamma, beta, (uint4*)y, rows, H, Hp / 8, eps, gated);
   VIT_LAUNCH_OK("swiglu_ln");
 }
 

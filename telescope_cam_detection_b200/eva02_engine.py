@@ -25,6 +25,8 @@ from . import _lib
 from ._lib import check
 from .rtdetr_engine import ACT_NONE, Act, Program, to_bf16_bits
 
+ACT_GLU = 4             # gated epilogue of the CTA-pair GEMM (include/tcd.h tcd_conv_desc.act)
+
 # registered EVA02 sizes (timm/models/eva.py): embed_dim -> heads (head_dim is 64 in all of them)
 _HEAD_DIM = 64
 _MAX_COUT = 2048        # conv engine: a layer's bias is staged in shared memory (kConvMaxBias)
@@ -67,7 +69,7 @@ class Eva02Engine:
     `run_topk` is the product path from a device frame and crop boxes.
     """
 
-    def __init__(self, sd, batch, img_size=336, ref_grid=16, ln_eps=1e-6, top_k=5, device=0, keep_taps=False):
+    def __init__(self, sd, batch, img_size=336, ref_grid=16, ln_eps=1e-6, top_k=5, device=0, keep_taps=False, fold_ln=True):
         self.sd = sd
         self.B, self.S = int(batch), int(img_size)
         pw = self._g("patch_embed.proj.weight")
@@ -92,6 +94,11 @@ class Eva02Engine:
         self.lib = _lib.load()
         self.prog = Program(device)
         self.taps = {} if keep_taps else None
+        # Every LayerNorm of the network feeds a Linear, so its affine part folds into that Linear at pack time
+        # (W' = W diag(gamma), b' = b + W beta, in float64): the LayerNorm kernels then load no parameters -- with them
+        # the parameter loads were 4x the data loads per chunk and the kernels L1-bound (ncu: memory pipes 66 % busy at
+        # 35 % of DRAM throughput).  fold_ln=False keeps the affine kernels (A/B, parity).
+        self.fold_ln = bool(fold_ln)
         self._build()
         self.sd = None
 
@@ -128,11 +135,28 @@ class Eva02Engine:
             self.prog.conv(name if cout == cw else "%s[%d:%d]" % (name, c0, c0 + cw), x, w[c0:c0 + cw], b[c0:c0 + cw],
                            act=ACT_NONE, y=y, y_coff=c0, resid=resid, r_coff=c0 if resid is not None else 0)
 
+    @staticmethod
+    def _pad_rows(a, n):
+        out = np.zeros((n,) + a.shape[1:], np.float32)
+        out[:a.shape[0]] = a
+        return out
+
     def _ln(self, name, a, prefix, y, rows):
         P = self.prog
+        if self.fold_ln:
+            P.op(name, "layernorm", [a.ptr, 0, 0, 0, y.ptr], [rows, a.C], [self.ln_eps])
+            return
         g = P.upload(self._g(prefix + ".weight"))
         b = P.upload(self._g(prefix + ".bias"))
         P.op(name, "layernorm", [a.ptr, 0, g, b, y.ptr], [rows, a.C], [self.ln_eps])
+
+    def _fold(self, w, b, prefix):
+        """(w, b) of a Linear that reads LayerNorm `prefix`'s output -> the pair that reads the un-scaled normalisation."""
+        if not self.fold_ln:
+            return w, b
+        g, be = self._g(prefix + ".weight").astype(np.float64), self._g(prefix + ".bias").astype(np.float64)
+        w64 = w.astype(np.float64)
+        return (w64 * g[None, :]).astype(np.float32), (b.astype(np.float64) + w64 @ be).astype(np.float32)
 
     # ---- the program
     def _build(self):
@@ -159,7 +183,13 @@ class Eva02Engine:
         yb = Act(P.alloc(rows * D * 2), 1, 1, rows, D)
         qkv = Act(P.alloc(rows * 3 * D * 2), 1, 1, rows, 3 * D)
         att = Act(P.alloc(rows * D * 2), 1, 1, rows, D)
-        gu = Act(P.alloc(rows * 2 * Hp * 2), 1, 1, rows, 2 * Hp)
+        # The gated epilogue exists in the CTA-pair GEMM only: same eligibility rule as csrc/conv_umma.cu
+        # (gemm_pair_eligible): >= 74 work items of 256 rows x 256 columns, K >= 512 in 64s.
+        self.fuse_glu = D >= 512 and D % 64 == 0 and all(((rows + 255) // 256) * (cw // 256) >= 74 and cw % 256 == 0
+                                                         for _, cw in _chunks(2 * Hp, 256))
+        j = np.arange(Hp)
+        self._glu_g = (j // 128) * 256 + ((j % 128) // 32) * 64 + (j % 32)    # GEMM column of the gate of hidden j
+        gu = Act(P.alloc(rows * Hp * 2), 1, 1, rows, Hp) if self.fuse_glu else Act(P.alloc(rows * 2 * Hp * 2), 1, 1, rows, 2 * Hp)
         hb = Act(P.alloc(rows * Hp * 2), 1, 1, rows, Hp)
         rope = P.upload(rope_cos_sin(self.G, self.ref_grid))
         zeros = np.zeros(D, np.float32)
@@ -177,28 +207,47 @@ class Eva02Engine:
                                        self._g(p + "attn.v_proj.weight")], 0)
                 bk = self._g(p + "attn.k_proj.bias") if self._has(p + "attn.k_proj.bias") else zeros
                 bqkv = np.concatenate([self._g(p + "attn.q_proj.bias"), bk, self._g(p + "attn.v_proj.bias")])
+            wqkv, bqkv = self._fold(wqkv, bqkv, p + "norm1")
             self._linear(n + "qkv", yb, wqkv, bqkv, qkv)
             P.op(n + "mha", "mha_rope", [qkv.ptr, qkv.ptr, qkv.ptr, att.ptr, rope],
                  [3 * D, 0, 3 * D, D, 3 * D, 2 * D, D, B, T, self.heads, 1], [_HEAD_DIM ** -0.5])
             a_in = att
+            wp, bp = self._g(p + "attn.proj.weight"), self._g(p + "attn.proj.bias")
             if self._has(p + "attn.norm.weight"):       # scale_attn_inner (the *_clip_* registrations)
                 self._ln(n + "attn_norm", att, p + "attn.norm", yb, rows)
+                wp, bp = self._fold(wp, bp, p + "attn.norm")
                 a_in = yb
-            self._linear(n + "proj", a_in, self._g(p + "attn.proj.weight"), self._g(p + "attn.proj.bias"), x2, resid=x)
+            self._linear(n + "proj", a_in, wp, bp, x2, resid=x)
             self._ln(n + "norm2", x2, p + "norm2", yb, rows)
             w1 = np.zeros((2 * Hp, D), np.float32)
             b1 = np.zeros(2 * Hp, np.float32)
-            w1[:H], w1[Hp:Hp + H] = self._g(p + "mlp.fc1_g.weight"), self._g(p + "mlp.fc1_x.weight")
-            b1[:H], b1[Hp:Hp + H] = self._g(p + "mlp.fc1_g.bias"), self._g(p + "mlp.fc1_x.bias")
-            self._linear(n + "fc1", yb, w1, b1, gu)
             if not self._has(p + "mlp.norm.weight"):
                 raise KeyError("EVA02 weights: %smlp.norm.* missing (scale_mlp = False variants are not supported)" % p)
-            ng, nb = np.zeros(Hp, np.float32), np.zeros(Hp, np.float32)
-            ng[:H], nb[:H] = self._g(p + "mlp.norm.weight"), self._g(p + "mlp.norm.bias")
-            P.op(n + "swiglu_ln", "swiglu_ln", [gu.ptr, P.upload(ng), P.upload(nb), hb.ptr], [rows, H, Hp], [self.ln_eps])
+            wg, bg = self._fold(self._g(p + "mlp.fc1_g.weight"), self._g(p + "mlp.fc1_g.bias"), p + "norm2")
+            wx, bx = self._fold(self._g(p + "mlp.fc1_x.weight"), self._g(p + "mlp.fc1_x.bias"), p + "norm2")
+            if self.fold_ln:
+                ng_ptr = nb_ptr = 0
+            else:
+                ng, nb = np.zeros(Hp, np.float32), np.zeros(Hp, np.float32)
+                ng[:H], nb[:H] = self._g(p + "mlp.norm.weight"), self._g(p + "mlp.norm.bias")
+                ng_ptr, nb_ptr = P.upload(ng), P.upload(nb)
+            if self.fuse_glu:
+                # gated epilogue of the CTA-pair GEMM: within every 256-column tile the 32-column slabs alternate
+                # gate / value, and the GEMM writes silu(g) * u straight into hb (hidden order, Hp columns)
+                w1[self._glu_g], w1[self._glu_g + 32] = self._pad_rows(wg, Hp), self._pad_rows(wx, Hp)
+                b1[self._glu_g], b1[self._glu_g + 32] = self._pad_rows(bg, Hp), self._pad_rows(bx, Hp)
+                for c0, cw in _chunks(2 * Hp, 256):
+                    P.conv("%sfc1[%d:%d]" % (n, c0, c0 + cw), yb, w1[c0:c0 + cw], b1[c0:c0 + cw], act=ACT_GLU, y=gu, y_coff=c0 // 2)
+                P.op(n + "swiglu_ln", "swiglu_ln", [gu.ptr, ng_ptr, nb_ptr, hb.ptr], [rows, H, Hp, 1], [self.ln_eps])
+            else:
+                w1[:H], w1[Hp:Hp + H] = wg, wx
+                b1[:H], b1[Hp:Hp + H] = bg, bx
+                self._linear(n + "fc1", yb, w1, b1, gu)
+                P.op(n + "swiglu_ln", "swiglu_ln", [gu.ptr, ng_ptr, nb_ptr, hb.ptr], [rows, H, Hp, 0], [self.ln_eps])
             w2 = np.zeros((D, Hp), np.float32)
-            w2[:, :H] = self._g(p + "mlp.fc2.weight")
-            self._linear(n + "fc2", hb, w2, self._g(p + "mlp.fc2.bias"), x, resid=x2)
+            wf2, bf2 = self._fold(self._g(p + "mlp.fc2.weight"), self._g(p + "mlp.fc2.bias"), p + "mlp.norm")
+            w2[:, :H] = wf2
+            self._linear(n + "fc2", hb, w2, bf2, x, resid=x2)
             self._tap("block%d" % i, x)
         # read-out: final LayerNorm on the class tokens only, head, softmax, top-k
         cls = Act(P.alloc(B * D * 2), 1, 1, B, D)
@@ -208,7 +257,7 @@ class Eva02Engine:
         self._ln("norm", cls, "norm", clsn, B)
         self.ld_logits = (self.NC + _HEAD_CHUNK - 1) // _HEAD_CHUNK * _HEAD_CHUNK
         self.logits = P.f32(B * self.ld_logits)
-        hw, hbias = self._g("head.weight"), self._g("head.bias")
+        hw, hbias = self._fold(self._g("head.weight"), self._g("head.bias"), "norm")
         if D <= 1024:
             # few rows x many classes: a weight-streaming kernel (csrc/vit_kernels.cu head_gemv), one launch
             P.op("head", "head_gemv", [clsn.ptr, P.upload(to_bf16_bits(hw)), P.upload(hbias), self.logits],
