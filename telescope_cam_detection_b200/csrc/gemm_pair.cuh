@@ -24,8 +24,8 @@ namespace tcd {
 
 constexpr int kGpABytes = 128 * 64 * 2;            // 128 token rows x 64 channels
 constexpr int kGpStageBytes = 2 * kGpABytes;       // + this CTA's 128 weight rows x 64 channels
-constexpr int kGpStages = 4;
-constexpr int kGpStaging = 128 * 256 * 2;          // 128 rows x 256 output channels, four 64-channel chunks
+constexpr int kGpStages = 5;                       // 160 KiB in flight per SM: at 64 B/clk and ~2 500 cycles of L2 latency four were too few
+constexpr int kGpStaging = 128 * 128 * 2;          // 128 rows x 128 output channels, two 64-channel chunks (drained in two phases)
 constexpr int kGpMaxCout = kConvMaxBias;
 constexpr int kGpSmem = kGpStages * kGpStageBytes + kGpStaging + 1024;
 
@@ -171,45 +171,53 @@ gemm_pair_kernel(const __grid_constant__ ConvMaps maps, const __grid_constant__ 
       const bool valid = x < p.Wo;
       mbar_wait(&tmem_full_bar[acc], (uint32_t)(it >> 1) & 1u);
       tc_fence_after();
-      if (it > 0) {
-        if (warp == 2 && lane == 0) tma_store_wait_read();    // the previous tile's stores have read the staging
-        asm volatile("bar.sync 1, %0;" ::"n"(32 * kConvEpiWarps) : "memory");
-      }
       const uint32_t taddr = tmem_base + (uint32_t)(acc * 256) + ((uint32_t)(q * 32) << 16);
       uint32_t ra[32], rb[32];
-      tmem_ld32(taddr, ra);
+      tmem_ld32(taddr, ra);       // the first slab is on its way while the staging area is still being read
+      // The staging area holds 128 output columns (32 KiB; the ring gets the fifth stage instead): the plain form
+      // drains its 256 columns in two phases, the gated form writes 128 columns in one.
+      constexpr int kPhases = ACT == 4 ? 1 : 2;
+      constexpr int kSlabs = 8 / kPhases;
 #pragma unroll
-      for (int sl = 0; sl < 8; sl += 2) {
-        tmem_ld_wait();
-        tmem_ld32(taddr + 32 * (sl + 1), rb);
-        if constexpr (ACT != 4) conv_finish_cols<32, 0, ACT, 0>(p, ra, 32 * sl, s_bias, row, valid, c, 0, x, staging);
-        tmem_ld_wait();
-        if constexpr (ACT == 4) {
-          // slab sl = gate, slab sl + 1 = value of hidden columns n_tile * 128 + sl * 16 .. + 31
-          const float* bg = s_bias + c.n_tile * 256 + 32 * sl;
-          float v[32];
+      for (int ph = 0; ph < kPhases; ++ph) {
+        if (it > 0 || ph > 0) {
+          if (warp == 2 && lane == 0) tma_store_wait_read();    // the previous stores have read the staging
+          asm volatile("bar.sync 1, %0;" ::"n"(32 * kConvEpiWarps) : "memory");
+        }
+        uint8_t* stg = staging - (size_t)ph * 2 * 128 * 128;     // conv_finish_cols places column c0 in chunk c0 / 64
 #pragma unroll
-          for (int i = 0; i < 32; ++i)
-            v[i] = silu_f(__uint_as_float(ra[i]) + bg[i]) * (__uint_as_float(rb[i]) + bg[32 + i]);
-          gp_stage_slab(v, 16 * sl, row, staging);
+        for (int sl = ph * kSlabs; sl < (ph + 1) * kSlabs; sl += 2) {
+          tmem_ld_wait();
+          tmem_ld32(taddr + 32 * (sl + 1), rb);
+          if constexpr (ACT != 4) conv_finish_cols<32, 0, ACT, 0>(p, ra, 32 * sl, s_bias, row, valid, c, 0, x, stg);
+          tmem_ld_wait();
+          if constexpr (ACT == 4) {
+            // slab sl = gate, slab sl + 1 = value of hidden columns n_tile * 128 + sl * 16 .. + 31
+            const float* bg = s_bias + c.n_tile * 256 + 32 * sl;
+            float v[32];
+#pragma unroll
+            for (int i = 0; i < 32; ++i)
+              v[i] = silu_f(__uint_as_float(ra[i]) + bg[i]) * (__uint_as_float(rb[i]) + bg[32 + i]);
+            gp_stage_slab(v, 16 * sl, row, staging);
+          }
+          if (sl + 2 < 8) {
+            tmem_ld32(taddr + 32 * (sl + 2), ra);
+          } else {
+            // every column has been read: hand the accumulator back to the leader's MMA thread
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive_cluster(acc ? empty_leader1 : empty_leader0);
+          }
+          if constexpr (ACT != 4) conv_finish_cols<32, 0, ACT, 0>(p, rb, 32 * (sl + 1), s_bias, row, valid, c, 0, x, stg);
         }
-        if (sl + 2 < 8) {
-          tmem_ld32(taddr + 32 * (sl + 2), ra);
-        } else {
-          // every column has been read: hand the accumulator back to the leader's MMA thread
-          tc_fence_before();
-          __syncwarp();
-          if (lane == 0) mbar_arrive_cluster(acc ? empty_leader1 : empty_leader0);
+        fence_proxy_async_smem();
+        asm volatile("bar.sync 1, %0;" ::"n"(32 * kConvEpiWarps) : "memory");
+        if (warp == 2 && lane == 0) {
+          constexpr int kOutCols = ACT == 4 ? 128 : 256;     // the gated form writes half as many columns
+          for (int ch = 0; ch < 2; ++ch)
+            tma_store_4d(&maps.o, staging + (size_t)ch * 128 * 128, p.cout_off + c.n_tile * kOutCols + (ph * 2 + ch) * 64, c.x0, 0, 0);
+          tma_store_commit();
         }
-        if constexpr (ACT != 4) conv_finish_cols<32, 0, ACT, 0>(p, rb, 32 * (sl + 1), s_bias, row, valid, c, 0, x, staging);
-      }
-      fence_proxy_async_smem();
-      asm volatile("bar.sync 1, %0;" ::"n"(32 * kConvEpiWarps) : "memory");
-      if (warp == 2 && lane == 0) {
-        constexpr int kOutCols = ACT == 4 ? 128 : 256;     // the gated form writes half as many columns
-        for (int ch = 0; ch < kOutCols / 64; ++ch)
-          tma_store_4d(&maps.o, staging + (size_t)ch * 128 * 128, p.cout_off + c.n_tile * kOutCols + ch * 64, c.x0, 0, 0);
-        tma_store_commit();
       }
     }
     if (warp == 2 && lane == 0) tma_store_wait_read();
