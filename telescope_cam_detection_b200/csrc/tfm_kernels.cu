@@ -38,7 +38,8 @@ __device__ __forceinline__ uint4 f32_to_bf16x8(const float (&f)[8]) {
 
 // ------------------------------------------------------------------ LayerNorm(a + b)
 // one warp per row; each lane owns C/256 chunks of 8 channels (C <= 1024)
-__global__ void __launch_bounds__(256)
+template <bool AFFINE>
+__global__ void __launch_bounds__(256, AFFINE ? 4 : 5)
 layernorm_kernel(const uint4* __restrict__ a, const uint4* __restrict__ b, const float* __restrict__ gamma,
                  const float* __restrict__ beta, uint4* __restrict__ y, int rows, int C8, float eps) {
   const int row = (blockIdx.x * 256 + threadIdx.x) >> 5;
@@ -84,7 +85,7 @@ layernorm_kernel(const uint4* __restrict__ a, const uint4* __restrict__ b, const
     const int c = lane + 32 * i;
     if (c < C8) {
       float o[8];
-      if (gamma != nullptr) {
+      if constexpr (AFFINE) {
         // gamma / beta as two 16-byte loads each (eight scalar loads per chunk made the kernel LSU-bound: 1.8 TB/s)
         const float4 g0 = *reinterpret_cast<const float4*>(gamma + c * 8), g1 = *reinterpret_cast<const float4*>(gamma + c * 8 + 4);
         const float4 b0 = *reinterpret_cast<const float4*>(beta + c * 8), b1 = *reinterpret_cast<const float4*>(beta + c * 8 + 4);
@@ -105,8 +106,10 @@ layernorm_kernel(const uint4* __restrict__ a, const uint4* __restrict__ b, const
 int layernorm_launch(const void* a, const void* b, const float* gamma, const float* beta, void* y,
                      int rows, int C, float eps, cudaStream_t st) {
   TCD_REQUIRE(C % 8 == 0 && C <= 1024, "layernorm: C %d unsupported", C);
-  layernorm_kernel<<<cdiv(rows, 8), 256, 0, st>>>((const uint4*)a, (const uint4*)b, gamma, beta, (uint4*)y,
-                                                 rows, C / 8, eps);
+  if (gamma != nullptr)
+    layernorm_kernel<true><<<cdiv(rows, 8), 256, 0, st>>>((const uint4*)a, (const uint4*)b, gamma, beta, (uint4*)y, rows, C / 8, eps);
+  else   // no affine part (folded into the consumer): fewer registers, five CTAs per SM
+    layernorm_kernel<false><<<cdiv(rows, 8), 256, 0, st>>>((const uint4*)a, (const uint4*)b, gamma, beta, (uint4*)y, rows, C / 8, eps);
   TFM_LAUNCH_OK("layernorm");
 }
 
