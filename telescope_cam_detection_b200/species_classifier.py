@@ -107,9 +107,7 @@ class SpeciesClassifier:
             if not self.checkpoint_path:
                 raise RuntimeError("%s: pretrained weights come from the HuggingFace hub in the reference "
                                    "(pretrained=True); give checkpoint_path= or weights= here" % self.model_name)
-            import torch
-            ck = torch.load(self.checkpoint_path, map_location="cpu")
-            sd = ck["model_state_dict"] if "model_state_dict" in ck else ck
+            sd = self._read_checkpoint(self.checkpoint_path)
         sd = {k: (v.detach().cpu().float().numpy() if hasattr(v, "detach") else np.asarray(v, np.float32))
               for k, v in sd.items()}
         if sd["head.weight"].shape[0] != num_classes:
@@ -136,6 +134,18 @@ class SpeciesClassifier:
         for e in self._engines.values():
             e.close()
         self._engines, self.engine, self._sd = {}, None, None
+
+    @staticmethod
+    def _read_checkpoint(path: str) -> Dict[str, Any]:
+        """State dict of a checkpoint file: a torch pickle as the reference loads it (`model_state_dict` or the dict
+        itself, reference :265-267), or the `model.safetensors` file timm's hub models ship as."""
+        if str(path).endswith(".safetensors"):
+            from safetensors.numpy import load_file
+            return dict(load_file(str(path)))
+        import torch
+        ck = torch.load(path, map_location="cpu")
+        sd = ck["model_state_dict"] if "model_state_dict" in ck else ck
+        return sd.get("state_dict", sd) if isinstance(sd, dict) else sd
 
     def load_model(self, num_classes: int = 1000, max_retries: int = 3) -> bool:
         from .eva02_engine import is_eva02

@@ -98,3 +98,19 @@ def test_species_classifier_fails_loudly_without_a_body():
         cfg = eva02.Eva02Config(img_size=112, embed_dim=64, depth=1, num_heads=1, num_classes=10)
         clf = SpeciesClassifier(model_name="eva02_tiny_patch14_224", input_size=112, weights=eva02.make_model(cfg).state_dict())
         assert clf.load_model(10) is False and clf.engine is None     # no sm_100 device: no CPU fallback
+
+
+def test_checkpoint_readers(tmp_path):
+    """The native body takes its weights from a torch pickle (the reference's checkpoint_path form) or a safetensors
+    file (what timm's hub models ship); both come back as the same state dict."""
+    from telescope_cam_detection_b200.species_classifier import SpeciesClassifier
+    cfg = eva02.Eva02Config(img_size=112, embed_dim=64, depth=1, num_heads=1, num_classes=10)
+    sd = eva02.make_model(cfg).state_dict()
+    torch.save({"model_state_dict": sd}, tmp_path / "a.pth")
+    torch.save(sd, tmp_path / "b.pth")
+    from safetensors.numpy import save_file
+    save_file({k: v.numpy() for k, v in sd.items()}, str(tmp_path / "c.safetensors"))
+    for name in ("a.pth", "b.pth", "c.safetensors"):
+        got = SpeciesClassifier._read_checkpoint(str(tmp_path / name))
+        assert set(got) == set(sd)
+        assert np.array_equal(np.asarray(got["head.weight"]), sd["head.weight"].numpy())
