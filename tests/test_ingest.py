@@ -69,7 +69,14 @@ def test_full_queue_drops_frames_without_consuming_ids():
     q = queue.Queue(maxsize=3)
     cap = _cap(q, 30, delay=0.002)
     cap.start()
-    time.sleep(1.0)                      # nobody reads: 3 frames queued, 27 dropped
+    # nobody reads: 3 frames queued, 27 dropped.  Wait for the writer's LAST frame rather than a fixed time (the
+    # decoder process needs anything from 0.3 s to well over a second to start on a loaded host).
+    t0 = time.time()
+    while time.time() - t0 < 30.0:
+        latest = cap.get_latest_frame_as_numpy()
+        if latest is not None and np.array_equal(latest, _expect(29)):
+            break
+        time.sleep(0.05)
     stats = cap.get_stats()
     items = _drain(q, 3, timeout=2.0)
     cap.stop()
