@@ -267,11 +267,13 @@ static bool gemm_pair_eligible(const ConvDesc& d, int mode) {
   if (d.x_nstride || d.y_nstride || d.r_nstride) return false;
   if (d.cin % 64 || d.cin < 512 || d.cout != d.cout_pad || d.cout % 256 || d.cout > kGpMaxCout) return false;
   const int share = d.share >= 0 ? d.share : env_int("TCD_CONV_SHARE", 2, 0);
-  if (share != 0) return false;             // whole-SM plans (the layer programs): a pair owns two SMs outright
+  // whole-SM plans (the layer programs): a pair owns two SMs outright.  TCD_GEMM_PAIR_SHARED=1 also lets the layers
+  // of the half-SM detector pipeline take it (A/B measurement)
+  if (share != 0 && !env_int("TCD_GEMM_PAIR_SHARED", 0, 0)) return false;
   const long rows = (long)d.N * d.H * d.W;
   if (rows >= (1L << 30)) return false;
   const long work = (long)cdiv(cdiv((int)rows, 128), 2) * (d.cout / 256);
-  return work >= sm_count() / 2;
+  return work >= env_int("TCD_GEMM_PAIR_MIN_WORK", sm_count() / 2);
 }
 
 static int gemm_pair_plan_build(const ConvDesc& d0, ConvPlan* plan) {
