@@ -472,7 +472,7 @@ def rtdetr_side(local, batch, peaks):
     return res
 
 
-def classifier_side(local, batch, peaks, model_name="timm/eva02_large_patch14_clip_336.merged2b_ft_inat21"):
+def classifier_side(local, batch, peaks, model_name="timm/eva02_large_patch14_clip_336.merged2b_ft_inat21", through_class=True):
     """BASELINE configs[4], Stage 2: `batch` crops of one 1080p device frame -> patch-row
     gather -> the shipped configuration's classifier body (EVA02-L/14 at 336, 10 000 classes, random-init weights) ->
     softmax / top-k.  Graph replays incl. the gather, CUDA events on the program's stream; per-op eager pass."""
@@ -540,6 +540,8 @@ def classifier_side(local, batch, peaks, model_name="timm/eva02_large_patch14_cl
            "ms_by_op_kind_eager": {k: round(v, 3) for k, v in sorted(by_kind.items(), key=lambda kv: -kv[1])},
            "top1_prob_mean": float(p[:, 0].mean())}
     eng.close()
+    if not through_class:
+        return res
     # BASELINE configs[4] through the reference's classes: TwoStageDetectionPipeline.process_detections(frame, dets) with a
     # SpeciesClassifier built from the same weights (src/two_stage_pipeline_yolox.py:203-451: crop geometry with 30 %
     # padding as the shipped config sets it, batched gather, classifier, softmax / top-k, taxonomy + result dicts)
@@ -1068,6 +1070,11 @@ def run_ours(args):
     if not args.no_aux and world == 1 and args.classifier_batch > 0:
         try:
             classifier = classifier_side(local, args.classifier_batch, peaks)
+            # BASELINE configs[4] names 224 x 224 crops: the same family at its 224 registration (257 tokens per crop)
+            c224 = classifier_side(local, args.classifier_batch, peaks, model_name="timm/eva02_large_patch14_clip_224.merged2b",
+                                   through_class=False)
+            classifier["at_224"] = {k: c224[k] for k in ("workload", "crops_per_s", "ms_per_batch", "gflop_per_crop", "tflops",
+                                                         "frac_bf16_burst")}
         except Exception as e:  # noqa: BLE001
             classifier = {"error": repr(e)}
     ingest = None
