@@ -384,13 +384,17 @@ typedef struct {
   void* y; int32_t y_ctot, y_coff; int64_t y_nstride; /* bf16 output view (NULL when out_f32 is set)   */
   const void* resid; int32_t r_ctot, r_coff, resid_pre; int64_t r_nstride;
   float* out_f32; int32_t out_ld, out_col, rows_per_img, row_off;  /* f32 row output (logits etc.)    */
+  /* LayerNorm applied by the CONSUMER (token linears on CTA pairs only): x is the UN-normalised tensor, ln_stats holds   */
+  /* (mean, 1/std) per row (TCD_OP_ROW_STATS) and ln_colsum_host the sums over cin of the (bf16-rounded) weight rows:     */
+  /* y = rstd * (x W^T - mean * colsum) + bias -- the normalised tensor is never written.  NULL: plain linear.            */
+  const float* ln_stats; const float* ln_colsum_host;
 } tcd_conv_desc;
 enum {
   TCD_OP_LAYERNORM = 1, TCD_OP_ADD_ROWS, TCD_OP_MASK_ROWS, TCD_OP_MHA, TCD_OP_MSDA, TCD_OP_ROWMAX,
   TCD_OP_TOPK, TCD_OP_GATHER, TCD_OP_REF_INIT, TCD_OP_REF_UPDATE, TCD_OP_DETR_POST, TCD_OP_MAXPOOL,
   TCD_OP_AVGPOOL, TCD_OP_UPSAMPLE,
   /* Stage-2 classifier body (EVA02 vision transformer) */
-  TCD_OP_VIT_ASSEMBLE, TCD_OP_MHA_ROPE, TCD_OP_SWIGLU_LN, TCD_OP_SOFTMAX, TCD_OP_TAKE, TCD_OP_HEAD_GEMV
+  TCD_OP_VIT_ASSEMBLE, TCD_OP_MHA_ROPE, TCD_OP_SWIGLU_LN, TCD_OP_SOFTMAX, TCD_OP_TAKE, TCD_OP_HEAD_GEMV, TCD_OP_ROW_STATS
 };
 typedef struct {
   char name[64];

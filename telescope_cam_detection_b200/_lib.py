@@ -45,7 +45,8 @@ class ConvDesc(C.Structure):
                 ("resid", C.c_void_p), ("r_ctot", C.c_int32), ("r_coff", C.c_int32), ("resid_pre", C.c_int32),
                 ("r_nstride", C.c_int64),
                 ("out_f32", C.c_void_p), ("out_ld", C.c_int32), ("out_col", C.c_int32),
-                ("rows_per_img", C.c_int32), ("row_off", C.c_int32)]
+                ("rows_per_img", C.c_int32), ("row_off", C.c_int32),
+                ("ln_stats", C.c_void_p), ("ln_colsum_host", C.c_void_p)]
 
 
 class OpDesc(C.Structure):
@@ -56,7 +57,7 @@ class OpDesc(C.Structure):
 
 OP_KINDS = {"layernorm": 1, "add_rows": 2, "mask_rows": 3, "mha": 4, "msda": 5, "rowmax": 6, "topk": 7,
             "gather": 8, "ref_init": 9, "ref_update": 10, "detr_post": 11, "maxpool": 12, "avgpool": 13,
-            "upsample": 14, "vit_assemble": 15, "mha_rope": 16, "swiglu_ln": 17, "softmax": 18, "take": 19, "head_gemv": 20}
+            "upsample": 14, "vit_assemble": 15, "mha_rope": 16, "swiglu_ln": 17, "softmax": 18, "take": 19, "head_gemv": 20, "row_stats": 21}
 
 
 class EnhanceCfg(C.Structure):

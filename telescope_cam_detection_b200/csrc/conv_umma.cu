@@ -261,7 +261,8 @@ static GemmPairKernelFn gemm_pair_kernel_variant(int act) {
 }
 
 static bool gemm_pair_eligible(const ConvDesc& d, int mode) {
-  if (!env_int("TCD_GEMM_PAIR", 1, 0) && d.silu != 4) return false;
+  if (!env_int("TCD_GEMM_PAIR", 1, 0) && d.silu != 4 && !d.ln_stats) return false;
+  if (d.ln_stats && d.silu != 0 && d.silu != 4) return false;   // the normalising epilogue exists for the plain and gated forms
   if (mode != 0 || d.k != 1 || d.stride != 1 || d.groups != 1) return false;
   // dense views only: a 1x1 conv over a dense NHWC tensor IS a GEMM over its N*H*W pixel rows (token rows: N = H = 1)
   if (d.x_nstride || d.y_nstride || d.r_nstride) return false;
@@ -291,6 +292,8 @@ static int gemm_pair_plan_build(const ConvDesc& d0, ConvPlan* plan) {
   a.resid = (const __nv_bfloat16*)d.resid; a.r_ctot = d.r_ctot; a.r_coff = d.r_coff; a.resid_pre = d.resid_pre;
   a.r_nstride = (long long)d.W * d.r_ctot;
   a.pdl = g_use_pdl;
+  a.ln_stats = d.ln_stats;
+  a.ln_colsum = d.ln_colsum;
   a.n_tiles_n = d.cout / 256;
   plan->pair = 2;
   plan->pair_n_tiles = d.cout / 256;
@@ -400,6 +403,7 @@ int conv_plan_build(const ConvDesc& d, ConvPlan* plan) {
   TCD_REQUIRE(!(d.silu == 4 && d.resid), "conv: the gated epilogue takes no residual");
   if (pair_eligible(d, mode)) return pair_plan_build(d, plan);
   if (gemm_pair_eligible(d, mode)) return gemm_pair_plan_build(d, plan);
+  TCD_REQUIRE(d.ln_stats == nullptr, "conv: the normalising epilogue exists for CTA-pair GEMM shapes only");
   TCD_REQUIRE(d.silu != 4, "conv: the gated (SwiGLU) epilogue exists for CTA-pair GEMM shapes only (1x1, dense rows, Cin >= 512 in "
                            "64s, Cout in 256s, >= %d tile pairs)", sm_count() / 2);
   TCD_REQUIRE(d.silu >= 0 && d.silu <= 3, "conv: activation %d", d.silu);

@@ -83,6 +83,9 @@ struct ConvArgs {
   int* maybe_count;             // [images]
   int* maybe_idx;               // [images][maybe_cap] anchor indices (row_off + y * Wo + x)
   int maybe_cap, emit_col;      // emit_col: accumulator column of the objectness logit
+  // gemm_pair.cuh only: LayerNorm applied in the epilogue -- (mean, 1/std) per input row and the column sums of the weights
+  const float* ln_stats;        // [rows][2], nullptr: plain linear
+  const float* ln_colsum;       // [cout]
 };
 
 #if defined(__CUDACC__) && defined(TCD_CONV_KERNEL_IMPL)
@@ -692,6 +695,8 @@ struct ConvDesc {
   float* out_f32 = nullptr;
   int out_ld = 0, out_col = 0, rows_per_img = 0, row_off = 0;
   // f32 rows only: candidate emission (see ConvArgs)
+  const float* ln_stats = nullptr;    // consumer-side LayerNorm (CTA-pair GEMM only), see ConvArgs
+  const float* ln_colsum = nullptr;
   const float* emit_thr = nullptr;
   int* maybe_count = nullptr;
   int* maybe_idx = nullptr;

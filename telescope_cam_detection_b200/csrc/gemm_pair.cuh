@@ -64,6 +64,7 @@ gemm_pair_kernel(const __grid_constant__ ConvMaps maps, const __grid_constant__ 
   __shared__ uint64_t tmem_full_bar[2];
   __shared__ uint64_t tmem_empty_bar[2];
   __shared__ __align__(16) float s_bias[kGpMaxCout];
+  __shared__ __align__(16) float s_cs[kGpMaxCout];     // column sums of the weights (consumer-side LayerNorm), else unused
   __shared__ uint32_t tmem_base_s;
 
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
@@ -94,7 +95,10 @@ gemm_pair_kernel(const __grid_constant__ ConvMaps maps, const __grid_constant__ 
   if (warp == 1) tmem_alloc2(&tmem_base_s, 512);
   if (warp >= 2)
     for (int i = threadIdx.x - 64; i < p.bias_n; i += 32 * kConvEpiWarps)
+    {
       s_bias[i] = (ACT == 1 ? 0.5f : 1.0f) * __ldg(p.bias + i);   // SiLU layers: see conv_finish_silu
+      if (p.ln_stats != nullptr) s_cs[i] = __ldg(p.ln_colsum + i);
+    }
   tc_fence_before();
   __syncthreads();
   cluster_sync_all();                    // the peer's barriers are initialised before anything arrives on them
@@ -156,7 +160,7 @@ gemm_pair_kernel(const __grid_constant__ ConvMaps maps, const __grid_constant__ 
     // ------------------------------------------------------------------ epilogue (4 warps per CTA, own 128 rows)
     const int q = warp & 3;
     const int row = q * 32 + lane;
-    if (p.pdl && p.resid != nullptr) pdl_wait();
+    if (p.pdl && (p.resid != nullptr || p.ln_stats != nullptr)) pdl_wait();   // both are the previous kernels' outputs
     const uint32_t empty_leader0 = mapa_u32(smem_u32(&tmem_empty_bar[0]), 0);
     const uint32_t empty_leader1 = mapa_u32(smem_u32(&tmem_empty_bar[1]), 0);
     for (int it = 0; it < n_mine; ++it) {
@@ -169,6 +173,13 @@ gemm_pair_kernel(const __grid_constant__ ConvMaps maps, const __grid_constant__ 
       c.x0 = (2 * (w / ga.n_tiles) + (int)rank) * 128;
       const int x = c.x0 + row;
       const bool valid = x < p.Wo;
+      // consumer-side LayerNorm: y = rstd * (acc - mean * colsum) + bias, (mean, rstd) of this thread's input row
+      float ln_mean = 0.f, ln_rstd = 1.f;
+      if (p.ln_stats != nullptr && valid) {
+        const float2 st2 = __ldg(reinterpret_cast<const float2*>(p.ln_stats) + x);
+        ln_mean = st2.x;
+        ln_rstd = st2.y;
+      }
       mbar_wait(&tmem_full_bar[acc], (uint32_t)(it >> 1) & 1u);
       tc_fence_after();
       const uint32_t taddr = tmem_base + (uint32_t)(acc * 256) + ((uint32_t)(q * 32) << 16);
@@ -199,14 +210,26 @@ gemm_pair_kernel(const __grid_constant__ ConvMaps maps, const __grid_constant__ 
         }
         auto finish_plain = [&](const uint32_t (&r)[32], int sl) {     // ACT == 0: bias (+ residual) -> bf16 -> staging
           const float4* b4 = reinterpret_cast<const float4*>(s_bias + c.n_tile * 256 + 32 * sl);
+          const float4* c4 = reinterpret_cast<const float4*>(s_cs + c.n_tile * 256 + 32 * sl);
           float v[32];
+          if (p.ln_stats != nullptr) {
 #pragma unroll
-          for (int j = 0; j < 8; ++j) {
-            const float4 b = b4[j];
-            v[4 * j + 0] = __uint_as_float(r[4 * j + 0]) + b.x;
-            v[4 * j + 1] = __uint_as_float(r[4 * j + 1]) + b.y;
-            v[4 * j + 2] = __uint_as_float(r[4 * j + 2]) + b.z;
-            v[4 * j + 3] = __uint_as_float(r[4 * j + 3]) + b.w;
+            for (int j = 0; j < 8; ++j) {
+              const float4 b = b4[j], cs = c4[j];
+              v[4 * j + 0] = fmaf(ln_rstd, fmaf(-ln_mean, cs.x, __uint_as_float(r[4 * j + 0])), b.x);
+              v[4 * j + 1] = fmaf(ln_rstd, fmaf(-ln_mean, cs.y, __uint_as_float(r[4 * j + 1])), b.y);
+              v[4 * j + 2] = fmaf(ln_rstd, fmaf(-ln_mean, cs.z, __uint_as_float(r[4 * j + 2])), b.z);
+              v[4 * j + 3] = fmaf(ln_rstd, fmaf(-ln_mean, cs.w, __uint_as_float(r[4 * j + 3])), b.w);
+            }
+          } else {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+              const float4 b = b4[j];
+              v[4 * j + 0] = __uint_as_float(r[4 * j + 0]) + b.x;
+              v[4 * j + 1] = __uint_as_float(r[4 * j + 1]) + b.y;
+              v[4 * j + 2] = __uint_as_float(r[4 * j + 2]) + b.z;
+              v[4 * j + 3] = __uint_as_float(r[4 * j + 3]) + b.w;
+            }
           }
           if (use_res) {
 #pragma unroll
@@ -232,10 +255,18 @@ gemm_pair_kernel(const __grid_constant__ ConvMaps maps, const __grid_constant__ 
           if constexpr (ACT == 4) {
             // slab sl = gate, slab sl + 1 = value of hidden columns n_tile * 128 + sl * 16 .. + 31
             const float* bg = s_bias + c.n_tile * 256 + 32 * sl;
+            const float* cg = s_cs + c.n_tile * 256 + 32 * sl;
             float v[32];
+            if (p.ln_stats != nullptr) {
 #pragma unroll
-            for (int i = 0; i < 32; ++i)
-              v[i] = silu_f(__uint_as_float(ra[i]) + bg[i]) * (__uint_as_float(rb[i]) + bg[32 + i]);
+              for (int i = 0; i < 32; ++i)
+                v[i] = silu_f(fmaf(ln_rstd, fmaf(-ln_mean, cg[i], __uint_as_float(ra[i])), bg[i])) *
+                       fmaf(ln_rstd, fmaf(-ln_mean, cg[32 + i], __uint_as_float(rb[i])), bg[32 + i]);
+            } else {
+#pragma unroll
+              for (int i = 0; i < 32; ++i)
+                v[i] = silu_f(__uint_as_float(ra[i]) + bg[i]) * (__uint_as_float(rb[i]) + bg[32 + i]);
+            }
             gp_stage_slab(v, 16 * sl, row, staging);
           }
           if (sl + 2 < 8) {

@@ -86,6 +86,8 @@ int launch_small(const tcd_op_desc& d, cudaStream_t st) {
       return softmax_rows_launch((const float*)p[0], i[2], (float*)p[1], i[3], i[0], i[1], st);
     case TCD_OP_HEAD_GEMV:  // p: x, w, bias, out; i: B, K, NC, ld
       return head_gemv_launch(p[0], p[1], (const float*)p[2], (float*)p[3], i[0], i[1], i[2], i[3], st);
+    case TCD_OP_ROW_STATS:  // p: x, stats; i: rows, H, Hp; f: eps
+      return row_stats_launch(p[0], (float*)p[1], i[0], i[1], i[2], d.f[0], st);
     case TCD_OP_TAKE:  // p: src, idx, out; i: N, k, ld
       return take_f32_launch((const float*)p[0], i[2], (const int*)p[1], (float*)p[2], i[0], i[1], st);
   }
@@ -186,6 +188,16 @@ tcd_status tcd_program_add_conv(tcd_program* p, const tcd_conv_desc* c) {
     const char* e = getenv("TCD_PROGRAM_SHARE");
     d.share = e ? atoi(e) : 0;
   }
+  if (c->ln_stats) {
+    TCD_REQUIRE(c->ln_colsum_host, "add_conv: ln_stats without ln_colsum_host");
+    std::vector<float> hc(cout_pad, 0.f);
+    memcpy(hc.data(), c->ln_colsum_host, sizeof(float) * c->cout);
+    void* dc = nullptr;
+    rc = tcd_program_upload(p, hc.data(), hc.size() * 4, &dc);
+    if (rc) return rc;
+    d.ln_stats = c->ln_stats;
+    d.ln_colsum = (const float*)dc;
+  }
   d.out_f32 = c->out_f32; d.out_ld = c->out_ld; d.out_col = c->out_col; d.rows_per_img = c->rows_per_img;
   d.row_off = c->row_off;
   ProgOp op;
@@ -205,7 +217,7 @@ tcd_status tcd_program_add_conv(tcd_program* p, const tcd_conv_desc* c) {
 tcd_status tcd_program_add_op(tcd_program* p, const tcd_op_desc* d) {
   TCD_REQUIRE(p && d, "add_op: null argument");
   TCD_REQUIRE(p->graph == nullptr, "add_op: program already captured");
-  TCD_REQUIRE(d->kind >= TCD_OP_LAYERNORM && d->kind <= TCD_OP_HEAD_GEMV, "add_op: kind %d", d->kind);
+  TCD_REQUIRE(d->kind >= TCD_OP_LAYERNORM && d->kind <= TCD_OP_ROW_STATS, "add_op: kind %d", d->kind);
   ProgOp op;
   op.name = std::string(d->name, strnlen(d->name, sizeof(d->name)));
   op.kind = d->kind;

@@ -79,6 +79,9 @@ int swiglu_ln_launch(const void* gu, const float* gamma, const float* beta, void
 // out[b,c] = x[b,:] . w[c,:] + bias[c]: x bf16 [B,K], w bf16 [NC,K] (K <= 1024, K % 8 == 0), out f32 [B, ld]
 int head_gemv_launch(const void* x, const void* w, const float* bias, float* out, int B, int K, int NC, int ld,
                      cudaStream_t st);
+// stats[r] = (mean, 1/sqrt(var + eps)) over the first H columns of bf16 row r (row stride Hp, Hp <= 3072): the
+// LayerNorm statistics for a consumer that normalises in its own epilogue (gemm_pair.cuh)
+int row_stats_launch(const void* x, float* stats, int rows, int H, int Hp, float eps, cudaStream_t st);
 int softmax_rows_launch(const float* x, int ldx, float* y, int ldy, int rows, int C, cudaStream_t st);
 // out[n,i] = src[n*ld + idx[n*k+i]]
 int take_f32_launch(const float* src, int ld, const int* idx, float* out, int N, int k, cudaStream_t st);

@@ -529,6 +529,65 @@ ln_wide_kernel(const uint4* __restrict__ h, const float* __restrict__ gamma, con
   }
 }
 
+// LayerNorm statistics only: one warp per row reads the row once and writes (mean, 1 / std) -- 8 bytes -- for a
+// consumer GEMM that normalises in its epilogue: y = rstd * (x W'^T - mean * colsum(W')) + b'.  The normalised
+// tensor (151 MB per LayerNorm, 203 MB for the MLP's hidden one at 64 crops) is never written or re-read.
+template <int CH>      // 8-channel chunks per lane: 4 covers rows of <= 1024 columns (40 registers, full occupancy), 12 up to 3072
+__global__ void __launch_bounds__(256, CH <= 4 ? 6 : 2)
+row_stats_kernel(const uint4* __restrict__ h, float2* __restrict__ stats, int rows, int H, int Hp8, float eps) {
+  const int row = (blockIdx.x * 256 + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  if (row >= rows) return;
+  const int full = H >> 3, tail = H & 7;
+  uint4 raw[CH];
+#pragma unroll
+  for (int i = 0; i < CH; ++i) {
+    const int c = lane + 32 * i;
+    raw[i] = c < full + (tail ? 1 : 0) ? h[(size_t)row * Hp8 + c] : make_uint4(0u, 0u, 0u, 0u);
+    if (c == full && tail) {
+      uint32_t w[4] = {raw[i].x, raw[i].y, raw[i].z, raw[i].w};
+#pragma unroll
+      for (int e = 0; e < 8; ++e)
+        if (e >= tail) w[e >> 1] &= (e & 1) ? 0x0000ffffu : 0xffff0000u;
+      raw[i] = make_uint4(w[0], w[1], w[2], w[3]);
+    }
+  }
+  float sum = 0.f;
+#pragma unroll
+  for (int i = 0; i < CH; ++i) {
+    float f[8];
+    v_bf16x8_to_f32(raw[i], f);
+#pragma unroll
+    for (int e = 0; e < 8; ++e) sum += f[e];
+  }
+#pragma unroll
+  for (int off = 16; off > 0; off >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, off);
+  const float mean = sum / (float)H;
+  float var = 0.f;
+#pragma unroll
+  for (int i = 0; i < CH; ++i) {
+    float f[8];
+    v_bf16x8_to_f32(raw[i], f);
+#pragma unroll
+    for (int e = 0; e < 8; ++e) {
+      const float d = f[e] - mean;
+      var = fmaf(d, d, var);
+    }
+  }
+#pragma unroll
+  for (int off = 16; off > 0; off >>= 1) var += __shfl_xor_sync(0xffffffffu, var, off);
+  var -= (float)(CH * 32 * 8 - H) * mean * mean;     // the zeroed slots contributed (0 - mean)^2 each
+  if (lane == 0) stats[row] = make_float2(mean, rsqrtf(fmaxf(var, 0.f) / (float)H + eps));
+}
+int row_stats_launch(const void* x, float* stats, int rows, int H, int Hp, float eps, cudaStream_t st) {
+  TCD_REQUIRE(Hp % 8 == 0 && Hp <= kWideChunks * 32 * 8 && H >= 1 && H <= Hp, "row_stats: H %d Hp %d", H, Hp);
+  if (Hp <= 4 * 32 * 8)
+    row_stats_kernel<4><<<cdiv(rows, 8), 256, 0, st>>>((const uint4*)x, (float2*)stats, rows, H, Hp / 8, eps);
+  else
+    row_stats_kernel<kWideChunks><<<cdiv(rows, 8), 256, 0, st>>>((const uint4*)x, (float2*)stats, rows, H, Hp / 8, eps);
+  VIT_LAUNCH_OK("row_stats");
+}
+
 int swiglu_ln_launch(const void* gu, const float* gamma, const float* beta, void* y, int rows, int H, int Hp,
                      float eps, int gated, cudaStream_t st) {
   if (gated && Hp % 8 == 0 && Hp <= kWideChunks * 32 * 8 && H >= 1 && H <= Hp) {

@@ -49,6 +49,12 @@ def rope_cos_sin(grid, ref_grid, head_dim=_HEAD_DIM, temperature=10000.0):
     return np.stack([np.cos(ang), np.sin(ang)], -1).astype(np.float32)
 
 
+def _colsum_bf16(w):
+    """Sum over the input channels of every weight row AS THE TENSOR CORE SEES IT (rounded to bf16), float64 accumulate."""
+    bits = to_bf16_bits(np.ascontiguousarray(w, np.float32).reshape(w.shape[0], -1))
+    return (bits.astype(np.uint32) << 16).view(np.float32).astype(np.float64).sum(1).astype(np.float32)
+
+
 def _chunks(cout, step, cap=_MAX_COUT):
     """Split cout columns into pieces of <= cap that are multiples of `step` (the last one takes the remainder)."""
     n = max(1, math.ceil(cout / cap))
@@ -69,7 +75,8 @@ class Eva02Engine:
     `run_topk` is the product path from a device frame and crop boxes.
     """
 
-    def __init__(self, sd, batch, img_size=336, ref_grid=16, ln_eps=1e-6, top_k=5, device=0, keep_taps=False, fold_ln=True):
+    def __init__(self, sd, batch, img_size=336, ref_grid=16, ln_eps=1e-6, top_k=5, device=0, keep_taps=False, fold_ln=True,
+                 ln_in_gemm=True):
         self.sd = sd
         self.B, self.S = int(batch), int(img_size)
         pw = self._g("patch_embed.proj.weight")
@@ -99,6 +106,9 @@ class Eva02Engine:
         # the parameter loads were 4x the data loads per chunk and the kernels L1-bound (ncu: memory pipes 66 % busy at
         # 35 % of DRAM throughput).  fold_ln=False keeps the affine kernels (A/B, parity).
         self.fold_ln = bool(fold_ln)
+        # Where every Linear behind a LayerNorm is a CTA-pair GEMM (many crops), the LayerNorm is applied in that GEMM's
+        # epilogue from per-row (mean, 1/std): the normalised tensors are never written.  ln_in_gemm=False: A/B, parity.
+        self.ln_in_gemm_wanted = bool(ln_in_gemm)
         self._build()
         self.sd = None
 
@@ -125,21 +135,36 @@ class Eva02Engine:
         P.op("tap." + name, "gather", [act.ptr, self._tap_idx, keep.ptr], [1, rows, rows, act.C])
         self.taps[name] = keep
 
-    def _linear(self, name, x, w, b, y, resid=None, step=256):
+    def _linear(self, name, x, w, b, y, resid=None, step=256, ln_stats=None):
         """y[:, :cout] = x @ w.T + b (+ resid), split along cout so that each launch stays within the engine's bias
-        staging limit.  x, y, resid: flat token views [1,1,rows,C]."""
+        staging limit.  x, y, resid: flat token views [1,1,rows,C].  ln_stats: x is un-normalised and the launch applies
+        the LayerNorm whose (mean, 1/std) per row sit at that device address (w, b already hold its affine part)."""
         cout = w.shape[0]
         if cout % step:
             step = 128 if cout % 128 == 0 else 32
+        cs = _colsum_bf16(w) if ln_stats is not None else None
         for c0, cw in _chunks(cout, step):
             self.prog.conv(name if cout == cw else "%s[%d:%d]" % (name, c0, c0 + cw), x, w[c0:c0 + cw], b[c0:c0 + cw],
-                           act=ACT_NONE, y=y, y_coff=c0, resid=resid, r_coff=c0 if resid is not None else 0)
+                           act=ACT_NONE, y=y, y_coff=c0, resid=resid, r_coff=c0 if resid is not None else 0,
+                           ln_stats=ln_stats, ln_colsum=None if cs is None else cs[c0:c0 + cw])
 
     @staticmethod
     def _pad_rows(a, n):
         out = np.zeros((n,) + a.shape[1:], np.float32)
         out[:a.shape[0]] = a
         return out
+
+    def _norm(self, name, a, prefix, y, rows, width=None):
+        """LayerNorm `prefix` of `a` for a following Linear -> (tensor the Linear reads, ln_stats for it).  With
+        consumer-side normalisation only the row statistics are computed here (8 bytes per row) and the Linear reads `a`
+        itself; otherwise the normalised rows are written to `y`."""
+        if self.ln_in_gemm:
+            stats = self._stats[self._stats_i % len(self._stats)]
+            self._stats_i += 1
+            self.prog.op(name + ".stats", "row_stats", [a.ptr, stats], [rows, width or a.C, a.C], [self.ln_eps])
+            return a, stats
+        self._ln(name, a, prefix, y, rows)
+        return y, None
 
     def _ln(self, name, a, prefix, y, rows):
         P = self.prog
@@ -187,6 +212,14 @@ class Eva02Engine:
         # (gemm_pair_eligible): >= 74 work items of 256 rows x 256 columns, K >= 512 in 64s.
         self.fuse_glu = D >= 512 and D % 64 == 0 and all(((rows + 255) // 256) * (cw // 256) >= 74 and cw % 256 == 0
                                                          for _, cw in _chunks(2 * Hp, 256))
+        # Consumer-side LayerNorm (csrc/gemm_pair.cuh): every Linear that follows a LayerNorm must be a CTA-pair GEMM
+        def pair_ok(cin, cout):
+            return cin >= 512 and cin % 64 == 0 and all(cw % 256 == 0 and ((rows + 255) // 256) * (cw // 256) >= 74
+                                                        for _, cw in _chunks(cout, 256))
+        self.ln_in_gemm = (self.fold_ln and self.fuse_glu and self.ln_in_gemm_wanted and pair_ok(D, 3 * D) and pair_ok(D, D)
+                           and pair_ok(Hp, D))
+        self._stats = [P.f32(rows * 2), P.f32(rows * 2)] if self.ln_in_gemm else []
+        self._stats_i = 0
         j = np.arange(Hp)
         self._glu_g = (j // 128) * 256 + ((j % 128) // 32) * 64 + (j % 32)    # GEMM column of the gate of hidden j
         gu = Act(P.alloc(rows * Hp * 2), 1, 1, rows, Hp) if self.fuse_glu else Act(P.alloc(rows * 2 * Hp * 2), 1, 1, rows, 2 * Hp)
@@ -196,7 +229,7 @@ class Eva02Engine:
         for i in range(self.depth):
             p = "blocks.%d." % i
             n = "b%d." % i
-            self._ln(n + "norm1", x, p + "norm1", yb, rows)
+            a_in, st = self._norm(n + "norm1", x, p + "norm1", yb, rows)
             if self._has(p + "attn.qkv.weight"):
                 wqkv = self._g(p + "attn.qkv.weight")
                 bq = self._g(p + "attn.q_bias") if self._has(p + "attn.q_bias") else zeros
@@ -208,17 +241,16 @@ class Eva02Engine:
                 bk = self._g(p + "attn.k_proj.bias") if self._has(p + "attn.k_proj.bias") else zeros
                 bqkv = np.concatenate([self._g(p + "attn.q_proj.bias"), bk, self._g(p + "attn.v_proj.bias")])
             wqkv, bqkv = self._fold(wqkv, bqkv, p + "norm1")
-            self._linear(n + "qkv", yb, wqkv, bqkv, qkv)
+            self._linear(n + "qkv", a_in, wqkv, bqkv, qkv, ln_stats=st)
             P.op(n + "mha", "mha_rope", [qkv.ptr, qkv.ptr, qkv.ptr, att.ptr, rope],
                  [3 * D, 0, 3 * D, D, 3 * D, 2 * D, D, B, T, self.heads, 1], [_HEAD_DIM ** -0.5])
-            a_in = att
+            a_in, st = att, None
             wp, bp = self._g(p + "attn.proj.weight"), self._g(p + "attn.proj.bias")
             if self._has(p + "attn.norm.weight"):       # scale_attn_inner (the *_clip_* registrations)
-                self._ln(n + "attn_norm", att, p + "attn.norm", yb, rows)
+                a_in, st = self._norm(n + "attn_norm", att, p + "attn.norm", yb, rows)
                 wp, bp = self._fold(wp, bp, p + "attn.norm")
-                a_in = yb
-            self._linear(n + "proj", a_in, wp, bp, x2, resid=x)
-            self._ln(n + "norm2", x2, p + "norm2", yb, rows)
+            self._linear(n + "proj", a_in, wp, bp, x2, resid=x, ln_stats=st)
+            a_in, st = self._norm(n + "norm2", x2, p + "norm2", yb, rows)
             w1 = np.zeros((2 * Hp, D), np.float32)
             b1 = np.zeros(2 * Hp, np.float32)
             if not self._has(p + "mlp.norm.weight"):
@@ -236,18 +268,25 @@ class Eva02Engine:
                 # gate / value, and the GEMM writes silu(g) * u straight into hb (hidden order, Hp columns)
                 w1[self._glu_g], w1[self._glu_g + 32] = self._pad_rows(wg, Hp), self._pad_rows(wx, Hp)
                 b1[self._glu_g], b1[self._glu_g + 32] = self._pad_rows(bg, Hp), self._pad_rows(bx, Hp)
+                cs1 = _colsum_bf16(w1) if st is not None else None
                 for c0, cw in _chunks(2 * Hp, 256):
-                    P.conv("%sfc1[%d:%d]" % (n, c0, c0 + cw), yb, w1[c0:c0 + cw], b1[c0:c0 + cw], act=ACT_GLU, y=gu, y_coff=c0 // 2)
-                P.op(n + "swiglu_ln", "swiglu_ln", [gu.ptr, ng_ptr, nb_ptr, hb.ptr], [rows, H, Hp, 1], [self.ln_eps])
+                    P.conv("%sfc1[%d:%d]" % (n, c0, c0 + cw), a_in, w1[c0:c0 + cw], b1[c0:c0 + cw], act=ACT_GLU, y=gu, y_coff=c0 // 2,
+                           ln_stats=st, ln_colsum=None if cs1 is None else cs1[c0:c0 + cw])
+                if self.ln_in_gemm:
+                    h_in, st = self._norm(n + "mlp_norm", gu, p + "mlp.norm", hb, rows, width=H)
+                else:
+                    P.op(n + "swiglu_ln", "swiglu_ln", [gu.ptr, ng_ptr, nb_ptr, hb.ptr], [rows, H, Hp, 1], [self.ln_eps])
+                    h_in, st = hb, None
             else:
                 w1[:H], w1[Hp:Hp + H] = wg, wx
                 b1[:H], b1[Hp:Hp + H] = bg, bx
-                self._linear(n + "fc1", yb, w1, b1, gu)
+                self._linear(n + "fc1", a_in, w1, b1, gu)
                 P.op(n + "swiglu_ln", "swiglu_ln", [gu.ptr, ng_ptr, nb_ptr, hb.ptr], [rows, H, Hp, 0], [self.ln_eps])
+                h_in, st = hb, None
             w2 = np.zeros((D, Hp), np.float32)
             wf2, bf2 = self._fold(self._g(p + "mlp.fc2.weight"), self._g(p + "mlp.fc2.bias"), p + "mlp.norm")
             w2[:, :H] = wf2
-            self._linear(n + "fc2", hb, w2, bf2, x, resid=x2)
+            self._linear(n + "fc2", h_in, w2, bf2, x, resid=x2, ln_stats=st)
             self._tap("block%d" % i, x)
         # read-out: final LayerNorm on the class tokens only, head, softmax, top-k
         cls = Act(P.alloc(B * D * 2), 1, 1, B, D)

@@ -119,7 +119,7 @@ class Program:
         return self.alloc(n * 4)
 
     def conv(self, name, x, w, b, k=1, stride=1, act=ACT_NONE, y=None, y_coff=0, x_coff=0, resid=None,
-             r_coff=0, resid_pre=0, out_f32=None, out_ld=0):
+             r_coff=0, resid_pre=0, out_f32=None, out_ld=0, ln_stats=None, ln_colsum=None):
         """w: [cout, cin, k, k] float32 (BN already folded), b: [cout]."""
         w = np.ascontiguousarray(w, np.float32).reshape(w.shape[0], -1, k, k)
         b = np.ascontiguousarray(b, np.float32)
@@ -135,6 +135,9 @@ class Program:
             d.y, d.y_ctot, d.y_coff, d.y_nstride = y.ptr, y.C, y_coff, y.nstride
         if resid is not None:
             d.resid, d.r_ctot, d.r_coff, d.resid_pre, d.r_nstride = resid.ptr, resid.C, r_coff, resid_pre, resid.nstride
+        if ln_stats is not None:       # LayerNorm applied in the consumer's epilogue (include/tcd.h tcd_conv_desc.ln_stats)
+            cs = np.ascontiguousarray(ln_colsum, np.float32)
+            d.ln_stats, d.ln_colsum_host = int(ln_stats), cs.ctypes.data
         check(self.lib.tcd_program_add_conv(self.handle, C.byref(d)), "tcd_program_add_conv(%s)" % name)
 
     def op(self, name, kind, ptrs, ints, floats=()):

@@ -145,6 +145,45 @@ def test_token_linear_on_cta_pairs(rows, cin, cout, act, resid):
     P.close()
 
 
+@pytest.mark.parametrize("H,Hp,act", [(1024, 1024, 0), (2730, 2816, 0), (512, 512, 4)])
+def test_layernorm_applied_in_the_pair_gemm_epilogue(H, Hp, act):
+    """row_stats (8 bytes per row) + a CTA-pair GEMM that reads the UN-normalised rows and normalises in its epilogue:
+    y = rstd * (x W'^T - mean * colsum(W')) + b'  ==  Linear(LayerNorm(x)) with the affine part folded into W', b'."""
+    import torch
+    from telescope_cam_detection_b200.eva02_engine import _colsum_bf16
+    from telescope_cam_detection_b200.rtdetr_engine import Act
+    torch.manual_seed(9)
+    P = _prog()
+    rows, cout = 19000 + 3, 512
+    x = torch.zeros(rows, Hp)
+    x[:, :H] = torch.randn(rows, H) * 2.0 + 0.4           # a row mean the correction term has to remove
+    x = _bf16(x)
+    g, be = torch.rand(H) + 0.5, torch.randn(H) * 0.1
+    n_out = cout * (2 if act == 4 else 1)
+    w = torch.randn(n_out, H) / H ** 0.5
+    b = torch.randn(n_out) * 0.1
+    wf = torch.zeros(n_out, Hp)
+    wf[:, :H] = _bf16(w * g[None])                        # what the engine packs: W diag(gamma), rounded like the GEMM operand
+    bf = b + w @ be
+    X = _up_bf16(P, x, (1, 1, rows, Hp))
+    stats = P.f32(rows * 2)
+    P.op("stats", "row_stats", [X.ptr, stats], [rows, H, Hp], [1e-6])
+    Y = Act(P.alloc(rows * cout * 2), 1, 1, rows, cout)
+    P.conv("lin", X, wf.numpy().reshape(n_out, Hp, 1, 1), bf.numpy(), act=act, y=Y, ln_stats=stats, ln_colsum=_colsum_bf16(wf.numpy()))
+    P.run(False); P.sync()
+    st = torch.from_numpy(P.d2h(stats, (rows, 2), np.float32))
+    xv = x[:, :H]
+    assert torch.allclose(st[:, 0], xv.mean(1), atol=1e-4) and torch.allclose(st[:, 1], (xv.var(1, unbiased=False) + 1e-6).rsqrt(), rtol=1e-4)
+    ln = (xv - xv.mean(1, keepdim=True)) * (xv.var(1, unbiased=False, keepdim=True) + 1e-6).rsqrt()
+    ref = ln @ wf[:, :H].T + bf
+    if act == 4:          # interleaved 32-column slabs: gate / value
+        r4 = ref.view(rows, n_out // 64, 2, 32)
+        ref = (torch.nn.functional.silu(r4[:, :, 0]) * r4[:, :, 1]).reshape(rows, cout)
+    got = torch.from_numpy(P.read_bf16(Y))[0, 0]
+    assert torch.allclose(got, ref, atol=4e-2, rtol=2e-2), float((got - ref).abs().max())
+    P.close()
+
+
 def test_gated_fc1_on_cta_pairs_and_layernorm():
     """fc1_g || fc1_x with the gated epilogue (act 4: interleaved 32-column slabs, silu(g) * u written directly) followed
     by the LayerNorm-only mode of swiglu_ln, against torch fp32 on the same bf16 operands."""
@@ -295,9 +334,17 @@ def test_eva02_many_crops_pair_gemm_and_gated_mlp():
     from telescope_cam_detection_b200.eva02_engine import Eva02Engine
     from oracle import eva02
     cfg = eva02.Eva02Config(img_size=336, embed_dim=512, depth=1, num_heads=8, num_classes=100)
-    eng = Eva02Engine(eva02.state_dict_numpy(eva02.make_model(cfg, 4)), batch=40, img_size=336, top_k=5)
-    assert eng.fuse_glu
+    sd = eva02.state_dict_numpy(eva02.make_model(cfg, 4))
+    x = eva02.synthetic_input(cfg, 40, seed=5).numpy()
+    eng = Eva02Engine(sd, batch=40, img_size=336, top_k=5)
+    assert eng.fuse_glu and eng.ln_in_gemm            # LayerNorms applied inside the consumer GEMMs' epilogues
+    a = eng.forward(x)
     eng.close()
+    eng = Eva02Engine(sd, batch=40, img_size=336, top_k=5, ln_in_gemm=False)   # normalised rows written by LayerNorm kernels
+    assert not eng.ln_in_gemm
+    b = eng.forward(x)
+    eng.close()
+    assert float(np.abs(a - b).max()) <= 0.08, float(np.abs(a - b).max())     # two bf16 pipelines, same network
     _compare(cfg, batch=40, n=40, seed=4)
 
 
