@@ -388,6 +388,13 @@ typedef struct {
   /* (mean, 1/std) per row (TCD_OP_ROW_STATS) and ln_colsum_host the sums over cin of the (bf16-rounded) weight rows:     */
   /* y = rstd * (x W^T - mean * colsum) + bias -- the normalised tensor is never written.  NULL: plain linear.            */
   const float* ln_stats; const float* ln_colsum_host;
+  /* ln_parts > 0: ln_stats holds ln_parts partial (sum, sum of squares) pairs per row instead -- written by the PRODUCER of  */
+  /* x (stats_out of the launches that wrote it, or TCD_OP_ROW_STATS) -- over ln_count columns; eps = ln_eps.               */
+  int32_t ln_parts, ln_count; float ln_eps;
+  /* stats_out (CTA-pair GEMM only): every 256-column tile (128 for act 4) of this launch also writes the (sum, sum of      */
+  /* squares) of its output values per row to stats_out[row * stats_parts + stats_slot0 + tile]: LayerNorm statistics for   */
+  /* the next consumer without another pass over the tensor.                                                               */
+  float* stats_out; int32_t stats_parts, stats_slot0;
 } tcd_conv_desc;
 enum {
   TCD_OP_LAYERNORM = 1, TCD_OP_ADD_ROWS, TCD_OP_MASK_ROWS, TCD_OP_MHA, TCD_OP_MSDA, TCD_OP_ROWMAX,

@@ -46,7 +46,9 @@ class ConvDesc(C.Structure):
                 ("r_nstride", C.c_int64),
                 ("out_f32", C.c_void_p), ("out_ld", C.c_int32), ("out_col", C.c_int32),
                 ("rows_per_img", C.c_int32), ("row_off", C.c_int32),
-                ("ln_stats", C.c_void_p), ("ln_colsum_host", C.c_void_p)]
+                ("ln_stats", C.c_void_p), ("ln_colsum_host", C.c_void_p),
+                ("ln_parts", C.c_int32), ("ln_count", C.c_int32), ("ln_eps", C.c_float),
+                ("stats_out", C.c_void_p), ("stats_parts", C.c_int32), ("stats_slot0", C.c_int32)]
 
 
 class OpDesc(C.Structure):

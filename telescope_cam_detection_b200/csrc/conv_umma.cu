@@ -261,7 +261,8 @@ static GemmPairKernelFn gemm_pair_kernel_variant(int act) {
 }
 
 static bool gemm_pair_eligible(const ConvDesc& d, int mode) {
-  if (!env_int("TCD_GEMM_PAIR", 1, 0) && d.silu != 4 && !d.ln_stats) return false;
+  if (!env_int("TCD_GEMM_PAIR", 1, 0) && d.silu != 4 && !d.ln_stats && !d.stats_out) return false;
+  if (d.stats_out && d.silu != 0 && d.silu != 4) return false;
   if (d.ln_stats && d.silu != 0 && d.silu != 4) return false;   // the normalising epilogue exists for the plain and gated forms
   if (mode != 0 || d.k != 1 || d.stride != 1 || d.groups != 1) return false;
   // dense views only: a 1x1 conv over a dense NHWC tensor IS a GEMM over its N*H*W pixel rows (token rows: N = H = 1)
@@ -294,6 +295,8 @@ static int gemm_pair_plan_build(const ConvDesc& d0, ConvPlan* plan) {
   a.pdl = g_use_pdl;
   a.ln_stats = d.ln_stats;
   a.ln_colsum = d.ln_colsum;
+  a.ln_parts = d.ln_parts; a.ln_count = d.ln_count; a.ln_eps = d.ln_eps;
+  a.stats_out = d.stats_out; a.stats_parts = d.stats_parts; a.stats_slot0 = d.stats_slot0;
   a.n_tiles_n = d.cout / 256;
   plan->pair = 2;
   plan->pair_n_tiles = d.cout / 256;
@@ -403,7 +406,8 @@ int conv_plan_build(const ConvDesc& d, ConvPlan* plan) {
   TCD_REQUIRE(!(d.silu == 4 && d.resid), "conv: the gated epilogue takes no residual");
   if (pair_eligible(d, mode)) return pair_plan_build(d, plan);
   if (gemm_pair_eligible(d, mode)) return gemm_pair_plan_build(d, plan);
-  TCD_REQUIRE(d.ln_stats == nullptr, "conv: the normalising epilogue exists for CTA-pair GEMM shapes only");
+  TCD_REQUIRE(d.ln_stats == nullptr && d.stats_out == nullptr,
+              "conv: the normalising / statistics epilogues exist for CTA-pair GEMM shapes only");
   TCD_REQUIRE(d.silu != 4, "conv: the gated (SwiGLU) epilogue exists for CTA-pair GEMM shapes only (1x1, dense rows, Cin >= 512 in "
                            "64s, Cout in 256s, >= %d tile pairs)", sm_count() / 2);
   TCD_REQUIRE(d.silu >= 0 && d.silu <= 3, "conv: activation %d", d.silu);

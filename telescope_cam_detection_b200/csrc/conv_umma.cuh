@@ -84,8 +84,12 @@ struct ConvArgs {
   int* maybe_idx;               // [images][maybe_cap] anchor indices (row_off + y * Wo + x)
   int maybe_cap, emit_col;      // emit_col: accumulator column of the objectness logit
   // gemm_pair.cuh only: LayerNorm applied in the epilogue -- (mean, 1/std) per input row and the column sums of the weights
-  const float* ln_stats;        // [rows][2], nullptr: plain linear
+  const float* ln_stats;        // [rows][2] (mean, rstd), or [rows][ln_parts][2] partial (sum, sumsq); nullptr: plain linear
   const float* ln_colsum;       // [cout]
+  int ln_parts, ln_count;       // ln_parts > 0: partial sums over ln_count columns
+  float ln_eps;
+  float* stats_out;             // [rows][stats_parts][2]: (sum, sumsq) of this launch's output tiles per row, or nullptr
+  int stats_parts, stats_slot0;
 };
 
 #if defined(__CUDACC__) && defined(TCD_CONV_KERNEL_IMPL)
@@ -697,6 +701,10 @@ struct ConvDesc {
   // f32 rows only: candidate emission (see ConvArgs)
   const float* ln_stats = nullptr;    // consumer-side LayerNorm (CTA-pair GEMM only), see ConvArgs
   const float* ln_colsum = nullptr;
+  int ln_parts = 0, ln_count = 0;
+  float ln_eps = 0.f;
+  float* stats_out = nullptr;
+  int stats_parts = 0, stats_slot0 = 0;
   const float* emit_thr = nullptr;
   int* maybe_count = nullptr;
   int* maybe_idx = nullptr;

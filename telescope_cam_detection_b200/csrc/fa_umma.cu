@@ -87,7 +87,8 @@ __device__ __forceinline__ void fa_rope_chunk(uint4& q, const float2* rope, int 
 __global__ void __launch_bounds__(kFaThreads, 1)
 fa64_umma_kernel(const __nv_bfloat16* __restrict__ q, int ldq, int qoff, const __nv_bfloat16* __restrict__ k, int ldk,
                  int koff, const __nv_bfloat16* __restrict__ v, int ldv, int voff, __nv_bfloat16* __restrict__ out, int ldo,
-                 int T, float scale_log2, const float2* __restrict__ rope, int prefix, int n_tiles, int n_last, int hd8, int trace) {
+                 int T, float scale_log2, const float2* __restrict__ rope, int prefix, int n_tiles, int n_last, int hd8, int trace,
+                 float2* __restrict__ stats_out) {
   extern __shared__ uint8_t fa_raw[];
   __shared__ uint32_t tr[2][8][8];   // TCD_FA_TRACE=1: clock stamps of CTA (0,0,0), first query tile (printed at exit)
   const bool tracing = trace != 0 && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0;
@@ -419,10 +420,15 @@ fa64_umma_kernel(const __nv_bfloat16* __restrict__ q, int ldq, int qoff, const _
         if (tok < T && half * 4 < hd8) {
           __nv_bfloat16* orow = out + ((size_t)n * T + tok) * ldo + h * (hd8 * 8) + half * 32;
           uint32_t w[16];
+          float ps = 0.f, pss = 0.f;      // LayerNorm statistics of the row for the consumer: this (head, half)'s partial
 #pragma unroll
-          for (int i = 0; i < 32; i += 2)
-            w[i >> 1] = pack_bf16x2(fmaf(o[i], c_prev, __uint_as_float(og[i])) * inv,
-                                    fmaf(o[i + 1], c_prev, __uint_as_float(og[i + 1])) * inv);
+          for (int i = 0; i < 32; i += 2) {
+            const float a0 = fmaf(o[i], c_prev, __uint_as_float(og[i])) * inv, a1 = fmaf(o[i + 1], c_prev, __uint_as_float(og[i + 1])) * inv;
+            ps += a0 + a1;
+            pss = fmaf(a0, a0, fmaf(a1, a1, pss));
+            w[i >> 1] = pack_bf16x2(a0, a1);
+          }
+          if (stats_out != nullptr) stats_out[((size_t)n * T + tok) * (gridDim.y * 2) + h * 2 + half] = make_float2(ps, pss);
 #pragma unroll
           for (int c4 = 0; c4 < 4; ++c4)
             *reinterpret_cast<uint4*>(orow + c4 * 8) = make_uint4(w[c4 * 4], w[c4 * 4 + 1], w[c4 * 4 + 2], w[c4 * 4 + 3]);
@@ -457,8 +463,9 @@ bool fa64_umma_eligible(int T) { return g_fa_enabled && T >= 1 && T <= kFaMaxTil
 
 int fa64_umma_launch(const void* q, int ldq, int qoff, const void* k, int ldk, int koff, const void* v, int ldv, int voff,
                      void* out, int ldo, int N, int T, int heads, int head_dim, float scale, const float* rope, int prefix,
-                     cudaStream_t st) {
+                     float* stats_out, cudaStream_t st) {
   TCD_REQUIRE(head_dim == 64 || (head_dim == 32 && rope == nullptr), "fa64: head_dim %d unsupported", head_dim);
+  TCD_REQUIRE(stats_out == nullptr || head_dim == 64, "fa64: row statistics need head_dim 64");
   const int n_tiles = (T + kFaTile - 1) / kFaTile;
   TCD_REQUIRE(n_tiles >= 1 && n_tiles <= kFaMaxTiles, "fa64: %d tokens unsupported", T);
   TCD_REQUIRE(ldq % 8 == 0 && ldk % 8 == 0 && ldv % 8 == 0 && ldo % 8 == 0 && qoff % 8 == 0 && koff % 8 == 0 &&
@@ -473,7 +480,7 @@ int fa64_umma_launch(const void* q, int ldq, int qoff, const void* k, int ldk, i
   if (gx > n_tiles) gx = n_tiles;
   fa64_umma_kernel<<<dim3(gx, heads, N), kFaThreads, smem, st>>>(
       (const __nv_bfloat16*)q, ldq, qoff, (const __nv_bfloat16*)k, ldk, koff, (const __nv_bfloat16*)v, ldv, voff,
-      (__nv_bfloat16*)out, ldo, T, scale * 1.4426950408889634f, (const float2*)rope, prefix, n_tiles, n_last, head_dim / 8, g_fa_trace ? 1 : 0);
+      (__nv_bfloat16*)out, ldo, T, scale * 1.4426950408889634f, (const float2*)rope, prefix, n_tiles, n_last, head_dim / 8, g_fa_trace ? 1 : 0, (float2*)stats_out);
   g_launch_count.fetch_add(1, std::memory_order_relaxed);
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) {

@@ -176,10 +176,27 @@ gemm_pair_kernel(const __grid_constant__ ConvMaps maps, const __grid_constant__ 
       // consumer-side LayerNorm: y = rstd * (acc - mean * colsum) + bias, (mean, rstd) of this thread's input row
       float ln_mean = 0.f, ln_rstd = 1.f;
       if (p.ln_stats != nullptr && valid) {
-        const float2 st2 = __ldg(reinterpret_cast<const float2*>(p.ln_stats) + x);
-        ln_mean = st2.x;
-        ln_rstd = st2.y;
+        if (p.ln_parts > 0) {
+          // partial (sum, sum of squares) pairs written by the producers of x (fixed order: deterministic)
+          // (ln_parts is even -- 4, 22, 32 in the classifier body: two partials per 16-byte load, four loads in flight)
+          const float4* pp = reinterpret_cast<const float4*>(reinterpret_cast<const float2*>(p.ln_stats) + (size_t)x * p.ln_parts);
+          float su = 0.f, sq = 0.f;
+#pragma unroll 4
+          for (int i = 0; i < (p.ln_parts >> 1); ++i) {
+            const float4 t4 = __ldg(pp + i);
+            su += t4.x + t4.z;
+            sq += t4.y + t4.w;
+          }
+          const float inv_n = 1.0f / (float)p.ln_count;
+          ln_mean = su * inv_n;
+          ln_rstd = rsqrtf(fmaxf(fmaf(-ln_mean, ln_mean, sq * inv_n), 0.f) + p.ln_eps);
+        } else {
+          const float2 st2 = __ldg(reinterpret_cast<const float2*>(p.ln_stats) + x);
+          ln_mean = st2.x;
+          ln_rstd = st2.y;
+        }
       }
+      float ps_out = 0.f, pss_out = 0.f;     // (sum, sum of squares) of this row's outputs in this tile (stats_out)
       mbar_wait(&tmem_full_bar[acc], (uint32_t)(it >> 1) & 1u);
       tc_fence_after();
       const uint32_t taddr = tmem_base + (uint32_t)(acc * 256) + ((uint32_t)(q * 32) << 16);
@@ -243,6 +260,13 @@ gemm_pair_kernel(const __grid_constant__ ConvMaps maps, const __grid_constant__ 
               }
             }
           }
+          if (p.stats_out != nullptr) {
+#pragma unroll
+            for (int i = 0; i < 32; ++i) {
+              ps_out += v[i];
+              pss_out = fmaf(v[i], v[i], pss_out);
+            }
+          }
           gp_stage_slab(v, 32 * (sl & 3), row, staging);
         };
 #pragma unroll
@@ -267,6 +291,13 @@ gemm_pair_kernel(const __grid_constant__ ConvMaps maps, const __grid_constant__ 
               for (int i = 0; i < 32; ++i)
                 v[i] = silu_f(__uint_as_float(ra[i]) + bg[i]) * (__uint_as_float(rb[i]) + bg[32 + i]);
             }
+            if (p.stats_out != nullptr) {
+#pragma unroll
+              for (int i = 0; i < 32; ++i) {
+                ps_out += v[i];
+                pss_out = fmaf(v[i], v[i], pss_out);
+              }
+            }
             gp_stage_slab(v, 16 * sl, row, staging);
           }
           if (sl + 2 < 8) {
@@ -289,6 +320,8 @@ gemm_pair_kernel(const __grid_constant__ ConvMaps maps, const __grid_constant__ 
           tma_store_commit();
         }
       }
+      if (p.stats_out != nullptr && valid)
+        reinterpret_cast<float2*>(p.stats_out)[(size_t)x * p.stats_parts + p.stats_slot0 + c.n_tile] = make_float2(ps_out, pss_out);
     }
     if (warp == 2 && lane == 0) tma_store_wait_read();
   }

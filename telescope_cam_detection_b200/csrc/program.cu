@@ -77,17 +77,17 @@ int launch_small(const tcd_op_desc& d, cudaStream_t st) {
       return upsample2x_launch(p[0], p[1], i[0], i[1], i[2], i[3], i[4], i[5], i[6], i[7], st);
     case TCD_OP_VIT_ASSEMBLE:  // p: emb, pos, x; i: N, T, D
       return vit_assemble_launch(p[0], (const float*)p[1], p[2], i[0], i[1], i[2], st);
-    case TCD_OP_MHA_ROPE:  // p: q, k, v, out, rope; i: ldq,qoff,ldk,koff,ldv,voff,ldo,N,T,heads,prefix; f: scale
+    case TCD_OP_MHA_ROPE:  // p: q, k, v, out, rope, stats_out (opt); i: ldq,qoff,ldk,koff,ldv,voff,ldo,N,T,heads,prefix; f: scale
       return mha64_rope_launch(p[0], i[0], i[1], p[1], i[2], i[3], p[2], i[4], i[5], p[3], i[6], i[7], i[8], i[9],
-                               d.f[0], (const float*)p[4], i[10], st);
+                               d.f[0], (const float*)p[4], i[10], (float*)p[5], st);
     case TCD_OP_SWIGLU_LN:  // p: gu, gamma, beta, y; i: rows, H, Hp, gated; f: eps
       return swiglu_ln_launch(p[0], (const float*)p[1], (const float*)p[2], p[3], i[0], i[1], i[2], d.f[0], i[3], st);
     case TCD_OP_SOFTMAX:  // p: x, y; i: rows, C, ldx, ldy
       return softmax_rows_launch((const float*)p[0], i[2], (float*)p[1], i[3], i[0], i[1], st);
     case TCD_OP_HEAD_GEMV:  // p: x, w, bias, out; i: B, K, NC, ld
       return head_gemv_launch(p[0], p[1], (const float*)p[2], (float*)p[3], i[0], i[1], i[2], i[3], st);
-    case TCD_OP_ROW_STATS:  // p: x, stats; i: rows, H, Hp; f: eps
-      return row_stats_launch(p[0], (float*)p[1], i[0], i[1], i[2], d.f[0], st);
+    case TCD_OP_ROW_STATS:  // p: x, stats; i: rows, H, Hp, parts (0: (mean, rstd); > 0: (sum, sumsq) in slot 0 of `parts`); f: eps
+      return row_stats_launch(p[0], (float*)p[1], i[0], i[1], i[2], d.f[0], i[3], st);
     case TCD_OP_TAKE:  // p: src, idx, out; i: N, k, ld
       return take_f32_launch((const float*)p[0], i[2], (const int*)p[1], (float*)p[2], i[0], i[1], st);
   }
@@ -197,6 +197,13 @@ tcd_status tcd_program_add_conv(tcd_program* p, const tcd_conv_desc* c) {
     if (rc) return rc;
     d.ln_stats = c->ln_stats;
     d.ln_colsum = (const float*)dc;
+    d.ln_parts = c->ln_parts; d.ln_count = c->ln_count; d.ln_eps = c->ln_eps;
+    TCD_REQUIRE(c->ln_parts >= 0 && c->ln_parts <= 64 && c->ln_parts % 2 == 0 && (c->ln_parts == 0 || c->ln_count > 0),
+                "add_conv: ln_parts %d (even, <= 64)", c->ln_parts);
+  }
+  if (c->stats_out) {
+    TCD_REQUIRE(c->stats_parts > 0 && c->stats_slot0 >= 0, "add_conv: stats_out without stats_parts");
+    d.stats_out = c->stats_out; d.stats_parts = c->stats_parts; d.stats_slot0 = c->stats_slot0;
   }
   d.out_f32 = c->out_f32; d.out_ld = c->out_ld; d.out_col = c->out_col; d.rows_per_img = c->rows_per_img;
   d.row_off = c->row_off;

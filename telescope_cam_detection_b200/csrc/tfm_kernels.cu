@@ -300,7 +300,7 @@ int mha_launch(const void* q, int ldq, int qoff, const void* k, int ldk, int kof
   // self-attention over <= 640 tokens runs on the tcgen05 kernel (fa_umma.cu; head_dim 32 zero-padded to 64 there);
   // TCD_MHA_UMMA=0 and cross-attention shapes keep the warp-level kernel below
   if (Tq == Tk && fa64_umma_eligible(Tk))
-    return fa64_umma_launch(q, ldq, qoff, k, ldk, koff, v, ldv, voff, out, ldo, N, Tk, heads, 32, scale, nullptr, 0, st);
+    return fa64_umma_launch(q, ldq, qoff, k, ldk, koff, v, ldv, voff, out, ldo, N, Tk, heads, 32, scale, nullptr, 0, nullptr, st);
   const int Tkp = (Tk + 15) & ~15;
   const size_t smem = ((size_t)Tkp * kMhaKStride + (size_t)32 * (Tkp + 8)) * 2;
   TCD_REQUIRE(smem <= 200 * 1024, "mha: %d keys do not fit shared memory", Tk);

@@ -62,15 +62,16 @@ int crop_patch_launch(const uint8_t* frame, long long stride, const int* boxes_d
 // x[n,0,:] = pos[0,:] (class token already folded in); x[n,1+t,:] = emb[n,t,:] + pos[1+t,:];  pos f32 [T,D]
 int vit_assemble_launch(const void* emb, const float* pos, void* x, int N, int T, int D, cudaStream_t st);
 // softmax(rot(q) rot(k)^T * scale) v, head_dim 64; rope f32 [(T-prefix), 32, 2] (cos, sin) or NULL (no rotation)
+// stats_out (optional, tcgen05 kernel only): [N*T][heads*2][2] partial (sum, sum of squares) of every output row
 int mha64_rope_launch(const void* q, int ldq, int qoff, const void* k, int ldk, int koff, const void* v, int ldv,
                       int voff, void* out, int ldo, int N, int T, int heads, float scale, const float* rope,
-                      int prefix, cudaStream_t st);
+                      int prefix, float* stats_out, cudaStream_t st);
 // the same attention on tcgen05 / TMEM (fa_umma.cu) for T <= 640 tokens; mha64_rope_launch takes it when eligible
 bool fa64_umma_eligible(int T);
 // head_dim 64, or 32 (rows zero-padded to 64 channels in shared memory; rope must be NULL)
 int fa64_umma_launch(const void* q, int ldq, int qoff, const void* k, int ldk, int koff, const void* v, int ldv,
                      int voff, void* out, int ldo, int N, int T, int heads, int head_dim, float scale,
-                     const float* rope, int prefix, cudaStream_t st);
+                     const float* rope, int prefix, float* stats_out, cudaStream_t st);
 // y[r,0:H) = LayerNorm(silu(gu[r,0:H)) * gu[r,Hp:Hp+H)); gu bf16 [rows, 2*Hp], y bf16 [rows, Hp] (pad zero);
 // gamma / beta: Hp floats each (16-byte aligned, padding ignored), or both NULL (no affine part)
 // gated != 0: gu is already silu(g) * u, bf16 [rows, Hp] (written by the gated GEMM epilogue): LayerNorm only
@@ -81,7 +82,8 @@ int head_gemv_launch(const void* x, const void* w, const float* bias, float* out
                      cudaStream_t st);
 // stats[r] = (mean, 1/sqrt(var + eps)) over the first H columns of bf16 row r (row stride Hp, Hp <= 3072): the
 // LayerNorm statistics for a consumer that normalises in its own epilogue (gemm_pair.cuh)
-int row_stats_launch(const void* x, float* stats, int rows, int H, int Hp, float eps, cudaStream_t st);
+// parts > 0: stats[r][0] = (sum, sum of squares), stats[r][1 .. parts) = 0 -- the partial-sum format the producers write
+int row_stats_launch(const void* x, float* stats, int rows, int H, int Hp, float eps, int parts, cudaStream_t st);
 int softmax_rows_launch(const float* x, int ldx, float* y, int ldy, int rows, int C, cudaStream_t st);
 // out[n,i] = src[n*ld + idx[n*k+i]]
 int take_f32_launch(const float* src, int ld, const int* idx, float* out, int N, int k, cudaStream_t st);

@@ -344,9 +344,10 @@ mha64_rope_kernel(const __nv_bfloat16* __restrict__ q, int ldq, int qoff, const 
 
 int mha64_rope_launch(const void* q, int ldq, int qoff, const void* k, int ldk, int koff, const void* v, int ldv,
                       int voff, void* out, int ldo, int N, int T, int heads, float scale, const float* rope,
-                      int prefix, cudaStream_t st) {
+                      int prefix, float* stats_out, cudaStream_t st) {
   if (fa64_umma_eligible(T))
-    return fa64_umma_launch(q, ldq, qoff, k, ldk, koff, v, ldv, voff, out, ldo, N, T, heads, 64, scale, rope, prefix, st);
+    return fa64_umma_launch(q, ldq, qoff, k, ldk, koff, v, ldv, voff, out, ldo, N, T, heads, 64, scale, rope, prefix, stats_out, st);
+  TCD_REQUIRE(stats_out == nullptr, "mha64: row statistics are written by the tcgen05 kernel only (T %d)", T);
   const int Tkp = (T + 15) & ~15;
   const size_t smem = ((size_t)Tkp * kMha64KStride + (size_t)64 * (Tkp + 8)) * 2;
   TCD_REQUIRE(smem <= 220 * 1024, "mha64: %d tokens do not fit shared memory", T);
@@ -534,7 +535,7 @@ ln_wide_kernel(const uint4* __restrict__ h, const float* __restrict__ gamma, con
 // tensor (151 MB per LayerNorm, 203 MB for the MLP's hidden one at 64 crops) is never written or re-read.
 template <int CH>      // 8-channel chunks per lane: 4 covers rows of <= 1024 columns (40 registers, full occupancy), 12 up to 3072
 __global__ void __launch_bounds__(256, CH <= 4 ? 6 : 2)
-row_stats_kernel(const uint4* __restrict__ h, float2* __restrict__ stats, int rows, int H, int Hp8, float eps) {
+row_stats_kernel(const uint4* __restrict__ h, float2* __restrict__ stats, int rows, int H, int Hp8, float eps, int parts) {
   const int row = (blockIdx.x * 256 + threadIdx.x) >> 5;
   const int lane = threadIdx.x & 31;
   if (row >= rows) return;
@@ -577,14 +578,18 @@ row_stats_kernel(const uint4* __restrict__ h, float2* __restrict__ stats, int ro
 #pragma unroll
   for (int off = 16; off > 0; off >>= 1) var += __shfl_xor_sync(0xffffffffu, var, off);
   var -= (float)(CH * 32 * 8 - H) * mean * mean;     // the zeroed slots contributed (0 - mean)^2 each
-  if (lane == 0) stats[row] = make_float2(mean, rsqrtf(fmaxf(var, 0.f) / (float)H + eps));
+  if (parts > 0) {      // partial-sum format: slot 0 = (sum, sum of squares) = (sum, var_sum + H mean^2), the other slots zero
+    if (lane < parts) stats[(size_t)row * parts + lane] = lane == 0 ? make_float2(sum, fmaxf(var, 0.f) + (float)H * mean * mean) : make_float2(0.f, 0.f);
+  } else if (lane == 0) {
+    stats[row] = make_float2(mean, rsqrtf(fmaxf(var, 0.f) / (float)H + eps));
+  }
 }
-int row_stats_launch(const void* x, float* stats, int rows, int H, int Hp, float eps, cudaStream_t st) {
-  TCD_REQUIRE(Hp % 8 == 0 && Hp <= kWideChunks * 32 * 8 && H >= 1 && H <= Hp, "row_stats: H %d Hp %d", H, Hp);
+int row_stats_launch(const void* x, float* stats, int rows, int H, int Hp, float eps, int parts, cudaStream_t st) {
+  TCD_REQUIRE(Hp % 8 == 0 && Hp <= kWideChunks * 32 * 8 && H >= 1 && H <= Hp && parts >= 0 && parts <= 32, "row_stats: H %d Hp %d parts %d", H, Hp, parts);
   if (Hp <= 4 * 32 * 8)
-    row_stats_kernel<4><<<cdiv(rows, 8), 256, 0, st>>>((const uint4*)x, (float2*)stats, rows, H, Hp / 8, eps);
+    row_stats_kernel<4><<<cdiv(rows, 8), 256, 0, st>>>((const uint4*)x, (float2*)stats, rows, H, Hp / 8, eps, parts);
   else
-    row_stats_kernel<kWideChunks><<<cdiv(rows, 8), 256, 0, st>>>((const uint4*)x, (float2*)stats, rows, H, Hp / 8, eps);
+    row_stats_kernel<kWideChunks><<<cdiv(rows, 8), 256, 0, st>>>((const uint4*)x, (float2*)stats, rows, H, Hp / 8, eps, parts);
   VIT_LAUNCH_OK("row_stats");
 }
 

@@ -76,7 +76,7 @@ class Eva02Engine:
     """
 
     def __init__(self, sd, batch, img_size=336, ref_grid=16, ln_eps=1e-6, top_k=5, device=0, keep_taps=False, fold_ln=True,
-                 ln_in_gemm=True):
+                 ln_in_gemm=True, ln_from_producers=True):
         self.sd = sd
         self.B, self.S = int(batch), int(img_size)
         pw = self._g("patch_embed.proj.weight")
@@ -109,6 +109,7 @@ class Eva02Engine:
         # Where every Linear behind a LayerNorm is a CTA-pair GEMM (many crops), the LayerNorm is applied in that GEMM's
         # epilogue from per-row (mean, 1/std): the normalised tensors are never written.  ln_in_gemm=False: A/B, parity.
         self.ln_in_gemm_wanted = bool(ln_in_gemm)
+        self.ln_from_producers_wanted = bool(ln_from_producers)
         self._build()
         self.sd = None
 
@@ -135,7 +136,7 @@ class Eva02Engine:
         P.op("tap." + name, "gather", [act.ptr, self._tap_idx, keep.ptr], [1, rows, rows, act.C])
         self.taps[name] = keep
 
-    def _linear(self, name, x, w, b, y, resid=None, step=256, ln_stats=None):
+    def _linear(self, name, x, w, b, y, resid=None, step=256, ln_stats=None, ln_parts=0, ln_count=0, stats_out=None, stats_parts=0):
         """y[:, :cout] = x @ w.T + b (+ resid), split along cout so that each launch stays within the engine's bias
         staging limit.  x, y, resid: flat token views [1,1,rows,C].  ln_stats: x is un-normalised and the launch applies
         the LayerNorm whose (mean, 1/std) per row sit at that device address (w, b already hold its affine part)."""
@@ -146,7 +147,20 @@ class Eva02Engine:
         for c0, cw in _chunks(cout, step):
             self.prog.conv(name if cout == cw else "%s[%d:%d]" % (name, c0, c0 + cw), x, w[c0:c0 + cw], b[c0:c0 + cw],
                            act=ACT_NONE, y=y, y_coff=c0, resid=resid, r_coff=c0 if resid is not None else 0,
-                           ln_stats=ln_stats, ln_colsum=None if cs is None else cs[c0:c0 + cw])
+                           ln_stats=ln_stats, ln_colsum=None if cs is None else cs[c0:c0 + cw], ln_parts=ln_parts, ln_count=ln_count,
+                           ln_eps=self.ln_eps, stats_out=stats_out, stats_parts=stats_parts, stats_slot0=c0 // 256)
+
+    def _qkv_weights(self, p, zeros):
+        """Fused [q; k; v] weight and bias of block prefix p (fused qkv + q_bias / v_bias, or separate projections)."""
+        if self._has(p + "attn.qkv.weight"):
+            wqkv = self._g(p + "attn.qkv.weight")
+            bq = self._g(p + "attn.q_bias") if self._has(p + "attn.q_bias") else zeros
+            bv = self._g(p + "attn.v_bias") if self._has(p + "attn.v_bias") else zeros
+            return wqkv, np.concatenate([bq, zeros, bv])
+        wqkv = np.concatenate([self._g(p + "attn.q_proj.weight"), self._g(p + "attn.k_proj.weight"),
+                               self._g(p + "attn.v_proj.weight")], 0)
+        bk = self._g(p + "attn.k_proj.bias") if self._has(p + "attn.k_proj.bias") else zeros
+        return wqkv, np.concatenate([self._g(p + "attn.q_proj.bias"), bk, self._g(p + "attn.v_proj.bias")])
 
     @staticmethod
     def _pad_rows(a, n):
@@ -218,8 +232,16 @@ class Eva02Engine:
                                                         for _, cw in _chunks(cout, 256))
         self.ln_in_gemm = (self.fold_ln and self.fuse_glu and self.ln_in_gemm_wanted and pair_ok(D, 3 * D) and pair_ok(D, D)
                            and pair_ok(Hp, D))
-        self._stats = [P.f32(rows * 2), P.f32(rows * 2)] if self.ln_in_gemm else []
+        # ... and where, additionally, every LayerNorm INPUT is written by a CTA-pair GEMM or the tcgen05 attention kernel,
+        # those producers write per-tile partial (sum, sum of squares) of their rows and no statistics kernel runs at all
+        self.ln_from_producers = self.ln_in_gemm and self.ln_from_producers_wanted and D % 256 == 0 and self.T <= 640
+        self._stats = [P.f32(rows * 2), P.f32(rows * 2)] if self.ln_in_gemm and not self.ln_from_producers else []
         self._stats_i = 0
+        if self.ln_from_producers:
+            # partial slots per row, rounded up to even (the consumers read them two per 16-byte load; a slot no producer
+            # writes stays at the zero the buffer was allocated with)
+            px, pa, ph = (D // 256 + 1) & ~1, self.heads * 2, (Hp // 128 + 1) & ~1
+            sx, sx2, satt, sh = P.f32(rows * px * 2), P.f32(rows * px * 2), P.f32(rows * pa * 2), P.f32(rows * ph * 2)
         j = np.arange(Hp)
         self._glu_g = (j // 128) * 256 + ((j % 128) // 32) * 64 + (j % 32)    # GEMM column of the gate of hidden j
         gu = Act(P.alloc(rows * Hp * 2), 1, 1, rows, Hp) if self.fuse_glu else Act(P.alloc(rows * 2 * Hp * 2), 1, 1, rows, 2 * Hp)
@@ -229,17 +251,42 @@ class Eva02Engine:
         for i in range(self.depth):
             p = "blocks.%d." % i
             n = "b%d." % i
+            if self.ln_from_producers:
+                # no normalisation or statistics kernel in the block: producers write partial row statistics, consumers
+                # normalise in their epilogues
+                if i == 0:
+                    P.op("tokens.stats", "row_stats", [x.ptr, sx], [rows, D, D, px], [self.ln_eps])
+                wqkv, bqkv = self._qkv_weights(p, zeros)
+                wqkv, bqkv = self._fold(wqkv, bqkv, p + "norm1")
+                self._linear(n + "qkv", x, wqkv, bqkv, qkv, ln_stats=sx, ln_parts=px, ln_count=D)
+                has_an = self._has(p + "attn.norm.weight")
+                P.op(n + "mha", "mha_rope", [qkv.ptr, qkv.ptr, qkv.ptr, att.ptr, rope, satt if has_an else 0],
+                     [3 * D, 0, 3 * D, D, 3 * D, 2 * D, D, B, T, self.heads, 1], [_HEAD_DIM ** -0.5])
+                wp, bp = self._g(p + "attn.proj.weight"), self._g(p + "attn.proj.bias")
+                if has_an:
+                    wp, bp = self._fold(wp, bp, p + "attn.norm")
+                    self._linear(n + "proj", att, wp, bp, x2, resid=x, ln_stats=satt, ln_parts=pa, ln_count=D, stats_out=sx2, stats_parts=px)
+                else:
+                    self._linear(n + "proj", att, wp, bp, x2, resid=x, stats_out=sx2, stats_parts=px)
+                wg, bg = self._fold(self._g(p + "mlp.fc1_g.weight"), self._g(p + "mlp.fc1_g.bias"), p + "norm2")
+                wx, bx = self._fold(self._g(p + "mlp.fc1_x.weight"), self._g(p + "mlp.fc1_x.bias"), p + "norm2")
+                w1 = np.zeros((2 * Hp, D), np.float32)
+                b1 = np.zeros(2 * Hp, np.float32)
+                w1[self._glu_g], w1[self._glu_g + 32] = self._pad_rows(wg, Hp), self._pad_rows(wx, Hp)
+                b1[self._glu_g], b1[self._glu_g + 32] = self._pad_rows(bg, Hp), self._pad_rows(bx, Hp)
+                cs1 = _colsum_bf16(w1)
+                for c0, cw in _chunks(2 * Hp, 256):
+                    P.conv("%sfc1[%d:%d]" % (n, c0, c0 + cw), x2, w1[c0:c0 + cw], b1[c0:c0 + cw], act=ACT_GLU, y=gu, y_coff=c0 // 2,
+                           ln_stats=sx2, ln_colsum=cs1[c0:c0 + cw], ln_parts=px, ln_count=D, ln_eps=self.ln_eps,
+                           stats_out=sh, stats_parts=ph, stats_slot0=c0 // 256)
+                w2 = np.zeros((D, Hp), np.float32)
+                wf2, bf2 = self._fold(self._g(p + "mlp.fc2.weight"), self._g(p + "mlp.fc2.bias"), p + "mlp.norm")
+                w2[:, :H] = wf2
+                self._linear(n + "fc2", gu, w2, bf2, x, resid=x2, ln_stats=sh, ln_parts=ph, ln_count=H, stats_out=sx, stats_parts=px)
+                self._tap("block%d" % i, x)
+                continue
             a_in, st = self._norm(n + "norm1", x, p + "norm1", yb, rows)
-            if self._has(p + "attn.qkv.weight"):
-                wqkv = self._g(p + "attn.qkv.weight")
-                bq = self._g(p + "attn.q_bias") if self._has(p + "attn.q_bias") else zeros
-                bv = self._g(p + "attn.v_bias") if self._has(p + "attn.v_bias") else zeros
-                bqkv = np.concatenate([bq, zeros, bv])
-            else:
-                wqkv = np.concatenate([self._g(p + "attn.q_proj.weight"), self._g(p + "attn.k_proj.weight"),
-                                       self._g(p + "attn.v_proj.weight")], 0)
-                bk = self._g(p + "attn.k_proj.bias") if self._has(p + "attn.k_proj.bias") else zeros
-                bqkv = np.concatenate([self._g(p + "attn.q_proj.bias"), bk, self._g(p + "attn.v_proj.bias")])
+            wqkv, bqkv = self._qkv_weights(p, zeros)
             wqkv, bqkv = self._fold(wqkv, bqkv, p + "norm1")
             self._linear(n + "qkv", a_in, wqkv, bqkv, qkv, ln_stats=st)
             P.op(n + "mha", "mha_rope", [qkv.ptr, qkv.ptr, qkv.ptr, att.ptr, rope],

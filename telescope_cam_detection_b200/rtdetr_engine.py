@@ -119,7 +119,8 @@ class Program:
         return self.alloc(n * 4)
 
     def conv(self, name, x, w, b, k=1, stride=1, act=ACT_NONE, y=None, y_coff=0, x_coff=0, resid=None,
-             r_coff=0, resid_pre=0, out_f32=None, out_ld=0, ln_stats=None, ln_colsum=None):
+             r_coff=0, resid_pre=0, out_f32=None, out_ld=0, ln_stats=None, ln_colsum=None, ln_parts=0, ln_count=0,
+             ln_eps=0.0, stats_out=None, stats_parts=0, stats_slot0=0):
         """w: [cout, cin, k, k] float32 (BN already folded), b: [cout]."""
         w = np.ascontiguousarray(w, np.float32).reshape(w.shape[0], -1, k, k)
         b = np.ascontiguousarray(b, np.float32)
@@ -138,6 +139,9 @@ class Program:
         if ln_stats is not None:       # LayerNorm applied in the consumer's epilogue (include/tcd.h tcd_conv_desc.ln_stats)
             cs = np.ascontiguousarray(ln_colsum, np.float32)
             d.ln_stats, d.ln_colsum_host = int(ln_stats), cs.ctypes.data
+            d.ln_parts, d.ln_count, d.ln_eps = int(ln_parts), int(ln_count), float(ln_eps)
+        if stats_out is not None:      # this launch's tiles also write the LayerNorm statistics of their rows
+            d.stats_out, d.stats_parts, d.stats_slot0 = int(stats_out), int(stats_parts), int(stats_slot0)
         check(self.lib.tcd_program_add_conv(self.handle, C.byref(d)), "tcd_program_add_conv(%s)" % name)
 
     def op(self, name, kind, ptrs, ints, floats=()):

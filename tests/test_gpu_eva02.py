@@ -337,9 +337,15 @@ def test_eva02_many_crops_pair_gemm_and_gated_mlp():
     sd = eva02.state_dict_numpy(eva02.make_model(cfg, 4))
     x = eva02.synthetic_input(cfg, 40, seed=5).numpy()
     eng = Eva02Engine(sd, batch=40, img_size=336, top_k=5)
-    assert eng.fuse_glu and eng.ln_in_gemm            # LayerNorms applied inside the consumer GEMMs' epilogues
+    # LayerNorms applied inside the consumer GEMMs' epilogues, their statistics written by the producers' epilogues
+    assert eng.fuse_glu and eng.ln_in_gemm and eng.ln_from_producers
     a = eng.forward(x)
     eng.close()
+    eng = Eva02Engine(sd, batch=40, img_size=336, top_k=5, ln_from_producers=False)   # statistics by row_stats kernels
+    assert eng.ln_in_gemm and not eng.ln_from_producers
+    c = eng.forward(x)
+    eng.close()
+    assert float(np.abs(a - c).max()) <= 0.08, float(np.abs(a - c).max())
     eng = Eva02Engine(sd, batch=40, img_size=336, top_k=5, ln_in_gemm=False)   # normalised rows written by LayerNorm kernels
     assert not eng.ln_in_gemm
     b = eng.forward(x)
