@@ -197,6 +197,19 @@ gemm_pair_kernel(const __grid_constant__ ConvMaps maps, const __grid_constant__ 
         }
       }
       float ps_out = 0.f, pss_out = 0.f;     // (sum, sum of squares) of this row's outputs in this tile (stats_out)
+      // Plain linears with a residual (proj, fc2): the row's 256 residual columns are requested NOW, before the wait for
+      // the accumulator, thirty-two 16-byte loads in flight -- the residual stream (75 MB) comes from HBM, and fetched
+      // inside the phases (first: four dependent loads per slab, then sixteen per phase) it paced proj: 580-700 TFLOP/s
+      // against 1 100-1 200 for the linears without one.
+      uint4 rres[ACT == 0 ? 32 : 1];
+      const bool use_res = ACT == 0 && p.resid != nullptr && valid;
+      if constexpr (ACT == 0) {
+        if (use_res) {
+          const uint4* rp = reinterpret_cast<const uint4*>(p.resid + (size_t)x * p.r_ctot + p.r_coff + c.n_tile * 256);
+#pragma unroll
+          for (int u = 0; u < 32; ++u) rres[u] = __ldg(rp + u);
+        }
+      }
       mbar_wait(&tmem_full_bar[acc], (uint32_t)(it >> 1) & 1u);
       tc_fence_after();
       const uint32_t taddr = tmem_base + (uint32_t)(acc * 256) + ((uint32_t)(q * 32) << 16);
@@ -213,18 +226,6 @@ gemm_pair_kernel(const __grid_constant__ ConvMaps maps, const __grid_constant__ 
           asm volatile("bar.sync 1, %0;" ::"n"(32 * kConvEpiWarps) : "memory");
         }
         uint8_t* stg = staging - (size_t)ph * 2 * 128 * 128;     // conv_finish_cols places column c0 in chunk c0 / 64
-        // Plain linears with a residual (proj, fc2): the row's 128 residual columns of this phase are fetched NOW,
-        // sixteen 16-byte loads in flight, instead of four dependent loads inside every slab (measured on proj,
-        // K = 1024: the epilogue took ~1 750 cycles per slab and paced the kernel: 704 TFLOP/s against 1 208 for qkv).
-        uint4 rres[ACT == 0 ? 16 : 1];
-        const bool use_res = ACT == 0 && p.resid != nullptr && valid;
-        if constexpr (ACT == 0) {
-          if (use_res) {
-            const uint4* rp = reinterpret_cast<const uint4*>(p.resid + (size_t)x * p.r_ctot + p.r_coff + c.n_tile * 256 + ph * 128);
-#pragma unroll
-            for (int u = 0; u < 16; ++u) rres[u] = __ldg(rp + u);
-          }
-        }
         auto finish_plain = [&](const uint32_t (&r)[32], int sl) {     // ACT == 0: bias (+ residual) -> bf16 -> staging
           const float4* b4 = reinterpret_cast<const float4*>(s_bias + c.n_tile * 256 + 32 * sl);
           const float4* c4 = reinterpret_cast<const float4*>(s_cs + c.n_tile * 256 + 32 * sl);
@@ -251,7 +252,7 @@ gemm_pair_kernel(const __grid_constant__ ConvMaps maps, const __grid_constant__ 
           if (use_res) {
 #pragma unroll
             for (int u = 0; u < 4; ++u) {
-              const uint4 q = rres[ACT == 0 ? (sl & 3) * 4 + u : 0];
+              const uint4 q = rres[ACT == 0 ? sl * 4 + u : 0];
               const uint32_t w[4] = {q.x, q.y, q.z, q.w};
 #pragma unroll
               for (int e = 0; e < 4; ++e) {
