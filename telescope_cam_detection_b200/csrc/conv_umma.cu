@@ -344,10 +344,11 @@ static int gemm_pair_plan_launch(const ConvPlan& plan, cudaStream_t stream) {
   ga.m_pairs = cdiv(plan.pair_m_tiles, 2);
   ga.n_tiles = plan.pair_n_tiles;
   ga.kchunks = plan.args.kchunks;
+  ga.flags = env_int("TCD_GEMM_PAIR_FLAGS", 7, 0);
   cudaLaunchConfig_t cfg;
   memset(&cfg, 0, sizeof(cfg));
   cfg.gridDim = plan.grid;
-  cfg.blockDim = dim3(kConvThreads, 1, 1);
+  cfg.blockDim = dim3(kGpThreads, 1, 1);
   cfg.dynamicSmemBytes = (size_t)plan.smem_bytes;
   cfg.stream = stream;
   cudaLaunchAttribute attr[2];
