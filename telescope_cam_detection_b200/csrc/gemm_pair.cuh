@@ -37,7 +37,7 @@ struct GemmPairArgs {
   int m_pairs;       // ceil(m_tiles / 2)
   int n_tiles;       // Cout / 256
   int kchunks;       // Cin / 64
-  int flags;         // TCD_GEMM_PAIR_FLAGS (default 7): 1 relaxed accumulator hand-back, 2 sixteen partial loads in flight, 4 residual by 32-byte loads
+  int flags;         // TCD_GEMM_PAIR_FLAGS (default 7): 1 relaxed accumulator hand-back, 2 sixteen partial loads in flight, 4 residual by 32-byte loads, 8 per-half staging barriers and stores
 };
 
 #if defined(__CUDACC__) && defined(TCD_CONV_KERNEL_IMPL)
@@ -76,7 +76,7 @@ gemm_pair_kernel(const __grid_constant__ ConvMaps maps, const __grid_constant__ 
   __shared__ __align__(16) float s_bias[kGpMaxCout];
   __shared__ __align__(16) float s_cs[kGpMaxCout];     // column sums of the weights (consumer-side LayerNorm), else unused
   __shared__ uint32_t tmem_base_s;
-  __shared__ float2 s_part[128][2];                   // the two epilogue threads of a row exchange their statistics
+  __shared__ float2 s_part[2][128][2];                // the two epilogue threads of a row exchange their statistics (per accumulator buffer)
 
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
   uint8_t* staging = smem + kGpStages * kGpStageBytes;
@@ -181,6 +181,12 @@ gemm_pair_kernel(const __grid_constant__ ConvMaps maps, const __grid_constant__ 
     const uint32_t empty_leader0 = mapa_u32(smem_u32(&tmem_empty_bar[0]), 0);
     const uint32_t empty_leader1 = mapa_u32(smem_u32(&tmem_empty_bar[1]), 0);
     constexpr int kPhases = ACT == 4 ? 1 : 2;          // the staging area holds 128 output columns (32 KiB)
+    // flags & 8: the two halves of the epilogue (sub 0 / sub 1) fill different 64-column chunks of the staging area, so each
+    // half syncs among its own four warps (named barriers 1 + sub) and stores its own chunk; they then drift apart and
+    // one half's store wait overlaps the other's arithmetic.  Otherwise all eight warps share barrier 1 and warp 2 stores.
+    const bool split = (ga.flags & 8) != 0;
+    const int bar_id = split ? 1 + sub : 1, bar_n = split ? 32 * kGpEpiWarps / 2 : 32 * kGpEpiWarps;
+    const bool issuer = lane == 0 && (split ? ((warp - 2) & 3) == 0 : warp == 2);
     for (int it = 0; it < n_mine; ++it) {
       const int acc = it & 1;
       const int w = cluster_id + it * n_clusters;
@@ -314,8 +320,8 @@ gemm_pair_kernel(const __grid_constant__ ConvMaps maps, const __grid_constant__ 
 #pragma unroll
       for (int ph = 0; ph < kPhases; ++ph) {
         if (it > 0 || ph > 0) {
-          if (warp == 2 && lane == 0) tma_store_wait_read();    // the previous stores have read the staging
-          asm volatile("bar.sync 1, %0;" ::"n"(32 * kGpEpiWarps) : "memory");
+          if (issuer) tma_store_wait_read();    // the previous stores have read the staging
+          asm volatile("bar.sync %0, %1;" ::"r"(bar_id), "r"(bar_n) : "memory");
         }
         uint8_t* stg = staging - (size_t)ph * 2 * 128 * 128;     // conv_finish_cols places column c0 in chunk c0 / 64
         if constexpr (ACT == 4) {
@@ -374,26 +380,26 @@ gemm_pair_kernel(const __grid_constant__ ConvMaps maps, const __grid_constant__ 
           else conv_finish_cols<32, 0, ACT, 0>(p, rb, 32 * (sl + 1), s_bias, row, valid, c, 0, x, stg);
         }
         fence_proxy_async_smem();
-        asm volatile("bar.sync 1, %0;" ::"n"(32 * kGpEpiWarps) : "memory");
-        if (warp == 2 && lane == 0) {
+        asm volatile("bar.sync %0, %1;" ::"r"(bar_id), "r"(bar_n) : "memory");
+        if (issuer) {
           constexpr int kOutCols = ACT == 4 ? 128 : 256;     // the gated form writes half as many columns
-          for (int ch = 0; ch < 2; ++ch)
+          for (int ch = split ? sub : 0; ch < (split ? sub + 1 : 2); ++ch)
             tma_store_4d(&maps.o, staging + (size_t)ch * 128 * 128, p.cout_off + c.n_tile * kOutCols + (ph * 2 + ch) * 64, c.x0, 0, 0);
           tma_store_commit();
         }
       }
       if (p.stats_out != nullptr) {
         // the two threads of a row add their halves through shared memory; sub 0 writes the tile's partial
-        s_part[row][sub] = make_float2(ps_out, pss_out);
-        asm volatile("bar.sync 1, %0;" ::"n"(32 * kGpEpiWarps) : "memory");
+        s_part[acc][row][sub] = make_float2(ps_out, pss_out);
+        asm volatile("bar.sync 3, %0;" ::"n"(32 * kGpEpiWarps) : "memory");
         if (sub == 0 && valid) {
-          const float2 o2 = s_part[row][1];
+          const float2 o2 = s_part[acc][row][1];
           reinterpret_cast<float2*>(p.stats_out)[(size_t)x * p.stats_parts + p.stats_slot0 + c.n_tile] =
               make_float2(ps_out + o2.x, pss_out + o2.y);
         }
       }
     }
-    if (warp == 2 && lane == 0) tma_store_wait_read();
+    if (issuer) tma_store_wait_read();
   }
   tc_fence_before();
   __syncthreads();
