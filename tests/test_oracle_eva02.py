@@ -114,3 +114,45 @@ def test_checkpoint_readers(tmp_path):
         got = SpeciesClassifier._read_checkpoint(str(tmp_path / name))
         assert set(got) == set(sd)
         assert np.array_equal(np.asarray(got["head.weight"]), sd["head.weight"].numpy())
+
+
+def test_layernorm_folded_into_the_consumer_gemm_is_the_same_function():
+    """The engine never materialises LayerNorm(x): it folds (gamma, beta) into the consumer's (W, b) (`_fold`) and the
+    GEMM epilogue applies  y = rstd * (x W'^T - mean * colsum(W')) + b'  from per-row (sum, sum of squares) partials.
+    In fp32 / float64 that must equal Linear(LayerNorm(x)) (timm's order, oracle/eva02.py blocks), partials in any split."""
+    from telescope_cam_detection_b200 import eva02_engine as E
+
+    rng = np.random.default_rng(5)
+    rows, d, cout, eps = 37, 256, 96, 1e-6
+    x = (rng.standard_normal((rows, d)) * 1.7 + 0.4).astype(np.float32)
+    g = rng.uniform(0.5, 1.5, d).astype(np.float32)
+    be = (rng.standard_normal(d) * 0.2).astype(np.float32)
+    w = (rng.standard_normal((cout, d)) / np.sqrt(d)).astype(np.float32)
+    b = (rng.standard_normal(cout) * 0.1).astype(np.float32)
+
+    x64 = x.astype(np.float64)
+    mu, var = x64.mean(1, keepdims=True), x64.var(1, keepdims=True)
+    want = ((x64 - mu) / np.sqrt(var + eps) * g + be) @ w.astype(np.float64).T + b
+
+    class Holder:                       # `_fold` reads the LayerNorm parameters through `_g`
+        fold_ln = True
+
+        def _g(self, name):
+            return {"n.weight": g, "n.bias": be}[name]
+
+    w2, b2 = E.Eva02Engine._fold(Holder(), w, b, "n")
+    # statistics the way the producers write them: (sum, sum of squares) partials over column slices, summed in order
+    parts = 4
+    sl = np.array_split(np.arange(d), parts)
+    su = sum(x64[:, s].sum(1) for s in sl)
+    sq = sum((x64[:, s] ** 2).sum(1) for s in sl)
+    mean = su / d
+    rstd = 1.0 / np.sqrt(np.maximum(sq / d - mean * mean, 0.0) + eps)
+    colsum = w2.astype(np.float64).sum(1)
+    got = rstd[:, None] * (x64 @ w2.astype(np.float64).T - mean[:, None] * colsum[None]) + b2
+    assert np.abs(got - want).max() < 2e-5
+    # the column sums the engine uploads are those of the bf16-ROUNDED weights (what the tensor core multiplies by)
+    cs = E._colsum_bf16(w2)
+    w2_bf16 = (E.to_bf16_bits(w2).astype(np.uint32) << 16).view(np.float32)
+    assert np.allclose(cs, w2_bf16.astype(np.float64).sum(1), rtol=0, atol=1e-5)
+    assert np.abs(cs - colsum).max() < 0.05          # near the fp32 sums, not equal: rounding of 256 weights per row
