@@ -156,3 +156,69 @@ def test_layernorm_folded_into_the_consumer_gemm_is_the_same_function():
     w2_bf16 = (E.to_bf16_bits(w2).astype(np.uint32) << 16).view(np.float32)
     assert np.allclose(cs, w2_bf16.astype(np.float64).sum(1), rtol=0, atol=1e-5)
     assert np.abs(cs - colsum).max() < 0.05          # near the fp32 sums, not equal: rounding of 256 weights per row
+
+
+def test_program_buckets_and_replay_chunking_with_a_stub_engine(monkeypatch):
+    """Host logic of the native Stage 2 without a GPU: the smallest program that holds n crops is chosen (built once),
+    more than max_batch crops run as several replays whose rows come back in crop order, close() closes every program."""
+    from telescope_cam_detection_b200 import eva02_engine
+    from telescope_cam_detection_b200.species_classifier import SpeciesClassifier
+
+    built, closed = [], []
+
+    class Stub:
+        def __init__(self, sd, batch, img_size, top_k, device):
+            self.batch, self.top_k = batch, top_k
+            built.append(batch)
+
+        def close(self):
+            closed.append(self.batch)
+
+        def patchify_device(self, ptr, n):
+            assert n <= self.batch
+            self.n, self.tag = n, ptr
+
+        def run(self):
+            pass
+
+        def sync(self):
+            pass
+
+        def read_topk(self, n):
+            p = np.tile(np.linspace(1.0, 0.1, self.top_k, dtype=np.float32), (n, 1))
+            i = np.tile(np.arange(self.top_k, dtype=np.int32), (n, 1)) + 1000 * self.tag
+            return p, i
+
+    monkeypatch.setattr(eva02_engine, "Eva02Engine", Stub)
+    sc = SpeciesClassifier.__new__(SpeciesClassifier)
+    sc.batch_buckets, sc.max_batch, sc.input_size, sc._dev_idx, sc._sd = (4, 16), 64, 336, 0, {}
+    sc.engine = Stub({}, 64, 336, 32, 0)
+    sc._engines = {64: sc.engine}
+    sizes = [sc._engine_for(n).batch for n in (1, 4, 5, 16, 17, 64)]
+    assert sizes == [4, 4, 16, 16, 64, 64]
+    assert built == [64, 4, 16]                       # every size built once
+    assert sc._engine_for(3) is sc._engine_for(2)
+
+    class Part:                                       # what `_topk` needs of a CUDA tensor
+        def __init__(self, n, s0=0):
+            self.shape, self.s0, self.device = (n, 3, 336, 336), s0, "cpu"
+
+        def contiguous(self):
+            return self
+
+        def float(self):
+            return self
+
+        def __getitem__(self, sl):
+            return Part(min(sl.stop, self.shape[0]) - sl.start, sl.start)
+
+        def data_ptr(self):
+            return self.s0
+
+    import torch
+    monkeypatch.setattr(torch.cuda, "current_stream", lambda dev=None: type("S", (), {"synchronize": lambda self: None})())
+    p, i = sc._topk(Part(64 + 64 + 5), top_k=5)      # 64 + 64 + 5 crops -> programs 64, 64, 16
+    assert p.shape == (133, 5) and i.shape == (133, 5)
+    assert (i[:64, 0] == 0).all() and (i[64:128, 0] == 64000).all() and (i[128:, 0] == 128000).all()
+    sc.close()
+    assert sorted(closed) == [4, 16, 64] and sc.engine is None and sc._engines == {}
